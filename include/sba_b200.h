@@ -1,0 +1,318 @@
+/*
+ * sba_b200.h -- C ABI of the B200-native bundle-adjustment hot path.
+ *
+ * This is the drop-in boundary for the path the reference runs inside
+ *   BundleAdjuster::Solve            /root/reference/src/optim/bundle_adjustment.cc:258-320
+ * i.e. what the reference hands to Ceres: a set of per-observation reprojection
+ * residual blocks (src/base/cost_functions.h:44-152) over pose / intrinsics /
+ * point parameter blocks, manifolds (src/base/cost_functions.h:270-287), a loss
+ * (src/optim/bundle_adjustment.cc:53-68) and `ceres::Solve`
+ * (src/optim/bundle_adjustment.cc:306).
+ *
+ * The host side (the C++ shim in semantic-bundle-adjustment-colmap_b200/shim/,
+ * mirroring BundleAdjuster / BundleAdjustmentConfig / BundleAdjustmentOptions)
+ * flattens a Reconstruction in the reference's residual order
+ * (src/optim/bundle_adjustment.cc:326-478) into the plain arrays below and calls
+ * these entry points.  Plain pointers and sizes only; no torch / Eigen / Ceres
+ * types cross this boundary.
+ *
+ * All functions return 0 on success and a non-zero sba_status otherwise; they
+ * never abort.  sba_last_error() returns a thread-local message for the last
+ * failure.  There is NO CPU fallback: every compute entry point fails with
+ * SBA_ERR_NO_DEVICE when no CUDA device is usable.
+ */
+#ifndef SBA_B200_H_
+#define SBA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SBA_MAX_CAMERA_PARAMS 12 /* FULL_OPENCV / THIN_PRISM_FISHEYE, camera_models.h:280,349 */
+#define SBA_POSE_TANGENT_DIM 6   /* quaternion manifold (3) + tvec (3) */
+
+/* Camera model ids == CameraModel::kModelId, src/base/camera_models.h:189-349 */
+enum sba_camera_model {
+  SBA_SIMPLE_PINHOLE = 0,
+  SBA_PINHOLE = 1,
+  SBA_SIMPLE_RADIAL = 2,
+  SBA_RADIAL = 3,
+  SBA_OPENCV = 4,
+  SBA_OPENCV_FISHEYE = 5,
+  SBA_FULL_OPENCV = 6,
+  SBA_FOV = 7,
+  SBA_SIMPLE_RADIAL_FISHEYE = 8,
+  SBA_RADIAL_FISHEYE = 9,
+  SBA_THIN_PRISM_FISHEYE = 10,
+  SBA_NUM_CAMERA_MODELS = 11
+};
+
+/* BundleAdjustmentOptions::LossFunctionType, src/optim/bundle_adjustment.h:51 */
+enum sba_loss_type { SBA_LOSS_TRIVIAL = 0, SBA_LOSS_SOFT_L1 = 1, SBA_LOSS_CAUCHY = 2 };
+
+/* Linear solver policy of BundleAdjuster::Solve, src/optim/bundle_adjustment.cc:271-286.
+ * SPARSE_SCHUR sizes run the same device dense Cholesky as DENSE_SCHUR. */
+enum sba_linear_solver {
+  SBA_SOLVER_AUTO = -1, /* reference policy from num_config_images: <=50 dense, <=1000 sparse, else iterative */
+  SBA_DENSE_SCHUR = 0,
+  SBA_SPARSE_SCHUR = 1,
+  SBA_ITERATIVE_SCHUR = 2
+};
+
+enum sba_status {
+  SBA_OK = 0,
+  SBA_ERR_INVALID_ARGUMENT = 1,
+  SBA_ERR_NO_DEVICE = 2,
+  SBA_ERR_CUDA = 3,
+  SBA_ERR_UNKNOWN_CAMERA_MODEL = 4, /* std::domain_error in the reference, camera_models.h:140 */
+  SBA_ERR_EMPTY_PROBLEM = 5,        /* Solve() returns false, bundle_adjustment.cc:267-269 */
+  SBA_ERR_ALREADY_SOLVED = 6,       /* CHECK(!problem_), bundle_adjustment.cc:260 */
+  SBA_ERR_COMM = 7,
+  SBA_ERR_INTERNAL = 8
+};
+
+/* ceres::TerminationType values the reference prints (bundle_adjustment.cc:1142-1196) */
+enum sba_termination {
+  SBA_CONVERGENCE = 0,
+  SBA_NO_CONVERGENCE = 1,
+  SBA_FAILURE = 2,
+  SBA_USER_SUCCESS = 3,
+  SBA_USER_FAILURE = 4
+};
+
+/*
+ * Flattened problem.  Everything is indexed densely; ids of the Reconstruction
+ * are mapped by the shim.  Observation k is residual block k of the reference
+ * (AddImageToProblem / AddPointToProblem order, bundle_adjustment.cc:348-478).
+ *
+ *  images   : qvec (w,x,y,z) and tvec as in Image::Qvec()/Tvec() (src/base/image.h:229-230)
+ *  cameras  : params as in Camera::Params() padded to SBA_MAX_CAMERA_PARAMS per camera
+ *  points   : Point3D::XYZ()
+ *
+ * Constness (what the reference expresses through SetParameterBlockConstant /
+ * SubsetManifold, bundle_adjustment.cc:417-425, 480-530):
+ *  image_pose_constant[i]      != 0 : constant-pose cost function (cost_functions.h:90-152)
+ *  image_tvec_constant_mask[i] bit k: tvec[k] held constant (SetConstantTvec)
+ *  camera_param_constant_mask[c] bit k: params[k] held constant; all params
+ *                                 constant == SetParameterBlockConstant
+ *  point_constant[p]           != 0 : point block constant
+ */
+typedef struct sba_problem_desc {
+  int32_t num_images;
+  int32_t num_cameras;
+  int32_t num_points;
+  int64_t num_observations;
+
+  const double* image_qvec;                /* [num_images*4] */
+  const double* image_tvec;                /* [num_images*3] */
+  const int32_t* image_camera;             /* [num_images]   index into cameras */
+  const uint8_t* image_pose_constant;      /* [num_images]   */
+  const uint8_t* image_tvec_constant_mask; /* [num_images]   */
+
+  const int32_t* camera_model;                /* [num_cameras] sba_camera_model */
+  const double* camera_params;                /* [num_cameras*SBA_MAX_CAMERA_PARAMS] */
+  const uint16_t* camera_param_constant_mask; /* [num_cameras] */
+
+  const double* points;          /* [num_points*3] */
+  const uint8_t* point_constant; /* [num_points]   */
+
+  const int32_t* obs_image; /* [num_observations] */
+  const int32_t* obs_point; /* [num_observations] */
+  const double* obs_xy;     /* [num_observations*2] Point2D::XY() */
+
+  /* ---- extension X1 (not in the reference) ----
+   * Optional per-image semantic maps sampled bilinearly at the projection
+   * (convention of Bitmap::InterpolateBilinear, src/util/bitmap.cc:238-269).
+   * NULL / 0 disables the third residual row. */
+  const float* sem_maps;         /* [num_images*sem_height*sem_width] row-major */
+  int32_t sem_height;
+  int32_t sem_width;
+  double sem_weight;             /* residual = sem_weight * map_img(x, y) */
+
+  /* ---- sharding (multi-GPU) ----
+   * A shard holds ALL images/cameras and a subset of points with all their
+   * observations.  For an unsharded problem: shard_rank=0, shard_count=1. */
+  int32_t shard_rank;
+  int32_t shard_count;
+  int64_t global_num_observations; /* 0 == num_observations */
+} sba_problem_desc;
+
+/* Subset of ceres::Solver::Options the reference sets or relies on
+ * (src/optim/bundle_adjustment.h:78-93; Ceres 2.1.0 defaults otherwise). */
+typedef struct sba_solver_options {
+  int32_t linear_solver_type;    /* sba_linear_solver */
+  int32_t num_config_images;     /* config_.NumImages() for SBA_SOLVER_AUTO; 0 == desc.num_images */
+  int32_t max_num_iterations;                /* 100 */
+  int32_t max_linear_solver_iterations;      /* 200 */
+  int32_t min_linear_solver_iterations;      /* 0   */
+  int32_t max_num_consecutive_invalid_steps; /* 10  */
+  double function_tolerance;                 /* 0.0 */
+  double gradient_tolerance;                 /* 0.0 */
+  double parameter_tolerance;                /* 0.0 */
+  int32_t loss_function_type;                /* sba_loss_type */
+  double loss_function_scale;                /* 1.0 */
+  double initial_trust_region_radius;        /* 1e4  */
+  double max_trust_region_radius;            /* 1e16 */
+  double min_trust_region_radius;            /* 1e-32 */
+  double min_relative_decrease;              /* 1e-3 */
+  double min_lm_diagonal;                    /* 1e-6 */
+  double max_lm_diagonal;                    /* 1e32 */
+  double eta;                                /* 1e-1 */
+  int32_t jacobi_scaling;                    /* 1 */
+  int32_t update_state_every_iteration;      /* 0; when 1 the callback may read parameters */
+} sba_solver_options;
+
+/* One row of the Ceres iteration table (IterationSummary). */
+typedef struct sba_iteration_summary {
+  int32_t iteration;
+  int32_t step_is_valid;
+  int32_t step_is_successful;
+  int32_t linear_solver_iterations;
+  double cost;
+  double cost_change;
+  double gradient_max_norm;
+  double step_norm;
+  double relative_decrease;
+  double trust_region_radius;
+  double eta;
+} sba_iteration_summary;
+
+/* Fields of ceres::Solver::Summary the reference's callers read
+ * (bundle_adjustment.cc:1142-1196, incremental_mapper.cc:635-636). */
+typedef struct sba_summary {
+  int32_t termination_type; /* sba_termination */
+  int32_t linear_solver_type_used;
+  int32_t num_iterations; /* rows in the trace, including iteration 0 */
+  int32_t num_successful_steps;
+  int32_t num_unsuccessful_steps;
+  int32_t num_residual_blocks;
+  int32_t num_residuals;
+  int32_t num_residuals_reduced;
+  int32_t num_parameter_blocks_reduced;
+  int32_t num_parameters_reduced;
+  int32_t num_effective_parameters_reduced;
+  int64_t num_linear_solver_iterations;
+  double initial_cost;
+  double final_cost;
+  double fixed_cost;
+  double total_time_in_seconds;
+  /* device-side stage times (CUDA events), seconds */
+  double time_evaluate_s;
+  double time_eliminate_s;
+  double time_linear_solve_s;
+  double time_update_s;
+} sba_summary;
+
+typedef struct sba_handle sba_handle;
+
+/* Return 0 to continue, 1 == SOLVER_TERMINATE_SUCCESSFULLY, 2 == SOLVER_ABORT
+ * (ceres::IterationCallback, used at src/controllers/bundle_adjustment.cc:43-61). */
+typedef int (*sba_iteration_callback)(const sba_iteration_summary* it, void* user);
+
+/* --- lifecycle ---------------------------------------------------------- */
+void sba_default_solver_options(sba_solver_options* o);
+int sba_create(const sba_problem_desc* desc, sba_handle** out);
+void sba_destroy(sba_handle* h);
+const char* sba_last_error(void);
+const char* sba_version(void);
+int sba_device_count(void);
+
+/* --- evaluation (parity surface; Problem::Evaluate equivalent) ----------
+ * All outputs are host pointers, nullable, in REFERENCE residual order:
+ *   residuals   [n_obs*2]   loss-corrected
+ *   jac_pose    [n_obs*2*6] row-major 2x6: d r / d (quat tangent(3), tvec(3)); zero columns when constant
+ *   jac_intr    [n_obs*2*SBA_MAX_CAMERA_PARAMS] d r / d camera params (ambient; constant params zeroed)
+ *   jac_point   [n_obs*2*3]
+ *   jac_qvec_ambient [n_obs*2*4] raw autodiff-equivalent block w.r.t. (w,x,y,z) before the manifold
+ *   sem_residuals [n_obs] (extension X1; only when maps were given)
+ * apply_loss: 0 = raw functor outputs (CostFunction::Evaluate), 1 = loss-corrected (Problem::Evaluate). */
+int sba_evaluate(sba_handle* h, int32_t loss_function_type, double loss_function_scale,
+                 int32_t apply_loss, double* cost, double* residuals, double* jac_pose,
+                 double* jac_intr, double* jac_point, double* jac_qvec_ambient,
+                 double* sem_residuals);
+
+/* --- solve -------------------------------------------------------------- */
+int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callback cb,
+              void* user, sba_summary* summary);
+/* Copy the per-iteration trace of the last solve (up to cap rows); returns rows written via *n. */
+int sba_get_trace(sba_handle* h, sba_iteration_summary* rows, int32_t cap, int32_t* n);
+/* D2H of the current parameters, layouts as in sba_problem_desc; any pointer may be NULL. */
+int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec,
+                       double* camera_params, double* points);
+
+/* --- hot-path pieces exposed for measurement (bench.py) -----------------
+ * Each runs `repeat` launches of the named stage on device-resident data and
+ * returns the mean CUDA-event time per launch in milliseconds. */
+int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms_per_launch,
+                    int64_t* algorithmic_bytes);
+/* Number of kernels this library launched on h's stream since creation. */
+int64_t sba_kernel_launch_count(sba_handle* h);
+
+/* --- multi-GPU (one process per GPU; NCCL over NVLink) ------------------ */
+#define SBA_COMM_ID_BYTES 128
+int sba_comm_get_unique_id(void* id128);
+int sba_comm_init(sba_handle* h, int32_t nranks, int32_t rank, const void* id128);
+
+/* Host-side sharding of a problem by point ownership (pure CPU).
+ * Fills obs_keep[num_observations] (1 = this rank owns the observation) and
+ * point_keep[num_points]; contiguous point ranges balanced by observation count. */
+int sba_shard_points(const sba_problem_desc* desc, int32_t nranks, int32_t rank,
+                     uint8_t* point_keep, uint8_t* obs_keep);
+
+/* --- semantic pair residual (reference a10/a11) -------------------------
+ * src/base/semantic_cost_functions.h:88-208 evaluated for a batch of residual
+ * blocks, with Ceres-style CENTRAL numeric differentiation (App. B.6). */
+typedef struct sba_semantic_desc {
+  int32_t num_images;
+  int32_t height, width;
+  const double* image_qvec;     /* [num_images*4] */
+  const double* image_tvec;     /* [num_images*3] */
+  const double* camera_params;  /* [num_images*3] SIMPLE_PINHOLE f,cx,cy of each image's camera */
+  const float* depth_maps;      /* [num_images*H*W] ROW-major (y*W+x) */
+  const float* semantic_maps;   /* [num_images*H*W] ROW-major */
+  int64_t num_blocks;
+  const int32_t* block_image1;  /* [num_blocks] */
+  const int32_t* block_image2;  /* [num_blocks] */
+  const int32_t* block_x1;      /* [num_blocks] */
+  const int32_t* block_y1;      /* [num_blocks] */
+  double depth_error_threshold; /* 2.0, semantic_bundle_adjustment.h:78 */
+  double relative_step_size;    /* 1e-3, semantic_bundle_adjustment.h:89 */
+} sba_semantic_desc;
+
+/* residuals[num_blocks]; status[num_blocks] (-1 OOB, -2 invalid depth, 10 valid);
+ * jac[num_blocks*14]: ambient central-difference d r/d(q1(4),t1(3),q2(4),t2(3)); nullable. */
+int sba_semantic_evaluate(const sba_semantic_desc* d, double* residuals, int32_t* status,
+                          double* jac, double* ms_device);
+
+/* --- cylinder IoU residual (reference a12) ------------------------------
+ * 1 - IoU of the projected cylinder quadrilateral against a boolean mask,
+ * src/util/cylinder.h:27-121, 352-540. */
+typedef struct sba_cylinder_desc {
+  int32_t num_images;
+  int32_t height, width;
+  const double* image_qvec;    /* [num_images*4] */
+  const double* image_tvec;    /* [num_images*3] */
+  const double* camera_params; /* [num_images*3] */
+  const uint8_t* masks;        /* [num_images*H*W] ROW-major, non-zero = trunk */
+  int32_t num_cylinders;
+  const double* cyl_qvec;      /* [num_cylinders*4] */
+  const double* cyl_tvec;      /* [num_cylinders*3] */
+  const double* cyl_radius;    /* [num_cylinders]   */
+  const double* cyl_height;    /* [num_cylinders]   */
+  int64_t num_blocks;
+  const int32_t* block_image;    /* [num_blocks] */
+  const int32_t* block_cylinder; /* [num_blocks] */
+  double relative_step_size;
+} sba_cylinder_desc;
+
+/* residuals[num_blocks] = 1 - IoU; jac[num_blocks*16] central differences over
+ * (cam q(4), cam t(3), cyl q(4), cyl t(3), radius, height); nullable. */
+int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residuals, double* jac,
+                          double* ms_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBA_B200_H_ */

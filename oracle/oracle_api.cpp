@@ -1,0 +1,177 @@
+// ORACLE (test infrastructure only -- never linked into the product library).
+// extern "C" surface of the CPU restatement, loaded with ctypes by tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+#include <omp.h>
+
+#include <cstring>
+#include <vector>
+
+#include "ba_oracle.h"
+#include "projection.h"
+#include "rotation.h"
+#include "semantic_oracle.h"
+
+using namespace oracle;
+
+extern "C" {
+
+int oracle_num_threads(void) { return omp_get_max_threads(); }
+
+void oracle_world_to_image(int model, const double* params, double u, double v, double* x, double* y) {
+  Project<double>(model, params, u, v, x, y);
+}
+void oracle_image_to_world(int model, const double* params, double x, double y, double* u, double* v) {
+  Unproject(model, params, x, y, u, v);
+}
+int oracle_model_num_params(int model) { return NumParams(model); }
+
+// CostFunction::Evaluate of one residual block (cost_functions.h:57-81 / 115-140)
+void oracle_eval_observation(int model, const double* q, const double* t, const double* X,
+                             const double* params, const double* xy, double* r, double* Jq,
+                             double* Jt, double* JX, double* Jk) {
+  EvalObservation(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk);
+}
+
+// Rig functor (cost_functions.h:173-209): residual only, for the known answers at
+// cost_functions_test.cc:101-132.
+void oracle_eval_rig_observation(int model, const double* rig_q, const double* rig_t,
+                                 const double* rel_q, const double* rel_t, const double* X,
+                                 const double* params, const double* xy, double* r) {
+  double q[4], t[3];
+  QuaternionProduct(rel_q, rig_q, q);
+  UnitQuaternionRotatePoint(rel_q, rig_t, t);
+  t[0] += rel_t[0]; t[1] += rel_t[1]; t[2] += rel_t[2];
+  EvalObservation(model, q, t, X, params, xy, r, nullptr, nullptr, nullptr, nullptr);
+}
+
+// Problem::Evaluate equivalent in the sba_evaluate() output format (include/sba_b200.h).
+int oracle_ba_evaluate(const sba_problem_desc* d, int loss_type, double loss_scale, int apply_loss,
+                       int threads, double* cost, double* residuals, double* jac_pose,
+                       double* jac_intr, double* jac_point, double* jac_qvec_ambient) {
+  BAProblem p;
+  p.Build(*d);
+  if (threads <= 0) threads = omp_get_max_threads();
+  Linearization lin;
+  Linearize(p, loss_type, loss_scale, apply_loss != 0, &lin, threads);
+  if (cost) *cost = lin.cost + lin.fixed_cost;
+  const int dc = p.dc_max;
+  for (int64_t k = 0; k < p.n_obs; ++k) {
+    const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
+    const double* F = &lin.F[(size_t)k * 2 * dc];
+    if (residuals) {
+      if (p.obs_active[k]) { residuals[2 * k] = lin.r[2 * k]; residuals[2 * k + 1] = lin.r[2 * k + 1]; }
+      else {
+        double r[2];
+        EvalObservation(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
+                        &p.obs_xy[2 * k], r, nullptr, nullptr, nullptr, nullptr);
+        residuals[2 * k] = r[0]; residuals[2 * k + 1] = r[1];
+      }
+    }
+    int n = 0;
+    if (jac_pose) std::memset(&jac_pose[k * 12], 0, 12 * sizeof(double));
+    if (jac_intr) std::memset(&jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS], 0, 2 * SBA_MAX_CAMERA_PARAMS * sizeof(double));
+    if (jac_point) std::memset(&jac_point[k * 6], 0, 6 * sizeof(double));
+    if (p.obs_active[k]) {
+      if (p.q_off[i] >= 0) {
+        if (jac_pose) for (int j = 0; j < 3; ++j) { jac_pose[k * 12 + j] = F[n + j]; jac_pose[k * 12 + 6 + j] = F[dc + n + j]; }
+        n += 3;
+      }
+      if (p.t_off[i] >= 0) {
+        if (jac_pose) for (int j = 0; j < p.t_dim[i]; ++j) {
+          const int a = p.t_cols[3 * i + j];
+          jac_pose[k * 12 + 3 + a] = F[n + j]; jac_pose[k * 12 + 9 + a] = F[dc + n + j];
+        }
+        n += p.t_dim[i];
+      }
+      if (p.k_off[c] >= 0) {
+        if (jac_intr) for (int j = 0; j < p.k_dim[c]; ++j) {
+          const int a = p.k_cols[SBA_MAX_CAMERA_PARAMS * c + j];
+          jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS + a] = F[n + j];
+          jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS + SBA_MAX_CAMERA_PARAMS + a] = F[dc + n + j];
+        }
+        n += p.k_dim[c];
+      }
+      if (jac_point && p.p_off[pt] >= 0) for (int j = 0; j < 6; ++j) jac_point[k * 6 + j] = lin.E[(size_t)k * 6 + j];
+    }
+    if (jac_qvec_ambient) {
+      double r[2], Jq[8];
+      EvalObservation(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
+                      &p.obs_xy[2 * k], r, Jq, nullptr, nullptr, nullptr);
+      for (int j = 0; j < 8; ++j) jac_qvec_ambient[k * 8 + j] = Jq[j];
+    }
+  }
+  return 0;
+}
+
+int oracle_ba_counts(const sba_problem_desc* d, sba_summary* s) {
+  BAProblem p;
+  p.Build(*d);
+  std::memset(s, 0, sizeof(*s));
+  s->num_residual_blocks = p.num_residual_blocks; s->num_residuals = p.num_residuals;
+  s->num_residuals_reduced = p.num_residuals_reduced;
+  s->num_parameter_blocks_reduced = p.num_parameter_blocks_reduced;
+  s->num_parameters_reduced = p.num_parameters_reduced;
+  s->num_effective_parameters_reduced = p.num_effective_parameters_reduced;
+  return 0;
+}
+
+int oracle_ba_solve(const sba_problem_desc* d, const sba_solver_options* o, int threads,
+                    sba_summary* summary, sba_iteration_summary* trace, int cap, int* n_trace,
+                    double* qvec, double* tvec, double* cams, double* points) {
+  BAProblem p;
+  p.Build(*d);
+  if (threads <= 0) threads = omp_get_max_threads();
+  std::vector<sba_iteration_summary> tr;
+  const int rc = Solve(&p, *o, summary, &tr, threads);
+  if (trace && n_trace) {
+    const int n = std::min<int>(cap, (int)tr.size());
+    for (int i = 0; i < n; ++i) trace[i] = tr[i];
+    *n_trace = n;
+  }
+  if (qvec) std::memcpy(qvec, p.q.data(), p.q.size() * sizeof(double));
+  if (tvec) std::memcpy(tvec, p.t.data(), p.t.size() * sizeof(double));
+  if (cams) std::memcpy(cams, p.cam.data(), p.cam.size() * sizeof(double));
+  if (points) std::memcpy(points, p.X.data(), p.X.size() * sizeof(double));
+  return rc;
+}
+
+// Timed pieces for bench.py's cpu_baseline: one residual+Jacobian evaluation
+// (Evaluator::Evaluate equivalent) on all cores; returns seconds.
+double oracle_ba_time_linearize(const sba_problem_desc* d, int loss_type, double loss_scale, int threads, int repeat) {
+  BAProblem p;
+  p.Build(*d);
+  if (threads <= 0) threads = omp_get_max_threads();
+  Linearization lin;
+  Linearize(p, loss_type, loss_scale, true, &lin, threads);  // warm
+  const double t0 = omp_get_wtime();
+  for (int i = 0; i < repeat; ++i) Linearize(p, loss_type, loss_scale, true, &lin, threads);
+  return (omp_get_wtime() - t0) / repeat;
+}
+
+int oracle_semantic_evaluate(const sba_semantic_desc* d, int threads, double* residuals, int32_t* status, double* jac) {
+  if (threads <= 0) threads = omp_get_max_threads();
+  SemanticEvaluate(*d, threads, residuals, status, jac);
+  return 0;
+}
+
+int oracle_cylinder_evaluate(const sba_cylinder_desc* d, int threads, double* residuals, double* jac) {
+  if (threads <= 0) threads = omp_get_max_threads();
+  CylinderEvaluate(*d, threads, residuals, jac);
+  return 0;
+}
+
+void oracle_draw_quadrilateral(const double* pts8, int H, int W, uint8_t* mask_rowmajor) {
+  DrawQuadrilateralRowMajor(pts8, H, W, mask_rowmajor);
+}
+
+int oracle_cylinder_quadrilateral(const double* cam_q, const double* cam_t, const double* cam_params,
+                                  const double* cyl_q, const double* cyl_t, double radius, double height,
+                                  double* pts8) {
+  return CylinderQuadrilateral(cam_q, cam_t, cam_params, cyl_q, cyl_t, radius, height, pts8) ? 1 : 0;
+}
+
+double oracle_bilinear(const float* map, int H, int W, double x, double y, int* ok) {
+  return BilinearSample(map, H, W, x, y, ok);
+}
+
+}  // extern "C"

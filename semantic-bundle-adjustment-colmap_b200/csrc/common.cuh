@@ -1,0 +1,102 @@
+// Shared declarations of the B200-native bundle-adjustment hot path.
+//
+// Reference boundary this library sits behind:
+//   BundleAdjuster::Solve   /root/reference/src/optim/bundle_adjustment.cc:258-320
+//   cost functors           /root/reference/src/base/cost_functions.h:44-152
+// Everything the reference hands to ceres::Solve (bundle_adjustment.cc:306) is
+// evaluated and solved on the device by the kernels declared here.
+//
+// Device data layout (all fp64):
+//   images  : pose record  double[8]  = q(w,x,y,z) t(x,y,z) pad     (64 B aligned gather unit)
+//   cameras : params       double[12]                               (96 B)
+//   points  : X            double[3]  packed
+//   observations are kept in POINT-SORTED order (stable by reference order);
+//   ref2pt / pt2ref permutations recover the reference residual order.
+//   per observation k:
+//     ER[k]  = double[8]  : E (2x3 d r/d X, row-major) + r(2)        (64 B record)
+//     F[k]   = double2[DC]: slot j -> (d r0/d s_j, d r1/d s_j)       (16*DC B record)
+//              slots 0..2 quaternion tangent, 3..5 tvec, 6.. free intrinsics
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/sba_b200.h"
+
+namespace sba {
+
+constexpr int kMaxDC = 18;  // 6 pose slots + 12 intrinsics slots
+constexpr int kTile = 32;   // observations per warp tile
+
+struct Err {
+  int code;
+  std::string msg;
+};
+void SetError(int code, const std::string& msg);
+#define SBA_CUDA(expr)                                                                     \
+  do {                                                                                     \
+    cudaError_t _e = (expr);                                                               \
+    if (_e != cudaSuccess) {                                                               \
+      ::sba::SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));   \
+      return SBA_ERR_CUDA;                                                                 \
+    }                                                                                      \
+  } while (0)
+
+// Views passed by value to kernels --------------------------------------------------
+struct ParamsView {
+  const double* pose;  // [n_img*8]
+  const double* cam;   // [n_cam*12]
+  const double* X;     // [n_pt*3]
+};
+
+struct StructView {
+  int n_img, n_cam, n_pt, n_obs;
+  int dc;                     // padded slots per observation (6, 8, 10, 14, 18)
+  int kmax;                   // max free intrinsics per camera
+  int n_cdim;                 // compact camera-side dimension
+  int n_pvar;                 // variable points
+  const int* img_cam;         // [n_img]
+  const int* model;           // [n_cam]
+  const int* col_img;         // [n_img*6]  compact column of pose slot or -1
+  const int* col_cam;         // [n_cam*12] compact column of intrinsics slot j (j<k_dim) or -1
+  const int* k_cols;          // [n_cam*12] ambient param index of intrinsics slot j
+  const int* k_slot;          // [n_cam*12] intrinsics slot of ambient param a, or -1 (constant)
+  const int* k_dim;           // [n_cam]
+  const int* p_off;           // [n_pt] variable-point index or -1
+  const int* obs_img;         // [n_obs] point-sorted
+  const int* obs_pt;          // [n_obs]
+  const double* obs_xy;       // [n_obs*2]
+  const uint8_t* obs_active;  // [n_obs] residual block kept in the reduced program
+  const uint8_t* pose_const;  // [n_img]
+};
+
+struct LossView {
+  int type;
+  double scale;
+  int apply;
+};
+
+// warp tiles over the point-sorted observation array: whole points packed into
+// <=32 observations; a point longer than 32 gets a tile of its own.
+struct TileView {
+  int n_tiles;
+  const int* tile_start;  // [n_tiles+1]
+};
+
+// camera-side chunks: runs of <=256 slots of the image-sorted index list that
+// never straddle an image.
+struct ChunkView {
+  int n_chunks;
+  const int* chunk_start;   // [n_chunks+1] into cam_order
+  const int* chunk_img;     // [n_chunks]
+  const int* cam_order;     // [n_obs] observation ids (point-sorted numbering), image-major
+  const int* img_chunk_ptr; // [n_img+1] chunk range of each image
+  const int* cam_img_ptr;   // [n_cam+1] CSR: images of each camera
+  const int* cam_img_list;  // [n_img]
+};
+
+inline int DivUp(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+}  // namespace sba

@@ -1,0 +1,299 @@
+// K-EVAL: per-observation reprojection residual + analytic Jacobian kernel (sm_100a, fp64).
+//
+// One thread per observation (point-sorted order).  What is computed is the
+// reference functor
+//   BundleAdjustmentCostFunction<CM>::operator()           /root/reference/src/base/cost_functions.h:57-81
+//   BundleAdjustmentConstantPoseCostFunction<CM>           /root/reference/src/base/cost_functions.h:115-140
+// followed by what Ceres does to the block before handing it to the linear
+// solver: J_local = J_ambient * PlusJacobian
+// (QuaternionManifold / SubsetManifold, cost_functions.h:270-287), loss corrector
+// (bundle_adjustment.cc:53-68) and Jacobi column scaling.
+//
+// HBM traffic per observation (algorithmic): 8 B indices + 16 B xy in,
+// 64 B ER record + 16*DC B F record out; poses / intrinsics / points are gathered
+// through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
+#include "device_math.cuh"
+#include "reduce.cuh"
+#include "solver.h"
+
+namespace sba {
+
+constexpr int kEvalThreads = 128;
+
+struct ObsGeom {
+  double p[3];      // R(q) X + t
+  double R[9];      // d p / d X  (the un-normalised rotation polynomial)
+  double G[9];      // d p / d (quaternion tangent), row-major 3x3
+};
+
+// ceres::UnitQuaternionRotatePoint polynomial (no normalisation) and its
+// derivatives, with the QuaternionManifold PlusJacobian folded in.
+__device__ inline void RotateWithJac(const double q[4], const double t[3], const double X[3], ObsGeom* g,
+                                     bool need_jac) {
+  const double q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+  const double t2 = q0 * q1, t3 = q0 * q2, t4 = q0 * q3, t5 = -q1 * q1, t6 = q1 * q2, t7 = q1 * q3,
+               t8 = -q2 * q2, t9 = q2 * q3, t1 = -q3 * q3;
+  g->p[0] = 2.0 * ((t8 + t1) * X[0] + (t6 - t4) * X[1] + (t3 + t7) * X[2]) + X[0] + t[0];
+  g->p[1] = 2.0 * ((t4 + t6) * X[0] + (t5 + t1) * X[1] + (t9 - t2) * X[2]) + X[1] + t[1];
+  g->p[2] = 2.0 * ((t7 - t3) * X[0] + (t2 + t9) * X[1] + (t5 + t8) * X[2]) + X[2] + t[2];
+  if (!need_jac) return;
+  g->R[0] = 1.0 + 2.0 * (t8 + t1); g->R[1] = 2.0 * (t6 - t4);       g->R[2] = 2.0 * (t3 + t7);
+  g->R[3] = 2.0 * (t4 + t6);       g->R[4] = 1.0 + 2.0 * (t5 + t1); g->R[5] = 2.0 * (t9 - t2);
+  g->R[6] = 2.0 * (t7 - t3);       g->R[7] = 2.0 * (t2 + t9);       g->R[8] = 1.0 + 2.0 * (t5 + t8);
+  // d p / d q (3x4), columns q0..q3
+  const double X0 = X[0], X1 = X[1], X2 = X[2];
+  const double D[12] = {
+      2.0 * (-q3 * X1 + q2 * X2), 2.0 * (q2 * X1 + q3 * X2),             2.0 * (-2.0 * q2 * X0 + q1 * X1 + q0 * X2), 2.0 * (-2.0 * q3 * X0 - q0 * X1 + q1 * X2),
+      2.0 * (q3 * X0 - q1 * X2),  2.0 * (q2 * X0 - 2.0 * q1 * X1 - q0 * X2), 2.0 * (q1 * X0 + q3 * X2),              2.0 * (q0 * X0 - 2.0 * q3 * X1 + q2 * X2),
+      2.0 * (-q2 * X0 + q1 * X1), 2.0 * (q3 * X0 + q0 * X1 - 2.0 * q1 * X2), 2.0 * (-q0 * X0 + q3 * X1 - 2.0 * q2 * X2), 2.0 * (q1 * X0 + q2 * X1)};
+  // PlusJacobian rows (w,x,y,z): [-q1,-q2,-q3],[q0,q3,-q2],[-q3,q0,q1],[q2,-q1,q0]
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const double a = D[4 * r], b = D[4 * r + 1], c = D[4 * r + 2], d = D[4 * r + 3];
+    g->G[3 * r + 0] = -a * q1 + b * q0 - c * q3 + d * q2;
+    g->G[3 * r + 1] = -a * q2 + b * q3 + c * q0 - d * q1;
+    g->G[3 * r + 2] = -a * q3 - b * q2 + c * q1 + d * q0;
+  }
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(kEvalThreads)
+eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_c,
+            const double* __restrict__ scale_p, double* __restrict__ ER, double2* __restrict__ F,
+            double* __restrict__ cost_partial, double* __restrict__ Jq_ambient) {
+  const int k = blockIdx.x * kEvalThreads + threadIdx.x;
+  double cost = 0.0, fixed = 0.0;
+  if (k < S.n_obs) {
+    const int i = S.obs_img[k], pt = S.obs_pt[k];
+    const int c = S.img_cam[i];
+    const int model = MODEL >= 0 ? MODEL : S.model[c];
+    const double2* pp = reinterpret_cast<const double2*>(P.pose + 8 * (size_t)i);
+    const double2 a0 = __ldg(pp), a1 = __ldg(pp + 1), a2 = __ldg(pp + 2), a3 = __ldg(pp + 3);
+    const double q[4] = {a0.x, a0.y, a1.x, a1.y};
+    const double t[3] = {a2.x, a2.y, a3.x};
+    const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
+    double prm[12];
+    {
+      const double2* cp = reinterpret_cast<const double2*>(P.cam + 12 * (size_t)c);
+      const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        if (2 * j < np) { const double2 v = __ldg(cp + j); prm[2 * j] = v.x; prm[2 * j + 1] = v.y; }
+        else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
+      }
+    }
+    const double2 xy = reinterpret_cast<const double2*>(S.obs_xy)[k];
+    ObsGeom g;
+    RotateWithJac(q, t, X, &g, true);
+    const double iz = 1.0 / g.p[2];
+    const double u = g.p[0] * iz, v = g.p[1] * iz;
+    double x, y, A[4], Jk[24];
+    if (MODEL >= 0) WorldToImageJac<(MODEL >= 0 ? MODEL : 0)>(prm, u, v, &x, &y, A, Jk);
+    else WorldToImageJacDyn(model, prm, u, v, &x, &y, A, Jk);
+    double r0 = x - xy.x, r1 = y - xy.y;
+    // AB = A * d(u,v)/dp   (2x3)
+    const double AB[6] = {A[0] * iz, A[1] * iz, -(A[0] * u + A[1] * v) * iz,
+                          A[2] * iz, A[3] * iz, -(A[2] * u + A[3] * v) * iz};
+    if (Jq_ambient) {  // raw 2x4 block w.r.t. (w,x,y,z): parity surface only
+      const double q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], X0 = X[0], X1 = X[1], X2 = X[2];
+      const double D[12] = {
+          2.0 * (-q3 * X1 + q2 * X2), 2.0 * (q2 * X1 + q3 * X2),             2.0 * (-2.0 * q2 * X0 + q1 * X1 + q0 * X2), 2.0 * (-2.0 * q3 * X0 - q0 * X1 + q1 * X2),
+          2.0 * (q3 * X0 - q1 * X2),  2.0 * (q2 * X0 - 2.0 * q1 * X1 - q0 * X2), 2.0 * (q1 * X0 + q3 * X2),              2.0 * (q0 * X0 - 2.0 * q3 * X1 + q2 * X2),
+          2.0 * (-q2 * X0 + q1 * X1), 2.0 * (q3 * X0 + q0 * X1 - 2.0 * q1 * X2), 2.0 * (-q0 * X0 + q3 * X1 - 2.0 * q2 * X2), 2.0 * (q1 * X0 + q2 * X1)};
+      for (int row = 0; row < 2; ++row)
+        for (int j = 0; j < 4; ++j)
+          Jq_ambient[(size_t)k * 8 + row * 4 + j] =
+              AB[3 * row] * D[j] + AB[3 * row + 1] * D[4 + j] + AB[3 * row + 2] * D[8 + j];
+    }
+    const double s = r0 * r0 + r1 * r1;
+    double rho[3];
+    LossEval(L.type, L.scale, s, rho);
+    const bool active = S.obs_active[k] != 0;
+    double2* Fk = F + (size_t)k * S.dc;
+    double* ERk = ER + (size_t)k * 8;
+    if (!active) {
+      fixed = 0.5 * rho[0];
+      for (int j = 0; j < S.dc; ++j) Fk[j] = make_double2(0.0, 0.0);
+      // raw residual is still exported for the parity surface; E = 0 keeps it out of every product
+      reinterpret_cast<double2*>(ERk)[0] = make_double2(0.0, 0.0);
+      reinterpret_cast<double2*>(ERk)[1] = make_double2(0.0, 0.0);
+      reinterpret_cast<double2*>(ERk)[2] = make_double2(0.0, 0.0);
+      reinterpret_cast<double2*>(ERk)[3] = make_double2(r0, r1);
+    } else {
+      cost = 0.5 * rho[0];
+      // corrector (ceres corrector.cc)
+      double sqrt_rho1 = 1.0, residual_scaling = 1.0, alpha_sq_norm = 0.0;
+      if (L.apply) {
+        sqrt_rho1 = sqrt(rho[1]);
+        if (s == 0.0 || rho[2] <= 0.0) {
+          residual_scaling = sqrt_rho1;
+        } else {
+          const double Dd = 1.0 + 2.0 * s * rho[2] / rho[1];
+          const double alpha = 1.0 - sqrt(Dd);
+          residual_scaling = sqrt_rho1 / (1.0 - alpha);
+          alpha_sq_norm = alpha / s;
+        }
+      }
+      auto correct = [&](double& j0, double& j1) {
+        if (alpha_sq_norm == 0.0) { j0 *= sqrt_rho1; j1 *= sqrt_rho1; return; }
+        const double rtj = r0 * j0 + r1 * j1;
+        j0 = sqrt_rho1 * (j0 - alpha_sq_norm * r0 * rtj);
+        j1 = sqrt_rho1 * (j1 - alpha_sq_norm * r1 * rtj);
+      };
+      const int* ci = S.col_img + 6 * (size_t)i;
+      // pose slots
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {  // quaternion tangent
+        double j0 = AB[0] * g.G[j] + AB[1] * g.G[3 + j] + AB[2] * g.G[6 + j];
+        double j1 = AB[3] * g.G[j] + AB[4] * g.G[3 + j] + AB[5] * g.G[6 + j];
+        const int col = ci[j];
+        if (col < 0) { j0 = 0.0; j1 = 0.0; }
+        else { correct(j0, j1); if (scale_c) { const double sc = scale_c[col]; j0 *= sc; j1 *= sc; } }
+        Fk[j] = make_double2(j0, j1);
+      }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {  // tvec
+        double j0 = AB[j], j1 = AB[3 + j];
+        const int col = ci[3 + j];
+        if (col < 0) { j0 = 0.0; j1 = 0.0; }
+        else { correct(j0, j1); if (scale_c) { const double sc = scale_c[col]; j0 *= sc; j1 *= sc; } }
+        Fk[3 + j] = make_double2(j0, j1);
+      }
+      // intrinsics slots
+      if (S.dc > 6) {
+        for (int j = 6; j < S.dc; ++j) Fk[j] = make_double2(0.0, 0.0);
+        const int* ks = S.k_slot + 12 * (size_t)c;
+        const int* cc = S.col_cam + 12 * (size_t)c;
+        const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+#pragma unroll
+        for (int a = 0; a < 12; ++a) {
+          if (a < np) {
+            const int slot = ks[a];
+            if (slot >= 0) {
+              double j0 = Jk[a], j1 = Jk[12 + a];
+              correct(j0, j1);
+              if (scale_c) { const double sc = scale_c[cc[slot]]; j0 *= sc; j1 *= sc; }
+              Fk[6 + slot] = make_double2(j0, j1);
+            }
+          }
+        }
+      }
+      // point block
+      double E[6];
+      const int po = S.p_off[pt];
+      if (po >= 0) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          double j0 = AB[0] * g.R[j] + AB[1] * g.R[3 + j] + AB[2] * g.R[6 + j];
+          double j1 = AB[3] * g.R[j] + AB[4] * g.R[3 + j] + AB[5] * g.R[6 + j];
+          correct(j0, j1);
+          if (scale_p) { const double sp = scale_p[3 * (size_t)po + j]; j0 *= sp; j1 *= sp; }
+          E[j] = j0; E[3 + j] = j1;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) E[j] = 0.0;
+      }
+      r0 *= residual_scaling; r1 *= residual_scaling;
+      reinterpret_cast<double2*>(ERk)[0] = make_double2(E[0], E[1]);
+      reinterpret_cast<double2*>(ERk)[1] = make_double2(E[2], E[3]);
+      reinterpret_cast<double2*>(ERk)[2] = make_double2(E[4], E[5]);
+      reinterpret_cast<double2*>(ERk)[3] = make_double2(r0, r1);
+    }
+  }
+  BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
+}
+
+// residual-only evaluation of the candidate point (Evaluator::Evaluate with no jacobian)
+template <int MODEL>
+__global__ void __launch_bounds__(kEvalThreads)
+cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_partial) {
+  const int k = blockIdx.x * kEvalThreads + threadIdx.x;
+  double cost = 0.0, fixed = 0.0;
+  if (k < S.n_obs) {
+    const int i = S.obs_img[k], pt = S.obs_pt[k];
+    const int c = S.img_cam[i];
+    const int model = MODEL >= 0 ? MODEL : S.model[c];
+    const double2* pp = reinterpret_cast<const double2*>(P.pose + 8 * (size_t)i);
+    const double2 a0 = __ldg(pp), a1 = __ldg(pp + 1), a2 = __ldg(pp + 2), a3 = __ldg(pp + 3);
+    const double q[4] = {a0.x, a0.y, a1.x, a1.y};
+    const double t[3] = {a2.x, a2.y, a3.x};
+    const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
+    double prm[12];
+    {
+      const double2* cp = reinterpret_cast<const double2*>(P.cam + 12 * (size_t)c);
+      const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        if (2 * j < np) { const double2 v = __ldg(cp + j); prm[2 * j] = v.x; prm[2 * j + 1] = v.y; }
+        else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
+      }
+    }
+    const double2 xy = reinterpret_cast<const double2*>(S.obs_xy)[k];
+    ObsGeom g;
+    RotateWithJac(q, t, X, &g, false);
+    const double iz = 1.0 / g.p[2];
+    double x, y;
+    if (MODEL >= 0) WorldToImageVal<(MODEL >= 0 ? MODEL : 0)>(prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
+    else WorldToImageValDyn(model, prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
+    const double r0 = x - xy.x, r1 = y - xy.y;
+    double rho[3];
+    LossEval(L.type, L.scale, r0 * r0 + r1 * r1, rho);
+    if (S.obs_active[k]) cost = 0.5 * rho[0]; else fixed = 0.5 * rho[0];
+  }
+  BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
+}
+
+double* g_Jq_ambient_out = nullptr;  // set by sba_evaluate for the parity surface only
+
+template <int MODEL>
+static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
+  eval_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(
+      p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_c.p : nullptr,
+      use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, g_Jq_ambient_out);
+}
+template <int MODEL>
+static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks) {
+  cost_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss,
+                                                             p->d_cost_partial.p);
+}
+
+#define SBA_MODEL_SWITCH(m, CALL)                                            \
+  switch (m) {                                                               \
+    case 0: CALL(0); break;  case 1: CALL(1); break;  case 2: CALL(2); break; \
+    case 3: CALL(3); break;  case 4: CALL(4); break;  case 5: CALL(5); break; \
+    case 6: CALL(6); break;  case 7: CALL(7); break;  case 8: CALL(8); break; \
+    case 9: CALL(9); break;  case 10: CALL(10); break; default: CALL(-1); break; \
+  }
+
+int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate) {
+  const int blocks = DivUp(p->n_obs, kEvalThreads);
+  if (blocks > 0) {
+#define CALL(M) LaunchEvalT<M>(p, loss, use_scale, candidate, blocks)
+    SBA_MODEL_SWITCH(p->uniform_model, CALL)
+#undef CALL
+    p->launches++;
+  }
+  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, blocks, &p->d_scalars.p->cost,
+                                                  &p->d_scalars.p->fixed_cost, 1.0);
+  p->launches++;
+  SBA_CUDA(cudaGetLastError());
+  p->linearized = true;
+  return SBA_OK;
+}
+
+int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost) {
+  const int blocks = DivUp(p->n_obs, kEvalThreads);
+  if (blocks > 0) {
+#define CALL(M) LaunchCostT<M>(p, loss, candidate, blocks)
+    SBA_MODEL_SWITCH(p->uniform_model, CALL)
+#undef CALL
+    p->launches++;
+  }
+  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, blocks, d_out_cost, nullptr, 1.0);
+  p->launches++;
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+}  // namespace sba

@@ -1,0 +1,322 @@
+// Host launchers for the elimination / product / update kernels (linalg_kernels.cuh)
+// and the device-resident trust-region bookkeeping.
+// Reference: the inside of ceres::Solve as called at
+//   /root/reference/src/optim/bundle_adjustment.cc:306   (SURVEY.md App. B.3-B.5).
+#include "linalg_kernels.cuh"
+#include "reduce.cuh"
+
+namespace sba {
+
+static int Expand(Problem* p, const double* x, double* xi, double* xc) {
+  const int n = p->n_img * 6 + p->n_cam * 12;
+  expand_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>(p->Struct(), x, xi, xc);
+  p->launches++;
+  return SBA_OK;
+}
+
+// mode 0: F^T v, 1: F^T r, 2: column square norms.  out (compact) = sum over LOCAL
+// observations, all-reduced over ranks, plus Dc^2 x when Dc != nullptr.
+static int CamReduce(Problem* p, int mode, const double2* v, double* out, const double* Dc, const double* x) {
+  if (p->n_cdim == 0) return SBA_OK;
+  if (p->n_chunks > 0) {
+#define CALL(DC)                                                                                                        \
+  do {                                                                                                                  \
+    if (mode == 0) cam_reduce_kernel<DC, 0><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
+    else if (mode == 1) cam_reduce_kernel<DC, 1><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
+    else cam_reduce_kernel<DC, 2><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
+  } while (0)
+    SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+    p->launches++;
+  }
+  const bool multi = p->comm != nullptr;
+  const int n = p->n_img * 6 + p->n_cam * 12;
+  cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_partial.p, out,
+                                                           multi ? nullptr : Dc, x);
+  p->launches++;
+  if (multi) {
+    int rc = AllReduceSum(p, out, p->n_cdim);
+    if (rc) return rc;
+    if (Dc) { add_diag_kernel<<<DivUp(p->n_cdim, 256), 256, 0, p->stream>>>(p->n_cdim, out, Dc, x); p->launches++; }
+  }
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+int ColumnNorms(Problem* p, double* d_nc, double* d_np) {
+  int rc = CamReduce(p, 2, nullptr, d_nc, nullptr, nullptr);
+  if (rc) return rc;
+  if (p->n_pvar > 0 && p->n_tiles > 0) {
+    point_sqnorm_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, d_np);
+    p->launches++;
+  }
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+// Jacobi scaling at iteration 0: scale = 1/(1+sqrt(colnorm^2)); the stored Jacobian is
+// rescaled in place, later evaluations apply the scale when storing.
+int InitJacobiScale(Problem* p) {
+  int rc = ColumnNorms(p, p->d_sq_c.p, p->d_sq_p.p);
+  if (rc) return rc;
+  if (p->n_cdim > 0) { jacobi_scale_kernel<<<DivUp(p->n_cdim, 256), 256, 0, p->stream>>>(p->n_cdim, p->d_sq_c.p, p->d_scale_c.p); p->launches++; }
+  if (p->n_pvar > 0) { jacobi_scale_kernel<<<DivUp(3 * p->n_pvar, 256), 256, 0, p->stream>>>(3 * p->n_pvar, p->d_sq_p.p, p->d_scale_p.p); p->launches++; }
+  Expand(p, p->d_scale_c.p, p->d_scale_i.p, p->d_scale_k.p);
+  if (p->n_obs > 0) {
+#define CALL(DC) scale_jacobian_kernel<DC><<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_scale_i.p, p->d_scale_k.p, p->d_scale_p.p, p->d_F.p, p->d_ER.p)
+    SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+    p->launches++;
+  }
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+// gradient max-norm of the UNSCALED problem: max |(J^T r)_j| = max |g_scaled_j / scale_j|
+int Gradient(Problem* p, double* d_gc, double* d_gp_unused) {
+  (void)d_gp_unused;
+  int rc = CamReduce(p, 1, nullptr, d_gc, nullptr, nullptr);
+  if (rc) return rc;
+  double* out = &p->d_scalars.p->gradient_max_norm;
+  const bool scaled = true;
+  int nb = std::min(1024, std::max(1, DivUp(p->n_cdim, 256)));
+  absmax_kernel<<<nb, 256, 0, p->stream>>>(p->n_cdim, d_gc, scaled ? p->d_scale_c.p : nullptr, p->d_red.p);
+  absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 0);
+  // point part: g_p = E^T r is produced by PointBlocks (d_gp); caller guarantees it is current
+  nb = std::min(1024, std::max(1, DivUp(3 * p->n_pvar, 256)));
+  absmax_kernel<<<nb, 256, 0, p->stream>>>(3 * p->n_pvar, p->d_gp.p, p->d_scale_p.p, p->d_red.p);
+  absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 1);
+  p->launches += 4;
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
+  const int refresh = p->h_scalars->reuse_diagonal ? 0 : 1;
+  if (refresh) {
+    int rc = ColumnNorms(p, p->d_sq_c.p, p->d_sq_p.p);
+    if (rc) return rc;
+  }
+  if (p->n_cdim > 0) {
+    lm_diag_kernel<<<DivUp(p->n_cdim, 256), 256, 0, p->stream>>>(p->n_cdim, p->d_sq_c.p, p->d_diag_c.p, p->d_Dc.p, refresh,
+                                                              o.min_lm_diagonal, o.max_lm_diagonal, p->d_scalars.p);
+    p->launches++;
+  }
+  if (p->n_pvar > 0) {
+    lm_diag_kernel<<<DivUp(3 * p->n_pvar, 256), 256, 0, p->stream>>>(3 * p->n_pvar, p->d_sq_p.p, p->d_diag_p.p, p->d_Dp.p, refresh,
+                                                                  o.min_lm_diagonal, o.max_lm_diagonal, p->d_scalars.p);
+    p->launches++;
+  }
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+int PointBlocks(Problem* p) {
+  if (p->n_pvar > 0 && p->n_tiles > 0) {
+    point_blocks_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_Dp.p,
+                                                                   p->d_Cinv.p, p->d_gp.p, p->d_scalars.p);
+    p->launches++;
+  }
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+// rhs = F^T (r - E C^{-1} g)   (reduced system right-hand side; Ceres solves S y = rhs, step = -y)
+int ReducedRhs(Problem* p) {
+  if (p->n_obs > 0) {
+    rhs_e_kernel<<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_ER.p, p->d_Cinv.p, p->d_gp.p,
+                                                            reinterpret_cast<double2*>(p->d_g2.p));
+    p->launches++;
+  }
+  return CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), p->d_rhs.p, nullptr, nullptr);
+}
+
+// y = S x with S = F^T F + Dc^2 - sum_p (F^T E)_p C_p^{-1} (E^T F)_p, never formed
+// (ImplicitSchurComplement::RightMultiply).
+int SchurMatVec(Problem* p, const double* d_x, double* d_y) {
+  Expand(p, d_x, p->d_xi.p, p->d_xc.p);
+  if (p->n_tiles > 0) {
+#define CALL(DC) matvec_point_kernel<DC><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p))
+    SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+    p->launches++;
+  }
+  return CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), d_y, p->d_Dc.p, d_x);
+}
+
+// y_p and model_cost_change from y_c (d_yc)
+int BackSubstitute(Problem* p) {
+  Expand(p, p->d_yc.p, p->d_xi.p, p->d_xc.p);
+  const int nb = DivUp(p->n_tiles, 4);
+  if (nb > 0) {
+#define CALL(DC) backsub_kernel<DC><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p)
+    SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+    p->launches++;
+  }
+  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &p->d_scalars.p->model_cost_change, nullptr, -1.0);
+  p->launches++;
+  SBA_CUDA(cudaGetLastError());
+  return AllReduceSum(p, &p->d_scalars.p->model_cost_change, 1);
+}
+
+// ---- x_plus = Plus(x, -y * scale) on every variable block (manifolds) ----
+__global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsView P, const double* __restrict__ yc,
+                                                         const double* __restrict__ yp, const double* __restrict__ scale_c,
+                                                         const double* __restrict__ scale_p, double* __restrict__ pose2,
+                                                         double* __restrict__ cam2, double* __restrict__ X2,
+                                                         int first, int count, double* __restrict__ partial) {
+  const int t = first + blockIdx.x * 128 + threadIdx.x;
+  double step2 = 0.0, x2 = 0.0;
+  if (t < first + count) {
+    if (t < S.n_img) {
+      const int i = t;
+      double rec[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rec[j] = P.pose[8 * (size_t)i + j];
+      const int* ci = S.col_img + 6 * (size_t)i;
+      if (ci[0] >= 0) {
+        double d[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) d[j] = -yc[ci[j]] * scale_c[ci[j]];
+        const double n = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        double q[4] = {rec[0], rec[1], rec[2], rec[3]};
+        if (n != 0.0) {  // QuaternionManifold::Plus: [cos|d|, sin|d|/|d| d] * x
+          const double s = sin(n) / n;
+          const double z0 = cos(n), z1 = s * d[0], z2 = s * d[1], z3 = s * d[2];
+          q[0] = z0 * rec[0] - z1 * rec[1] - z2 * rec[2] - z3 * rec[3];
+          q[1] = z0 * rec[1] + z1 * rec[0] + z2 * rec[3] - z3 * rec[2];
+          q[2] = z0 * rec[2] - z1 * rec[3] + z2 * rec[0] + z3 * rec[1];
+          q[3] = z0 * rec[3] + z1 * rec[2] - z2 * rec[1] + z3 * rec[0];
+        }
+        double tt[3] = {rec[4], rec[5], rec[6]};
+#pragma unroll
+        for (int j = 0; j < 3; ++j) if (ci[3 + j] >= 0) tt[j] += -yc[ci[3 + j]] * scale_c[ci[3 + j]];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { step2 += (q[j] - rec[j]) * (q[j] - rec[j]); x2 += rec[j] * rec[j]; }
+        if (ci[3] >= 0 || ci[4] >= 0 || ci[5] >= 0) {
+#pragma unroll
+          for (int j = 0; j < 3; ++j) { step2 += (tt[j] - rec[4 + j]) * (tt[j] - rec[4 + j]); x2 += rec[4 + j] * rec[4 + j]; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rec[j] = q[j];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) rec[4 + j] = tt[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) pose2[8 * (size_t)i + j] = rec[j];
+    } else if (t < S.n_img + S.n_cam) {
+      const int c = t - S.n_img;
+      double prm[12];
+#pragma unroll
+      for (int j = 0; j < 12; ++j) prm[j] = P.cam[12 * (size_t)c + j];
+      const int kd = S.k_dim[c];
+      if (kd > 0 && S.col_cam[12 * (size_t)c] >= 0) {
+        const int np = ModelNumParamsDev(S.model[c]);
+        for (int j = 0; j < np; ++j) x2 += prm[j] * prm[j];
+        for (int j = 0; j < kd; ++j) {
+          const int col = S.col_cam[12 * (size_t)c + j];
+          const double d = -yc[col] * scale_c[col];
+          cam2[12 * (size_t)c + S.k_cols[12 * (size_t)c + j]] = P.cam[12 * (size_t)c + S.k_cols[12 * (size_t)c + j]] + d;
+          step2 += d * d;
+        }
+        // constant entries copied below
+        for (int j = 0; j < 12; ++j) if (S.k_slot[12 * (size_t)c + j] < 0) cam2[12 * (size_t)c + j] = prm[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 12; ++j) cam2[12 * (size_t)c + j] = prm[j];
+      }
+    } else {
+      const int q = t - S.n_img - S.n_cam;
+      const int po = S.p_off[q];
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const double x = P.X[3 * (size_t)q + a];
+        double xn = x;
+        if (po >= 0) {
+          const double d = -yp[3 * (size_t)po + a] * scale_p[3 * (size_t)po + a];
+          xn = x + d;
+          step2 += (xn - x) * (xn - x); x2 += x * x;
+        }
+        X2[3 * (size_t)q + a] = xn;
+      }
+    }
+  }
+  BlockSum2<128>(step2, x2, partial);
+}
+
+int ApplyStep(Problem* p) {
+  DeviceScalars* sc = p->d_scalars.p;
+  const int n_camside = p->n_img + p->n_cam;
+  int nb = DivUp(n_camside, 128);
+  if (nb > 0) {
+    apply_step_kernel<<<nb, 128, 0, p->stream>>>(p->Struct(), p->Params(false), p->d_yc.p, p->d_yp.p, p->d_scale_c.p,
+                                                 p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, 0, n_camside,
+                                                 p->d_cost_partial.p);
+    p->launches++;
+  }
+  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &sc->step2_c, &sc->x2_c, 1.0);
+  nb = DivUp(p->n_pt, 128);
+  if (nb > 0) {
+    apply_step_kernel<<<nb, 128, 0, p->stream>>>(p->Struct(), p->Params(false), p->d_yc.p, p->d_yp.p, p->d_scale_c.p,
+                                                 p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, n_camside, p->n_pt,
+                                                 p->d_cost_partial.p);
+    p->launches++;
+  }
+  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &sc->step2_p, &sc->x2_p, 1.0);
+  p->launches += 2;
+  SBA_CUDA(cudaGetLastError());
+  return AllReduceSum(p, &sc->step2_p, 2);
+}
+
+// ---- trust-region bookkeeping on the device (LevenbergMarquardtStrategy + TrustRegionMinimizer,
+//      SURVEY.md App. B.4).  phase 0: after the linear solve; phase 1: after the candidate cost. ----
+__global__ void tr_update_kernel(DeviceScalars* s, int phase, double min_relative_decrease, double max_radius,
+                                 double parameter_tolerance, double function_tolerance) {
+  if (phase == 0) {
+    const bool valid = !s->solver_failed && (s->model_cost_change > 0.0);
+    s->step_valid = valid ? 1 : 0;
+    s->step_accepted = 0;
+    s->converged = 0;
+    if (!valid) {
+      s->radius = s->radius / s->decrease_factor;
+      s->decrease_factor *= 2.0;
+      s->reuse_diagonal = 1;
+      s->cost_change = 0.0; s->relative_decrease = 0.0; s->step_norm = 0.0;
+    }
+    s->solver_failed = 0;
+  } else {
+    double cand = s->cand_cost;
+    if (!isfinite(cand)) cand = 1.7976931348623157e308;
+    s->step_norm = sqrt(s->step2_c + s->step2_p);
+    s->x_norm = sqrt(s->x2_c + s->x2_p);
+    s->cost_change = s->cost - cand;
+    if (s->step_norm <= parameter_tolerance * (s->x_norm + parameter_tolerance)) { s->converged = 1; return; }
+    if (fabs(s->cost_change) <= function_tolerance * s->cost) { s->converged = 2; return; }
+    const double rd = s->cost_change / s->model_cost_change;
+    s->relative_decrease = rd;
+    if (rd > min_relative_decrease) {
+      s->step_accepted = 1;
+      const double t = 2.0 * rd - 1.0;
+      s->radius = fmin(max_radius, s->radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
+      s->decrease_factor = 2.0;
+      s->reuse_diagonal = 0;
+    } else {
+      s->step_accepted = 0;
+      s->radius = s->radius / s->decrease_factor;
+      s->decrease_factor *= 2.0;
+      s->reuse_diagonal = 1;
+    }
+  }
+}
+
+int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase) {
+  tr_update_kernel<<<1, 1, 0, p->stream>>>(p->d_scalars.p, phase, o.min_relative_decrease, o.max_trust_region_radius,
+                                           o.parameter_tolerance, o.function_tolerance);
+  p->launches++;
+  SBA_CUDA(cudaMemcpyAsync(p->h_scalars, p->d_scalars.p, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, p->stream));
+  SBA_CUDA(cudaStreamSynchronize(p->stream));
+  return SBA_OK;
+}
+
+}  // namespace sba

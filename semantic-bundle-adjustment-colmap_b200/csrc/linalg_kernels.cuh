@@ -1,0 +1,494 @@
+// Point-block Schur elimination pieces, implicit reduced-camera-matrix product,
+// back-substitution and the camera-side segmented reductions.
+//
+// These kernels re-create on the device what ceres::Solve does for the problem the
+// reference builds (/root/reference/src/optim/bundle_adjustment.cc:306, :326-530):
+// SchurEliminator / ImplicitSchurComplement arithmetic per SURVEY.md App. B.5,
+// Jacobi scaling and the LM diagonal per App. B.3/B.4.
+//
+// Conventions: per observation k (point-sorted): ER[k] = {E 2x3 row-major, r(2)},
+// F[k] = double2[DC].  Camera-space vectors exist in two forms: compact
+// (n_cdim) and padded (n_img*6 | n_cam*12, zeros at constant slots) -- the padded
+// form lets an observation fetch its pose's six entries with three 16 B loads.
+#pragma once
+#include "solver.h"
+#include "tiles.cuh"
+
+namespace sba {
+
+#define SBA_DC_SWITCH(dc, CALL)                                                       \
+  switch (dc) {                                                                       \
+    case 6: CALL(6); break; case 8: CALL(8); break; case 10: CALL(10); break;         \
+    case 14: CALL(14); break; default: CALL(18); break;                               \
+  }
+
+// ---- compact <-> padded camera vectors ----------------------------------------------
+__global__ void expand_kernel(StructView S, const double* __restrict__ x, double* __restrict__ xi,
+                              double* __restrict__ xc) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ni = S.n_img * 6;
+  if (t < ni) {
+    const int col = S.col_img[t];
+    xi[t] = col >= 0 ? x[col] : 0.0;
+  } else if (t < ni + S.n_cam * 12) {
+    const int col = S.col_cam[t - ni];
+    xc[t - ni] = col >= 0 ? x[col] : 0.0;
+  }
+}
+
+template <int DC>
+__device__ inline void LoadRow(const double2* __restrict__ F, int k, double2 (&row)[DC]) {
+  const double2* f = F + (size_t)k * DC;
+#pragma unroll
+  for (int j = 0; j < DC; ++j) row[j] = f[j];
+}
+
+// f = F_k * x  (2-vector), x in padded form
+template <int DC>
+__device__ inline double2 RowTimesX(const double2 (&row)[DC], const double* __restrict__ xi,
+                                    const double* __restrict__ xc, int i, int c) {
+  const double2* pi = reinterpret_cast<const double2*>(xi + 6 * (size_t)i);
+  double f0 = 0.0, f1 = 0.0;
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const double2 v = __ldg(pi + j);
+    f0 += row[2 * j].x * v.x + row[2 * j + 1].x * v.y;
+    f1 += row[2 * j].y * v.x + row[2 * j + 1].y * v.y;
+  }
+  if (DC > 6) {
+    const double2* pc = reinterpret_cast<const double2*>(xc + 12 * (size_t)c);
+#pragma unroll
+    for (int j = 0; j < (DC - 6) / 2; ++j) {
+      const double2 v = __ldg(pc + j);
+      f0 += row[6 + 2 * j].x * v.x + row[7 + 2 * j].x * v.y;
+      f1 += row[6 + 2 * j].y * v.x + row[7 + 2 * j].y * v.y;
+    }
+  }
+  return make_double2(f0, f1);
+}
+
+struct ERec { double E[6]; double r0, r1; };
+__device__ inline ERec LoadER(const double* __restrict__ ER, int k) {
+  const double2* p = reinterpret_cast<const double2*>(ER + (size_t)k * 8);
+  const double2 a = p[0], b = p[1], c = p[2], d = p[3];
+  ERec e;
+  e.E[0] = a.x; e.E[1] = a.y; e.E[2] = b.x; e.E[3] = b.y; e.E[4] = c.x; e.E[5] = c.y;
+  e.r0 = d.x; e.r1 = d.y;
+  return e;
+}
+
+// ---- point-side squared column norms (Jacobi scaling / LM diagonal) -----------------
+__global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileView T, const double* __restrict__ ER,
+                                                           double* __restrict__ np) {
+  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= T.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
+  if (n <= 32) {
+    const bool valid = lane < n;
+    const int k = s0 + lane;
+    const int pt = valid ? S.obs_pt[k] : -1 - lane;
+    double v[3] = {0.0, 0.0, 0.0};
+    if (valid) {
+      const ERec e = LoadER(ER, k);
+#pragma unroll
+      for (int a = 0; a < 3; ++a) v[a] = e.E[a] * e.E[a] + e.E[3 + a] * e.E[3 + a];
+    }
+    const Seg sg = MakeSeg(pt);
+    SegSum<3>(sg, v);
+    if (valid && sg.is_head) {
+      const int po = S.p_off[pt];
+      if (po >= 0) { np[3 * (size_t)po] = v[0]; np[3 * (size_t)po + 1] = v[1]; np[3 * (size_t)po + 2] = v[2]; }
+    }
+  } else {
+    const int pt = S.obs_pt[s0];
+    double v[3] = {0.0, 0.0, 0.0};
+    for (int k = s0 + lane; k < s0 + n; k += 32) {
+      const ERec e = LoadER(ER, k);
+#pragma unroll
+      for (int a = 0; a < 3; ++a) v[a] += e.E[a] * e.E[a] + e.E[3 + a] * e.E[3 + a];
+    }
+    WarpAllSum<3>(v);
+    const int po = S.p_off[pt];
+    if (lane == 0 && po >= 0) { np[3 * (size_t)po] = v[0]; np[3 * (size_t)po + 1] = v[1]; np[3 * (size_t)po + 2] = v[2]; }
+  }
+}
+
+// ---- point blocks: C_p = E^T E + D_p^2, its inverse, and g_p = E^T r -----------------
+__global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileView T, const double* __restrict__ ER,
+                                                           const double* __restrict__ Dp, double* __restrict__ Cinv,
+                                                           double* __restrict__ gp, DeviceScalars* sc) {
+  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= T.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
+  double v[9];
+#pragma unroll
+  for (int a = 0; a < 9; ++a) v[a] = 0.0;
+  auto accum = [&](const ERec& e) {
+    v[0] += e.E[0] * e.E[0] + e.E[3] * e.E[3];
+    v[1] += e.E[0] * e.E[1] + e.E[3] * e.E[4];
+    v[2] += e.E[0] * e.E[2] + e.E[3] * e.E[5];
+    v[3] += e.E[1] * e.E[1] + e.E[4] * e.E[4];
+    v[4] += e.E[1] * e.E[2] + e.E[4] * e.E[5];
+    v[5] += e.E[2] * e.E[2] + e.E[5] * e.E[5];
+    v[6] += e.E[0] * e.r0 + e.E[3] * e.r1;
+    v[7] += e.E[1] * e.r0 + e.E[4] * e.r1;
+    v[8] += e.E[2] * e.r0 + e.E[5] * e.r1;
+  };
+  int pt; bool writer;
+  if (n <= 32) {
+    const bool valid = lane < n;
+    pt = valid ? S.obs_pt[s0 + lane] : -1 - lane;
+    if (valid) accum(LoadER(ER, s0 + lane));
+    const Seg sg = MakeSeg(pt);
+    SegSum<9>(sg, v);
+    writer = valid && sg.is_head;
+  } else {
+    pt = S.obs_pt[s0];
+    for (int k = s0 + lane; k < s0 + n; k += 32) accum(LoadER(ER, k));
+    WarpAllSum<9>(v);
+    writer = lane == 0;
+  }
+  if (writer) {
+    const int po = S.p_off[pt];
+    if (po >= 0) {
+      const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
+      const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
+      double inv[6];
+      if (!InvertSym3(c, inv)) {
+        sc->solver_failed = 1;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) inv[a] = 0.0;
+      }
+#pragma unroll
+      for (int a = 0; a < 6; ++a) Cinv[6 * (size_t)po + a] = inv[a];
+      gp[3 * (size_t)po] = v[6]; gp[3 * (size_t)po + 1] = v[7]; gp[3 * (size_t)po + 2] = v[8];
+    }
+  }
+}
+
+// ---- e_k = r_k - E_k C_p^{-1} g_p  (right-hand side of the reduced system, before F^T) ----
+__global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const double* __restrict__ ER,
+                                                    const double* __restrict__ Cinv, const double* __restrict__ gp,
+                                                    double2* __restrict__ out) {
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  if (k >= S.n_obs) return;
+  const ERec e = LoadER(ER, k);
+  double e0 = e.r0, e1 = e.r1;
+  const int po = S.p_off[S.obs_pt[k]];
+  if (po >= 0) {
+    const double g[3] = {gp[3 * (size_t)po], gp[3 * (size_t)po + 1], gp[3 * (size_t)po + 2]};
+    double w[3];
+    Sym3Mul(Cinv + 6 * (size_t)po, g, w);
+    e0 -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
+    e1 -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+  }
+  out[k] = make_double2(e0, e1);
+}
+
+// ---- implicit Schur product, point pass:  g_k = F_k x - E_k C_p^{-1} sum_{j in p} E_j^T F_j x ----
+template <int DC>
+__global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileView T, const double* __restrict__ ER,
+                                                           const double2* __restrict__ F, const double* __restrict__ Cinv,
+                                                           const double* __restrict__ xi, const double* __restrict__ xc,
+                                                           double2* __restrict__ out) {
+  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= T.n_tiles) return;
+  const int lane = threadIdx.x & 31;
+  const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
+  if (n <= 32) {
+    const bool valid = lane < n;
+    const int k = s0 + lane;
+    int pt = -1 - lane;
+    double2 f = make_double2(0.0, 0.0);
+    ERec e;
+    double u[3] = {0.0, 0.0, 0.0};
+    if (valid) {
+      pt = S.obs_pt[k];
+      const int i = S.obs_img[k];
+      double2 row[DC];
+      LoadRow<DC>(F, k, row);
+      f = RowTimesX<DC>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0);
+      e = LoadER(ER, k);
+#pragma unroll
+      for (int a = 0; a < 3; ++a) u[a] = e.E[a] * f.x + e.E[3 + a] * f.y;
+    }
+    const Seg sg = MakeSeg(pt);
+    SegSum<3>(sg, u);
+    if (valid) {
+      const int po = S.p_off[pt];
+      if (po >= 0) {
+        double w[3];
+        Sym3Mul(Cinv + 6 * (size_t)po, u, w);
+        f.x -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
+        f.y -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+      }
+      out[k] = f;
+    }
+  } else {  // one long point: two strided passes
+    const int pt = S.obs_pt[s0];
+    const int po = S.p_off[pt];
+    double u[3] = {0.0, 0.0, 0.0};
+    for (int k = s0 + lane; k < s0 + n; k += 32) {
+      const int i = S.obs_img[k];
+      double2 row[DC];
+      LoadRow<DC>(F, k, row);
+      const double2 f = RowTimesX<DC>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0);
+      const ERec e = LoadER(ER, k);
+#pragma unroll
+      for (int a = 0; a < 3; ++a) u[a] += e.E[a] * f.x + e.E[3 + a] * f.y;
+      out[k] = f;
+    }
+    WarpAllSum<3>(u);
+    if (po >= 0) {
+      double w[3];
+      Sym3Mul(Cinv + 6 * (size_t)po, u, w);
+      for (int k = s0 + lane; k < s0 + n; k += 32) {
+        const ERec e = LoadER(ER, k);
+        double2 f = out[k];
+        f.x -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
+        f.y -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+        out[k] = f;
+      }
+    }
+  }
+}
+
+// ---- back-substitution y_p = C_p^{-1}(g_p - sum E^T F y_c), fused with the model cost change
+//      -(J step)^T (r + J step / 2), step = -y   ----
+template <int DC>
+__global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, const double* __restrict__ ER,
+                                                      const double2* __restrict__ F, const double* __restrict__ Cinv,
+                                                      const double* __restrict__ gp, const double* __restrict__ yi,
+                                                      const double* __restrict__ yc, double* __restrict__ yp,
+                                                      double* __restrict__ partial) {
+  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  double acc = 0.0;
+  if (tile < T.n_tiles) {
+    const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
+    if (n <= 32) {
+      const bool valid = lane < n;
+      const int k = s0 + lane;
+      int pt = -1 - lane;
+      double2 f = make_double2(0.0, 0.0);
+      ERec e;
+      double u[3] = {0.0, 0.0, 0.0};
+      if (valid) {
+        pt = S.obs_pt[k];
+        const int i = S.obs_img[k];
+        double2 row[DC];
+        LoadRow<DC>(F, k, row);
+        f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
+        e = LoadER(ER, k);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) u[a] = e.E[a] * f.x + e.E[3 + a] * f.y;
+      }
+      const Seg sg = MakeSeg(pt);
+      SegSum<3>(sg, u);
+      if (valid) {
+        const int po = S.p_off[pt];
+        double m0 = -f.x, m1 = -f.y;
+        if (po >= 0) {
+          const double d[3] = {gp[3 * (size_t)po] - u[0], gp[3 * (size_t)po + 1] - u[1], gp[3 * (size_t)po + 2] - u[2]};
+          double w[3];
+          Sym3Mul(Cinv + 6 * (size_t)po, d, w);
+          if (sg.is_head) { yp[3 * (size_t)po] = w[0]; yp[3 * (size_t)po + 1] = w[1]; yp[3 * (size_t)po + 2] = w[2]; }
+          m0 -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
+          m1 -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+        }
+        acc = m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
+      }
+    } else {
+      const int pt = S.obs_pt[s0];
+      const int po = S.p_off[pt];
+      double u[3] = {0.0, 0.0, 0.0};
+      for (int k = s0 + lane; k < s0 + n; k += 32) {
+        const int i = S.obs_img[k];
+        double2 row[DC];
+        LoadRow<DC>(F, k, row);
+        const double2 f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
+        const ERec e = LoadER(ER, k);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) u[a] += e.E[a] * f.x + e.E[3 + a] * f.y;
+      }
+      WarpAllSum<3>(u);
+      double w[3] = {0.0, 0.0, 0.0};
+      if (po >= 0) {
+        const double d[3] = {gp[3 * (size_t)po] - u[0], gp[3 * (size_t)po + 1] - u[1], gp[3 * (size_t)po + 2] - u[2]};
+        Sym3Mul(Cinv + 6 * (size_t)po, d, w);
+        if (lane == 0) { yp[3 * (size_t)po] = w[0]; yp[3 * (size_t)po + 1] = w[1]; yp[3 * (size_t)po + 2] = w[2]; }
+      }
+      for (int k = s0 + lane; k < s0 + n; k += 32) {
+        const int i = S.obs_img[k];
+        double2 row[DC];
+        LoadRow<DC>(F, k, row);
+        const double2 f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
+        const ERec e = LoadER(ER, k);
+        const double m0 = -f.x - (e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2]);
+        const double m1 = -f.y - (e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2]);
+        acc += m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
+      }
+    }
+  }
+  // block partial (4 warps)
+  __shared__ double sm[4];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+  if (lane == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) { partial[2 * blockIdx.x] = (sm[0] + sm[1]) + (sm[2] + sm[3]); partial[2 * blockIdx.x + 1] = 0.0; }
+}
+
+// ---- camera-side segmented reduction over image-major chunks ------------------------
+// MODE 0: F^T v (v per observation)   MODE 1: F^T r (r from ER)   MODE 2: column square norms
+template <int DC, int MODE>
+__global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const double2* __restrict__ F,
+                                                         const double* __restrict__ ER, const double2* __restrict__ v,
+                                                         double* __restrict__ partial) {
+  const int ch = blockIdx.x;
+  const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
+  double acc[DC];
+#pragma unroll
+  for (int j = 0; j < DC; ++j) acc[j] = 0.0;
+  if (threadIdx.x < n) {
+    const int k = C.cam_order[s0 + threadIdx.x];
+    double2 row[DC];
+    LoadRow<DC>(F, k, row);
+    if (MODE == 2) {
+#pragma unroll
+      for (int j = 0; j < DC; ++j) acc[j] = row[j].x * row[j].x + row[j].y * row[j].y;
+    } else {
+      const double2 w = MODE == 0 ? v[k] : reinterpret_cast<const double2*>(ER + (size_t)k * 8)[3];
+#pragma unroll
+      for (int j = 0; j < DC; ++j) acc[j] = row[j].x * w.x + row[j].y * w.y;
+    }
+  }
+  __shared__ double sm[8][DC];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < DC; ++j) {
+    double a = acc[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+    if (lane == 0) sm[w][j] = a;
+  }
+  __syncthreads();
+  if (threadIdx.x < DC) {
+    double a = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a += sm[i][threadIdx.x];
+    partial[(size_t)ch * DC + threadIdx.x] = a;
+  }
+}
+
+// sums the chunk partials of each image (pose slots) / each camera (intrinsics slots)
+// in a fixed order into the compact camera-space vector; optionally adds D_c^2 x.
+__global__ void __launch_bounds__(128) cam_finalize_kernel(StructView S, ChunkView C, const double* __restrict__ partial,
+                                                           double* __restrict__ out, const double* __restrict__ Dc,
+                                                           const double* __restrict__ x) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ni = S.n_img * 6;
+  int col; double a = 0.0;
+  if (t < ni) {
+    col = S.col_img[t];
+    if (col < 0) return;
+    const int i = t / 6, j = t - 6 * i;
+    for (int ch = C.img_chunk_ptr[i]; ch < C.img_chunk_ptr[i + 1]; ++ch) a += partial[(size_t)ch * S.dc + j];
+  } else if (t < ni + S.n_cam * 12) {
+    const int u = t - ni;
+    col = S.col_cam[u];
+    if (col < 0) return;
+    const int c = u / 12, j = u - 12 * c;
+    for (int q = C.cam_img_ptr[c]; q < C.cam_img_ptr[c + 1]; ++q) {
+      const int i = C.cam_img_list[q];
+      for (int ch = C.img_chunk_ptr[i]; ch < C.img_chunk_ptr[i + 1]; ++ch) a += partial[(size_t)ch * S.dc + 6 + j];
+    }
+  } else {
+    return;
+  }
+  if (Dc) a += Dc[col] * Dc[col] * x[col];
+  out[col] = a;
+}
+
+__global__ void add_diag_kernel(int n, double* __restrict__ y, const double* __restrict__ Dc, const double* __restrict__ x) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) y[j] += Dc[j] * Dc[j] * x[j];
+}
+
+// ---- Jacobi scaling ---------------------------------------------
+__global__ void jacobi_scale_kernel(int n, const double* __restrict__ sqnorm, double* __restrict__ scale) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) scale[j] = 1.0 / (1.0 + sqrt(sqnorm[j]));
+}
+template <int DC>
+__global__ void __launch_bounds__(256) scale_jacobian_kernel(StructView S, const double* __restrict__ si,
+                                                             const double* __restrict__ sc, const double* __restrict__ sp,
+                                                             double2* __restrict__ F, double* __restrict__ ER) {
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  if (k >= S.n_obs) return;
+  const int i = S.obs_img[k];
+  double2* f = F + (size_t)k * DC;
+#pragma unroll
+  for (int j = 0; j < 6; ++j) { const double s = si[6 * (size_t)i + j]; double2 v = f[j]; v.x *= s; v.y *= s; f[j] = v; }
+  if (DC > 6) {
+    const int c = S.img_cam[i];
+#pragma unroll
+    for (int j = 6; j < DC; ++j) { const double s = sc[12 * (size_t)c + j - 6]; double2 v = f[j]; v.x *= s; v.y *= s; f[j] = v; }
+  }
+  const int po = S.p_off[S.obs_pt[k]];
+  if (po >= 0) {
+    double* e = ER + (size_t)k * 8;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { const double s = sp[3 * (size_t)po + a]; e[a] *= s; e[3 + a] *= s; }
+  }
+}
+
+// LM diagonal: diag = clamp(colnorm^2), D = sqrt(diag / radius)
+__global__ void lm_diag_kernel(int n, const double* __restrict__ sqnorm, double* __restrict__ diag, double* __restrict__ D,
+                               int refresh, double lo, double hi, const DeviceScalars* sc) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double d = diag[j];
+  if (refresh) { d = fmin(fmax(sqnorm[j], lo), hi); diag[j] = d; }
+  D[j] = sqrt(d / sc->radius);
+}
+
+// max |g_j / scale_j| over a vector -> partial maxima
+__global__ void __launch_bounds__(256) absmax_kernel(int n, const double* __restrict__ g, const double* __restrict__ scale,
+                                                     double* __restrict__ partial) {
+  double m = 0.0;
+  for (int j = blockIdx.x * 256 + threadIdx.x; j < n; j += gridDim.x * 256) m = fmax(m, fabs(scale ? g[j] / scale[j] : g[j]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_down_sync(0xffffffffu, m, o));
+  __shared__ double sm[8];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < 8; ++i) m = fmax(m, sm[i]);
+    partial[blockIdx.x] = m;
+  }
+}
+__global__ void absmax_final_kernel(int n, const double* __restrict__ partial, double* out, int accumulate) {
+  double m = accumulate ? *out : 0.0;
+  for (int i = 0; i < n; ++i) m = fmax(m, partial[i]);
+  *out = m;
+}
+__global__ void sum_partial_neg_kernel(int n, const double* __restrict__ partial, double* out) {
+  // fixed-order sum of partial[2*i]; writes the negated total (model cost change)
+  __shared__ double sm[32];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < n; i += 1024) a += partial[2 * i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    a = sm[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+    if (threadIdx.x == 0) *out = -a;
+  }
+}
+}  // namespace sba

@@ -1,0 +1,188 @@
+// Host-side state of one bundle-adjustment problem resident on one B200.
+// The drop-in boundary is include/sba_b200.h; this struct is what sba_handle points at.
+// Reference path: BundleAdjuster::SetUp + ceres::Solve,
+//   /root/reference/src/optim/bundle_adjustment.cc:326-530, :306.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+
+namespace sba {
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { Free(); }
+  void Free() {
+    if (p) cudaFree(p);
+    p = nullptr; n = 0;
+  }
+  cudaError_t Alloc(size_t count) {
+    if (count <= n && p) return cudaSuccess;
+    Free();
+    n = count;
+    return cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
+  }
+  cudaError_t Upload(const std::vector<T>& h, cudaStream_t s) {
+    cudaError_t e = Alloc(h.size());
+    if (e != cudaSuccess) return e;
+    if (h.empty()) return cudaSuccess;
+    return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+  }
+  cudaError_t Zero(cudaStream_t s) { return cudaMemsetAsync(p, 0, (n ? n : 1) * sizeof(T), s); }
+};
+
+// scalar block shared between kernels and polled by the host once per LM
+// iteration (trust-region bookkeeping stays on the device).
+struct DeviceScalars {
+  double cost;              // 0.5 sum rho (active blocks), current linearisation point
+  double fixed_cost;        // blocks with only constant parameters
+  double cand_cost;         // candidate cost
+  double model_cost_change;
+  double radius;
+  double decrease_factor;
+  double relative_decrease;
+  double step_norm;
+  double x_norm;
+  double gradient_max_norm;
+  double cost_change;
+  int step_valid;
+  int step_accepted;
+  int reuse_diagonal;
+  int solver_failed;
+  // PCG scalars
+  double cg_rho, cg_last_rho, cg_alpha, cg_beta, cg_pq, cg_Q0, cg_Q1, cg_zeta, cg_norm_b;
+  int cg_iter;
+  int cg_state;  // 0 running, 1 converged, 2 no-convergence stop, 3 failure
+  // Cholesky
+  int chol_fail;
+  int converged;  // 1 parameter tolerance, 2 function tolerance reached in this iteration
+  // squared norms for step_norm / x_norm: camera-side (replicated) and point-side (sharded)
+  double step2_c, x2_c, step2_p, x2_p;
+};
+
+class Comm;  // NCCL wrapper (comm.cu)
+
+struct Problem {
+  // ---- sizes ----
+  int n_img = 0, n_cam = 0, n_pt = 0;  // global images / cameras, LOCAL points
+  int n_obs = 0;                       // LOCAL observations
+  int64_t n_obs_global = 0;
+  int n_pt_global = 0;
+  int dc = 6, kmax = 0, n_cdim = 0, n_pvar = 0;
+  int uniform_model = -1;  // camera model shared by all used cameras, else -1
+  int shard_rank = 0, shard_count = 1;
+  bool shared_intrinsics = false;  // some camera with free intrinsics is used by >1 image
+
+  // ---- host copies of structure (small) ----
+  std::vector<int> h_img_cam, h_model, h_col_img, h_col_cam, h_k_cols, h_k_slot, h_k_dim, h_p_off;
+  std::vector<int> h_blk_off, h_blk_dim;       // SCHUR_JACOBI parameter blocks (compact cols)
+  std::vector<int> h_obs_img, h_obs_pt;        // local, point-sorted
+  std::vector<int64_t> h_local2ref;            // local point-sorted position -> reference residual index
+  std::vector<int> h_pt_local2global;          // local point -> global point
+  std::vector<uint8_t> h_pose_const;
+  std::vector<int> h_t_dim;
+  sba_summary counts;                          // structural counts (global problem)
+  std::vector<sba_iteration_summary> trace;
+
+  // ---- device: structure ----
+  DevBuf<int> d_img_cam, d_model, d_col_img, d_col_cam, d_k_cols, d_k_slot, d_k_dim, d_p_off;
+  DevBuf<int> d_obs_img, d_obs_pt;
+  DevBuf<double> d_obs_xy;
+  DevBuf<uint8_t> d_obs_active, d_pose_const;
+  DevBuf<int> d_tile_start;  int n_tiles = 0;
+  DevBuf<int> d_chunk_start, d_chunk_img, d_cam_order, d_img_chunk_ptr, d_cam_img_ptr, d_cam_img_list;
+  int n_chunks = 0;
+  DevBuf<int> d_pt_ptr;      // [n_pt+1] CSR over point-sorted observations
+  DevBuf<int> d_blk_off, d_blk_dim, d_col_blk;  int n_blk = 0;
+
+  // reduced-camera-matrix block entries (dense S) and diagonal entries (SCHUR_JACOBI)
+  DevBuf<int> d_pair_key_ptr, d_pair_a, d_pair_b, d_pair_key_gi, d_pair_key_gj;  int n_pair_keys = 0; int64_t n_pairs = 0;
+  DevBuf<int> d_diag_key_ptr, d_diag_a, d_diag_b;                                 int64_t n_diag_pairs = 0;
+  bool pairs_built = false, diag_built = false;
+
+  // ---- device: parameters (current / candidate) ----
+  DevBuf<double> d_pose, d_cam, d_X, d_pose2, d_cam2, d_X2;
+
+  // ---- device: linearisation ----
+  DevBuf<double> d_ER;   // [n_obs*8]
+  DevBuf<double2> d_F;   // [n_obs*dc]
+  DevBuf<double> d_cost_partial;  // [blocks*2]
+  DevBuf<double> d_scale_c, d_scale_p;      // Jacobi scaling
+  DevBuf<double> d_diag_c, d_diag_p;        // clamped column square norms
+  DevBuf<double> d_Dc, d_Dp;                // LM diagonal
+  DevBuf<double> d_Cinv, d_gp;              // [n_pvar*6] sym inverse, [n_pvar*3]
+  DevBuf<double> d_chunk_partial;           // [n_chunks*dc] (or dc*dc for block sums)
+  DevBuf<double> d_g2;                      // [n_obs*2] per-observation 2-vector scratch
+  DevBuf<double> d_rhs, d_yc, d_yp, d_step_c, d_grad_c, d_grad_p, d_tmp_c;
+  DevBuf<double> d_S;                       // dense reduced camera matrix [n_cdim^2]
+  DevBuf<double> d_Linv;                    // inverted diagonal blocks of the Cholesky factor
+  DevBuf<double> d_Minv;                    // SCHUR_JACOBI inverse blocks
+  DevBuf<double> d_cg_r, d_cg_z, d_cg_p, d_cg_q, d_cg_x;
+  DevBuf<double> d_xi, d_xc;                // padded camera-space vector (n_img*6 | n_cam*12)
+  DevBuf<double> d_scale_i, d_scale_k;      // padded Jacobi scale
+  DevBuf<double> d_sq_c, d_sq_p;            // raw column square norms
+  DevBuf<double> d_red;                     // small reduction scratch (>= 1024 doubles)
+  int n_partial = 0;                        // capacity (pairs) of d_cost_partial
+  DevBuf<DeviceScalars> d_scalars;
+  DeviceScalars* h_scalars = nullptr;       // pinned
+
+  cudaStream_t stream = nullptr;
+  int device = 0;
+  int64_t launches = 0;
+  bool solved = false;
+  bool linearized = false;
+  Comm* comm = nullptr;
+
+  // stage timers
+  double t_eval = 0, t_elim = 0, t_solve = 0, t_update = 0;
+
+  ~Problem();
+  ParamsView Params(bool candidate = false) const;
+  StructView Struct() const;
+  TileView Tiles() const;
+  ChunkView Chunks() const;
+};
+
+// problem.cu
+int BuildProblem(const sba_problem_desc* d, Problem** out, bool host_only);
+int ProblemCounts(const sba_problem_desc* d, sba_summary* s);
+// eval.cu
+int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate);
+int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost /* &scalars->cand_cost */);
+// linalg.cu (column norms, point blocks, rhs, matvec, back-substitution, update)
+int ColumnNorms(Problem* p, double* d_nc, double* d_np);
+int Gradient(Problem* p, double* d_gc, double* d_gp);
+int InitJacobiScale(Problem* p);
+int PrepareLMDiagonal(Problem* p, const sba_solver_options& o);
+int PointBlocks(Problem* p);
+int ReducedRhs(Problem* p);
+int SchurMatVec(Problem* p, const double* d_x, double* d_y);
+int BackSubstitute(Problem* p);
+int ModelCostChange(Problem* p);
+int ApplyStep(Problem* p);
+int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase);
+int AllReduceSum(Problem* p, double* d_buf, size_t n);
+// schur.cu
+int BuildPairLists(Problem* p, bool dense);
+int BuildDenseSchur(Problem* p);
+int BuildSchurJacobi(Problem* p);
+// cholesky.cu
+int CholeskySolve(Problem* p);  // d_S, d_rhs -> d_yc ; sets scalars.chol_fail
+// pcg.cu
+int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
+// lm.cu
+int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, void* user, sba_summary* s);
+// comm.cu
+int CommGetUniqueId(void* id128);
+int CommInit(Problem* p, int nranks, int rank, const void* id128);
+void CommDestroy(Problem* p);
+
+}  // namespace sba
