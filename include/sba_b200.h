@@ -214,6 +214,10 @@ typedef int (*sba_iteration_callback)(const sba_iteration_summary* it, void* use
 /* --- lifecycle ---------------------------------------------------------- */
 void sba_default_solver_options(sba_solver_options* o);
 int sba_create(const sba_problem_desc* desc, sba_handle** out);
+/* Host-only: the structural counts Ceres reports for this problem (Solver::Summary
+ * num_residuals_reduced, num_effective_parameters_reduced, ... as pinned by
+ * src/optim/bundle_adjustment_test.cc:186-645).  Needs no device. */
+int sba_problem_counts(const sba_problem_desc* desc, sba_summary* counts);
 void sba_destroy(sba_handle* h);
 const char* sba_last_error(void);
 const char* sba_version(void);

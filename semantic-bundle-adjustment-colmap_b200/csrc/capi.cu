@@ -1,0 +1,311 @@
+// extern "C" surface declared in include/sba_b200.h: the drop-in boundary behind
+//   BundleAdjuster::Solve   /root/reference/src/optim/bundle_adjustment.cc:258-320
+// No Eigen / Ceres / torch types cross it.  There is no CPU fallback: every compute entry
+// point needs a CUDA device and says so when there is none.
+#include <algorithm>
+#include <cstdio>
+#include <functional>
+
+#include "device_math.cuh"
+#include "solver.h"
+
+namespace sba {
+const char* LastErrorMessage();
+void ShardPointRange(const std::vector<int64_t>& pt_obs_prefix, int nranks, int rank, int* p0, int* p1);
+}  // namespace sba
+
+using namespace sba;
+
+struct sba_handle {
+  Problem* p;
+};
+
+extern "C" {
+
+void sba_default_solver_options(sba_solver_options* o) {
+  // src/optim/bundle_adjustment.h:78-93 on top of ceres::Solver::Options 2.1.0 defaults
+  std::memset(o, 0, sizeof(*o));
+  o->linear_solver_type = SBA_SOLVER_AUTO;
+  o->num_config_images = 0;
+  o->max_num_iterations = 100;
+  o->max_linear_solver_iterations = 200;
+  o->min_linear_solver_iterations = 0;
+  o->max_num_consecutive_invalid_steps = 10;
+  o->function_tolerance = 0.0;
+  o->gradient_tolerance = 0.0;
+  o->parameter_tolerance = 0.0;
+  o->loss_function_type = SBA_LOSS_TRIVIAL;
+  o->loss_function_scale = 1.0;
+  o->initial_trust_region_radius = 1e4;
+  o->max_trust_region_radius = 1e16;
+  o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3;
+  o->min_lm_diagonal = 1e-6;
+  o->max_lm_diagonal = 1e32;
+  o->eta = 1e-1;
+  o->jacobi_scaling = 1;
+  o->update_state_every_iteration = 0;
+}
+
+const char* sba_last_error(void) { return LastErrorMessage(); }
+const char* sba_version(void) { return "sba_b200 0.1 (sm_100a, fp64)"; }
+
+int sba_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int sba_problem_counts(const sba_problem_desc* desc, sba_summary* counts) {
+  if (!counts) { SetError(SBA_ERR_INVALID_ARGUMENT, "null output"); return SBA_ERR_INVALID_ARGUMENT; }
+  return ProblemCounts(desc, counts);
+}
+
+int sba_create(const sba_problem_desc* desc, sba_handle** out) {
+  if (!out) { SetError(SBA_ERR_INVALID_ARGUMENT, "null output handle"); return SBA_ERR_INVALID_ARGUMENT; }
+  *out = nullptr;
+  Problem* p = nullptr;
+  const int rc = BuildProblem(desc, &p, false);
+  if (rc) return rc;
+  *out = new sba_handle{p};
+  return SBA_OK;
+}
+
+void sba_destroy(sba_handle* h) {
+  if (!h) return;
+  delete h->p;
+  delete h;
+}
+
+static int CheckHandle(sba_handle* h) {
+  if (!h || !h->p) { SetError(SBA_ERR_INVALID_ARGUMENT, "null handle"); return SBA_ERR_INVALID_ARGUMENT; }
+  return SBA_OK;
+}
+
+int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t apply_loss, double* cost,
+                 double* residuals, double* jac_pose, double* jac_intr, double* jac_point,
+                 double* jac_qvec_ambient, double* sem_residuals) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  cudaStream_t st = p->stream;
+  const int n = p->n_obs, dc = p->dc;
+  DevBuf<double> d_jq;
+  if (jac_qvec_ambient) { SBA_CUDA(d_jq.Alloc((size_t)std::max(1, n) * 8)); p->jq_out = d_jq.p; }
+  const LossView loss = {loss_type, loss_scale, apply_loss ? 1 : 0};
+  rc = LaunchEvaluate(p, loss, false, false);
+  p->jq_out = nullptr;
+  if (rc) return rc;
+  std::vector<double> ER((size_t)n * 8), F((size_t)n * dc * 2), JQ;
+  if (n > 0) {
+    SBA_CUDA(cudaMemcpyAsync(ER.data(), p->d_ER.p, ER.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaMemcpyAsync(F.data(), p->d_F.p, F.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (jac_qvec_ambient) {
+      JQ.resize((size_t)n * 8);
+      SBA_CUDA(cudaMemcpyAsync(JQ.data(), d_jq.p, JQ.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
+  }
+  SBA_CUDA(cudaMemcpyAsync(p->h_scalars, p->d_scalars.p, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, st));
+  SBA_CUDA(cudaStreamSynchronize(st));
+  if (cost) *cost = p->h_scalars->cost + p->h_scalars->fixed_cost;
+  for (int k = 0; k < n; ++k) {
+    const int64_t r = p->h_local2ref[k];
+    const int i = p->h_obs_img[k], c = p->h_img_cam[i];
+    const double* er = &ER[(size_t)k * 8];
+    const double* f = &F[(size_t)k * dc * 2];  // double2[dc]: (d r0, d r1) per slot
+    if (residuals) { residuals[2 * r] = er[6]; residuals[2 * r + 1] = er[7]; }
+    if (jac_point) {
+      for (int j = 0; j < 6; ++j) jac_point[6 * r + j] = er[j];
+    }
+    if (jac_pose) {
+      for (int j = 0; j < 6; ++j) { jac_pose[12 * r + j] = f[2 * j]; jac_pose[12 * r + 6 + j] = f[2 * j + 1]; }
+    }
+    if (jac_intr) {
+      double* out = &jac_intr[(size_t)r * 2 * SBA_MAX_CAMERA_PARAMS];
+      for (int j = 0; j < 2 * SBA_MAX_CAMERA_PARAMS; ++j) out[j] = 0.0;
+      for (int s = 0; s < p->h_k_dim[c] && 6 + s < dc; ++s) {
+        const int a = p->h_k_cols[12 * (size_t)c + s];
+        out[a] = f[2 * (6 + s)]; out[SBA_MAX_CAMERA_PARAMS + a] = f[2 * (6 + s) + 1];
+      }
+    }
+    if (jac_qvec_ambient) for (int j = 0; j < 8; ++j) jac_qvec_ambient[8 * r + j] = JQ[(size_t)k * 8 + j];
+  }
+  if (sem_residuals) {
+    rc = EvaluateSemanticRows(p, sem_residuals);
+    if (rc) return rc;
+  }
+  return SBA_OK;
+}
+
+int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callback cb, void* user,
+              sba_summary* summary) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  if (!summary) { SetError(SBA_ERR_INVALID_ARGUMENT, "null summary"); return SBA_ERR_INVALID_ARGUMENT; }
+  sba_solver_options o;
+  if (opts) o = *opts; else sba_default_solver_options(&o);
+  if (o.max_num_iterations < 0 || o.max_linear_solver_iterations < 0 || !(o.initial_trust_region_radius > 0.0) ||
+      !(o.loss_function_scale > 0.0) || o.loss_function_type < 0 || o.loss_function_type > SBA_LOSS_CAUCHY ||
+      o.linear_solver_type < SBA_SOLVER_AUTO || o.linear_solver_type > SBA_ITERATIVE_SCHUR) {
+    // Solver::Options::IsValid / BundleAdjustmentOptions::Check (bundle_adjustment.cc:70-73, 303-304)
+    SetError(SBA_ERR_INVALID_ARGUMENT, "invalid solver options");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  return SolveLM(h->p, &o, cb, user, summary);
+}
+
+int sba_get_trace(sba_handle* h, sba_iteration_summary* rows, int32_t cap, int32_t* n) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  const int m = std::min<int>(cap, (int)h->p->trace.size());
+  for (int i = 0; i < m; ++i) rows[i] = h->p->trace[i];
+  if (n) *n = m;
+  return SBA_OK;
+}
+
+int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec, double* camera_params, double* points) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  cudaStream_t st = p->stream;
+  std::vector<double> pose((size_t)p->n_img * 8), X((size_t)p->n_pt * 3);
+  if ((image_qvec || image_tvec) && p->n_img > 0)
+    SBA_CUDA(cudaMemcpyAsync(pose.data(), p->d_pose.p, pose.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (camera_params && p->n_cam > 0)
+    SBA_CUDA(cudaMemcpyAsync(camera_params, p->d_cam.p, (size_t)p->n_cam * 12 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (points && p->n_pt > 0)
+    SBA_CUDA(cudaMemcpyAsync(X.data(), p->d_X.p, X.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  SBA_CUDA(cudaStreamSynchronize(st));
+  for (int i = 0; i < p->n_img; ++i) {
+    if (image_qvec) for (int j = 0; j < 4; ++j) image_qvec[4 * (size_t)i + j] = pose[8 * (size_t)i + j];
+    if (image_tvec) for (int j = 0; j < 3; ++j) image_tvec[3 * (size_t)i + j] = pose[8 * (size_t)i + 4 + j];
+  }
+  if (points)
+    for (int q = 0; q < p->n_pt; ++q)
+      for (int a = 0; a < 3; ++a) points[3 * (size_t)p->h_pt_local2global[q] + a] = X[3 * (size_t)q + a];
+  return SBA_OK;
+}
+
+int64_t sba_kernel_launch_count(sba_handle* h) { return (h && h->p) ? h->p->launches : 0; }
+
+// ---- stage benchmarks --------------------------------------------------------------------
+static int PrepareLinearSystem(Problem* p, const sba_solver_options& o) {
+  DeviceScalars* hs = p->h_scalars;
+  std::memset(hs, 0, sizeof(*hs));
+  hs->radius = o.initial_trust_region_radius;
+  hs->decrease_factor = 2.0;
+  SBA_CUDA(cudaMemcpyAsync(p->d_scalars.p, hs, sizeof(*hs), cudaMemcpyHostToDevice, p->stream));
+  const LossView loss = {o.loss_function_type, o.loss_function_scale, 1};
+  int rc;
+  if ((rc = FillOnes(p))) return rc;
+  if ((rc = LaunchEvaluate(p, loss, false, false))) return rc;
+  if ((rc = PointBlocks(p, true))) return rc;
+  if ((rc = Gradient(p))) return rc;
+  if ((rc = InitJacobiScale(p))) return rc;
+  if ((rc = PrepareLMDiagonal(p, o))) return rc;
+  if ((rc = PointBlocks(p, false))) return rc;
+  if ((rc = ReducedRhs(p))) return rc;
+  SBA_CUDA(cudaStreamSynchronize(p->stream));
+  return SBA_OK;
+}
+
+int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms_per_launch, int64_t* algorithmic_bytes) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  if (!stage || repeat <= 0) { SetError(SBA_ERR_INVALID_ARGUMENT, "bad stage / repeat"); return SBA_ERR_INVALID_ARGUMENT; }
+  sba_solver_options o;
+  sba_default_solver_options(&o);
+  const std::string s(stage);
+  const LossView loss = {SBA_LOSS_TRIVIAL, 1.0, 1};
+  const int64_t n_obs = p->n_obs, dc = p->dc;
+  const int64_t gathers = (int64_t)p->n_img * 64 + (int64_t)p->n_cam * 96 + (int64_t)p->n_pt * 24;
+  std::function<int()> prep = []() { return SBA_OK; }, run;
+  int64_t bytes = 0;
+  if (s == "eval") {
+    run = [&]() { return LaunchEvaluate(p, loss, true, false); };
+    // idx 8 + xy 16 in; r 16 + J 16*(dc+3) out; + parameter gathers once
+    bytes = n_obs * (8 + 16 + 16 + 16 * (dc + 3)) + gathers;
+  } else if (s == "cost") {
+    run = [&]() { return LaunchCostOnly(p, loss, false, &p->d_scalars.p->cand_cost); };
+    bytes = n_obs * 24 + gathers;
+  } else if (s == "point_blocks") {
+    run = [&]() { return PointBlocks(p, false); };
+    bytes = n_obs * (64 + 4) + (int64_t)p->n_pvar * (24 + 48 + 24);
+  } else if (s == "rhs") {
+    run = [&]() { return ReducedRhs(p); };
+    bytes = n_obs * (64 + 16 * dc + 16 + 16 + 8);
+  } else if (s == "matvec") {
+    run = [&]() { return SchurMatVec(p, p->d_rhs.p, p->d_tmp_c.p); };
+    // two passes over the stored F (16*dc) + E (48) per observation + 48 B / point
+    bytes = n_obs * (2 * 16 * (dc + 3)) + (int64_t)p->n_pvar * 48;
+  } else if (s == "backsub") {
+    run = [&]() { return BackSubstitute(p); };
+    bytes = n_obs * (64 + 16 * dc + 8) + (int64_t)p->n_pvar * (48 + 24 + 24);
+  } else if (s == "schur_dense") {
+    run = [&]() { return BuildDenseSchur(p); };
+    bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 96 + 8 * (int64_t)p->n_cdim * p->n_cdim;
+  } else if (s == "schur_jacobi") {
+    run = [&]() { return BuildSchurJacobi(p); };
+    bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 48;
+  } else if (s == "cholesky") {
+    prep = [&]() { return BuildDenseSchur(p); };
+    run = [&]() { return CholeskySolve(p); };
+    bytes = 8 * (int64_t)p->n_cdim * p->n_cdim;  // flops are n^3/3; bytes reported for completeness
+  } else {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "unknown stage: " + s);
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  if ((rc = PrepareLinearSystem(p, o))) return rc;
+  const size_t flush_bytes = 256u << 20;  // > 126 MB L2
+  SBA_CUDA(p->d_flush.Alloc(flush_bytes));
+  cudaEvent_t e0, e1;
+  SBA_CUDA(cudaEventCreate(&e0)); SBA_CUDA(cudaEventCreate(&e1));
+  double total = 0.0;
+  for (int it = -1; it < repeat; ++it) {  // it == -1: untimed warm-up
+    if ((rc = prep())) return rc;
+    SBA_CUDA(cudaMemsetAsync(p->d_flush.p, it & 0xff, flush_bytes, p->stream));
+    SBA_CUDA(cudaEventRecord(e0, p->stream));
+    if ((rc = run())) return rc;
+    SBA_CUDA(cudaEventRecord(e1, p->stream));
+    SBA_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    SBA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    if (it >= 0) total += ms;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (ms_per_launch) *ms_per_launch = total / repeat;
+  if (algorithmic_bytes) *algorithmic_bytes = bytes;
+  return SBA_OK;
+}
+
+// ---- multi-GPU ------------------------------------------------------------------------------
+int sba_comm_get_unique_id(void* id128) { return CommGetUniqueId(id128); }
+int sba_comm_init(sba_handle* h, int32_t nranks, int32_t rank, const void* id128) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  return CommInit(h->p, nranks, rank, id128);
+}
+
+int sba_shard_points(const sba_problem_desc* d, int32_t nranks, int32_t rank, uint8_t* point_keep, uint8_t* obs_keep) {
+  if (!d || nranks <= 0 || rank < 0 || rank >= nranks) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "bad shard arguments");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  const int n_pt = d->num_points;
+  std::vector<int64_t> prefix(n_pt + 1, 0);
+  for (int64_t k = 0; k < d->num_observations; ++k) {
+    const int q = d->obs_point[k];
+    if (q < 0 || q >= n_pt) { SetError(SBA_ERR_INVALID_ARGUMENT, "observation index out of range"); return SBA_ERR_INVALID_ARGUMENT; }
+    prefix[q + 1]++;
+  }
+  for (int q = 0; q < n_pt; ++q) prefix[q + 1] += prefix[q];
+  int p0, p1;
+  ShardPointRange(prefix, nranks, rank, &p0, &p1);
+  if (point_keep) for (int q = 0; q < n_pt; ++q) point_keep[q] = (q >= p0 && q < p1) ? 1 : 0;
+  if (obs_keep)
+    for (int64_t k = 0; k < d->num_observations; ++k) obs_keep[k] = (d->obs_point[k] >= p0 && d->obs_point[k] < p1) ? 1 : 0;
+  return SBA_OK;
+}
+
+}  // extern "C"

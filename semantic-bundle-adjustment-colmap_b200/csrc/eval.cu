@@ -244,13 +244,12 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
   BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
 }
 
-double* g_Jq_ambient_out = nullptr;  // set by sba_evaluate for the parity surface only
 
 template <int MODEL>
 static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
   eval_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(
       p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_c.p : nullptr,
-      use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, g_Jq_ambient_out);
+      use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, p->jq_out);
 }
 template <int MODEL>
 static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks) {
@@ -279,7 +278,7 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
   p->launches++;
   SBA_CUDA(cudaGetLastError());
   p->linearized = true;
-  return SBA_OK;
+  return AllReduceSum(p, &p->d_scalars.p->cost, 2);  // cost, fixed_cost are adjacent
 }
 
 int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost) {
@@ -293,7 +292,7 @@ int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_o
   finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, blocks, d_out_cost, nullptr, 1.0);
   p->launches++;
   SBA_CUDA(cudaGetLastError());
-  return SBA_OK;
+  return AllReduceSum(p, d_out_cost, 1);
 }
 
 }  // namespace sba

@@ -2,6 +2,7 @@
 // and the device-resident trust-region bookkeeping.
 // Reference: the inside of ceres::Solve as called at
 //   /root/reference/src/optim/bundle_adjustment.cc:306   (SURVEY.md App. B.3-B.5).
+#include "device_math.cuh"
 #include "linalg_kernels.cuh"
 #include "reduce.cuh"
 
@@ -72,21 +73,35 @@ int InitJacobiScale(Problem* p) {
   return SBA_OK;
 }
 
-// gradient max-norm of the UNSCALED problem: max |(J^T r)_j| = max |g_scaled_j / scale_j|
-int Gradient(Problem* p, double* d_gc, double* d_gp_unused) {
-  (void)d_gp_unused;
-  int rc = CamReduce(p, 1, nullptr, d_gc, nullptr, nullptr);
+// gradient max-norm of the UNSCALED problem: max |(J^T r)_j| = max |g_scaled_j / scale_j|.
+// The point part g_p = E^T r must be current (PointBlocks).
+int Gradient(Problem* p) {
+  int rc = CamReduce(p, 1, nullptr, p->d_grad_c.p, nullptr, nullptr);
   if (rc) return rc;
   double* out = &p->d_scalars.p->gradient_max_norm;
-  const bool scaled = true;
   int nb = std::min(1024, std::max(1, DivUp(p->n_cdim, 256)));
-  absmax_kernel<<<nb, 256, 0, p->stream>>>(p->n_cdim, d_gc, scaled ? p->d_scale_c.p : nullptr, p->d_red.p);
+  absmax_kernel<<<nb, 256, 0, p->stream>>>(p->n_cdim, p->d_grad_c.p, p->d_scale_c.p, p->d_red.p);
   absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 0);
-  // point part: g_p = E^T r is produced by PointBlocks (d_gp); caller guarantees it is current
   nb = std::min(1024, std::max(1, DivUp(3 * p->n_pvar, 256)));
   absmax_kernel<<<nb, 256, 0, p->stream>>>(3 * p->n_pvar, p->d_gp.p, p->d_scale_p.p, p->d_red.p);
   absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 1);
   p->launches += 4;
+  SBA_CUDA(cudaGetLastError());
+  return AllReduceMax(p, out, 1);
+}
+
+__global__ void fill_kernel(int n, double* __restrict__ x, double v) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) x[j] = v;
+}
+int FillOnes(Problem* p) {
+  auto fill = [&](double* x, size_t n) {
+    if (n == 0) return;
+    fill_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, x, 1.0);
+    p->launches++;
+  };
+  fill(p->d_scale_c.p, p->n_cdim); fill(p->d_scale_p.p, 3 * (size_t)p->n_pvar);
+  fill(p->d_scale_i.p, 6 * (size_t)p->n_img); fill(p->d_scale_k.p, 12 * (size_t)p->n_cam);
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }
@@ -111,10 +126,12 @@ int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
   return SBA_OK;
 }
 
-int PointBlocks(Problem* p) {
+// grad_only: only g_p = E^T r (no LM diagonal needed yet)
+int PointBlocks(Problem* p, bool grad_only) {
   if (p->n_pvar > 0 && p->n_tiles > 0) {
-    point_blocks_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_Dp.p,
-                                                                   p->d_Cinv.p, p->d_gp.p, p->d_scalars.p);
+    point_blocks_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p,
+                                                                   grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
+                                                                   p->d_gp.p, p->d_scalars.p);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
@@ -212,7 +229,7 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
       for (int j = 0; j < 12; ++j) prm[j] = P.cam[12 * (size_t)c + j];
       const int kd = S.k_dim[c];
       if (kd > 0 && S.col_cam[12 * (size_t)c] >= 0) {
-        const int np = ModelNumParamsDev(S.model[c]);
+        const int np = ModelNumParams(S.model[c]);
         for (int j = 0; j < np; ++j) x2 += prm[j] * prm[j];
         for (int j = 0; j < kd; ++j) {
           const int col = S.col_cam[12 * (size_t)c + j];

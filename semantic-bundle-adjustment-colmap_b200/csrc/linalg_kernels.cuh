@@ -153,16 +153,18 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
   if (writer) {
     const int po = S.p_off[pt];
     if (po >= 0) {
-      const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
-      const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
-      double inv[6];
-      if (!InvertSym3(c, inv)) {
-        sc->solver_failed = 1;
+      if (Dp) {
+        const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
+        const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
+        double inv[6];
+        if (!InvertSym3(c, inv)) {
+          sc->solver_failed = 1;
 #pragma unroll
-        for (int a = 0; a < 6; ++a) inv[a] = 0.0;
+          for (int a = 0; a < 6; ++a) inv[a] = 0.0;
+        }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) Cinv[6 * (size_t)po + a] = inv[a];
       }
-#pragma unroll
-      for (int a = 0; a < 6; ++a) Cinv[6 * (size_t)po + a] = inv[a];
       gp[3 * (size_t)po] = v[6]; gp[3 * (size_t)po + 1] = v[7]; gp[3 * (size_t)po + 2] = v[8];
     }
   }

@@ -352,6 +352,12 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_grad_c.Alloc(nc)); UP(p->d_grad_p.Alloc(np3)); UP(p->d_tmp_c.Alloc(nc));
   UP(p->d_cg_r.Alloc(nc)); UP(p->d_cg_z.Alloc(nc)); UP(p->d_cg_p.Alloc(nc)); UP(p->d_cg_q.Alloc(nc)); UP(p->d_cg_x.Alloc(nc));
   UP(p->d_scalars.Alloc(1)); UP(p->d_scalars.Zero(st));
+  if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0) {
+    const size_t n_map = (size_t)p->n_img * d.sem_height * d.sem_width;
+    UP(p->d_sem_maps.Alloc(n_map));
+    UP(cudaMemcpyAsync(p->d_sem_maps.p, d.sem_maps, n_map * sizeof(float), cudaMemcpyHostToDevice, st));
+    p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
+  }
   UP(cudaStreamSynchronize(st));
 #undef UP
   return SBA_OK;

@@ -329,7 +329,7 @@ int BuildDenseSchur(Problem* p) {
   int rc = BuildPairLists(p, true);
   if (rc) return rc;
   const size_t n = p->n_cdim;
-  SBA_CUDA(p->d_S.Alloc(std::max<size_t>(1, n * n)));
+  SBA_CUDA(p->d_S.Alloc(std::max<size_t>(1, (n + 1) * n)));  // + one row: the right-hand side (cholesky.cu)
   SBA_CUDA(cudaMemsetAsync(p->d_S.p, 0, n * n * sizeof(double), p->stream));
   Sink sink;
   std::memset(&sink, 0, sizeof(sink));

@@ -1,0 +1,567 @@
+// K-SEM-PAIR, K-CYL-IOU and K-SEM-BILIN: the fork's semantic residuals as CUDA kernels.
+//
+//  * semantic pair residual (0/1 label mismatch with depth gate)
+//      /root/reference/src/base/semantic_cost_functions.h:88-208, pose algebra
+//      /root/reference/src/util/rotation_extension.h:44-101
+//  * cylinder IoU residual (1 - IoU of the rasterised tangent quadrilateral vs a mask)
+//      /root/reference/src/util/cylinder.h:27-121 (drawQuadrilateral), :352-474, :497-540,
+//      /root/reference/src/util/xywh.h:85-131, /root/reference/src/util/utils.h:23-55,
+//      /root/reference/src/base/geometric_semantic_cost_functions.h:55-93
+//  * both differentiated the way the reference asks Ceres to: NumericDiff CENTRAL,
+//    step max(sqrt(eps), |x| * relative_step_size) (semantic_cost_functions.h:248-258,
+//    SURVEY.md App. B.6)
+//  * extension X1 (not in the reference): bilinear map sample at the projection with the
+//    rule of Bitmap::InterpolateBilinear, /root/reference/src/util/bitmap.cc:238-269
+//
+// This file is compiled with -fmad=false: the pair residual is an integer-valued function
+// of rounded pixel coordinates, and IEEE mul/add/div/sqrt without contraction reproduce the
+// CPU evaluation order bit for bit, so rounding ties fall the same way.
+#include <cfloat>
+
+#include "device_math.cuh"
+#include "reduce.cuh"
+#include "solver.h"
+
+namespace sba {
+
+// ---- small pose algebra (ceres/rotation.h semantics) ----------------------------------------
+__device__ inline void UnitQuatRotate(const double q[4], const double pt[3], double out[3]) {
+  const double t2 = q[0] * q[1], t3 = q[0] * q[2], t4 = q[0] * q[3], t5 = -q[1] * q[1], t6 = q[1] * q[2],
+               t7 = q[1] * q[3], t8 = -q[2] * q[2], t9 = q[2] * q[3], t1 = -q[3] * q[3];
+  out[0] = 2.0 * ((t8 + t1) * pt[0] + (t6 - t4) * pt[1] + (t3 + t7) * pt[2]) + pt[0];
+  out[1] = 2.0 * ((t4 + t6) * pt[0] + (t5 + t1) * pt[1] + (t9 - t2) * pt[2]) + pt[1];
+  out[2] = 2.0 * ((t7 - t3) * pt[0] + (t2 + t9) * pt[1] + (t5 + t8) * pt[2]) + pt[2];
+}
+__device__ inline void QuatRotate(const double q[4], const double pt[3], double out[3]) {
+  const double scale = 1.0 / sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  const double unit[4] = {scale * q[0], scale * q[1], scale * q[2], scale * q[3]};
+  UnitQuatRotate(unit, pt, out);
+}
+__device__ inline void QuatToRotation(const double q[4], double R[9]) {
+  const double a = q[0], b = q[1], c = q[2], d = q[3];
+  const double aa = a * a, ab = a * b, ac = a * c, ad = a * d, bb = b * b, bc = b * c, bd = b * d, cc = c * c,
+               cd = c * d, dd = d * d;
+  R[0] = aa + bb - cc - dd; R[1] = 2.0 * (bc - ad);   R[2] = 2.0 * (ac + bd);
+  R[3] = 2.0 * (ad + bc);   R[4] = aa - bb + cc - dd; R[5] = 2.0 * (cd - ab);
+  R[6] = 2.0 * (bd - ac);   R[7] = 2.0 * (ab + cd);   R[8] = aa - bb - cc + dd;
+  const double normalizer = 1.0 / (aa + bb + cc + dd);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R[i] *= normalizer;
+}
+__device__ inline void PoseInverse(const double q[4], const double t[3], double qi[4], double ti[3]) {
+  const double scale = 1.0 / sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  qi[0] = scale * q[0]; qi[1] = -(scale * q[1]); qi[2] = -(scale * q[2]); qi[3] = -(scale * q[3]);
+  double R[9];
+  QuatToRotation(qi, R);
+  ti[0] = -(R[0] * t[0] + R[1] * t[1] + R[2] * t[2]);
+  ti[1] = -(R[3] * t[0] + R[4] * t[1] + R[5] * t[2]);
+  ti[2] = -(R[6] * t[0] + R[7] * t[1] + R[8] * t[2]);
+}
+__device__ inline void PoseTransform(const double q[4], const double t[3], const double pt[3], double out[3]) {
+  QuatRotate(q, pt, out);
+  out[0] += t[0]; out[1] += t[1]; out[2] += t[2];
+}
+// double -> int the way the host (x86 cvttsd2si) does it: out-of-range / NaN give INT_MIN
+__device__ inline int CvtInt(double v) {
+  if (!(v > -2147483649.0 && v < 2147483648.0)) return INT_MIN;
+  return (int)v;
+}
+__device__ inline double NumDiffDelta(double x, double rel) { return fmax(sqrt(DBL_EPSILON), fabs(x) * rel); }
+
+// =================================== K-SEM-PAIR ===============================================
+struct SemView {
+  int H, W;
+  const double* q;      // [n_img*4]
+  const double* t;      // [n_img*3]
+  const double* cam;    // [n_img*3]
+  const float* depth;   // [n_img*H*W] row-major
+  const float* label;   // [n_img*H*W]
+  const int* i1; const int* i2; const int* x1; const int* y1;
+  double thr, rel;
+};
+
+__device__ inline double PairResidual(const SemView& V, int x1, int y1, float depth1, float sem1, const float* depth2,
+                                      const float* sem2, const double* x /*q1 t1 q2 t2*/, const double* cam1,
+                                      const double* cam2, int* status) {
+  const double u1 = ((double)x1 - cam1[1]) / cam1[0];
+  const double v1 = ((double)y1 - cam1[2]) / cam1[0];
+  const double P[3] = {u1 * depth1, v1 * depth1, (double)depth1};
+  double qi[4], ti[3], Pw[3], Pc[3];
+  PoseInverse(x, x + 4, qi, ti);
+  PoseTransform(qi, ti, P, Pw);
+  PoseTransform(x + 7, x + 11, Pw, Pc);
+  const double u2 = Pc[0] / Pc[2], v2 = Pc[1] / Pc[2];
+  const double x2 = cam2[0] * u2 + cam2[1], y2 = cam2[0] * v2 + cam2[2];
+  const int px = CvtInt(round(x2)), py = CvtInt(round(y2));
+  if (px < 0 || px >= V.W || py < 0 || py >= V.H) { *status = -1; return 0.0; }
+  const size_t o = (size_t)py * V.W + px;
+  const double d2 = (double)__ldg(depth2 + o);
+  if (fabs(d2 - Pc[2]) > V.thr) { *status = -2; return 0.0; }
+  *status = 10;
+  return (sem1 == __ldg(sem2 + o)) ? 0.0 : 1.0;
+}
+
+// One warp per residual block: lane 0 evaluates the block, lanes 1..28 the +/- perturbations
+// of the 14 ambient coordinates; the central differences are formed with shuffles.
+template <bool JAC>
+__global__ void __launch_bounds__(128) semantic_pair_kernel(SemView V, int64_t n_blocks, double* __restrict__ res,
+                                                            int* __restrict__ status, double* __restrict__ jac) {
+  const int lane = threadIdx.x & 31;
+  const int64_t k = JAC ? ((int64_t)blockIdx.x * 4 + (threadIdx.x >> 5)) : ((int64_t)blockIdx.x * 128 + threadIdx.x);
+  if (k >= n_blocks) return;
+  const int i1 = V.i1[k], i2 = V.i2[k], x1 = V.x1[k], y1 = V.y1[k];
+  const size_t HW = (size_t)V.H * V.W;
+  const float depth1 = __ldg(V.depth + i1 * HW + (size_t)y1 * V.W + x1);
+  const float sem1 = __ldg(V.label + i1 * HW + (size_t)y1 * V.W + x1);
+  double x[14];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { x[j] = V.q[4 * i1 + j]; x[7 + j] = V.q[4 * i2 + j]; }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) { x[4 + j] = V.t[3 * i1 + j]; x[11 + j] = V.t[3 * i2 + j]; }
+  double delta = 0.0;
+  if (JAC && lane >= 1 && lane <= 28) {
+    const int j = (lane - 1) >> 1;
+    double xj = 0.0;
+#pragma unroll
+    for (int a = 0; a < 14; ++a) if (a == j) xj = x[a];
+    delta = NumDiffDelta(xj, V.rel);
+    const double xn = ((lane - 1) & 1) ? xj - delta : xj + delta;
+#pragma unroll
+    for (int a = 0; a < 14; ++a) if (a == j) x[a] = xn;
+  }
+  int st = 0;
+  double r = 0.0;
+  if (!JAC || lane <= 28)
+    r = PairResidual(V, x1, y1, depth1, sem1, V.depth + i2 * HW, V.label + i2 * HW, x, V.cam + 3 * i1, V.cam + 3 * i2, &st);
+  if (!JAC) {
+    if (res) res[k] = r;
+    if (status) status[k] = st;
+    return;
+  }
+  if (lane == 0) {
+    if (res) res[k] = r;
+    if (status) status[k] = st;
+  }
+  // lane j (0..13) gathers f(x + d e_j) from lane 1+2j and f(x - d e_j) from lane 2+2j
+  const int src_p = (1 + 2 * lane) & 31, src_m = (2 + 2 * lane) & 31;
+  const double fp = __shfl_sync(0xffffffffu, r, src_p);
+  const double fm = __shfl_sync(0xffffffffu, r, src_m);
+  const double dl = __shfl_sync(0xffffffffu, delta, src_p);
+  if (lane < 14) jac[k * 14 + lane] = (fp - fm) * ((1.0 / dl) / 2.0);
+}
+
+}  // namespace sba
+
+using namespace sba;
+
+extern "C" int sba_semantic_evaluate(const sba_semantic_desc* d, double* residuals, int32_t* status, double* jac,
+                                     double* ms_device) {
+  if (!d || d->num_images <= 0 || d->height <= 0 || d->width <= 0 || d->num_blocks < 0 || !d->image_qvec ||
+      !d->image_tvec || !d->camera_params || !d->depth_maps || !d->semantic_maps ||
+      (d->num_blocks > 0 && (!d->block_image1 || !d->block_image2 || !d->block_x1 || !d->block_y1))) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "bad semantic description");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  const int64_t nb = d->num_blocks;
+  for (int64_t k = 0; k < nb; ++k)
+    if (d->block_image1[k] < 0 || d->block_image1[k] >= d->num_images || d->block_image2[k] < 0 ||
+        d->block_image2[k] >= d->num_images || d->block_x1[k] < 0 || d->block_x1[k] >= d->width ||
+        d->block_y1[k] < 0 || d->block_y1[k] >= d->height) {
+      SetError(SBA_ERR_INVALID_ARGUMENT, "semantic block index out of range");
+      return SBA_ERR_INVALID_ARGUMENT;
+    }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+    return SBA_ERR_NO_DEVICE;
+  }
+  cudaStream_t st;
+  SBA_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  const size_t HW = (size_t)d->height * d->width, n_img = d->num_images;
+  DevBuf<double> dq, dt, dc, dres, djac;
+  DevBuf<float> ddepth, dlabel;
+  DevBuf<int> di1, di2, dx1, dy1, dstatus;
+  auto up = [&](auto& buf, const auto* src, size_t n) -> cudaError_t {
+    cudaError_t e = buf.Alloc(n);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(buf.p, src, n * sizeof(*src), cudaMemcpyHostToDevice, st);
+  };
+  SBA_CUDA(up(dq, d->image_qvec, n_img * 4)); SBA_CUDA(up(dt, d->image_tvec, n_img * 3));
+  SBA_CUDA(up(dc, d->camera_params, n_img * 3));
+  SBA_CUDA(up(ddepth, d->depth_maps, n_img * HW)); SBA_CUDA(up(dlabel, d->semantic_maps, n_img * HW));
+  if (nb > 0) {
+    SBA_CUDA(up(di1, d->block_image1, nb)); SBA_CUDA(up(di2, d->block_image2, nb));
+    SBA_CUDA(up(dx1, d->block_x1, nb)); SBA_CUDA(up(dy1, d->block_y1, nb));
+  }
+  SBA_CUDA(dres.Alloc(std::max<int64_t>(1, nb))); SBA_CUDA(dstatus.Alloc(std::max<int64_t>(1, nb)));
+  if (jac) SBA_CUDA(djac.Alloc(std::max<int64_t>(1, nb * 14)));
+  SemView V;
+  V.H = d->height; V.W = d->width; V.q = dq.p; V.t = dt.p; V.cam = dc.p; V.depth = ddepth.p; V.label = dlabel.p;
+  V.i1 = di1.p; V.i2 = di2.p; V.x1 = dx1.p; V.y1 = dy1.p; V.thr = d->depth_error_threshold; V.rel = d->relative_step_size;
+  cudaEvent_t e0, e1;
+  SBA_CUDA(cudaEventCreate(&e0)); SBA_CUDA(cudaEventCreate(&e1));
+  SBA_CUDA(cudaEventRecord(e0, st));
+  if (nb > 0) {
+    if (jac) semantic_pair_kernel<true><<<DivUp(nb, 4), 128, 0, st>>>(V, nb, dres.p, dstatus.p, djac.p);
+    else semantic_pair_kernel<false><<<DivUp(nb, 128), 128, 0, st>>>(V, nb, dres.p, dstatus.p, nullptr);
+  }
+  SBA_CUDA(cudaEventRecord(e1, st));
+  SBA_CUDA(cudaGetLastError());
+  if (nb > 0) {
+    if (residuals) SBA_CUDA(cudaMemcpyAsync(residuals, dres.p, nb * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (status) SBA_CUDA(cudaMemcpyAsync(status, dstatus.p, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (jac) SBA_CUDA(cudaMemcpyAsync(jac, djac.p, nb * 14 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  }
+  SBA_CUDA(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  if (ms_device) *ms_device = ms;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaStreamDestroy(st);
+  return SBA_OK;
+}
+
+// =================================== K-CYL-IOU ================================================
+namespace sba {
+
+struct IBox { int x, y, w, h; };
+__device__ inline IBox BoundPts(const double* pts, int npts) {
+  double mnx = pts[0], mxx = pts[0], mny = pts[1], mxy = pts[1];
+  for (int i = 0; i < npts; ++i) {
+    mnx = fmin(mnx, pts[2 * i]); mxx = fmax(mxx, pts[2 * i]);
+    mny = fmin(mny, pts[2 * i + 1]); mxy = fmax(mxy, pts[2 * i + 1]);
+  }
+  IBox b;
+  b.x = CvtInt(floor(mnx)); b.y = CvtInt(floor(mny));
+  b.w = CvtInt(ceil(mxx)) - b.x + 1; b.h = CvtInt(ceil(mxy)) - b.y + 1;
+  return b;
+}
+__device__ inline IBox ClipBox(const IBox& b, int W, int H) {
+  const int tlx = max(b.x, 0), tly = max(b.y, 0);
+  const int brx = min(b.x + b.w - 1, W - 1), bry = min(b.y + b.h - 1, H - 1);
+  IBox o = {0, 0, 0, 0};
+  if (brx < tlx || bry < tly) return o;
+  o.x = tlx; o.y = tly; o.w = brx - tlx + 1; o.h = bry - tly + 1;
+  return o;
+}
+__device__ inline bool InBox(const IBox& b, int x, int y) { return x >= b.x && x < b.x + b.w && y >= b.y && y < b.y + b.h; }
+
+__device__ inline void AngleAxisRotateZ(double beta, const double pt[3], double out[3]) {
+  // ceres::AngleAxisRotatePoint with angle_axis = (0, 0, beta)
+  const double aa[3] = {0.0, 0.0, beta};
+  const double th2 = beta * beta;
+  if (th2 > 2.220446049250313e-16) {
+    const double th = sqrt(th2), c = cos(th), s = sin(th), it = 1.0 / th;
+    const double w[3] = {aa[0] * it, aa[1] * it, aa[2] * it};
+    const double wxp[3] = {w[1] * pt[2] - w[2] * pt[1], w[2] * pt[0] - w[0] * pt[2], w[0] * pt[1] - w[1] * pt[0]};
+    const double tmp = (w[0] * pt[0] + w[1] * pt[1] + w[2] * pt[2]) * (1.0 - c);
+    for (int i = 0; i < 3; ++i) out[i] = pt[i] * c + wxp[i] * s + w[i] * tmp;
+  } else {
+    const double wxp[3] = {aa[1] * pt[2] - aa[2] * pt[1], aa[2] * pt[0] - aa[0] * pt[2], aa[0] * pt[1] - aa[1] * pt[0]};
+    for (int i = 0; i < 3; ++i) out[i] = pt[i] + wxp[i];
+  }
+}
+
+// Cylinder::ProjectToQuadrilateral (cylinder.h:352-474); false where the reference throws
+__device__ inline bool CylinderQuad(const double* x16, const double* cam, double* pts8) {
+  const double* cam_q = x16; const double* cam_t = x16 + 4; const double* cyl_q = x16 + 7; const double* cyl_t = x16 + 11;
+  double radius = x16[14], height = x16[15];
+  if (radius <= 0) radius = 1e-4;
+  if (height <= 0) height = 1e-4;
+  double cwq[4], cwt[3], qi[4], ti[3], c[3];
+  PoseInverse(cam_q, cam_t, cwq, cwt);
+  PoseInverse(cyl_q, cyl_t, qi, ti);
+  PoseTransform(qi, ti, cwt, c);
+  c[2] = 0;
+  const double dist = sqrt(c[0] * c[0] + c[1] * c[1]);
+  if (!(dist > radius)) return false;
+  const double dir[3] = {c[0] / dist * radius, c[1] / dist * radius, 0.0};
+  const double beta = acos(radius / dist);
+  double p[4][3];
+  AngleAxisRotateZ(beta, dir, p[0]);
+  AngleAxisRotateZ(-beta, dir, p[1]);
+  p[2][0] = p[1][0]; p[2][1] = p[1][1]; p[2][2] = p[1][2] + height;
+  p[3][0] = p[0][0]; p[3][1] = p[0][1]; p[3][2] = p[0][2] + height;
+  for (int i = 0; i < 4; ++i) {
+    double pw[3], pc[3];
+    PoseTransform(cyl_q, cyl_t, p[i], pw);
+    PoseTransform(cam_q, cam_t, pw, pc);
+    if (!(pc[2] > 0)) return false;
+    pc[0] /= pc[2]; pc[1] /= pc[2];
+    pts8[2 * i] = cam[0] * pc[0] + cam[1];
+    pts8[2 * i + 1] = cam[0] * pc[1] + cam[2];
+  }
+  const double v0x = pts8[2] - pts8[0], v0y = pts8[3] - pts8[1];
+  const double v1x = pts8[4] - pts8[0], v1y = pts8[5] - pts8[1];
+  if (v0x * v1y - v0y * v1x < 0) {
+    double t = pts8[2]; pts8[2] = pts8[6]; pts8[6] = t;
+    t = pts8[3]; pts8[3] = pts8[7]; pts8[7] = t;
+  }
+  return true;
+}
+
+// drawQuadrilateral as a per-pixel predicate: start from "inside the clipped bbox", clear by
+// every edge inside that edge's own clipped bbox, then clear the corner rectangles.
+struct QuadRaster {
+  IBox bb;
+  IBox eb[4];
+  IBox cb[4];
+  bool corner_on[4];
+  double p[8];
+};
+__device__ inline void BuildRaster(const double* p, int H, int W, QuadRaster* R) {
+  for (int i = 0; i < 8; ++i) R->p[i] = p[i];
+  R->bb = ClipBox(BoundPts(p, 4), W, H);
+  for (int e = 0; e < 4; ++e) {
+    const double two[4] = {p[2 * e], p[2 * e + 1], p[2 * ((e + 1) & 3)], p[2 * ((e + 1) & 3) + 1]};
+    R->eb[e] = ClipBox(BoundPts(two, 2), W, H);
+  }
+  const IBox& bb = R->bb;
+  const int xe = bb.x + bb.w - 1, ye = bb.y + bb.h - 1;
+  for (int v = 0; v < 4; ++v) {
+    const double vx = p[2 * v], vy = p[2 * v + 1];
+    R->corner_on[v] = !(vx - bb.x < 1 || xe - vx < 1 || vy - bb.y < 1 || ye - vy < 1);
+    R->cb[v] = IBox{0, 0, 0, 0};
+    if (!R->corner_on[v]) continue;
+    const int cx[4] = {bb.x, xe, xe, bb.x};
+    const int cy[4] = {bb.y, bb.y, ye, ye};
+    int best = 0; double bd = 1e300;
+    for (int i = 0; i < 4; ++i) {
+      const double dx = vx - cx[i], dy = vy - cy[i];
+      const double dist = sqrt(dx * dx + dy * dy);
+      if (dist < bd) { bd = dist; best = i; }
+    }
+    const double two[4] = {(double)cx[best], (double)cy[best], vx, vy};
+    R->cb[v] = ClipBox(BoundPts(two, 2), W, H);
+  }
+}
+__device__ inline bool RasterInside(const QuadRaster& R, int x, int y) {
+  bool m = true;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    if (R.eb[e].w * R.eb[e].h == 0 || !InBox(R.eb[e], x, y)) continue;
+    const double ax = R.p[2 * e], ay = R.p[2 * e + 1], bx = R.p[2 * ((e + 1) & 3)], by = R.p[2 * ((e + 1) & 3) + 1];
+    const double cross = ((double)x - ax) * (by - ay) - ((double)y - ay) * (bx - ax);
+    if (cross > 0) m = false;
+  }
+#pragma unroll
+  for (int v = 0; v < 4; ++v)
+    if (R.corner_on[v] && InBox(R.cb[v], x, y)) m = false;
+  return m;
+}
+
+__global__ void __launch_bounds__(256) mask_count_kernel(const uint8_t* __restrict__ masks, size_t HW, int* __restrict__ count) {
+  const uint8_t* m = masks + (size_t)blockIdx.x * HW;
+  int c = 0;
+  for (size_t j = threadIdx.x; j < HW; j += 256) c += m[j] != 0;
+  __shared__ int sm[8];
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) { int t = 0; for (int i = 0; i < 8; ++i) t += sm[i]; count[blockIdx.x] = t; }
+}
+
+struct CylView {
+  int H, W;
+  const double* q; const double* t; const double* cam;  // per image
+  const uint8_t* masks; const int* pos_count;
+  const double* cq; const double* ct; const double* cr; const double* ch;  // per cylinder
+  const int* b_img; const int* b_cyl;
+  double rel;
+};
+
+// One CTA per (residual block, evaluation): evaluation 0 is the block itself, 1+2j / 2+2j are
+// the +/- perturbations of ambient coordinate j (16 of them).  vals[k*33 + e] = 1 - IoU.
+__global__ void __launch_bounds__(256) cylinder_iou_kernel(CylView V, int n_eval, double* __restrict__ vals,
+                                                           double* __restrict__ deltas) {
+  const int64_t k = blockIdx.x / n_eval;
+  const int e = blockIdx.x - (int)(k * n_eval);
+  const int im = V.b_img[k], cy = V.b_cyl[k];
+  __shared__ QuadRaster R;
+  __shared__ int ok;
+  __shared__ int red[8][4];
+  if (threadIdx.x == 0) {
+    double x[16];
+    for (int j = 0; j < 4; ++j) { x[j] = V.q[4 * im + j]; x[7 + j] = V.cq[4 * cy + j]; }
+    for (int j = 0; j < 3; ++j) { x[4 + j] = V.t[3 * im + j]; x[11 + j] = V.ct[3 * cy + j]; }
+    x[14] = V.cr[cy]; x[15] = V.ch[cy];
+    if (e > 0) {
+      const int j = (e - 1) >> 1;
+      const double delta = NumDiffDelta(x[j], V.rel);
+      x[j] = ((e - 1) & 1) ? x[j] - delta : x[j] + delta;
+      if (!((e - 1) & 1)) deltas[k * 16 + j] = delta;
+    }
+    double pts[8];
+    ok = CylinderQuad(x, V.cam + 3 * im, pts) ? 1 : 0;
+    if (ok) BuildRaster(pts, V.H, V.W, &R);
+  }
+  __syncthreads();
+  if (!ok) {
+    if (threadIdx.x == 0) vals[k * n_eval + e] = 1.0;
+    return;
+  }
+  const uint8_t* sem = V.masks + (size_t)im * V.H * V.W;
+  int inside_pos = 0, tp = 0, fp = 0, snm = 0;
+  const int n_px = R.bb.w * R.bb.h;
+  for (int idx = threadIdx.x; idx < n_px; idx += 256) {
+    const int yy = idx / R.bb.w, xx = idx - yy * R.bb.w;
+    const int x = R.bb.x + xx, y = R.bb.y + yy;
+    const bool s = sem[(size_t)y * V.W + x] != 0;
+    const bool m = RasterInside(R, x, y);
+    inside_pos += s; tp += (s && m); fp += (!s && m); snm += (s && !m);
+  }
+  int v[4] = {inside_pos, tp, fp, snm};
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    for (int o = 16; o > 0; o >>= 1) v[a] += __shfl_down_sync(0xffffffffu, v[a], o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][a] = v[a];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t[4] = {0, 0, 0, 0};
+    for (int w = 0; w < 8; ++w) for (int a = 0; a < 4; ++a) t[a] += red[w][a];
+    const int fn = (V.pos_count[im] - t[0]) + t[3];
+    const double iou = (double)t[1] / (t[1] * 1. + t[2] + fn);
+    vals[k * n_eval + e] = 1.0 - iou;
+  }
+}
+
+__global__ void cylinder_jac_kernel(int64_t n_blocks, const double* __restrict__ vals, const double* __restrict__ deltas,
+                                    double* __restrict__ jac) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_blocks * 16) return;
+  const int64_t k = t / 16;
+  const int j = (int)(t - k * 16);
+  const double fp = vals[k * 33 + 1 + 2 * j], fm = vals[k * 33 + 2 + 2 * j];
+  jac[t] = (fp - fm) * ((1.0 / deltas[t]) / 2.0);
+}
+
+}  // namespace sba
+
+extern "C" int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residuals, double* jac, double* ms_device) {
+  if (!d || d->num_images <= 0 || d->height <= 0 || d->width <= 0 || d->num_cylinders < 0 || d->num_blocks < 0 ||
+      !d->image_qvec || !d->image_tvec || !d->camera_params || !d->masks ||
+      (d->num_blocks > 0 && (!d->block_image || !d->block_cylinder || !d->cyl_qvec || !d->cyl_tvec || !d->cyl_radius || !d->cyl_height))) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "bad cylinder description");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  const int64_t nb = d->num_blocks;
+  for (int64_t k = 0; k < nb; ++k)
+    if (d->block_image[k] < 0 || d->block_image[k] >= d->num_images || d->block_cylinder[k] < 0 ||
+        d->block_cylinder[k] >= d->num_cylinders) {
+      SetError(SBA_ERR_INVALID_ARGUMENT, "cylinder block index out of range");
+      return SBA_ERR_INVALID_ARGUMENT;
+    }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+    return SBA_ERR_NO_DEVICE;
+  }
+  cudaStream_t st;
+  SBA_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  const size_t HW = (size_t)d->height * d->width, n_img = d->num_images, n_cyl = std::max(1, d->num_cylinders);
+  DevBuf<double> dq, dt, dc, dcq, dct, dcr, dch, dvals, ddel, djac;
+  DevBuf<uint8_t> dmask;
+  DevBuf<int> dpos, dbi, dbc;
+  auto up = [&](auto& buf, const auto* src, size_t n) -> cudaError_t {
+    cudaError_t e = buf.Alloc(n);
+    if (e != cudaSuccess || !src || n == 0) return e;
+    return cudaMemcpyAsync(buf.p, src, n * sizeof(*src), cudaMemcpyHostToDevice, st);
+  };
+  SBA_CUDA(up(dq, d->image_qvec, n_img * 4)); SBA_CUDA(up(dt, d->image_tvec, n_img * 3));
+  SBA_CUDA(up(dc, d->camera_params, n_img * 3)); SBA_CUDA(up(dmask, d->masks, n_img * HW));
+  SBA_CUDA(up(dcq, d->cyl_qvec, (size_t)d->num_cylinders * 4)); SBA_CUDA(up(dct, d->cyl_tvec, (size_t)d->num_cylinders * 3));
+  SBA_CUDA(up(dcr, d->cyl_radius, (size_t)d->num_cylinders)); SBA_CUDA(up(dch, d->cyl_height, (size_t)d->num_cylinders));
+  (void)n_cyl;
+  SBA_CUDA(up(dbi, d->block_image, nb)); SBA_CUDA(up(dbc, d->block_cylinder, nb));
+  SBA_CUDA(dpos.Alloc(n_img));
+  const int n_eval = jac ? 33 : 1;
+  SBA_CUDA(dvals.Alloc(std::max<int64_t>(1, nb * n_eval))); SBA_CUDA(ddel.Alloc(std::max<int64_t>(1, nb * 16)));
+  if (jac) SBA_CUDA(djac.Alloc(std::max<int64_t>(1, nb * 16)));
+  CylView V;
+  V.H = d->height; V.W = d->width; V.q = dq.p; V.t = dt.p; V.cam = dc.p; V.masks = dmask.p; V.pos_count = dpos.p;
+  V.cq = dcq.p; V.ct = dct.p; V.cr = dcr.p; V.ch = dch.p; V.b_img = dbi.p; V.b_cyl = dbc.p; V.rel = d->relative_step_size;
+  cudaEvent_t e0, e1;
+  SBA_CUDA(cudaEventCreate(&e0)); SBA_CUDA(cudaEventCreate(&e1));
+  SBA_CUDA(cudaEventRecord(e0, st));
+  mask_count_kernel<<<(int)n_img, 256, 0, st>>>(dmask.p, HW, dpos.p);
+  if (nb > 0) {
+    cylinder_iou_kernel<<<(unsigned)(nb * n_eval), 256, 0, st>>>(V, n_eval, dvals.p, ddel.p);
+    if (jac) cylinder_jac_kernel<<<DivUp(nb * 16, 256), 256, 0, st>>>(nb, dvals.p, ddel.p, djac.p);
+  }
+  SBA_CUDA(cudaEventRecord(e1, st));
+  SBA_CUDA(cudaGetLastError());
+  if (nb > 0) {
+    if (residuals) SBA_CUDA(cudaMemcpy2DAsync(residuals, sizeof(double), dvals.p, n_eval * sizeof(double), sizeof(double), nb,
+                                              cudaMemcpyDeviceToHost, st));
+    if (jac) SBA_CUDA(cudaMemcpyAsync(jac, djac.p, nb * 16 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  }
+  SBA_CUDA(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  if (ms_device) *ms_device = ms;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaStreamDestroy(st);
+  return SBA_OK;
+}
+
+// =================================== K-SEM-BILIN (extension X1) ===============================
+namespace sba {
+
+__device__ inline double BilinearSample(const float* __restrict__ map, int H, int W, double x, double y, int* ok) {
+  const double inv_y = H - 1 - y;
+  const int x0 = CvtInt(floor(x)), x1 = x0 + 1;
+  const int y0 = CvtInt(floor(inv_y)), y1 = y0 + 1;
+  if (x0 < 0 || x1 >= W || y0 < 0 || y1 >= H || x1 < 0 || y1 < 0) { *ok = 0; return 0.0; }
+  const double dx = x - x0, dy = inv_y - y0, dx_1 = 1 - dx, dy_1 = 1 - dy;
+  const float* line0 = map + (size_t)(H - 1 - y0) * W;
+  const float* line1 = map + (size_t)(H - 1 - y1) * W;
+  const double v0 = dx_1 * __ldg(line0 + x0) + dx * __ldg(line0 + x1);
+  const double v1 = dx_1 * __ldg(line1 + x0) + dx * __ldg(line1 + x1);
+  *ok = 1;
+  return dy_1 * v0 + dy * v1;
+}
+
+__global__ void __launch_bounds__(128) sem_rows_kernel(ParamsView P, StructView S, const float* __restrict__ maps, int H, int W,
+                                                       double weight, double* __restrict__ out) {
+  const int k = blockIdx.x * 128 + threadIdx.x;
+  if (k >= S.n_obs) return;
+  const int i = S.obs_img[k], pt = S.obs_pt[k], c = S.img_cam[i];
+  const double* pose = P.pose + 8 * (size_t)i;
+  const double q[4] = {pose[0], pose[1], pose[2], pose[3]};
+  const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
+  double pr[3];
+  UnitQuatRotate(q, X, pr);
+  pr[0] += pose[4]; pr[1] += pose[5]; pr[2] += pose[6];
+  pr[0] /= pr[2]; pr[1] /= pr[2];
+  double prm[12];
+  for (int j = 0; j < 12; ++j) prm[j] = P.cam[12 * (size_t)c + j];
+  double x, y;
+  WorldToImageValDyn(S.model[c], prm, pr[0], pr[1], &x, &y);
+  int ok;
+  const double v = BilinearSample(maps + (size_t)i * H * W, H, W, x, y, &ok);
+  out[k] = ok ? weight * v : 0.0;
+}
+
+int EvaluateSemanticRows(Problem* p, double* sem_residuals_host) {
+  if (!p->d_sem_maps.p) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sem_residuals requested but the problem has no semantic maps");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  const int n = p->n_obs;
+  if (n == 0) return SBA_OK;
+  DevBuf<double> d_out;
+  SBA_CUDA(d_out.Alloc(n));
+  sem_rows_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Params(false), p->Struct(), p->d_sem_maps.p, p->sem_h, p->sem_w,
+                                                        p->sem_weight, d_out.p);
+  p->launches++;
+  std::vector<double> h(n);
+  SBA_CUDA(cudaMemcpyAsync(h.data(), d_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  SBA_CUDA(cudaStreamSynchronize(p->stream));
+  for (int k = 0; k < n; ++k) sem_residuals_host[p->h_local2ref[k]] = h[k];
+  return SBA_OK;
+}
+
+}  // namespace sba

@@ -105,7 +105,10 @@ struct Problem {
 
   // reduced-camera-matrix block entries (dense S) and diagonal entries (SCHUR_JACOBI)
   DevBuf<int> d_pair_key_ptr, d_pair_a, d_pair_b, d_pair_key_gi, d_pair_key_gj;  int n_pair_keys = 0; int64_t n_pairs = 0;
-  DevBuf<int> d_diag_key_ptr, d_diag_a, d_diag_b;                                 int64_t n_diag_pairs = 0;
+  DevBuf<int> d_diag_key_ptr, d_diag_a, d_diag_b, d_diag_key_gi, d_diag_key_gj;   int n_diag_keys = 0; int64_t n_diag_pairs = 0;
+  DevBuf<int> d_blk_moff;  int m_size = 0;      // offsets of the SCHUR_JACOBI blocks inside d_M / d_Minv
+  DevBuf<double> d_M;                           // block diagonal of S before inversion
+  DevBuf<double> d_chunk_block;                 // [n_chunks*dc*dc] per-chunk diagonal block partials
   bool pairs_built = false, diag_built = false;
 
   // ---- device: parameters (current / candidate) ----
@@ -137,8 +140,14 @@ struct Problem {
   cudaStream_t stream = nullptr;
   int device = 0;
   int64_t launches = 0;
+  int64_t collectives = 0;
+  // extension X1: per-image semantic maps (row-major float), sampled bilinearly at the projection
+  DevBuf<float> d_sem_maps;  int sem_h = 0, sem_w = 0;  double sem_weight = 0.0;
   bool solved = false;
   bool linearized = false;
+  int cg_poll_every = 1;                    // host polls the CG state every this many iterations
+  double* jq_out = nullptr;                 // parity surface: raw 2x4 quaternion block per observation
+  DevBuf<char> d_flush;                     // L2 flush scratch for sba_bench_stage
   Comm* comm = nullptr;
 
   // stage timers
@@ -159,10 +168,12 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
 int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost /* &scalars->cand_cost */);
 // linalg.cu (column norms, point blocks, rhs, matvec, back-substitution, update)
 int ColumnNorms(Problem* p, double* d_nc, double* d_np);
-int Gradient(Problem* p, double* d_gc, double* d_gp);
+int Gradient(Problem* p);
+int FillOnes(Problem* p);
+int AllReduceMax(Problem* p, double* d_buf, size_t n);
 int InitJacobiScale(Problem* p);
 int PrepareLMDiagonal(Problem* p, const sba_solver_options& o);
-int PointBlocks(Problem* p);
+int PointBlocks(Problem* p, bool grad_only);
 int ReducedRhs(Problem* p);
 int SchurMatVec(Problem* p, const double* d_x, double* d_y);
 int BackSubstitute(Problem* p);
@@ -180,6 +191,8 @@ int CholeskySolve(Problem* p);  // d_S, d_rhs -> d_yc ; sets scalars.chol_fail
 int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
 // lm.cu
 int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, void* user, sba_summary* s);
+// semantic.cu
+int EvaluateSemanticRows(Problem* p, double* sem_residuals_host);
 // comm.cu
 int CommGetUniqueId(void* id128);
 int CommInit(Problem* p, int nranks, int rank, const void* id128);

@@ -1,0 +1,167 @@
+"""Flattened bundle-adjustment problem (the arrays of `sba_problem_desc`) and a thin
+object wrapper over the C-ABI handle.
+
+`FlatProblem` is what the host side produces from a Reconstruction in the reference's
+residual order (/root/reference/src/optim/bundle_adjustment.cc:326-478); `Solver` owns one
+`sba_handle` and forwards to the CUDA library.  Nothing here computes residuals on the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+
+
+class FlatProblem:
+    def __init__(self, image_qvec, image_tvec, image_camera, camera_model, camera_params, points,
+                 obs_image, obs_point, obs_xy, image_pose_constant=None, image_tvec_constant_mask=None,
+                 camera_param_constant_mask=None, point_constant=None, sem_maps=None, sem_weight=1.0):
+        self.image_qvec = capi.as_f64(image_qvec).reshape(-1, 4)
+        self.image_tvec = capi.as_f64(image_tvec).reshape(-1, 3)
+        self.image_camera = capi.as_i32(image_camera)
+        self.camera_model = capi.as_i32(camera_model)
+        cp = capi.as_f64(camera_params)
+        self.camera_params = np.zeros((len(self.camera_model), capi.MAX_CAMERA_PARAMS))
+        cp = cp.reshape(len(self.camera_model), -1)
+        self.camera_params[:, :cp.shape[1]] = cp
+        self.points = capi.as_f64(points).reshape(-1, 3)
+        self.obs_image = capi.as_i32(obs_image)
+        self.obs_point = capi.as_i32(obs_point)
+        self.obs_xy = capi.as_f64(obs_xy).reshape(-1, 2)
+        n_img, n_cam, n_pt = len(self.image_camera), len(self.camera_model), len(self.points)
+
+        def u8(a, n):
+            return np.zeros(n, np.uint8) if a is None else np.ascontiguousarray(a, dtype=np.uint8)
+        self.image_pose_constant = u8(image_pose_constant, n_img)
+        self.image_tvec_constant_mask = u8(image_tvec_constant_mask, n_img)
+        self.point_constant = u8(point_constant, n_pt)
+        self.camera_param_constant_mask = (np.zeros(n_cam, np.uint16) if camera_param_constant_mask is None
+                                           else np.ascontiguousarray(camera_param_constant_mask, dtype=np.uint16))
+        self.sem_maps = None if sem_maps is None else np.ascontiguousarray(sem_maps, dtype=np.float32)
+        self.sem_weight = float(sem_weight)
+
+    @property
+    def num_observations(self):
+        return len(self.obs_image)
+
+    def desc(self, shard_rank=0, shard_count=1):
+        d = capi.ProblemDesc()
+        d.num_images, d.num_cameras, d.num_points = len(self.image_camera), len(self.camera_model), len(self.points)
+        d.num_observations = len(self.obs_image)
+        d.image_qvec = capi.ptr(self.image_qvec, capi._dp)
+        d.image_tvec = capi.ptr(self.image_tvec, capi._dp)
+        d.image_camera = capi.ptr(self.image_camera, capi._ip)
+        d.image_pose_constant = capi.ptr(self.image_pose_constant, capi._u8p)
+        d.image_tvec_constant_mask = capi.ptr(self.image_tvec_constant_mask, capi._u8p)
+        d.camera_model = capi.ptr(self.camera_model, capi._ip)
+        d.camera_params = capi.ptr(self.camera_params, capi._dp)
+        d.camera_param_constant_mask = capi.ptr(self.camera_param_constant_mask, capi._u16p)
+        d.points = capi.ptr(self.points, capi._dp)
+        d.point_constant = capi.ptr(self.point_constant, capi._u8p)
+        d.obs_image = capi.ptr(self.obs_image, capi._ip)
+        d.obs_point = capi.ptr(self.obs_point, capi._ip)
+        d.obs_xy = capi.ptr(self.obs_xy, capi._dp)
+        if self.sem_maps is not None:
+            d.sem_maps = capi.ptr(self.sem_maps, capi._fp)
+            d.sem_height, d.sem_width = self.sem_maps.shape[1], self.sem_maps.shape[2]
+            d.sem_weight = self.sem_weight
+        d.shard_rank, d.shard_count = shard_rank, shard_count
+        d.global_num_observations = d.num_observations
+        return d
+
+    def counts(self):
+        """Structural counts of the reduced program (host only; no device needed)."""
+        s = capi.Summary()
+        capi.check(capi.load().sba_problem_counts(C.byref(self.desc()), C.byref(s)))
+        return s
+
+    def shard_masks(self, nranks, rank):
+        pk = np.zeros(len(self.points), np.uint8)
+        ok = np.zeros(len(self.obs_image), np.uint8)
+        capi.check(capi.load().sba_shard_points(C.byref(self.desc()), nranks, rank,
+                                                capi.ptr(pk, capi._u8p), capi.ptr(ok, capi._u8p)))
+        return pk, ok
+
+
+class Solver:
+    """One `sba_handle`: device-resident problem + LM solver."""
+
+    def __init__(self, problem, shard_rank=0, shard_count=1):
+        self.problem = problem
+        self.lib = capi.load()
+        self._h = C.c_void_p()
+        self._desc = problem.desc(shard_rank, shard_count)
+        capi.check(self.lib.sba_create(C.byref(self._desc), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self.lib.sba_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def init_comm(self, nranks, rank, unique_id):
+        buf = (C.c_char * capi.COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
+        capi.check(self.lib.sba_comm_init(self._h, nranks, rank, C.cast(buf, C.c_void_p)))
+
+    def evaluate(self, loss_type=capi.LOSS_TRIVIAL, loss_scale=1.0, apply_loss=True, want=("r", "pose", "intr", "point")):
+        n = self.problem.num_observations
+        out = {}
+        cost = C.c_double()
+        bufs = {
+            "r": np.zeros((n, 2)) if "r" in want else None,
+            "pose": np.zeros((n, 2, 6)) if "pose" in want else None,
+            "intr": np.zeros((n, 2, capi.MAX_CAMERA_PARAMS)) if "intr" in want else None,
+            "point": np.zeros((n, 2, 3)) if "point" in want else None,
+            "qvec": np.zeros((n, 2, 4)) if "qvec" in want else None,
+            "sem": np.zeros(n) if "sem" in want else None,
+        }
+        capi.check(self.lib.sba_evaluate(self._h, loss_type, loss_scale, 1 if apply_loss else 0, C.byref(cost),
+                                         *[capi.ptr(bufs[k], capi._dp) for k in ("r", "pose", "intr", "point", "qvec", "sem")]))
+        out = {k: v for k, v in bufs.items() if v is not None}
+        out["cost"] = cost.value
+        return out
+
+    def solve(self, options=None, callback=None):
+        o = options if options is not None else capi.default_solver_options()
+        s = capi.Summary()
+        if callback is not None:
+            def _cb(it_ptr, _user):
+                return int(callback(it_ptr.contents) or 0)
+            cb = capi.ITERATION_CALLBACK(_cb)
+        else:
+            cb = C.cast(None, capi.ITERATION_CALLBACK)
+        capi.check(self.lib.sba_solve(self._h, C.byref(o), cb, None, C.byref(s)))
+        return s
+
+    def trace(self, cap=4096):
+        rows = (capi.IterationSummary * cap)()
+        n = C.c_int32()
+        capi.check(self.lib.sba_get_trace(self._h, rows, cap, C.byref(n)))
+        return [rows[i] for i in range(n.value)]
+
+    def parameters(self):
+        p = self.problem
+        q = np.zeros_like(p.image_qvec); t = np.zeros_like(p.image_tvec)
+        cam = np.zeros_like(p.camera_params); X = p.points.copy()
+        capi.check(self.lib.sba_get_parameters(self._h, capi.ptr(q, capi._dp), capi.ptr(t, capi._dp),
+                                               capi.ptr(cam, capi._dp), capi.ptr(X, capi._dp)))
+        return q, t, cam, X
+
+    def bench_stage(self, stage, repeat=10):
+        ms = C.c_double(); nbytes = C.c_int64()
+        capi.check(self.lib.sba_bench_stage(self._h, stage.encode(), repeat, C.byref(ms), C.byref(nbytes)))
+        return ms.value, nbytes.value
+
+    def launches(self):
+        return int(self.lib.sba_kernel_launch_count(self._h))
+
+
+def comm_unique_id():
+    buf = (C.c_char * capi.COMM_ID_BYTES)()
+    capi.check(capi.load().sba_comm_get_unique_id(C.cast(buf, C.c_void_p)))
+    return bytes(buf)
