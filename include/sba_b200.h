@@ -203,6 +203,7 @@ typedef struct sba_summary {
   double time_eliminate_s;
   double time_linear_solve_s;
   double time_update_s;
+  double device_time_s; /* first kernel to last kernel of the solve, CUDA events on the solver's stream */
 } sba_summary;
 
 typedef struct sba_handle sba_handle;
@@ -219,6 +220,12 @@ int sba_create(const sba_problem_desc* desc, sba_handle** out);
  * src/optim/bundle_adjustment_test.cc:186-645).  Needs no device. */
 int sba_problem_counts(const sba_problem_desc* desc, sba_summary* counts);
 void sba_destroy(sba_handle* h);
+/* Select the CUDA device used by subsequent sba_create calls of this thread (one process per GPU). */
+int sba_set_device(int32_t device);
+/* Restore the parameters the handle was created with (kept resident on the device) and make the
+ * handle solvable again.  The reference's BundleAdjuster is one-shot (bundle_adjustment.cc:260);
+ * this exists so that a benchmark can time repeated solves with all inputs already in HBM. */
+int sba_reset(sba_handle* h);
 const char* sba_last_error(void);
 const char* sba_version(void);
 int sba_device_count(void);

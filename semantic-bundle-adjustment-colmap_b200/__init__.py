@@ -1,0 +1,13 @@
+"""B200-native bundle-adjustment hot path behind COLMAP's BundleAdjuster API.
+
+The product is `libsba_b200.so` (CUDA, sm_100a; C ABI in include/sba_b200.h).  This package
+is the host-side mirror used by tests and bench.py: ctypes binding (`_capi`), flattened problem
++ handle wrapper (`problem`), the BundleAdjuster / BundleAdjustmentConfig /
+BundleAdjustmentOptions mirror (`bundle_adjustment`) and the synthetic scene generator (`scene`).
+"""
+from . import _capi as capi  # noqa: F401
+from .problem import FlatProblem, Solver, comm_unique_id  # noqa: F401
+from .bundle_adjustment import (  # noqa: F401
+    BundleAdjuster, BundleAdjustmentConfig, BundleAdjustmentOptions, Camera, Image, Point2D, Point3D,
+    Reconstruction, Track, TrackElement)
+from . import scene  # noqa: F401

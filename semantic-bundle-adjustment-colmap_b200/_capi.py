@@ -92,7 +92,7 @@ class Summary(C.Structure):
         ("initial_cost", C.c_double), ("final_cost", C.c_double), ("fixed_cost", C.c_double),
         ("total_time_in_seconds", C.c_double),
         ("time_evaluate_s", C.c_double), ("time_eliminate_s", C.c_double),
-        ("time_linear_solve_s", C.c_double), ("time_update_s", C.c_double),
+        ("time_linear_solve_s", C.c_double), ("time_update_s", C.c_double), ("device_time_s", C.c_double),
     ]
 
     def as_dict(self):
@@ -129,6 +129,8 @@ SYMBOLS = {
     "sba_create": (C.c_int, [C.POINTER(ProblemDesc), C.POINTER(C.c_void_p)]),
     "sba_problem_counts": (C.c_int, [C.POINTER(ProblemDesc), C.POINTER(Summary)]),
     "sba_destroy": (None, [C.c_void_p]),
+    "sba_set_device": (C.c_int, [C.c_int32]),
+    "sba_reset": (C.c_int, [C.c_void_p]),
     "sba_last_error": (C.c_char_p, []),
     "sba_version": (C.c_char_p, []),
     "sba_device_count": (C.c_int, []),

@@ -77,6 +77,11 @@ void sba_destroy(sba_handle* h) {
   delete h;
 }
 
+int sba_set_device(int32_t device) {
+  SBA_CUDA(cudaSetDevice(device));
+  return SBA_OK;
+}
+
 static int CheckHandle(sba_handle* h) {
   if (!h || !h->p) { SetError(SBA_ERR_INVALID_ARGUMENT, "null handle"); return SBA_ERR_INVALID_ARGUMENT; }
   return SBA_OK;
@@ -152,6 +157,23 @@ int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callb
     return SBA_ERR_INVALID_ARGUMENT;
   }
   return SolveLM(h->p, &o, cb, user, summary);
+}
+
+int sba_reset(sba_handle* h) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  cudaStream_t st = p->stream;
+  auto cp = [&](double* dst, const double* src, size_t n) {
+    return n ? cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, st) : cudaSuccess;
+  };
+  SBA_CUDA(cp(p->d_pose.p, p->d_pose0.p, (size_t)p->n_img * 8)); SBA_CUDA(cp(p->d_pose2.p, p->d_pose0.p, (size_t)p->n_img * 8));
+  SBA_CUDA(cp(p->d_cam.p, p->d_cam0.p, (size_t)p->n_cam * 12)); SBA_CUDA(cp(p->d_cam2.p, p->d_cam0.p, (size_t)p->n_cam * 12));
+  SBA_CUDA(cp(p->d_X.p, p->d_X0.p, (size_t)p->n_pt * 3)); SBA_CUDA(cp(p->d_X2.p, p->d_X0.p, (size_t)p->n_pt * 3));
+  SBA_CUDA(cudaStreamSynchronize(st));
+  p->solved = false;
+  p->trace.clear();
+  return SBA_OK;
 }
 
 int sba_get_trace(sba_handle* h, sba_iteration_summary* rows, int32_t cap, int32_t* n) {

@@ -61,6 +61,9 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   DeviceScalars* hs = p->h_scalars;
   const LossView loss = {o.loss_function_type, o.loss_function_scale, 1};
   StageTimer tm;
+  cudaEvent_t ev_begin, ev_end;
+  SBA_CUDA(cudaEventCreate(&ev_begin)); SBA_CUDA(cudaEventCreate(&ev_end));
+  SBA_CUDA(cudaEventRecord(ev_begin, st));
   int rc;
   p->t_eval = p->t_elim = p->t_solve = p->t_update = 0.0;
 
@@ -200,6 +203,14 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     it.trust_region_radius = radius;
     p->trace.push_back(it);
     if (user_stop(it)) break;
+  }
+  {
+    float ms = 0.f;
+    cudaEventRecord(ev_end, st);
+    cudaEventSynchronize(ev_end);
+    cudaEventElapsedTime(&ms, ev_begin, ev_end);
+    sum->device_time_s = ms * 1e-3;
+    cudaEventDestroy(ev_begin); cudaEventDestroy(ev_end);
   }
   sum->termination_type = termination;
   sum->final_cost = x_cost + fixed_cost;

@@ -320,6 +320,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
     for (int a = 0; a < 3; ++a) X[3 * (size_t)q + a] = d.points[3 * (size_t)(p0 + q) + a];
   UP(p->d_pose.Upload(pose, st)); UP(p->d_cam.Upload(cam, st)); UP(p->d_X.Upload(X, st));
   UP(p->d_pose2.Upload(pose, st)); UP(p->d_cam2.Upload(cam, st)); UP(p->d_X2.Upload(X, st));
+  UP(p->d_pose0.Upload(pose, st)); UP(p->d_cam0.Upload(cam, st)); UP(p->d_X0.Upload(X, st));
   UP(p->d_img_cam.Upload(p->h_img_cam, st)); UP(p->d_model.Upload(p->h_model, st));
   UP(p->d_col_img.Upload(p->h_col_img, st)); UP(p->d_col_cam.Upload(p->h_col_cam, st));
   UP(p->d_k_cols.Upload(p->h_k_cols, st)); UP(p->d_k_slot.Upload(p->h_k_slot, st)); UP(p->d_k_dim.Upload(p->h_k_dim, st));

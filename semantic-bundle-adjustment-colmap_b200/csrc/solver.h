@@ -113,6 +113,7 @@ struct Problem {
 
   // ---- device: parameters (current / candidate) ----
   DevBuf<double> d_pose, d_cam, d_X, d_pose2, d_cam2, d_X2;
+  DevBuf<double> d_pose0, d_cam0, d_X0;  // parameters at creation (sba_reset)
 
   // ---- device: linearisation ----
   DevBuf<double> d_ER;   // [n_obs*8]

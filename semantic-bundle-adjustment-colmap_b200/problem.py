@@ -138,6 +138,9 @@ class Solver:
         capi.check(self.lib.sba_solve(self._h, C.byref(o), cb, None, C.byref(s)))
         return s
 
+    def reset(self):
+        capi.check(self.lib.sba_reset(self._h))
+
     def trace(self, cap=4096):
         rows = (capi.IterationSummary * cap)()
         n = C.c_int32()

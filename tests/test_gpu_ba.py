@@ -1,0 +1,49 @@
+"""GPU parity tests proper: the CUDA path through the C ABI against the CPU oracle."""
+import numpy as np
+import pytest
+
+from util import assert_eval_parity, oracle_evaluate, oracle_solve
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("model,refine", [("SIMPLE_RADIAL", True), ("SIMPLE_PINHOLE", False), ("SIMPLE_PINHOLE", True)])
+def test_eval_parity_small(sba, oracle, model, refine):
+    prob, _ = sba.scene.make_scene(n_cam=8, n_pt=500, mean_track=5.0, model=model, refine_intr=refine, seed=1,
+                                   width=640 if model == "SIMPLE_PINHOLE" else 1000, height=480 if model == "SIMPLE_PINHOLE" else 1000)
+    s = sba.Solver(prob)
+    ev = s.evaluate(want=("r", "pose", "intr", "point", "qvec"))
+    ref = oracle_evaluate(oracle, sba.capi, prob, qvec=True)
+    assert_eval_parity(ev, ref, prob)
+    assert np.linalg.norm(ev["qvec"] - ref["qvec"]) <= 1e-10 * np.linalg.norm(ref["qvec"])
+    s.close()
+
+
+@pytest.mark.parametrize("loss", [1, 2])
+def test_eval_parity_robust_loss(sba, oracle, loss):
+    prob, _ = sba.scene.make_scene(n_cam=8, n_pt=500, mean_track=5.0, seed=2)
+    s = sba.Solver(prob)
+    ev = s.evaluate(loss_type=loss, loss_scale=1.5)
+    ref = oracle_evaluate(oracle, sba.capi, prob, loss_type=loss, loss_scale=1.5)
+    assert_eval_parity(ev, ref, prob)
+    s.close()
+
+
+@pytest.mark.parametrize("solver", [0, 2])
+def test_solve_parity_c1(sba, oracle, solver):
+    prob, _ = sba.scene.make_config("C1")
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations = 10
+    o.linear_solver_type = solver
+    rc, so, tro, po = oracle_solve(oracle, sba.capi, prob, o)
+    s = sba.Solver(prob)
+    sg = s.solve(o)
+    trg = s.trace()
+    assert sg.initial_cost == pytest.approx(so.initial_cost, rel=1e-12)
+    assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
+    assert [r.step_is_successful for r in trg] == [r.step_is_successful for r in tro]
+    assert sg.num_residuals_reduced == so.num_residuals_reduced
+    assert sg.num_effective_parameters_reduced == so.num_effective_parameters_reduced
+    q, t, cam, X = s.parameters()
+    assert np.allclose(X, po[3], rtol=0, atol=1e-5)
+    s.close()
