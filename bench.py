@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 bundle-adjustment hot path.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload C2]
+
+A "step" is one Levenberg-Marquardt solve of LM_ITERS fixed iterations (tolerances 0, as the
+reference sets them: src/optim/bundle_adjustment.h:81-83) over one synthetic scene of the
+BASELINE.json shape: residual + Jacobian evaluation over all observations, point-block Schur
+elimination, reduced-system solve, update, candidate cost -- the whole hot path.
+`value` = observations x LM iterations per second with all inputs already resident in HBM
+(sba_reset between steps); `e2e` = the same through the C-ABI from HOST buffers (sba_create uploads,
+sba_solve, sba_get_parameters reads back) with the copies inside the timed region.
+N > 1: one process per GPU (torchrun), observations sharded by point, NCCL allreduce of the
+camera-space quantities; weak scaling (points per GPU fixed).
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+LM_ITERS = 10
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2", help="C1..C5 (BASELINE.json configs); C2 is the headline")
+    ap.add_argument("--extra", default="C4", help="larger workload whose stage rooflines are appended ('' = none)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc, self.lines = None, []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def make_workload(m, name, n_gpus):
+    """Weak scaling: points (and with them observations) per GPU fixed, cameras fixed."""
+    cfg = dict(m.scene.CONFIGS[name])
+    cfg["n_pt"] = cfg["n_pt"] * n_gpus
+    label_maps = name in ("C2",)  # C5's 5k maps (6 GB) are generated only on request
+    prob, _ = m.scene.make_scene(seed=0, label_maps=label_maps, **cfg)
+    return prob, cfg
+
+
+def solver_options(m, n_img):
+    o = m.capi.default_solver_options()
+    o.max_num_iterations = LM_ITERS
+    o.num_config_images = n_img
+    return o
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def cpu_solve(m, prob, opts, threads):
+    from oracle import loader
+    ora = loader.load(m.capi)
+    s = m.capi.Summary()
+    d = prob.desc()
+    t = time.perf_counter()
+    ora.oracle_ba_solve(C.byref(d), C.byref(opts), threads, C.byref(s), None, 0, None, None, None, None, None)
+    return time.perf_counter() - t, s, ora.oracle_num_threads() if threads <= 0 else threads
+
+
+def run_reference(args, m):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.  Ceres is not
+    installable here (no Eigen/Ceres/glog), so this arm times the oracle port of the Ceres path."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    prob, cfg = make_workload(m, args.workload, args.gpus)
+    o = solver_options(m, len(prob.image_camera))
+    for _ in range(args.warmup):
+        cpu_solve(m, prob, o, 0)
+    ts = []
+    for _ in range(args.steps):
+        dt, s, threads = cpu_solve(m, prob, o, 0)
+        ts.append(dt)
+    n_iter = s.num_successful_steps + s.num_unsuccessful_steps
+    sec = float(np.sum(ts)) / args.steps
+    val = prob.num_observations * n_iter / sec
+    line = {
+        "impl": "reference", "metric": "residual+Jacobian observations/s through the LM solve (observations x LM iterations / s)",
+        "value": val, "unit": "observations/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "lm_iterations_per_s": n_iter / sec,
+        "config": {"workload": "%s x%d: %d cams / %d pts / %d obs, %d LM iterations, reference solver policy" % (
+            args.workload, args.gpus, len(prob.image_camera), len(prob.points), prob.num_observations, LM_ITERS)},
+        "cpu_baseline": {"value": val, "unit": "observations/s", "cores": threads, "kind": "port",
+                         "sample": "%d full solves of %d LM iterations on the whole workload" % (args.steps, LM_ITERS)},
+        "e2e": {"value": val, "unit": "observations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "final_cost": s.final_cost,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def stage_table(solver, stages, repeat, hbm_peak):
+    out = {}
+    for st in stages:
+        try:
+            ms, nbytes = solver.bench_stage(st, repeat)
+        except Exception as e:  # a stage that does not apply to this solver regime
+            out[st] = {"error": str(e)}
+            continue
+        gbs = nbytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        out[st] = {"ms": ms, "algorithmic_bytes": nbytes, "GBps": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
+    return out
+
+
+def run_b200(args, m):
+    rank, world, local = dist_env()
+    lib = m.capi.load()
+    if lib.sba_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: the product has no CPU fallback")
+    m.capi.check(lib.sba_set_device(local))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    prob, cfg = make_workload(m, args.workload, args.gpus)
+    n_obs = prob.num_observations
+    o = solver_options(m, len(prob.image_camera))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    uid = None
+    if world > 1:
+        obj = [m.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        uid = obj[0]
+
+    def new_solver():
+        s = m.Solver(prob, shard_rank=rank, shard_count=world)
+        if world > 1:
+            s.init_comm(world, rank, uid)
+        return s
+
+    s = new_solver()
+    for _ in range(args.warmup):
+        s.reset(); summ = s.solve(o)
+    barrier()
+    clocks = ClockSampler(local)
+    l0 = s.launches()
+    dev_s, wall_s = 0.0, 0.0
+    for _ in range(args.steps):
+        s.reset()
+        barrier()
+        t = time.perf_counter()
+        summ = s.solve(o)  # ends with a stream synchronize
+        wall_s += time.perf_counter() - t
+        dev_s += summ.device_time_s
+    barrier()
+    clk = clocks.stop()
+    launches = s.launches() - l0
+    dev_s, wall_s = max_over_ranks(dev_s), max_over_ranks(wall_s)
+    n_iter = summ.num_successful_steps + summ.num_unsuccessful_steps
+    value = n_obs * n_iter * args.steps / dev_s
+
+    # ---- end to end through the C ABI from host buffers ----
+    e2e_s = 0.0
+    for i in range(args.warmup + args.steps):
+        barrier()
+        t = time.perf_counter()
+        s2 = new_solver()
+        s2.solve(o)
+        q, tt, cam, X = s2.parameters()
+        s2.close()
+        dt = time.perf_counter() - t
+        if i >= args.warmup:
+            e2e_s += dt
+    e2e_s = max_over_ranks(e2e_s)
+    h2d = int(prob.image_qvec.nbytes + prob.image_tvec.nbytes + prob.camera_params.nbytes + prob.points.nbytes +
+              prob.obs_xy.nbytes + prob.obs_image.nbytes + prob.obs_point.nbytes +
+              (prob.sem_maps.nbytes if prob.sem_maps is not None else 0))
+    d2h = int(q.nbytes + tt.nbytes + cam.nbytes + X.nbytes)
+
+    # ---- stage times (L2 flushed between launches) and the roofline of the dominant HBM-bound stage ----
+    hbm_peak, peak_kind = peaks()
+    dense = summ.linear_solver_type_used != m.capi.ITERATIVE_SCHUR
+    stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (["schur_dense", "cholesky"] if dense else ["schur_jacobi", "matvec"])
+    table = stage_table(s, stages, 20, hbm_peak)
+    hbm_stages = {k: v for k, v in table.items() if "ms" in v and k != "cholesky"}
+    top = max(hbm_stages, key=lambda k: hbm_stages[k]["ms"])
+    roof = {"bound": "hbm", "kernel": top, "achieved": table[top]["GBps"], "peak": hbm_peak, "unit": "GB/s",
+            "frac": table[top]["GBps"] / hbm_peak, "traffic": None, "peak_source": peak_kind,
+            "eval_frac": table["eval"]["GBps"] / hbm_peak}
+    line = {
+        "metric": "residual+Jacobian observations/s through the LM solve (observations x LM iterations / s)",
+        "value": value, "unit": "observations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_s / args.steps * 1e3, "wall_ms_per_step": wall_s / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "lm_iterations_per_s": n_iter * args.steps / dev_s,
+        "eval_observations_per_s": n_obs / world / (table["eval"]["ms"] * 1e-3) * world,
+        "config": {"workload": "%s x%d: %d cams / %d pts / %d obs, %d LM iterations, %s" % (
+            args.workload, world, len(prob.image_camera), len(prob.points), n_obs, LM_ITERS,
+            "DENSE_SCHUR device Cholesky" if dense else "ITERATIVE_SCHUR PCG + SCHUR_JACOBI"),
+            "l2": "stage timings flush L2 (256 MB memset) between launches; the LM step re-reads its own Jacobian",
+            "sharding": "points (with their observations) split across ranks, cameras replicated"},
+        "clocks": clk, "gpu_launches": int(launches),
+        "e2e": {"value": n_obs * n_iter * args.steps / e2e_s, "unit": "observations/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / args.steps * 1e3},
+        "roofline": roof, "stages": table, "final_cost": summ.final_cost,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        dt, so, threads = cpu_solve(m, prob, o, 0)
+        it_o = so.num_successful_steps + so.num_unsuccessful_steps
+        line["cpu_baseline"] = {"value": n_obs * it_o / dt, "unit": "observations/s", "cores": threads, "kind": "port",
+                                "sample": "1 full solve of %d LM iterations on the whole workload (%.2f s)" % (LM_ITERS, dt),
+                                "final_cost": so.final_cost,
+                                "final_cost_rel_diff": abs(so.final_cost - summ.final_cost) / so.final_cost}
+    if rank == 0 and world == 1 and args.extra and args.extra != args.workload:
+        s.close()
+        big, _ = make_workload(m, args.extra, 1)
+        sb = m.Solver(big)
+        ob = solver_options(m, len(big.image_camera))
+        sm = sb.solve(ob)
+        itb = sm.num_successful_steps + sm.num_unsuccessful_steps
+        it_stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (
+            ["schur_jacobi", "matvec"] if sm.linear_solver_type_used == m.capi.ITERATIVE_SCHUR else ["schur_dense", "cholesky"])
+        line["extra_workloads"] = {args.extra: {
+            "n_obs": big.num_observations, "lm_iterations_per_s": itb / sm.device_time_s,
+            "observations_per_s": big.num_observations * itb / sm.device_time_s,
+            "linear_solver_iterations": int(sm.num_linear_solver_iterations), "final_cost": sm.final_cost,
+            "stages": stage_table(sb, it_stages, 10, hbm_peak)}}
+        sb.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    m = importlib.import_module("semantic-bundle-adjustment-colmap_b200")
+    if args.impl == "reference":
+        run_reference(args, m)
+    else:
+        run_b200(args, m)
+
+
+if __name__ == "__main__":
+    main()

@@ -72,22 +72,23 @@ int CommInit(Problem* p, int nranks, int rank, const void* id128) {
     return SBA_ERR_INVALID_ARGUMENT;
   }
   if (!g_nccl.Load()) { SetError(SBA_ERR_COMM, "libnccl.so.2 could not be loaded"); return SBA_ERR_COMM; }
+  // One communicator per process and shape, shared by every handle (creating a communicator costs
+  // far more than a solve); it lives until the process exits.
+  static std::vector<Comm*> cache;
+  for (Comm* c : cache)
+    if (c->nranks == nranks && c->rank == rank) { p->comm = c; return SBA_OK; }
   ncclUniqueId id;
   std::memcpy(&id, id128, sizeof(id));
   Comm* c = new Comm();
   c->nranks = nranks; c->rank = rank;
   const ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
   if (r != ncclSuccess) { delete c; return NcclFail("ncclCommInitRank", r); }
+  cache.push_back(c);
   p->comm = c;
   return SBA_OK;
 }
 
-void CommDestroy(Problem* p) {
-  if (!p->comm) return;
-  if (p->comm->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(p->comm->comm);
-  delete p->comm;
-  p->comm = nullptr;
-}
+void CommDestroy(Problem* p) { p->comm = nullptr; }  // communicators are process-wide (see CommInit)
 
 static int AllReduce(Problem* p, double* d_buf, size_t n, ncclRedOp_t op) {
   if (!p->comm || n == 0) return SBA_OK;
