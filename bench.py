@@ -234,17 +234,20 @@ def run_b200(args, m):
     value = n_obs * n_iter * args.steps / dev_s
 
     # ---- end to end through the C ABI from host buffers ----
-    e2e_s = 0.0
+    e2e_s, e2e_phases = 0.0, np.zeros(3)
     for i in range(args.warmup + args.steps):
         barrier()
         t = time.perf_counter()
         s2 = new_solver()
+        t1 = time.perf_counter()
         s2.solve(o)
+        t2 = time.perf_counter()
         q, tt, cam, X = s2.parameters()
         s2.close()
         dt = time.perf_counter() - t
         if i >= args.warmup:
             e2e_s += dt
+            e2e_phases += np.array([t1 - t, t2 - t1, t + dt - t2])
     e2e_s = max_over_ranks(e2e_s)
     h2d = int(prob.image_qvec.nbytes + prob.image_tvec.nbytes + prob.camera_params.nbytes + prob.points.nbytes +
               prob.obs_xy.nbytes + prob.obs_image.nbytes + prob.obs_point.nbytes +
@@ -275,7 +278,8 @@ def run_b200(args, m):
             "sharding": "points (with their observations) split across ranks, cameras replicated"},
         "clocks": clk, "gpu_launches": int(launches),
         "e2e": {"value": n_obs * n_iter * args.steps / e2e_s, "unit": "observations/s",
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / args.steps * 1e3},
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / args.steps * 1e3,
+                "phases_ms": dict(zip(("create_h2d", "solve", "read_back_destroy"), (e2e_phases / args.steps * 1e3).round(3).tolist()))},
         "roofline": roof, "stages": table, "final_cost": summ.final_cost,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -32,52 +32,152 @@ __global__ void __launch_bounds__(256) chol_load_rhs_kernel(int n, const double*
   if (j < n) S[(size_t)n * n + j] = rhs[j];
 }
 
-__global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ S, int n, int k0,
+// ---- 64x64 diagonal block: warp-register Cholesky -----------------------------------------
+// The block is split 2x2 into 32x32 sub-blocks.  A 32x32 factorisation runs in ONE warp with
+// lane r holding row r in registers (fully unrolled, shuffles broadcast the pivot column), so
+// the 32-step dependency chain costs a shuffle + FMA per step instead of block-wide barriers.
+constexpr unsigned kFull = 0xffffffffu;
+
+// in: a[c] = A[lane][c] (lower part valid).  out: a[c] = L[lane][c] (zero above the diagonal).
+__device__ inline bool Chol32(double (&a)[32], int lane) {
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    double d = __shfl_sync(kFull, a[j], j);
+    if (!(d > 0.0) || !isfinite(d)) { ok = false; d = 1.0; }
+    const double s = sqrt(d), inv = 1.0 / s;
+    const double l = (lane == j) ? s : (lane > j ? a[j] * inv : 0.0);
+    a[j] = l;
+#pragma unroll
+    for (int c = j + 1; c < 32; ++c) {
+      const double lc = __shfl_sync(kFull, l, c);
+      a[c] -= l * lc;
+    }
+  }
+  return ok;
+}
+
+// lane c: column c of the inverse of the lower-triangular 32x32 L stored in shared memory
+// (row stride LDS, at L[0][0]); x[i] = Linv[i][c].
+__device__ inline void TriInv32(const double* __restrict__ L, int lane, double (&x)[32]) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    double s = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+    for (int k = 0; k < i; ++k) s -= L[i * LDS + k] * x[k];   // x[k] == 0 for k < lane
+    x[i] = (i >= lane) ? s / L[i * LDS + i] : 0.0;
+  }
+}
+
+__global__ void __launch_bounds__(128) potrf_diag_kernel(double* __restrict__ S, int n, int k0,
                                                          double* __restrict__ Linv, DeviceScalars* sc) {
   extern __shared__ double smem[];
-  double(*A)[LDS] = reinterpret_cast<double(*)[LDS]>(smem);
-  double(*X)[LDS] = reinterpret_cast<double(*)[LDS]>(smem + NB * LDS);
-  const int tid = threadIdx.x;
+  double(*A)[LDS] = reinterpret_cast<double(*)[LDS]>(smem);             // block, then its factor
+  double(*X)[LDS] = reinterpret_cast<double(*)[LDS]>(smem + NB * LDS);  // inverse of the factor
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const int nb = min(NB, n - k0);
-  for (int idx = tid; idx < NB * NB; idx += 256) {
+  for (int idx = tid; idx < NB * NB; idx += 128) {
     const int r = idx / NB, c = idx - r * NB;
-    double v = (r == c) ? 1.0 : 0.0;
+    double v = (r == c) ? 1.0 : 0.0;   // identity padding keeps a partial block well posed
     if (r < nb && c <= r) v = S[(size_t)(k0 + r) * n + k0 + c];
     A[r][c] = v;
     X[r][c] = 0.0;
   }
   __syncthreads();
-  for (int j = 0; j < nb; ++j) {
-    if (tid == 0) {
-      double d = A[j][j];
-      if (!(d > 0.0) || !isfinite(d)) { sc->chol_fail = 1; sc->solver_failed = 1; d = 1.0; }
-      A[j][j] = sqrt(d);
-    }
-    __syncthreads();
-    if (tid > j && tid < nb) A[tid][j] /= A[j][j];
-    __syncthreads();
-    for (int idx = tid; idx < nb * nb; idx += 256) {
-      const int r = idx / nb, c = idx - r * nb;
-      if (c > j && r >= c) A[r][c] -= A[r][j] * A[c][j];
-    }
-    __syncthreads();
-  }
-  for (int idx = tid; idx < nb * nb; idx += 256) {
-    const int r = idx / nb, c = idx - r * nb;
-    if (c <= r) S[(size_t)(k0 + r) * n + k0 + c] = A[r][c];
-  }
-  // Linv: column c of the inverse by forward substitution (thread c)
-  if (tid < NB) {
-    const int c = tid;
-    for (int i = c; i < NB; ++i) {
-      double s = (i == c) ? 1.0 : 0.0;
-      for (int k = c; k < i; ++k) s -= A[i][k] * X[k][c];
-      X[i][c] = s / A[i][i];
-    }
+  bool ok = true;
+  // (1) L11 = chol(A11)
+  if (w == 0) {
+    double a[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) a[c] = A[lane][c];
+    ok = Chol32(a, lane);
+#pragma unroll
+    for (int c = 0; c < 32; ++c) A[lane][c] = a[c];
   }
   __syncthreads();
-  for (int idx = tid; idx < NB * NB; idx += 256) {
+  // (2) warp 0: L21 = A21 L11^{-T} (one row per lane, forward substitution along the row);
+  //     warp 1: X11 = L11^{-1}
+  if (w == 0) {
+    double x[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      double s = A[32 + lane][c];
+#pragma unroll
+      for (int m = 0; m < c; ++m) s -= x[m] * A[c][m];
+      x[c] = s / A[c][c];
+    }
+#pragma unroll
+    for (int c = 0; c < 32; ++c) A[32 + lane][c] = x[c];
+  } else if (w == 1) {
+    double x[32];
+    TriInv32(&A[0][0], lane, x);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) X[i][lane] = x[i];
+  }
+  __syncthreads();
+  // (3) A22 -= L21 L21^T   (4 warps: row = lane, 8 columns each)
+  {
+    double acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
+    for (int m = 0; m < 32; ++m) {
+      const double l = A[32 + lane][m];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += l * A[32 + w * 8 + e][m];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) A[32 + lane][32 + w * 8 + e] -= acc[e];
+  }
+  __syncthreads();
+  // (4) L22 = chol(A22)
+  if (w == 0) {
+    double a[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) a[c] = A[32 + lane][32 + c];
+    ok = Chol32(a, lane) && ok;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) A[32 + lane][32 + c] = a[c];
+    if (!ok && lane == 0) { sc->chol_fail = 1; sc->solver_failed = 1; }
+  }
+  __syncthreads();
+  // (5) warp 0: X22 = L22^{-1};  warps 1..3 + 0 afterwards: T = L21 X11 (into the unused upper-right of A)
+  if (w == 0) {
+    double x[32];
+    TriInv32(&A[32][32], lane, x);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) X[32 + i][32 + lane] = x[i];
+  }
+  {
+    double acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
+    for (int m = 0; m < 32; ++m) {
+      const double l = A[32 + lane][m];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += l * X[m][w * 8 + e];
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) A[lane][32 + w * 8 + e] = acc[e];   // T[lane][.] parked above the diagonal
+  }
+  __syncthreads();
+  // (6) X21 = -X22 T
+  {
+    double acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
+    for (int m = 0; m < 32; ++m) {
+      const double l = X[32 + lane][32 + m];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += l * A[m][32 + w * 8 + e];
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) X[32 + lane][w * 8 + e] = -acc[e];
+  }
+  __syncthreads();
+  for (int idx = tid; idx < NB * NB; idx += 128) {
     const int r = idx / NB, c = idx - r * NB;
+    if (r < nb && c <= r) S[(size_t)(k0 + r) * n + k0 + c] = A[r][c];
     Linv[idx] = X[r][c];
   }
 }
@@ -234,7 +334,7 @@ int CholeskySolve(Problem* p) {
   for (int kb = 0; kb < nblk; ++kb) {
     const int k0 = kb * NB, nb = std::min(NB, n - k0);
     double* Linv = p->d_Linv.p + (size_t)kb * NB * NB;
-    potrf_diag_kernel<<<1, 256, dyn, st>>>(S, n, k0, Linv, p->d_scalars.p);
+    potrf_diag_kernel<<<1, 128, dyn, st>>>(S, n, k0, Linv, p->d_scalars.p);
     const int rem_rows = n_rows - (k0 + nb);
     const int row_tiles = DivUp(rem_rows, NB);
     trsm_panel_kernel<<<row_tiles, 256, dyn, st>>>(S, n, n_rows, k0, Linv);

@@ -62,6 +62,15 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
             const double* __restrict__ scale_p, double* __restrict__ ER, double2* __restrict__ F,
             double* __restrict__ cost_partial, double* __restrict__ Jq_ambient) {
   const int k = blockIdx.x * kEvalThreads + threadIdx.x;
+  // Output staging: every thread produces one 64 B ER record and one 16*dc B F record.  Written
+  // straight to HBM that is a 32-way strided store per instruction; instead each warp assembles its
+  // 32 records in shared memory (row strides of 5 and dc+1 16-byte units: odd, so conflict-free) and
+  // streams them out as one contiguous, fully coalesced block.
+  extern __shared__ double2 stage[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int dcs = S.dc + 1;
+  double2* sER = stage + (size_t)warp * 32 * (5 + dcs);
+  double2* sF = sER + 32 * 5;
   double cost = 0.0, fixed = 0.0;
   if (k < S.n_obs) {
     const int i = S.obs_img[k], pt = S.obs_pt[k];
@@ -82,7 +91,7 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
         else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
       }
     }
-    const double2 xy = reinterpret_cast<const double2*>(S.obs_xy)[k];
+    const double2 xy = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k);
     ObsGeom g;
     RotateWithJac(q, t, X, &g, true);
     const double iz = 1.0 / g.p[2];
@@ -109,8 +118,8 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
     double rho[3];
     LossEval(L.type, L.scale, s, rho);
     const bool active = S.obs_active[k] != 0;
-    double2* Fk = F + (size_t)k * S.dc;
-    double* ERk = ER + (size_t)k * 8;
+    double2* Fk = sF + lane * dcs;
+    double* ERk = reinterpret_cast<double*>(sER + lane * 5);
     if (!active) {
       fixed = 0.5 * rho[0];
       for (int j = 0; j < S.dc; ++j) Fk[j] = make_double2(0.0, 0.0);
@@ -201,6 +210,21 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
       reinterpret_cast<double2*>(ERk)[3] = make_double2(r0, r1);
     }
   }
+  __syncwarp();
+  {
+    const int k0 = blockIdx.x * kEvalThreads + warp * 32;  // first observation of this warp
+    const int n_valid = min(32, S.n_obs - k0);
+    if (n_valid > 0) {
+      double2* gER = reinterpret_cast<double2*>(ER) + (size_t)k0 * 4;
+      for (int idx = lane; idx < n_valid * 4; idx += 32) gER[idx] = sER[(idx >> 2) * 5 + (idx & 3)];
+      double2* gF = F + (size_t)k0 * S.dc;
+      const int dc = S.dc;
+      for (int idx = lane; idx < n_valid * dc; idx += 32) {
+        const int row = idx / dc;
+        gF[idx] = sF[row * dcs + (idx - row * dc)];
+      }
+    }
+  }
   BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
 }
 
@@ -247,7 +271,9 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
 
 template <int MODEL>
 static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
-  eval_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(
+  const size_t smem = (size_t)(kEvalThreads / 32) * 32 * (5 + p->dc + 1) * sizeof(double2);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(eval_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  eval_kernel<MODEL><<<blocks, kEvalThreads, smem, p->stream>>>(
       p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_c.p : nullptr,
       use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, p->jq_out);
 }

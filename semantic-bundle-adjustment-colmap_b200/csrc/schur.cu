@@ -9,12 +9,15 @@
 // selected at bundle_adjustment.cc:283-286.
 //
 // Work decomposition
-//   * "diagonal" contributions (observation a with itself): image-major chunks of <=256
-//     observations; a warp walks 32 observations, lanes own the DCxDC output elements;
-//     chunk partials are summed per image in a fixed order.
-//   * "off-diagonal" contributions: host-built list of observation pairs (a,b) of one
-//     point with image(a) > image(b), sorted by (image(a), image(b)) key; one warp per
-//     key accumulates its block in registers and is its only writer.
+//   * per observation a (one pass): W_a = F_a^T E_a (DC x 3) and H_a = W_a C_p^{-1}.
+//   * "diagonal" contributions F_a^T F_a - H_a W_a^T: image-major chunks of <= 256
+//     observations; lanes own the DC x DC output elements; chunk partials are summed per
+//     image in a fixed order.
+//   * "off-diagonal" contributions -H_a W_b^T: host-built list of observation pairs (a,b)
+//     of one point with image(a) > image(b), counting-sorted by the (image(a), image(b)) key
+//     and cut into segments of <= kSegPairs pairs.  One warp reduces one segment in registers
+//     (a warp-level segmented reduction keyed by camera pair); the segment partials of a key
+//     are then summed in a fixed order by the key's single writer.  Bit-reproducible.
 //   * intrinsics shared by several images (and duplicate observations of one point in
 //     one image) have several writers per entry; only those entries use fp64 atomics.
 #include <algorithm>
@@ -30,54 +33,26 @@ namespace sba {
     case 14: CALL(14); break; default: CALL(18); break;                               \
   }
 
+constexpr int kSegPairs = 64;
 template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; };
 
-struct PairSmem {            // per warp
-  double Ha[kMaxDC][3];
-  double Wb[kMaxDC][3];
-  double2 Fa[kMaxDC];
-};
-
-// accumulate the contribution of the ordered observation pair (a,b) of one point:
-//   acc[e] -= (W_a C^{-1}) [ja] . W_b[jb]     (+ F_a[ja].F_a[jb] when a == b)
+// W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (observation, slot)
 template <int DC>
-__device__ inline void AccumulatePair(const StructView& S, const double* __restrict__ ER, const double2* __restrict__ F,
-                                      const double* __restrict__ Cinv, int a, int b, PairSmem* sm,
-                                      double (&acc)[Elems<DC>::N]) {
-  const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const double* __restrict__ ER,
+                                                       const double2* __restrict__ F, const double* __restrict__ Cinv,
+                                                       double* __restrict__ W, double* __restrict__ H) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= (int64_t)S.n_obs * DC) return;
+  const int a = (int)(t / DC);
+  const double2 f = F[t];
+  const double2* ea = reinterpret_cast<const double2*>(ER + (size_t)a * 8);
+  const double2 e0 = ea[0], e1 = ea[1], e2 = ea[2];  // E row0 = (e0.x e0.y e1.x), row1 = (e1.y e2.x e2.y)
+  const double w[3] = {f.x * e0.x + f.y * e1.y, f.x * e0.y + f.y * e2.x, f.x * e1.x + f.y * e2.y};
+  double h[3] = {0.0, 0.0, 0.0};
   const int po = S.p_off[S.obs_pt[a]];
-  if (lane < DC) {
-    const double2 fa = F[(size_t)a * DC + lane];
-    const double2* ea = reinterpret_cast<const double2*>(ER + (size_t)a * 8);
-    const double2 e0 = ea[0], e1 = ea[1], e2 = ea[2];
-    double wa[3] = {fa.x * e0.x + fa.y * e1.y, fa.x * e0.y + fa.y * e2.x, fa.x * e1.x + fa.y * e2.y};
-    double h[3] = {0.0, 0.0, 0.0};
-    if (po >= 0) Sym3Mul(Cinv + 6 * (size_t)po, wa, h);
-    sm->Ha[lane][0] = h[0]; sm->Ha[lane][1] = h[1]; sm->Ha[lane][2] = h[2];
-    if (a == b) {
-      sm->Wb[lane][0] = wa[0]; sm->Wb[lane][1] = wa[1]; sm->Wb[lane][2] = wa[2];
-      sm->Fa[lane] = fa;
-    } else {
-      const double2 fb = F[(size_t)b * DC + lane];
-      const double2* eb = reinterpret_cast<const double2*>(ER + (size_t)b * 8);
-      const double2 g0 = eb[0], g1 = eb[1], g2 = eb[2];
-      sm->Wb[lane][0] = fb.x * g0.x + fb.y * g1.y;
-      sm->Wb[lane][1] = fb.x * g0.y + fb.y * g2.x;
-      sm->Wb[lane][2] = fb.x * g1.x + fb.y * g2.y;
-    }
-  }
-  __syncwarp();
-#pragma unroll
-  for (int q = 0; q < Elems<DC>::N; ++q) {
-    const int e = lane + 32 * q;
-    if (e < DC * DC) {
-      const int ja = e / DC, jb = e - ja * DC;
-      double v = -(sm->Ha[ja][0] * sm->Wb[jb][0] + sm->Ha[ja][1] * sm->Wb[jb][1] + sm->Ha[ja][2] * sm->Wb[jb][2]);
-      if (a == b) v += sm->Fa[ja].x * sm->Fa[jb].x + sm->Fa[ja].y * sm->Fa[jb].y;
-      acc[q] += v;
-    }
-  }
-  __syncwarp();
+  if (po >= 0) Sym3Mul(Cinv + 6 * (size_t)po, w, h);
+  W[3 * t] = w[0]; W[3 * t + 1] = w[1]; W[3 * t + 2] = w[2];
+  H[3 * t] = h[0]; H[3 * t + 1] = h[1]; H[3 * t + 2] = h[2];
 }
 
 // compact column of slot j of an observation of image i (camera c)
@@ -117,20 +92,30 @@ __device__ inline void Emit(const Sink& k, int row, int col, double v, bool same
 
 // ---- diagonal contributions: chunk partial blocks -------------------------------------
 template <int DC>
-__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(StructView S, ChunkView C, const double* __restrict__ ER,
-                                                               const double2* __restrict__ F, const double* __restrict__ Cinv,
+__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, const double2* __restrict__ F,
+                                                               const double* __restrict__ W, const double* __restrict__ H,
                                                                double* __restrict__ partial) {
-  __shared__ PairSmem sm[8];
   __shared__ double red[8][DC * DC];
   const int ch = blockIdx.x, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
   double acc[Elems<DC>::N];
+  int ja[Elems<DC>::N], jb[Elems<DC>::N];
 #pragma unroll
-  for (int q = 0; q < Elems<DC>::N; ++q) acc[q] = 0.0;
+  for (int q = 0; q < Elems<DC>::N; ++q) {
+    acc[q] = 0.0;
+    const int e = min(lane + 32 * q, DC * DC - 1);
+    ja[q] = e / DC; jb[q] = e - ja[q] * DC;
+  }
   const int lo = w * 32, hi = min(n, lo + 32);
   for (int t = lo; t < hi; ++t) {
-    const int a = C.cam_order[s0 + t];
-    AccumulatePair<DC>(S, ER, F, Cinv, a, a, &sm[w], acc);
+    const size_t a = (size_t)C.cam_order[s0 + t] * DC;
+#pragma unroll
+    for (int q = 0; q < Elems<DC>::N; ++q) {
+      const double2 fa = F[a + ja[q]], fb = F[a + jb[q]];
+      const double* h = H + 3 * (a + ja[q]);
+      const double* wv = W + 3 * (a + jb[q]);
+      acc[q] += (fa.x * fb.x + fa.y * fb.y) - (h[0] * wv[0] + h[1] * wv[1] + h[2] * wv[2]);
+    }
   }
 #pragma unroll
   for (int q = 0; q < Elems<DC>::N; ++q) { const int e = lane + 32 * q; if (e < DC * DC) red[w][e] = acc[q]; }
@@ -159,35 +144,61 @@ __global__ void __launch_bounds__(128) schur_diag_finalize_kernel(StructView S, 
   }
 }
 
-// ---- off-diagonal contributions: one warp per (image a, image b) key --------------------
+// ---- off-diagonal contributions ---------------------------------------------------------
+// one warp per segment (<= kSegPairs pairs of one key): partial[seg] = - sum H_a W_b^T
 template <int DC>
-__global__ void __launch_bounds__(128) schur_pair_kernel(StructView S, int n_keys, const int* __restrict__ key_ptr,
-                                                         const int* __restrict__ key_gi, const int* __restrict__ key_gj,
-                                                         const int* __restrict__ pa, const int* __restrict__ pb,
-                                                         const double* __restrict__ ER, const double2* __restrict__ F,
-                                                         const double* __restrict__ Cinv, Sink sink, int cam_only) {
-  __shared__ PairSmem sm[4];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int key = blockIdx.x * 4 + w;
-  if (key >= n_keys) return;
+__global__ void __launch_bounds__(128) schur_pair_segment_kernel(int n_seg, const int* __restrict__ seg_ptr,
+                                                                 const int* __restrict__ pa, const int* __restrict__ pb,
+                                                                 const double* __restrict__ W, const double* __restrict__ H,
+                                                                 double* __restrict__ partial) {
+  const int seg = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (seg >= n_seg) return;
   double acc[Elems<DC>::N];
+  int ja[Elems<DC>::N], jb[Elems<DC>::N];
 #pragma unroll
-  for (int q = 0; q < Elems<DC>::N; ++q) acc[q] = 0.0;
-  for (int t = key_ptr[key]; t < key_ptr[key + 1]; ++t) AccumulatePair<DC>(S, ER, F, Cinv, pa[t], pb[t], &sm[w], acc);
+  for (int q = 0; q < Elems<DC>::N; ++q) {
+    acc[q] = 0.0;
+    const int e = min(lane + 32 * q, DC * DC - 1);
+    ja[q] = e / DC; jb[q] = e - ja[q] * DC;
+  }
+  const int t0 = seg_ptr[seg], t1 = seg_ptr[seg + 1];
+  for (int t = t0; t < t1; ++t) {
+    const size_t a = (size_t)pa[t] * DC, b = (size_t)pb[t] * DC;
+#pragma unroll
+    for (int q = 0; q < Elems<DC>::N; ++q) {
+      const double* h = H + 3 * (a + ja[q]);
+      const double* wv = W + 3 * (b + jb[q]);
+      acc[q] -= h[0] * wv[0] + h[1] * wv[1] + h[2] * wv[2];
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < Elems<DC>::N; ++q) {
+    const int e = lane + 32 * q;
+    if (e < DC * DC) partial[(size_t)seg * DC * DC + e] = acc[q];
+  }
+}
+
+// one warp per key: fixed-order sum of its segment partials, then the single write per entry
+template <int DC>
+__global__ void __launch_bounds__(128) schur_pair_emit_kernel(StructView S, int n_keys, const int* __restrict__ key_seg_ptr,
+                                                              const int* __restrict__ key_gi, const int* __restrict__ key_gj,
+                                                              const double* __restrict__ partial, Sink sink) {
+  const int key = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (key >= n_keys) return;
+  const int s0 = key_seg_ptr[key], s1 = key_seg_ptr[key + 1];
   const int gi = key_gi[key], gj = key_gj[key];
   const int ci = S.img_cam[gi], cj = S.img_cam[gj];
   const bool same = gi == gj;
 #pragma unroll
   for (int q = 0; q < Elems<DC>::N; ++q) {
     const int e = lane + 32 * q;
-    if (e < DC * DC) {
-      const int ja = e / DC, jb = e - ja * DC;
-      const bool intr = (ja >= 6 || jb >= 6);
-      if (cam_only && !(ja >= 6 && jb >= 6)) continue;
-      // duplicate-observation keys (same image) add on top of the chunk result -> atomics
-      const bool atomic = same || (sink.shared_intr && intr);
-      Emit(sink, SlotCol(S, gi, ci, ja), SlotCol(S, gj, cj, jb), acc[q], same, atomic);
-    }
+    if (e >= DC * DC) continue;
+    double a = 0.0;
+    for (int sg = s0; sg < s1; ++sg) a += partial[(size_t)sg * DC * DC + e];
+    const int ja = e / DC, jb = e - ja * DC;
+    // duplicate-observation keys (same image) add on top of the chunk result -> atomics
+    const bool atomic = same || (sink.shared_intr && (ja >= 6 || jb >= 6));
+    Emit(sink, SlotCol(S, gi, ci, ja), SlotCol(S, gj, cj, jb), a, same, atomic);
   }
 }
 
@@ -246,55 +257,94 @@ __global__ void __launch_bounds__(64) invert_blocks_kernel(int n_blk, const int*
 // dense == false: only what SCHUR_JACOBI needs beyond the per-observation diagonal terms:
 //                 duplicates inside one image, and -- when intrinsics are shared -- all pairs
 //                 whose two images use the same camera (camera x camera block only).
+// Pairs are counting-sorted by key (stable in point order) and cut into <= kSegPairs segments.
 int BuildPairLists(Problem* p, bool dense) {
-  if (dense ? p->pairs_built : p->diag_built) return SBA_OK;
-  const int n_pt = p->n_pt;
+  PairList& L = dense ? p->pairs_dense : p->pairs_diag;
+  if (L.built) return SBA_OK;
+  const int n_pt = p->n_pt, n_img = p->n_img;
+  const std::vector<int>& img = p->h_obs_img;
   std::vector<int> pt_ptr(n_pt + 1, 0);
   for (int k = 0; k < p->n_obs; ++k) pt_ptr[p->h_obs_pt[k] + 1]++;
   for (int q = 0; q < n_pt; ++q) pt_ptr[q + 1] += pt_ptr[q];
-  const std::vector<int>& img = p->h_obs_img;
-  auto wanted = [&](int a, int b) -> bool {  // a != b, ordered so that img[a] >= img[b]
-    if (p->h_p_off[p->h_obs_pt[a]] < 0) return false;   // constant point: E = 0
-    if (img[a] == img[b]) return true;
-    if (dense) return true;
-    if (!p->shared_intrinsics) return false;
-    const int ca = p->h_img_cam[img[a]], cb = p->h_img_cam[img[b]];
-    return ca == cb && p->h_k_dim[ca] > 0;
-  };
+  // which points can contribute at all
+  bool any = dense;
+  std::vector<uint8_t> has_dup(n_pt, 0);
+  {
+    std::vector<int> stamp(std::max(1, n_img), -1);
+    for (int q = 0; q < n_pt; ++q) {
+      if (p->h_p_off[q] < 0) continue;
+      for (int s = pt_ptr[q]; s < pt_ptr[q + 1]; ++s) {
+        if (stamp[img[s]] == q) { has_dup[q] = 1; any = true; }
+        stamp[img[s]] = q;
+      }
+    }
+  }
+  const bool shared = !dense && p->shared_intrinsics;
+  if (shared) any = true;
   struct Ent { int64_t key; int a, b; };
   std::vector<Ent> ents;
-  for (int q = 0; q < n_pt; ++q) {
-    for (int s = pt_ptr[q]; s < pt_ptr[q + 1]; ++s)
-      for (int t = pt_ptr[q]; t < pt_ptr[q + 1]; ++t) {
-        if (s == t) continue;
-        int a = s, b = t;
-        if (img[a] < img[b]) continue;                 // the (b,a) visit handles it
-        if (img[a] == img[b]) { /* ordered both ways */ }
-        if (!wanted(a, b)) continue;
-        ents.push_back({(int64_t)img[a] * p->n_img + img[b], a, b});
-      }
-  }
-  std::stable_sort(ents.begin(), ents.end(), [](const Ent& x, const Ent& y) { return x.key < y.key; });
-  std::vector<int> key_ptr, key_gi, key_gj, pa(ents.size()), pb(ents.size());
-  for (size_t e = 0; e < ents.size(); ++e) {
-    if (e == 0 || ents[e].key != ents[e - 1].key) {
-      key_ptr.push_back((int)e);
-      key_gi.push_back((int)(ents[e].key / p->n_img)); key_gj.push_back((int)(ents[e].key % p->n_img));
+  if (any) {
+    auto wanted = [&](int a, int b) -> bool {  // img[a] >= img[b]
+      if (img[a] == img[b]) return true;
+      if (dense) return true;
+      if (!shared) return false;
+      const int ca = p->h_img_cam[img[a]], cb = p->h_img_cam[img[b]];
+      return ca == cb && p->h_k_dim[ca] > 0;
+    };
+    size_t guess = 0;
+    if (dense) for (int q = 0; q < n_pt; ++q) { const size_t l = pt_ptr[q + 1] - pt_ptr[q]; guess += l * (l - 1) / 2; }
+    ents.reserve(guess);
+    for (int q = 0; q < n_pt; ++q) {
+      if (p->h_p_off[q] < 0) continue;            // constant point: E = 0
+      if (!dense && !shared && !has_dup[q]) continue;
+      for (int s = pt_ptr[q]; s < pt_ptr[q + 1]; ++s)
+        for (int t = pt_ptr[q]; t < pt_ptr[q + 1]; ++t) {
+          if (s == t || img[s] < img[t]) continue;  // the (t,s) visit handles img[s] < img[t]
+          if (!wanted(s, t)) continue;
+          ents.push_back({(int64_t)img[s] * n_img + img[t], s, t});
+        }
     }
-    pa[e] = ents[e].a; pb[e] = ents[e].b;
+  }
+  // counting sort by key when the key space is small enough, else comparison sort
+  const int64_t key_space = (int64_t)n_img * n_img;
+  std::vector<int> pa(ents.size()), pb(ents.size()), key_ptr, key_gi, key_gj;
+  if (!ents.empty() && key_space <= (int64_t)4 << 20) {
+    std::vector<int> cnt(key_space + 1, 0);
+    for (const Ent& e : ents) cnt[e.key + 1]++;
+    for (int64_t k = 0; k < key_space; ++k) {
+      if (cnt[k + 1] > 0) { key_ptr.push_back(cnt[k]); key_gi.push_back((int)(k / n_img)); key_gj.push_back((int)(k % n_img)); }
+      cnt[k + 1] += cnt[k];
+    }
+    for (const Ent& e : ents) { const int pos = cnt[e.key]++; pa[pos] = e.a; pb[pos] = e.b; }
+  } else {
+    std::stable_sort(ents.begin(), ents.end(), [](const Ent& x, const Ent& y) { return x.key < y.key; });
+    for (size_t e = 0; e < ents.size(); ++e) {
+      if (e == 0 || ents[e].key != ents[e - 1].key) {
+        key_ptr.push_back((int)e);
+        key_gi.push_back((int)(ents[e].key / n_img)); key_gj.push_back((int)(ents[e].key % n_img));
+      }
+      pa[e] = ents[e].a; pb[e] = ents[e].b;
+    }
   }
   key_ptr.push_back((int)ents.size());
-  cudaStream_t st = p->stream;
-  if (dense) {
-    SBA_CUDA(p->d_pair_key_ptr.Upload(key_ptr, st)); SBA_CUDA(p->d_pair_key_gi.Upload(key_gi, st));
-    SBA_CUDA(p->d_pair_key_gj.Upload(key_gj, st)); SBA_CUDA(p->d_pair_a.Upload(pa, st)); SBA_CUDA(p->d_pair_b.Upload(pb, st));
-    p->n_pair_keys = (int)key_gi.size(); p->n_pairs = (int64_t)ents.size(); p->pairs_built = true;
-  } else {
-    SBA_CUDA(p->d_diag_key_ptr.Upload(key_ptr, st)); SBA_CUDA(p->d_diag_key_gi.Upload(key_gi, st));
-    SBA_CUDA(p->d_diag_key_gj.Upload(key_gj, st)); SBA_CUDA(p->d_diag_a.Upload(pa, st)); SBA_CUDA(p->d_diag_b.Upload(pb, st));
-    p->n_diag_keys = (int)key_gi.size(); p->n_diag_pairs = (int64_t)ents.size(); p->diag_built = true;
+  // segments
+  std::vector<int> seg_ptr, key_seg_ptr;
+  for (size_t k = 0; k + 1 < key_ptr.size(); ++k) {
+    key_seg_ptr.push_back((int)seg_ptr.size());
+    for (int s = key_ptr[k]; s < key_ptr[k + 1]; s += kSegPairs) seg_ptr.push_back(s);
   }
+  key_seg_ptr.push_back((int)seg_ptr.size());
+  L.n_seg = (int)seg_ptr.size();
+  seg_ptr.push_back((int)ents.size());
+  L.n_keys = (int)key_gi.size();
+  L.n_pairs = (int64_t)ents.size();
+  cudaStream_t st = p->stream;
+  SBA_CUDA(L.seg_ptr.Upload(seg_ptr, st)); SBA_CUDA(L.key_seg_ptr.Upload(key_seg_ptr, st));
+  SBA_CUDA(L.key_gi.Upload(key_gi, st)); SBA_CUDA(L.key_gj.Upload(key_gj, st));
+  SBA_CUDA(L.a.Upload(pa, st)); SBA_CUDA(L.b.Upload(pb, st));
+  SBA_CUDA(L.partial.Alloc((size_t)std::max(1, L.n_seg) * p->dc * p->dc));
   SBA_CUDA(cudaStreamSynchronize(st));
+  L.built = true;
   return SBA_OK;
 }
 
@@ -309,18 +359,30 @@ static int EnsureBlockStorage(Problem* p) {
   return SBA_OK;
 }
 
-static int DiagChunks(Problem* p, const Sink& sink) {
-  if (p->n_chunks == 0) return SBA_OK;
-  SBA_CUDA(p->d_chunk_block.Alloc((size_t)p->n_chunks * p->dc * p->dc));
-#define CALL(DC)                                                                                                     \
-  do {                                                                                                               \
-    schur_diag_chunk_kernel<DC><<<p->n_chunks, 256, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p,    \
-                                                                    p->d_Cinv.p, p->d_chunk_block.p);                 \
-    schur_diag_finalize_kernel<DC><<<p->n_img, 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink); \
+// W/H pass + diagonal chunks + pair segments into `sink`
+static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
+  const int dc = p->dc;
+  cudaStream_t st = p->stream;
+  if (p->n_obs == 0) return SBA_OK;
+  SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * dc * 3)); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * dc * 3));
+  SBA_CUDA(p->d_chunk_block.Alloc((size_t)std::max(1, p->n_chunks) * dc * dc));
+#define CALL(DC)                                                                                                          \
+  do {                                                                                                                    \
+    schur_wh_kernel<DC><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, \
+                                                                          p->d_W.p, p->d_H.p);                            \
+    schur_diag_chunk_kernel<DC><<<p->n_chunks, 256, 0, st>>>(p->Chunks(), p->d_F.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p); \
+    schur_diag_finalize_kernel<DC><<<p->n_img, 128, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);          \
+    p->launches += 3;                                                                                                     \
+    if (L.n_seg > 0) {                                                                                                    \
+      schur_pair_segment_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.a.p, L.b.p, p->d_W.p,       \
+                                                                      p->d_H.p, L.partial.p);                             \
+      schur_pair_emit_kernel<DC><<<DivUp(L.n_keys, 4), 128, 0, st>>>(p->Struct(), L.n_keys, L.key_seg_ptr.p, L.key_gi.p,   \
+                                                                    L.key_gj.p, L.partial.p, sink);                       \
+      p->launches += 2;                                                                                                   \
+    }                                                                                                                     \
   } while (0)
-  SBA_DC_SWITCH(p->dc, CALL)
+  SBA_DC_SWITCH(dc, CALL)
 #undef CALL
-  p->launches += 2;
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }
@@ -334,14 +396,8 @@ int BuildDenseSchur(Problem* p) {
   Sink sink;
   std::memset(&sink, 0, sizeof(sink));
   sink.kind = 0; sink.S = p->d_S.p; sink.n = (int)n; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
-  rc = DiagChunks(p, sink);
+  rc = Accumulate(p, p->pairs_dense, sink);
   if (rc) return rc;
-  if (p->n_pair_keys > 0) {
-#define CALL(DC) schur_pair_kernel<DC><<<DivUp(p->n_pair_keys, 4), 128, 0, p->stream>>>(p->Struct(), p->n_pair_keys, p->d_pair_key_ptr.p, p->d_pair_key_gi.p, p->d_pair_key_gj.p, p->d_pair_a.p, p->d_pair_b.p, p->d_ER.p, p->d_F.p, p->d_Cinv.p, sink, 0)
-    SBA_DC_SWITCH(p->dc, CALL)
-#undef CALL
-    p->launches++;
-  }
   rc = AllReduceSum(p, p->d_S.p, n * n);
   if (rc) return rc;
   if (n > 0) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, p->d_S.p, p->d_Dc.p); p->launches++; }
@@ -360,15 +416,8 @@ int BuildSchurJacobi(Problem* p) {
   std::memset(&sink, 0, sizeof(sink));
   sink.kind = 1; sink.M = p->d_M.p; sink.col_blk = p->d_col_blk.p; sink.blk_off = p->d_blk_off.p;
   sink.blk_dim = p->d_blk_dim.p; sink.blk_moff = p->d_blk_moff.p; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
-  rc = DiagChunks(p, sink);
+  rc = Accumulate(p, p->pairs_diag, sink);
   if (rc) return rc;
-  if (p->n_diag_keys > 0) {
-    // keys of one image: all elements; keys of two images sharing a camera: camera x camera elements only
-#define CALL(DC) schur_pair_kernel<DC><<<DivUp(p->n_diag_keys, 4), 128, 0, p->stream>>>(p->Struct(), p->n_diag_keys, p->d_diag_key_ptr.p, p->d_diag_key_gi.p, p->d_diag_key_gj.p, p->d_diag_a.p, p->d_diag_b.p, p->d_ER.p, p->d_F.p, p->d_Cinv.p, sink, 0)
-    SBA_DC_SWITCH(p->dc, CALL)
-#undef CALL
-    p->launches++;
-  }
   rc = AllReduceSum(p, p->d_M.p, p->m_size);
   if (rc) return rc;
   invert_blocks_kernel<<<DivUp(p->n_blk, 64), 64, 0, p->stream>>>(p->n_blk, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,

@@ -70,6 +70,15 @@ struct DeviceScalars {
 
 class Comm;  // NCCL wrapper (comm.cu)
 
+// pairs (a,b) of observations of one point, sorted by (image(a), image(b)) key, in segments
+struct PairList {
+  DevBuf<int> seg_ptr, key_seg_ptr, key_gi, key_gj, a, b;
+  DevBuf<double> partial;  // [n_seg*dc*dc]
+  int n_seg = 0, n_keys = 0;
+  int64_t n_pairs = 0;
+  bool built = false;
+};
+
 struct Problem {
   // ---- sizes ----
   int n_img = 0, n_cam = 0, n_pt = 0;  // global images / cameras, LOCAL points
@@ -103,13 +112,12 @@ struct Problem {
   DevBuf<int> d_pt_ptr;      // [n_pt+1] CSR over point-sorted observations
   DevBuf<int> d_blk_off, d_blk_dim, d_col_blk;  int n_blk = 0;
 
-  // reduced-camera-matrix block entries (dense S) and diagonal entries (SCHUR_JACOBI)
-  DevBuf<int> d_pair_key_ptr, d_pair_a, d_pair_b, d_pair_key_gi, d_pair_key_gj;  int n_pair_keys = 0; int64_t n_pairs = 0;
-  DevBuf<int> d_diag_key_ptr, d_diag_a, d_diag_b, d_diag_key_gi, d_diag_key_gj;   int n_diag_keys = 0; int64_t n_diag_pairs = 0;
+  // observation-pair lists for the off-diagonal Schur contributions (schur.cu)
+  PairList pairs_dense, pairs_diag;
   DevBuf<int> d_blk_moff;  int m_size = 0;      // offsets of the SCHUR_JACOBI blocks inside d_M / d_Minv
   DevBuf<double> d_M;                           // block diagonal of S before inversion
   DevBuf<double> d_chunk_block;                 // [n_chunks*dc*dc] per-chunk diagonal block partials
-  bool pairs_built = false, diag_built = false;
+  DevBuf<double> d_W, d_H;                      // [n_obs*dc*3] F^T E and F^T E C^{-1}
 
   // ---- device: parameters (current / candidate) ----
   DevBuf<double> d_pose, d_cam, d_X, d_pose2, d_cam2, d_X2;

@@ -12,7 +12,8 @@ solver = int(sys.argv[2]) if len(sys.argv) > 2 else -1
 iters = int(sys.argv[3]) if len(sys.argv) > 3 else 10
 prob, _ = m.scene.make_config(name)
 print(name, "obs", prob.num_observations)
-s = m.Solver(prob)
+t = time.time(); s = m.Solver(prob); print("create %.1f ms" % ((time.time() - t) * 1e3))
+t = time.time(); s2 = m.Solver(prob); print("create again %.1f ms" % ((time.time() - t) * 1e3)); s2.close()
 ev = s.evaluate()
 ref = oracle_evaluate(ora, m.capi, prob)
 for k in ("r", "pose", "intr", "point"):
