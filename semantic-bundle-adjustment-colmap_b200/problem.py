@@ -22,8 +22,9 @@ class FlatProblem:
         self.camera_model = capi.as_i32(camera_model)
         cp = capi.as_f64(camera_params)
         self.camera_params = np.zeros((len(self.camera_model), capi.MAX_CAMERA_PARAMS))
-        cp = cp.reshape(len(self.camera_model), -1)
-        self.camera_params[:, :cp.shape[1]] = cp
+        if len(self.camera_model):
+            cp = cp.reshape(len(self.camera_model), -1)
+            self.camera_params[:, :cp.shape[1]] = cp
         self.points = capi.as_f64(points).reshape(-1, 3)
         self.obs_image = capi.as_i32(obs_image)
         self.obs_point = capi.as_i32(obs_point)

@@ -113,6 +113,11 @@ def test_oracle_jacobians_match_central_differences(oracle, model, params):
     blocks = [(q, Jq), (t, Jt), (X, JX), (prm, Jk)]
     for vec, J in blocks:
         for j in range(J.shape[1]):
+            if model == 7 and vec is prm and j == 4 and abs(prm[4] ** 2 - 1e-4) < 1e-8:
+                # omega = 1e-2 sits exactly on the reference's branch border (omega^2 < 1e-4,
+                # camera_models.h:1147) where its order-3 Taylor branch is discontinuous with the
+                # closed form; a central difference would straddle the two branches
+                continue
             h = 1e-6 * max(1.0, abs(vec[j]))
             old = vec[j]
             vec[j] = old + h; rp = _eval(oracle, model, q, t, X, prm, xy)
