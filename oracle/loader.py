@@ -49,6 +49,8 @@ def load(capi):
     lib.oracle_draw_quadrilateral.argtypes = [dp, C.c_int, C.c_int, C.POINTER(C.c_uint8)]
     lib.oracle_cylinder_quadrilateral.argtypes = [dp, dp, dp, dp, dp, C.c_double, C.c_double, dp]
     lib.oracle_cylinder_quadrilateral.restype = C.c_int
+    lib.oracle_ba_sem_rows.argtypes = [PD, dp]
+    lib.oracle_ba_sem_rows.restype = C.c_int
     lib.oracle_bilinear.argtypes = [C.POINTER(C.c_float), C.c_int, C.c_int, C.c_double, C.c_double, ip]
     lib.oracle_bilinear.restype = C.c_double
     _lib = lib

@@ -170,6 +170,26 @@ int oracle_cylinder_quadrilateral(const double* cam_q, const double* cam_t, cons
   return CylinderQuadrilateral(cam_q, cam_t, cam_params, cyl_q, cyl_t, radius, height, pts8) ? 1 : 0;
 }
 
+// extension X1 (no reference implementation): per observation,
+// weight * bilinear(map_of_image, projection), 0 where the sample is rejected.
+int oracle_ba_sem_rows(const sba_problem_desc* d, double* out) {
+  if (!d->sem_maps) return 1;
+  const size_t HW = (size_t)d->sem_height * d->sem_width;
+  for (int64_t k = 0; k < d->num_observations; ++k) {
+    const int i = d->obs_image[k], c = d->image_camera[i], pt = d->obs_point[k];
+    double p[3];
+    UnitQuaternionRotatePoint(&d->image_qvec[4 * i], &d->points[3 * pt], p);
+    p[0] += d->image_tvec[3 * i]; p[1] += d->image_tvec[3 * i + 1]; p[2] += d->image_tvec[3 * i + 2];
+    p[0] /= p[2]; p[1] /= p[2];
+    double x, y;
+    Project<double>(d->camera_model[c], &d->camera_params[SBA_MAX_CAMERA_PARAMS * c], p[0], p[1], &x, &y);
+    int ok = 0;
+    const double v = BilinearSample(d->sem_maps + i * HW, d->sem_height, d->sem_width, x, y, &ok);
+    out[k] = ok ? d->sem_weight * v : 0.0;
+  }
+  return 0;
+}
+
 double oracle_bilinear(const float* map, int H, int W, double x, double y, int* ok) {
   return BilinearSample(map, H, W, x, y, ok);
 }

@@ -272,7 +272,7 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
 template <int MODEL>
 static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
   const size_t smem = (size_t)(kEvalThreads / 32) * 32 * (5 + p->dc + 1) * sizeof(double2);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(eval_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (smem > 40 * 1024) cudaFuncSetAttribute(eval_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   eval_kernel<MODEL><<<blocks, kEvalThreads, smem, p->stream>>>(
       p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_c.p : nullptr,
       use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, p->jq_out);

@@ -118,16 +118,12 @@ __global__ void __launch_bounds__(128) semantic_pair_kernel(SemView V, int64_t n
   for (int j = 0; j < 4; ++j) { x[j] = V.q[4 * i1 + j]; x[7 + j] = V.q[4 * i2 + j]; }
 #pragma unroll
   for (int j = 0; j < 3; ++j) { x[4 + j] = V.t[3 * i1 + j]; x[11 + j] = V.t[3 * i2 + j]; }
-  double delta = 0.0;
+  // step of MY column (lane j < 14 owns Jacobian column j), taken before any perturbation
+  const double my_delta = (JAC && lane < 14) ? NumDiffDelta(x[lane], V.rel) : 1.0;
   if (JAC && lane >= 1 && lane <= 28) {
     const int j = (lane - 1) >> 1;
-    double xj = 0.0;
-#pragma unroll
-    for (int a = 0; a < 14; ++a) if (a == j) xj = x[a];
-    delta = NumDiffDelta(xj, V.rel);
-    const double xn = ((lane - 1) & 1) ? xj - delta : xj + delta;
-#pragma unroll
-    for (int a = 0; a < 14; ++a) if (a == j) x[a] = xn;
+    const double delta = NumDiffDelta(x[j], V.rel);
+    x[j] = ((lane - 1) & 1) ? x[j] - delta : x[j] + delta;
   }
   int st = 0;
   double r = 0.0;
@@ -146,8 +142,7 @@ __global__ void __launch_bounds__(128) semantic_pair_kernel(SemView V, int64_t n
   const int src_p = (1 + 2 * lane) & 31, src_m = (2 + 2 * lane) & 31;
   const double fp = __shfl_sync(0xffffffffu, r, src_p);
   const double fm = __shfl_sync(0xffffffffu, r, src_m);
-  const double dl = __shfl_sync(0xffffffffu, delta, src_p);
-  if (lane < 14) jac[k * 14 + lane] = (fp - fm) * ((1.0 / dl) / 2.0);
+  if (lane < 14) jac[k * 14 + lane] = (fp - fm) * ((1.0 / my_delta) / 2.0);
 }
 
 }  // namespace sba
