@@ -317,6 +317,7 @@ __global__ void __launch_bounds__(256) chol_fetch_y_kernel(int n, const double* 
 int CholeskySolve(Problem* p) {
   const int n = p->n_cdim;
   if (n == 0) return SBA_OK;
+  if (n <= kCholSmallMax) return CholeskySolveSmall(p);
   static bool attr_set = false;
   const int dyn = 2 * NB * LDS * (int)sizeof(double);
   if (!attr_set) {

@@ -97,6 +97,14 @@ struct ChunkView {
   const int* cam_img_list;  // [n_img]
 };
 
+// host phase timer, printed when SBA_TIMING is set (diagnostics only)
+struct HostTimer {
+  const char* what; double t0; bool on;
+  static double Now();
+  explicit HostTimer(const char* w);
+  void Lap(const char* label);
+};
+
 inline int DivUp(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 }  // namespace sba

@@ -42,6 +42,7 @@ static int ResolveSolver(const Problem* p, const sba_solver_options& o) {
 int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb, void* user, sba_summary* sum) {
   const sba_solver_options& o = *op;
   const auto t_start = std::chrono::steady_clock::now();
+  HostTimer tmh("solve");
   *sum = p->counts;
   p->trace.clear();
   if (p->n_obs_global == 0) {
@@ -106,6 +107,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     return false;
   };
   bool stop = user_stop(it0);
+  tmh.Lap("iteration 0");
 
   while (!stop) {
     if (iteration >= o.max_num_iterations) { termination = SBA_NO_CONVERGENCE; break; }
@@ -202,6 +204,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     it.cost = x_cost + fixed_cost;
     it.trust_region_radius = radius;
     p->trace.push_back(it);
+    tmh.Lap("iteration");
     if (user_stop(it)) break;
   }
   {

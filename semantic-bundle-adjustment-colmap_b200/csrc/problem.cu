@@ -6,6 +6,9 @@
 // are variable, tangent sizes), point-sorted observation order, warp tiles,
 // image-major chunk lists, and the per-rank shard (points + their observations).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <numeric>
 
 #include "device_math.cuh"
@@ -17,7 +20,33 @@ static thread_local Err g_err = {0, ""};
 void SetError(int code, const std::string& msg) { g_err.code = code; g_err.msg = msg; }
 const char* LastErrorMessage() { return g_err.msg.c_str(); }
 
+double HostTimer::Now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+HostTimer::HostTimer(const char* w) : what(w), t0(Now()) { static const bool e = getenv("SBA_TIMING") != nullptr; on = e; }
+void HostTimer::Lap(const char* label) {
+  if (!on) return;
+  const double t = Now();
+  fprintf(stderr, "[sba timing] %s / %s: %.3f ms\n", what, label, (t - t0) * 1e3);
+  t0 = t;
+}
+
+cudaStream_t AllocStream() {
+  static cudaStream_t streams[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!streams[dev]) {
+    cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking);
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      uint64_t keep = ~0ull;  // never hand freed blocks back to the OS: the next handle reuses them
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
+  return streams[dev];
+}
+
 Problem::~Problem() {
+  if (stream) cudaStreamSynchronize(stream);  // buffers go back to the pool only once nothing uses them
   CommDestroy(this);
   if (h_scalars) cudaFreeHost(h_scalars);
   if (stream) cudaStreamDestroy(stream);
@@ -186,11 +215,14 @@ void ShardPointRange(const std::vector<int64_t>& pt_obs_prefix, int nranks, int 
 }
 
 int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
+  HostTimer tm("create");
   int rc = Validate(dp);
   if (rc) return rc;
+  tm.Lap("validate");
   const sba_problem_desc& d = *dp;
   GlobalStructure g;
   Analyse(d, &g);
+  tm.Lap("analyse");
   Problem* p = new Problem();
   p->counts = g.counts;
   p->n_img = d.num_images; p->n_cam = d.num_cameras;
@@ -250,6 +282,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   std::vector<int> h_pt_ptr(p->n_pt + 1);
   for (int q = 0; q <= p->n_pt; ++q) h_pt_ptr[q] = (int)(prefix[p0 + q] - prefix[p0]);
 
+  tm.Lap("shard + point sort");
   // ---- warp tiles: whole points packed into <= kTile observations ----
   std::vector<int> tile_start;
   {
@@ -294,6 +327,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   for (int b = 0; b < p->n_blk; ++b)
     for (int j = 0; j < p->h_blk_dim[b]; ++j) col_blk[p->h_blk_off[b] + j] = b;
 
+  tm.Lap("tiles + chunks");
   *out = p;
   if (host_only) return SBA_OK;
 
@@ -318,6 +352,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   for (size_t j = 0; j < cam.size(); ++j) cam[j] = d.camera_params[j];
   for (int q = 0; q < p->n_pt; ++q)
     for (int a = 0; a < 3; ++a) X[3 * (size_t)q + a] = d.points[3 * (size_t)(p0 + q) + a];
+  tm.Lap("stream + pinned + pack");
   UP(p->d_pose.Upload(pose, st)); UP(p->d_cam.Upload(cam, st)); UP(p->d_X.Upload(X, st));
   UP(p->d_pose2.Upload(pose, st)); UP(p->d_cam2.Upload(cam, st)); UP(p->d_X2.Upload(X, st));
   UP(p->d_pose0.Upload(pose, st)); UP(p->d_cam0.Upload(cam, st)); UP(p->d_X0.Upload(X, st));
@@ -335,6 +370,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_pt_ptr.Upload(h_pt_ptr, st));
   UP(p->d_blk_off.Upload(p->h_blk_off, st)); UP(p->d_blk_dim.Upload(p->h_blk_dim, st));
   UP(p->d_col_blk.Upload(col_blk, st));
+  tm.Lap("uploads");
   const size_t nc = std::max(1, p->n_cdim), np3 = std::max(1, 3 * p->n_pvar);
   UP(p->d_ER.Alloc((size_t)std::max(1, n_obs) * 8)); UP(p->d_F.Alloc((size_t)std::max(1, n_obs) * p->dc));
   p->n_partial = std::max(std::max(DivUp(std::max(1, n_obs), 128), DivUp(std::max(1, p->n_tiles), 4)),
@@ -353,6 +389,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_grad_c.Alloc(nc)); UP(p->d_grad_p.Alloc(np3)); UP(p->d_tmp_c.Alloc(nc));
   UP(p->d_cg_r.Alloc(nc)); UP(p->d_cg_z.Alloc(nc)); UP(p->d_cg_p.Alloc(nc)); UP(p->d_cg_q.Alloc(nc)); UP(p->d_cg_x.Alloc(nc));
   UP(p->d_scalars.Alloc(1)); UP(p->d_scalars.Zero(st));
+  tm.Lap("allocs");
   if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0) {
     const size_t n_map = (size_t)p->n_img * d.sem_height * d.sem_width;
     UP(p->d_sem_maps.Alloc(n_map));
@@ -360,6 +397,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
     p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
   }
   UP(cudaStreamSynchronize(st));
+  tm.Lap("maps + sync");
 #undef UP
   return SBA_OK;
 }

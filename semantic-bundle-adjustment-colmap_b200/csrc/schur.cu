@@ -33,7 +33,7 @@ namespace sba {
     case 14: CALL(14); break; default: CALL(18); break;                               \
   }
 
-constexpr int kSegPairs = 64;
+constexpr int kSegPairs = 32;  // one warp-load of pair ids per segment (schur_pair_segment_kernel)
 template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; };
 
 // W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (observation, slot)
@@ -162,8 +162,14 @@ __global__ void __launch_bounds__(128) schur_pair_segment_kernel(int n_seg, cons
     ja[q] = e / DC; jb[q] = e - ja[q] * DC;
   }
   const int t0 = seg_ptr[seg], t1 = seg_ptr[seg + 1];
-  for (int t = t0; t < t1; ++t) {
-    const size_t a = (size_t)pa[t] * DC, b = (size_t)pb[t] * DC;
+  // a segment holds <= kSegPairs (= 32) pairs: one coalesced index load per lane, then the pair ids are
+  // broadcast by shuffle, so the operand loads of several pairs are in flight together instead of
+  // each waiting for its own index load.
+  const int np = t1 - t0;
+  const int my_a = lane < np ? pa[t0 + lane] : 0, my_b = lane < np ? pb[t0 + lane] : 0;
+#pragma unroll 4
+  for (int t = 0; t < np; ++t) {
+    const size_t a = (size_t)__shfl_sync(0xffffffffu, my_a, t) * DC, b = (size_t)__shfl_sync(0xffffffffu, my_b, t) * DC;
 #pragma unroll
     for (int q = 0; q < Elems<DC>::N; ++q) {
       const double* h = H + 3 * (a + ja[q]);
@@ -261,6 +267,7 @@ __global__ void __launch_bounds__(64) invert_blocks_kernel(int n_blk, const int*
 int BuildPairLists(Problem* p, bool dense) {
   PairList& L = dense ? p->pairs_dense : p->pairs_diag;
   if (L.built) return SBA_OK;
+  HostTimer tm("pair lists");
   const int n_pt = p->n_pt, n_img = p->n_img;
   const std::vector<int>& img = p->h_obs_img;
   std::vector<int> pt_ptr(n_pt + 1, 0);
@@ -305,6 +312,7 @@ int BuildPairLists(Problem* p, bool dense) {
         }
     }
   }
+  tm.Lap("enumerate");
   // counting sort by key when the key space is small enough, else comparison sort
   const int64_t key_space = (int64_t)n_img * n_img;
   std::vector<int> pa(ents.size()), pb(ents.size()), key_ptr, key_gi, key_gj;
@@ -327,6 +335,7 @@ int BuildPairLists(Problem* p, bool dense) {
     }
   }
   key_ptr.push_back((int)ents.size());
+  tm.Lap("sort");
   // segments
   std::vector<int> seg_ptr, key_seg_ptr;
   for (size_t k = 0; k + 1 < key_ptr.size(); ++k) {
@@ -345,6 +354,7 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(L.partial.Alloc((size_t)std::max(1, L.n_seg) * p->dc * p->dc));
   SBA_CUDA(cudaStreamSynchronize(st));
   L.built = true;
+  tm.Lap("segments + upload");
   return SBA_OK;
 }
 
@@ -400,7 +410,8 @@ int BuildDenseSchur(Problem* p) {
   if (rc) return rc;
   rc = AllReduceSum(p, p->d_S.p, n * n);
   if (rc) return rc;
-  if (n > 0) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, p->d_S.p, p->d_Dc.p); p->launches++; }
+  p->chol_add_diag = (int)n <= kCholSmallMax;  // the small-system Cholesky adds D^2 while loading its diagonal tiles
+  if (n > 0 && !p->chol_add_diag) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, p->d_S.p, p->d_Dc.p); p->launches++; }
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }

@@ -12,6 +12,12 @@
 
 namespace sba {
 
+// Device memory comes from CUDA's stream-ordered pool (cudaMallocAsync) on one long-lived allocation stream
+// per device, with the pool's release threshold lifted: the ~70 buffers of a problem cost microseconds to
+// create and destroy after the first handle, instead of a cudaMalloc / synchronising cudaFree each.
+// Contract: a buffer is freed only after the stream that used it has been synchronised (sba_destroy does).
+cudaStream_t AllocStream();  // problem.cu
+
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
@@ -21,14 +27,17 @@ struct DevBuf {
   DevBuf& operator=(const DevBuf&) = delete;
   ~DevBuf() { Free(); }
   void Free() {
-    if (p) cudaFree(p);
+    if (p) cudaFreeAsync(p, AllocStream());
     p = nullptr; n = 0;
   }
   cudaError_t Alloc(size_t count) {
     if (count <= n && p) return cudaSuccess;
+    if (p) cudaDeviceSynchronize();  // growing a live buffer: nothing in flight may still read the old one
     Free();
     n = count;
-    return cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
+    cudaError_t e = cudaMallocAsync((void**)&p, (count ? count : 1) * sizeof(T), AllocStream());
+    // the allocation stream carries no kernels, so this returns at once; it makes the block usable from any stream
+    return e == cudaSuccess ? cudaStreamSynchronize(AllocStream()) : e;
   }
   cudaError_t Upload(const std::vector<T>& h, cudaStream_t s) {
     cudaError_t e = Alloc(h.size());
@@ -136,6 +145,7 @@ struct Problem {
   DevBuf<double> d_rhs, d_yc, d_yp, d_step_c, d_grad_c, d_grad_p, d_tmp_c;
   DevBuf<double> d_S;                       // dense reduced camera matrix [n_cdim^2]
   DevBuf<double> d_Linv;                    // inverted diagonal blocks of the Cholesky factor
+  DevBuf<int> chol_flags;  int chol_epoch = 0;  bool chol_add_diag = false;  // chol_small.cu tile epochs
   DevBuf<double> d_Minv;                    // SCHUR_JACOBI inverse blocks
   DevBuf<double> d_cg_r, d_cg_z, d_cg_p, d_cg_q, d_cg_x;
   DevBuf<double> d_xi, d_xc;                // padded camera-space vector (n_img*6 | n_cam*12)
@@ -196,6 +206,9 @@ int BuildDenseSchur(Problem* p);
 int BuildSchurJacobi(Problem* p);
 // cholesky.cu
 int CholeskySolve(Problem* p);  // d_S, d_rhs -> d_yc ; sets scalars.chol_fail
+// chol_small.cu
+constexpr int kCholSmallMax = 1024;
+int CholeskySolveSmall(Problem* p);  // n_cdim <= kCholSmallMax: one dataflow kernel
 // pcg.cu
 int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
 // lm.cu
