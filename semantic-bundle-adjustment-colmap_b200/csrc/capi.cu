@@ -101,10 +101,11 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
   rc = LaunchEvaluate(p, loss, false, false);
   p->jq_out = nullptr;
   if (rc) return rc;
-  std::vector<double> ER((size_t)n * 8), F((size_t)n * dc * 2), JQ;
+  std::vector<D4> ER(TilePad(n) * 2), F(TilePad(n) * (dc / 2));  // tile-blocked, common.cuh
+  std::vector<double> JQ;
   if (n > 0) {
-    SBA_CUDA(cudaMemcpyAsync(ER.data(), p->d_ER.p, ER.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
-    SBA_CUDA(cudaMemcpyAsync(F.data(), p->d_F.p, F.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaMemcpyAsync(ER.data(), p->d_ER.p, ER.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaMemcpyAsync(F.data(), p->d_F.p, F.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
     if (jac_qvec_ambient) {
       JQ.resize((size_t)n * 8);
       SBA_CUDA(cudaMemcpyAsync(JQ.data(), d_jq.p, JQ.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -113,24 +114,29 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
   SBA_CUDA(cudaMemcpyAsync(p->h_scalars, p->d_scalars.p, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, st));
   SBA_CUDA(cudaStreamSynchronize(st));
   if (cost) *cost = p->h_scalars->cost + p->h_scalars->fixed_cost;
+  auto slot = [&](int k, int j, double* d0, double* d1) {  // (d r0 / d s_j, d r1 / d s_j)
+    const D4& u = F[FUnit(k, j >> 1, dc / 2)];
+    if (j & 1) { *d0 = u.z; *d1 = u.w; } else { *d0 = u.x; *d1 = u.y; }
+  };
   for (int k = 0; k < n; ++k) {
     const int64_t r = p->h_local2ref[k];
     const int i = p->h_obs_img[k], c = p->h_img_cam[i];
-    const double* er = &ER[(size_t)k * 8];
-    const double* f = &F[(size_t)k * dc * 2];  // double2[dc]: (d r0, d r1) per slot
-    if (residuals) { residuals[2 * r] = er[6]; residuals[2 * r + 1] = er[7]; }
+    const D4& ea = ER[EUnit(k, 0)];
+    const D4& eb = ER[EUnit(k, 1)];
+    if (residuals) { residuals[2 * r] = eb.z; residuals[2 * r + 1] = eb.w; }
     if (jac_point) {
-      for (int j = 0; j < 6; ++j) jac_point[6 * r + j] = er[j];
+      const double e[6] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y};
+      for (int j = 0; j < 6; ++j) jac_point[6 * r + j] = e[j];
     }
     if (jac_pose) {
-      for (int j = 0; j < 6; ++j) { jac_pose[12 * r + j] = f[2 * j]; jac_pose[12 * r + 6 + j] = f[2 * j + 1]; }
+      for (int j = 0; j < 6; ++j) slot(k, j, &jac_pose[12 * r + j], &jac_pose[12 * r + 6 + j]);
     }
     if (jac_intr) {
       double* out = &jac_intr[(size_t)r * 2 * SBA_MAX_CAMERA_PARAMS];
       for (int j = 0; j < 2 * SBA_MAX_CAMERA_PARAMS; ++j) out[j] = 0.0;
-      for (int s = 0; s < p->h_k_dim[c] && 6 + s < dc; ++s) {
-        const int a = p->h_k_cols[12 * (size_t)c + s];
-        out[a] = f[2 * (6 + s)]; out[SBA_MAX_CAMERA_PARAMS + a] = f[2 * (6 + s) + 1];
+      for (int s2 = 0; s2 < p->h_k_dim[c] && 6 + s2 < dc; ++s2) {
+        const int a = p->h_k_cols[12 * (size_t)c + s2];
+        slot(k, 6 + s2, &out[a], &out[SBA_MAX_CAMERA_PARAMS + a]);
       }
     }
     if (jac_qvec_ambient) for (int j = 0; j < 8; ++j) jac_qvec_ambient[8 * r + j] = JQ[(size_t)k * 8 + j];

@@ -12,14 +12,22 @@
 //   points  : X            double[3]  packed
 //   observations are kept in POINT-SORTED order (stable by reference order);
 //   ref2pt / pt2ref permutations recover the reference residual order.
-//   per observation k:
-//     ER[k]  = double[8]  : E (2x3 d r/d X, row-major) + r(2)        (64 B record)
-//     F[k]   = double2[DC]: slot j -> (d r0/d s_j, d r1/d s_j)       (16*DC B record)
-//              slots 0..2 quaternion tangent, 3..5 tvec, 6.. free intrinsics
+//   per observation k the linearisation is two records
+//     ER = double[8]  : E (2x3 d r/d X, row-major) + r(2)
+//     F  = double2[DC]: slot j -> (d r0/d s_j, d r1/d s_j); slots 0..2 quaternion tangent, 3..5 tvec,
+//                       6.. free intrinsics
+//   stored TILE-BLOCKED in 32-byte units (D4): observations are grouped in tiles of 32; inside a tile,
+//   unit u of all 32 observations is contiguous (1 KB):
+//     F  unit jj (slots 2jj, 2jj+1) of observation k : F [((k >> 5) * DC/2 + jj) * 32 + (k & 31)]
+//     ER unit u  (0: E0..E3, 1: E4 E5 r0 r1)         : ER[((k >> 5) * 2    + u ) * 32 + (k & 31)]
+//   A warp that walks consecutive observations (the point-sorted passes) moves whole 1 KB rows with one
+//   256-bit access per lane; a pass that gathers observations in image order touches DC/2 full 32 B sectors
+//   per observation -- no sector is ever fetched half used.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -29,6 +37,28 @@ namespace sba {
 
 constexpr int kMaxDC = 18;  // 6 pose slots + 12 intrinsics slots
 constexpr int kTile = 32;   // observations per warp tile
+
+// 32-byte unit of the tile-blocked Jacobian storage; moved with one 256-bit LDG / STG (sm_100)
+struct __align__(32) D4 { double x, y, z, w; };
+#ifdef __CUDACC__
+__device__ __forceinline__ D4 Ld256(const D4* p) {
+  D4 v;
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void St256(D4* p, const D4& v) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
+}
+#endif
+__host__ __device__ inline size_t FUnit(int k, int jj, int dch) { return ((size_t)(k >> 5) * dch + jj) * 32 + (k & 31); }
+__host__ __device__ inline size_t EUnit(int k, int u) { return ((size_t)(k >> 5) * 2 + u) * 32 + (k & 31); }
+inline size_t TilePad(size_t n_obs) { return (n_obs + 31) / 32 * 32; }
+#ifdef __CUDACC__
+// (d r0 / d s, d r1 / d s) of one slot of one observation: half a unit
+__device__ __forceinline__ double2 LoadSlot(const D4* __restrict__ F, int k, int slot, int dch) {
+  return reinterpret_cast<const double2*>(F + FUnit(k, slot >> 1, dch))[slot & 1];
+}
+#endif
 
 struct Err {
   int code;
@@ -96,6 +126,10 @@ struct ChunkView {
   const int* cam_img_ptr;   // [n_cam+1] CSR: images of each camera
   const int* cam_img_list;  // [n_img]
 };
+
+// Host worker threads for the integer set-up work (sorting, pair lists, staging copies).
+int HostThreads();
+void ParallelFor(int n_tasks, const std::function<void(int)>& fn);  // fn(task), tasks spread over HostThreads()
 
 // host phase timer, printed when SBA_TIMING is set (diagnostics only)
 struct HostTimer {

@@ -15,7 +15,7 @@
 
 namespace sba {
 
-__host__ __device__ inline int ModelNumParams(int m) {
+__host__ __device__ constexpr inline int ModelNumParams(int m) {
   switch (m) {
     case SBA_SIMPLE_PINHOLE: return 3;
     case SBA_PINHOLE: return 4;

@@ -10,8 +10,8 @@
 // (bundle_adjustment.cc:53-68) and Jacobi column scaling.
 //
 // HBM traffic per observation (algorithmic): 8 B indices + 16 B xy in,
-// 64 B ER record + 16*DC B F record out; poses / intrinsics / points are gathered
-// through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
+// 64 B ER record + 16*DC B F record out (tile-blocked 32 B units, common.cuh); poses / intrinsics /
+// points are gathered through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
 #include "device_math.cuh"
 #include "reduce.cuh"
 #include "solver.h"
@@ -56,39 +56,48 @@ __device__ inline void RotateWithJac(const double q[4], const double t[3], const
   }
 }
 
+// value of Jk[amb] (row 0) / Jk[12 + amb] (row 1) without a dynamic register index
+template <int NP>
+__device__ __forceinline__ void PickParam(const double (&Jk)[24], int amb, double* j0, double* j1) {
+  double a = 0.0, b = 0.0;
+#pragma unroll
+  for (int t = 0; t < NP; ++t) { a = (t == amb) ? Jk[t] : a; b = (t == amb) ? Jk[12 + t] : b; }
+  *j0 = a; *j1 = b;
+}
+
+// scale_i [n_img*6] / scale_k [n_cam*12, by intrinsics slot]: Jacobi scale of the slot, 0 where the slot is
+// constant or unused (the plain evaluation passes 1 / 0 masks).  Folding "is this slot free" into the scale
+// replaces the per-slot column-index lookups: an observation gathers its pose (two 32 B loads), its pose
+// scales (three 16 B loads), its camera record and one packed slot map -- a third of the scattered loads the
+// index-table version needed, which is what bounded it (L1 wavefronts, profiles/r01_ncu_full_c4_eval_v1.txt).
+// The records leave as 32 B units of the tile-blocked layout: every store instruction of a warp writes 1 KB
+// contiguous, straight from registers.
 template <int MODEL>
 __global__ void __launch_bounds__(kEvalThreads)
-eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_c,
-            const double* __restrict__ scale_p, double* __restrict__ ER, double2* __restrict__ F,
-            double* __restrict__ cost_partial, double* __restrict__ Jq_ambient) {
+eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_i,
+            const double* __restrict__ scale_k, const unsigned long long* __restrict__ k_pack,
+            const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F,
+            double* __restrict__ cost_partial, double* __restrict__ Jq_ambient, unsigned* ticket,
+            DeviceScalars* sc) {
+  constexpr int NP = MODEL >= 0 ? ModelNumParams(MODEL >= 0 ? MODEL : 0) : 12;
   const int k = blockIdx.x * kEvalThreads + threadIdx.x;
-  // Output staging: every thread produces one 64 B ER record and one 16*dc B F record.  Written
-  // straight to HBM that is a 32-way strided store per instruction; instead each warp assembles its
-  // 32 records in shared memory (row strides of 5 and dc+1 16-byte units: odd, so conflict-free) and
-  // streams them out as one contiguous, fully coalesced block.
-  extern __shared__ double2 stage[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int dcs = S.dc + 1;
-  double2* sER = stage + (size_t)warp * 32 * (5 + dcs);
-  double2* sF = sER + 32 * 5;
   double cost = 0.0, fixed = 0.0;
   if (k < S.n_obs) {
     const int i = S.obs_img[k], pt = S.obs_pt[k];
     const int c = S.img_cam[i];
     const int model = MODEL >= 0 ? MODEL : S.model[c];
-    const double2* pp = reinterpret_cast<const double2*>(P.pose + 8 * (size_t)i);
-    const double2 a0 = __ldg(pp), a1 = __ldg(pp + 1), a2 = __ldg(pp + 2), a3 = __ldg(pp + 3);
-    const double q[4] = {a0.x, a0.y, a1.x, a1.y};
-    const double t[3] = {a2.x, a2.y, a3.x};
+    const D4* pp = reinterpret_cast<const D4*>(P.pose + 8 * (size_t)i);
+    const D4 a0 = Ld256(pp), a1 = Ld256(pp + 1);
+    const double q[4] = {a0.x, a0.y, a0.z, a0.w};
+    const double t[3] = {a1.x, a1.y, a1.z};
     const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
     double prm[12];
     {
-      const double2* cp = reinterpret_cast<const double2*>(P.cam + 12 * (size_t)c);
-      const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+      const D4* cp = reinterpret_cast<const D4*>(P.cam + 12 * (size_t)c);
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        if (2 * j < np) { const double2 v = __ldg(cp + j); prm[2 * j] = v.x; prm[2 * j + 1] = v.y; }
-        else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
+      for (int j = 0; j < 3; ++j) {
+        if (4 * j < NP) { const D4 v = Ld256(cp + j); prm[4 * j] = v.x; prm[4 * j + 1] = v.y; prm[4 * j + 2] = v.z; prm[4 * j + 3] = v.w; }
+        else { prm[4 * j] = 0.0; prm[4 * j + 1] = 0.0; prm[4 * j + 2] = 0.0; prm[4 * j + 3] = 0.0; }
       }
     }
     const double2 xy = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k);
@@ -118,16 +127,16 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
     double rho[3];
     LossEval(L.type, L.scale, s, rho);
     const bool active = S.obs_active[k] != 0;
-    double2* Fk = sF + lane * dcs;
-    double* ERk = reinterpret_cast<double*>(sER + lane * 5);
+    const int dch = S.dc >> 1;
+    D4* Fk = F + FUnit(k, 0, dch);
+    D4* Ek = ER + EUnit(k, 0);
+    const D4 zero = {0.0, 0.0, 0.0, 0.0};
     if (!active) {
       fixed = 0.5 * rho[0];
-      for (int j = 0; j < S.dc; ++j) Fk[j] = make_double2(0.0, 0.0);
-      // raw residual is still exported for the parity surface; E = 0 keeps it out of every product
-      reinterpret_cast<double2*>(ERk)[0] = make_double2(0.0, 0.0);
-      reinterpret_cast<double2*>(ERk)[1] = make_double2(0.0, 0.0);
-      reinterpret_cast<double2*>(ERk)[2] = make_double2(0.0, 0.0);
-      reinterpret_cast<double2*>(ERk)[3] = make_double2(r0, r1);
+      for (int jj = 0; jj < dch; ++jj) St256(Fk + 32 * jj, zero);
+      // the raw residual is still exported for the parity surface; E = 0 keeps it out of every product
+      St256(Ek, zero);
+      St256(Ek + 32, D4{0.0, 0.0, r0, r1});
     } else {
       cost = 0.5 * rho[0];
       // corrector (ceres corrector.cc)
@@ -143,47 +152,51 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
           alpha_sq_norm = alpha / s;
         }
       }
-      auto correct = [&](double& j0, double& j1) {
-        if (alpha_sq_norm == 0.0) { j0 *= sqrt_rho1; j1 *= sqrt_rho1; return; }
-        const double rtj = r0 * j0 + r1 * j1;
-        j0 = sqrt_rho1 * (j0 - alpha_sq_norm * r0 * rtj);
-        j1 = sqrt_rho1 * (j1 - alpha_sq_norm * r1 * rtj);
+      auto correct = [&](double& j0, double& j1, double scale) {
+        if (alpha_sq_norm != 0.0) {
+          const double rtj = r0 * j0 + r1 * j1;
+          j0 -= alpha_sq_norm * r0 * rtj;
+          j1 -= alpha_sq_norm * r1 * rtj;
+        }
+        j0 = sqrt_rho1 * j0 * scale; j1 = sqrt_rho1 * j1 * scale;
       };
-      const int* ci = S.col_img + 6 * (size_t)i;
-      // pose slots
+      // pose slots: 0..2 quaternion tangent, 3..5 tvec
+      {
+        const double2* sp2 = reinterpret_cast<const double2*>(scale_i + 6 * (size_t)i);
+        const double2 s01 = __ldg(sp2), s23 = __ldg(sp2 + 1), s45 = __ldg(sp2 + 2);
+        const double si[6] = {s01.x, s01.y, s23.x, s23.y, s45.x, s45.y};
+        double f0[6], f1[6];
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {  // quaternion tangent
-        double j0 = AB[0] * g.G[j] + AB[1] * g.G[3 + j] + AB[2] * g.G[6 + j];
-        double j1 = AB[3] * g.G[j] + AB[4] * g.G[3 + j] + AB[5] * g.G[6 + j];
-        const int col = ci[j];
-        if (col < 0) { j0 = 0.0; j1 = 0.0; }
-        else { correct(j0, j1); if (scale_c) { const double sc = scale_c[col]; j0 *= sc; j1 *= sc; } }
-        Fk[j] = make_double2(j0, j1);
-      }
+        for (int j = 0; j < 3; ++j) {
+          f0[j] = AB[0] * g.G[j] + AB[1] * g.G[3 + j] + AB[2] * g.G[6 + j];
+          f1[j] = AB[3] * g.G[j] + AB[4] * g.G[3 + j] + AB[5] * g.G[6 + j];
+          f0[3 + j] = AB[j]; f1[3 + j] = AB[3 + j];
+        }
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {  // tvec
-        double j0 = AB[j], j1 = AB[3 + j];
-        const int col = ci[3 + j];
-        if (col < 0) { j0 = 0.0; j1 = 0.0; }
-        else { correct(j0, j1); if (scale_c) { const double sc = scale_c[col]; j0 *= sc; j1 *= sc; } }
-        Fk[3 + j] = make_double2(j0, j1);
+        for (int j = 0; j < 6; ++j) {
+          if (si[j] == 0.0) { f0[j] = 0.0; f1[j] = 0.0; }  // constant slot: exactly zero, whatever the value
+          else correct(f0[j], f1[j], si[j]);
+        }
+#pragma unroll
+        for (int jj = 0; jj < 3; ++jj) St256(Fk + 32 * jj, D4{f0[2 * jj], f1[2 * jj], f0[2 * jj + 1], f1[2 * jj + 1]});
       }
       // intrinsics slots
-      if (S.dc > 6) {
-        for (int j = 6; j < S.dc; ++j) Fk[j] = make_double2(0.0, 0.0);
-        const int* ks = S.k_slot + 12 * (size_t)c;
-        const int* cc = S.col_cam + 12 * (size_t)c;
-        const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+      if (dch > 3) {
+        const unsigned long long pack = k_pack[c];
+        const double* sk = scale_k + 12 * (size_t)c;
 #pragma unroll
-        for (int a = 0; a < 12; ++a) {
-          if (a < np) {
-            const int slot = ks[a];
-            if (slot >= 0) {
-              double j0 = Jk[a], j1 = Jk[12 + a];
-              correct(j0, j1);
-              if (scale_c) { const double sc = scale_c[cc[slot]]; j0 *= sc; j1 *= sc; }
-              Fk[6 + slot] = make_double2(j0, j1);
+        for (int jj = 3; jj < 3 + (NP + 1) / 2; ++jj) {
+          if (jj < dch) {
+            double f0[2], f1[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int slot = 2 * jj - 6 + h;
+              const double scl = sk[slot];
+              PickParam<NP>(Jk, (int)((pack >> (4 * slot)) & 15ull), &f0[h], &f1[h]);
+              if (scl == 0.0) { f0[h] = 0.0; f1[h] = 0.0; }
+              else correct(f0[h], f1[h], scl);
             }
+            St256(Fk + 32 * jj, D4{f0[0], f1[0], f0[1], f1[1]});
           }
         }
       }
@@ -195,8 +208,7 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
         for (int j = 0; j < 3; ++j) {
           double j0 = AB[0] * g.R[j] + AB[1] * g.R[3 + j] + AB[2] * g.R[6 + j];
           double j1 = AB[3] * g.R[j] + AB[4] * g.R[3 + j] + AB[5] * g.R[6 + j];
-          correct(j0, j1);
-          if (scale_p) { const double sp = scale_p[3 * (size_t)po + j]; j0 *= sp; j1 *= sp; }
+          correct(j0, j1, scale_p ? scale_p[3 * (size_t)po + j] : 1.0);
           E[j] = j0; E[3 + j] = j1;
         }
       } else {
@@ -204,34 +216,20 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
         for (int j = 0; j < 6; ++j) E[j] = 0.0;
       }
       r0 *= residual_scaling; r1 *= residual_scaling;
-      reinterpret_cast<double2*>(ERk)[0] = make_double2(E[0], E[1]);
-      reinterpret_cast<double2*>(ERk)[1] = make_double2(E[2], E[3]);
-      reinterpret_cast<double2*>(ERk)[2] = make_double2(E[4], E[5]);
-      reinterpret_cast<double2*>(ERk)[3] = make_double2(r0, r1);
+      St256(Ek, D4{E[0], E[1], E[2], E[3]});
+      St256(Ek + 32, D4{E[4], E[5], r0, r1});
     }
   }
-  __syncwarp();
-  {
-    const int k0 = blockIdx.x * kEvalThreads + warp * 32;  // first observation of this warp
-    const int n_valid = min(32, S.n_obs - k0);
-    if (n_valid > 0) {
-      double2* gER = reinterpret_cast<double2*>(ER) + (size_t)k0 * 4;
-      for (int idx = lane; idx < n_valid * 4; idx += 32) gER[idx] = sER[(idx >> 2) * 5 + (idx & 3)];
-      double2* gF = F + (size_t)k0 * S.dc;
-      const int dc = S.dc;
-      for (int idx = lane; idx < n_valid * dc; idx += 32) {
-        const int row = idx / dc;
-        gF[idx] = sF[row * dcs + (idx - row * dc)];
-      }
-    }
-  }
-  BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
+  double v[2] = {cost, fixed};
+  double* const out[2] = {&sc->cost, &sc->fixed_cost};
+  GridSum<kEvalThreads, 2>(v, cost_partial, ticket, out);
 }
 
 // residual-only evaluation of the candidate point (Evaluator::Evaluate with no jacobian)
 template <int MODEL>
 __global__ void __launch_bounds__(kEvalThreads)
-cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_partial) {
+cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_partial, unsigned* ticket,
+            double* out_cost) {
   const int k = blockIdx.x * kEvalThreads + threadIdx.x;
   double cost = 0.0, fixed = 0.0;
   if (k < S.n_obs) {
@@ -265,22 +263,23 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
     LossEval(L.type, L.scale, r0 * r0 + r1 * r1, rho);
     if (S.obs_active[k]) cost = 0.5 * rho[0]; else fixed = 0.5 * rho[0];
   }
-  BlockSum2<kEvalThreads>(cost, fixed, cost_partial);
+  double v[2] = {cost, fixed};
+  double* const out[2] = {out_cost, nullptr};
+  GridSum<kEvalThreads, 2>(v, cost_partial, ticket, out);
 }
 
 
 template <int MODEL>
 static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
-  const size_t smem = (size_t)(kEvalThreads / 32) * 32 * (5 + p->dc + 1) * sizeof(double2);
-  if (smem > 40 * 1024) cudaFuncSetAttribute(eval_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  eval_kernel<MODEL><<<blocks, kEvalThreads, smem, p->stream>>>(
-      p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_c.p : nullptr,
-      use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p, p->d_F.p, p->d_cost_partial.p, p->jq_out);
+  eval_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(
+      p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_i.p : p->d_mask_i.p,
+      use_scale ? p->d_scale_k.p : p->d_mask_k.p, p->d_k_pack.p, use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p,
+      p->d_F.p, p->d_cost_partial.p, p->jq_out, p->d_tickets.p + 0, p->d_scalars.p);
 }
 template <int MODEL>
-static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks) {
+static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks, double* d_out_cost) {
   cost_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss,
-                                                             p->d_cost_partial.p);
+                                                             p->d_cost_partial.p, p->d_tickets.p + 1, d_out_cost);
 }
 
 #define SBA_MODEL_SWITCH(m, CALL)                                            \
@@ -298,10 +297,9 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
     SBA_MODEL_SWITCH(p->uniform_model, CALL)
 #undef CALL
     p->launches++;
+  } else {  // empty shard: the sums are zero
+    SBA_CUDA(cudaMemsetAsync(&p->d_scalars.p->cost, 0, 2 * sizeof(double), p->stream));
   }
-  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, blocks, &p->d_scalars.p->cost,
-                                                  &p->d_scalars.p->fixed_cost, 1.0);
-  p->launches++;
   SBA_CUDA(cudaGetLastError());
   p->linearized = true;
   return AllReduceSum(p, &p->d_scalars.p->cost, 2);  // cost, fixed_cost are adjacent
@@ -310,13 +308,13 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
 int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost) {
   const int blocks = DivUp(p->n_obs, kEvalThreads);
   if (blocks > 0) {
-#define CALL(M) LaunchCostT<M>(p, loss, candidate, blocks)
+#define CALL(M) LaunchCostT<M>(p, loss, candidate, blocks, d_out_cost)
     SBA_MODEL_SWITCH(p->uniform_model, CALL)
 #undef CALL
     p->launches++;
+  } else {
+    SBA_CUDA(cudaMemsetAsync(d_out_cost, 0, sizeof(double), p->stream));
   }
-  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, blocks, d_out_cost, nullptr, 1.0);
-  p->launches++;
   SBA_CUDA(cudaGetLastError());
   return AllReduceSum(p, d_out_cost, 1);
 }

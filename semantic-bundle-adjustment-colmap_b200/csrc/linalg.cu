@@ -79,13 +79,11 @@ int Gradient(Problem* p) {
   int rc = CamReduce(p, 1, nullptr, p->d_grad_c.p, nullptr, nullptr);
   if (rc) return rc;
   double* out = &p->d_scalars.p->gradient_max_norm;
-  int nb = std::min(1024, std::max(1, DivUp(p->n_cdim, 256)));
-  absmax_kernel<<<nb, 256, 0, p->stream>>>(p->n_cdim, p->d_grad_c.p, p->d_scale_c.p, p->d_red.p);
-  absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 0);
-  nb = std::min(1024, std::max(1, DivUp(3 * p->n_pvar, 256)));
-  absmax_kernel<<<nb, 256, 0, p->stream>>>(3 * p->n_pvar, p->d_gp.p, p->d_scale_p.p, p->d_red.p);
-  absmax_final_kernel<<<1, 1, 0, p->stream>>>(nb, p->d_red.p, out, 1);
-  p->launches += 4;
+  SBA_CUDA(cudaMemsetAsync(out, 0, sizeof(double), p->stream));
+  const int nb = std::min(1184, std::max(1, DivUp((int64_t)p->n_cdim + 3 * (int64_t)p->n_pvar, 256)));
+  grad_maxnorm_kernel<<<nb, 256, 0, p->stream>>>(p->n_cdim, p->d_grad_c.p, p->d_scale_c.p, 3 * p->n_pvar, p->d_gp.p,
+                                                 p->d_scale_p.p, out);
+  p->launches += 1;
   SBA_CUDA(cudaGetLastError());
   return AllReduceMax(p, out, 1);
 }
@@ -112,14 +110,10 @@ int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
     int rc = ColumnNorms(p, p->d_sq_c.p, p->d_sq_p.p);
     if (rc) return rc;
   }
-  if (p->n_cdim > 0) {
-    lm_diag_kernel<<<DivUp(p->n_cdim, 256), 256, 0, p->stream>>>(p->n_cdim, p->d_sq_c.p, p->d_diag_c.p, p->d_Dc.p, refresh,
-                                                              o.min_lm_diagonal, o.max_lm_diagonal, p->d_scalars.p);
-    p->launches++;
-  }
-  if (p->n_pvar > 0) {
-    lm_diag_kernel<<<DivUp(3 * p->n_pvar, 256), 256, 0, p->stream>>>(3 * p->n_pvar, p->d_sq_p.p, p->d_diag_p.p, p->d_Dp.p, refresh,
-                                                                  o.min_lm_diagonal, o.max_lm_diagonal, p->d_scalars.p);
+  if (p->n_cdim + p->n_pvar > 0) {
+    lm_diag_kernel<<<DivUp((int64_t)p->n_cdim + 3 * (int64_t)p->n_pvar, 256), 256, 0, p->stream>>>(
+        p->n_cdim, 3 * p->n_pvar, p->d_sq_c.p, p->d_diag_c.p, p->d_Dc.p, p->d_sq_p.p, p->d_diag_p.p, p->d_Dp.p, refresh,
+        o.min_lm_diagonal, o.max_lm_diagonal, p->d_scalars.p);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
@@ -166,13 +160,13 @@ int BackSubstitute(Problem* p) {
   Expand(p, p->d_yc.p, p->d_xi.p, p->d_xc.p);
   const int nb = DivUp(p->n_tiles, 4);
   if (nb > 0) {
-#define CALL(DC) backsub_kernel<DC><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p)
+#define CALL(DC) backsub_kernel<DC><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p, p->d_tickets.p + 2, &p->d_scalars.p->model_cost_change)
     SBA_DC_SWITCH(p->dc, CALL)
 #undef CALL
     p->launches++;
+  } else {
+    SBA_CUDA(cudaMemsetAsync(&p->d_scalars.p->model_cost_change, 0, sizeof(double), p->stream));
   }
-  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &p->d_scalars.p->model_cost_change, nullptr, -1.0);
-  p->launches++;
   SBA_CUDA(cudaGetLastError());
   return AllReduceSum(p, &p->d_scalars.p->model_cost_change, 1);
 }
@@ -182,10 +176,11 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
                                                          const double* __restrict__ yp, const double* __restrict__ scale_c,
                                                          const double* __restrict__ scale_p, double* __restrict__ pose2,
                                                          double* __restrict__ cam2, double* __restrict__ X2,
-                                                         int first, int count, double* __restrict__ partial) {
-  const int t = first + blockIdx.x * 128 + threadIdx.x;
+                                                         int count, double* __restrict__ partial, unsigned* ticket,
+                                                         DeviceScalars* sc) {
+  const int t = blockIdx.x * 128 + threadIdx.x;
   double step2 = 0.0, x2 = 0.0;
-  if (t < first + count) {
+  if (t < count) {
     if (t < S.n_img) {
       const int i = t;
       double rec[8];
@@ -259,29 +254,23 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
       }
     }
   }
-  BlockSum2<128>(step2, x2, partial);
+  // camera-side blocks are replicated on every rank, point blocks are sharded: keep their norms apart
+  const bool cam_side = t < S.n_img + S.n_cam;
+  double v[4] = {cam_side ? step2 : 0.0, cam_side ? x2 : 0.0, cam_side ? 0.0 : step2, cam_side ? 0.0 : x2};
+  double* const out[4] = {&sc->step2_c, &sc->x2_c, &sc->step2_p, &sc->x2_p};
+  GridSum<128, 4>(v, partial, ticket, out);
 }
 
 int ApplyStep(Problem* p) {
   DeviceScalars* sc = p->d_scalars.p;
-  const int n_camside = p->n_img + p->n_cam;
-  int nb = DivUp(n_camside, 128);
+  const int count = p->n_img + p->n_cam + p->n_pt;
+  const int nb = DivUp(count, 128);
   if (nb > 0) {
     apply_step_kernel<<<nb, 128, 0, p->stream>>>(p->Struct(), p->Params(false), p->d_yc.p, p->d_yp.p, p->d_scale_c.p,
-                                                 p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, 0, n_camside,
-                                                 p->d_cost_partial.p);
+                                                 p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, count,
+                                                 p->d_cost_partial.p, p->d_tickets.p + 3, sc);
     p->launches++;
   }
-  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &sc->step2_c, &sc->x2_c, 1.0);
-  nb = DivUp(p->n_pt, 128);
-  if (nb > 0) {
-    apply_step_kernel<<<nb, 128, 0, p->stream>>>(p->Struct(), p->Params(false), p->d_yc.p, p->d_yp.p, p->d_scale_c.p,
-                                                 p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, n_camside, p->n_pt,
-                                                 p->d_cost_partial.p);
-    p->launches++;
-  }
-  finalize_pair_kernel<<<1, 1024, 0, p->stream>>>(p->d_cost_partial.p, nb, &sc->step2_p, &sc->x2_p, 1.0);
-  p->launches += 2;
   SBA_CUDA(cudaGetLastError());
   return AllReduceSum(p, &sc->step2_p, 2);
 }
@@ -303,6 +292,7 @@ __global__ void tr_update_kernel(DeviceScalars* s, int phase, double min_relativ
     }
     s->solver_failed = 0;
   } else {
+    if (!s->step_valid) return;  // phase 0 rejected the step: the candidate that was enqueued anyway is ignored
     double cand = s->cand_cost;
     if (!isfinite(cand)) cand = 1.7976931348623157e308;
     s->step_norm = sqrt(s->step2_c + s->step2_p);
@@ -327,10 +317,11 @@ __global__ void tr_update_kernel(DeviceScalars* s, int phase, double min_relativ
   }
 }
 
-int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase) {
+int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase, bool sync) {
   tr_update_kernel<<<1, 1, 0, p->stream>>>(p->d_scalars.p, phase, o.min_relative_decrease, o.max_trust_region_radius,
                                            o.parameter_tolerance, o.function_tolerance);
   p->launches++;
+  if (!sync) return SBA_OK;
   SBA_CUDA(cudaMemcpyAsync(p->h_scalars, p->d_scalars.p, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, p->stream));
   SBA_CUDA(cudaStreamSynchronize(p->stream));
   return SBA_OK;

@@ -11,6 +11,7 @@
 // (n_cdim) and padded (n_img*6 | n_cam*12, zeros at constant slots) -- the padded
 // form lets an observation fetch its pose's six entries with three 16 B loads.
 #pragma once
+#include "reduce.cuh"
 #include "solver.h"
 #include "tiles.cuh"
 
@@ -37,10 +38,13 @@ __global__ void expand_kernel(StructView S, const double* __restrict__ x, double
 }
 
 template <int DC>
-__device__ inline void LoadRow(const double2* __restrict__ F, int k, double2 (&row)[DC]) {
-  const double2* f = F + (size_t)k * DC;
+__device__ inline void LoadRow(const D4* __restrict__ F, int k, double2 (&row)[DC]) {
+  const D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
-  for (int j = 0; j < DC; ++j) row[j] = f[j];
+  for (int jj = 0; jj < DC / 2; ++jj) {
+    const D4 v = Ld256(f + 32 * jj);
+    row[2 * jj] = make_double2(v.x, v.y); row[2 * jj + 1] = make_double2(v.z, v.w);
+  }
 }
 
 // f = F_k * x  (2-vector), x in padded form
@@ -68,17 +72,16 @@ __device__ inline double2 RowTimesX(const double2 (&row)[DC], const double* __re
 }
 
 struct ERec { double E[6]; double r0, r1; };
-__device__ inline ERec LoadER(const double* __restrict__ ER, int k) {
-  const double2* p = reinterpret_cast<const double2*>(ER + (size_t)k * 8);
-  const double2 a = p[0], b = p[1], c = p[2], d = p[3];
+__device__ inline ERec LoadER(const D4* __restrict__ ER, int k) {
+  const D4 a = Ld256(ER + EUnit(k, 0)), b = Ld256(ER + EUnit(k, 1));
   ERec e;
-  e.E[0] = a.x; e.E[1] = a.y; e.E[2] = b.x; e.E[3] = b.y; e.E[4] = c.x; e.E[5] = c.y;
-  e.r0 = d.x; e.r1 = d.y;
+  e.E[0] = a.x; e.E[1] = a.y; e.E[2] = a.z; e.E[3] = a.w; e.E[4] = b.x; e.E[5] = b.y;
+  e.r0 = b.z; e.r1 = b.w;
   return e;
 }
 
 // ---- point-side squared column norms (Jacobi scaling / LM diagonal) -----------------
-__global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileView T, const double* __restrict__ ER,
+__global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileView T, const D4* __restrict__ ER,
                                                            double* __restrict__ np) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
@@ -115,7 +118,7 @@ __global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileVie
 }
 
 // ---- point blocks: C_p = E^T E + D_p^2, its inverse, and g_p = E^T r -----------------
-__global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileView T, const double* __restrict__ ER,
+__global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileView T, const D4* __restrict__ ER,
                                                            const double* __restrict__ Dp, double* __restrict__ Cinv,
                                                            double* __restrict__ gp, DeviceScalars* sc) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
 }
 
 // ---- e_k = r_k - E_k C_p^{-1} g_p  (right-hand side of the reduced system, before F^T) ----
-__global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const double* __restrict__ ER,
+__global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const D4* __restrict__ ER,
                                                     const double* __restrict__ Cinv, const double* __restrict__ gp,
                                                     double2* __restrict__ out) {
   const int k = blockIdx.x * 256 + threadIdx.x;
@@ -191,8 +194,8 @@ __global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const double* 
 
 // ---- implicit Schur product, point pass:  g_k = F_k x - E_k C_p^{-1} sum_{j in p} E_j^T F_j x ----
 template <int DC>
-__global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileView T, const double* __restrict__ ER,
-                                                           const double2* __restrict__ F, const double* __restrict__ Cinv,
+__global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileView T, const D4* __restrict__ ER,
+                                                           const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                            const double* __restrict__ xi, const double* __restrict__ xc,
                                                            double2* __restrict__ out) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -260,11 +263,12 @@ __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileVie
 // ---- back-substitution y_p = C_p^{-1}(g_p - sum E^T F y_c), fused with the model cost change
 //      -(J step)^T (r + J step / 2), step = -y   ----
 template <int DC>
-__global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, const double* __restrict__ ER,
-                                                      const double2* __restrict__ F, const double* __restrict__ Cinv,
+__global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, const D4* __restrict__ ER,
+                                                      const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                       const double* __restrict__ gp, const double* __restrict__ yi,
                                                       const double* __restrict__ yc, double* __restrict__ yp,
-                                                      double* __restrict__ partial) {
+                                                      double* __restrict__ partial, unsigned* ticket,
+                                                      double* model_cost_change) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   double acc = 0.0;
@@ -334,20 +338,17 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
       }
     }
   }
-  // block partial (4 warps)
-  __shared__ double sm[4];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-  if (lane == 0) sm[threadIdx.x >> 5] = acc;
-  __syncthreads();
-  if (threadIdx.x == 0) { partial[2 * blockIdx.x] = (sm[0] + sm[1]) + (sm[2] + sm[3]); partial[2 * blockIdx.x + 1] = 0.0; }
+  // model cost change = -sum; grid-wide sum finished by the last block (reduce.cuh)
+  double v[1] = {-acc};
+  double* const out[1] = {model_cost_change};
+  GridSum<128, 1>(v, partial, ticket, out);
 }
 
 // ---- camera-side segmented reduction over image-major chunks ------------------------
 // MODE 0: F^T v (v per observation)   MODE 1: F^T r (r from ER)   MODE 2: column square norms
 template <int DC, int MODE>
-__global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const double2* __restrict__ F,
-                                                         const double* __restrict__ ER, const double2* __restrict__ v,
+__global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* __restrict__ F,
+                                                         const D4* __restrict__ ER, const double2* __restrict__ v,
                                                          double* __restrict__ partial) {
   const int ch = blockIdx.x;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const doub
 #pragma unroll
       for (int j = 0; j < DC; ++j) acc[j] = row[j].x * row[j].x + row[j].y * row[j].y;
     } else {
-      const double2 w = MODE == 0 ? v[k] : reinterpret_cast<const double2*>(ER + (size_t)k * 8)[3];
+      const double2 w = MODE == 0 ? v[k] : reinterpret_cast<const double2*>(ER + EUnit(k, 1))[1];  // r = unit 1, z w
 #pragma unroll
       for (int j = 0; j < DC; ++j) acc[j] = row[j].x * w.x + row[j].y * w.y;
     }
@@ -427,34 +428,71 @@ __global__ void jacobi_scale_kernel(int n, const double* __restrict__ sqnorm, do
 template <int DC>
 __global__ void __launch_bounds__(256) scale_jacobian_kernel(StructView S, const double* __restrict__ si,
                                                              const double* __restrict__ sc, const double* __restrict__ sp,
-                                                             double2* __restrict__ F, double* __restrict__ ER) {
+                                                             D4* __restrict__ F, D4* __restrict__ ER) {
   const int k = blockIdx.x * 256 + threadIdx.x;
   if (k >= S.n_obs) return;
   const int i = S.obs_img[k];
-  double2* f = F + (size_t)k * DC;
+  D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
-  for (int j = 0; j < 6; ++j) { const double s = si[6 * (size_t)i + j]; double2 v = f[j]; v.x *= s; v.y *= s; f[j] = v; }
+  for (int jj = 0; jj < 3; ++jj) {
+    const double s0 = si[6 * (size_t)i + 2 * jj], s1 = si[6 * (size_t)i + 2 * jj + 1];
+    D4 v = Ld256(f + 32 * jj);
+    v.x *= s0; v.y *= s0; v.z *= s1; v.w *= s1;
+    St256(f + 32 * jj, v);
+  }
   if (DC > 6) {
     const int c = S.img_cam[i];
 #pragma unroll
-    for (int j = 6; j < DC; ++j) { const double s = sc[12 * (size_t)c + j - 6]; double2 v = f[j]; v.x *= s; v.y *= s; f[j] = v; }
+    for (int jj = 3; jj < DC / 2; ++jj) {
+      const double s0 = sc[12 * (size_t)c + 2 * jj - 6], s1 = sc[12 * (size_t)c + 2 * jj - 5];
+      D4 v = Ld256(f + 32 * jj);
+      v.x *= s0; v.y *= s0; v.z *= s1; v.w *= s1;
+      St256(f + 32 * jj, v);
+    }
   }
   const int po = S.p_off[S.obs_pt[k]];
   if (po >= 0) {
-    double* e = ER + (size_t)k * 8;
-#pragma unroll
-    for (int a = 0; a < 3; ++a) { const double s = sp[3 * (size_t)po + a]; e[a] *= s; e[3 + a] *= s; }
+    const double s0 = sp[3 * (size_t)po], s1 = sp[3 * (size_t)po + 1], s2 = sp[3 * (size_t)po + 2];
+    D4 a = Ld256(ER + EUnit(k, 0)), b = Ld256(ER + EUnit(k, 1));
+    a.x *= s0; a.y *= s1; a.z *= s2; a.w *= s0; b.x *= s1; b.y *= s2;  // E row-major 2x3: (E0 E1 E2 | E3 E4 E5)
+    St256(ER + EUnit(k, 0), a); St256(ER + EUnit(k, 1), b);
   }
 }
 
 // LM diagonal: diag = clamp(colnorm^2), D = sqrt(diag / radius)
-__global__ void lm_diag_kernel(int n, const double* __restrict__ sqnorm, double* __restrict__ diag, double* __restrict__ D,
-                               int refresh, double lo, double hi, const DeviceScalars* sc) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
+// camera columns [0, nc) and point columns [nc, nc + np) in one launch
+__global__ void lm_diag_kernel(int nc, int np, const double* __restrict__ sq_c, double* __restrict__ diag_c,
+                               double* __restrict__ D_c, const double* __restrict__ sq_p, double* __restrict__ diag_p,
+                               double* __restrict__ D_p, int refresh, double lo, double hi, const DeviceScalars* sc) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nc + np) return;
+  const double* sq = sq_c; double* diag = diag_c; double* D = D_c;
+  if (j >= nc) { j -= nc; sq = sq_p; diag = diag_p; D = D_p; }
   double d = diag[j];
-  if (refresh) { d = fmin(fmax(sqnorm[j], lo), hi); diag[j] = d; }
+  if (refresh) { d = fmin(fmax(sq[j], lo), hi); diag[j] = d; }
   D[j] = sqrt(d / sc->radius);
+}
+
+// max |g_j / scale_j| over the camera part and the point part in one launch.  max is order-independent, and
+// non-negative doubles order like their bit patterns, so an integer atomicMax gives a deterministic result.
+// *out must be zero on entry.
+__global__ void __launch_bounds__(256) grad_maxnorm_kernel(int nc, const double* __restrict__ gc, const double* __restrict__ sc_,
+                                                           int np, const double* __restrict__ gp, const double* __restrict__ sp,
+                                                           double* out) {
+  double m = 0.0;
+  for (int j = blockIdx.x * 256 + threadIdx.x; j < nc + np; j += gridDim.x * 256) {
+    const double v = j < nc ? gc[j] / sc_[j] : gp[j - nc] / sp[j - nc];
+    m = fmax(m, fabs(v));  // fmax drops NaN, as std::max(m, |v|) over a NaN-free gradient does
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_down_sync(0xffffffffu, m, o));
+  __shared__ double sm[8];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < 8; ++i) m = fmax(m, sm[i]);
+    atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(m));
+  }
 }
 
 // max |g_j / scale_j| over a vector -> partial maxima

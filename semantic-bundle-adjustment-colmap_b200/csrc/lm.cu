@@ -109,9 +109,26 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   bool stop = user_stop(it0);
   tmh.Lap("iteration 0");
 
+  // One host synchronisation per iteration.  The step-validity test (phase 0) and the acceptance test
+  // (phase 1) both run on the device; the candidate point and its cost are enqueued unconditionally (an
+  // invalid step -- rare -- makes phase 1 a no-op and wastes one cost pass).  After an accepted step the new
+  // linearisation is enqueued and, unless a callback or a gradient tolerance needs its numbers right away, the
+  // host does not wait for it: cost and gradient norm of that row are filled in at the next synchronisation.
+  const bool eager = cb != nullptr || o.gradient_tolerance > 0.0;
+  int pending_row = -1;       // trace row whose cost / gradient are still on the device
+  bool pending_eval_time = false;
+  auto settle = [&]() {       // hs is current: complete the deferred row
+    if (pending_eval_time) { p->t_eval += tm.Ms(6, 7) * 1e-3; pending_eval_time = false; }
+    if (pending_row >= 0) {
+      x_cost = hs->cost;
+      p->trace[pending_row].cost = x_cost + fixed_cost;
+      p->trace[pending_row].gradient_max_norm = hs->gradient_max_norm;
+      pending_row = -1;
+    }
+  };
   while (!stop) {
     if (iteration >= o.max_num_iterations) { termination = SBA_NO_CONVERGENCE; break; }
-    if (p->trace.back().gradient_max_norm <= o.gradient_tolerance) { termination = SBA_CONVERGENCE; break; }
+    if (pending_row < 0 && p->trace.back().gradient_max_norm <= o.gradient_tolerance) { termination = SBA_CONVERGENCE; break; }
     if (radius < o.min_trust_region_radius) { termination = SBA_CONVERGENCE; break; }
     ++iteration;
     sba_iteration_summary it;
@@ -141,7 +158,17 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     }
     tm.Mark(2, st);
     if ((rc = BackSubstitute(p))) return rc;
-    if ((rc = TrustRegionUpdate(p, o, 0))) return rc;  // syncs; hs is current
+    if ((rc = TrustRegionUpdate(p, o, 0, false))) return rc;
+    // ---- candidate point and its cost ----
+    tm.Mark(3, st);
+    if ((rc = ApplyStep(p))) return rc;
+    tm.Mark(4, st);
+    if ((rc = LaunchCostOnly(p, loss, true, &sc->cand_cost))) return rc;
+    tm.Mark(5, st);
+    if ((rc = TrustRegionUpdate(p, o, 1, true))) return rc;  // syncs; hs is current
+    settle();
+    p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;
+    p->t_update += (tm.Ms(2, 3) + tm.Ms(3, 4)) * 1e-3; p->t_eval += tm.Ms(4, 5) * 1e-3;
     it.linear_solver_iterations = lin_iters;
     sum->num_linear_solver_iterations += lin_iters;
     it.step_is_valid = hs->step_valid;
@@ -153,22 +180,11 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       it.trust_region_radius = radius;
       p->trace.push_back(it);
       sum->num_unsuccessful_steps++;
-      p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;
       if (num_consecutive_invalid >= o.max_num_consecutive_invalid_steps) { termination = SBA_FAILURE; break; }
       if (user_stop(it)) break;
       continue;
     }
     num_consecutive_invalid = 0;
-
-    // ---- candidate point and its cost ----
-    tm.Mark(3, st);
-    if ((rc = ApplyStep(p))) return rc;
-    tm.Mark(4, st);
-    if ((rc = LaunchCostOnly(p, loss, true, &sc->cand_cost))) return rc;
-    tm.Mark(5, st);
-    if ((rc = TrustRegionUpdate(p, o, 1))) return rc;  // syncs
-    p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;
-    p->t_update += (tm.Ms(2, 3) + tm.Ms(3, 4)) * 1e-3; p->t_eval += tm.Ms(4, 5) * 1e-3;
     it.step_norm = hs->step_norm;
     it.cost_change = hs->cost_change;
     if (hs->converged) {  // parameter / function tolerance
@@ -181,6 +197,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     }
     it.relative_decrease = hs->relative_decrease;
     radius = hs->radius;
+    it.trust_region_radius = radius;
     if (hs->step_accepted) {
       std::swap(p->d_pose.p, p->d_pose2.p);
       std::swap(p->d_cam.p, p->d_cam2.p);
@@ -190,22 +207,31 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       if ((rc = PointBlocks(p, true))) return rc;
       if ((rc = Gradient(p))) return rc;
       tm.Mark(7, st);
-      SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
-      SBA_CUDA(cudaStreamSynchronize(st));
-      p->t_eval += tm.Ms(6, 7) * 1e-3;
-      x_cost = hs->cost;
-      it.gradient_max_norm = hs->gradient_max_norm;
       it.step_is_successful = 1;
       sum->num_successful_steps++;
+      it.cost = x_cost + fixed_cost;  // provisional; settled below or at the next synchronisation
+      it.gradient_max_norm = p->trace.back().gradient_max_norm;
+      p->trace.push_back(it);
+      pending_row = (int)p->trace.size() - 1;
+      pending_eval_time = true;
+      if (eager || iteration >= o.max_num_iterations) {
+        SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
+        SBA_CUDA(cudaStreamSynchronize(st));
+        settle();
+      }
     } else {
       it.gradient_max_norm = p->trace.back().gradient_max_norm;
       sum->num_unsuccessful_steps++;
+      it.cost = x_cost + fixed_cost;
+      p->trace.push_back(it);
     }
-    it.cost = x_cost + fixed_cost;
-    it.trust_region_radius = radius;
-    p->trace.push_back(it);
     tmh.Lap("iteration");
-    if (user_stop(it)) break;
+    if (eager && user_stop(p->trace.back())) break;
+  }
+  if (pending_row >= 0 || pending_eval_time) {
+    SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaStreamSynchronize(st));
+    settle();
   }
   {
     float ms = 0.f;

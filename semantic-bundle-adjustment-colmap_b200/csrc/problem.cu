@@ -9,7 +9,10 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
+#include <mutex>
 #include <numeric>
+#include <thread>
 
 #include "device_math.cuh"
 #include "solver.h"
@@ -29,6 +32,25 @@ void HostTimer::Lap(const char* label) {
   t0 = t;
 }
 
+int HostThreads() {
+  static const int n = [] {
+    const char* e = getenv("SBA_HOST_THREADS");
+    int v = e ? atoi(e) : (int)std::thread::hardware_concurrency();
+    return std::max(1, std::min(v, 16));
+  }();
+  return n;
+}
+void ParallelFor(int n_tasks, const std::function<void(int)>& fn) {
+  const int nt = std::min(HostThreads(), n_tasks);
+  if (nt <= 1) { for (int t = 0; t < n_tasks; ++t) fn(t); return; }
+  std::atomic<int> next(0);
+  auto work = [&]() { for (int t; (t = next.fetch_add(1)) < n_tasks;) fn(t); };
+  std::vector<std::thread> th;
+  for (int i = 1; i < nt; ++i) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+}
+
 cudaStream_t AllocStream() {
   static cudaStream_t streams[64] = {};
   int dev = 0;
@@ -45,11 +67,89 @@ cudaStream_t AllocStream() {
   return streams[dev];
 }
 
+// A handle's stream and its pinned scalar block are recycled across handles of the same device:
+// cudaMallocHost alone costs about a millisecond, which is a tenth of a whole C2-sized solve.
+namespace {
+struct Ctx { int device; cudaStream_t stream; DeviceScalars* pinned; };
+std::mutex g_ctx_mu;
+std::vector<Ctx> g_ctx_free;
+}  // namespace
+static cudaError_t AcquireCtx(int device, cudaStream_t* stream, DeviceScalars** pinned) {
+  {
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    for (size_t i = 0; i < g_ctx_free.size(); ++i)
+      if (g_ctx_free[i].device == device) {
+        *stream = g_ctx_free[i].stream; *pinned = g_ctx_free[i].pinned;
+        g_ctx_free.erase(g_ctx_free.begin() + i);
+        return cudaSuccess;
+      }
+  }
+  cudaError_t e = cudaStreamCreateWithFlags(stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) return e;
+  return cudaMallocHost((void**)pinned, sizeof(DeviceScalars));
+}
+
+// Large host -> device copies from the caller's PAGEABLE arrays (label maps: 61 MB at C2, 6 GB at C5).
+// A plain cudaMemcpyAsync stages them through the driver on one thread (~8 GB/s measured); here four host
+// threads copy 2 MB chunks into process-lifetime pinned buffers (two per thread) and queue the DMA of each
+// chunk themselves, so the staging memcpy of one chunk overlaps the DMA of the others.
+namespace {
+constexpr size_t kStageChunk = 2u << 20;
+constexpr int kStageThreads = 4, kStageDepth = 2;
+struct StageBufs {
+  char* buf[kStageThreads][kStageDepth] = {};
+  cudaEvent_t ev[kStageThreads][kStageDepth] = {};
+  bool ok = false;
+};
+std::mutex g_stage_mu;  // one large upload at a time per process
+StageBufs g_stage;
+}  // namespace
+cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes < 4 * kStageChunk) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  std::lock_guard<std::mutex> lk(g_stage_mu);
+  if (!g_stage.ok) {
+    for (int t = 0; t < kStageThreads; ++t)
+      for (int d = 0; d < kStageDepth; ++d) {
+        cudaError_t e = cudaMallocHost((void**)&g_stage.buf[t][d], kStageChunk);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g_stage.ev[t][d], cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+      }
+    g_stage.ok = true;
+  }
+  const size_t n_chunks = (bytes + kStageChunk - 1) / kStageChunk;
+  std::atomic<size_t> next(0);
+  std::atomic<int> err((int)cudaSuccess);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto work = [&](int t) {
+    cudaSetDevice(dev);
+    int d = 0;
+    for (size_t c; (c = next.fetch_add(1)) < n_chunks; d ^= 1) {
+      const size_t off = c * kStageChunk, len = std::min(kStageChunk, bytes - off);
+      cudaEventSynchronize(g_stage.ev[t][d]);  // the DMA that last read this buffer has finished
+      std::memcpy(g_stage.buf[t][d], (const char*)src + off, len);
+      cudaError_t e = cudaMemcpyAsync((char*)dst + off, g_stage.buf[t][d], len, cudaMemcpyHostToDevice, st);
+      if (e == cudaSuccess) e = cudaEventRecord(g_stage.ev[t][d], st);
+      if (e != cudaSuccess) err.store((int)e);
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < kStageThreads; ++t) th.emplace_back(work, t);
+  work(0);
+  for (auto& t : th) t.join();
+  return (cudaError_t)err.load();
+}
+
 Problem::~Problem() {
   if (stream) cudaStreamSynchronize(stream);  // buffers go back to the pool only once nothing uses them
   CommDestroy(this);
-  if (h_scalars) cudaFreeHost(h_scalars);
-  if (stream) cudaStreamDestroy(stream);
+  if (stream && h_scalars) {
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    g_ctx_free.push_back(Ctx{device, stream, h_scalars});
+  } else {
+    if (h_scalars) cudaFreeHost(h_scalars);
+    if (stream) cudaStreamDestroy(stream);
+  }
 }
 
 ParamsView Problem::Params(bool candidate) const {
@@ -279,7 +379,8 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   p->h_p_off.assign(p->n_pt, -1);
   p->n_pvar = 0;
   for (int q = 0; q < p->n_pt; ++q) if (g.p_off_global[p0 + q] >= 0) p->h_p_off[q] = p->n_pvar++;
-  std::vector<int> h_pt_ptr(p->n_pt + 1);
+  std::vector<int>& h_pt_ptr = p->h_pt_ptr;
+  h_pt_ptr.resize(p->n_pt + 1);
   for (int q = 0; q <= p->n_pt; ++q) h_pt_ptr[q] = (int)(prefix[p0 + q] - prefix[p0]);
 
   tm.Lap("shard + point sort");
@@ -300,7 +401,8 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   p->n_tiles = (int)tile_start.size() - 1;
 
   // ---- image-major index list + chunks of <= 256 ----
-  std::vector<int> img_ptr(p->n_img + 1, 0), cam_order(n_obs);
+  std::vector<int>& img_ptr = p->h_img_ptr; std::vector<int>& cam_order = p->h_cam_order;
+  img_ptr.assign(p->n_img + 1, 0); cam_order.resize(n_obs);
   for (int k = 0; k < n_obs; ++k) img_ptr[p->h_obs_img[k] + 1]++;
   for (int i = 0; i < p->n_img; ++i) img_ptr[i + 1] += img_ptr[i];
   {
@@ -340,8 +442,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   }
   cudaGetDevice(&p->device);
 #define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
-  UP(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
-  UP(cudaMallocHost((void**)&p->h_scalars, sizeof(DeviceScalars)));
+  UP(AcquireCtx(p->device, &p->stream, &p->h_scalars));
   std::memset(p->h_scalars, 0, sizeof(DeviceScalars));
   cudaStream_t st = p->stream;
   std::vector<double> pose((size_t)p->n_img * 8, 0.0), cam((size_t)p->n_cam * 12, 0.0), X((size_t)p->n_pt * 3);
@@ -372,12 +473,24 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_col_blk.Upload(col_blk, st));
   tm.Lap("uploads");
   const size_t nc = std::max(1, p->n_cdim), np3 = std::max(1, 3 * p->n_pvar);
-  UP(p->d_ER.Alloc((size_t)std::max(1, n_obs) * 8)); UP(p->d_F.Alloc((size_t)std::max(1, n_obs) * p->dc));
+  UP(p->d_ER.Alloc(TilePad(std::max(1, n_obs)) * 2)); UP(p->d_F.Alloc(TilePad(std::max(1, n_obs)) * (p->dc / 2)));
   p->n_partial = std::max(std::max(DivUp(std::max(1, n_obs), 128), DivUp(std::max(1, p->n_tiles), 4)),
                           DivUp(p->n_img + p->n_cam + p->n_pt, 128)) + 8;
-  UP(p->d_cost_partial.Alloc(2 * (size_t)p->n_partial));
+  UP(p->d_cost_partial.Alloc(4 * (size_t)p->n_partial));
   UP(p->d_xi.Alloc((size_t)std::max(1, p->n_img) * 6)); UP(p->d_xc.Alloc((size_t)std::max(1, p->n_cam) * 12));
   UP(p->d_scale_i.Alloc((size_t)std::max(1, p->n_img) * 6)); UP(p->d_scale_k.Alloc((size_t)std::max(1, p->n_cam) * 12));
+  {  // 1 / 0 masks of the free slots (the scale of the unscaled evaluation) and the packed slot -> parameter map
+    std::vector<double> mi((size_t)std::max(1, p->n_img) * 6, 0.0), mk((size_t)std::max(1, p->n_cam) * 12, 0.0);
+    std::vector<unsigned long long> pack(std::max(1, p->n_cam), 0ull);
+    for (size_t j = 0; j < (size_t)p->n_img * 6; ++j) mi[j] = p->h_col_img[j] >= 0 ? 1.0 : 0.0;
+    for (int c = 0; c < p->n_cam; ++c)
+      for (int j = 0; j < p->h_k_dim[c]; ++j) {
+        mk[12 * (size_t)c + j] = p->h_col_cam[12 * (size_t)c + j] >= 0 ? 1.0 : 0.0;
+        pack[c] |= (unsigned long long)(p->h_k_cols[12 * (size_t)c + j] & 15) << (4 * j);
+      }
+    UP(p->d_mask_i.Upload(mi, st)); UP(p->d_mask_k.Upload(mk, st)); UP(p->d_k_pack.Upload(pack, st));
+    UP(cudaStreamSynchronize(st));  // the vectors above go out of scope
+  }
   UP(p->d_red.Alloc(2048));
   UP(p->d_scale_c.Alloc(nc)); UP(p->d_scale_p.Alloc(np3));
   UP(p->d_sq_c.Alloc(nc)); UP(p->d_sq_p.Alloc(np3));
@@ -389,11 +502,12 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_grad_c.Alloc(nc)); UP(p->d_grad_p.Alloc(np3)); UP(p->d_tmp_c.Alloc(nc));
   UP(p->d_cg_r.Alloc(nc)); UP(p->d_cg_z.Alloc(nc)); UP(p->d_cg_p.Alloc(nc)); UP(p->d_cg_q.Alloc(nc)); UP(p->d_cg_x.Alloc(nc));
   UP(p->d_scalars.Alloc(1)); UP(p->d_scalars.Zero(st));
+  UP(p->d_tickets.Alloc(8)); UP(p->d_tickets.Zero(st));
   tm.Lap("allocs");
   if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0) {
     const size_t n_map = (size_t)p->n_img * d.sem_height * d.sem_width;
     UP(p->d_sem_maps.Alloc(n_map));
-    UP(cudaMemcpyAsync(p->d_sem_maps.p, d.sem_maps, n_map * sizeof(float), cudaMemcpyHostToDevice, st));
+    UP(UploadLarge(p->d_sem_maps.p, d.sem_maps, n_map * sizeof(float), st));
     p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
   }
   UP(cudaStreamSynchronize(st));

@@ -26,6 +26,54 @@ __device__ inline void BlockSum2(double a, double b, double* out) {
   }
 }
 
+// Grid-wide sum of N values per thread without a second launch: every block writes its partial sums, takes a
+// ticket, and the block that draws the last ticket adds all partials in a FIXED order (strided per thread,
+// then the same shuffle tree) -- the result does not depend on which block happened to finish last.
+// out[i] may be null.  `ticket` must be zero on entry and is left at zero.
+template <int THREADS, int N>
+__device__ inline void GridSum(double (&v)[N], double* __restrict__ partial, unsigned* ticket, double* const (&out)[N]) {
+  __shared__ double sm[THREADS / 32][N];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < N; ++i) { const double t = WarpSum(v[i]); if (lane == 0) sm[w][i] = t; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      double t = 0.0;
+#pragma unroll
+      for (int k = 0; k < THREADS / 32; ++k) t += sm[k][i];
+      partial[(size_t)N * blockIdx.x + i] = t;
+    }
+    __threadfence();
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  double acc[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) acc[i] = 0.0;
+  for (unsigned b = threadIdx.x; b < gridDim.x; b += THREADS) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) acc[i] += __ldcg(partial + (size_t)N * b + i);
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) { const double t = WarpSum(acc[i]); if (lane == 0) sm[w][i] = t; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      double t = 0.0;
+#pragma unroll
+      for (int k = 0; k < THREADS / 32; ++k) t += sm[k][i];
+      if (out[i]) *out[i] = t;
+    }
+    *ticket = 0u;
+  }
+}
+
 // fixed-order final reduction of per-block pairs -> out0 (sum of [2i]), out1 (sum of [2i+1])
 static __global__ void __launch_bounds__(1024) finalize_pair_kernel(const double* __restrict__ partial, int n,
                                                                     double* out0, double* out1, double sign0) {

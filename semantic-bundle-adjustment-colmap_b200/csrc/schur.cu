@@ -38,16 +38,16 @@ template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; }
 
 // W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (observation, slot)
 template <int DC>
-__global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const double* __restrict__ ER,
-                                                       const double2* __restrict__ F, const double* __restrict__ Cinv,
+__global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const D4* __restrict__ ER,
+                                                       const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                        double* __restrict__ W, double* __restrict__ H) {
   const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (t >= (int64_t)S.n_obs * DC) return;
   const int a = (int)(t / DC);
-  const double2 f = F[t];
-  const double2* ea = reinterpret_cast<const double2*>(ER + (size_t)a * 8);
-  const double2 e0 = ea[0], e1 = ea[1], e2 = ea[2];  // E row0 = (e0.x e0.y e1.x), row1 = (e1.y e2.x e2.y)
-  const double w[3] = {f.x * e0.x + f.y * e1.y, f.x * e0.y + f.y * e2.x, f.x * e1.x + f.y * e2.y};
+  const double2 f = LoadSlot(F, a, (int)(t - (int64_t)a * DC), DC / 2);
+  const D4 ea = Ld256(ER + EUnit(a, 0));                                          // E0 E1 E2 E3
+  const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];       // E4 E5
+  const double w[3] = {f.x * ea.x + f.y * ea.w, f.x * ea.y + f.y * eb.x, f.x * ea.z + f.y * eb.y};
   double h[3] = {0.0, 0.0, 0.0};
   const int po = S.p_off[S.obs_pt[a]];
   if (po >= 0) Sym3Mul(Cinv + 6 * (size_t)po, w, h);
@@ -92,7 +92,7 @@ __device__ inline void Emit(const Sink& k, int row, int col, double v, bool same
 
 // ---- diagonal contributions: chunk partial blocks -------------------------------------
 template <int DC>
-__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, const double2* __restrict__ F,
+__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, const D4* __restrict__ F,
                                                                const double* __restrict__ W, const double* __restrict__ H,
                                                                double* __restrict__ partial) {
   __shared__ double red[8][DC * DC];
@@ -108,10 +108,11 @@ __global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, cons
   }
   const int lo = w * 32, hi = min(n, lo + 32);
   for (int t = lo; t < hi; ++t) {
-    const size_t a = (size_t)C.cam_order[s0 + t] * DC;
+    const int obs = C.cam_order[s0 + t];
+    const size_t a = (size_t)obs * DC;
 #pragma unroll
     for (int q = 0; q < Elems<DC>::N; ++q) {
-      const double2 fa = F[a + ja[q]], fb = F[a + jb[q]];
+      const double2 fa = LoadSlot(F, obs, ja[q], DC / 2), fb = LoadSlot(F, obs, jb[q], DC / 2);
       const double* h = H + 3 * (a + ja[q]);
       const double* wv = W + 3 * (a + jb[q]);
       acc[q] += (fa.x * fb.x + fa.y * fb.y) - (h[0] * wv[0] + h[1] * wv[1] + h[2] * wv[2]);
@@ -270,9 +271,7 @@ int BuildPairLists(Problem* p, bool dense) {
   HostTimer tm("pair lists");
   const int n_pt = p->n_pt, n_img = p->n_img;
   const std::vector<int>& img = p->h_obs_img;
-  std::vector<int> pt_ptr(n_pt + 1, 0);
-  for (int k = 0; k < p->n_obs; ++k) pt_ptr[p->h_obs_pt[k] + 1]++;
-  for (int q = 0; q < n_pt; ++q) pt_ptr[q + 1] += pt_ptr[q];
+  const std::vector<int>& pt_ptr = p->h_pt_ptr;
   // which points can contribute at all
   bool any = dense;
   std::vector<uint8_t> has_dup(n_pt, 0);
@@ -288,65 +287,81 @@ int BuildPairLists(Problem* p, bool dense) {
   }
   const bool shared = !dense && p->shared_intrinsics;
   if (shared) any = true;
-  struct Ent { int64_t key; int a, b; };
-  std::vector<Ent> ents;
-  if (any) {
-    auto wanted = [&](int a, int b) -> bool {  // img[a] >= img[b]
-      if (img[a] == img[b]) return true;
-      if (dense) return true;
-      if (!shared) return false;
-      const int ca = p->h_img_cam[img[a]], cb = p->h_img_cam[img[b]];
-      return ca == cb && p->h_k_dim[ca] > 0;
-    };
-    size_t guess = 0;
-    if (dense) for (int q = 0; q < n_pt; ++q) { const size_t l = pt_ptr[q + 1] - pt_ptr[q]; guess += l * (l - 1) / 2; }
-    ents.reserve(guess);
-    for (int q = 0; q < n_pt; ++q) {
-      if (p->h_p_off[q] < 0) continue;            // constant point: E = 0
-      if (!dense && !shared && !has_dup[q]) continue;
-      for (int s = pt_ptr[q]; s < pt_ptr[q + 1]; ++s)
+  tm.Lap("duplicates");
+  // The key (image(a), image(b)) is owned by image(a): every image enumerates, over its own observations in
+  // image-major order, the partner observations of the same point and groups them by image(b) with a local
+  // counting sort.  Images are independent, so the enumeration runs on all host threads; concatenating the
+  // per-image results in image order IS the key-sorted list, and the order inside a key (point order, then
+  // partner order) does not depend on the thread count -- the reductions stay bit-reproducible.
+  struct Part { std::vector<int> a, b, key_j, key_n; };
+  std::vector<Part> parts(std::max(1, n_img));
+  if (any && p->n_obs > 0) {
+    ParallelFor(n_img, [&](int i) {
+      Part& P = parts[i];
+      const int s0 = p->h_img_ptr[i], s1 = p->h_img_ptr[i + 1];
+      if (s0 == s1) return;
+      const int ci = p->h_img_cam[i];
+      std::vector<int> ta, tb, tj;
+      for (int pos = s0; pos < s1; ++pos) {
+        const int s = p->h_cam_order[pos];
+        const int q = p->h_obs_pt[s];
+        if (p->h_p_off[q] < 0) continue;               // constant point: E = 0
+        if (!dense && !shared && !has_dup[q]) continue;
         for (int t = pt_ptr[q]; t < pt_ptr[q + 1]; ++t) {
-          if (s == t || img[s] < img[t]) continue;  // the (t,s) visit handles img[s] < img[t]
-          if (!wanted(s, t)) continue;
-          ents.push_back({(int64_t)img[s] * n_img + img[t], s, t});
+          const int j = img[t];
+          if (t == s || j > i) continue;                // the partner's own visit handles image(b) > image(a)
+          if (j != i && !dense) {
+            if (!shared) continue;
+            if (p->h_img_cam[j] != ci || p->h_k_dim[ci] <= 0) continue;
+          }
+          ta.push_back(s); tb.push_back(t); tj.push_back(j);
         }
-    }
-  }
-  tm.Lap("enumerate");
-  // counting sort by key when the key space is small enough, else comparison sort
-  const int64_t key_space = (int64_t)n_img * n_img;
-  std::vector<int> pa(ents.size()), pb(ents.size()), key_ptr, key_gi, key_gj;
-  if (!ents.empty() && key_space <= (int64_t)4 << 20) {
-    std::vector<int> cnt(key_space + 1, 0);
-    for (const Ent& e : ents) cnt[e.key + 1]++;
-    for (int64_t k = 0; k < key_space; ++k) {
-      if (cnt[k + 1] > 0) { key_ptr.push_back(cnt[k]); key_gi.push_back((int)(k / n_img)); key_gj.push_back((int)(k % n_img)); }
-      cnt[k + 1] += cnt[k];
-    }
-    for (const Ent& e : ents) { const int pos = cnt[e.key]++; pa[pos] = e.a; pb[pos] = e.b; }
-  } else {
-    std::stable_sort(ents.begin(), ents.end(), [](const Ent& x, const Ent& y) { return x.key < y.key; });
-    for (size_t e = 0; e < ents.size(); ++e) {
-      if (e == 0 || ents[e].key != ents[e - 1].key) {
-        key_ptr.push_back((int)e);
-        key_gi.push_back((int)(ents[e].key / n_img)); key_gj.push_back((int)(ents[e].key % n_img));
       }
-      pa[e] = ents[e].a; pb[e] = ents[e].b;
-    }
+      if (ta.empty()) return;
+      std::vector<int> cnt(i + 2, 0);                   // partner images are <= i
+      for (int j : tj) cnt[j + 1]++;
+      for (int j = 0; j <= i; ++j) {
+        if (cnt[j + 1] > 0) { P.key_j.push_back(j); P.key_n.push_back(cnt[j + 1]); }
+        cnt[j + 1] += cnt[j];
+      }
+      P.a.resize(ta.size()); P.b.resize(ta.size());
+      for (size_t e = 0; e < ta.size(); ++e) { const int pos = cnt[tj[e]]++; P.a[pos] = ta[e]; P.b[pos] = tb[e]; }
+    });
   }
-  key_ptr.push_back((int)ents.size());
-  tm.Lap("sort");
+  tm.Lap("enumerate + sort");
+  size_t n_pairs = 0, n_keys = 0;
+  std::vector<size_t> pair_off(n_img + 1, 0), key_off(n_img + 1, 0);
+  for (int i = 0; i < n_img; ++i) {
+    pair_off[i] = n_pairs; key_off[i] = n_keys;
+    n_pairs += parts[i].a.size(); n_keys += parts[i].key_j.size();
+  }
+  pair_off[n_img] = n_pairs; key_off[n_img] = n_keys;
+  std::vector<int> pa(n_pairs), pb(n_pairs), key_ptr(n_keys + 1), key_gi(n_keys), key_gj(n_keys);
+  ParallelFor(n_img, [&](int i) {
+    const Part& P = parts[i];
+    if (P.a.empty()) return;
+    std::copy(P.a.begin(), P.a.end(), pa.begin() + pair_off[i]);
+    std::copy(P.b.begin(), P.b.end(), pb.begin() + pair_off[i]);
+    size_t at = pair_off[i];
+    for (size_t k = 0; k < P.key_j.size(); ++k) {
+      key_ptr[key_off[i] + k] = (int)at; key_gi[key_off[i] + k] = i; key_gj[key_off[i] + k] = P.key_j[k];
+      at += P.key_n[k];
+    }
+  });
+  key_ptr[n_keys] = (int)n_pairs;
   // segments
   std::vector<int> seg_ptr, key_seg_ptr;
-  for (size_t k = 0; k + 1 < key_ptr.size(); ++k) {
+  seg_ptr.reserve(n_pairs / kSegPairs + n_keys + 1); key_seg_ptr.reserve(n_keys + 1);
+  for (size_t k = 0; k < n_keys; ++k) {
     key_seg_ptr.push_back((int)seg_ptr.size());
     for (int s = key_ptr[k]; s < key_ptr[k + 1]; s += kSegPairs) seg_ptr.push_back(s);
   }
   key_seg_ptr.push_back((int)seg_ptr.size());
   L.n_seg = (int)seg_ptr.size();
-  seg_ptr.push_back((int)ents.size());
-  L.n_keys = (int)key_gi.size();
-  L.n_pairs = (int64_t)ents.size();
+  seg_ptr.push_back((int)n_pairs);
+  L.n_keys = (int)n_keys;
+  L.n_pairs = (int64_t)n_pairs;
+  tm.Lap("merge + segments");
   cudaStream_t st = p->stream;
   SBA_CUDA(L.seg_ptr.Upload(seg_ptr, st)); SBA_CUDA(L.key_seg_ptr.Upload(key_seg_ptr, st));
   SBA_CUDA(L.key_gi.Upload(key_gi, st)); SBA_CUDA(L.key_gj.Upload(key_gj, st));
@@ -354,7 +369,7 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(L.partial.Alloc((size_t)std::max(1, L.n_seg) * p->dc * p->dc));
   SBA_CUDA(cudaStreamSynchronize(st));
   L.built = true;
-  tm.Lap("segments + upload");
+  tm.Lap("upload");
   return SBA_OK;
 }
 

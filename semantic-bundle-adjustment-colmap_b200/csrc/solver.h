@@ -103,6 +103,7 @@ struct Problem {
   std::vector<int> h_img_cam, h_model, h_col_img, h_col_cam, h_k_cols, h_k_slot, h_k_dim, h_p_off;
   std::vector<int> h_blk_off, h_blk_dim;       // SCHUR_JACOBI parameter blocks (compact cols)
   std::vector<int> h_obs_img, h_obs_pt;        // local, point-sorted
+  std::vector<int> h_pt_ptr, h_img_ptr, h_cam_order;  // CSR over points; image-major list of local observation ids
   std::vector<int64_t> h_local2ref;            // local point-sorted position -> reference residual index
   std::vector<int> h_pt_local2global;          // local point -> global point
   std::vector<uint8_t> h_pose_const;
@@ -133,8 +134,8 @@ struct Problem {
   DevBuf<double> d_pose0, d_cam0, d_X0;  // parameters at creation (sba_reset)
 
   // ---- device: linearisation ----
-  DevBuf<double> d_ER;   // [n_obs*8]
-  DevBuf<double2> d_F;   // [n_obs*dc]
+  DevBuf<D4> d_ER;       // [TilePad(n_obs)*2]       tile-blocked (common.cuh)
+  DevBuf<D4> d_F;        // [TilePad(n_obs)*dc/2]    tile-blocked
   DevBuf<double> d_cost_partial;  // [blocks*2]
   DevBuf<double> d_scale_c, d_scale_p;      // Jacobi scaling
   DevBuf<double> d_diag_c, d_diag_p;        // clamped column square norms
@@ -149,10 +150,13 @@ struct Problem {
   DevBuf<double> d_Minv;                    // SCHUR_JACOBI inverse blocks
   DevBuf<double> d_cg_r, d_cg_z, d_cg_p, d_cg_q, d_cg_x;
   DevBuf<double> d_xi, d_xc;                // padded camera-space vector (n_img*6 | n_cam*12)
-  DevBuf<double> d_scale_i, d_scale_k;      // padded Jacobi scale
+  DevBuf<double> d_scale_i, d_scale_k;      // padded Jacobi scale (0 at constant slots)
+  DevBuf<double> d_mask_i, d_mask_k;        // padded 1 / 0 masks: the unscaled evaluation uses these as its scale
+  DevBuf<unsigned long long> d_k_pack;      // [n_cam] nibble s = ambient parameter index of intrinsics slot s
   DevBuf<double> d_sq_c, d_sq_p;            // raw column square norms
   DevBuf<double> d_red;                     // small reduction scratch (>= 1024 doubles)
   int n_partial = 0;                        // capacity (pairs) of d_cost_partial
+  DevBuf<unsigned> d_tickets;               // GridSum tickets (reduce.cuh), zero between launches
   DevBuf<DeviceScalars> d_scalars;
   DeviceScalars* h_scalars = nullptr;       // pinned
 
@@ -198,7 +202,7 @@ int SchurMatVec(Problem* p, const double* d_x, double* d_y);
 int BackSubstitute(Problem* p);
 int ModelCostChange(Problem* p);
 int ApplyStep(Problem* p);
-int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase);
+int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase, bool sync);
 int AllReduceSum(Problem* p, double* d_buf, size_t n);
 // schur.cu
 int BuildPairLists(Problem* p, bool dense);
