@@ -12,6 +12,8 @@
 // HBM traffic per observation (algorithmic): 8 B indices + 16 B xy in,
 // 64 B ER record + 16*DC B F record out (tile-blocked 32 B units, common.cuh); poses / intrinsics /
 // points are gathered through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
+#include <algorithm>
+
 #include "device_math.cuh"
 #include "reduce.cuh"
 #include "solver.h"
@@ -72,18 +74,37 @@ __device__ __forceinline__ void PickParam(const double (&Jk)[24], int amb, doubl
 // index-table version needed, which is what bounded it (L1 wavefronts, profiles/r01_ncu_full_c4_eval_v1.txt).
 // The records leave as 32 B units of the tile-blocked layout: every store instruction of a warp writes 1 KB
 // contiguous, straight from registers.
+#ifndef SBA_EVAL_MINB
+#define SBA_EVAL_MINB 4
+#endif
 template <int MODEL>
-__global__ void __launch_bounds__(kEvalThreads)
+__global__ void __launch_bounds__(kEvalThreads, SBA_EVAL_MINB)
 eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_i,
             const double* __restrict__ scale_k, const unsigned long long* __restrict__ k_pack,
             const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F,
             double* __restrict__ cost_partial, double* __restrict__ Jq_ambient, unsigned* ticket,
             DeviceScalars* sc) {
   constexpr int NP = MODEL >= 0 ? ModelNumParams(MODEL >= 0 ? MODEL : 0) : 12;
-  const int k = blockIdx.x * kEvalThreads + threadIdx.x;
   double cost = 0.0, fixed = 0.0;
+  // grid-stride: the grid is sized to the machine (a few CTAs per SM), not to the problem, so the
+  // per-block partial sums that the last block folds stay in the hundreds however large the scene is
+  // The streamed per-observation inputs of the NEXT trip are requested before this trip's arithmetic, so
+  // the DRAM latency of the index loads (which the pose / point gathers depend on) is off the chain.
+  const int stride = gridDim.x * kEvalThreads;
+  int k = blockIdx.x * kEvalThreads + threadIdx.x;
+  int i_n = 0, pt_n = 0; double2 xy_n = make_double2(0.0, 0.0); bool act_n = false;
   if (k < S.n_obs) {
-    const int i = S.obs_img[k], pt = S.obs_pt[k];
+    i_n = S.obs_img[k]; pt_n = S.obs_pt[k];
+    xy_n = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k); act_n = S.obs_active[k] != 0;
+  }
+  for (; k < S.n_obs; k += stride) {
+    const int i = i_n, pt = pt_n;
+    const double2 xy = xy_n;
+    const bool active = act_n;
+    if (k + stride < S.n_obs) {
+      i_n = S.obs_img[k + stride]; pt_n = S.obs_pt[k + stride];
+      xy_n = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k + stride); act_n = S.obs_active[k + stride] != 0;
+    }
     const int c = S.img_cam[i];
     const int model = MODEL >= 0 ? MODEL : S.model[c];
     const D4* pp = reinterpret_cast<const D4*>(P.pose + 8 * (size_t)i);
@@ -100,7 +121,6 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
         else { prm[4 * j] = 0.0; prm[4 * j + 1] = 0.0; prm[4 * j + 2] = 0.0; prm[4 * j + 3] = 0.0; }
       }
     }
-    const double2 xy = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k);
     ObsGeom g;
     RotateWithJac(q, t, X, &g, true);
     const double iz = 1.0 / g.p[2];
@@ -126,19 +146,18 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
     const double s = r0 * r0 + r1 * r1;
     double rho[3];
     LossEval(L.type, L.scale, s, rho);
-    const bool active = S.obs_active[k] != 0;
     const int dch = S.dc >> 1;
     D4* Fk = F + FUnit(k, 0, dch);
     D4* Ek = ER + EUnit(k, 0);
     const D4 zero = {0.0, 0.0, 0.0, 0.0};
     if (!active) {
-      fixed = 0.5 * rho[0];
+      fixed += 0.5 * rho[0];
       for (int jj = 0; jj < dch; ++jj) St256(Fk + 32 * jj, zero);
       // the raw residual is still exported for the parity surface; E = 0 keeps it out of every product
       St256(Ek, zero);
       St256(Ek + 32, D4{0.0, 0.0, r0, r1});
     } else {
-      cost = 0.5 * rho[0];
+      cost += 0.5 * rho[0];
       // corrector (ceres corrector.cc)
       double sqrt_rho1 = 1.0, residual_scaling = 1.0, alpha_sq_norm = 0.0;
       if (L.apply) {
@@ -230,9 +249,8 @@ template <int MODEL>
 __global__ void __launch_bounds__(kEvalThreads)
 cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_partial, unsigned* ticket,
             double* out_cost) {
-  const int k = blockIdx.x * kEvalThreads + threadIdx.x;
   double cost = 0.0, fixed = 0.0;
-  if (k < S.n_obs) {
+  for (int k = blockIdx.x * kEvalThreads + threadIdx.x; k < S.n_obs; k += gridDim.x * kEvalThreads) {
     const int i = S.obs_img[k], pt = S.obs_pt[k];
     const int c = S.img_cam[i];
     const int model = MODEL >= 0 ? MODEL : S.model[c];
@@ -261,7 +279,7 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
     const double r0 = x - xy.x, r1 = y - xy.y;
     double rho[3];
     LossEval(L.type, L.scale, r0 * r0 + r1 * r1, rho);
-    if (S.obs_active[k]) cost = 0.5 * rho[0]; else fixed = 0.5 * rho[0];
+    if (S.obs_active[k]) cost += 0.5 * rho[0]; else fixed += 0.5 * rho[0];
   }
   double v[2] = {cost, fixed};
   double* const out[2] = {out_cost, nullptr};
@@ -290,8 +308,11 @@ static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int bl
     case 9: CALL(9); break;  case 10: CALL(10); break; default: CALL(-1); break; \
   }
 
+// CTAs per launch: enough to fill every SM several times over, never more than the problem needs
+static int EvalGrid(const Problem* p) { return std::min(DivUp(p->n_obs, kEvalThreads), p->n_sm * 16); }
+
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate) {
-  const int blocks = DivUp(p->n_obs, kEvalThreads);
+  const int blocks = EvalGrid(p);
   if (blocks > 0) {
 #define CALL(M) LaunchEvalT<M>(p, loss, use_scale, candidate, blocks)
     SBA_MODEL_SWITCH(p->uniform_model, CALL)
@@ -306,7 +327,7 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
 }
 
 int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost) {
-  const int blocks = DivUp(p->n_obs, kEvalThreads);
+  const int blocks = EvalGrid(p);
   if (blocks > 0) {
 #define CALL(M) LaunchCostT<M>(p, loss, candidate, blocks, d_out_cost)
     SBA_MODEL_SWITCH(p->uniform_model, CALL)

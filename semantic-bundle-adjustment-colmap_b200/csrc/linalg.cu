@@ -158,7 +158,7 @@ int SchurMatVec(Problem* p, const double* d_x, double* d_y) {
 // y_p and model_cost_change from y_c (d_yc)
 int BackSubstitute(Problem* p) {
   Expand(p, p->d_yc.p, p->d_xi.p, p->d_xc.p);
-  const int nb = DivUp(p->n_tiles, 4);
+  const int nb = std::min(DivUp(p->n_tiles, 4), p->n_sm * 16);  // grid-stride over warp tiles
   if (nb > 0) {
 #define CALL(DC) backsub_kernel<DC><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p, p->d_tickets.p + 2, &p->d_scalars.p->model_cost_change)
     SBA_DC_SWITCH(p->dc, CALL)
@@ -178,9 +178,9 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
                                                          double* __restrict__ cam2, double* __restrict__ X2,
                                                          int count, double* __restrict__ partial, unsigned* ticket,
                                                          DeviceScalars* sc) {
-  const int t = blockIdx.x * 128 + threadIdx.x;
-  double step2 = 0.0, x2 = 0.0;
-  if (t < count) {
+  double step2_c = 0.0, x2_c = 0.0, step2_p = 0.0, x2_p = 0.0;
+  for (int t = blockIdx.x * 128 + threadIdx.x; t < count; t += gridDim.x * 128) {
+    double step2 = 0.0, x2 = 0.0;
     if (t < S.n_img) {
       const int i = t;
       double rec[8];
@@ -253,10 +253,10 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
         X2[3 * (size_t)q + a] = xn;
       }
     }
+    // camera-side blocks are replicated on every rank, point blocks are sharded: keep their norms apart
+    if (t < S.n_img + S.n_cam) { step2_c += step2; x2_c += x2; } else { step2_p += step2; x2_p += x2; }
   }
-  // camera-side blocks are replicated on every rank, point blocks are sharded: keep their norms apart
-  const bool cam_side = t < S.n_img + S.n_cam;
-  double v[4] = {cam_side ? step2 : 0.0, cam_side ? x2 : 0.0, cam_side ? 0.0 : step2, cam_side ? 0.0 : x2};
+  double v[4] = {step2_c, x2_c, step2_p, x2_p};
   double* const out[4] = {&sc->step2_c, &sc->x2_c, &sc->step2_p, &sc->x2_p};
   GridSum<128, 4>(v, partial, ticket, out);
 }
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
 int ApplyStep(Problem* p) {
   DeviceScalars* sc = p->d_scalars.p;
   const int count = p->n_img + p->n_cam + p->n_pt;
-  const int nb = DivUp(count, 128);
+  const int nb = std::min(DivUp(count, 128), p->n_sm * 16);
   if (nb > 0) {
     apply_step_kernel<<<nb, 128, 0, p->stream>>>(p->Struct(), p->Params(false), p->d_yc.p, p->d_yp.p, p->d_scale_c.p,
                                                  p->d_scale_p.p, p->d_pose2.p, p->d_cam2.p, p->d_X2.p, count,

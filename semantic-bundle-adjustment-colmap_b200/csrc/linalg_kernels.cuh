@@ -269,10 +269,9 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
                                                       const double* __restrict__ yc, double* __restrict__ yp,
                                                       double* __restrict__ partial, unsigned* ticket,
                                                       double* model_cost_change) {
-  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   double acc = 0.0;
-  if (tile < T.n_tiles) {
+  for (int tile = blockIdx.x * 4 + (threadIdx.x >> 5); tile < T.n_tiles; tile += gridDim.x * 4) {
     const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
     if (n <= 32) {
       const bool valid = lane < n;
@@ -304,7 +303,7 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
           m0 -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
           m1 -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
         }
-        acc = m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
+        acc += m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
       }
     } else {
       const int pt = S.obs_pt[s0];

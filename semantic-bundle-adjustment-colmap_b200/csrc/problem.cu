@@ -441,6 +441,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
     return SBA_ERR_NO_DEVICE;
   }
   cudaGetDevice(&p->device);
+  if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
 #define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
   UP(AcquireCtx(p->device, &p->stream, &p->h_scalars));
   std::memset(p->h_scalars, 0, sizeof(DeviceScalars));

@@ -162,6 +162,7 @@ struct Problem {
 
   cudaStream_t stream = nullptr;
   int device = 0;
+  int n_sm = 148;                           // multiprocessors of `device`
   int64_t launches = 0;
   int64_t collectives = 0;
   // extension X1: per-image semantic maps (row-major float), sampled bilinearly at the projection
