@@ -1,0 +1,36 @@
+"""The C++ shim (shim/sba_bundle_adjuster.h) replays the reference's BundleAdjuster test scenarios
+(src/optim/bundle_adjustment_test.cc:186-645) over the mock Reconstruction: host part on CPU, solve part on the GPU."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "semantic-bundle-adjustment-colmap_b200")
+EXE = os.path.join(ROOT, "tests", "shim_test.bin")
+
+
+@pytest.fixture(scope="module")
+def shim_exe(sba):
+    sba.capi.load()  # the C-ABI library must exist (build() made it); never built lazily here
+    src = os.path.join(ROOT, "tests", "shim_test.cpp")
+    hdrs = [os.path.join(PKG, "shim", h) for h in ("sba_bundle_adjuster.h", "mock_reconstruction.h")]
+    lib = os.path.join(PKG, "libsba_b200.so")
+    newest = max(os.path.getmtime(p) for p in [src, lib] + hdrs)
+    if not os.path.exists(EXE) or os.path.getmtime(EXE) < newest:
+        subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror",
+                               "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(PKG, "shim"), src, "-o", EXE,
+                               "-L" + PKG, "-lsba_b200", "-Wl,-rpath,$ORIGIN/../semantic-bundle-adjustment-colmap_b200"])
+    return EXE
+
+
+def test_shim_counts_and_errors(shim_exe):
+    out = subprocess.run([shim_exe, "counts"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+
+
+@pytest.mark.gpu
+def test_shim_solve_on_device(shim_exe):
+    out = subprocess.run([shim_exe, "solve"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "two_view: cost" in out.stdout
