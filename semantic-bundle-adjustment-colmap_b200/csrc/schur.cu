@@ -13,9 +13,9 @@
 //   * "diagonal" contributions F_a^T F_a - H_a W_a^T: image-major chunks of <= 256
 //     observations; lanes own the DC x DC output elements; chunk partials are summed per
 //     image in a fixed order.
-//   * "off-diagonal" contributions -H_a W_b^T: host-built list of observation pairs (a,b)
+//   * "off-diagonal" contributions -H_a W_b^T: device-built list (pairs.cu) of observation pairs (a,b)
 //     of one point with image(a) > image(b), counting-sorted by the (image(a), image(b)) key
-//     and cut into segments of <= kSegPairs pairs.  One warp reduces one segment in registers
+//     and cut into segments of <= PairSegmentSize(dc) pairs (pairs.cu).  One warp reduces one segment in registers
 //     (a warp-level segmented reduction keyed by camera pair); the segment partials of a key
 //     are then summed in a fixed order by the key's single writer.  Bit-reproducible.
 //   * intrinsics shared by several images (and duplicate observations of one point in
@@ -33,7 +33,6 @@ namespace sba {
     case 14: CALL(14); break; default: CALL(18); break;                               \
   }
 
-constexpr int kSegPairs = 32;  // one warp-load of pair ids per segment (schur_pair_segment_kernel)
 template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; };
 
 // W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (observation, slot)
@@ -146,10 +145,10 @@ __global__ void __launch_bounds__(128) schur_diag_finalize_kernel(StructView S, 
 }
 
 // ---- off-diagonal contributions ---------------------------------------------------------
-// one warp per segment (<= kSegPairs pairs of one key): partial[seg] = - sum H_a W_b^T
+// one warp per segment (<= 32 pairs of one key): partial[seg] = - sum H_a W_b^T
 template <int DC>
 __global__ void __launch_bounds__(128) schur_pair_segment_kernel(int n_seg, const int* __restrict__ seg_ptr,
-                                                                 const int* __restrict__ pa, const int* __restrict__ pb,
+                                                                 const unsigned long long* __restrict__ ab,
                                                                  const double* __restrict__ W, const double* __restrict__ H,
                                                                  double* __restrict__ partial) {
   const int seg = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -163,11 +162,12 @@ __global__ void __launch_bounds__(128) schur_pair_segment_kernel(int n_seg, cons
     ja[q] = e / DC; jb[q] = e - ja[q] * DC;
   }
   const int t0 = seg_ptr[seg], t1 = seg_ptr[seg + 1];
-  // a segment holds <= kSegPairs (= 32) pairs: one coalesced index load per lane, then the pair ids are
+  // a segment holds <= 32 pairs (PairSegmentSize, dc > 8): one coalesced index load per lane, then the pair ids are
   // broadcast by shuffle, so the operand loads of several pairs are in flight together instead of
   // each waiting for its own index load.
   const int np = t1 - t0;
-  const int my_a = lane < np ? pa[t0 + lane] : 0, my_b = lane < np ? pb[t0 + lane] : 0;
+  const unsigned long long my_ab = lane < np ? ab[t0 + lane] : 0ull;
+  const int my_a = (int)(my_ab >> 32), my_b = (int)(my_ab & 0xffffffffull);
 #pragma unroll 4
   for (int t = 0; t < np; ++t) {
     const size_t a = (size_t)__shfl_sync(0xffffffffu, my_a, t) * DC, b = (size_t)__shfl_sync(0xffffffffu, my_b, t) * DC;
@@ -206,6 +206,213 @@ __global__ void __launch_bounds__(128) schur_pair_emit_kernel(StructView S, int 
     // duplicate-observation keys (same image) add on top of the chunk result -> atomics
     const bool atomic = same || (sink.shared_intr && (ja >= 6 || jb >= 6));
     Emit(sink, SlotCol(S, gi, ci, ja), SlotCol(S, gj, cj, jb), a, same, atomic);
+  }
+}
+
+// ---- lane-per-unit kernels (DC <= 8: const intrinsics / f,k free -- the C1..C3 regimes) --------------------------
+// The kernels above spread the DC x DC outputs of ONE observation / pair over the lanes of a warp; with DC = 6 that
+// keeps 36 of 64 lane-slots busy and spends most instructions on addressing.  Here a lane owns a whole observation
+// (or pair): it loads its records with wide accesses, forms the full block in registers, and the warp pays ONE
+// transposing reduction through shared memory per 32 observations (per <= 128 pairs).  Fixed summation order.
+
+template <int DC> struct ObsLane {
+  static constexpr int CH = DC * 3 / 2;                 // 16 B units per W / H row
+  static constexpr int RU = (CH & 1) ? CH : CH + 1;     // padded row stride in 16 B units (odd)
+  static constexpr int NT = DC * (DC + 1) / 2;
+  static constexpr size_t kStage = (size_t)256 * 2 * RU * 16, kRed = (size_t)(NT * 256 + NT * 8) * 8;
+  static constexpr size_t kSmem = kStage > kRed ? kStage : kRed;
+};
+
+// W_a, H_a and the diagonal contribution F_a^T F_a - H_a W_a^T of every observation of one image chunk.
+// partial[ch][e], e over the lower triangle (ja >= jb, e = ja (ja + 1) / 2 + jb).
+template <int DC>
+__global__ void __launch_bounds__(256) schur_obs_lane_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
+                                                             const D4* __restrict__ F, const double* __restrict__ Cinv,
+                                                             double* __restrict__ W, double* __restrict__ H,
+                                                             double* __restrict__ partial) {
+  constexpr int NT = DC * (DC + 1) / 2, DH = DC / 2;
+  constexpr int CH = ObsLane<DC>::CH, RU = ObsLane<DC>::RU;
+  extern __shared__ __align__(16) double sm[];  // W/H staging [2][256][RU x 16 B]; then [NT][256] blocks + [NT][8] partials
+  double* stage = sm;
+  double* part = sm + NT * 256;
+  const int ch = blockIdx.x, t = threadIdx.x, lane = t & 31;
+  const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
+  double v[NT];
+#pragma unroll
+  for (int e = 0; e < NT; ++e) v[e] = 0.0;
+  int a = -1;
+  if (t < n) {
+    a = C.cam_order[s0 + t];
+    double2 f[DC];
+#pragma unroll
+    for (int jj = 0; jj < DH; ++jj) {
+      const D4 u = Ld256(F + FUnit(a, jj, DH));
+      f[2 * jj] = make_double2(u.x, u.y); f[2 * jj + 1] = make_double2(u.z, u.w);
+    }
+    const D4 ea = Ld256(ER + EUnit(a, 0));
+    const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];
+    const double E[6] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y};
+    const int po = S.p_off[S.obs_pt[a]];
+    double ci[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (po >= 0) {
+      const double2* cp = reinterpret_cast<const double2*>(Cinv + 6 * (size_t)po);
+      const double2 c0 = cp[0], c1 = cp[1], c2 = cp[2];
+      ci[0] = c0.x; ci[1] = c0.y; ci[2] = c1.x; ci[3] = c1.y; ci[4] = c2.x; ci[5] = c2.y;
+    }
+    double w[DC][3], h[DC][3];
+#pragma unroll
+    for (int j = 0; j < DC; ++j) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) w[j][c] = f[j].x * E[c] + f[j].y * E[3 + c];
+      Sym3Mul(ci, w[j], h[j]);
+    }
+    // stage the two rows in shared memory (row stride = an odd number of 16 B units: conflict-free 128-bit stores);
+    // the warp writes them out below with consecutive lanes on consecutive 16 B chunks of a row
+    double2* ws = reinterpret_cast<double2*>(stage) + (size_t)t * RU;  // [row][thread][RU]
+#pragma unroll
+    for (int q = 0; q < CH; ++q) {
+      ws[q] = make_double2((&w[0][0])[2 * q], (&w[0][0])[2 * q + 1]);
+      ws[256 * RU + q] = make_double2((&h[0][0])[2 * q], (&h[0][0])[2 * q + 1]);
+    }
+#pragma unroll
+    for (int ja = 0; ja < DC; ++ja)
+#pragma unroll
+      for (int jb = 0; jb <= ja; ++jb)
+        v[ja * (ja + 1) / 2 + jb] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y) -
+                                    (h[ja][0] * w[jb][0] + h[ja][1] * w[jb][1] + h[ja][2] * w[jb][2]);
+  }
+  __syncwarp();
+  {  // copy-out of this warp's 32 x 2 rows: chunk k -> observation k / (2 CH), row (k / CH) & 1, 16 B unit k % CH
+    const double2* src = reinterpret_cast<const double2*>(stage) + (size_t)(t & ~31) * RU;
+#pragma unroll
+    for (int i = 0; i < 2 * CH; ++i) {
+      const int k = lane + 32 * i;
+      const int o = k / (2 * CH), rem = k - o * (2 * CH), row = rem / CH, c = rem - row * CH;
+      const int ao = __shfl_sync(0xffffffffu, a, o);
+      if (ao >= 0) reinterpret_cast<double2*>((row ? H : W) + (size_t)ao * DC * 3)[c] = src[(size_t)(row * 256 + o) * RU + c];
+    }
+  }
+  __syncthreads();  // staging area is reused by the reduction
+#pragma unroll
+  for (int e = 0; e < NT; ++e) sm[e * 256 + t] = v[e];
+  __syncthreads();
+  for (int k = t; k < NT * 8; k += 256) {  // task (e, warp): 32 values; the rotation keeps the 16 lanes of a phase on 16 banks
+    const int e = k >> 3, wq = k & 7;
+    const double* src = sm + e * 256 + wq * 32;
+    const int rot = wq + 8 * (e & 1);
+    double acc = 0.0;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) acc += src[(j + rot) & 31];
+    part[k] = acc;
+  }
+  __syncthreads();
+  if (t < NT) {
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += part[t * 8 + i];
+    partial[(size_t)ch * NT + t] = acc;
+  }
+}
+
+template <int DC>
+__global__ void __launch_bounds__(64) schur_diag_finalize_tri_kernel(StructView S, ChunkView C, const double* __restrict__ partial,
+                                                                     Sink sink) {
+  constexpr int NT = DC * (DC + 1) / 2;
+  const int i = blockIdx.x;
+  const int c = S.img_cam[i];
+  const int c0 = C.img_chunk_ptr[i], c1 = C.img_chunk_ptr[i + 1];
+  if (c0 == c1) return;
+  for (int e = threadIdx.x; e < NT; e += 64) {
+    double a = 0.0;
+    for (int ch = c0; ch < c1; ++ch) a += partial[(size_t)ch * NT + e];
+    int ja = 0;
+    while ((ja + 1) * (ja + 2) / 2 <= e) ++ja;
+    const int jb = e - ja * (ja + 1) / 2;
+    int row = SlotCol(S, i, c, ja), col = SlotCol(S, i, c, jb);
+    if (row < col) { const int x = row; row = col; col = x; }  // the block is symmetric: store its lower image
+    const bool atomic = sink.shared_intr && (ja >= 6 || jb >= 6);
+    Emit(sink, row, col, a, true, atomic);
+  }
+}
+
+// One warp per segment (<= 128 pairs of one key).  G lanes share a pair (G = 1: the lane holds the whole
+// DC x DC block; G = 2: half of its rows), so a lane carries RPL x DC accumulators over its <= 4 pairs.
+// The H_a / W_b rows of the 32 / G pairs of one trip are gathered by the whole warp with 16-byte cp.async
+// (consecutive lanes on consecutive chunks of a row: ~5 cache lines per instruction instead of 32), then every
+// lane reads its own two rows from shared memory with conflict-free 128-bit loads.
+template <int DC> struct PairLane {
+  static constexpr int G = DC > 6 ? 2 : 1, RPL = DC / G, PPI = 32 / G, NE = DC * DC, LD = PPI + 1;
+  static constexpr int CH = DC * 3 / 2, RU = (CH & 1) ? CH : CH + 1;
+  static constexpr int kStageD = 2 * PPI * RU * 2, kRedD = NE * LD;        // doubles
+  static constexpr int kWarpD = kStageD > kRedD ? kStageD : kRedD;
+};
+
+__device__ __forceinline__ void CpAsync16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+template <int DC>
+__global__ void __launch_bounds__(128, 4) schur_pair_lane_kernel(int n_seg, const int* __restrict__ seg_ptr,
+                                                              const unsigned long long* __restrict__ ab,
+                                                              const double* __restrict__ W, const double* __restrict__ H,
+                                                              double* __restrict__ partial) {
+  using P = PairLane<DC>;
+  constexpr int G = P::G, RPL = P::RPL, PPI = P::PPI, NE = P::NE, LD = P::LD, CH = P::CH, RU = P::RU;
+  __shared__ __align__(16) double smem[4][P::kWarpD];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int seg = blockIdx.x * 4 + warp;
+  if (seg >= n_seg) return;  // warps are independent (only __syncwarp below)
+  const int slot = lane / G, rg = lane % G;
+  const int t0 = seg_ptr[seg], np = seg_ptr[seg + 1] - t0;
+  double* my = smem[warp];
+  double2* st = reinterpret_cast<double2*>(my);  // [row 0: H_a | row 1: W_b][PPI][RU]
+  double acc[RPL][DC];
+#pragma unroll
+  for (int r = 0; r < RPL; ++r)
+#pragma unroll
+    for (int c = 0; c < DC; ++c) acc[r][c] = 0.0;
+  unsigned long long nxt = slot < np ? ab[t0 + slot] : ~0ull;
+  for (int base = 0; base < np; base += PPI) {
+    const unsigned long long cur = nxt;
+    nxt = (base + PPI + slot < np) ? ab[t0 + base + PPI + slot] : ~0ull;  // next trip's pair ids in flight
+    const int a = (int)(cur >> 32), b = (int)(cur & 0xffffffffull);      // -1 / -1 past the end of the segment
+#pragma unroll
+    for (int i = 0; i < 2 * PPI * CH / 32; ++i) {
+      const int k = lane + 32 * i;
+      const int row = k / (PPI * CH), rem = k - row * (PPI * CH), o = rem / CH, c = rem - o * CH;
+      const int src = __shfl_sync(0xffffffffu, row ? b : a, o * G);
+      if (src >= 0) CpAsync16(st + (size_t)(row * PPI + o) * RU + c, (row ? W : H) + (size_t)src * DC * 3 + 2 * c);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    if (a >= 0) {
+      const double2* hp = st + (size_t)slot * RU + rg * (RPL * 3 / 2);
+      const double2* wp = st + (size_t)(PPI + slot) * RU;
+      double h[RPL * 3], w[DC * 3];
+#pragma unroll
+      for (int q = 0; q < RPL * 3 / 2; ++q) { const double2 x = hp[q]; h[2 * q] = x.x; h[2 * q + 1] = x.y; }
+#pragma unroll
+      for (int q = 0; q < DC * 3 / 2; ++q) { const double2 x = wp[q]; w[2 * q] = x.x; w[2 * q + 1] = x.y; }
+#pragma unroll
+      for (int r = 0; r < RPL; ++r)
+#pragma unroll
+        for (int c = 0; c < DC; ++c)
+          acc[r][c] -= h[3 * r] * w[3 * c] + h[3 * r + 1] * w[3 * c + 1] + h[3 * r + 2] * w[3 * c + 2];
+    }
+    __syncwarp();  // the staging rows are overwritten by the next trip (and by the reduction)
+  }
+#pragma unroll
+  for (int r = 0; r < RPL; ++r)
+#pragma unroll
+    for (int c = 0; c < DC; ++c) my[((rg * RPL + r) * DC + c) * LD + slot] = acc[r][c];
+  __syncwarp();
+  for (int e = lane; e < NE; e += 32) {
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < PPI; ++j) s += my[e * LD + j];
+    partial[(size_t)seg * NE + e] = s;
   }
 }
 
@@ -258,121 +465,6 @@ __global__ void __launch_bounds__(64) invert_blocks_kernel(int n_blk, const int*
   }
 }
 
-// ---- host: pair lists --------------------------------------------------------------------
-// dense == true : every pair of observations of one point in different images (key = image pair,
-//                 larger image first) plus duplicate observations inside one image.
-// dense == false: only what SCHUR_JACOBI needs beyond the per-observation diagonal terms:
-//                 duplicates inside one image, and -- when intrinsics are shared -- all pairs
-//                 whose two images use the same camera (camera x camera block only).
-// Pairs are counting-sorted by key (stable in point order) and cut into <= kSegPairs segments.
-int BuildPairLists(Problem* p, bool dense) {
-  PairList& L = dense ? p->pairs_dense : p->pairs_diag;
-  if (L.built) return SBA_OK;
-  HostTimer tm("pair lists");
-  const int n_pt = p->n_pt, n_img = p->n_img;
-  const std::vector<int>& img = p->h_obs_img;
-  const std::vector<int>& pt_ptr = p->h_pt_ptr;
-  // which points can contribute at all
-  bool any = dense;
-  std::vector<uint8_t> has_dup(n_pt, 0);
-  {
-    std::vector<int> stamp(std::max(1, n_img), -1);
-    for (int q = 0; q < n_pt; ++q) {
-      if (p->h_p_off[q] < 0) continue;
-      for (int s = pt_ptr[q]; s < pt_ptr[q + 1]; ++s) {
-        if (stamp[img[s]] == q) { has_dup[q] = 1; any = true; }
-        stamp[img[s]] = q;
-      }
-    }
-  }
-  const bool shared = !dense && p->shared_intrinsics;
-  if (shared) any = true;
-  tm.Lap("duplicates");
-  // The key (image(a), image(b)) is owned by image(a): every image enumerates, over its own observations in
-  // image-major order, the partner observations of the same point and groups them by image(b) with a local
-  // counting sort.  Images are independent, so the enumeration runs on all host threads; concatenating the
-  // per-image results in image order IS the key-sorted list, and the order inside a key (point order, then
-  // partner order) does not depend on the thread count -- the reductions stay bit-reproducible.
-  struct Part { std::vector<int> a, b, key_j, key_n; };
-  std::vector<Part> parts(std::max(1, n_img));
-  if (any && p->n_obs > 0) {
-    ParallelFor(n_img, [&](int i) {
-      Part& P = parts[i];
-      const int s0 = p->h_img_ptr[i], s1 = p->h_img_ptr[i + 1];
-      if (s0 == s1) return;
-      const int ci = p->h_img_cam[i];
-      std::vector<int> ta, tb, tj;
-      for (int pos = s0; pos < s1; ++pos) {
-        const int s = p->h_cam_order[pos];
-        const int q = p->h_obs_pt[s];
-        if (p->h_p_off[q] < 0) continue;               // constant point: E = 0
-        if (!dense && !shared && !has_dup[q]) continue;
-        for (int t = pt_ptr[q]; t < pt_ptr[q + 1]; ++t) {
-          const int j = img[t];
-          if (t == s || j > i) continue;                // the partner's own visit handles image(b) > image(a)
-          if (j != i && !dense) {
-            if (!shared) continue;
-            if (p->h_img_cam[j] != ci || p->h_k_dim[ci] <= 0) continue;
-          }
-          ta.push_back(s); tb.push_back(t); tj.push_back(j);
-        }
-      }
-      if (ta.empty()) return;
-      std::vector<int> cnt(i + 2, 0);                   // partner images are <= i
-      for (int j : tj) cnt[j + 1]++;
-      for (int j = 0; j <= i; ++j) {
-        if (cnt[j + 1] > 0) { P.key_j.push_back(j); P.key_n.push_back(cnt[j + 1]); }
-        cnt[j + 1] += cnt[j];
-      }
-      P.a.resize(ta.size()); P.b.resize(ta.size());
-      for (size_t e = 0; e < ta.size(); ++e) { const int pos = cnt[tj[e]]++; P.a[pos] = ta[e]; P.b[pos] = tb[e]; }
-    });
-  }
-  tm.Lap("enumerate + sort");
-  size_t n_pairs = 0, n_keys = 0;
-  std::vector<size_t> pair_off(n_img + 1, 0), key_off(n_img + 1, 0);
-  for (int i = 0; i < n_img; ++i) {
-    pair_off[i] = n_pairs; key_off[i] = n_keys;
-    n_pairs += parts[i].a.size(); n_keys += parts[i].key_j.size();
-  }
-  pair_off[n_img] = n_pairs; key_off[n_img] = n_keys;
-  std::vector<int> pa(n_pairs), pb(n_pairs), key_ptr(n_keys + 1), key_gi(n_keys), key_gj(n_keys);
-  ParallelFor(n_img, [&](int i) {
-    const Part& P = parts[i];
-    if (P.a.empty()) return;
-    std::copy(P.a.begin(), P.a.end(), pa.begin() + pair_off[i]);
-    std::copy(P.b.begin(), P.b.end(), pb.begin() + pair_off[i]);
-    size_t at = pair_off[i];
-    for (size_t k = 0; k < P.key_j.size(); ++k) {
-      key_ptr[key_off[i] + k] = (int)at; key_gi[key_off[i] + k] = i; key_gj[key_off[i] + k] = P.key_j[k];
-      at += P.key_n[k];
-    }
-  });
-  key_ptr[n_keys] = (int)n_pairs;
-  // segments
-  std::vector<int> seg_ptr, key_seg_ptr;
-  seg_ptr.reserve(n_pairs / kSegPairs + n_keys + 1); key_seg_ptr.reserve(n_keys + 1);
-  for (size_t k = 0; k < n_keys; ++k) {
-    key_seg_ptr.push_back((int)seg_ptr.size());
-    for (int s = key_ptr[k]; s < key_ptr[k + 1]; s += kSegPairs) seg_ptr.push_back(s);
-  }
-  key_seg_ptr.push_back((int)seg_ptr.size());
-  L.n_seg = (int)seg_ptr.size();
-  seg_ptr.push_back((int)n_pairs);
-  L.n_keys = (int)n_keys;
-  L.n_pairs = (int64_t)n_pairs;
-  tm.Lap("merge + segments");
-  cudaStream_t st = p->stream;
-  SBA_CUDA(L.seg_ptr.Upload(seg_ptr, st)); SBA_CUDA(L.key_seg_ptr.Upload(key_seg_ptr, st));
-  SBA_CUDA(L.key_gi.Upload(key_gi, st)); SBA_CUDA(L.key_gj.Upload(key_gj, st));
-  SBA_CUDA(L.a.Upload(pa, st)); SBA_CUDA(L.b.Upload(pb, st));
-  SBA_CUDA(L.partial.Alloc((size_t)std::max(1, L.n_seg) * p->dc * p->dc));
-  SBA_CUDA(cudaStreamSynchronize(st));
-  L.built = true;
-  tm.Lap("upload");
-  return SBA_OK;
-}
-
 static int EnsureBlockStorage(Problem* p) {
   if (p->d_blk_moff.p) return SBA_OK;
   std::vector<int> moff(p->n_blk + 1, 0);
@@ -385,12 +477,37 @@ static int EnsureBlockStorage(Problem* p) {
 }
 
 // W/H pass + diagonal chunks + pair segments into `sink`
+template <int DC>
+static cudaError_t AccumulateLane(Problem* p, const PairList& L, const Sink& sink) {
+  constexpr size_t smem = ObsLane<DC>::kSmem;
+  static bool attr_set[64] = {};
+  if (!attr_set[p->device & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(schur_obs_lane_kernel<DC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set[p->device & 63] = true;
+  }
+  cudaStream_t st = p->stream;
+  schur_obs_lane_kernel<DC><<<p->n_chunks, 256, smem, st>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p, p->d_Cinv.p,
+                                                            p->d_W.p, p->d_H.p, p->d_chunk_block.p);
+  schur_diag_finalize_tri_kernel<DC><<<p->n_img, 64, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);
+  p->launches += 2;
+  if (L.n_seg > 0) {
+    schur_pair_lane_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.ab.p, p->d_W.p, p->d_H.p, L.partial.p);
+    schur_pair_emit_kernel<DC><<<DivUp(L.n_keys, 4), 128, 0, st>>>(p->Struct(), L.n_keys, L.key_seg_ptr.p, L.key_gi.p,
+                                                                  L.key_gj.p, L.partial.p, sink);
+    p->launches += 2;
+  }
+  return cudaGetLastError();
+}
+
 static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
   const int dc = p->dc;
   cudaStream_t st = p->stream;
   if (p->n_obs == 0) return SBA_OK;
   SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * dc * 3)); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * dc * 3));
   SBA_CUDA(p->d_chunk_block.Alloc((size_t)std::max(1, p->n_chunks) * dc * dc));
+  if (dc == 6) { SBA_CUDA(AccumulateLane<6>(p, L, sink)); return SBA_OK; }
+  if (dc == 8) { SBA_CUDA(AccumulateLane<8>(p, L, sink)); return SBA_OK; }
 #define CALL(DC)                                                                                                          \
   do {                                                                                                                    \
     schur_wh_kernel<DC><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, \
@@ -399,14 +516,16 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
     schur_diag_finalize_kernel<DC><<<p->n_img, 128, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);          \
     p->launches += 3;                                                                                                     \
     if (L.n_seg > 0) {                                                                                                    \
-      schur_pair_segment_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.a.p, L.b.p, p->d_W.p,       \
+      schur_pair_segment_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.ab.p, p->d_W.p,             \
                                                                       p->d_H.p, L.partial.p);                             \
       schur_pair_emit_kernel<DC><<<DivUp(L.n_keys, 4), 128, 0, st>>>(p->Struct(), L.n_keys, L.key_seg_ptr.p, L.key_gi.p,   \
                                                                     L.key_gj.p, L.partial.p, sink);                       \
       p->launches += 2;                                                                                                   \
     }                                                                                                                     \
   } while (0)
-  SBA_DC_SWITCH(dc, CALL)
+  switch (dc) {
+    case 10: CALL(10); break; case 14: CALL(14); break; default: CALL(18); break;
+  }
 #undef CALL
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;

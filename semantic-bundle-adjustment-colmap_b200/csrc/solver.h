@@ -81,9 +81,10 @@ class Comm;  // NCCL wrapper (comm.cu)
 
 // pairs (a,b) of observations of one point, sorted by (image(a), image(b)) key, in segments
 struct PairList {
-  DevBuf<int> seg_ptr, key_seg_ptr, key_gi, key_gj, a, b;
+  DevBuf<int> seg_ptr, key_seg_ptr, key_gi, key_gj;
+  DevBuf<unsigned long long> ab;  // packed pair: a in the high word, b in the low word (pairs.cu)
   DevBuf<double> partial;  // [n_seg*dc*dc]
-  int n_seg = 0, n_keys = 0;
+  int n_seg = 0, n_keys = 0, seg_pairs = 32;
   int64_t n_pairs = 0;
   bool built = false;
 };
@@ -205,8 +206,11 @@ int ModelCostChange(Problem* p);
 int ApplyStep(Problem* p);
 int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase, bool sync);
 int AllReduceSum(Problem* p, double* d_buf, size_t n);
-// schur.cu
+// pairs.cu
 int BuildPairLists(Problem* p, bool dense);
+// pairs per segment: the lane-per-pair kernels (dc <= 8) amortise one reduction over 4 pairs per lane
+inline int PairSegmentSize(int dc) { return dc <= 8 ? 128 : 32; }
+// schur.cu
 int BuildDenseSchur(Problem* p);
 int BuildSchurJacobi(Problem* p);
 // cholesky.cu
