@@ -226,6 +226,11 @@ int sba_set_device(int32_t device);
  * handle solvable again.  The reference's BundleAdjuster is one-shot (bundle_adjustment.cc:260);
  * this exists so that a benchmark can time repeated solves with all inputs already in HBM. */
 int sba_reset(sba_handle* h);
+/* Page-locked host memory for the caller's input arrays (cudaHostAlloc).  Arrays that live here are copied to the
+ * device by DMA straight from the caller's buffer; pageable arrays are staged through the library's own pinned
+ * buffers first.  Purely an optimisation: every entry point accepts either kind.  NULL when no device / no memory. */
+void* sba_host_alloc(uint64_t bytes);
+void sba_host_free(void* ptr);
 const char* sba_last_error(void);
 const char* sba_version(void);
 int sba_device_count(void);

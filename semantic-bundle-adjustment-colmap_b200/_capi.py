@@ -131,6 +131,8 @@ SYMBOLS = {
     "sba_destroy": (None, [C.c_void_p]),
     "sba_set_device": (C.c_int, [C.c_int32]),
     "sba_reset": (C.c_int, [C.c_void_p]),
+    "sba_host_alloc": (C.c_void_p, [C.c_uint64]),
+    "sba_host_free": (None, [C.c_void_p]),
     "sba_last_error": (C.c_char_p, []),
     "sba_version": (C.c_char_p, []),
     "sba_device_count": (C.c_int, []),
@@ -198,3 +200,28 @@ def default_solver_options():
     o = SolverOptions()
     load().sba_default_solver_options(C.byref(o))
     return o
+
+
+class PinnedArena:
+    """numpy arrays backed by page-locked host memory (sba_host_alloc): inputs kept here reach the device by DMA
+    straight from the caller's buffer.  Keep the arena alive as long as the arrays are in use."""
+
+    def __init__(self):
+        self._blocks = []
+
+    def copy(self, a):
+        a = np.ascontiguousarray(a)
+        if a.nbytes == 0:
+            return a
+        p = load().sba_host_alloc(a.nbytes)
+        if not p:
+            raise SbaError(3, (load().sba_last_error() or b"").decode())
+        self._blocks.append(p)
+        out = np.frombuffer((C.c_char * a.nbytes).from_address(p), dtype=a.dtype).reshape(a.shape)
+        out[...] = a
+        return out
+
+    def close(self):
+        for p in self._blocks:
+            load().sba_host_free(p)
+        self._blocks = []

@@ -71,6 +71,17 @@ int sba_create(const sba_problem_desc* desc, sba_handle** out) {
   return SBA_OK;
 }
 
+void* sba_host_alloc(uint64_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    SetError(SBA_ERR_CUDA, "cudaHostAlloc failed (no device or out of page-locked memory)");
+    return nullptr;
+  }
+  return p;
+}
+void sba_host_free(void* ptr) { if (ptr) cudaFreeHost(ptr); }
+
 void sba_destroy(sba_handle* h) {
   if (!h) return;
   delete h->p;
@@ -114,6 +125,7 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
   SBA_CUDA(cudaMemcpyAsync(p->h_scalars, p->d_scalars.p, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, st));
   SBA_CUDA(cudaStreamSynchronize(st));
   if (cost) *cost = p->h_scalars->cost + p->h_scalars->fixed_cost;
+  if ((rc = FetchHostOrder(p))) return rc;
   auto slot = [&](int k, int j, double* d0, double* d1) {  // (d r0 / d s_j, d r1 / d s_j)
     const D4& u = F[FUnit(k, j >> 1, dc / 2)];
     if (j & 1) { *d0 = u.z; *d1 = u.w; } else { *d0 = u.x; *d1 = u.y; }

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <atomic>
+#include <condition_variable>
 #include <mutex>
 #include <numeric>
 #include <thread>
@@ -40,15 +41,73 @@ int HostThreads() {
   }();
   return n;
 }
+// Persistent worker pool: the set-up passes below are a few hundred microseconds each, so spawning threads per
+// pass (tens of microseconds per thread) would eat the gain.  Workers live for the life of the process.
+namespace {
+class Pool {
+ public:
+  explicit Pool(int n_workers) {
+    for (int i = 0; i < n_workers; ++i) std::thread([this] { Loop(); }).detach();
+  }
+  void Run(int n_tasks, const std::function<void(int)>& fn) {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      fn_ = &fn; n_tasks_ = n_tasks; next_.store(0); active_ = 0; ++gen_;
+    }
+    cv_.notify_all();
+    for (int t; (t = next_.fetch_add(1)) < n_tasks;) fn(t);
+    std::unique_lock<std::mutex> lk(mu_);
+    fn_ = nullptr;                                   // late wakers find no job
+    done_.wait(lk, [this] { return active_ == 0; });
+  }
+ private:
+  void Loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      const std::function<void(int)>* fn;
+      int n;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (!fn_) continue;
+        fn = fn_; n = n_tasks_; ++active_;
+      }
+      for (int t; (t = next_.fetch_add(1)) < n;) (*fn)(t);
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        --active_;
+      }
+      done_.notify_all();
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_, done_;
+  const std::function<void(int)>* fn_ = nullptr;
+  int n_tasks_ = 0, active_ = 0;
+  uint64_t gen_ = 0;
+  std::atomic<int> next_{0};
+};
+std::mutex g_pool_mu;  // one parallel pass at a time per process; a second caller runs its pass inline
+}  // namespace
 void ParallelFor(int n_tasks, const std::function<void(int)>& fn) {
   const int nt = std::min(HostThreads(), n_tasks);
-  if (nt <= 1) { for (int t = 0; t < n_tasks; ++t) fn(t); return; }
-  std::atomic<int> next(0);
-  auto work = [&]() { for (int t; (t = next.fetch_add(1)) < n_tasks;) fn(t); };
-  std::vector<std::thread> th;
-  for (int i = 1; i < nt; ++i) th.emplace_back(work);
-  work();
-  for (auto& t : th) t.join();
+  std::unique_lock<std::mutex> lk(g_pool_mu, std::try_to_lock);
+  if (nt <= 1 || !lk.owns_lock()) { for (int t = 0; t < n_tasks; ++t) fn(t); return; }
+  static Pool* pool = new Pool(HostThreads() - 1);  // never destroyed: workers may outlive static destruction
+  pool->Run(n_tasks, fn);
+}
+// [begin, end) of slice `t` of `n` items cut into `parts` contiguous slices
+static inline void Slice(int64_t n, int parts, int t, int64_t* b, int64_t* e) { *b = n * t / parts; *e = n * (t + 1) / parts; }
+
+// Side stream for the large map upload, so that its DMA overlaps the host set-up and the small uploads.
+static cudaStream_t CopyStream() {
+  static cudaStream_t streams[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!streams[dev]) cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking);
+  return streams[dev];
 }
 
 cudaStream_t AllocStream() {
@@ -106,6 +165,12 @@ StageBufs g_stage;
 }  // namespace
 cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st) {
   if (bytes < 4 * kStageChunk) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  {  // a caller that keeps its arrays in page-locked memory (sba_host_alloc, cudaHostRegister) needs no staging
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost)
+      return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    cudaGetLastError();
+  }
   std::lock_guard<std::mutex> lk(g_stage_mu);
   if (!g_stage.ok) {
     for (int t = 0; t < kStageThreads; ++t)
@@ -197,11 +262,19 @@ static int Validate(const sba_problem_desc* d) {
     if (d->image_camera[i] < 0 || d->image_camera[i] >= d->num_cameras) {
       SetError(SBA_ERR_INVALID_ARGUMENT, "image_camera out of range"); return SBA_ERR_INVALID_ARGUMENT;
     }
-  for (int64_t k = 0; k < d->num_observations; ++k)
-    if (d->obs_image[k] < 0 || d->obs_image[k] >= d->num_images || d->obs_point[k] < 0 ||
-        d->obs_point[k] >= d->num_points) {
-      SetError(SBA_ERR_INVALID_ARGUMENT, "observation index out of range"); return SBA_ERR_INVALID_ARGUMENT;
-    }
+  {
+    const int64_t n = d->num_observations;
+    const int NT = std::max(1, std::min(HostThreads(), (int)(n / 16384) + 1));
+    std::atomic<int> bad(0);
+    ParallelFor(NT, [&](int t) {
+      int64_t kb, ke; Slice(n, NT, t, &kb, &ke);
+      const unsigned ni = (unsigned)d->num_images, np = (unsigned)d->num_points;
+      int b = 0;
+      for (int64_t k = kb; k < ke; ++k) b |= ((unsigned)d->obs_image[k] >= ni) | ((unsigned)d->obs_point[k] >= np);
+      if (b) bad.store(1);
+    });
+    if (bad.load()) { SetError(SBA_ERR_INVALID_ARGUMENT, "observation index out of range"); return SBA_ERR_INVALID_ARGUMENT; }
+  }
   if (d->shard_count < 0 || (d->shard_count > 0 && (d->shard_rank < 0 || d->shard_rank >= d->shard_count))) {
     SetError(SBA_ERR_INVALID_ARGUMENT, "bad shard_rank / shard_count"); return SBA_ERR_INVALID_ARGUMENT;
   }
@@ -224,9 +297,15 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
   const int64_t n_obs = d.num_observations;
   std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used(n_pt, 0);
   std::vector<int> cam_img_count(n_cam, 0);
-  for (int64_t k = 0; k < n_obs; ++k) {
-    img_used[d.obs_image[k]] = 1; pt_used[d.obs_point[k]] = 1;
-  }
+  const int NT = std::max(1, std::min(HostThreads(), (int)(n_obs / 16384) + 1));
+  // every writer stores the same value 1 into a byte: the passes can share the mark arrays
+  ParallelFor(NT, [&](int t) {
+    int64_t kb, ke; Slice(n_obs, NT, t, &kb, &ke);
+    for (int64_t k = kb; k < ke; ++k) {
+      uint8_t& iu = img_used[d.obs_image[k]]; if (!iu) iu = 1;
+      uint8_t& pu = pt_used[d.obs_point[k]]; if (!pu) pu = 1;
+    }
+  });
   for (int i = 0; i < n_img; ++i) if (img_used[i]) { cam_used[d.image_camera[i]] = 1; cam_img_count[d.image_camera[i]]++; }
   std::memset(&g->counts, 0, sizeof(g->counts));
   sba_summary& s = g->counts;
@@ -275,12 +354,18 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
   }
   g->obs_active.assign(n_obs, 0);
   s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(2 * n_obs);
-  for (int64_t k = 0; k < n_obs; ++k) {
-    const int i = d.obs_image[k], c = d.image_camera[i], p = d.obs_point[k];
-    const bool act = g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off_global[p] >= 0;
-    g->obs_active[k] = act;
-    if (act) s.num_residuals_reduced += 2;
-  }
+  std::vector<int64_t> n_act(NT, 0);
+  ParallelFor(NT, [&](int t) {
+    int64_t kb, ke, na = 0; Slice(n_obs, NT, t, &kb, &ke);
+    for (int64_t k = kb; k < ke; ++k) {
+      const int i = d.obs_image[k], c = d.image_camera[i], p = d.obs_point[k];
+      const bool act = g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off_global[p] >= 0;
+      g->obs_active[k] = act;
+      na += act;
+    }
+    n_act[t] = na;
+  });
+  for (int t = 0; t < NT; ++t) s.num_residuals_reduced += (int)(2 * n_act[t]);
 }
 
 int ProblemCounts(const sba_problem_desc* d, sba_summary* s) {
@@ -320,10 +405,60 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   if (rc) return rc;
   tm.Lap("validate");
   const sba_problem_desc& d = *dp;
+  Problem* p = new Problem();
+  // ---- device first: the label maps (61 MB at C2, 6 GB at C5) start moving on a side stream right away, so their
+  //      DMA runs under the host set-up below instead of after it ----
+  DevBuf<int> raw_img, raw_pt;   // the caller's observation arrays on the device (released after the final sync)
+  DevBuf<double> raw_xy;
+#define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); maps.Join(); cudaStreamSynchronize(CopyStream()); if (p->stream) cudaStreamSynchronize(p->stream); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
+  struct MapUpload {
+    std::thread th;
+    cudaError_t err = cudaSuccess;
+    void Join() { if (th.joinable()) th.join(); }
+    ~MapUpload() { Join(); }
+  } maps;
+  if (!host_only) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+      delete p;
+      SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+      return SBA_ERR_NO_DEVICE;
+    }
+    cudaGetDevice(&p->device);
+    {
+      cudaError_t e = AcquireCtx(p->device, &p->stream, &p->h_scalars);
+      const size_t no = (size_t)std::max<int64_t>(1, d.num_observations);
+      if (e == cudaSuccess) e = raw_img.Alloc(no);
+      if (e == cudaSuccess) e = raw_pt.Alloc(no);
+      if (e == cudaSuccess) e = raw_xy.Alloc(2 * no);
+      if (e == cudaSuccess && d.num_observations > 0) {
+        // the caller's observation arrays go up as they are; the device sorts them (order.cu)
+        e = UploadLarge(raw_pt.p, d.obs_point, no * sizeof(int), p->stream);
+        if (e == cudaSuccess) e = UploadLarge(raw_img.p, d.obs_image, no * sizeof(int), p->stream);
+        if (e == cudaSuccess) e = UploadLarge(raw_xy.p, d.obs_xy, 2 * no * sizeof(double), p->stream);
+      }
+      if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("observation upload: ") + cudaGetErrorString(e)); delete p; return SBA_ERR_CUDA; }
+      std::memset(p->h_scalars, 0, sizeof(DeviceScalars));
+    }
+    if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) {
+      const size_t n_map = (size_t)d.num_images * d.sem_height * d.sem_width;
+      cudaError_t e = p->d_sem_maps.Alloc(n_map);
+      if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("label maps: ") + cudaGetErrorString(e)); delete p; return SBA_ERR_CUDA; }
+      p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
+      const int dev = p->device;
+      float* dst = p->d_sem_maps.p;
+      const float* src = d.sem_maps;
+      cudaStream_t cs = CopyStream();
+      maps.th = std::thread([&maps, dev, dst, src, n_map, cs] {
+        cudaSetDevice(dev);
+        maps.err = UploadLarge(dst, src, n_map * sizeof(float), cs);
+      });
+    }
+  }
+  tm.Lap("start map upload");
   GlobalStructure g;
   Analyse(d, &g);
   tm.Lap("analyse");
-  Problem* p = new Problem();
   p->counts = g.counts;
   p->n_img = d.num_images; p->n_cam = d.num_cameras;
   p->n_pt_global = d.num_points; p->n_obs_global = d.num_observations;
@@ -342,48 +477,35 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   for (int i = 0; i < p->n_img; ++i) p->h_pose_const[i] = g.col_img[6 * (size_t)i] < 0 ? 1 : 0;
 
   // ---- shard: contiguous global point range balanced by observation count ----
+  // Host: one counting pass by point (worker t owns a contiguous range of points and scans obs_point for them: no
+  // atomics, no per-thread counters) gives the CSR over points, the shard's range and the warp tiles.  The sort itself
+  // -- and every per-observation array -- is made on the DEVICE from the caller's arrays (cub stable radix sort).
   const int n_pt_g = d.num_points;
   const int64_t n_obs_g = d.num_observations;
+  const int NT = std::max(1, std::min(HostThreads(), (int)(n_obs_g / 16384) + 1));
   std::vector<int64_t> prefix(n_pt_g + 1, 0);
-  for (int64_t k = 0; k < n_obs_g; ++k) prefix[d.obs_point[k] + 1]++;
+  ParallelFor(NT, [&](int t) {
+    int64_t qb, qe; Slice(n_pt_g, NT, t, &qb, &qe);
+    int64_t* cnt = prefix.data() + 1;
+    for (int64_t k = 0; k < n_obs_g; ++k) { const int q = d.obs_point[k]; if (q >= qb && q < qe) cnt[q]++; }
+  });
   for (int q = 0; q < n_pt_g; ++q) prefix[q + 1] += prefix[q];
   int p0 = 0, p1 = n_pt_g;
   ShardPointRange(prefix, p->shard_count, p->shard_rank, &p0, &p1);
   p->n_pt = p1 - p0;
   p->n_obs = (int)(prefix[p1] - prefix[p0]);
+  const int64_t obs_base = prefix[p0];
   p->h_pt_local2global.resize(p->n_pt);
   std::iota(p->h_pt_local2global.begin(), p->h_pt_local2global.end(), p0);
-
-  // ---- point-sorted local observations (stable in reference order) ----
   const int n_obs = p->n_obs;
-  p->h_local2ref.resize(n_obs);
-  {
-    std::vector<int64_t> fill(prefix.begin() + p0, prefix.begin() + p1);
-    const int64_t base = prefix[p0];
-    for (int64_t k = 0; k < n_obs_g; ++k) {
-      const int q = d.obs_point[k];
-      if (q < p0 || q >= p1) continue;
-      p->h_local2ref[fill[q - p0]++ - base] = k;
-    }
-  }
-  p->h_obs_img.resize(n_obs); p->h_obs_pt.resize(n_obs);
-  std::vector<double> h_xy((size_t)n_obs * 2);
-  std::vector<uint8_t> h_active(n_obs);
-  for (int k = 0; k < n_obs; ++k) {
-    const int64_t r = p->h_local2ref[k];
-    p->h_obs_img[k] = d.obs_image[r];
-    p->h_obs_pt[k] = d.obs_point[r] - p0;
-    h_xy[2 * (size_t)k] = d.obs_xy[2 * r]; h_xy[2 * (size_t)k + 1] = d.obs_xy[2 * r + 1];
-    h_active[k] = g.obs_active[r];
-  }
   p->h_p_off.assign(p->n_pt, -1);
   p->n_pvar = 0;
   for (int q = 0; q < p->n_pt; ++q) if (g.p_off_global[p0 + q] >= 0) p->h_p_off[q] = p->n_pvar++;
   std::vector<int>& h_pt_ptr = p->h_pt_ptr;
   h_pt_ptr.resize(p->n_pt + 1);
-  for (int q = 0; q <= p->n_pt; ++q) h_pt_ptr[q] = (int)(prefix[p0 + q] - prefix[p0]);
+  for (int q = 0; q <= p->n_pt; ++q) h_pt_ptr[q] = (int)(prefix[p0 + q] - obs_base);
+  tm.Lap("shard + point counts");
 
-  tm.Lap("shard + point sort");
   // ---- warp tiles: whole points packed into <= kTile observations ----
   std::vector<int> tile_start;
   {
@@ -400,15 +522,20 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   }
   p->n_tiles = (int)tile_start.size() - 1;
 
-  // ---- image-major index list + chunks of <= 256 ----
-  std::vector<int>& img_ptr = p->h_img_ptr; std::vector<int>& cam_order = p->h_cam_order;
-  img_ptr.assign(p->n_img + 1, 0); cam_order.resize(n_obs);
-  for (int k = 0; k < n_obs; ++k) img_ptr[p->h_obs_img[k] + 1]++;
-  for (int i = 0; i < p->n_img; ++i) img_ptr[i + 1] += img_ptr[i];
+  // ---- image-major chunks of <= 256: sizes from a counting pass by image over the shard's observations ----
+  std::vector<int>& img_ptr = p->h_img_ptr;
+  img_ptr.assign(p->n_img + 1, 0);
   {
-    std::vector<int> fill(img_ptr.begin(), img_ptr.end() - 1);
-    for (int k = 0; k < n_obs; ++k) cam_order[fill[p->h_obs_img[k]]++] = k;
+    const int NI = std::max(1, std::min(NT, p->n_img));
+    ParallelFor(NI, [&](int t) {
+      int64_t ib, ie; Slice(p->n_img, NI, t, &ib, &ie);
+      for (int64_t k = 0; k < n_obs_g; ++k) {
+        const int i = d.obs_image[k], q = d.obs_point[k];
+        if (i >= ib && i < ie && q >= p0 && q < p1) img_ptr[i + 1]++;
+      }
+    });
   }
+  for (int i = 0; i < p->n_img; ++i) img_ptr[i + 1] += img_ptr[i];
   std::vector<int> chunk_start, chunk_img, img_chunk_ptr(p->n_img + 1, 0);
   for (int i = 0; i < p->n_img; ++i) {
     img_chunk_ptr[i] = (int)chunk_img.size();
@@ -428,51 +555,70 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   std::vector<int> col_blk(std::max(1, p->n_cdim), 0);
   for (int b = 0; b < p->n_blk; ++b)
     for (int j = 0; j < p->h_blk_dim[b]; ++j) col_blk[p->h_blk_off[b] + j] = b;
-
   tm.Lap("tiles + chunks");
   *out = p;
   if (host_only) return SBA_OK;
 
   // ---- device ----
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
-    delete p; *out = nullptr;
-    SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
-    return SBA_ERR_NO_DEVICE;
-  }
-  cudaGetDevice(&p->device);
   if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
-#define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
-  UP(AcquireCtx(p->device, &p->stream, &p->h_scalars));
-  std::memset(p->h_scalars, 0, sizeof(DeviceScalars));
   cudaStream_t st = p->stream;
-  std::vector<double> pose((size_t)p->n_img * 8, 0.0), cam((size_t)p->n_cam * 12, 0.0), X((size_t)p->n_pt * 3);
+  // parameters: one upload into the creation copies, device-to-device into the current / candidate buffers
+  // (these three triples swap pointers during the solve, so they own their memory)
+  std::vector<double> pose((size_t)p->n_img * 8, 0.0), cam((size_t)p->n_cam * 12, 0.0);
   for (int i = 0; i < p->n_img; ++i) {
     for (int j = 0; j < 4; ++j) pose[8 * (size_t)i + j] = d.image_qvec[4 * (size_t)i + j];
     for (int j = 0; j < 3; ++j) pose[8 * (size_t)i + 4 + j] = d.image_tvec[3 * (size_t)i + j];
   }
   for (size_t j = 0; j < cam.size(); ++j) cam[j] = d.camera_params[j];
-  for (int q = 0; q < p->n_pt; ++q)
-    for (int a = 0; a < 3; ++a) X[3 * (size_t)q + a] = d.points[3 * (size_t)(p0 + q) + a];
-  tm.Lap("stream + pinned + pack");
-  UP(p->d_pose.Upload(pose, st)); UP(p->d_cam.Upload(cam, st)); UP(p->d_X.Upload(X, st));
-  UP(p->d_pose2.Upload(pose, st)); UP(p->d_cam2.Upload(cam, st)); UP(p->d_X2.Upload(X, st));
-  UP(p->d_pose0.Upload(pose, st)); UP(p->d_cam0.Upload(cam, st)); UP(p->d_X0.Upload(X, st));
-  UP(p->d_img_cam.Upload(p->h_img_cam, st)); UP(p->d_model.Upload(p->h_model, st));
-  UP(p->d_col_img.Upload(p->h_col_img, st)); UP(p->d_col_cam.Upload(p->h_col_cam, st));
-  UP(p->d_k_cols.Upload(p->h_k_cols, st)); UP(p->d_k_slot.Upload(p->h_k_slot, st)); UP(p->d_k_dim.Upload(p->h_k_dim, st));
-  UP(p->d_p_off.Upload(p->h_p_off, st));
-  UP(p->d_obs_img.Upload(p->h_obs_img, st)); UP(p->d_obs_pt.Upload(p->h_obs_pt, st));
-  UP(p->d_obs_xy.Upload(h_xy, st)); UP(p->d_obs_active.Upload(h_active, st));
-  UP(p->d_pose_const.Upload(p->h_pose_const, st));
-  UP(p->d_tile_start.Upload(tile_start, st));
-  UP(p->d_chunk_start.Upload(chunk_start, st)); UP(p->d_chunk_img.Upload(chunk_img, st));
-  UP(p->d_cam_order.Upload(cam_order, st)); UP(p->d_img_chunk_ptr.Upload(img_chunk_ptr, st));
-  UP(p->d_cam_img_ptr.Upload(cam_img_ptr, st)); UP(p->d_cam_img_list.Upload(cam_img_list, st));
-  UP(p->d_pt_ptr.Upload(h_pt_ptr, st));
-  UP(p->d_blk_off.Upload(p->h_blk_off, st)); UP(p->d_blk_dim.Upload(p->h_blk_dim, st));
-  UP(p->d_col_blk.Upload(col_blk, st));
-  tm.Lap("uploads");
+  const size_t nX = (size_t)std::max(1, p->n_pt) * 3;
+  UP(p->d_pose0.Upload(pose, st)); UP(p->d_cam0.Upload(cam, st));
+  UP(p->d_X0.Alloc(nX));
+  if (p->n_pt > 0) UP(UploadLarge(p->d_X0.p, d.points + 3 * (size_t)p0, (size_t)p->n_pt * 3 * sizeof(double), st));
+  UP(p->d_pose.Alloc(pose.size())); UP(p->d_pose2.Alloc(pose.size()));
+  UP(p->d_cam.Alloc(cam.size())); UP(p->d_cam2.Alloc(cam.size()));
+  UP(p->d_X.Alloc(nX)); UP(p->d_X2.Alloc(nX));
+  for (double* dst : {p->d_pose.p, p->d_pose2.p})
+    if (!pose.empty()) UP(cudaMemcpyAsync(dst, p->d_pose0.p, pose.size() * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  for (double* dst : {p->d_cam.p, p->d_cam2.p})
+    if (!cam.empty()) UP(cudaMemcpyAsync(dst, p->d_cam0.p, cam.size() * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  for (double* dst : {p->d_X.p, p->d_X2.p})
+    if (p->n_pt > 0) UP(cudaMemcpyAsync(dst, p->d_X0.p, (size_t)p->n_pt * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  tm.Lap("parameters");
+
+  // structure arrays: one packed block, one copy
+  std::vector<double> mi((size_t)std::max(1, p->n_img) * 6, 0.0), mk((size_t)std::max(1, p->n_cam) * 12, 0.0);
+  std::vector<unsigned long long> pack(std::max(1, p->n_cam), 0ull);
+  for (size_t j = 0; j < (size_t)p->n_img * 6; ++j) mi[j] = p->h_col_img[j] >= 0 ? 1.0 : 0.0;
+  for (int c = 0; c < p->n_cam; ++c)
+    for (int j = 0; j < p->h_k_dim[c]; ++j) {
+      mk[12 * (size_t)c + j] = p->h_col_cam[12 * (size_t)c + j] >= 0 ? 1.0 : 0.0;
+      pack[c] |= (unsigned long long)(p->h_k_cols[12 * (size_t)c + j] & 15) << (4 * j);
+    }
+  DeviceArena& A = p->arena;
+  const auto s_img_cam = A.Push(p->h_img_cam), s_model = A.Push(p->h_model), s_col_img = A.Push(p->h_col_img),
+             s_col_cam = A.Push(p->h_col_cam), s_k_cols = A.Push(p->h_k_cols), s_k_slot = A.Push(p->h_k_slot),
+             s_k_dim = A.Push(p->h_k_dim), s_p_off = A.Push(p->h_p_off), s_pose_const = A.Push(p->h_pose_const),
+             s_tile = A.Push(tile_start), s_chunk_start = A.Push(chunk_start), s_chunk_img = A.Push(chunk_img),
+             s_img_chunk = A.Push(img_chunk_ptr), s_cam_img_ptr = A.Push(cam_img_ptr), s_cam_img_list = A.Push(cam_img_list),
+             s_pt_ptr = A.Push(h_pt_ptr), s_blk_off = A.Push(p->h_blk_off), s_blk_dim = A.Push(p->h_blk_dim),
+             s_col_blk = A.Push(col_blk), s_mi = A.Push(mi), s_mk = A.Push(mk), s_pack = A.Push(pack);
+  UP(A.Upload(st));
+  A.Bind(&p->d_img_cam, s_img_cam); A.Bind(&p->d_model, s_model); A.Bind(&p->d_col_img, s_col_img);
+  A.Bind(&p->d_col_cam, s_col_cam); A.Bind(&p->d_k_cols, s_k_cols); A.Bind(&p->d_k_slot, s_k_slot);
+  A.Bind(&p->d_k_dim, s_k_dim); A.Bind(&p->d_p_off, s_p_off); A.Bind(&p->d_pose_const, s_pose_const);
+  A.Bind(&p->d_tile_start, s_tile); A.Bind(&p->d_chunk_start, s_chunk_start); A.Bind(&p->d_chunk_img, s_chunk_img);
+  A.Bind(&p->d_img_chunk_ptr, s_img_chunk); A.Bind(&p->d_cam_img_ptr, s_cam_img_ptr);
+  A.Bind(&p->d_cam_img_list, s_cam_img_list); A.Bind(&p->d_pt_ptr, s_pt_ptr); A.Bind(&p->d_blk_off, s_blk_off);
+  A.Bind(&p->d_blk_dim, s_blk_dim); A.Bind(&p->d_col_blk, s_col_blk); A.Bind(&p->d_mask_i, s_mi);
+  A.Bind(&p->d_mask_k, s_mk); A.Bind(&p->d_k_pack, s_pack);
+  tm.Lap("structure block");
+
+  // point-sorted observations and the image-major list, sorted on the device from the raw copies
+  {
+    const int orc = BuildDeviceOrder(p, p0, obs_base, n_obs_g, n_pt_g, raw_img.p, raw_pt.p, raw_xy.p);
+    if (orc) { maps.Join(); cudaStreamSynchronize(CopyStream()); delete p; *out = nullptr; return orc; }
+  }
+  tm.Lap("device order");
   const size_t nc = std::max(1, p->n_cdim), np3 = std::max(1, 3 * p->n_pvar);
   UP(p->d_ER.Alloc(TilePad(std::max(1, n_obs)) * 2)); UP(p->d_F.Alloc(TilePad(std::max(1, n_obs)) * (p->dc / 2)));
   p->n_partial = std::max(std::max(DivUp(std::max(1, n_obs), 128), DivUp(std::max(1, p->n_tiles), 4)),
@@ -480,18 +626,6 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_cost_partial.Alloc(4 * (size_t)p->n_partial));
   UP(p->d_xi.Alloc((size_t)std::max(1, p->n_img) * 6)); UP(p->d_xc.Alloc((size_t)std::max(1, p->n_cam) * 12));
   UP(p->d_scale_i.Alloc((size_t)std::max(1, p->n_img) * 6)); UP(p->d_scale_k.Alloc((size_t)std::max(1, p->n_cam) * 12));
-  {  // 1 / 0 masks of the free slots (the scale of the unscaled evaluation) and the packed slot -> parameter map
-    std::vector<double> mi((size_t)std::max(1, p->n_img) * 6, 0.0), mk((size_t)std::max(1, p->n_cam) * 12, 0.0);
-    std::vector<unsigned long long> pack(std::max(1, p->n_cam), 0ull);
-    for (size_t j = 0; j < (size_t)p->n_img * 6; ++j) mi[j] = p->h_col_img[j] >= 0 ? 1.0 : 0.0;
-    for (int c = 0; c < p->n_cam; ++c)
-      for (int j = 0; j < p->h_k_dim[c]; ++j) {
-        mk[12 * (size_t)c + j] = p->h_col_cam[12 * (size_t)c + j] >= 0 ? 1.0 : 0.0;
-        pack[c] |= (unsigned long long)(p->h_k_cols[12 * (size_t)c + j] & 15) << (4 * j);
-      }
-    UP(p->d_mask_i.Upload(mi, st)); UP(p->d_mask_k.Upload(mk, st)); UP(p->d_k_pack.Upload(pack, st));
-    UP(cudaStreamSynchronize(st));  // the vectors above go out of scope
-  }
   UP(p->d_red.Alloc(2048));
   UP(p->d_scale_c.Alloc(nc)); UP(p->d_scale_p.Alloc(np3));
   UP(p->d_sq_c.Alloc(nc)); UP(p->d_sq_p.Alloc(np3));
@@ -505,12 +639,9 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_scalars.Alloc(1)); UP(p->d_scalars.Zero(st));
   UP(p->d_tickets.Alloc(8)); UP(p->d_tickets.Zero(st));
   tm.Lap("allocs");
-  if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0) {
-    const size_t n_map = (size_t)p->n_img * d.sem_height * d.sem_width;
-    UP(p->d_sem_maps.Alloc(n_map));
-    UP(UploadLarge(p->d_sem_maps.p, d.sem_maps, n_map * sizeof(float), st));
-    p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
-  }
+  maps.Join();  // every chunk of the map upload has been queued on the side stream
+  UP(maps.err);
+  UP(cudaStreamSynchronize(CopyStream()));
   UP(cudaStreamSynchronize(st));
   tm.Lap("maps + sync");
 #undef UP

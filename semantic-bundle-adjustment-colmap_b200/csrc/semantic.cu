@@ -555,6 +555,10 @@ int EvaluateSemanticRows(Problem* p, double* sem_residuals_host) {
   std::vector<double> h(n);
   SBA_CUDA(cudaMemcpyAsync(h.data(), d_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
   SBA_CUDA(cudaStreamSynchronize(p->stream));
+  {
+    const int frc = FetchHostOrder(p);
+    if (frc) return frc;
+  }
   for (int k = 0; k < n; ++k) sem_residuals_host[p->h_local2ref[k]] = h[k];
   return SBA_OK;
 }

@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstring>
 #include <vector>
 
@@ -26,10 +27,12 @@ struct DevBuf {
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
   ~DevBuf() { Free(); }
+  bool owned = true;  // false: a view into a DeviceArena block
   void Free() {
-    if (p) cudaFreeAsync(p, AllocStream());
-    p = nullptr; n = 0;
+    if (p && owned) cudaFreeAsync(p, AllocStream());
+    p = nullptr; n = 0; owned = true;
   }
+  void View(T* ptr, size_t count) { Free(); p = ptr; n = count; owned = false; }
   cudaError_t Alloc(size_t count) {
     if (count <= n && p) return cudaSuccess;
     if (p) cudaDeviceSynchronize();  // growing a live buffer: nothing in flight may still read the old one
@@ -46,6 +49,28 @@ struct DevBuf {
     return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
   }
   cudaError_t Zero(cudaStream_t s) { return cudaMemsetAsync(p, 0, (n ? n : 1) * sizeof(T), s); }
+};
+
+// The ~30 small structure arrays of a problem travel in ONE host -> device copy: they are packed (256 B aligned)
+// into a host block, copied once, and the DevBufs become views into the device block.
+struct DeviceArena {
+  std::vector<char> host;
+  DevBuf<char> dev;
+  struct Slot { size_t off, bytes; };
+  template <typename T>
+  Slot Push(const std::vector<T>& v) {
+    const size_t off = (host.size() + 255) / 256 * 256, bytes = v.size() * sizeof(T);
+    host.resize(off + std::max<size_t>(bytes, 1));
+    if (bytes) std::memcpy(host.data() + off, v.data(), bytes);
+    return Slot{off, bytes};
+  }
+  cudaError_t Upload(cudaStream_t s) {
+    cudaError_t e = dev.Alloc(std::max<size_t>(host.size(), 1));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(dev.p, host.data(), host.size(), cudaMemcpyHostToDevice, s);
+  }
+  template <typename T>
+  void Bind(DevBuf<T>* b, const Slot& s) { b->View(reinterpret_cast<T*>(dev.p + s.off), s.bytes / sizeof(T)); }
 };
 
 // scalar block shared between kernels and polled by the host once per LM
@@ -112,7 +137,11 @@ struct Problem {
   sba_summary counts;                          // structural counts (global problem)
   std::vector<sba_iteration_summary> trace;
 
+  DeviceArena arena;                           // backing store of the small structure arrays below
+  bool host_order_ready = false;               // h_local2ref / h_obs_img fetched from the device (parity surface only)
+
   // ---- device: structure ----
+  DevBuf<unsigned> d_local2ref;                // [n_obs] local point-sorted position -> reference residual index
   DevBuf<int> d_img_cam, d_model, d_col_img, d_col_cam, d_k_cols, d_k_slot, d_k_dim, d_p_off;
   DevBuf<int> d_obs_img, d_obs_pt;
   DevBuf<double> d_obs_xy;
@@ -187,6 +216,10 @@ struct Problem {
 
 // problem.cu
 int BuildProblem(const sba_problem_desc* d, Problem** out, bool host_only);
+int FetchHostOrder(Problem* p);  // order.cu
+int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int n_pt_g, const int* d_raw_img,
+                     const int* d_raw_pt, const double* d_raw_xy);
+cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st);  // fills h_local2ref / h_obs_img / h_obs_pt on first use (sba_evaluate)
 int ProblemCounts(const sba_problem_desc* d, sba_summary* s);
 // eval.cu
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate);

@@ -45,6 +45,17 @@ class FlatProblem:
     def num_observations(self):
         return len(self.obs_image)
 
+    def pin(self):
+        """Move the input arrays into page-locked host memory (sba_host_alloc): sba_create then DMAs them straight
+        from these buffers.  Needs a CUDA device."""
+        arena = capi.PinnedArena()
+        for name in ("image_qvec", "image_tvec", "camera_params", "points", "obs_image", "obs_point", "obs_xy", "sem_maps"):
+            a = getattr(self, name)
+            if a is not None:
+                setattr(self, name, arena.copy(a))
+        self._arena = arena
+        return self
+
     def desc(self, shard_rank=0, shard_count=1):
         d = capi.ProblemDesc()
         d.num_images, d.num_cameras, d.num_points = len(self.image_camera), len(self.camera_model), len(self.points)
