@@ -160,6 +160,35 @@ def run_reference(args, m):
     print(json.dumps(line), flush=True)
 
 
+def pba_second_opinion(m):
+    """The reference's own lib/PBA CPU solver (oracle/_ref/libpba_ref.so, compiled from /root/reference/lib/PBA where the
+    sources lie) beside this library on the C1 shape -- the one BASELINE config PBA accepts (SIMPLE_RADIAL, unshared
+    intrinsics; bundle_adjustment.cc:629-651).  A different LM, reported as a second opinion only."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "libpba_ref.so")
+    if not os.path.exists(ref):
+        return {"unavailable": "oracle/_ref/libpba_ref.so not built"}
+    lib = C.CDLL(ref)
+    lib.pba_ref_solve.argtypes = [C.POINTER(m.capi.ProblemDesc), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                  C.POINTER(C.c_double)]
+    prob, _ = m.scene.make_config("C1")
+    d = prob.desc()
+    out = np.zeros(5)
+    threads = os.cpu_count() or 1
+    if lib.pba_ref_solve(C.byref(d), LM_ITERS, threads, 1, out.ctypes.data_as(C.POINTER(C.c_double)), None) != 0:
+        return {"unavailable": "PBA rejected the problem"}
+    s = m.Solver(prob)
+    o = solver_options(m, len(prob.image_camera))
+    s.solve(o); s.reset()
+    summ = s.solve(o)
+    s.close()
+    it_gpu = summ.num_successful_steps + summ.num_unsuccessful_steps
+    return {"workload": "C1: %d cams / %d pts / %d obs, SIMPLE_RADIAL" % (len(prob.image_camera), len(prob.points), prob.num_observations),
+            "pba_cpu_double": {"observations_per_s": prob.num_observations * max(out[2], 1) / out[3], "lm_iterations": int(out[2]),
+                               "seconds": out[3], "threads": threads, "final_cost": out[1]},
+            "b200": {"observations_per_s": prob.num_observations * it_gpu / summ.device_time_s, "lm_iterations": it_gpu,
+                     "seconds": summ.device_time_s, "final_cost": summ.final_cost}}
+
+
 def stage_table(solver, stages, repeat, hbm_peak):
     out = {}
     for st in stages:
@@ -264,9 +293,18 @@ def run_b200(args, m):
     table = stage_table(s, stages, 20, hbm_peak)
     hbm_stages = {k: v for k, v in table.items() if "ms" in v and k != "cholesky"}
     top = max(hbm_stages, key=lambda k: hbm_stages[k]["ms"])
+    traffic = None
+    try:  # per-launch DRAM bytes of the same stage from the committed ncu --set full capture (profiles/traffic.json)
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("%s/%s" % (args.workload, top), {}).get("bytes")
+    except Exception:  # noqa: BLE001
+        pass
     roof = {"bound": "hbm", "kernel": top, "achieved": table[top]["GBps"], "peak": hbm_peak, "unit": "GB/s",
-            "frac": table[top]["GBps"] / hbm_peak, "traffic": None, "peak_source": peak_kind,
-            "eval_frac": table["eval"]["GBps"] / hbm_peak}
+            "frac": table[top]["GBps"] / hbm_peak, "traffic": traffic, "peak_source": peak_kind,
+            "eval_frac": table["eval"]["GBps"] / hbm_peak,
+            "note": "stage = all kernels of the named step, L2 flushed before each launch; at C2 the whole working set "
+                    "(28 MB) is smaller than L2 and every stage is launch/latency-bound -- the C4 stage table in "
+                    "extra_workloads is the HBM-bound regime"}
     line = {
         "metric": "residual+Jacobian observations/s through the LM solve (observations x LM iterations / s)",
         "value": value, "unit": "observations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -274,8 +312,8 @@ def run_b200(args, m):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "lm_iterations_per_s": n_iter * args.steps / dev_s,
         "eval_observations_per_s": n_obs / world / (table["eval"]["ms"] * 1e-3) * world,
-        "config": {"workload": "%s x%d: %d cams / %d pts / %d obs, %d LM iterations, %s" % (
-            args.workload, world, len(prob.image_camera), len(prob.points), n_obs, LM_ITERS,
+        "config": {"workload": "%s x%d: %d cams / %d pts / %d obs, max %d LM iterations (tolerances 0; ran %d), %s" % (
+            args.workload, world, len(prob.image_camera), len(prob.points), n_obs, LM_ITERS, n_iter,
             "DENSE_SCHUR device Cholesky" if dense else "ITERATIVE_SCHUR PCG + SCHUR_JACOBI"),
             "l2": "stage timings flush L2 (256 MB memset) between launches; the LM step re-reads its own Jacobian",
             "sharding": "points (with their observations) split across ranks, cameras replicated"},
@@ -307,6 +345,8 @@ def run_b200(args, m):
             "linear_solver_iterations": int(sm.num_linear_solver_iterations), "final_cost": sm.final_cost,
             "stages": stage_table(sb, it_stages, 10, hbm_peak)}}
         sb.close()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["pba_reference"] = pba_second_opinion(m)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:

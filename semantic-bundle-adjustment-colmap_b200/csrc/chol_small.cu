@@ -441,16 +441,15 @@ int CholeskySolveSmall(Problem* p) {
   const int n = p->n_cdim;
   const int nbr = DivUp(n, SB);
   cudaStream_t st = p->stream;
-  if (p->chol_flags.n < (size_t)(nbr + 1)) {
-    SBA_CUDA(p->chol_flags.Alloc((size_t)(kCholSmallMax / SB + 2)));
-    SBA_CUDA(p->chol_flags.Zero(st));
-    p->chol_epoch = 0;
-  }
+  if (p->chol_flags.n < (size_t)(nbr + 1)) SBA_CUDA(p->chol_flags.Alloc((size_t)(kCholSmallMax / SB + 2)));
+  // progress counters start from zero on every solve (a memset node: the launch sequence of an LM iteration has no
+  // per-call kernel argument, so that it can be replayed as a CUDA graph -- lm.cu)
+  SBA_CUDA(p->chol_flags.Zero(st));
   SBA_CUDA(p->d_Linv.Alloc((size_t)std::max(nbr, 1) * 64 * 64));
   CholSmall a;
   a.S = p->d_S.p; a.Dc = p->chol_add_diag ? p->d_Dc.p : nullptr; a.rhs = p->d_rhs.p; a.y = p->d_yc.p;
   a.Linv = p->d_Linv.p; a.flags = p->chol_flags.p; a.sc = p->d_scalars.p;
-  a.n = n; a.nbr = nbr; a.epoch = ++p->chol_epoch;
+  a.n = n; a.nbr = nbr; a.epoch = 1;
   const int own_cap = std::min(nbr, kOwnCap);
   const size_t smem = ((size_t)(3 + own_cap) * kTileD + 16 * 17 + 2 * SB + 1024 + SB) * sizeof(double);
   static size_t smem_set = 0;

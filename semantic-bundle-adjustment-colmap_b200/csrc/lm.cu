@@ -10,6 +10,8 @@
 // linear solve, after the candidate cost) to decide which kernels to enqueue next and to
 // fill the iteration table handed to the caller's callbacks.
 #include <chrono>
+#include <cstdlib>
+#include <cstring>
 #include <utility>
 
 #include "solver.h"
@@ -29,6 +31,37 @@ struct StageTimer {
   double Ms(int a, int b) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev[a], ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.0; } return ms; }
 };
 }  // namespace
+
+// Replays `body` (a fixed launch sequence on p->stream, no host synchronisation inside) as a CUDA graph: captured
+// the first time a key is seen, launched as one graph afterwards.  An LM iteration at C2 is ~45 launches of
+// 3-150 us kernels; as a graph the launch gaps and the host's per-launch cost leave the critical path.
+template <class F>
+static int RunSegment(Problem* p, int key, bool use_graph, F&& body) {
+  if (!use_graph) return body();
+  cudaStream_t st = p->stream;
+  if (!p->graph_exec[key]) {
+    const int64_t l0 = p->launches;
+    SBA_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = body();
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(st, &g);
+    if (rc || e != cudaSuccess || !g) {
+      if (g) cudaGraphDestroy(g);
+      cudaGetLastError();
+      if (rc) return rc;
+      SetError(SBA_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
+      return SBA_ERR_CUDA;
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&p->graph_exec[key], g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) { p->graph_exec[key] = nullptr; SetError(SBA_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ei)); return SBA_ERR_CUDA; }
+    p->graph_launches[key] = p->launches - l0;
+  } else {
+    p->launches += p->graph_launches[key];
+  }
+  SBA_CUDA(cudaGraphLaunch(p->graph_exec[key], st));
+  return SBA_OK;
+}
 
 static int ResolveSolver(const Problem* p, const sba_solver_options& o) {
   int solver = o.linear_solver_type;
@@ -114,6 +147,19 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   // invalid step -- rare -- makes phase 1 a no-op and wastes one cost pass).  After an accepted step the new
   // linearisation is enqueued and, unless a callback or a gradient tolerance needs its numbers right away, the
   // host does not wait for it: cost and gradient norm of that row are filled in at the next synchronisation.
+  // Graph replay: direct solvers on one GPU (the PCG path polls its state from the host; NCCL stays outside).
+  // SBA_NO_GRAPHS=1 keeps plain launches with the per-stage event timers (time_*_s of the summary).
+  static const bool graphs_off = getenv("SBA_NO_GRAPHS") != nullptr || getenv("SBA_CHOL_TRACE") != nullptr;
+  // Capturing and instantiating the (up to six) graphs costs about as much as they save over ~10 iterations, so a
+  // fresh handle asked for a short solve keeps plain launches; a handle that is solved again (sba_reset) or a long
+  // solve (the reference's default is max_num_iterations = 100) replays graphs.
+  const bool worth_it = p->solve_count > 0 || o.max_num_iterations > 25;
+  p->solve_count++;
+  const bool graphs_ok = !graphs_off && worth_it && !iterative && p->comm == nullptr && p->n_cdim > 0;
+  if (graphs_ok && (!p->graph_opts_valid || std::memcmp(&p->graph_opts, &o, sizeof(o)) != 0)) {
+    p->DropGraphs();
+    p->graph_opts = o; p->graph_opts_valid = true;
+  }
   const bool eager = cb != nullptr || o.gradient_tolerance > 0.0;
   int pending_row = -1;       // trace row whose cost / gradient are still on the device
   bool pending_eval_time = false;
@@ -136,39 +182,52 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     it.iteration = iteration;
     it.eta = o.eta;
 
-    // ---- LevenbergMarquardtStrategy::ComputeStep ----
-    tm.Mark(0, st);
-    if ((rc = PrepareLMDiagonal(p, o))) return rc;
-    if ((rc = PointBlocks(p, false))) return rc;
+    // ---- LevenbergMarquardtStrategy::ComputeStep, candidate point and its cost: one launch sequence ----
+    // (the first iteration runs as plain launches: it allocates, builds the pair lists and sets kernel attributes)
+    const bool use_graph = graphs_ok && iteration >= 2;
+    const bool marks = !use_graph;
     int lin_iters = 0;
-    if (p->n_cdim > 0) {
-      if ((rc = ReducedRhs(p))) return rc;
-      if (iterative) {
-        if ((rc = BuildSchurJacobi(p))) return rc;
+    auto step_segment = [&]() -> int {
+      int r;
+      if (marks) tm.Mark(0, st);
+      if ((r = PrepareLMDiagonal(p, o))) return r;
+      if ((r = PointBlocks(p, false))) return r;
+      if (p->n_cdim > 0) {
+        if ((r = ReducedRhs(p))) return r;
+        if (iterative) {
+          if ((r = BuildSchurJacobi(p))) return r;
+          if (marks) tm.Mark(1, st);
+          if ((r = SolvePCG(p, o, &lin_iters))) return r;
+        } else {
+          if ((r = BuildDenseSchur(p))) return r;
+          if (marks) tm.Mark(1, st);
+          if ((r = CholeskySolve(p))) return r;
+          lin_iters = 1;
+        }
+      } else if (marks) {
         tm.Mark(1, st);
-        if ((rc = SolvePCG(p, o, &lin_iters))) return rc;
-      } else {
-        if ((rc = BuildDenseSchur(p))) return rc;
-        tm.Mark(1, st);
-        if ((rc = CholeskySolve(p))) return rc;
-        lin_iters = 1;
       }
-    } else {
-      tm.Mark(1, st);
-    }
-    tm.Mark(2, st);
-    if ((rc = BackSubstitute(p))) return rc;
-    if ((rc = TrustRegionUpdate(p, o, 0, false))) return rc;
-    // ---- candidate point and its cost ----
-    tm.Mark(3, st);
-    if ((rc = ApplyStep(p))) return rc;
-    tm.Mark(4, st);
-    if ((rc = LaunchCostOnly(p, loss, true, &sc->cand_cost))) return rc;
-    tm.Mark(5, st);
-    if ((rc = TrustRegionUpdate(p, o, 1, true))) return rc;  // syncs; hs is current
+      if (marks) tm.Mark(2, st);
+      if ((r = BackSubstitute(p))) return r;
+      if ((r = TrustRegionUpdate(p, o, 0, false))) return r;
+      if (marks) tm.Mark(3, st);
+      if ((r = ApplyStep(p))) return r;
+      if (marks) tm.Mark(4, st);
+      if ((r = LaunchCostOnly(p, loss, true, &sc->cand_cost))) return r;
+      if (marks) tm.Mark(5, st);
+      if ((r = TrustRegionUpdate(p, o, 1, false))) return r;
+      SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
+      return SBA_OK;
+    };
+    const int refresh = hs->reuse_diagonal ? 0 : 1;  // PrepareLMDiagonal branches on the same host flag
+    if ((rc = RunSegment(p, p->parity * 2 + refresh, use_graph, step_segment))) return rc;
+    if (use_graph) lin_iters = 1;
+    SBA_CUDA(cudaStreamSynchronize(st));  // hs is current
     settle();
-    p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;
-    p->t_update += (tm.Ms(2, 3) + tm.Ms(3, 4)) * 1e-3; p->t_eval += tm.Ms(4, 5) * 1e-3;
+    if (marks) {
+      p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;
+      p->t_update += (tm.Ms(2, 3) + tm.Ms(3, 4)) * 1e-3; p->t_eval += tm.Ms(4, 5) * 1e-3;
+    }
     it.linear_solver_iterations = lin_iters;
     sum->num_linear_solver_iterations += lin_iters;
     it.step_is_valid = hs->step_valid;
@@ -202,18 +261,24 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       std::swap(p->d_pose.p, p->d_pose2.p);
       std::swap(p->d_cam.p, p->d_cam2.p);
       std::swap(p->d_X.p, p->d_X2.p);
-      tm.Mark(6, st);
-      if ((rc = LaunchEvaluate(p, loss, o.jacobi_scaling != 0, false))) return rc;
-      if ((rc = PointBlocks(p, true))) return rc;
-      if ((rc = Gradient(p))) return rc;
-      tm.Mark(7, st);
+      p->parity ^= 1;
+      auto linearise_segment = [&]() -> int {
+        int r;
+        if (marks) tm.Mark(6, st);
+        if ((r = LaunchEvaluate(p, loss, o.jacobi_scaling != 0, false))) return r;
+        if ((r = PointBlocks(p, true))) return r;
+        if ((r = Gradient(p))) return r;
+        if (marks) tm.Mark(7, st);
+        return SBA_OK;
+      };
+      if ((rc = RunSegment(p, 4 + p->parity, use_graph, linearise_segment))) return rc;
       it.step_is_successful = 1;
       sum->num_successful_steps++;
       it.cost = x_cost + fixed_cost;  // provisional; settled below or at the next synchronisation
       it.gradient_max_norm = p->trace.back().gradient_max_norm;
       p->trace.push_back(it);
       pending_row = (int)p->trace.size() - 1;
-      pending_eval_time = true;
+      pending_eval_time = marks;
       if (eager || iteration >= o.max_num_iterations) {
         SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
         SBA_CUDA(cudaStreamSynchronize(st));

@@ -205,8 +205,14 @@ cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t s
   return (cudaError_t)err.load();
 }
 
+void Problem::DropGraphs() {
+  for (auto& g : graph_exec) { if (g) cudaGraphExecDestroy(g); g = nullptr; }
+  graph_opts_valid = false;
+}
+
 Problem::~Problem() {
   if (stream) cudaStreamSynchronize(stream);  // buffers go back to the pool only once nothing uses them
+  DropGraphs();
   CommDestroy(this);
   if (stream && h_scalars) {
     std::lock_guard<std::mutex> lk(g_ctx_mu);

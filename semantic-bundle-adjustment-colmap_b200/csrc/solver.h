@@ -190,6 +190,16 @@ struct Problem {
   DevBuf<DeviceScalars> d_scalars;
   DeviceScalars* h_scalars = nullptr;       // pinned
 
+  // CUDA graphs of the LM iteration's launch sequence (lm.cu): [0..3] step segment by (parity, refresh), [4..5]
+  // re-linearisation segment by parity; parity = which of the two parameter buffers is current
+  cudaGraphExec_t graph_exec[6] = {};
+  int64_t graph_launches[6] = {};
+  sba_solver_options graph_opts;             // the options the graphs were captured with
+  bool graph_opts_valid = false;
+  int parity = 0;
+  int solve_count = 0;                       // sba_solve calls on this handle
+  void DropGraphs();
+
   cudaStream_t stream = nullptr;
   int device = 0;
   int n_sm = 148;                           // multiprocessors of `device`
