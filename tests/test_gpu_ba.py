@@ -54,3 +54,27 @@ def test_solve_parity_c1(sba, oracle, solver):
     q, t, cam, X = s.parameters()
     assert np.allclose(X, po[3], rtol=0, atol=1e-5)
     s.close()
+
+
+def test_graph_replay_is_bit_identical_to_plain_launches(sba, oracle):
+    """A handle that is solved again (sba_reset) replays the LM iteration as CUDA graphs (csrc/lm.cu); a long solve
+    does so from its second iteration.  Same kernels, same order: costs and parameters must not change by one bit."""
+    prob, _ = sba.scene.make_scene(n_cam=12, n_pt=1500, mean_track=5.0, seed=21)
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations, o.linear_solver_type = 8, 0
+    s = sba.Solver(prob)
+    first = s.solve(o)                       # fresh handle, short solve: plain launches
+    tr1, par1 = [t.cost for t in s.trace()], [a.copy() for a in s.parameters()]
+    s.reset()
+    second = s.solve(o)                      # graphs
+    tr2, par2 = [t.cost for t in s.trace()], s.parameters()
+    assert first.final_cost == second.final_cost and tr1 == tr2
+    assert all(np.array_equal(a, b) for a, b in zip(par1, par2))
+    s.close()
+    o.max_num_iterations = 30                # long solve on a fresh handle: graphs from iteration 2
+    s = sba.Solver(prob)
+    sg = s.solve(o)
+    rc, so, tro, _ = oracle_solve(oracle, sba.capi, prob, o)
+    assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
+    # (iteration counts differ at the noise floor: with tolerances 0 a solve stops when a cost change rounds to exactly 0)
+    s.close()
