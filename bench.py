@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--workload", default="C2", help="C1..C5 (BASELINE.json configs); C2 is the headline")
     ap.add_argument("--extra", default="C4", help="larger workload whose stage rooflines are appended ('' = none)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling: the named config is the TOTAL problem, split over the ranks (default: weak, per-GPU work fixed)")
     return ap.parse_args()
 
 
@@ -94,10 +96,10 @@ def dist_env():
     return rank, world, local
 
 
-def make_workload(m, name, n_gpus):
-    """Weak scaling: points (and with them observations) per GPU fixed, cameras fixed."""
+def make_workload(m, name, n_gpus, strong=False):
+    """Weak scaling (default): points (and with them observations) per GPU fixed, cameras fixed."""
     cfg = dict(m.scene.CONFIGS[name])
-    cfg["n_pt"] = cfg["n_pt"] * n_gpus
+    cfg["n_pt"] = cfg["n_pt"] * (1 if strong else n_gpus)
     label_maps = name in ("C2",)  # C5's 5k maps (6 GB) are generated only on request
     prob, _ = m.scene.make_scene(seed=0, label_maps=label_maps, **cfg)
     return prob, cfg
@@ -134,7 +136,7 @@ def run_reference(args, m):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    prob, cfg = make_workload(m, args.workload, args.gpus)
+    prob, cfg = make_workload(m, args.workload, args.gpus, args.strong)
     o = solver_options(m, len(prob.image_camera))
     for _ in range(args.warmup):
         cpu_solve(m, prob, o, 0)
@@ -214,7 +216,7 @@ def run_b200(args, m):
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    prob, cfg = make_workload(m, args.workload, args.gpus)
+    prob, cfg = make_workload(m, args.workload, args.gpus, args.strong)
     n_obs = prob.num_observations
     o = solver_options(m, len(prob.image_camera))
 
@@ -309,7 +311,7 @@ def run_b200(args, m):
         "metric": "residual+Jacobian observations/s through the LM solve (observations x LM iterations / s)",
         "value": value, "unit": "observations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "wall_ms_per_step": wall_s / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "lm_iterations_per_s": n_iter * args.steps / dev_s,
         "eval_observations_per_s": n_obs / world / (table["eval"]["ms"] * 1e-3) * world,
         "config": {"workload": "%s x%d: %d cams / %d pts / %d obs, max %d LM iterations (tolerances 0; ran %d), %s" % (

@@ -17,14 +17,15 @@ static int Expand(Problem* p, const double* x, double* xi, double* xc) {
 
 // mode 0: F^T v, 1: F^T r, 2: column square norms.  out (compact) = sum over LOCAL
 // observations, all-reduced over ranks, plus Dc^2 x when Dc != nullptr.
-static int CamReduce(Problem* p, int mode, const double2* v, double* out, const double* Dc, const double* x) {
+static int CamReduce(Problem* p, int mode, const double2* v, double* out, const double* Dc, const double* x,
+                     const int* skip = nullptr) {
   if (p->n_cdim == 0) return SBA_OK;
   if (p->n_chunks > 0) {
 #define CALL(DC)                                                                                                        \
   do {                                                                                                                  \
-    if (mode == 0) cam_reduce_kernel<DC, 0><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
-    else if (mode == 1) cam_reduce_kernel<DC, 1><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
-    else cam_reduce_kernel<DC, 2><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p); \
+    if (mode == 0) cam_reduce_kernel<DC, 0><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
+    else if (mode == 1) cam_reduce_kernel<DC, 1><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
+    else cam_reduce_kernel<DC, 2><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
   } while (0)
     SBA_DC_SWITCH(p->dc, CALL)
 #undef CALL
@@ -144,15 +145,15 @@ int ReducedRhs(Problem* p) {
 
 // y = S x with S = F^T F + Dc^2 - sum_p (F^T E)_p C_p^{-1} (E^T F)_p, never formed
 // (ImplicitSchurComplement::RightMultiply).
-int SchurMatVec(Problem* p, const double* d_x, double* d_y) {
+int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip) {
   Expand(p, d_x, p->d_xi.p, p->d_xc.p);
   if (p->n_tiles > 0) {
-#define CALL(DC) matvec_point_kernel<DC><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p))
+#define CALL(DC) matvec_point_kernel<DC><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p), skip)
     SBA_DC_SWITCH(p->dc, CALL)
 #undef CALL
     p->launches++;
   }
-  return CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), d_y, p->d_Dc.p, d_x);
+  return CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), d_y, p->d_Dc.p, d_x, skip);
 }
 
 // y_p and model_cost_change from y_c (d_yc)

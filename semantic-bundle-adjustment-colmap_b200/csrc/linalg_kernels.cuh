@@ -197,7 +197,8 @@ template <int DC>
 __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileView T, const D4* __restrict__ ER,
                                                            const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                            const double* __restrict__ xi, const double* __restrict__ xc,
-                                                           double2* __restrict__ out) {
+                                                           double2* __restrict__ out, const int* __restrict__ skip) {
+  if (skip && *skip != 0) return;  // CG already stopped (the host polls its state only every few iterations)
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
   const int lane = threadIdx.x & 31;
@@ -348,7 +349,8 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
 template <int DC, int MODE>
 __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* __restrict__ F,
                                                          const D4* __restrict__ ER, const double2* __restrict__ v,
-                                                         double* __restrict__ partial) {
+                                                         double* __restrict__ partial, const int* __restrict__ skip) {
+  if (skip && *skip != 0) return;
   const int ch = blockIdx.x;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
   double acc[DC];

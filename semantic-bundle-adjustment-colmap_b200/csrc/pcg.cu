@@ -170,14 +170,14 @@ int SolvePCG(Problem* p, const sba_solver_options& o, int* iters) {
     cg_direction_kernel<<<1, kCgThreads, 0, st>>>(n, it, p->d_col_blk.p, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,
                                                   p->d_Minv.p, p->d_cg_r.p, p->d_cg_z.p, p->d_cg_p.p, sc);
     p->launches++;
-    int rc = SchurMatVec(p, p->d_cg_p.p, p->d_cg_q.p);
+    int rc = SchurMatVec(p, p->d_cg_p.p, p->d_cg_q.p, &sc->cg_state);
     if (rc) return rc;
     const int reset = (it % 10 == 0) ? 1 : 0;
     cg_update_kernel<<<1, kCgThreads, 0, st>>>(n, it, reset, min_it, max_it, o.eta, b, p->d_cg_p.p, p->d_cg_q.p, x,
                                                p->d_cg_r.p, sc);
     p->launches++;
     if (reset) {
-      rc = SchurMatVec(p, x, p->d_tmp_c.p);
+      rc = SchurMatVec(p, x, p->d_tmp_c.p, &sc->cg_state);
       if (rc) return rc;
       cg_reset_kernel<<<1, kCgThreads, 0, st>>>(n, it, min_it, max_it, o.eta, b, p->d_tmp_c.p, x, p->d_cg_r.p, sc);
       p->launches++;

@@ -209,7 +209,7 @@ struct Problem {
   DevBuf<float> d_sem_maps;  int sem_h = 0, sem_w = 0;  double sem_weight = 0.0;
   bool solved = false;
   bool linearized = false;
-  int cg_poll_every = 1;                    // host polls the CG state every this many iterations
+  int cg_poll_every = 4;                    // host polls the CG state every this many iterations
   double* jq_out = nullptr;                 // parity surface: raw 2x4 quaternion block per observation
   DevBuf<char> d_flush;                     // L2 flush scratch for sba_bench_stage
   Comm* comm = nullptr;
@@ -243,7 +243,7 @@ int InitJacobiScale(Problem* p);
 int PrepareLMDiagonal(Problem* p, const sba_solver_options& o);
 int PointBlocks(Problem* p, bool grad_only);
 int ReducedRhs(Problem* p);
-int SchurMatVec(Problem* p, const double* d_x, double* d_y);
+int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip = nullptr);  // *skip != 0: the big kernels return at once
 int BackSubstitute(Problem* p);
 int ModelCostChange(Problem* p);
 int ApplyStep(Problem* p);
