@@ -328,6 +328,35 @@ typedef struct sba_cylinder_desc {
 int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residuals, double* jac,
                           double* ms_device);
 
+/* --- camera-rig reprojection functor (reference a3) ----------------------
+ * RigBundleAdjustmentCostFunction, src/base/cost_functions.h:160-214: composed pose
+ * q = rel_q (x) rig_q, t = R(rel_q) rig_t + rel_t, then the reprojection residual.  Evaluates a batch of
+ * residual blocks as RigBundleAdjuster adds them (src/optim/bundle_adjustment.cc:1017-1031). */
+typedef struct sba_rig_desc {
+  int32_t num_rig_poses;        /* rig snapshots */
+  const double* rig_qvec;       /* [num_rig_poses*4] */
+  const double* rig_tvec;       /* [num_rig_poses*3] */
+  int32_t num_rel_poses;        /* cameras of the rig */
+  const double* rel_qvec;       /* [num_rel_poses*4] CameraRig::RelativeQvec */
+  const double* rel_tvec;       /* [num_rel_poses*3] CameraRig::RelativeTvec */
+  int32_t num_cameras;
+  const int32_t* camera_model;  /* [num_cameras] sba_camera_model */
+  const double* camera_params;  /* [num_cameras*SBA_MAX_CAMERA_PARAMS] */
+  int32_t num_points;
+  const double* points;         /* [num_points*3] */
+  int64_t num_blocks;
+  const int32_t* block_rig;     /* [num_blocks] */
+  const int32_t* block_rel;     /* [num_blocks] */
+  const int32_t* block_camera;  /* [num_blocks] */
+  const int32_t* block_point;   /* [num_blocks] */
+  const double* block_xy;       /* [num_blocks*2] observed Point2D::XY() */
+} sba_rig_desc;
+
+#define SBA_RIG_JAC_COLS (4 + 3 + 4 + 3 + 3 + SBA_MAX_CAMERA_PARAMS)
+/* residuals[num_blocks*2]; jac[num_blocks*2*SBA_RIG_JAC_COLS] (nullable): per residual row the ambient blocks
+ * d r / d (rig_q(4), rig_t(3), rel_q(4), rel_t(3), point(3), camera params(12)), as CostFunction::Evaluate returns. */
+int sba_rig_evaluate(const sba_rig_desc* d, double* residuals, double* jac, double* ms_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -140,6 +140,52 @@ static void EvalObsJet(int model, const double* q, const double* t, const double
   }
 }
 
+// Rig functor (cost_functions.h:173-209) with Jet<4+3+4+3+3+P>, as
+// AutoDiffCostFunction<..., 2, 4, 3, 4, 3, 3, kNumParams> does (cost_functions.h:171-176).
+// J: per residual row 17 + 12 columns (rig_q, rig_t, rel_q, rel_t, X, params padded to 12).
+template <int P>
+static void EvalRigJet(int model, const double* rig_q, const double* rig_t, const double* rel_q, const double* rel_t,
+                       const double* X, const double* params, const double* xy, double* r, double* Jout) {
+  constexpr int N = 17 + P;
+  typedef Jet<N> J;
+  J gq[4], gt[3], lq[4], lt[3], jX[3], jp[P];
+  for (int i = 0; i < 4; ++i) gq[i] = J(rig_q[i], i);
+  for (int i = 0; i < 3; ++i) gt[i] = J(rig_t[i], 4 + i);
+  for (int i = 0; i < 4; ++i) lq[i] = J(rel_q[i], 7 + i);
+  for (int i = 0; i < 3; ++i) lt[i] = J(rel_t[i], 11 + i);
+  for (int i = 0; i < 3; ++i) jX[i] = J(X[i], 14 + i);
+  for (int i = 0; i < P; ++i) jp[i] = J(params[i], 17 + i);
+  J q[4], t[3], proj[3];
+  QuaternionProduct(lq, gq, q);
+  UnitQuaternionRotatePoint(lq, gt, t);
+  t[0] += lt[0]; t[1] += lt[1]; t[2] += lt[2];
+  UnitQuaternionRotatePoint(q, jX, proj);
+  proj[0] += t[0]; proj[1] += t[1]; proj[2] += t[2];
+  proj[0] /= proj[2];
+  proj[1] /= proj[2];
+  J res[2];
+  Project<J>(model, jp, proj[0], proj[1], &res[0], &res[1]);
+  res[0] = res[0] - xy[0];
+  res[1] = res[1] - xy[1];
+  for (int row = 0; row < 2; ++row) {
+    r[row] = res[row].a;
+    if (!Jout) continue;
+    for (int i = 0; i < 29; ++i) Jout[row * 29 + i] = i < N ? res[row].v[i] : 0.0;
+  }
+}
+
+void EvalRigObservation(int model, const double* rig_q, const double* rig_t, const double* rel_q, const double* rel_t,
+                        const double* X, const double* params, const double* xy, double* r, double* J) {
+  switch (NumParams(model)) {
+    case 3: EvalRigJet<3>(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J); break;
+    case 4: EvalRigJet<4>(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J); break;
+    case 5: EvalRigJet<5>(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J); break;
+    case 8: EvalRigJet<8>(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J); break;
+    case 12: EvalRigJet<12>(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J); break;
+    default: r[0] = r[1] = std::numeric_limits<double>::quiet_NaN();
+  }
+}
+
 // residual-only (double) evaluation, used for candidate-step cost
 static inline void EvalObsValue(int model, const double* q, const double* t, const double* X,
                                 const double* params, const double* xy, double* r) {

@@ -69,6 +69,8 @@ struct Linearization {
 
 // raw functor evaluation of observation k at explicit parameter values:
 // r[2], Jq[2x4], Jt[2x3], JX[2x3], Jk[2xP] (P = NumParams(model)), row-major.
+void EvalRigObservation(int model, const double* rig_q, const double* rig_t, const double* rel_q, const double* rel_t,
+                        const double* X, const double* params, const double* xy, double* r, double* J /* 2x29 or null */);
 void EvalObservation(int model, const double* q, const double* t, const double* X,
                      const double* params, const double* xy, double* r, double* Jq, double* Jt,
                      double* JX, double* Jk);

@@ -44,6 +44,14 @@ void oracle_eval_rig_observation(int model, const double* rig_q, const double* r
   EvalObservation(model, q, t, X, params, xy, r, nullptr, nullptr, nullptr, nullptr);
 }
 
+// Rig functor with its autodiff Jacobian (2 x 29: rig_q, rig_t, rel_q, rel_t, X, params padded to 12) -- the layout
+// of sba_rig_evaluate (include/sba_b200.h).
+void oracle_eval_rig_observation_jac(int model, const double* rig_q, const double* rig_t, const double* rel_q,
+                                     const double* rel_t, const double* X, const double* params, const double* xy,
+                                     double* r, double* J) {
+  EvalRigObservation(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J);
+}
+
 // Problem::Evaluate equivalent in the sba_evaluate() output format (include/sba_b200.h).
 int oracle_ba_evaluate(const sba_problem_desc* d, int loss_type, double loss_scale, int apply_loss,
                        int threads, double* cost, double* residuals, double* jac_pose,

@@ -121,6 +121,19 @@ class CylinderDesc(C.Structure):
     ]
 
 
+class RigDesc(C.Structure):
+    _fields_ = [
+        ("num_rig_poses", C.c_int32), ("rig_qvec", _dp), ("rig_tvec", _dp),
+        ("num_rel_poses", C.c_int32), ("rel_qvec", _dp), ("rel_tvec", _dp),
+        ("num_cameras", C.c_int32), ("camera_model", _ip), ("camera_params", _dp),
+        ("num_points", C.c_int32), ("points", _dp),
+        ("num_blocks", C.c_int64), ("block_rig", _ip), ("block_rel", _ip), ("block_camera", _ip), ("block_point", _ip),
+        ("block_xy", _dp),
+    ]
+
+
+RIG_JAC_COLS = 4 + 3 + 4 + 3 + 3 + 12
+
 ITERATION_CALLBACK = C.CFUNCTYPE(C.c_int, C.POINTER(IterationSummary), C.c_void_p)
 
 # every entry point include/sba_b200.h declares: name -> (restype, argtypes)
@@ -147,6 +160,7 @@ SYMBOLS = {
     "sba_shard_points": (C.c_int, [C.POINTER(ProblemDesc), C.c_int32, C.c_int32, _u8p, _u8p]),
     "sba_semantic_evaluate": (C.c_int, [C.POINTER(SemanticDesc), _dp, _ip, _dp, _dp]),
     "sba_cylinder_evaluate": (C.c_int, [C.POINTER(CylinderDesc), _dp, _dp, _dp]),
+    "sba_rig_evaluate": (C.c_int, [C.POINTER(RigDesc), _dp, _dp, _dp]),
 }
 
 _lib = None

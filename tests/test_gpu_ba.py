@@ -78,3 +78,26 @@ def test_graph_replay_is_bit_identical_to_plain_launches(sba, oracle):
     assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
     # (iteration counts differ at the noise floor: with tolerances 0 a solve stops when a cost change rounds to exactly 0)
     s.close()
+
+
+def test_sharded_handles_see_exactly_their_observations(sba):
+    """Multi-GPU layout on one device: each shard sorts the WHOLE problem on the device and keeps its contiguous slice
+    (csrc/order.cu).  Per-observation residuals / Jacobians do not depend on the sharding: bit-identical to the
+    unsharded handle for owned observations, untouched for the others; the shards partition the observations."""
+    prob, _ = sba.scene.make_scene(n_cam=9, n_pt=700, mean_track=4.5, seed=31)
+    s = sba.Solver(prob)
+    full = s.evaluate()
+    s.close()
+    covered = np.zeros(prob.num_observations, bool)
+    for rank in range(3):
+        _, obs_keep = prob.shard_masks(3, rank)
+        own = obs_keep.astype(bool)
+        sh = sba.Solver(prob, shard_rank=rank, shard_count=3)
+        ev = sh.evaluate()
+        sh.close()
+        for k in ("r", "pose", "intr", "point"):
+            assert np.array_equal(ev[k][own], full[k][own]), k
+            assert not ev[k][~own].any(), k
+        assert not (covered & own).any()
+        covered |= own
+    assert covered.all()
