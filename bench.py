@@ -291,7 +291,7 @@ def run_b200(args, m):
     # ---- stage times (L2 flushed between launches) and the roofline of the dominant HBM-bound stage ----
     hbm_peak, peak_kind = peaks()
     dense = summ.linear_solver_type_used != m.capi.ITERATIVE_SCHUR
-    stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (["schur_dense", "cholesky"] if dense else ["schur_jacobi", "matvec"])
+    stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (["schur_dense", "cholesky"] if dense else ["schur_jacobi", "matvec", "schur_blocks", "matvec_blocks"])
     table = stage_table(s, stages, 20, hbm_peak)
     hbm_stages = {k: v for k, v in table.items() if "ms" in v and k != "cholesky"}
     top = max(hbm_stages, key=lambda k: hbm_stages[k]["ms"])
@@ -340,7 +340,7 @@ def run_b200(args, m):
         sm = sb.solve(ob)
         itb = sm.num_successful_steps + sm.num_unsuccessful_steps
         it_stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (
-            ["schur_jacobi", "matvec"] if sm.linear_solver_type_used == m.capi.ITERATIVE_SCHUR else ["schur_dense", "cholesky"])
+            ["schur_jacobi", "matvec", "schur_blocks", "matvec_blocks"] if sm.linear_solver_type_used == m.capi.ITERATIVE_SCHUR else ["schur_dense", "cholesky"])
         line["extra_workloads"] = {args.extra: {
             "n_obs": big.num_observations, "lm_iterations_per_s": itb / sm.device_time_s,
             "observations_per_s": big.num_observations * itb / sm.device_time_s,

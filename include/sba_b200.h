@@ -263,6 +263,11 @@ int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec,
  * returns the mean CUDA-event time per launch in milliseconds. */
 int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms_per_launch,
                     int64_t* algorithmic_bytes);
+/* Parity surface for the reduced camera system: y = (S + D^2) x of the current linearisation (Jacobi-scaled, LM
+ * diagonal of the default options), through the implicit products (use_blocks = 0; what Ceres' ITERATIVE_SCHUR does,
+ * SURVEY.md App. B.5) or the explicit block-sparse S (use_blocks = 1; SBA_ERR_INVALID_ARGUMENT when the problem does
+ * not use it).  *n receives the reduced dimension; x / y may be NULL to query it. */
+int sba_schur_product(sba_handle* h, int32_t use_blocks, const double* x, double* y, int32_t* n);
 /* Number of kernels this library launched on h's stream since creation. */
 int64_t sba_kernel_launch_count(sba_handle* h);
 

@@ -262,6 +262,7 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
   const int64_t gathers = (int64_t)p->n_img * 64 + (int64_t)p->n_cam * 96 + (int64_t)p->n_pt * 24;
   std::function<int()> prep = []() { return SBA_OK; }, run;
   int64_t bytes = 0;
+  bool blocks_built = false;
   if (s == "eval") {
     run = [&]() { return LaunchEvaluate(p, loss, true, false); };
     // idx 8 + xy 16 in; r 16 + J 16*(dc+3) out; + parameter gathers once
@@ -288,6 +289,20 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
   } else if (s == "schur_jacobi") {
     run = [&]() { return BuildSchurJacobi(p); };
     bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 48;
+  } else if (s == "schur_blocks" || s == "matvec_blocks") {
+    // explicit block-sparse S (bsr.cu): build = one pass over the stored Jacobian + the blocks written once;
+    // product = off-diagonal blocks twice (straight + transposed), diagonal once, three camera vectors
+    if ((rc = DecideBlockSchur(p))) return rc;
+    if (!p->bsr.enabled) { SetError(SBA_ERR_INVALID_ARGUMENT, "the block-sparse Schur complement is not in use for this problem"); return SBA_ERR_INVALID_ARGUMENT; }
+    const int64_t ne = dc * dc;
+    if (s == "schur_blocks") {
+      run = [&]() { return BuildExplicitSchur(p); };
+      bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 48 + 8 * p->bsr.n_blocks * ne;
+    } else {
+      prep = [&]() { if (blocks_built) return (int)SBA_OK; blocks_built = true; return BuildExplicitSchur(p); };
+      run = [&]() { return BlockSchurMatVec(p, p->d_rhs.p, p->d_tmp_c.p, nullptr); };
+      bytes = 8 * ((int64_t)p->n_img + 2 * (int64_t)p->bsr.n_keys) * ne + 24 * (int64_t)p->n_cdim;
+    }
   } else if (s == "cholesky") {
     prep = [&]() { return BuildDenseSchur(p); };
     run = [&]() { return CholeskySolve(p); };
@@ -316,6 +331,33 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   if (ms_per_launch) *ms_per_launch = total / repeat;
   if (algorithmic_bytes) *algorithmic_bytes = bytes;
+  return SBA_OK;
+}
+
+int sba_schur_product(sba_handle* h, int32_t use_blocks, const double* x, double* y, int32_t* n) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  if (n) *n = p->n_cdim;
+  if (!x || !y || p->n_cdim == 0) return SBA_OK;
+  sba_solver_options o;
+  sba_default_solver_options(&o);
+  if ((rc = PrepareLinearSystem(p, o))) return rc;
+  SBA_CUDA(cudaMemcpyAsync(p->d_cg_p.p, x, (size_t)p->n_cdim * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+  if (use_blocks) {
+    if ((rc = DecideBlockSchur(p))) return rc;
+    if (!p->bsr.enabled) { SetError(SBA_ERR_INVALID_ARGUMENT, "the block-sparse Schur complement is not in use for this problem"); return SBA_ERR_INVALID_ARGUMENT; }
+    if ((rc = BuildExplicitSchur(p))) return rc;
+    if ((rc = BlockSchurMatVec(p, p->d_cg_p.p, p->d_cg_q.p, nullptr))) return rc;
+  } else {
+    const bool keep = p->bsr.enabled;
+    p->bsr.enabled = false;
+    rc = SchurMatVec(p, p->d_cg_p.p, p->d_cg_q.p);
+    p->bsr.enabled = keep;
+    if (rc) return rc;
+  }
+  SBA_CUDA(cudaMemcpyAsync(y, p->d_cg_q.p, (size_t)p->n_cdim * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  SBA_CUDA(cudaStreamSynchronize(p->stream));
   return SBA_OK;
 }
 

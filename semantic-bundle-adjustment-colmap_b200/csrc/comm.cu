@@ -99,5 +99,12 @@ static int AllReduce(Problem* p, double* d_buf, size_t n, ncclRedOp_t op) {
 }
 int AllReduceSum(Problem* p, double* d_buf, size_t n) { return AllReduce(p, d_buf, n, ncclSum); }
 int AllReduceMax(Problem* p, double* d_buf, size_t n) { return AllReduce(p, d_buf, n, ncclMax); }
+int AllReduceMaxInt(Problem* p, int* d_buf, size_t n) {
+  if (!p->comm || n == 0) return SBA_OK;
+  const ncclResult_t r = g_nccl.AllReduce(d_buf, d_buf, n, ncclInt32, ncclMax, p->comm->comm, p->stream);
+  if (r != ncclSuccess) return NcclFail("ncclAllReduce", r);
+  p->collectives++;
+  return SBA_OK;
+}
 
 }  // namespace sba

@@ -146,6 +146,7 @@ int ReducedRhs(Problem* p) {
 // y = S x with S = F^T F + Dc^2 - sum_p (F^T E)_p C_p^{-1} (E^T F)_p, never formed
 // (ImplicitSchurComplement::RightMultiply).
 int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip) {
+  if (p->bsr.enabled) return BlockSchurMatVec(p, d_x, d_y, skip);  // explicit block-sparse S (bsr.cu)
   Expand(p, d_x, p->d_xi.p, p->d_xc.p);
   if (p->n_tiles > 0) {
 #define CALL(DC) matvec_point_kernel<DC><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p), skip)

@@ -195,7 +195,8 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       if (p->n_cdim > 0) {
         if ((r = ReducedRhs(p))) return r;
         if (iterative) {
-          if ((r = BuildSchurJacobi(p))) return r;
+          if ((r = DecideBlockSchur(p))) return r;  // once per problem: explicit block-sparse S or implicit products
+          if ((r = p->bsr.enabled ? BuildExplicitSchur(p) : BuildSchurJacobi(p))) return r;
           if (marks) tm.Mark(1, st);
           if ((r = SolvePCG(p, o, &lin_iters))) return r;
         } else {

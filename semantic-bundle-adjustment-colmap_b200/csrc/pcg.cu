@@ -162,11 +162,17 @@ int SolvePCG(Problem* p, const sba_solver_options& o, int* iters) {
   DeviceScalars* sc = p->d_scalars.p;
   const double* b = p->d_rhs.p;
   double* x = p->d_yc.p;
-  cg_init_kernel<<<1, kCgThreads, 0, st>>>(n, b, x, p->d_cg_r.p, sc);
-  p->launches++;
   const int min_it = o.min_linear_solver_iterations, max_it = std::max(1, o.max_linear_solver_iterations);
   const int poll_every = p->cg_poll_every > 0 ? p->cg_poll_every : 1;
-  for (int it = 1; it <= max_it; ++it) {
+  const bool persistent = p->bsr.enabled && !std::getenv("SBA_PCG_LAUNCHES");
+  if (persistent) {  // explicit block-sparse S: the whole solve is one cooperative kernel (pcg_blocks.cu)
+    const int rc = SolvePCGBlocks(p, o);
+    if (rc) return rc;
+  } else {
+    cg_init_kernel<<<1, kCgThreads, 0, st>>>(n, b, x, p->d_cg_r.p, sc);
+    p->launches++;
+  }
+  for (int it = 1; it <= max_it && !persistent; ++it) {
     cg_direction_kernel<<<1, kCgThreads, 0, st>>>(n, it, p->d_col_blk.p, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,
                                                   p->d_Minv.p, p->d_cg_r.p, p->d_cg_z.p, p->d_cg_p.p, sc);
     p->launches++;

@@ -60,12 +60,14 @@ __device__ inline int SlotCol(const StructView& S, int i, int c, int j) {
 }
 
 // Destination of a block element.  kind 0: dense lower-triangular S (row-major n x n);
-// kind 1: SCHUR_JACOBI block-diagonal storage.
+// kind 1: SCHUR_JACOBI block-diagonal storage; kind 2: block-sparse S in SLOT space (bsr.cu): block i < n_img is
+// the full diagonal block of image i, block n_img + key the (gi > gj) block of a camera-pair key.
 struct Sink {
   int kind;
   double* S; int n;                 // dense
   double* M; const int* col_blk; const int* blk_off; const int* blk_dim; const int* blk_moff;  // block diagonal
   int shared_intr;                  // intrinsics columns have several writers -> atomics
+  double* B; int n_img; const int* key_block;  // block-sparse: key -> block index (null: n_img + key)
 };
 
 // same_image: the block is a diagonal (i,i) block made of ordered pairs -> keep only row >= col;
@@ -138,6 +140,7 @@ __global__ void __launch_bounds__(128) schur_diag_finalize_kernel(StructView S, 
   for (int e = threadIdx.x; e < DC * DC; e += 128) {
     double a = 0.0;
     for (int ch = c0; ch < c1; ++ch) a += partial[(size_t)ch * DC * DC + e];
+    if (sink.kind == 2) { sink.B[(size_t)i * DC * DC + e] = a; continue; }
     const int ja = e / DC, jb = e - ja * DC;
     const bool atomic = sink.shared_intr && (ja >= 6 || jb >= 6);
     Emit(sink, SlotCol(S, i, c, ja), SlotCol(S, i, c, jb), a, true, atomic);
@@ -202,6 +205,11 @@ __global__ void __launch_bounds__(128) schur_pair_emit_kernel(StructView S, int 
     if (e >= DC * DC) continue;
     double a = 0.0;
     for (int sg = s0; sg < s1; ++sg) a += partial[(size_t)sg * DC * DC + e];
+    if (sink.kind == 2) {  // single writer per entry: the diagonal blocks were written by the finalize kernel before
+      if (same) sink.B[(size_t)gi * DC * DC + e] += a;
+      else sink.B[(size_t)(sink.key_block ? sink.key_block[key] : sink.n_img + key) * DC * DC + e] = a;
+      continue;
+    }
     const int ja = e / DC, jb = e - ja * DC;
     // duplicate-observation keys (same image) add on top of the chunk result -> atomics
     const bool atomic = same || (sink.shared_intr && (ja >= 6 || jb >= 6));
@@ -328,6 +336,11 @@ __global__ void __launch_bounds__(64) schur_diag_finalize_tri_kernel(StructView 
     int ja = 0;
     while ((ja + 1) * (ja + 2) / 2 <= e) ++ja;
     const int jb = e - ja * (ja + 1) / 2;
+    if (sink.kind == 2) {
+      double* blk = sink.B + (size_t)i * DC * DC;
+      blk[ja * DC + jb] = a; blk[jb * DC + ja] = a;
+      continue;
+    }
     int row = SlotCol(S, i, c, ja), col = SlotCol(S, i, c, jb);
     if (row < col) { const int x = row; row = col; col = x; }  // the block is symmetric: store its lower image
     const bool atomic = sink.shared_intr && (ja >= 6 || jb >= 6);
@@ -568,6 +581,68 @@ int BuildSchurJacobi(Problem* p) {
   invert_blocks_kernel<<<DivUp(p->n_blk, 64), 64, 0, p->stream>>>(p->n_blk, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,
                                                                  p->d_M.p, p->d_Dc.p, p->d_Minv.p, p->d_scalars.p);
   p->launches++;
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
+// SCHUR_JACOBI blocks out of the diagonal blocks of the block-sparse S (every parameter block lies inside one image)
+template <int DC>
+__global__ void __launch_bounds__(128) bsr_extract_jacobi_kernel(StructView S, const double* __restrict__ B, Sink sink) {
+  const int i = blockIdx.x, c = S.img_cam[i];
+  for (int e = threadIdx.x; e < DC * DC; e += 128) {
+    const int ja = e / DC, jb = e - ja * DC;
+    Emit(sink, SlotCol(S, i, c, ja), SlotCol(S, i, c, jb), B[(size_t)i * DC * DC + e], true, false);
+  }
+}
+
+// the inverted SCHUR_JACOBI blocks re-laid per image in slot space, for the persistent PCG kernel (pcg_blocks.cu)
+template <int DC>
+__global__ void __launch_bounds__(128) bsr_precond_slots_kernel(StructView S, const int* __restrict__ col_blk,
+                                                                const int* __restrict__ blk_off, const int* __restrict__ blk_dim,
+                                                                const int* __restrict__ blk_moff, const double* __restrict__ Minv,
+                                                                double* __restrict__ out) {
+  const int i = blockIdx.x, c = S.img_cam[i];
+  for (int e = threadIdx.x; e < DC * DC; e += 128) {
+    const int ja = e / DC, jb = e - ja * DC;
+    const int row = SlotCol(S, i, c, ja), col = SlotCol(S, i, c, jb);
+    double v = 0.0;
+    if (row >= 0 && col >= 0 && col_blk[row] == col_blk[col]) {
+      const int b = col_blk[row], o = blk_off[b], d = blk_dim[b];
+      v = Minv[blk_moff[b] + (size_t)(row - o) * d + (col - o)];
+    }
+    out[(size_t)i * DC * DC + e] = v;
+  }
+}
+
+// Block-sparse S (bsr.cu) and the SCHUR_JACOBI preconditioner read off its diagonal blocks.
+int BuildExplicitSchur(Problem* p) {
+  BlockSchur& B = p->bsr;
+  int rc = EnsureBlockStorage(p);
+  if (rc) return rc;
+  const size_t ne = (size_t)p->dc * p->dc;
+  SBA_CUDA(cudaMemsetAsync(B.blocks.p, 0, (size_t)B.n_blocks * ne * sizeof(double), p->stream));
+  Sink sink;
+  std::memset(&sink, 0, sizeof(sink));
+  sink.kind = 2; sink.B = B.blocks.p; sink.n_img = p->n_img; sink.key_block = p->comm ? B.key_block.p : nullptr;
+  rc = Accumulate(p, p->pairs_dense, sink);
+  if (rc) return rc;
+  rc = AllReduceSum(p, B.blocks.p, (size_t)B.n_blocks * ne);
+  if (rc) return rc;
+  if (p->n_blk == 0) return SBA_OK;
+  Sink m;
+  std::memset(&m, 0, sizeof(m));
+  m.kind = 1; m.M = p->d_M.p; m.col_blk = p->d_col_blk.p; m.blk_off = p->d_blk_off.p;
+  m.blk_dim = p->d_blk_dim.p; m.blk_moff = p->d_blk_moff.p;
+#define CALL(DC) bsr_extract_jacobi_kernel<DC><<<p->n_img, 128, 0, p->stream>>>(p->Struct(), B.blocks.p, m)
+  SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+  invert_blocks_kernel<<<DivUp(p->n_blk, 64), 64, 0, p->stream>>>(p->n_blk, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,
+                                                                 p->d_M.p, p->d_Dc.p, p->d_Minv.p, p->d_scalars.p);
+  SBA_CUDA(B.minv_s.Alloc((size_t)p->n_img * ne));
+#define CALL(DC) bsr_precond_slots_kernel<DC><<<p->n_img, 128, 0, p->stream>>>(p->Struct(), p->d_col_blk.p, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p, p->d_Minv.p, B.minv_s.p)
+  SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+  p->launches += 3;
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }

@@ -114,6 +114,24 @@ struct PairList {
   bool built = false;
 };
 
+// Explicit block-sparse reduced camera matrix for the iterative solver (bsr.cu): blocks live in SLOT space (dc x dc
+// per camera pair), block i < n_img = diagonal block of image i, block n_img + k = global camera-pair key k (gi > gj).
+struct BlockSchur {
+  bool decided = false, enabled = false;
+  int n_keys = 0;                    // global camera-pair keys (same on every rank)
+  int64_t n_blocks = 0, n_entries = 0;
+  DevBuf<double> blocks;             // [n_blocks * dc * dc]
+  DevBuf<int> row_ptr;               // [n_img + 1] into entries
+  DevBuf<int2> entries;              // {block, other image | transposed << 31}: diagonal, lower, then upper neighbours
+  DevBuf<int> slot_col;              // [n_img * dc] compact column of a slot or -1
+  DevBuf<int> key_block;             // multi-GPU: local key -> block index (single GPU: n_img + key)
+  int pcg_grid = 0;                  // CTAs of the persistent PCG kernel (pcg_blocks.cu), co-resident by construction
+  int pcg_rows = 0;                  // block rows per CTA
+  DevBuf<double> pcg_partials;       // [3 * pcg_grid]
+  DevBuf<double> minv_s;             // [n_img * dc * dc] SCHUR_JACOBI inverse in slot space (zero outside a parameter block)
+  DevBuf<double> p_s, x_s;           // slot-space CG vectors other CTAs read
+};
+
 struct Problem {
   // ---- sizes ----
   int n_img = 0, n_cam = 0, n_pt = 0;  // global images / cameras, LOCAL points
@@ -154,6 +172,7 @@ struct Problem {
 
   // observation-pair lists for the off-diagonal Schur contributions (schur.cu)
   PairList pairs_dense, pairs_diag;
+  BlockSchur bsr;
   DevBuf<int> d_blk_moff;  int m_size = 0;      // offsets of the SCHUR_JACOBI blocks inside d_M / d_Minv
   DevBuf<double> d_M;                           // block diagonal of S before inversion
   DevBuf<double> d_chunk_block;                 // [n_chunks*dc*dc] per-chunk diagonal block partials
@@ -249,6 +268,7 @@ int ModelCostChange(Problem* p);
 int ApplyStep(Problem* p);
 int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase, bool sync);
 int AllReduceSum(Problem* p, double* d_buf, size_t n);
+int AllReduceMaxInt(Problem* p, int* d_buf, size_t n);
 // pairs.cu
 int BuildPairLists(Problem* p, bool dense);
 // pairs per segment: the lane-per-pair kernels (dc <= 8) amortise one reduction over 4 pairs per lane
@@ -256,6 +276,10 @@ inline int PairSegmentSize(int dc) { return dc <= 8 ? 128 : 32; }
 // schur.cu
 int BuildDenseSchur(Problem* p);
 int BuildSchurJacobi(Problem* p);
+int BuildExplicitSchur(Problem* p);   // iterative solver: block-sparse S + its SCHUR_JACOBI blocks (when bsr.enabled)
+// bsr.cu
+int DecideBlockSchur(Problem* p);     // builds the pair lists and the block structure; sets bsr.enabled
+int BlockSchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip);
 // cholesky.cu
 int CholeskySolve(Problem* p);  // d_S, d_rhs -> d_yc ; sets scalars.chol_fail
 // chol_small.cu
@@ -263,6 +287,7 @@ constexpr int kCholSmallMax = 1024;
 int CholeskySolveSmall(Problem* p);  // n_cdim <= kCholSmallMax: one dataflow kernel
 // pcg.cu
 int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
+int SolvePCGBlocks(Problem* p, const sba_solver_options& o);  // pcg_blocks.cu: one persistent kernel on the block-sparse S
 // lm.cu
 int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, void* user, sba_summary* s);
 // semantic.cu

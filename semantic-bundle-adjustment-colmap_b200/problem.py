@@ -172,6 +172,17 @@ class Solver:
         capi.check(self.lib.sba_bench_stage(self._h, stage.encode(), repeat, C.byref(ms), C.byref(nbytes)))
         return ms.value, nbytes.value
 
+    def schur_product(self, x=None, use_blocks=False):
+        """y = (S + D^2) x of the current linearisation; x=None returns the reduced dimension."""
+        n = C.c_int32()
+        if x is None:
+            capi.check(self.lib.sba_schur_product(self._h, 0, None, None, C.byref(n)))
+            return n.value
+        x = capi.as_f64(x)
+        y = np.zeros_like(x)
+        capi.check(self.lib.sba_schur_product(self._h, 1 if use_blocks else 0, capi.ptr(x, capi._dp), capi.ptr(y, capi._dp), C.byref(n)))
+        return y
+
     def launches(self):
         return int(self.lib.sba_kernel_launch_count(self._h))
 

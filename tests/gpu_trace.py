@@ -7,6 +7,9 @@ prob, _ = m.scene.make_config(name)
 o = m.capi.default_solver_options(); o.max_num_iterations = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 s = m.Solver(prob)
 summ = s.solve(o)
+print("stage ms: evaluate %.2f eliminate %.2f linear_solve %.2f update %.2f ; linear iterations %d" % (
+    summ.time_evaluate_s * 1e3, summ.time_eliminate_s * 1e3, summ.time_linear_solve_s * 1e3, summ.time_update_s * 1e3,
+    summ.num_linear_solver_iterations))
 print("termination", summ.termination_type, "iterations", summ.num_iterations, "device ms", summ.device_time_s * 1e3)
 for t in s.trace():
     print("%3d ok=%d valid=%d cost %.12e change %.3e |g| %.3e step %.3e rho %.3e radius %.3e lin %d" % (
