@@ -14,6 +14,12 @@
 
 namespace sba {
 
+// cam_pos[cam_order[k]] = k: image-major position of a point-sorted observation
+__global__ void invert_order_kernel(int n, const int* __restrict__ order, int* __restrict__ pos) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) pos[order[k]] = k;
+}
+
 __global__ void iota_kernel(unsigned* __restrict__ v, int64_t n) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) v[k] = (unsigned)k;
@@ -50,7 +56,7 @@ int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int 
   SBA_CUDA(p->d_local2ref.Alloc(std::max(1, n_obs)));
   SBA_CUDA(p->d_obs_img.Alloc(std::max(1, n_obs))); SBA_CUDA(p->d_obs_pt.Alloc(std::max(1, n_obs)));
   SBA_CUDA(p->d_obs_xy.Alloc((size_t)std::max(1, n_obs) * 2)); SBA_CUDA(p->d_obs_active.Alloc(std::max(1, n_obs)));
-  SBA_CUDA(p->d_cam_order.Alloc(std::max(1, n_obs)));
+  SBA_CUDA(p->d_cam_order.Alloc(std::max(1, n_obs))); SBA_CUDA(p->d_cam_pos.Alloc(std::max(1, n_obs)));
   if (n_obs == 0 || n_obs_g == 0) return SBA_OK;
   DevBuf<unsigned> idx, keys_out, vals_out, img_key;
   DevBuf<char> tmp;
@@ -72,7 +78,8 @@ int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int 
   // idx[0..n_obs) is still 0,1,2,...: the values of the image sort are the local point-sorted positions
   SBA_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, b2, img_key.p, keys_out.p, idx.p,
                                            reinterpret_cast<unsigned*>(p->d_cam_order.p), n_obs, 0, Bits(p->n_img), st));
-  p->launches += 2;
+  invert_order_kernel<<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, p->d_cam_order.p, p->d_cam_pos.p);
+  p->launches += 3;
   SBA_CUDA(cudaGetLastError());
   SBA_CUDA(cudaStreamSynchronize(st));  // the temporaries above are released on return
   return SBA_OK;

@@ -41,7 +41,8 @@ __device__ inline bool PairEligible(const PairRule& r, int s, int t, int i, int 
 template <int MODE>
 __global__ void __launch_bounds__(256) pair_enum_kernel(int n_obs, int n_img, const int* __restrict__ obs_img,
                                                         const int* __restrict__ obs_pt, const int* __restrict__ pt_ptr,
-                                                        const int* __restrict__ p_off, PairRule rule,
+                                                        const int* __restrict__ p_off, const int* __restrict__ cam_pos,
+                                                        PairRule rule,
                                                         int* __restrict__ cnt, const int* __restrict__ off,
                                                         unsigned* __restrict__ keys, unsigned long long* __restrict__ ab) {
   const int s = blockIdx.x * 256 + threadIdx.x;
@@ -57,7 +58,8 @@ __global__ void __launch_bounds__(256) pair_enum_kernel(int n_obs, int n_img, co
       if (!PairEligible(rule, s, t, i, j)) continue;
       if (MODE) {
         keys[base + c] = (unsigned)i * (unsigned)n_img + (unsigned)j;
-        ab[base + c] = ((unsigned long long)(unsigned)s << 32) | (unsigned)t;
+        // the ids are ROWS of W / H (image-major positions); the order of the pairs is that of the enumeration
+        ab[base + c] = ((unsigned long long)(unsigned)cam_pos[s] << 32) | (unsigned)cam_pos[t];
       }
       ++c;
     }
@@ -119,7 +121,7 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(cnt.Alloc(n_obs)); SBA_CUDA(off.Alloc(n_obs)); SBA_CUDA(totals.Alloc(4));
   int h_total_pairs = 0;
   pair_enum_kernel<0><<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, n_img, p->d_obs_img.p, p->d_obs_pt.p, p->d_pt_ptr.p,
-                                                         p->d_p_off.p, rule, cnt.p, nullptr, nullptr, nullptr);
+                                                         p->d_p_off.p, p->d_cam_pos.p, rule, cnt.p, nullptr, nullptr, nullptr);
   size_t tmp_bytes = 0;
   SBA_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, cnt.p, off.p, n_obs, st));
   DevBuf<char> tmp;
@@ -138,7 +140,7 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(keys.Alloc(n_pairs)); SBA_CUDA(keys_sorted.Alloc(n_pairs));
   SBA_CUDA(ab.Alloc(n_pairs)); SBA_CUDA(L.ab.Alloc(n_pairs));
   pair_enum_kernel<1><<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, n_img, p->d_obs_img.p, p->d_obs_pt.p, p->d_pt_ptr.p,
-                                                         p->d_p_off.p, rule, nullptr, off.p, keys.p, ab.p);
+                                                         p->d_p_off.p, p->d_cam_pos.p, rule, nullptr, off.p, keys.p, ab.p);
   int key_bits = 1;
   while (key_bits < 32 && (1ll << key_bits) < (int64_t)n_img * n_img) ++key_bits;
   size_t sort_bytes = 0, rle_bytes = 0, scan_bytes = 0;

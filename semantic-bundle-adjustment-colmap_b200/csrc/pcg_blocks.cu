@@ -8,7 +8,9 @@
 //     local to its CTA; only the product reads other rows' p (or x);
 //   * the three scalars of an iteration (p.q, r.z, x.(b + r)) are per-CTA partials summed by EVERY CTA in the same
 //     fixed order after a grid barrier, so all CTAs take the same branch without a broadcast;
-//   * three grid barriers per iteration (p complete | p.q | r.z and the stopping test), none of them on the host.
+//   * two grid barriers per iteration (p.q | r.z and the stopping test), none of them on the host: the product forms
+//     the neighbours' direction p_j = z_j + beta p_j(previous) on the fly from two slot-space vectors every CTA
+//     published before the last barrier, instead of waiting for a third barrier after the direction update.
 // Deterministic: fixed ownership, fixed summation order, no atomics.
 #include <cooperative_groups.h>
 
@@ -28,7 +30,8 @@ struct PcgBlocks {
   const double* Minv_s;  // [n_img][DC x DC] SCHUR_JACOBI inverse blocks laid out in slot space (zero outside a block)
   const double* Dc; const double* b;
   double* y;             // compact solution (n_cdim)
-  double *p_s, *x_s;     // slot-space vectors [n_img * DC] read by other CTAs (x_s only on residual-reset iterations)
+  double *p_s, *z_s, *x_s;  // slot-space vectors read by other CTAs: p_s [2][n_img * DC] (ping-pong), z_s, x_s [n_img * DC]
+                            // (x_s only on residual-reset iterations)
   double* partials;      // [3][gridDim.x]
   DeviceScalars* sc;
   int n_img, rows_per_cta, min_it, max_it;
@@ -63,12 +66,14 @@ __device__ inline double GridTotal(const double* partials, int G) {
 
 __device__ inline bool BadScalar(double x) { return x == 0.0 || isinf(x) || isnan(x); }
 
-// (S v) restricted to the rows of image i, v in slot space; thread r < DC returns the entry of slot r.
+// (S u) restricted to the rows of image i, u = v + beta vold in slot space (vold may be null); thread r < DC returns
+// the entry of slot r.
 // A warp takes a contiguous quarter of the row's entries: one coalesced load brings 32 of them, the loop below then
 // has no load that depends on another load, so several blocks are in flight per warp.
 // v is written by other CTAs during the kernel: plain loads only.
 template <int DC>
-__device__ inline double RowProduct(const PcgBlocks& a, int i, const double* v, double (*red)[2][DC * DC]) {
+__device__ inline double RowProduct(const PcgBlocks& a, int i, const double* v, const double* vold, double beta,
+                                    double (*red)[2][DC * DC]) {
   constexpr int NE = DC * DC, N = (NE + 31) / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int er[N], ec[N];
@@ -89,7 +94,11 @@ __device__ inline double RowProduct(const PcgBlocks& a, int i, const double* v, 
     for (int k = 0; k < m; ++k) {
       const int blk_id = __shfl_sync(0xffffffffu, mine.x, k), jy = __shfl_sync(0xffffffffu, mine.y, k);
       const int j = jy & 0x7fffffff;
-      const double xv = lane < DC ? v[(size_t)j * DC + lane] : 0.0;
+      double xv = 0.0;
+      if (lane < DC) {
+        xv = v[(size_t)j * DC + lane];
+        if (vold) xv += beta * vold[(size_t)j * DC + lane];  // the direction of row j, as its owner forms it
+      }
       const double* blk = a.B + (size_t)blk_id * NE;
       double w[N];
 #pragma unroll
@@ -149,6 +158,7 @@ __global__ void __launch_bounds__(128) pcg_blocks_kernel(PcgBlocks a) {
 #pragma unroll
       for (int c = 0; c < DC; ++c) zj += m[c] * rs[r0 + c];
       zs[k] = zj;
+      a.z_s[(size_t)image_of(k) * DC + slot] = zj;
       rz += rs[k] * zj;
     }
     return rz;
@@ -162,7 +172,10 @@ __global__ void __launch_bounds__(128) pcg_blocks_kernel(PcgBlocks a) {
     const double v = col >= 0 ? a.b[col] : 0.0, d = col >= 0 ? a.Dc[col] : 0.0;
     xs[k] = 0.0; rs[k] = v; bs[k] = v; zs[k] = 0.0; qs[k] = 0.0; ps[k] = 0.0; ds[k] = d * d;
     s += v * v;
-    if (i < a.n_img) { a.p_s[(size_t)i * DC + k % DC] = 0.0; a.x_s[(size_t)i * DC + k % DC] = 0.0; }
+    if (i < a.n_img) {
+      const size_t g = (size_t)i * DC + k % DC;
+      a.p_s[g] = 0.0; a.p_s[(size_t)a.n_img * DC + g] = 0.0; a.z_s[g] = 0.0; a.x_s[g] = 0.0;
+    }
   }
   s = BlockAllSum128(s);  // (also orders rs for the preconditioner below)
   if (t == 0) PA[blockIdx.x] = s;
@@ -186,19 +199,21 @@ __global__ void __launch_bounds__(128) pcg_blocks_kernel(PcgBlocks a) {
         if (BadScalar(beta)) { state = 3; iter = it; break; }
       }
       last_rho = rho; rho = rho_new;
+      // p = z + beta p: own rows here (published for the NEXT iteration's products), neighbours inside the product
+      const double* p_prev = a.p_s + (size_t)((it - 1) & 1) * a.n_img * DC;
+      double* p_cur = a.p_s + (size_t)(it & 1) * a.n_img * DC;
       for (int k = t; k < M; k += 128) {
         if (cols[k] < 0) continue;
-        const double pv = (it == 1) ? zs[k] : zs[k] + beta * ps[k];
+        const double pv = zs[k] + beta * ps[k];  // beta = 0 and p = 0 in the first iteration
         ps[k] = pv;
-        a.p_s[(size_t)image_of(k) * DC + k % DC] = pv;
+        p_cur[(size_t)image_of(k) * DC + k % DC] = pv;
       }
       PcgStamp(a, it, 1);
-      grid.sync();  // p complete
       PcgStamp(a, it, 2);
       for (int lr = 0; lr < R; ++lr) {
         const int i = blockIdx.x + lr * G;
         if (i >= a.n_img) break;
-        const double v = RowProduct<DC>(a, i, a.p_s, red);
+        const double v = RowProduct<DC>(a, i, a.z_s, p_prev, beta, red);
         if (t < DC) qs[lr * DC + t] = v;
       }
       __syncthreads();
@@ -230,7 +245,7 @@ __global__ void __launch_bounds__(128) pcg_blocks_kernel(PcgBlocks a) {
         for (int lr = 0; lr < R; ++lr) {
           const int i = blockIdx.x + lr * G;
           if (i >= a.n_img) break;
-          const double v = RowProduct<DC>(a, i, a.x_s, red);
+          const double v = RowProduct<DC>(a, i, a.x_s, nullptr, 0.0, red);
           if (t < DC) qs[lr * DC + t] = v;
         }
         __syncthreads();
@@ -301,12 +316,13 @@ int SolvePCGBlocks(Problem* p, const sba_solver_options& o) {
     B.pcg_rows = DivUp(p->n_img, grid);
     SBA_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem_for(B.pcg_rows), 1024)));
     SBA_CUDA(B.pcg_partials.Alloc((size_t)3 * B.pcg_grid));
-    SBA_CUDA(B.p_s.Alloc((size_t)p->n_img * dc)); SBA_CUDA(B.x_s.Alloc((size_t)p->n_img * dc));
+    SBA_CUDA(B.p_s.Alloc((size_t)2 * p->n_img * dc)); SBA_CUDA(B.x_s.Alloc((size_t)p->n_img * dc));
+    SBA_CUDA(B.z_s.Alloc((size_t)p->n_img * dc));
   }
   PcgBlocks a;
   a.row_ptr = B.row_ptr.p; a.entries = B.entries.p; a.B = B.blocks.p; a.slot_col = B.slot_col.p;
   a.Minv_s = B.minv_s.p; a.Dc = p->d_Dc.p; a.b = p->d_rhs.p; a.y = p->d_yc.p;
-  a.p_s = B.p_s.p; a.x_s = B.x_s.p;
+  a.p_s = B.p_s.p; a.x_s = B.x_s.p; a.z_s = B.z_s.p;
   a.partials = B.pcg_partials.p; a.sc = p->d_scalars.p;
   a.n_img = p->n_img; a.rows_per_cta = B.pcg_rows;
   a.min_it = o.min_linear_solver_iterations; a.max_it = std::max(1, o.max_linear_solver_iterations);
@@ -322,7 +338,7 @@ int SolvePCGBlocks(Problem* p, const sba_solver_options& o) {
     std::vector<long long> h(64 * 8);
     SBA_CUDA(cudaMemcpyAsync(h.data(), trace.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, p->stream));
     SBA_CUDA(cudaStreamSynchronize(p->stream));
-    std::fprintf(stderr, "[pcg trace] grid %d rows/cta %d : it | totals+p | sync1 | product | sync2 | update+precond | sync3 (us)\n", B.pcg_grid, B.pcg_rows);
+    std::fprintf(stderr, "[pcg trace] grid %d rows/cta %d : it | totals+p | - | product | sync(p.q) | update+precond | sync(r.z) (us)\n", B.pcg_grid, B.pcg_rows);
     for (int it = 1; it < 16 && h[it * 8 + 6]; ++it) {
       const long long* r = &h[it * 8];
       std::fprintf(stderr, "[pcg trace] %2d | %6.2f | %6.2f | %6.2f | %6.2f | %6.2f | %6.2f\n", it, (r[1] - r[0]) * 1e-3,

@@ -35,15 +35,17 @@ namespace sba {
 
 template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; };
 
-// W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (observation, slot)
+// W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (image-major position, slot) -- the rows of W / H are stored in
+// image-major order so that a chunk's rows are contiguous
 template <int DC>
-__global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const D4* __restrict__ ER,
+__global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const int* __restrict__ cam_order, const D4* __restrict__ ER,
                                                        const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                        double* __restrict__ W, double* __restrict__ H) {
   const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (t >= (int64_t)S.n_obs * DC) return;
-  const int a = (int)(t / DC);
-  const double2 f = LoadSlot(F, a, (int)(t - (int64_t)a * DC), DC / 2);
+  const int pos = (int)(t / DC);
+  const int a = cam_order[pos];
+  const double2 f = LoadSlot(F, a, (int)(t - (int64_t)pos * DC), DC / 2);
   const D4 ea = Ld256(ER + EUnit(a, 0));                                          // E0 E1 E2 E3
   const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];       // E4 E5
   const double w[3] = {f.x * ea.x + f.y * ea.w, f.x * ea.y + f.y * eb.x, f.x * ea.z + f.y * eb.y};
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, cons
   const int lo = w * 32, hi = min(n, lo + 32);
   for (int t = lo; t < hi; ++t) {
     const int obs = C.cam_order[s0 + t];
-    const size_t a = (size_t)obs * DC;
+    const size_t a = (size_t)(s0 + t) * DC;  // row of W / H
 #pragma unroll
     for (int q = 0; q < Elems<DC>::N; ++q) {
       const double2 fa = LoadSlot(F, obs, ja[q], DC / 2), fb = LoadSlot(F, obs, jb[q], DC / 2);
@@ -290,14 +292,16 @@ __global__ void __launch_bounds__(256) schur_obs_lane_kernel(StructView S, Chunk
                                     (h[ja][0] * w[jb][0] + h[ja][1] * w[jb][1] + h[ja][2] * w[jb][2]);
   }
   __syncwarp();
-  {  // copy-out of this warp's 32 x 2 rows: chunk k -> observation k / (2 CH), row (k / CH) & 1, 16 B unit k % CH
-    const double2* src = reinterpret_cast<const double2*>(stage) + (size_t)(t & ~31) * RU;
+  {  // copy-out: the rows of W / H are image-major, so this warp's 32 rows are one contiguous run of 32 x CH units
+    const int wb = t & ~31, nw = min(32, n - wb);
+    const double2* src = reinterpret_cast<const double2*>(stage) + (size_t)wb * RU;
+    double2* wdst = reinterpret_cast<double2*>(W + (size_t)(s0 + wb) * DC * 3);
+    double2* hdst = reinterpret_cast<double2*>(H + (size_t)(s0 + wb) * DC * 3);
 #pragma unroll
-    for (int i = 0; i < 2 * CH; ++i) {
+    for (int i = 0; i < CH; ++i) {
       const int k = lane + 32 * i;
-      const int o = k / (2 * CH), rem = k - o * (2 * CH), row = rem / CH, c = rem - row * CH;
-      const int ao = __shfl_sync(0xffffffffu, a, o);
-      if (ao >= 0) reinterpret_cast<double2*>((row ? H : W) + (size_t)ao * DC * 3)[c] = src[(size_t)(row * 256 + o) * RU + c];
+      const int o = k / CH, c = k - o * CH;
+      if (o < nw) { wdst[k] = src[(size_t)o * RU + c]; hdst[k] = src[(size_t)(256 + o) * RU + c]; }
     }
   }
   __syncthreads();  // staging area is reused by the reduction
@@ -523,7 +527,7 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
   if (dc == 8) { SBA_CUDA(AccumulateLane<8>(p, L, sink)); return SBA_OK; }
 #define CALL(DC)                                                                                                          \
   do {                                                                                                                    \
-    schur_wh_kernel<DC><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, \
+    schur_wh_kernel<DC><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_cam_order.p, p->d_ER.p, p->d_F.p, p->d_Cinv.p, \
                                                                           p->d_W.p, p->d_H.p);                            \
     schur_diag_chunk_kernel<DC><<<p->n_chunks, 256, 0, st>>>(p->Chunks(), p->d_F.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p); \
     schur_diag_finalize_kernel<DC><<<p->n_img, 128, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);          \

@@ -129,7 +129,7 @@ struct BlockSchur {
   int pcg_rows = 0;                  // block rows per CTA
   DevBuf<double> pcg_partials;       // [3 * pcg_grid]
   DevBuf<double> minv_s;             // [n_img * dc * dc] SCHUR_JACOBI inverse in slot space (zero outside a parameter block)
-  DevBuf<double> p_s, x_s;           // slot-space CG vectors other CTAs read
+  DevBuf<double> p_s, z_s, x_s;      // slot-space CG vectors other CTAs read (p_s: two buffers)
 };
 
 struct Problem {
@@ -166,6 +166,7 @@ struct Problem {
   DevBuf<uint8_t> d_obs_active, d_pose_const;
   DevBuf<int> d_tile_start;  int n_tiles = 0;
   DevBuf<int> d_chunk_start, d_chunk_img, d_cam_order, d_img_chunk_ptr, d_cam_img_ptr, d_cam_img_list;
+  DevBuf<int> d_cam_pos;     // [n_obs] inverse of d_cam_order: image-major position of an observation (rows of d_W / d_H)
   int n_chunks = 0;
   DevBuf<int> d_pt_ptr;      // [n_pt+1] CSR over point-sorted observations
   DevBuf<int> d_blk_off, d_blk_dim, d_col_blk;  int n_blk = 0;
@@ -176,7 +177,7 @@ struct Problem {
   DevBuf<int> d_blk_moff;  int m_size = 0;      // offsets of the SCHUR_JACOBI blocks inside d_M / d_Minv
   DevBuf<double> d_M;                           // block diagonal of S before inversion
   DevBuf<double> d_chunk_block;                 // [n_chunks*dc*dc] per-chunk diagonal block partials
-  DevBuf<double> d_W, d_H;                      // [n_obs*dc*3] F^T E and F^T E C^{-1}
+  DevBuf<double> d_W, d_H;                      // [n_obs*dc*3] F^T E and F^T E C^{-1}, rows in IMAGE-MAJOR order (d_cam_pos)
 
   // ---- device: parameters (current / candidate) ----
   DevBuf<double> d_pose, d_cam, d_X, d_pose2, d_cam2, d_X2;
