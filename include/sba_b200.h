@@ -263,6 +263,9 @@ int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec,
  * returns the mean CUDA-event time per launch in milliseconds. */
 int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms_per_launch,
                     int64_t* algorithmic_bytes);
+/* Device blocks released by destroyed handles are kept (per device, up to a third of its memory) for the next handle
+ * of the same shape; this hands them all back to the driver's pool.  Current device; no handle may be in a call. */
+void sba_release_cached_memory(void);
 /* Parity surface for the reduced camera system: y = (S + D^2) x of the current linearisation (Jacobi-scaled, LM
  * diagonal of the default options), through the implicit products (use_blocks = 0; what Ceres' ITERATIVE_SCHUR does,
  * SURVEY.md App. B.5) or the explicit block-sparse S (use_blocks = 1; SBA_ERR_INVALID_ARGUMENT when the problem does

@@ -334,6 +334,8 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
   return SBA_OK;
 }
 
+void sba_release_cached_memory(void) { ReleaseCachedBlocks(); }
+
 int sba_schur_product(sba_handle* h, int32_t use_blocks, const double* x, double* y, int32_t* n) {
   int rc = CheckHandle(h);
   if (rc) return rc;

@@ -139,6 +139,7 @@ int BuildPairLists(Problem* p, bool dense) {
   DevBuf<unsigned long long> ab;
   SBA_CUDA(keys.Alloc(n_pairs)); SBA_CUDA(keys_sorted.Alloc(n_pairs));
   SBA_CUDA(ab.Alloc(n_pairs)); SBA_CUDA(L.ab.Alloc(n_pairs));
+  tm.Lap("pair buffers");
   pair_enum_kernel<1><<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, n_img, p->d_obs_img.p, p->d_obs_pt.p, p->d_pt_ptr.p,
                                                          p->d_p_off.p, p->d_cam_pos.p, rule, nullptr, off.p, keys.p, ab.p);
   int key_bits = 1;
@@ -153,6 +154,8 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(cub::DeviceRunLengthEncode::Encode(nullptr, rle_bytes, keys_sorted.p, ukeys.p, kcnt.p, n_keys_d.p, n_pairs, st));
   SBA_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, kcnt.p, key_ptr.p, key_cap, st));
   SBA_CUDA(tmp.Alloc(std::max(sort_bytes, std::max(rle_bytes, scan_bytes))));
+  SBA_CUDA(cudaStreamSynchronize(st));
+  tm.Lap("enumerate + key buffers");
   size_t b = sort_bytes;
   SBA_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, b, keys.p, keys_sorted.p, ab.p,
                                            L.ab.p, n_pairs, 0, key_bits, st));
@@ -174,8 +177,9 @@ int BuildPairLists(Problem* p, bool dense) {
   SBA_CUDA(cudaMemcpyAsync(h_totals, totals.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
   SBA_CUDA(cudaStreamSynchronize(st));  // also: the temporaries above may go out of scope
   L.n_keys = h_totals[0]; L.n_seg = h_totals[1]; L.n_pairs = n_pairs;
+  tm.Lap("sort + segments");
   SBA_CUDA(L.partial.Alloc((size_t)std::max(1, L.n_seg) * p->dc * p->dc));
-  tm.Lap("enumerate + sort + segments");
+  tm.Lap("segment partials buffer");
   return SBA_OK;
 }
 

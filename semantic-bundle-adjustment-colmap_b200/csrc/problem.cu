@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <atomic>
 #include <condition_variable>
+#include <map>
 #include <mutex>
 #include <numeric>
 #include <thread>
@@ -124,6 +125,67 @@ cudaStream_t AllocStream() {
     }
   }
   return streams[dev];
+}
+
+namespace {
+struct BlockCache {
+  std::mutex mu;
+  std::multimap<size_t, void*> free_blocks[64];
+  size_t cached_bytes[64] = {};
+};
+BlockCache g_blocks;
+}  // namespace
+
+cudaError_t CachedAlloc(void** ptr, size_t bytes, size_t* cap) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  bytes = (bytes + 511) / 512 * 512;
+  {
+    std::lock_guard<std::mutex> lk(g_blocks.mu);
+    auto& fb = g_blocks.free_blocks[dev];
+    auto it = fb.lower_bound(bytes);
+    if (it != fb.end() && it->first <= bytes + bytes / 8 + 65536) {  // a block at most ~12 % larger
+      *ptr = it->second; *cap = it->first;
+      g_blocks.cached_bytes[dev] -= it->first;
+      fb.erase(it);
+      return cudaSuccess;
+    }
+  }
+  *cap = bytes;
+  cudaError_t e = cudaMallocAsync(ptr, bytes, AllocStream());
+  if (e != cudaSuccess) {  // out of memory with blocks parked in the cache: give them back and retry once
+    cudaGetLastError();
+    ReleaseCachedBlocks();
+    e = cudaMallocAsync(ptr, bytes, AllocStream());
+  }
+  // the allocation stream carries no kernels, so this returns at once; it makes the block usable from any stream
+  return e == cudaSuccess ? cudaStreamSynchronize(AllocStream()) : e;
+}
+
+// Contract (DevBuf): the stream that used the block has been synchronised, so any stream may reuse it at once.
+void CachedFree(void* ptr, size_t cap) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  size_t free_b = 0, total_b = 0;
+  static size_t limit[64] = {};
+  if (!limit[dev] && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) limit[dev] = total_b / 3;
+  std::lock_guard<std::mutex> lk(g_blocks.mu);
+  if (cap == 0 || g_blocks.cached_bytes[dev] + cap > limit[dev]) { cudaFreeAsync(ptr, AllocStream()); return; }
+  g_blocks.free_blocks[dev].emplace(cap, ptr);
+  g_blocks.cached_bytes[dev] += cap;
+}
+
+void ReleaseCachedBlocks() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  std::lock_guard<std::mutex> lk(g_blocks.mu);
+  for (auto& kv : g_blocks.free_blocks[dev]) cudaFreeAsync(kv.second, AllocStream());
+  g_blocks.free_blocks[dev].clear();
+  g_blocks.cached_bytes[dev] = 0;
+  cudaStreamSynchronize(AllocStream());
 }
 
 // A handle's stream and its pinned scalar block are recycled across handles of the same device:

@@ -18,6 +18,12 @@ namespace sba {
 // create and destroy after the first handle, instead of a cudaMalloc / synchronising cudaFree each.
 // Contract: a buffer is freed only after the stream that used it has been synchronised (sba_destroy does).
 cudaStream_t AllocStream();  // problem.cu
+// Blocks released by a handle are kept in a per-device size-keyed cache and handed to the next request of (nearly)
+// the same size: repeated problems of one shape then make no driver allocation call at all -- the pool's own reuse
+// costs tens of milliseconds now and then once blocks reach hundreds of MB.  `*cap` receives the true block size.
+cudaError_t CachedAlloc(void** ptr, size_t bytes, size_t* cap);
+void CachedFree(void* ptr, size_t cap);
+void ReleaseCachedBlocks();  // current device: hand every cached block back to the pool
 
 template <typename T>
 struct DevBuf {
@@ -28,9 +34,10 @@ struct DevBuf {
   DevBuf& operator=(const DevBuf&) = delete;
   ~DevBuf() { Free(); }
   bool owned = true;  // false: a view into a DeviceArena block
+  size_t cap_bytes = 0;  // true size of the owned block (CachedAlloc may hand out a slightly larger one)
   void Free() {
-    if (p && owned) cudaFreeAsync(p, AllocStream());
-    p = nullptr; n = 0; owned = true;
+    if (p && owned) CachedFree(p, cap_bytes);
+    p = nullptr; n = 0; owned = true; cap_bytes = 0;
   }
   void View(T* ptr, size_t count) { Free(); p = ptr; n = count; owned = false; }
   cudaError_t Alloc(size_t count) {
@@ -38,9 +45,7 @@ struct DevBuf {
     if (p) cudaDeviceSynchronize();  // growing a live buffer: nothing in flight may still read the old one
     Free();
     n = count;
-    cudaError_t e = cudaMallocAsync((void**)&p, (count ? count : 1) * sizeof(T), AllocStream());
-    // the allocation stream carries no kernels, so this returns at once; it makes the block usable from any stream
-    return e == cudaSuccess ? cudaStreamSynchronize(AllocStream()) : e;
+    return CachedAlloc((void**)&p, (count ? count : 1) * sizeof(T), &cap_bytes);
   }
   cudaError_t Upload(const std::vector<T>& h, cudaStream_t s) {
     cudaError_t e = Alloc(h.size());

@@ -6,7 +6,7 @@ name = sys.argv[1] if len(sys.argv) > 1 else "C2"
 maps = (len(sys.argv) > 2 and sys.argv[2] == "maps")
 prob, _ = m.scene.make_config(name, label_maps=maps)
 o = m.capi.default_solver_options(); o.max_num_iterations = 10
-for it in range(4):
+for it in range(int(os.environ.get('E2E_ROUNDS', '4'))):
     t0 = time.perf_counter(); s = m.Solver(prob)
     t1 = time.perf_counter(); summ = s.solve(o)
     t2 = time.perf_counter(); s.parameters()
