@@ -3,7 +3,8 @@
 The product is `libsba_b200.so` (CUDA, sm_100a; C ABI in include/sba_b200.h).  This package
 is the host-side mirror used by tests and bench.py: ctypes binding (`_capi`), flattened problem
 + handle wrapper (`problem`), the BundleAdjuster / BundleAdjustmentConfig /
-BundleAdjustmentOptions mirror (`bundle_adjustment`) and the synthetic scene generator (`scene`).
+BundleAdjustmentOptions mirror (`bundle_adjustment`), the synthetic scene generator (`scene`) and the on-disk formats
+either side of the path (`model_io`: sparse model binary / text, float32 TIFF maps, cylinders.txt).
 """
 from . import _capi as capi  # noqa: F401
 from .problem import FlatProblem, Solver, comm_unique_id  # noqa: F401
@@ -11,3 +12,4 @@ from .bundle_adjustment import (  # noqa: F401
     BundleAdjuster, BundleAdjustmentConfig, BundleAdjustmentOptions, Camera, Image, Point2D, Point3D,
     Reconstruction, Track, TrackElement)
 from . import scene  # noqa: F401
+from . import model_io  # noqa: F401

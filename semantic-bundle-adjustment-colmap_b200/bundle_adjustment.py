@@ -58,9 +58,10 @@ class Point2D:
 
 
 class Point3D:
-    def __init__(self, xyz):
+    def __init__(self, xyz, color=(0, 0, 0), error=-1.0):
         self.xyz = np.asarray(xyz, dtype=np.float64).copy()
         self.track = Track()
+        self.color, self.error = tuple(int(c) for c in color), float(error)  # src/base/point3d.h (Color, Error)
 
     def XYZ(self):
         return self.xyz
@@ -70,8 +71,8 @@ class Point3D:
 
 
 class Camera:
-    def __init__(self, camera_id, model, params):
-        self.camera_id = camera_id
+    def __init__(self, camera_id, model, params, width=0, height=0):
+        self.camera_id, self.width, self.height = camera_id, int(width), int(height)
         self.model_id = capi.CAMERA_MODELS[model] if isinstance(model, str) else int(model)
         if self.model_id not in capi.MODEL_NUM_PARAMS:
             raise ValueError("Camera model does not exist")  # std::domain_error, camera_models.h:140
@@ -97,8 +98,8 @@ class Camera:
 
 
 class Image:
-    def __init__(self, image_id, camera_id, qvec=(1, 0, 0, 0), tvec=(0, 0, 0)):
-        self.image_id, self.camera_id = image_id, camera_id
+    def __init__(self, image_id, camera_id, qvec=(1, 0, 0, 0), tvec=(0, 0, 0), name=""):
+        self.image_id, self.camera_id, self.name = image_id, camera_id, name
         self.qvec = np.asarray(qvec, dtype=np.float64).copy()
         self.tvec = np.asarray(tvec, dtype=np.float64).copy()
         self.points2D = []
@@ -146,6 +147,16 @@ class Reconstruction:
             self.images[image_id].points2D[idx].point3D_id = pid
         self.points3D[pid] = p
         return pid
+
+    def AddPoint3DWithId(self, point3D_id, xyz, track_elements, color=(0, 0, 0), error=-1.0):
+        """A point read from a model file (src/base/reconstruction.cc:1640-1680): its id and track come from the file; the
+        images' Point2D::point3D_id stay as the image file stored them."""
+        p = Point3D(xyz, color, error)
+        for image_id, idx in track_elements:
+            p.track.AddElement(image_id, idx)
+        self.points3D[point3D_id] = p
+        self._next_point3D_id = max(self._next_point3D_id, point3D_id + 1)
+        return point3D_id
 
     def Camera(self, camera_id):
         return self.cameras[camera_id]

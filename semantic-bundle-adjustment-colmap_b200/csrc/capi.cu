@@ -277,7 +277,14 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
     run = [&]() { return ReducedRhs(p); };
     bytes = n_obs * (64 + 16 * dc + 16 + 16 + 8);
   } else if (s == "matvec") {
-    run = [&]() { return SchurMatVec(p, p->d_rhs.p, p->d_tmp_c.p); };
+    // the IMPLICIT product (what Ceres' ITERATIVE_SCHUR does), also when the problem solves with the block-sparse S
+    run = [&]() {
+      const bool keep = p->bsr.enabled;
+      p->bsr.enabled = false;
+      const int r = SchurMatVec(p, p->d_rhs.p, p->d_tmp_c.p);
+      p->bsr.enabled = keep;
+      return r;
+    };
     // two passes over the stored F (16*dc) + E (48) per observation + 48 B / point
     bytes = n_obs * (2 * 16 * (dc + 3)) + (int64_t)p->n_pvar * 48;
   } else if (s == "backsub") {

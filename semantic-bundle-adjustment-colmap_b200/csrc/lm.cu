@@ -259,9 +259,10 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     radius = hs->radius;
     it.trust_region_radius = radius;
     if (hs->step_accepted) {
-      std::swap(p->d_pose.p, p->d_pose2.p);
-      std::swap(p->d_cam.p, p->d_cam2.p);
-      std::swap(p->d_X.p, p->d_X2.p);
+      // (the true block size travels with the pointer: the block cache may have handed one of the two a larger block)
+      std::swap(p->d_pose.p, p->d_pose2.p); std::swap(p->d_pose.cap_bytes, p->d_pose2.cap_bytes);
+      std::swap(p->d_cam.p, p->d_cam2.p);   std::swap(p->d_cam.cap_bytes, p->d_cam2.cap_bytes);
+      std::swap(p->d_X.p, p->d_X2.p);       std::swap(p->d_X.cap_bytes, p->d_X2.cap_bytes);
       p->parity ^= 1;
       auto linearise_segment = [&]() -> int {
         int r;
