@@ -263,6 +263,15 @@ int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec,
  * returns the mean CUDA-event time per launch in milliseconds. */
 int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms_per_launch,
                     int64_t* algorithmic_bytes);
+/* Mapper-side per-observation pass: for every observation of `desc`, in the caller's order,
+ *   sq_error[k] = CalculateSquaredReprojectionError(xy, X, qvec, tvec, camera)   src/base/projection.cc:111-128
+ *                 (DBL_MAX when the point is not in front of the camera), and
+ *   depth[k]    = third row of the projection matrix times the point, the quantity HasPointPositiveDepth tests
+ *                 (src/base/projection.cc:191-195).
+ * Replaces the per-track-element loops of Reconstruction::FilterPoints3DWithLargeReprojectionError and
+ * ::FilterObservationsWithNegativeDepth (src/base/reconstruction.cc:1472-1523, 647-665).  Either output may be NULL.
+ * Only the geometry fields of `desc` are read (no constancy masks, no maps). */
+int sba_observation_errors(const sba_problem_desc* desc, double* sq_error, double* depth);
 /* Device blocks released by destroyed handles are kept (per device, up to a third of its memory) for the next handle
  * of the same shape; this hands them all back to the driver's pool.  Current device; no handle may be in a call. */
 void sba_release_cached_memory(void);

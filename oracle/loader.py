@@ -37,6 +37,8 @@ def load(capi):
     lib.oracle_eval_observation.argtypes = [C.c_int] + [dp] * 10
     lib.oracle_eval_rig_observation.argtypes = [C.c_int] + [dp] * 8
     lib.oracle_eval_rig_observation_jac.argtypes = [C.c_int] + [dp] * 9
+    lib.oracle_observation_error.argtypes = [C.c_int] + [dp] * 7
+    lib.oracle_observation_error.restype = None
     lib.oracle_ba_evaluate.argtypes = [PD, C.c_int, C.c_double, C.c_int, C.c_int, dp, dp, dp, dp, dp, dp]
     lib.oracle_ba_evaluate.restype = C.c_int
     lib.oracle_ba_counts.argtypes = [PD, C.POINTER(capi.Summary)]

@@ -1,6 +1,7 @@
 // ORACLE (test infrastructure only -- never linked into the product library).
 // extern "C" surface of the CPU restatement, loaded with ctypes by tests/,
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+#include <limits>
 #include <omp.h>
 
 #include <cstring>
@@ -24,6 +25,26 @@ void oracle_image_to_world(int model, const double* params, double x, double y, 
   Unproject(model, params, x, y, u, v);
 }
 int oracle_model_num_params(int model) { return NumParams(model); }
+
+// CalculateSquaredReprojectionError (src/base/projection.cc:111-128) and the depth HasPointPositiveDepth tests
+// (:191-195), with the rotation matrix of the normalised quaternion (src/base/pose.cc:63-91).
+void oracle_observation_error(int model, const double* q, const double* t, const double* X, const double* params,
+                              const double* xy, double* sq_error, double* depth) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  const double n = std::sqrt(w * w + x * x + y * y + z * z);
+  if (n == 0.0) { w = 1.0; x = y = z = 0.0; } else { w /= n; x /= n; y /= n; z /= n; }
+  const double R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - w * z),     2 * (x * z + w * y),
+                       2 * (x * y + w * z),     1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                       2 * (x * z - w * y),     2 * (y * z + w * x),     1 - 2 * (x * x + y * y)};
+  const double px = R[0] * X[0] + R[1] * X[1] + R[2] * X[2] + t[0];
+  const double py = R[3] * X[0] + R[4] * X[1] + R[5] * X[2] + t[1];
+  const double pz = R[6] * X[0] + R[7] * X[1] + R[8] * X[2] + t[2];
+  *depth = pz;
+  if (pz < std::numeric_limits<double>::epsilon()) { *sq_error = std::numeric_limits<double>::max(); return; }
+  double ix, iy;
+  Project<double>(model, params, px / pz, py / pz, &ix, &iy);
+  *sq_error = (ix - xy[0]) * (ix - xy[0]) + (iy - xy[1]) * (iy - xy[1]);
+}
 
 // CostFunction::Evaluate of one residual block (cost_functions.h:57-81 / 115-140)
 void oracle_eval_observation(int model, const double* q, const double* t, const double* X,

@@ -13,3 +13,5 @@ from .bundle_adjustment import (  # noqa: F401
     Reconstruction, Track, TrackElement)
 from . import scene  # noqa: F401
 from . import model_io  # noqa: F401
+from . import filters  # noqa: F401
+from . import bundle_adjustment  # noqa: F401

@@ -1,0 +1,169 @@
+"""Mapper-side filters around global BA: per-observation squared reprojection error and depth
+on the device (sba_observation_errors) + the reference's bookkeeping loops (filters.py).
+Reference: src/base/projection.cc:111-128, 191-195; src/base/reconstruction.cc:236-277, 647-665, 1472-1523."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+dp = C.POINTER(C.c_double)
+
+
+def scene_reconstruction(sba, prob):
+    rec = sba.Reconstruction()
+    for c in range(len(prob.camera_model)):
+        mid = int(prob.camera_model[c])
+        rec.AddCamera(sba.Camera(c + 1, mid, prob.camera_params[c, :sba.capi.MODEL_NUM_PARAMS[mid]], width=1000, height=1000))
+    for i in range(len(prob.image_camera)):
+        rec.AddImage(sba.Image(i + 1, int(prob.image_camera[i]) + 1, prob.image_qvec[i], prob.image_tvec[i], name="im%d.png" % i))
+    tracks = {}
+    for k in range(prob.num_observations):
+        img = rec.Image(int(prob.obs_image[k]) + 1)
+        img.points2D.append(sba.Point2D(prob.obs_xy[k].copy()))
+        tracks.setdefault(int(prob.obs_point[k]), []).append((img.image_id, len(img.points2D) - 1))
+    for q in range(len(prob.points)):
+        rec.AddPoint3D(prob.points[q], tracks.get(q, []))
+    return rec
+
+
+def oracle_errors(oracle):
+    def fn(prob):
+        n = prob.num_observations
+        err, depth = np.zeros(n), np.zeros(n)
+        e, z = C.c_double(), C.c_double()
+        for k in range(n):
+            i, q = int(prob.obs_image[k]), int(prob.obs_point[k])
+            c = int(prob.image_camera[i])
+            a = [np.ascontiguousarray(v) for v in (prob.image_qvec[i], prob.image_tvec[i], prob.points[q], prob.camera_params[c], prob.obs_xy[k])]
+            oracle.oracle_observation_error(int(prob.camera_model[c]), *[v.ctypes.data_as(dp) for v in a], C.byref(e), C.byref(z))
+            err[k], depth[k] = e.value, z.value
+        return err, depth
+    return fn
+
+
+def planted(sba, seed=2):
+    prob, _ = sba.scene.make_scene(n_cam=8, n_pt=120, mean_track=4.0, seed=seed, perturb=False, noise_px=0.5)
+    rec = scene_reconstruction(sba, prob)
+    return rec
+
+
+def snapshot(rec):
+    return ({pid: [(e.image_id, e.point2D_idx) for e in p.track.Elements()] for pid, p in rec.points3D.items()},
+            {iid: [p.point3D_id for p in im.points2D] for iid, im in rec.images.items()},
+            {pid: p.error for pid, p in rec.points3D.items()})
+
+
+def test_known_answers_of_the_error_function(oracle):
+    """A point on the optical axis projects to the principal point; behind the camera the error is DBL_MAX."""
+    e, z = C.c_double(), C.c_double()
+    q, t = np.array([2.0, 0, 0, 0]), np.array([0.0, 0, 0])          # non-unit quaternion: normalised first
+    cam, xy = np.array([100.0, 320, 240] + [0.0] * 9), np.array([323.0, 244.0])
+    X = np.array([0.0, 0, 5])
+    oracle.oracle_observation_error(0, *[v.ctypes.data_as(dp) for v in (q, t, X, cam, xy)], C.byref(e), C.byref(z))
+    assert e.value == 25.0 and z.value == 5.0
+    X = np.array([0.0, 0, -5])
+    oracle.oracle_observation_error(0, *[v.ctypes.data_as(dp) for v in (q, t, X, cam, xy)], C.byref(e), C.byref(z))
+    assert e.value == np.finfo(np.float64).max and z.value == -5.0
+    X = np.array([0.1, -0.2, 2.0])                                  # f * (0.05, -0.1) + pp = (325, 230)
+    oracle.oracle_observation_error(0, *[v.ctypes.data_as(dp) for v in (q, t, X, cam, xy)], C.byref(e), C.byref(z))
+    assert e.value == pytest.approx(2.0 ** 2 + 14.0 ** 2, rel=1e-14)
+
+
+def test_negative_depth_filter_follows_the_reference_loop(sba, oracle):
+    rec = planted(sba)
+    far = [pid for pid, p in rec.points3D.items() if p.track.Length() >= 4][:3]
+    short = [pid for pid, p in rec.points3D.items() if p.track.Length() == 2][:1]
+    for pid in far + short:
+        rec.points3D[pid].xyz[:] = rec.points3D[pid].xyz * -40.0     # far on the other side: behind most cameras
+    before = snapshot(rec)
+    fn = oracle_errors(oracle)
+    prob, keys = sba.filters.flatten_observations(rec)
+    depth = dict(zip(keys, fn(prob)[1]))
+    n = sba.filters.filter_observations_with_negative_depth(rec, errors_fn=fn)
+    assert n > 0
+    tracks, p2d, _ = snapshot(rec)
+    for pid, tr in before[0].items():
+        bad = [k for k in tr if not depth[k] >= np.finfo(float).eps]
+        if not bad:
+            assert tracks[pid] == tr
+        elif len(tr) - len(bad) < 2:
+            assert pid not in tracks                                  # DeleteObservation on a 2-track deletes the point
+            assert all(p2d[i][j] == sba.bundle_adjustment.kInvalidPoint3DId for i, j in tr)
+        else:
+            assert tracks[pid] == [k for k in tr if k not in bad]
+    assert sba.filters.filter_observations_with_negative_depth(rec, errors_fn=fn) == 0   # idempotent
+
+
+def test_reprojection_error_filter_follows_the_reference_loop(sba, oracle):
+    rec = planted(sba, seed=4)
+    pids = [pid for pid, p in rec.points3D.items() if p.track.Length() >= 4]
+    one_bad, all_but_one_bad = pids[0], pids[1]
+    el = rec.points3D[one_bad].track.Elements()[1]
+    rec.images[el.image_id].points2D[el.point2D_idx].xy += 60.0
+    for el in rec.points3D[all_but_one_bad].track.Elements()[1:]:
+        rec.images[el.image_id].points2D[el.point2D_idx].xy -= 45.0
+    lonely = [pid for pid, p in rec.points3D.items() if p.track.Length() == 2][0]
+    gone = rec.points3D[lonely].track.elements.pop()
+    rec.images[gone.image_id].points2D[gone.point2D_idx].point3D_id = sba.bundle_adjustment.kInvalidPoint3DId
+    before = snapshot(rec)
+    fn = oracle_errors(oracle)
+    n = sba.filters.filter_points3D_with_large_reprojection_error(rec, 4.0, errors_fn=fn)
+    tracks, p2d, errs = snapshot(rec)
+    assert lonely not in tracks and all_but_one_bad not in tracks                  # track < 2, and >= length - 1 bad elements
+    assert tracks[one_bad] == [k for j, k in enumerate(before[0][one_bad]) if j != 1]
+    assert n == 1 + len(before[0][all_but_one_bad]) + 1
+    assert 0 < errs[one_bad] < 4.0                                                   # mean error over the remaining elements
+    untouched = [pid for pid in tracks if pid not in (one_bad,)]
+    assert all(tracks[pid] == before[0][pid] for pid in untouched)
+    assert all(0 <= errs[pid] < 4.0 for pid in untouched)
+
+
+def test_observation_errors_need_a_device(sba):
+    prob, _ = sba.scene.make_scene(n_cam=3, n_pt=20, mean_track=3.0, seed=1)
+    lib = sba.capi.load()
+    d = prob.desc()
+    err = np.zeros(prob.num_observations)
+    rc = lib.sba_observation_errors(C.byref(d), err.ctypes.data_as(dp), None)
+    assert rc == (0 if lib.sba_device_count() >= 1 else 2)
+    assert lib.sba_observation_errors(None, err.ctypes.data_as(dp), None) == 1
+
+
+@pytest.mark.gpu
+def test_device_errors_match_the_oracle_for_every_model(sba, oracle):
+    from test_rig import MODEL_PARAMS
+    rng = np.random.default_rng(17)
+    n_img, n_pt, n = 11, 60, 900
+    q = rng.normal(size=(n_img, 4)) * [1, 0.1, 0.1, 0.1] * 3.0           # not normalised on purpose
+    t = rng.normal(0, 0.2, (n_img, 3)) + [0, 0, 4.0]
+    cam = np.zeros((11, 12))
+    for m, p in MODEL_PARAMS.items():
+        cam[m, :len(p)] = p
+    pts = rng.uniform(-1, 1, (n_pt, 3))
+    pts[:5, 2] -= 30.0                                                      # some behind every camera
+    prob = sba.FlatProblem(q, t, np.arange(n_img), np.arange(11), cam, pts, rng.integers(0, n_img, n), rng.integers(0, n_pt, n),
+                           rng.uniform(100, 700, (n, 2)))
+    err, depth = sba.filters.device_observation_errors(prob)
+    ref_err, ref_depth = oracle_errors(oracle)(prob)
+    assert np.array_equal(err == np.finfo(float).max, ref_err == np.finfo(float).max) and (err == np.finfo(float).max).any()
+    ok = ref_err != np.finfo(float).max
+    assert np.allclose(depth, ref_depth, rtol=1e-13, atol=1e-13)
+    assert np.allclose(err[ok], ref_err[ok], rtol=1e-10, atol=0)
+
+
+@pytest.mark.gpu
+def test_filters_on_the_device_equal_the_oracle_run(sba, oracle):
+    a, b = planted(sba, seed=6), planted(sba, seed=6)
+    for rec in (a, b):
+        pids = [pid for pid, p in rec.points3D.items() if p.track.Length() >= 3]
+        for pid in pids[:4]:
+            el = rec.points3D[pid].track.Elements()[0]
+            rec.images[el.image_id].points2D[el.point2D_idx].xy += 25.0
+        rec.points3D[pids[5]].xyz[:] *= -30.0
+    na = (sba.filters.filter_observations_with_negative_depth(a), sba.filters.filter_points3D_with_large_reprojection_error(a, 4.0))
+    fn = oracle_errors(oracle)
+    nb = (sba.filters.filter_observations_with_negative_depth(b, errors_fn=fn),
+          sba.filters.filter_points3D_with_large_reprojection_error(b, 4.0, errors_fn=fn))
+    assert na == nb and na[0] > 0 and na[1] > 0
+    sa, sb = snapshot(a), snapshot(b)
+    assert sa[0] == sb[0] and sa[1] == sb[1]
+    assert all(abs(sa[2][k] - sb[2][k]) <= 1e-10 * max(1.0, abs(sb[2][k])) for k in sb[2])
