@@ -126,6 +126,22 @@ int DecideBlockSchur(Problem* p) {
   const int n_img = p->n_img, dc = p->dc;
   const int64_t cells = (int64_t)n_img * n_img;
   if (cells > 0x7fffffffLL || (p->comm && cells > (1ll << 27))) return SBA_OK;
+  {  // the pair list grows with the square of the track length: bound it before building it
+    double pairs = 0.0;
+    for (int q = 0; q < p->n_pt; ++q) { const double k = p->h_pt_ptr[q + 1] - p->h_pt_ptr[q]; pairs += 0.5 * k * (k - 1.0); }
+    size_t free_b = 0, total_b = 0;
+    SBA_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    double too_many = (pairs > 1.5e9 || pairs * 40.0 > 0.25 * (double)free_b) ? 1.0 : 0.0;  // 32-bit pair offsets; 40 B per pair while sorting
+    if (p->comm) {  // every rank must take the same path
+      double* flag = p->d_red.p;
+      SBA_CUDA(cudaMemcpyAsync(flag, &too_many, sizeof(double), cudaMemcpyHostToDevice, p->stream));
+      int rcf = AllReduceMax(p, flag, 1);
+      if (rcf) return rcf;
+      SBA_CUDA(cudaMemcpyAsync(&too_many, flag, sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+      SBA_CUDA(cudaStreamSynchronize(p->stream));
+    }
+    if (too_many != 0.0) return SBA_OK;
+  }
   HostTimer tm("block-sparse S structure");
   int rc = BuildPairLists(p, true);
   if (rc) return rc;
@@ -179,7 +195,8 @@ int DecideBlockSchur(Problem* p) {
   size_t free_b = 0, total_b = 0;
   SBA_CUDA(cudaMemGetInfo(&free_b, &total_b));
   const bool force = env && env[0] == '0';
-  if (!force && (explicit_bytes > implicit_bytes || explicit_bytes > 0.25 * (double)free_b)) return SBA_OK;
+  // (total, not free, memory: every rank must reach the same verdict)
+  if (!force && (explicit_bytes > implicit_bytes || explicit_bytes > 0.125 * (double)total_b)) return SBA_OK;
 
   // row lists (host; n_keys entries): diagonal, lower neighbours in key order, upper neighbours in key order
   std::vector<int> cnt((size_t)n_img + 1, 0);

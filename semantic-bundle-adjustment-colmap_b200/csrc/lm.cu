@@ -37,7 +37,7 @@ struct StageTimer {
 // 3-150 us kernels; as a graph the launch gaps and the host's per-launch cost leave the critical path.
 template <class F>
 static int RunSegment(Problem* p, int key, bool use_graph, F&& body) {
-  if (!use_graph) return body();
+  if (!use_graph || p->graphs_unusable) return body();
   cudaStream_t st = p->stream;
   if (!p->graph_exec[key]) {
     const int64_t l0 = p->launches;
@@ -48,13 +48,21 @@ static int RunSegment(Problem* p, int key, bool use_graph, F&& body) {
     if (rc || e != cudaSuccess || !g) {
       if (g) cudaGraphDestroy(g);
       cudaGetLastError();
-      if (rc) return rc;
-      SetError(SBA_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
-      return SBA_ERR_CUDA;
+      if (rc && e == cudaSuccess) return rc;
+      // a launch that cannot be captured on this driver: nothing ran, so run the segment as plain launches from now on
+      p->graphs_unusable = true;
+      p->launches = l0;
+      return body();
     }
     const cudaError_t ei = cudaGraphInstantiate(&p->graph_exec[key], g, 0);
     cudaGraphDestroy(g);
-    if (ei != cudaSuccess) { p->graph_exec[key] = nullptr; SetError(SBA_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ei)); return SBA_ERR_CUDA; }
+    if (ei != cudaSuccess) {
+      p->graph_exec[key] = nullptr;
+      cudaGetLastError();
+      p->graphs_unusable = true;
+      p->launches = l0;
+      return body();
+    }
     p->graph_launches[key] = p->launches - l0;
   } else {
     p->launches += p->graph_launches[key];
@@ -155,7 +163,10 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   // solve (the reference's default is max_num_iterations = 100) replays graphs.
   const bool worth_it = p->solve_count > 0 || o.max_num_iterations > 25;
   p->solve_count++;
-  const bool graphs_ok = !graphs_off && worth_it && !iterative && p->comm == nullptr && p->n_cdim > 0;
+  // The iterative solver qualifies once it runs on the block-sparse S: its PCG is then one persistent launch with no
+  // host poll inside (decided in the first iteration, which always runs as plain launches).
+  static const bool pcg_host_driven = getenv("SBA_PCG_LAUNCHES") != nullptr || getenv("SBA_PCG_TRACE") != nullptr;
+  const bool graphs_ok = !graphs_off && worth_it && p->comm == nullptr && p->n_cdim > 0 && !(iterative && pcg_host_driven);
   if (graphs_ok && (!p->graph_opts_valid || std::memcmp(&p->graph_opts, &o, sizeof(o)) != 0)) {
     p->DropGraphs();
     p->graph_opts = o; p->graph_opts_valid = true;
@@ -184,7 +195,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
 
     // ---- LevenbergMarquardtStrategy::ComputeStep, candidate point and its cost: one launch sequence ----
     // (the first iteration runs as plain launches: it allocates, builds the pair lists and sets kernel attributes)
-    const bool use_graph = graphs_ok && iteration >= 2;
+    const bool use_graph = graphs_ok && iteration >= 2 && (!iterative || p->bsr.enabled) && !p->graphs_unusable;
     const bool marks = !use_graph;
     int lin_iters = 0;
     auto step_segment = [&]() -> int {
@@ -222,8 +233,8 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     };
     const int refresh = hs->reuse_diagonal ? 0 : 1;  // PrepareLMDiagonal branches on the same host flag
     if ((rc = RunSegment(p, p->parity * 2 + refresh, use_graph, step_segment))) return rc;
-    if (use_graph) lin_iters = 1;
     SBA_CUDA(cudaStreamSynchronize(st));  // hs is current
+    if (use_graph) lin_iters = iterative ? hs->cg_iter : 1;
     settle();
     if (marks) {
       p->t_elim += tm.Ms(0, 1) * 1e-3; p->t_solve += tm.Ms(1, 2) * 1e-3;

@@ -168,6 +168,9 @@ int SolvePCG(Problem* p, const sba_solver_options& o, int* iters) {
   if (persistent) {  // explicit block-sparse S: the whole solve is one cooperative kernel (pcg_blocks.cu)
     const int rc = SolvePCGBlocks(p, o);
     if (rc) return rc;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    SBA_CUDA(cudaStreamIsCapturing(st, &cap));
+    if (cap != cudaStreamCaptureStatusNone) return SBA_OK;  // graph capture: the kernel itself flags a breakdown; the caller reads cg_iter later
   } else {
     cg_init_kernel<<<1, kCgThreads, 0, st>>>(n, b, x, p->d_cg_r.p, sc);
     p->launches++;

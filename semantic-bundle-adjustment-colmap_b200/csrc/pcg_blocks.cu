@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(128) pcg_blocks_kernel(PcgBlocks a) {
     sc->cg_rho = rho; sc->cg_last_rho = last_rho; sc->cg_alpha = alpha; sc->cg_beta = beta; sc->cg_pq = pq;
     sc->cg_Q0 = Q0; sc->cg_Q1 = Q0; sc->cg_zeta = zeta;
     sc->cg_iter = iter; sc->cg_state = state;
+    if (state == 3) sc->solver_failed = 1;  // LinearSolver FAILURE: the step is unusable (TrustRegionMinimizer treats it as invalid)
   }
 }
 

@@ -223,6 +223,7 @@ struct Problem {
   bool graph_opts_valid = false;
   int parity = 0;
   int solve_count = 0;                       // sba_solve calls on this handle
+  bool graphs_unusable = false;              // a capture failed once (e.g. a launch kind the driver cannot capture)
   void DropGraphs();
 
   cudaStream_t stream = nullptr;

@@ -109,6 +109,26 @@ def test_persistent_pcg_matches_launch_per_step_pcg(sba, kind):
     assert again[0].final_cost == one[0].final_cost and all(np.array_equal(a, b) for a, b in zip(again[2], one[2]))
 
 
+def test_graph_replay_of_the_iterative_path_is_bit_identical(sba):
+    """A re-solved handle replays each LM iteration -- block-sparse S build, the persistent PCG launch, back-substitution,
+    step -- as a CUDA graph (csrc/lm.cu); same kernels, same order, so nothing may change by a bit, and the CG iteration
+    counts read back after the replay are those of the plain run."""
+    prob = _scene(sba, "radial", seed=13)
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations, o.linear_solver_type = 7, ITERATIVE
+    s = sba.Solver(prob)
+    first = s.solve(o)
+    tr1 = [(t.cost, t.linear_solver_iterations) for t in s.trace()]
+    par1 = [a.copy() for a in s.parameters()]
+    s.reset()
+    second = s.solve(o)
+    tr2 = [(t.cost, t.linear_solver_iterations) for t in s.trace()]
+    assert first.final_cost == second.final_cost and tr1 == tr2
+    assert all(np.array_equal(a, b) for a, b in zip(par1, s.parameters()))
+    assert first.num_linear_solver_iterations == second.num_linear_solver_iterations > 0
+    s.close()
+
+
 def test_block_sparse_schur_matches_oracle(sba, oracle):
     prob = _scene(sba, "radial", seed=8)
     o = sba.capi.default_solver_options()
