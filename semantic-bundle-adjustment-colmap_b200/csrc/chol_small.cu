@@ -55,6 +55,7 @@ struct CholSmall {
   DeviceScalars* sc;
   int n, nbr, epoch;
   long long* trace;     // optional [nbr+1][8] globaltimer stamps (SBA_CHOL_TRACE=1), else null
+  int warm_icache;      // rows >= 1 pre-run the diagonal factorisation while they wait (SBA_CHOL_NO_WARM=1 turns it off)
 };
 
 __device__ inline void Stamp(const CholSmall& a, int slot) {
@@ -293,6 +294,14 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_small_kernel(CholSmall a
     for (int c = tid; c < n; c += kCholThreads) S[(size_t)n * n + c] = a.rhs[c];
     __syncthreads();
   }
+  // Rows >= 1 cannot start before row 0's factor is published (~28 us): one otherwise idle warp spends that wait running
+  // the (fully unrolled, ~100 KB of SASS) diagonal factorisation on an identity tile, so the instruction cache of this
+  // SM is warm when the real factor -- which sits on the critical path of every later row -- arrives.
+  if (!is_rhs && i > 0 && warp == (kCholThreads >> 5) - 1 && a.warm_icache) {
+    for (int idx = lane; idx < SB * SLD; idx += 32) sV[idx] = (idx / SLD == idx % SLD) ? 1.0 : 0.0;
+    __syncwarp();
+    FactorTileWarp(sV, sX, a.Linv + (size_t)i * SB * SB);  // scratch outputs: overwritten by this row's inverse later
+  }
   double accD[4] = {0.0, 0.0, 0.0, 0.0};
   if (!is_rhs) {  // diagonal tile, lower part, + D^2; identity padding keeps a partial block well posed
 #pragma unroll
@@ -458,6 +467,8 @@ int CholeskySolveSmall(Problem* p) {
     smem_set = smem;
   }
   static const bool trace = getenv("SBA_CHOL_TRACE") != nullptr;
+  static const bool no_warm = getenv("SBA_CHOL_NO_WARM") != nullptr;
+  a.warm_icache = no_warm ? 0 : 1;
   DevBuf<long long> d_trace;
   a.trace = nullptr;
   if (trace) { SBA_CUDA(d_trace.Alloc((size_t)(nbr + 1) * 8)); SBA_CUDA(d_trace.Zero(st)); a.trace = d_trace.p; }
