@@ -337,6 +337,8 @@ def run_b200(args, m):
         big, _ = make_workload(m, args.extra, 1)
         sb = m.Solver(big)
         ob = solver_options(m, len(big.image_camera))
+        sb.solve(ob)   # first solve of the handle: pair lists, block structure, first-touch allocations
+        sb.reset()
         sm = sb.solve(ob)
         itb = sm.num_successful_steps + sm.num_unsuccessful_steps
         it_stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (
