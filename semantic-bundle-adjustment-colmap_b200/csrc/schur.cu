@@ -225,34 +225,32 @@ __global__ void __launch_bounds__(128) schur_pair_emit_kernel(StructView S, int 
 // (or pair): it loads its records with wide accesses, forms the full block in registers, and the warp pays ONE
 // transposing reduction through shared memory per 32 observations (per <= 128 pairs).  Fixed summation order.
 
+// doubles per W / H row: the lane kernels (DC <= 8) pad a row to a multiple of 32 B, so that a row starts on a sector
+// boundary (DC = 6: 144 -> 160 B = exactly five sectors per gather instead of five or six) and is written with
+// 256-bit stores; the generic kernels keep DC * 3.
+__host__ __device__ constexpr int WRow(int dc) { return dc <= 8 ? (dc * 3 + 3) / 4 * 4 : dc * 3; }
+
 template <int DC> struct ObsLane {
-  static constexpr int CH = DC * 3 / 2;                 // 16 B units per W / H row
-  static constexpr int RU = (CH & 1) ? CH : CH + 1;     // padded row stride in 16 B units (odd)
   static constexpr int NT = DC * (DC + 1) / 2;
-  static constexpr size_t kStage = (size_t)256 * 2 * RU * 16, kRed = (size_t)(NT * 256 + NT * 8) * 8;
-  static constexpr size_t kSmem = kStage > kRed ? kStage : kRed;
+  static constexpr size_t kSmem = (size_t)(NT * 256 + NT * 8) * 8;
 };
 
 // W_a, H_a and the diagonal contribution F_a^T F_a - H_a W_a^T of every observation of one image chunk.
 // partial[ch][e], e over the lower triangle (ja >= jb, e = ja (ja + 1) / 2 + jb).
+// A lane owns an observation and writes its own two rows (image-major, sector-aligned, 256-bit stores); only the current
+// H row is kept in registers, the diagonal entries of slot ja being formed as soon as H_ja exists.
 template <int DC>
-__global__ void __launch_bounds__(256) schur_obs_lane_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
+__global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
                                                              const D4* __restrict__ F, const double* __restrict__ Cinv,
                                                              double* __restrict__ W, double* __restrict__ H,
                                                              double* __restrict__ partial) {
-  constexpr int NT = DC * (DC + 1) / 2, DH = DC / 2;
-  constexpr int CH = ObsLane<DC>::CH, RU = ObsLane<DC>::RU;
-  extern __shared__ __align__(16) double sm[];  // W/H staging [2][256][RU x 16 B]; then [NT][256] blocks + [NT][8] partials
-  double* stage = sm;
+  constexpr int NT = DC * (DC + 1) / 2, DH = DC / 2, RW = WRow(DC);
+  extern __shared__ __align__(16) double sm[];  // [NT][256] blocks + [NT][8] partials
   double* part = sm + NT * 256;
-  const int ch = blockIdx.x, t = threadIdx.x, lane = t & 31;
+  const int ch = blockIdx.x, t = threadIdx.x;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
-  double v[NT];
-#pragma unroll
-  for (int e = 0; e < NT; ++e) v[e] = 0.0;
-  int a = -1;
   if (t < n) {
-    a = C.cam_order[s0 + t];
+    const int a = C.cam_order[s0 + t];
     double2 f[DC];
 #pragma unroll
     for (int jj = 0; jj < DH; ++jj) {
@@ -269,44 +267,39 @@ __global__ void __launch_bounds__(256) schur_obs_lane_kernel(StructView S, Chunk
       const double2 c0 = cp[0], c1 = cp[1], c2 = cp[2];
       ci[0] = c0.x; ci[1] = c0.y; ci[2] = c1.x; ci[3] = c1.y; ci[4] = c2.x; ci[5] = c2.y;
     }
-    double w[DC][3], h[DC][3];
+    D4* wrow = reinterpret_cast<D4*>(W + (size_t)(s0 + t) * RW);
+    D4* hrow = reinterpret_cast<D4*>(H + (size_t)(s0 + t) * RW);
+    double w[RW], h[RW];
 #pragma unroll
-    for (int j = 0; j < DC; ++j) {
+    for (int q = DC * 3; q < RW; ++q) { w[q] = 0.0; h[q] = 0.0; }
 #pragma unroll
-      for (int c = 0; c < 3; ++c) w[j][c] = f[j].x * E[c] + f[j].y * E[3 + c];
-      Sym3Mul(ci, w[j], h[j]);
-    }
-    // stage the two rows in shared memory (row stride = an odd number of 16 B units: conflict-free 128-bit stores);
-    // the warp writes them out below with consecutive lanes on consecutive 16 B chunks of a row
-    double2* ws = reinterpret_cast<double2*>(stage) + (size_t)t * RU;  // [row][thread][RU]
+    for (int ja = 0; ja < DC; ++ja) {
 #pragma unroll
-    for (int q = 0; q < CH; ++q) {
-      ws[q] = make_double2((&w[0][0])[2 * q], (&w[0][0])[2 * q + 1]);
-      ws[256 * RU + q] = make_double2((&h[0][0])[2 * q], (&h[0][0])[2 * q + 1]);
-    }
-#pragma unroll
-    for (int ja = 0; ja < DC; ++ja)
+      for (int c = 0; c < 3; ++c) w[3 * ja + c] = f[ja].x * E[c] + f[ja].y * E[3 + c];
+      Sym3Mul(ci, &w[3 * ja], &h[3 * ja]);
+      // the entries of slot ja are final: they go straight to the reduction area, not through registers
 #pragma unroll
       for (int jb = 0; jb <= ja; ++jb)
-        v[ja * (ja + 1) / 2 + jb] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y) -
-                                    (h[ja][0] * w[jb][0] + h[ja][1] * w[jb][1] + h[ja][2] * w[jb][2]);
-  }
-  __syncwarp();
-  {  // copy-out: the rows of W / H are image-major, so this warp's 32 rows are one contiguous run of 32 x CH units
-    const int wb = t & ~31, nw = min(32, n - wb);
-    const double2* src = reinterpret_cast<const double2*>(stage) + (size_t)wb * RU;
-    double2* wdst = reinterpret_cast<double2*>(W + (size_t)(s0 + wb) * DC * 3);
-    double2* hdst = reinterpret_cast<double2*>(H + (size_t)(s0 + wb) * DC * 3);
+        sm[(ja * (ja + 1) / 2 + jb) * 256 + t] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y) -
+                                                 (h[3 * ja] * w[3 * jb] + h[3 * ja + 1] * w[3 * jb + 1] + h[3 * ja + 2] * w[3 * jb + 2]);
+      // 32-byte units of the two rows leave as soon as they are complete (H is not needed again)
 #pragma unroll
-    for (int i = 0; i < CH; ++i) {
-      const int k = lane + 32 * i;
-      const int o = k / CH, c = k - o * CH;
-      if (o < nw) { wdst[k] = src[(size_t)o * RU + c]; hdst[k] = src[(size_t)(256 + o) * RU + c]; }
+      for (int q = 0; q < RW / 4; ++q)
+        if (4 * q + 3 < 3 * (ja + 1) && 4 * q + 3 >= 3 * ja) {
+          St256(wrow + q, D4{w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]});
+          St256(hrow + q, D4{h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]});
+        }
     }
-  }
-  __syncthreads();  // staging area is reused by the reduction
 #pragma unroll
-  for (int e = 0; e < NT; ++e) sm[e * 256 + t] = v[e];
+    for (int q = 0; q < RW / 4; ++q)
+      if (4 * q + 3 >= 3 * DC) {  // the unit(s) that hold the padding
+        St256(wrow + q, D4{w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]});
+        St256(hrow + q, D4{h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]});
+      }
+  } else {
+#pragma unroll
+    for (int e = 0; e < NT; ++e) sm[e * 256 + t] = 0.0;
+  }
   __syncthreads();
   for (int k = t; k < NT * 8; k += 256) {  // task (e, warp): 32 values; the rotation keeps the 16 lanes of a phase on 16 banks
     const int e = k >> 3, wq = k & 7;
@@ -399,7 +392,7 @@ __global__ void __launch_bounds__(128, 4) schur_pair_lane_kernel(int n_seg, cons
       const int k = lane + 32 * i;
       const int row = k / (PPI * CH), rem = k - row * (PPI * CH), o = rem / CH, c = rem - o * CH;
       const int src = __shfl_sync(0xffffffffu, row ? b : a, o * G);
-      if (src >= 0) CpAsync16(st + (size_t)(row * PPI + o) * RU + c, (row ? W : H) + (size_t)src * DC * 3 + 2 * c);
+      if (src >= 0) CpAsync16(st + (size_t)(row * PPI + o) * RU + c, (row ? W : H) + (size_t)src * WRow(DC) + 2 * c);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -521,7 +514,7 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
   const int dc = p->dc;
   cudaStream_t st = p->stream;
   if (p->n_obs == 0) return SBA_OK;
-  SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * dc * 3)); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * dc * 3));
+  SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * WRow(dc))); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * WRow(dc)));
   SBA_CUDA(p->d_chunk_block.Alloc((size_t)std::max(1, p->n_chunks) * dc * dc));
   if (dc == 6) { SBA_CUDA(AccumulateLane<6>(p, L, sink)); return SBA_OK; }
   if (dc == 8) { SBA_CUDA(AccumulateLane<8>(p, L, sink)); return SBA_OK; }
