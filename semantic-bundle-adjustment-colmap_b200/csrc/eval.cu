@@ -312,6 +312,7 @@ static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int bl
 static int EvalGrid(const Problem* p) { return std::min(DivUp(p->n_obs, kEvalThreads), p->n_sm * 16); }
 
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate) {
+  p->colnorm_current = false;  // a new Jacobian: d_sq_c is stale until ColumnNorms / Gradient(with_norms)
   const int blocks = EvalGrid(p);
   if (blocks > 0) {
 #define CALL(M) LaunchEvalT<M>(p, loss, use_scale, candidate, blocks)

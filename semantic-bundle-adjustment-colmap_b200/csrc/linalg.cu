@@ -45,8 +45,8 @@ static int CamReduce(Problem* p, int mode, const double2* v, double* out, const 
   return SBA_OK;
 }
 
-int ColumnNorms(Problem* p, double* d_nc, double* d_np) {
-  int rc = CamReduce(p, 2, nullptr, d_nc, nullptr, nullptr);
+int ColumnNorms(Problem* p, double* d_nc, double* d_np, bool camera_part) {
+  int rc = camera_part ? CamReduce(p, 2, nullptr, d_nc, nullptr, nullptr) : SBA_OK;
   if (rc) return rc;
   if (p->n_pvar > 0 && p->n_tiles > 0) {
     point_sqnorm_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, d_np);
@@ -70,14 +70,33 @@ int InitJacobiScale(Problem* p) {
 #undef CALL
     p->launches++;
   }
+  p->colnorm_current = false;  // the stored Jacobian was rescaled
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }
 
 // gradient max-norm of the UNSCALED problem: max |(J^T r)_j| = max |g_scaled_j / scale_j|.
 // The point part g_p = E^T r must be current (PointBlocks).
-int Gradient(Problem* p) {
-  int rc = CamReduce(p, 1, nullptr, p->d_grad_c.p, nullptr, nullptr);
+// `with_norms`: the same pass over F also leaves the camera column square norms in d_sq_c (cam_reduce MODE 3), which
+// the next LM diagonal would otherwise recompute with a pass of its own.
+int Gradient(Problem* p, bool with_norms) {
+  int rc = SBA_OK;
+  if (with_norms && p->n_cdim > 0 && p->n_chunks > 0) {
+    double* part2 = p->d_chunk_partial.p + (size_t)p->n_chunks * kMaxDC;
+#define CALL(DC) cam_reduce_kernel<DC, 3><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, nullptr, p->d_chunk_partial.p, nullptr, part2)
+    SBA_DC_SWITCH(p->dc, CALL)
+#undef CALL
+    const int n = p->n_img * 6 + p->n_cam * 12;
+    cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_partial.p, p->d_grad_c.p, nullptr, nullptr);
+    cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), part2, p->d_sq_c.p, nullptr, nullptr);
+    p->launches += 3;
+    SBA_CUDA(cudaGetLastError());
+    if ((rc = AllReduceSum(p, p->d_grad_c.p, p->n_cdim))) return rc;
+    if ((rc = AllReduceSum(p, p->d_sq_c.p, p->n_cdim))) return rc;
+    p->colnorm_current = true;
+  } else {
+    rc = CamReduce(p, 1, nullptr, p->d_grad_c.p, nullptr, nullptr);
+  }
   if (rc) return rc;
   double* out = &p->d_scalars.p->gradient_max_norm;
   SBA_CUDA(cudaMemsetAsync(out, 0, sizeof(double), p->stream));
@@ -107,9 +126,10 @@ int FillOnes(Problem* p) {
 
 int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
   const int refresh = p->h_scalars->reuse_diagonal ? 0 : 1;
-  if (refresh) {
-    int rc = ColumnNorms(p, p->d_sq_c.p, p->d_sq_p.p);
+  if (refresh) {  // the camera norms may already be there: Gradient(with_norms) of the linearisation that made this J
+    int rc = ColumnNorms(p, p->d_sq_c.p, p->d_sq_p.p, !p->colnorm_current);
     if (rc) return rc;
+    p->colnorm_current = false;  // (host bookkeeping only: a replayed graph keeps the launch sequence it was captured with)
   }
   if (p->n_cdim + p->n_pvar > 0) {
     lm_diag_kernel<<<DivUp((int64_t)p->n_cdim + 3 * (int64_t)p->n_pvar, 256), 256, 0, p->stream>>>(

@@ -346,21 +346,33 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
 
 // ---- camera-side segmented reduction over image-major chunks ------------------------
 // MODE 0: F^T v (v per observation)   MODE 1: F^T r (r from ER)   MODE 2: column square norms
+// MODE 3: F^T r into partial AND the column square norms into partial2, one pass over F (after a new linearisation both
+//         are wanted: the gradient now, the norms by the next LM diagonal)
 template <int DC, int MODE>
 __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* __restrict__ F,
                                                          const D4* __restrict__ ER, const double2* __restrict__ v,
-                                                         double* __restrict__ partial, const int* __restrict__ skip) {
+                                                         double* __restrict__ partial, const int* __restrict__ skip,
+                                                         double* __restrict__ partial2 = nullptr) {
   if (skip && *skip != 0) return;
   const int ch = blockIdx.x;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
-  double acc[DC];
+  double acc[DC], acc2[MODE == 3 ? DC : 1];
 #pragma unroll
   for (int j = 0; j < DC; ++j) acc[j] = 0.0;
+#pragma unroll
+  for (int j = 0; j < (MODE == 3 ? DC : 1); ++j) acc2[j] = 0.0;
   if (threadIdx.x < n) {
     const int k = C.cam_order[s0 + threadIdx.x];
     double2 row[DC];
     LoadRow<DC>(F, k, row);
-    if (MODE == 2) {
+    if (MODE == 3) {
+      const double2 w = reinterpret_cast<const double2*>(ER + EUnit(k, 1))[1];
+#pragma unroll
+      for (int j = 0; j < DC; ++j) {
+        acc[j] = row[j].x * w.x + row[j].y * w.y;
+        acc2[j] = row[j].x * row[j].x + row[j].y * row[j].y;
+      }
+    } else if (MODE == 2) {
 #pragma unroll
       for (int j = 0; j < DC; ++j) acc[j] = row[j].x * row[j].x + row[j].y * row[j].y;
     } else {
@@ -384,6 +396,23 @@ __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* 
 #pragma unroll
     for (int i = 0; i < 8; ++i) a += sm[i][threadIdx.x];
     partial[(size_t)ch * DC + threadIdx.x] = a;
+  }
+  if (MODE == 3) {  // same fixed-order reduction for the norms
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < DC; ++j) {
+      double a = acc2[MODE == 3 ? j : 0];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+      if (lane == 0) sm[w][j] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x < DC) {
+      double a = 0.0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a += sm[i][threadIdx.x];
+      partial2[(size_t)ch * DC + threadIdx.x] = a;
+    }
   }
 }
 

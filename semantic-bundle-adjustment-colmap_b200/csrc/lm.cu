@@ -280,11 +280,12 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
         if (marks) tm.Mark(6, st);
         if ((r = LaunchEvaluate(p, loss, o.jacobi_scaling != 0, false))) return r;
         if ((r = PointBlocks(p, true))) return r;
-        if ((r = Gradient(p))) return r;
+        if ((r = Gradient(p, true))) return r;  // + the camera column norms the next LM diagonal needs, same pass over F
         if (marks) tm.Mark(7, st);
         return SBA_OK;
       };
       if ((rc = RunSegment(p, 4 + p->parity, use_graph, linearise_segment))) return rc;
+      p->colnorm_current = true;  // (also when the segment was replayed as a graph: host code inside it did not run)
       it.step_is_successful = 1;
       sum->num_successful_steps++;
       it.cost = x_cost + fixed_cost;  // provisional; settled below or at the next synchronisation

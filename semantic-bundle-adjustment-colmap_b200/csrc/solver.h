@@ -235,6 +235,7 @@ struct Problem {
   DevBuf<float> d_sem_maps;  int sem_h = 0, sem_w = 0;  double sem_weight = 0.0;
   bool solved = false;
   bool linearized = false;
+  bool colnorm_current = false;             // d_sq_c holds the camera column norms of the CURRENT Jacobian (Gradient(with_norms))
   int cg_poll_every = 4;                    // host polls the CG state every this many iterations
   double* jq_out = nullptr;                 // parity surface: raw 2x4 quaternion block per observation
   DevBuf<char> d_flush;                     // L2 flush scratch for sba_bench_stage
@@ -261,8 +262,8 @@ int ProblemCounts(const sba_problem_desc* d, sba_summary* s);
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate);
 int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost /* &scalars->cand_cost */);
 // linalg.cu (column norms, point blocks, rhs, matvec, back-substitution, update)
-int ColumnNorms(Problem* p, double* d_nc, double* d_np);
-int Gradient(Problem* p);
+int ColumnNorms(Problem* p, double* d_nc, double* d_np, bool camera_part = true);
+int Gradient(Problem* p, bool with_norms = false);
 int FillOnes(Problem* p);
 int AllReduceMax(Problem* p, double* d_buf, size_t n);
 int InitJacobiScale(Problem* p);
