@@ -218,7 +218,7 @@ int DecideBlockSchur(Problem* p) {
   SBA_CUDA(B.slot_col.Alloc((size_t)n_img * dc));
   bsr_slot_col_kernel<<<DivUp((int64_t)n_img * dc, 256), 256, 0, st>>>(p->Struct(), dc, B.slot_col.p);
   p->launches++;
-  SBA_CUDA(B.blocks.Alloc((size_t)B.n_blocks * dc * dc));
+  SBA_CUDA(B.blocks.Alloc((size_t)B.n_blocks * dc * dc + p->n_cdim));  // + room for the rhs riding on the all-reduce
   SBA_CUDA(B.blocks.Zero(st));  // blocks of keys other ranks own stay zero here until the allreduce
   SBA_CUDA(cudaGetLastError());
   SBA_CUDA(cudaStreamSynchronize(st));  // the host vectors above go out of scope

@@ -98,6 +98,16 @@ static int AllReduce(Problem* p, double* d_buf, size_t n, ncclRedOp_t op) {
   return SBA_OK;
 }
 int AllReduceSum(Problem* p, double* d_buf, size_t n) { return AllReduce(p, d_buf, n, ncclSum); }
+int AllReduceSumWithRhs(Problem* p, double* d_buf, size_t n) {
+  if (!p->comm || !p->rhs_unreduced || p->n_cdim == 0) { p->rhs_unreduced = false; return AllReduceSum(p, d_buf, n); }
+  const size_t nb = (size_t)p->n_cdim * sizeof(double);
+  SBA_CUDA(cudaMemcpyAsync(d_buf + n, p->d_rhs.p, nb, cudaMemcpyDeviceToDevice, p->stream));
+  const int rc = AllReduceSum(p, d_buf, n + p->n_cdim);
+  if (rc) return rc;
+  SBA_CUDA(cudaMemcpyAsync(p->d_rhs.p, d_buf + n, nb, cudaMemcpyDeviceToDevice, p->stream));
+  p->rhs_unreduced = false;
+  return SBA_OK;
+}
 int AllReduceMax(Problem* p, double* d_buf, size_t n) { return AllReduce(p, d_buf, n, ncclMax); }
 int AllReduceMaxInt(Problem* p, int* d_buf, size_t n) {
   if (!p->comm || n == 0) return SBA_OK;

@@ -311,7 +311,7 @@ static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int bl
 // CTAs per launch: enough to fill every SM several times over, never more than the problem needs
 static int EvalGrid(const Problem* p) { return std::min(DivUp(p->n_obs, kEvalThreads), p->n_sm * 16); }
 
-int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate) {
+int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate, bool defer_allreduce) {
   p->colnorm_current = false;  // a new Jacobian: d_sq_c is stale until ColumnNorms / Gradient(with_norms)
   const int blocks = EvalGrid(p);
   if (blocks > 0) {
@@ -324,10 +324,12 @@ int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candid
   }
   SBA_CUDA(cudaGetLastError());
   p->linearized = true;
+  p->cost_unreduced = defer_allreduce && p->comm != nullptr;
+  if (p->cost_unreduced) return SBA_OK;
   return AllReduceSum(p, &p->d_scalars.p->cost, 2);  // cost, fixed_cost are adjacent
 }
 
-int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost) {
+int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost, bool with_step_scalars) {
   const int blocks = EvalGrid(p);
   if (blocks > 0) {
 #define CALL(M) LaunchCostT<M>(p, loss, candidate, blocks, d_out_cost)
@@ -338,7 +340,9 @@ int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_o
     SBA_CUDA(cudaMemsetAsync(d_out_cost, 0, sizeof(double), p->stream));
   }
   SBA_CUDA(cudaGetLastError());
-  return AllReduceSum(p, d_out_cost, 1);
+  // with_step_scalars: d_out_cost is &scalars->cand_cost and model_cost_change, step2_p, x2_p behind it still hold this
+  // rank's partial sums (BackSubstitute / ApplyStep deferred theirs): one collective for the four
+  return AllReduceSum(p, d_out_cost, with_step_scalars ? 4 : 1);
 }
 
 }  // namespace sba

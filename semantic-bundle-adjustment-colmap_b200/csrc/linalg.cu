@@ -18,7 +18,7 @@ static int Expand(Problem* p, const double* x, double* xi, double* xc) {
 // mode 0: F^T v, 1: F^T r, 2: column square norms.  out (compact) = sum over LOCAL
 // observations, all-reduced over ranks, plus Dc^2 x when Dc != nullptr.
 static int CamReduce(Problem* p, int mode, const double2* v, double* out, const double* Dc, const double* x,
-                     const int* skip = nullptr) {
+                     const int* skip = nullptr, bool defer_allreduce = false) {
   if (p->n_cdim == 0) return SBA_OK;
   if (p->n_chunks > 0) {
 #define CALL(DC)                                                                                                        \
@@ -36,7 +36,7 @@ static int CamReduce(Problem* p, int mode, const double2* v, double* out, const 
   cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_partial.p, out,
                                                            multi ? nullptr : Dc, x);
   p->launches++;
-  if (multi) {
+  if (multi && !defer_allreduce) {
     int rc = AllReduceSum(p, out, p->n_cdim);
     if (rc) return rc;
     if (Dc) { add_diag_kernel<<<DivUp(p->n_cdim, 256), 256, 0, p->stream>>>(p->n_cdim, out, Dc, x); p->launches++; }
@@ -81,20 +81,26 @@ int InitJacobiScale(Problem* p) {
 // the next LM diagonal would otherwise recompute with a pass of its own.
 int Gradient(Problem* p, bool with_norms) {
   int rc = SBA_OK;
-  if (with_norms && p->n_cdim > 0 && p->n_chunks > 0) {
+  if (with_norms && p->n_cdim > 0) {  // (every rank takes the same branch: the collectives below must pair up)
     double* part2 = p->d_chunk_partial.p + (size_t)p->n_chunks * kMaxDC;
 #define CALL(DC) cam_reduce_kernel<DC, 3><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, nullptr, p->d_chunk_partial.p, nullptr, part2)
-    SBA_DC_SWITCH(p->dc, CALL)
+    if (p->n_chunks > 0) { SBA_DC_SWITCH(p->dc, CALL) }
 #undef CALL
     const int n = p->n_img * 6 + p->n_cam * 12;
     cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_partial.p, p->d_grad_c.p, nullptr, nullptr);
     cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), part2, p->d_sq_c.p, nullptr, nullptr);
     p->launches += 3;
     SBA_CUDA(cudaGetLastError());
-    if ((rc = AllReduceSum(p, p->d_grad_c.p, p->n_cdim))) return rc;
-    if ((rc = AllReduceSum(p, p->d_sq_c.p, p->n_cdim))) return rc;
+    // d_sq_c lies right behind d_grad_c, and two more doubles behind it take the cost sums along when they are pending
+    const size_t n2 = 2 * (size_t)p->n_cdim;
+    double* cost = &p->d_scalars.p->cost;
+    if (p->cost_unreduced) SBA_CUDA(cudaMemcpyAsync(p->d_grad_c.p + n2, cost, 2 * sizeof(double), cudaMemcpyDeviceToDevice, p->stream));
+    if ((rc = AllReduceSum(p, p->d_grad_c.p, n2 + (p->cost_unreduced ? 2 : 0)))) return rc;
+    if (p->cost_unreduced) SBA_CUDA(cudaMemcpyAsync(cost, p->d_grad_c.p + n2, 2 * sizeof(double), cudaMemcpyDeviceToDevice, p->stream));
+    p->cost_unreduced = false;
     p->colnorm_current = true;
   } else {
+    if (p->cost_unreduced) { if ((rc = AllReduceSum(p, &p->d_scalars.p->cost, 2))) return rc; p->cost_unreduced = false; }
     rc = CamReduce(p, 1, nullptr, p->d_grad_c.p, nullptr, nullptr);
   }
   if (rc) return rc;
@@ -154,13 +160,16 @@ int PointBlocks(Problem* p, bool grad_only) {
 }
 
 // rhs = F^T (r - E C^{-1} g)   (reduced system right-hand side; Ceres solves S y = rhs, step = -y)
-int ReducedRhs(Problem* p) {
+int ReducedRhs(Problem* p, bool defer_allreduce) {
   if (p->n_obs > 0) {
     rhs_e_kernel<<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_ER.p, p->d_Cinv.p, p->d_gp.p,
                                                             reinterpret_cast<double2*>(p->d_g2.p));
     p->launches++;
   }
-  return CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), p->d_rhs.p, nullptr, nullptr);
+  defer_allreduce = defer_allreduce && p->comm != nullptr;
+  const int rc = CamReduce(p, 0, reinterpret_cast<const double2*>(p->d_g2.p), p->d_rhs.p, nullptr, nullptr, nullptr, defer_allreduce);
+  p->rhs_unreduced = defer_allreduce;
+  return rc;
 }
 
 // y = S x with S = F^T F + Dc^2 - sum_p (F^T E)_p C_p^{-1} (E^T F)_p, never formed
@@ -178,7 +187,7 @@ int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip) {
 }
 
 // y_p and model_cost_change from y_c (d_yc)
-int BackSubstitute(Problem* p) {
+int BackSubstitute(Problem* p, bool defer_allreduce) {
   Expand(p, p->d_yc.p, p->d_xi.p, p->d_xc.p);
   const int nb = std::min(DivUp(p->n_tiles, 4), p->n_sm * 16);  // grid-stride over warp tiles
   if (nb > 0) {
@@ -190,7 +199,7 @@ int BackSubstitute(Problem* p) {
     SBA_CUDA(cudaMemsetAsync(&p->d_scalars.p->model_cost_change, 0, sizeof(double), p->stream));
   }
   SBA_CUDA(cudaGetLastError());
-  return AllReduceSum(p, &p->d_scalars.p->model_cost_change, 1);
+  return defer_allreduce ? SBA_OK : AllReduceSum(p, &p->d_scalars.p->model_cost_change, 1);
 }
 
 // ---- x_plus = Plus(x, -y * scale) on every variable block (manifolds) ----
@@ -283,7 +292,7 @@ __global__ void __launch_bounds__(128) apply_step_kernel(StructView S, ParamsVie
   GridSum<128, 4>(v, partial, ticket, out);
 }
 
-int ApplyStep(Problem* p) {
+int ApplyStep(Problem* p, bool defer_allreduce) {
   DeviceScalars* sc = p->d_scalars.p;
   const int count = p->n_img + p->n_cam + p->n_pt;
   const int nb = std::min(DivUp(count, 128), p->n_sm * 16);
@@ -294,7 +303,7 @@ int ApplyStep(Problem* p) {
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
-  return AllReduceSum(p, &sc->step2_p, 2);
+  return defer_allreduce ? SBA_OK : AllReduceSum(p, &sc->step2_p, 2);
 }
 
 // ---- trust-region bookkeeping on the device (LevenbergMarquardtStrategy + TrustRegionMinimizer,

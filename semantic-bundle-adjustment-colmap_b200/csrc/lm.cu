@@ -166,6 +166,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   // The iterative solver qualifies once it runs on the block-sparse S: its PCG is then one persistent launch with no
   // host poll inside (decided in the first iteration, which always runs as plain launches).
   static const bool pcg_host_driven = getenv("SBA_PCG_LAUNCHES") != nullptr || getenv("SBA_PCG_TRACE") != nullptr;
+  const bool multi = p->comm != nullptr;  // sharded by point: partial sums meet in as few collectives as the data flow allows
   const bool graphs_ok = !graphs_off && worth_it && p->comm == nullptr && p->n_cdim > 0 && !(iterative && pcg_host_driven);
   if (graphs_ok && (!p->graph_opts_valid || std::memcmp(&p->graph_opts, &o, sizeof(o)) != 0)) {
     p->DropGraphs();
@@ -204,7 +205,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       if ((r = PrepareLMDiagonal(p, o))) return r;
       if ((r = PointBlocks(p, false))) return r;
       if (p->n_cdim > 0) {
-        if ((r = ReducedRhs(p))) return r;
+        if ((r = ReducedRhs(p, multi))) return r;  // multi-GPU: summed across ranks by the Schur build's all-reduce
         if (iterative) {
           if ((r = DecideBlockSchur(p))) return r;  // once per problem: explicit block-sparse S or implicit products
           if ((r = p->bsr.enabled ? BuildExplicitSchur(p) : BuildSchurJacobi(p))) return r;
@@ -216,17 +217,24 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
           if ((r = CholeskySolve(p))) return r;
           lin_iters = 1;
         }
+        if (p->rhs_unreduced) {  // no Schur build carried it (no preconditioner blocks)
+          if ((r = AllReduceSum(p, p->d_rhs.p, p->n_cdim))) return r;
+          p->rhs_unreduced = false;
+        }
       } else if (marks) {
         tm.Mark(1, st);
       }
       if (marks) tm.Mark(2, st);
-      if ((r = BackSubstitute(p))) return r;
-      if ((r = TrustRegionUpdate(p, o, 0, false))) return r;
+      // multi-GPU: model_cost_change and the point-side norms stay per-rank partial sums until the candidate cost's
+      // all-reduce, which carries all four; the step's validity (phase 0) is then decided after it.  Nothing between reads it.
+      if ((r = BackSubstitute(p, multi))) return r;
+      if (!multi && (r = TrustRegionUpdate(p, o, 0, false))) return r;
       if (marks) tm.Mark(3, st);
-      if ((r = ApplyStep(p))) return r;
+      if ((r = ApplyStep(p, multi))) return r;
       if (marks) tm.Mark(4, st);
-      if ((r = LaunchCostOnly(p, loss, true, &sc->cand_cost))) return r;
+      if ((r = LaunchCostOnly(p, loss, true, &sc->cand_cost, multi))) return r;
       if (marks) tm.Mark(5, st);
+      if (multi && (r = TrustRegionUpdate(p, o, 0, false))) return r;
       if ((r = TrustRegionUpdate(p, o, 1, false))) return r;
       SBA_CUDA(cudaMemcpyAsync(hs, sc, sizeof(*hs), cudaMemcpyDeviceToHost, st));
       return SBA_OK;
@@ -278,7 +286,7 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       auto linearise_segment = [&]() -> int {
         int r;
         if (marks) tm.Mark(6, st);
-        if ((r = LaunchEvaluate(p, loss, o.jacobi_scaling != 0, false))) return r;
+        if ((r = LaunchEvaluate(p, loss, o.jacobi_scaling != 0, false, multi))) return r;  // cost sums ride on the gradient's all-reduce
         if ((r = PointBlocks(p, true))) return r;
         if ((r = Gradient(p, true))) return r;  // + the camera column norms the next LM diagonal needs, same pass over F
         if (marks) tm.Mark(7, st);

@@ -696,13 +696,14 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_scale_i.Alloc((size_t)std::max(1, p->n_img) * 6)); UP(p->d_scale_k.Alloc((size_t)std::max(1, p->n_cam) * 12));
   UP(p->d_red.Alloc(2048));
   UP(p->d_scale_c.Alloc(nc)); UP(p->d_scale_p.Alloc(np3));
-  UP(p->d_sq_c.Alloc(nc)); UP(p->d_sq_p.Alloc(np3));
+  UP(p->d_sq_p.Alloc(np3));
   UP(p->d_diag_c.Alloc(nc)); UP(p->d_diag_p.Alloc(np3)); UP(p->d_Dc.Alloc(nc)); UP(p->d_Dp.Alloc(np3));
   UP(p->d_Cinv.Alloc((size_t)std::max(1, p->n_pvar) * 6)); UP(p->d_gp.Alloc(np3));
   UP(p->d_chunk_partial.Alloc((size_t)std::max(1, p->n_chunks) * kMaxDC * 2));
   UP(p->d_g2.Alloc((size_t)std::max(1, n_obs) * 2));
   UP(p->d_rhs.Alloc(nc)); UP(p->d_yc.Alloc(nc)); UP(p->d_yp.Alloc(np3)); UP(p->d_step_c.Alloc(nc));
-  UP(p->d_grad_c.Alloc(nc)); UP(p->d_grad_p.Alloc(np3)); UP(p->d_tmp_c.Alloc(nc));
+  UP(p->d_grad_c.Alloc(2 * nc + 2)); p->d_sq_c.View(p->d_grad_c.p + p->n_cdim, nc);  // adjacent: Gradient(with_norms) all-reduces both at once
+  UP(p->d_grad_p.Alloc(np3)); UP(p->d_tmp_c.Alloc(nc));
   UP(p->d_cg_r.Alloc(nc)); UP(p->d_cg_z.Alloc(nc)); UP(p->d_cg_p.Alloc(nc)); UP(p->d_cg_q.Alloc(nc)); UP(p->d_cg_x.Alloc(nc));
   UP(p->d_scalars.Alloc(1)); UP(p->d_scalars.Zero(st));
   UP(p->d_tickets.Alloc(8)); UP(p->d_tickets.Zero(st));

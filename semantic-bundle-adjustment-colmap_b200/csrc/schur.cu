@@ -481,7 +481,7 @@ static int EnsureBlockStorage(Problem* p) {
   for (int b = 0; b < p->n_blk; ++b) moff[b + 1] = moff[b] + p->h_blk_dim[b] * p->h_blk_dim[b];
   p->m_size = moff[p->n_blk];
   SBA_CUDA(p->d_blk_moff.Upload(moff, p->stream));
-  SBA_CUDA(p->d_M.Alloc(std::max(1, p->m_size))); SBA_CUDA(p->d_Minv.Alloc(std::max(1, p->m_size)));
+  SBA_CUDA(p->d_M.Alloc(std::max(1, p->m_size) + p->n_cdim)); SBA_CUDA(p->d_Minv.Alloc(std::max(1, p->m_size)));
   SBA_CUDA(cudaStreamSynchronize(p->stream));
   return SBA_OK;
 }
@@ -552,7 +552,7 @@ int BuildDenseSchur(Problem* p) {
   sink.kind = 0; sink.S = p->d_S.p; sink.n = (int)n; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
   rc = Accumulate(p, p->pairs_dense, sink);
   if (rc) return rc;
-  rc = AllReduceSum(p, p->d_S.p, n * n);
+  rc = AllReduceSumWithRhs(p, p->d_S.p, n * n);  // the row behind S carries the reduced right-hand side along
   if (rc) return rc;
   p->chol_add_diag = (int)n <= kCholSmallMax;  // the small-system Cholesky adds D^2 while loading its diagonal tiles
   if (n > 0 && !p->chol_add_diag) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, p->d_S.p, p->d_Dc.p); p->launches++; }
@@ -573,7 +573,7 @@ int BuildSchurJacobi(Problem* p) {
   sink.blk_dim = p->d_blk_dim.p; sink.blk_moff = p->d_blk_moff.p; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
   rc = Accumulate(p, p->pairs_diag, sink);
   if (rc) return rc;
-  rc = AllReduceSum(p, p->d_M.p, p->m_size);
+  rc = AllReduceSumWithRhs(p, p->d_M.p, p->m_size);
   if (rc) return rc;
   invert_blocks_kernel<<<DivUp(p->n_blk, 64), 64, 0, p->stream>>>(p->n_blk, p->d_blk_off.p, p->d_blk_dim.p, p->d_blk_moff.p,
                                                                  p->d_M.p, p->d_Dc.p, p->d_Minv.p, p->d_scalars.p);
@@ -623,7 +623,7 @@ int BuildExplicitSchur(Problem* p) {
   sink.kind = 2; sink.B = B.blocks.p; sink.n_img = p->n_img; sink.key_block = p->comm ? B.key_block.p : nullptr;
   rc = Accumulate(p, p->pairs_dense, sink);
   if (rc) return rc;
-  rc = AllReduceSum(p, B.blocks.p, (size_t)B.n_blocks * ne);
+  rc = AllReduceSumWithRhs(p, B.blocks.p, (size_t)B.n_blocks * ne);
   if (rc) return rc;
   if (p->n_blk == 0) return SBA_OK;
   Sink m;

@@ -85,6 +85,7 @@ struct DeviceScalars {
   double fixed_cost;        // blocks with only constant parameters
   double cand_cost;         // candidate cost
   double model_cost_change;
+  double step2_p, x2_p;     // point-side step / parameter square norms (sharded); with the two above: ONE all-reduce of 4
   double radius;
   double decrease_factor;
   double relative_decrease;
@@ -104,7 +105,7 @@ struct DeviceScalars {
   int chol_fail;
   int converged;  // 1 parameter tolerance, 2 function tolerance reached in this iteration
   // squared norms for step_norm / x_norm: camera-side (replicated) and point-side (sharded)
-  double step2_c, x2_c, step2_p, x2_p;
+  double step2_c, x2_c;
 };
 
 class Comm;  // NCCL wrapper (comm.cu)
@@ -235,6 +236,8 @@ struct Problem {
   DevBuf<float> d_sem_maps;  int sem_h = 0, sem_w = 0;  double sem_weight = 0.0;
   bool solved = false;
   bool linearized = false;
+  bool cost_unreduced = false;              // multi-GPU: scalars->cost / fixed_cost are partial sums; Gradient(with_norms) carries them
+  bool rhs_unreduced = false;               // multi-GPU: d_rhs holds this rank's partial sum; the Schur build's all-reduce carries it
   bool colnorm_current = false;             // d_sq_c holds the camera column norms of the CURRENT Jacobian (Gradient(with_norms))
   int cg_poll_every = 4;                    // host polls the CG state every this many iterations
   double* jq_out = nullptr;                 // parity surface: raw 2x4 quaternion block per observation
@@ -259,8 +262,9 @@ int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int 
 cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st);  // fills h_local2ref / h_obs_img / h_obs_pt on first use (sba_evaluate)
 int ProblemCounts(const sba_problem_desc* d, sba_summary* s);
 // eval.cu
-int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate);
-int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost /* &scalars->cand_cost */);
+int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate, bool defer_allreduce = false);
+int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_out_cost /* &scalars->cand_cost */,
+                   bool with_step_scalars = false);
 // linalg.cu (column norms, point blocks, rhs, matvec, back-substitution, update)
 int ColumnNorms(Problem* p, double* d_nc, double* d_np, bool camera_part = true);
 int Gradient(Problem* p, bool with_norms = false);
@@ -269,13 +273,15 @@ int AllReduceMax(Problem* p, double* d_buf, size_t n);
 int InitJacobiScale(Problem* p);
 int PrepareLMDiagonal(Problem* p, const sba_solver_options& o);
 int PointBlocks(Problem* p, bool grad_only);
-int ReducedRhs(Problem* p);
+int ReducedRhs(Problem* p, bool defer_allreduce = false);  // deferred: see Problem::rhs_unreduced, AllReduceSumWithRhs
 int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip = nullptr);  // *skip != 0: the big kernels return at once
-int BackSubstitute(Problem* p);
+int BackSubstitute(Problem* p, bool defer_allreduce = false);
 int ModelCostChange(Problem* p);
-int ApplyStep(Problem* p);
+int ApplyStep(Problem* p, bool defer_allreduce = false);
 int TrustRegionUpdate(Problem* p, const sba_solver_options& o, int phase, bool sync);
 int AllReduceSum(Problem* p, double* d_buf, size_t n);
+// sums d_buf[0..n) and, when rhs_unreduced, d_rhs in the same collective (d_buf needs n + n_cdim doubles of room)
+int AllReduceSumWithRhs(Problem* p, double* d_buf, size_t n);
 int AllReduceMaxInt(Problem* p, int* d_buf, size_t n);
 // pairs.cu
 int BuildPairLists(Problem* p, bool dense);
