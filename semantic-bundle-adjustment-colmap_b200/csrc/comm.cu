@@ -44,15 +44,139 @@ struct NcclApi {
 NcclApi g_nccl;
 }  // namespace
 
+// ---- small all-reduces over NVLink peer memory --------------------------------------------------------------------
+// The LM iteration's collectives are short (a few scalars, a camera-space vector, the reduced camera matrix of a
+// small problem) and latency-bound: an NCCL launch costs ~25 us where the data needs ~2.  For up to kP2PCapacity
+// doubles every rank instead owns one cudaMalloc'ed exchange area that all peers map through CUDA IPC.  One launch:
+// CTA b copies its slice of the operand into its slot of the local area, raises flag (rank, b) on every peer with a
+// system-scope release store, waits for the same flag from every peer, then reads slot b of every rank over NVLink and
+// combines them IN RANK ORDER -- so every rank computes bit-identical results, which the replicated camera-side state
+// relies on.  Slots are double-buffered on the parity of a per-CTA epoch kept in device memory (a peer can run at most
+// one collective ahead: it cannot finish collective e+1 without this rank's flag e+1), and nothing in the protocol is a
+// kernel argument that changes between launches, so the launch replays inside a CUDA graph.
+constexpr int kP2PCtas = 64, kP2PThreads = 512, kP2PSlot = 2048, kP2PMaxRanks = 8;
+constexpr size_t kP2PCapacity = (size_t)kP2PCtas * kP2PSlot;                         // doubles per collective
+constexpr size_t kP2PDataBytes = 2 * kP2PCapacity * sizeof(double);                  // two parities
+constexpr size_t kP2PAreaBytes = kP2PDataBytes + (size_t)(kP2PMaxRanks + 1) * kP2PCtas * sizeof(unsigned);
+
+struct P2PView {
+  double* data[kP2PMaxRanks];     // every rank's exchange area as mapped here ([rank] is the local one)
+  unsigned* flags[kP2PMaxRanks];  // every rank's flag array [kP2PMaxRanks][kP2PCtas]
+  unsigned* epoch;                // local: collectives completed, per CTA
+  int nranks, rank;
+};
+
+__device__ __forceinline__ void StoreReleaseSys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned LoadAcquireSys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double LoadRelaxedSys(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <bool MAX>
+__global__ void __launch_bounds__(kP2PThreads) p2p_allreduce_kernel(P2PView V, double* __restrict__ buf, int n) {
+  const int b = blockIdx.x, t = threadIdx.x;
+  __shared__ unsigned s_epoch;
+  if (t == 0) s_epoch = V.epoch[b] + 1;
+  __syncthreads();
+  const unsigned e = s_epoch;
+  const int per = (n + gridDim.x - 1) / gridDim.x, lo = b * per, cnt = max(0, min(per, n - lo));
+  const size_t slot = ((size_t)(e & 1) * kP2PCtas + b) * kP2PSlot;
+  double* mine = V.data[V.rank] + slot;
+  for (int i = t; i < cnt; i += kP2PThreads) mine[i] = buf[lo + i];
+  __syncthreads();
+  if (t < V.nranks && t != V.rank) {
+    __threadfence_system();
+    StoreReleaseSys(V.flags[t] + (size_t)V.rank * kP2PCtas + b, e);
+    const unsigned* f = V.flags[V.rank] + (size_t)t * kP2PCtas + b;
+    while ((int)(LoadAcquireSys(f) - e) < 0) {}
+  }
+  __syncthreads();
+  for (int i = t; i < cnt; i += kP2PThreads) {
+    double a = LoadRelaxedSys(V.data[0] + slot + i);
+    for (int r = 1; r < V.nranks; ++r) {
+      const double v = LoadRelaxedSys(V.data[r] + slot + i);
+      a = MAX ? fmax(a, v) : a + v;
+    }
+    buf[lo + i] = a;
+  }
+  if (t == 0) V.epoch[b] = e;
+}
+
 class Comm {
  public:
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  bool p2p = false;  // the exchange areas are mapped on every rank
+  P2PView view{};
 };
 
 static int NcclFail(const char* what, ncclResult_t r) {
   SetError(SBA_ERR_COMM, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "nccl error"));
   return SBA_ERR_COMM;
+}
+
+// Maps every rank's exchange area into this process.  Every step is followed by a consensus over NCCL, so either all
+// ranks switch to the peer-memory path or none does (SBA_NO_P2P_ALLREDUCE=1 keeps every collective on NCCL).
+static void SetupP2P(Comm* c) {
+  if (getenv("SBA_NO_P2P_ALLREDUCE") || c->nranks > kP2PMaxRanks) return;
+  const int nr = c->nranks, hw = (int)(sizeof(cudaIpcMemHandle_t) / sizeof(int)), words = nr * (hw + 1);
+  int ok = 1;
+  void* area = nullptr;
+  if (cudaMalloc(&area, kP2PAreaBytes) != cudaSuccess) { ok = 0; area = nullptr; }
+  if (ok && cudaMemset(area, 0, kP2PAreaBytes) != cudaSuccess) ok = 0;
+  cudaIpcMemHandle_t mine;
+  std::memset(&mine, 0, sizeof(mine));
+  if (ok && cudaIpcGetMemHandle(&mine, area) != cudaSuccess) ok = 0;
+  cudaGetLastError();
+  std::vector<int> h((size_t)words, 0);
+  std::memcpy(h.data() + (size_t)c->rank * hw, &mine, sizeof(mine));
+  h[(size_t)nr * hw + c->rank] = ok;
+  int* d = nullptr;
+  auto gather = [&]() -> bool {  // a sum over slots only their owner fills = an all-gather
+    if (cudaMemcpy(d, h.data(), words * sizeof(int), cudaMemcpyHostToDevice) != cudaSuccess) return false;
+    if (g_nccl.AllReduce(d, d, words, ncclInt32, ncclSum, c->comm, nullptr) != ncclSuccess) return false;
+    if (cudaStreamSynchronize(nullptr) != cudaSuccess) return false;
+    return cudaMemcpy(h.data(), d, words * sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess;
+  };
+  auto all_ok = [&]() { for (int r = 0; r < nr; ++r) if (h[(size_t)nr * hw + r] != 1) return false; return true; };
+  if (cudaMalloc(&d, words * sizeof(int)) != cudaSuccess) { cudaGetLastError(); if (area) cudaFree(area); return; }  // (cannot even vote: NCCL only, and so will the peers' first gather fail loudly)
+  bool good = gather() && all_ok();
+  void* peer[kP2PMaxRanks] = {nullptr};
+  if (good) {
+    for (int r = 0; r < nr; ++r) {
+      if (r == c->rank) { peer[r] = area; continue; }
+      cudaIpcMemHandle_t hr;
+      std::memcpy(&hr, h.data() + (size_t)r * hw, sizeof(hr));
+      if (cudaIpcOpenMemHandle(&peer[r], hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; peer[r] = nullptr; }
+    }
+    cudaGetLastError();
+    std::fill(h.begin(), h.end(), 0);
+    h[(size_t)nr * hw + c->rank] = ok;
+    good = gather() && all_ok();  // (also a barrier: every area is zeroed and mapped before the first flag is raised)
+  }
+  cudaFree(d);
+  if (!good) {
+    for (int r = 0; r < nr; ++r) if (r != c->rank && peer[r]) cudaIpcCloseMemHandle(peer[r]);
+    if (area) cudaFree(area);
+    cudaGetLastError();
+    return;
+  }
+  P2PView& V = c->view;
+  V.nranks = nr; V.rank = c->rank;
+  for (int r = 0; r < nr; ++r) {
+    V.data[r] = static_cast<double*>(peer[r]);
+    V.flags[r] = reinterpret_cast<unsigned*>(static_cast<char*>(peer[r]) + kP2PDataBytes);
+  }
+  V.epoch = V.flags[c->rank] + (size_t)kP2PMaxRanks * kP2PCtas;
+  c->p2p = true;
 }
 
 int CommGetUniqueId(void* id128) {
@@ -83,6 +207,7 @@ int CommInit(Problem* p, int nranks, int rank, const void* id128) {
   c->nranks = nranks; c->rank = rank;
   const ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
   if (r != ncclSuccess) { delete c; return NcclFail("ncclCommInitRank", r); }
+  SetupP2P(c);
   cache.push_back(c);
   p->comm = c;
   return SBA_OK;
@@ -92,6 +217,15 @@ void CommDestroy(Problem* p) { p->comm = nullptr; }  // communicators are proces
 
 static int AllReduce(Problem* p, double* d_buf, size_t n, ncclRedOp_t op) {
   if (!p->comm || n == 0) return SBA_OK;
+  if (p->comm->p2p && n <= kP2PCapacity && (op == ncclSum || op == ncclMax)) {  // latency-bound sizes: peer memory, one launch
+    // (a CTA's epoch advances only in the collectives it takes part in; the same CTAs take part on every rank)
+    const int grid = (int)std::min<size_t>(kP2PCtas, (n + 1023) / 1024);
+    if (op == ncclSum) p2p_allreduce_kernel<false><<<grid, kP2PThreads, 0, p->stream>>>(p->comm->view, d_buf, (int)n);
+    else p2p_allreduce_kernel<true><<<grid, kP2PThreads, 0, p->stream>>>(p->comm->view, d_buf, (int)n);
+    SBA_CUDA(cudaGetLastError());
+    p->collectives++; p->launches++;
+    return SBA_OK;
+  }
   const ncclResult_t r = g_nccl.AllReduce(d_buf, d_buf, n, ncclDouble, op, p->comm->comm, p->stream);
   if (r != ncclSuccess) return NcclFail("ncclAllReduce", r);
   p->collectives++;

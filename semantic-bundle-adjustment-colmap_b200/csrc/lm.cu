@@ -167,7 +167,8 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
   // host poll inside (decided in the first iteration, which always runs as plain launches).
   static const bool pcg_host_driven = getenv("SBA_PCG_LAUNCHES") != nullptr || getenv("SBA_PCG_TRACE") != nullptr;
   const bool multi = p->comm != nullptr;  // sharded by point: partial sums meet in as few collectives as the data flow allows
-  const bool graphs_ok = !graphs_off && worth_it && p->comm == nullptr && p->n_cdim > 0 && !(iterative && pcg_host_driven);
+  static const bool comm_graphs = getenv("SBA_NO_COMM_GRAPHS") == nullptr;  // the collectives (NCCL or peer-memory) are captured with the rest
+  const bool graphs_ok = !graphs_off && worth_it && (!multi || comm_graphs) && p->n_cdim > 0 && !(iterative && pcg_host_driven);
   if (graphs_ok && (!p->graph_opts_valid || std::memcmp(&p->graph_opts, &o, sizeof(o)) != 0)) {
     p->DropGraphs();
     p->graph_opts = o; p->graph_opts_valid = true;
