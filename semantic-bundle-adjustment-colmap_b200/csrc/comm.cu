@@ -54,7 +54,7 @@ NcclApi g_nccl;
 // relies on.  Slots are double-buffered on the parity of a per-CTA epoch kept in device memory (a peer can run at most
 // one collective ahead: it cannot finish collective e+1 without this rank's flag e+1), and nothing in the protocol is a
 // kernel argument that changes between launches, so the launch replays inside a CUDA graph.
-constexpr int kP2PCtas = 64, kP2PThreads = 512, kP2PSlot = 2048, kP2PMaxRanks = 8;
+constexpr int kP2PCtas = 128, kP2PThreads = 512, kP2PSlot = 1024, kP2PMaxRanks = 8;
 constexpr size_t kP2PCapacity = (size_t)kP2PCtas * kP2PSlot;                         // doubles per collective
 constexpr size_t kP2PDataBytes = 2 * kP2PCapacity * sizeof(double);                  // two parities
 constexpr size_t kP2PAreaBytes = kP2PDataBytes + (size_t)(kP2PMaxRanks + 1) * kP2PCtas * sizeof(unsigned);
@@ -80,6 +80,12 @@ __device__ __forceinline__ double LoadRelaxedSys(const double* p) {
   return v;
 }
 
+__device__ __forceinline__ double2 LoadRelaxedSys2(const double* p) {  // p is 16-byte aligned
+  double2 v;
+  asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+}
+
 template <bool MAX>
 __global__ void __launch_bounds__(kP2PThreads) p2p_allreduce_kernel(P2PView V, double* __restrict__ buf, int n) {
   const int b = blockIdx.x, t = threadIdx.x;
@@ -93,19 +99,27 @@ __global__ void __launch_bounds__(kP2PThreads) p2p_allreduce_kernel(P2PView V, d
   for (int i = t; i < cnt; i += kP2PThreads) mine[i] = buf[lo + i];
   __syncthreads();
   if (t < V.nranks && t != V.rank) {
-    __threadfence_system();
+    // (the release is cumulative over the barrier above: the whole CTA's slot writes are visible before the flag)
     StoreReleaseSys(V.flags[t] + (size_t)V.rank * kP2PCtas + b, e);
     const unsigned* f = V.flags[V.rank] + (size_t)t * kP2PCtas + b;
     while ((int)(LoadAcquireSys(f) - e) < 0) {}
   }
   __syncthreads();
-  for (int i = t; i < cnt; i += kP2PThreads) {
-    double a = LoadRelaxedSys(V.data[0] + slot + i);
-    for (int r = 1; r < V.nranks; ++r) {
-      const double v = LoadRelaxedSys(V.data[r] + slot + i);
-      a = MAX ? fmax(a, v) : a + v;
-    }
-    buf[lo + i] = a;
+  // all ranks' loads are issued before the first use (an NVLink round trip is ~2 us: a load-add chain would pay it per rank)
+  for (int i = 2 * t; i < cnt; i += 2 * kP2PThreads) {
+    double2 v[kP2PMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kP2PMaxRanks; ++r)
+      if (r < V.nranks) v[r] = LoadRelaxedSys2(V.data[r] + slot + i);  // (i + 1 may lie past cnt, never past the slot)
+    double2 a = v[0];
+#pragma unroll
+    for (int r = 1; r < kP2PMaxRanks; ++r)
+      if (r < V.nranks) {
+        a.x = MAX ? fmax(a.x, v[r].x) : a.x + v[r].x;
+        a.y = MAX ? fmax(a.y, v[r].y) : a.y + v[r].y;
+      }
+    buf[lo + i] = a.x;
+    if (i + 1 < cnt) buf[lo + i + 1] = a.y;
   }
   if (t == 0) V.epoch[b] = e;
 }
