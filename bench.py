@@ -185,7 +185,17 @@ def pba_second_opinion(m):
     d = prob.desc()
     out = np.zeros(5)
     threads = os.cpu_count() or 1
-    if lib.pba_ref_solve(C.byref(d), LM_ITERS, threads, 1, out.ctypes.data_as(C.POINTER(C.c_double)), None) != 0:
+    # lib/PBA prints a banner from C: keep stdout to the one JSON line (the banner goes to stderr)
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        rc = lib.pba_ref_solve(C.byref(d), LM_ITERS, threads, 1, out.ctypes.data_as(C.POINTER(C.c_double)), None)
+        C.CDLL(None).fflush(None)
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+    if rc != 0:
         return {"unavailable": "PBA rejected the problem"}
     s = m.Solver(prob)
     o = solver_options(m, len(prob.image_camera))
