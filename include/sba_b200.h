@@ -283,7 +283,9 @@ int sba_schur_product(sba_handle* h, int32_t use_blocks, const double* x, double
 /* Number of kernels this library launched on h's stream since creation. */
 int64_t sba_kernel_launch_count(sba_handle* h);
 
-/* --- multi-GPU (one process per GPU; NCCL over NVLink) ------------------ */
+/* --- multi-GPU (one process per GPU; NCCL over NVLink, and for collectives
+ * of <= 1 MB this library's own all-reduce kernel over CUDA-IPC peer memory,
+ * set up inside sba_comm_init; SBA_NO_P2P_ALLREDUCE=1 keeps all on NCCL) --- */
 #define SBA_COMM_ID_BYTES 128
 int sba_comm_get_unique_id(void* id128);
 int sba_comm_init(sba_handle* h, int32_t nranks, int32_t rank, const void* id128);
