@@ -102,7 +102,16 @@ __global__ void __launch_bounds__(kP2PThreads) p2p_allreduce_kernel(P2PView V, d
     // (the release is cumulative over the barrier above: the whole CTA's slot writes are visible before the flag)
     StoreReleaseSys(V.flags[t] + (size_t)V.rank * kP2PCtas + b, e);
     const unsigned* f = V.flags[V.rank] + (size_t)t * kP2PCtas + b;
-    while ((int)(LoadAcquireSys(f) - e) < 0) {}
+    // a peer that died or left the sequence must not leave this GPU spinning for ever: after 30 s the kernel traps and
+    // every later CUDA call of this process reports the failure
+    unsigned long long t0 = 0;
+    for (unsigned spins = 0; (int)(LoadAcquireSys(f) - e) < 0; ++spins) {
+      if ((spins & 0xfff) != 0xfff) continue;
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 30000000000ull) __trap();
+    }
   }
   __syncthreads();
   // all ranks' loads are issued before the first use (an NVLink round trip is ~2 us: a load-add chain would pay it per rank)
