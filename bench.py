@@ -358,7 +358,12 @@ def run_b200(args, m):
         ob = solver_options(m, len(big.image_camera))
         sb.solve(ob)   # first solve of the handle: pair lists, block structure, first-touch allocations
         sb.reset()
-        sm = sb.solve(ob)
+        sb.solve(ob)   # second: the iteration's CUDA graphs are captured and instantiated here
+        runs = []
+        for _ in range(3):  # steady state of a re-solved handle, like the headline's timed steps: median of three
+            sb.reset()
+            runs.append(sb.solve(ob))
+        sm = sorted(runs, key=lambda r: r.device_time_s)[1]
         itb = sm.num_successful_steps + sm.num_unsuccessful_steps
         it_stages = ["eval", "cost", "point_blocks", "rhs", "backsub"] + (
             ["schur_jacobi", "matvec", "schur_blocks", "matvec_blocks"] if sm.linear_solver_type_used == m.capi.ITERATIVE_SCHUR else ["schur_dense", "cholesky"])
