@@ -5,7 +5,8 @@
 // Here observations are sharded by point ownership (problem.cu) and camera-space
 // quantities -- cost scalars, gradient / reduced right-hand side, the reduced camera
 // matrix or its SCHUR_JACOBI block diagonal, and one camera-space vector per PCG
-// product -- are summed across ranks with fp64 ncclAllReduce.
+// product -- are summed across ranks: operands of up to 1 MB by the peer-memory all-reduce kernel
+// below, larger ones by fp64 ncclAllReduce.  lm.cu lets partial sums that meet at the same point share one collective.
 //
 // NCCL is resolved at run time with dlopen("libnccl.so.2"): inside a PyTorch process
 // this binds to the copy torch already loaded (one NCCL per process); in a plain C++
@@ -46,7 +47,8 @@ NcclApi g_nccl;
 
 // ---- small all-reduces over NVLink peer memory --------------------------------------------------------------------
 // The LM iteration's collectives are short (a few scalars, a camera-space vector, the reduced camera matrix of a
-// small problem) and latency-bound: an NCCL launch costs ~25 us where the data needs ~2.  For up to kP2PCapacity
+// small problem) and latency-bound: at 8 GPUs ncclAllReduce measured ~17 us more per call than this kernel (C2 weak, 30
+// collectives per solve: 3.47 vs 2.95 ms, profiles/r01_bench_c2_8gpu_weak*.json).  For up to kP2PCapacity
 // doubles every rank instead owns one cudaMalloc'ed exchange area that all peers map through CUDA IPC.  One launch:
 // CTA b copies its slice of the operand into its slot of the local area, raises flag (rank, b) on every peer with a
 // system-scope release store, waits for the same flag from every peer, then reads slot b of every rank over NVLink and
