@@ -123,13 +123,19 @@ typedef struct sba_problem_desc {
   const double* obs_xy;     /* [num_observations*2] Point2D::XY() */
 
   /* ---- extension X1 (not in the reference) ----
-   * Optional per-image semantic maps sampled bilinearly at the projection
-   * (convention of Bitmap::InterpolateBilinear, src/util/bitmap.cc:238-269).
-   * NULL / 0 disables the third residual row. */
-  const float* sem_maps;         /* [num_images*sem_height*sem_width] row-major */
+   * Optional per-image semantic maps (label-probability or distance maps) sampled bilinearly at the
+   * projection (x, y) of the point (convention of Bitmap::InterpolateBilinear,
+   * src/util/bitmap.cc:238-269).  When given, EVERY residual block has three rows,
+   *   r = (x - obs_x, y - obs_y, sem_weight * map_img(x, y)),
+   * the third with the analytic Jacobian sem_weight * (d map/dx, d map/dy) * d(x,y)/d(pose, point, intrinsics)
+   * (d map/d. = differences of the four texels of the cell); a rejected sample (neighbour outside the map)
+   * gives r_s = 0 and a zero row.  The loss acts on the squared norm of all three rows.  sba_evaluate,
+   * sba_solve and the structural counts (num_residuals = 3 per block) all include the row.
+   * NULL / 0 keeps the reference's two-row blocks. */
+  const float* sem_maps;         /* [num_images*sem_height*sem_width] row-major, top-down */
   int32_t sem_height;
   int32_t sem_width;
-  double sem_weight;             /* residual = sem_weight * map_img(x, y) */
+  double sem_weight;
 
   /* ---- sharding (multi-GPU) ----
    * A shard holds ALL images/cameras and a subset of points with all their
@@ -242,12 +248,17 @@ int sba_device_count(void);
  *   jac_intr    [n_obs*2*SBA_MAX_CAMERA_PARAMS] d r / d camera params (ambient; constant params zeroed)
  *   jac_point   [n_obs*2*3]
  *   jac_qvec_ambient [n_obs*2*4] raw autodiff-equivalent block w.r.t. (w,x,y,z) before the manifold
- *   sem_residuals [n_obs] (extension X1; only when maps were given)
+ *   sem_residuals [n_obs] third residual row (extension X1; only when maps were given), loss-corrected like `residuals`
  * apply_loss: 0 = raw functor outputs (CostFunction::Evaluate), 1 = loss-corrected (Problem::Evaluate). */
 int sba_evaluate(sba_handle* h, int32_t loss_function_type, double loss_function_scale,
                  int32_t apply_loss, double* cost, double* residuals, double* jac_pose,
                  double* jac_intr, double* jac_point, double* jac_qvec_ambient,
                  double* sem_residuals);
+
+/* Jacobian of the third (semantic) residual row as left by the last sba_evaluate / linearisation on this handle,
+ * REFERENCE residual order, same column conventions as sba_evaluate: jac_pose [n_obs*6] (quat tangent, tvec),
+ * jac_intr [n_obs*SBA_MAX_CAMERA_PARAMS] (ambient, constant params zero), jac_point [n_obs*3].  Any may be NULL. */
+int sba_get_semantic_jacobian(sba_handle* h, double* jac_pose, double* jac_intr, double* jac_point);
 
 /* --- solve -------------------------------------------------------------- */
 int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callback cb,

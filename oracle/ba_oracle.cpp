@@ -23,6 +23,11 @@ namespace oracle {
 // ---------------------------------------------------------------------------
 void BAProblem::Build(const sba_problem_desc& d) {
   n_img = d.num_images; n_cam = d.num_cameras; n_pt = d.num_points; n_obs = d.num_observations;
+  if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) {
+    nr = 3; sem_maps = d.sem_maps; sem_h = d.sem_height; sem_w = d.sem_width; sem_weight = d.sem_weight;
+  } else {
+    nr = 2; sem_maps = nullptr;
+  }
   q.assign(d.image_qvec, d.image_qvec + 4 * (size_t)n_img);
   t.assign(d.image_tvec, d.image_tvec + 3 * (size_t)n_img);
   cam.assign(d.camera_params, d.camera_params + SBA_MAX_CAMERA_PARAMS * (size_t)n_cam);
@@ -82,12 +87,12 @@ void BAProblem::Build(const sba_problem_desc& d) {
     num_parameter_blocks_reduced++; num_parameters_reduced += 3; num_effective_parameters_reduced += 3;
   }
   obs_active.assign(n_obs, 0);
-  num_residual_blocks = (int)n_obs; num_residuals = (int)(2 * n_obs); num_residuals_reduced = 0;
+  num_residual_blocks = (int)n_obs; num_residuals = (int)(nr * n_obs); num_residuals_reduced = 0;
   for (int64_t k = 0; k < n_obs; ++k) {
     const int i = obs_img[k], c = img_cam[i], p = obs_pt[k];
     const bool act = (q_off[i] >= 0) || (t_off[i] >= 0) || (k_off[c] >= 0) || (p_off[p] >= 0);
     obs_active[k] = act;
-    if (act) num_residuals_reduced += 2;
+    if (act) num_residuals_reduced += nr;
   }
   // CSR by point
   pt_ptr.assign(n_pt + 1, 0);
@@ -111,10 +116,34 @@ int BAProblem::ObsCols(int64_t k, int* cols) const {
 // Functor evaluation (cost_functions.h:57-81) with Jet<4+3+3+P>, as
 // AutoDiffCostFunction<..., 2, 4, 3, 3, kNumParams> does (cost_functions.h:50-55).
 // ---------------------------------------------------------------------------
+static inline double ScalarPart(double x) { return x; }
+template <int N> static inline double ScalarPart(const Jet<N>& x) { return x.a; }
+
+// Bitmap::InterpolateBilinear (src/util/bitmap.cc:238-269) over T (double or Jet) on a top-down ROW-major float
+// map: the cell is chosen by the VALUE (floor acts on the scalar part, as every Jet comparison does), the
+// interpolation weights carry the derivatives -- so the Jet result is the exact Jacobian of the interpolant
+// inside its cell.  false: the sample is rejected (x0 < 0, x1 >= W, y0 < 0, y1 >= H).
+template <typename T>
+static bool BilinearT(const float* map, int H, int W, const T& x, const T& y, T* out) {
+  const T inv_y = double(H - 1) - y;
+  const double fx = std::floor(ScalarPart(x)), fy = std::floor(ScalarPart(inv_y));
+  if (!(fx >= 0.0 && fx + 1.0 < (double)W && fy >= 0.0 && fy + 1.0 < (double)H)) return false;
+  const int x0 = (int)fx, x1 = x0 + 1, y0 = (int)fy, y1 = y0 + 1;
+  const T dx = x - double(x0), dy = inv_y - double(y0);
+  const T dx_1 = 1.0 - dx, dy_1 = 1.0 - dy;
+  const float* line0 = map + (size_t)(H - 1 - y0) * W;  // FreeImage scanline y0 (bottom-up) in the top-down map
+  const float* line1 = map + (size_t)(H - 1 - y1) * W;
+  const T v0 = dx_1 * double(line0[x0]) + dx * double(line0[x1]);
+  const T v1 = dx_1 * double(line1[x0]) + dx * double(line1[x1]);
+  *out = dy_1 * v0 + dy * v1;
+  return true;
+}
+
+// rows = 2, or 3 when map != nullptr (the semantic row, extension X1); J blocks are row-major rows x cols
 template <int P>
 static void EvalObsJet(int model, const double* q, const double* t, const double* X,
-                       const double* params, const double* xy, double* r, double* Jq, double* Jt,
-                       double* JX, double* Jk) {
+                       const double* params, const double* xy, const float* map, int H, int W, double weight,
+                       double* r, double* Jq, double* Jt, double* JX, double* Jk) {
   constexpr int N = 10 + P;
   typedef Jet<N> J;
   J jq[4], jt[3], jX[3], jp[P];
@@ -127,11 +156,16 @@ static void EvalObsJet(int model, const double* q, const double* t, const double
   proj[0] += jt[0]; proj[1] += jt[1]; proj[2] += jt[2];
   proj[0] /= proj[2];
   proj[1] /= proj[2];
-  J res[2];
+  J res[3];
   Project<J>(model, jp, proj[0], proj[1], &res[0], &res[1]);
+  const int rows = map ? 3 : 2;
+  if (map) {
+    J m;
+    if (BilinearT<J>(map, H, W, res[0], res[1], &m)) res[2] = weight * m; else res[2] = J(0.0);
+  }
   res[0] = res[0] - xy[0];
   res[1] = res[1] - xy[1];
-  for (int row = 0; row < 2; ++row) {
+  for (int row = 0; row < rows; ++row) {
     r[row] = res[row].a;
     if (Jq) for (int i = 0; i < 4; ++i) Jq[row * 4 + i] = res[row].v[i];
     if (Jt) for (int i = 0; i < 3; ++i) Jt[row * 3 + i] = res[row].v[4 + i];
@@ -186,9 +220,10 @@ void EvalRigObservation(int model, const double* rig_q, const double* rig_t, con
   }
 }
 
-// residual-only (double) evaluation, used for candidate-step cost
+// residual-only (double) evaluation, used for candidate-step cost; r[2], or r[3] with a map
 static inline void EvalObsValue(int model, const double* q, const double* t, const double* X,
-                                const double* params, const double* xy, double* r) {
+                                const double* params, const double* xy, const float* map, int H, int W, double weight,
+                                double* r) {
   double proj[3];
   UnitQuaternionRotatePoint(q, X, proj);
   proj[0] += t[0]; proj[1] += t[1]; proj[2] += t[2];
@@ -198,19 +233,28 @@ static inline void EvalObsValue(int model, const double* q, const double* t, con
   Project<double>(model, params, proj[0], proj[1], &x, &y);
   r[0] = x - xy[0];
   r[1] = y - xy[1];
+  if (map) {
+    double m;
+    r[2] = BilinearT<double>(map, H, W, x, y, &m) ? weight * m : 0.0;
+  }
 }
 
+void EvalObservationSem(int model, const double* q, const double* t, const double* X, const double* params,
+                        const double* xy, const float* map, int H, int W, double weight, double* r, double* Jq,
+                        double* Jt, double* JX, double* Jk) {
+  switch (NumParams(model)) {
+    case 3: EvalObsJet<3>(model, q, t, X, params, xy, map, H, W, weight, r, Jq, Jt, JX, Jk); break;
+    case 4: EvalObsJet<4>(model, q, t, X, params, xy, map, H, W, weight, r, Jq, Jt, JX, Jk); break;
+    case 5: EvalObsJet<5>(model, q, t, X, params, xy, map, H, W, weight, r, Jq, Jt, JX, Jk); break;
+    case 8: EvalObsJet<8>(model, q, t, X, params, xy, map, H, W, weight, r, Jq, Jt, JX, Jk); break;
+    case 12: EvalObsJet<12>(model, q, t, X, params, xy, map, H, W, weight, r, Jq, Jt, JX, Jk); break;
+    default: r[0] = r[1] = std::numeric_limits<double>::quiet_NaN(); if (map) r[2] = r[0];
+  }
+}
 void EvalObservation(int model, const double* q, const double* t, const double* X,
                      const double* params, const double* xy, double* r, double* Jq, double* Jt,
                      double* JX, double* Jk) {
-  switch (NumParams(model)) {
-    case 3: EvalObsJet<3>(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk); break;
-    case 4: EvalObsJet<4>(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk); break;
-    case 5: EvalObsJet<5>(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk); break;
-    case 8: EvalObsJet<8>(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk); break;
-    case 12: EvalObsJet<12>(model, q, t, X, params, xy, r, Jq, Jt, JX, Jk); break;
-    default: r[0] = r[1] = std::numeric_limits<double>::quiet_NaN();
-  }
+  EvalObservationSem(model, q, t, X, params, xy, nullptr, 0, 0, 0.0, r, Jq, Jt, JX, Jk);
 }
 
 // ceres loss functions (TrivialLoss / SoftLOneLoss / CauchyLoss), App. B.2
@@ -232,33 +276,42 @@ static inline void LossEval(int type, double a, double s, double rho[3]) {
   }
 }
 
+static inline const float* MapOf(const BAProblem& p, int i) {
+  return p.sem_maps ? p.sem_maps + (size_t)i * p.sem_h * p.sem_w : nullptr;
+}
+
 void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_loss,
                Linearization* lin, int num_threads) {
-  const int dc = p.dc_max;
-  lin->r.assign(2 * p.n_obs, 0.0);
-  lin->F.assign((size_t)p.n_obs * 2 * dc, 0.0);
-  lin->E.assign((size_t)p.n_obs * 6, 0.0);
+  const int dc = p.dc_max, nr = p.nr;
+  lin->r.assign((size_t)nr * p.n_obs, 0.0);
+  lin->F.assign((size_t)p.n_obs * nr * dc, 0.0);
+  lin->E.assign((size_t)p.n_obs * nr * 3, 0.0);
   double cost = 0.0, fixed = 0.0;
 #pragma omp parallel for num_threads(num_threads) reduction(+ : cost, fixed) schedule(static)
   for (int64_t k = 0; k < p.n_obs; ++k) {
     const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
     const int m = p.model[c], P = NumParams(m);
-    double r[2], Jq[8], Jt[6], JX[6], Jk[24];
-    EvalObservation(m, &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
-                    &p.obs_xy[2 * k], r, Jq, Jt, JX, Jk);
-    const double s = r[0] * r[0] + r[1] * r[1];
+    double r[3] = {0, 0, 0}, Jq[12], Jt[9], JX[9], Jk[36];
+    EvalObservationSem(m, &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
+                       &p.obs_xy[2 * k], MapOf(p, i), p.sem_h, p.sem_w, p.sem_weight, r, Jq, Jt, JX, Jk);
+    double s = 0.0;
+    for (int row = 0; row < nr; ++row) s += r[row] * r[row];
     double rho[3];
     LossEval(loss_type, loss_scale, s, rho);
-    if (!p.obs_active[k]) { fixed += 0.5 * rho[0]; continue; }
+    if (!p.obs_active[k]) {
+      fixed += 0.5 * rho[0];
+      for (int row = 0; row < nr; ++row) lin->r[(size_t)nr * k + row] = r[row];  // raw, parity surface only
+      continue;
+    }
     cost += 0.5 * rho[0];
     // local (tangent) Jacobian, compact camera-side layout [q(3)][t cols][k cols]
-    double* F = &lin->F[(size_t)k * 2 * dc];
-    double* E = &lin->E[(size_t)k * 6];
+    double* F = &lin->F[(size_t)k * nr * dc];
+    double* E = &lin->E[(size_t)k * nr * 3];
     int n = 0;
     if (p.q_off[i] >= 0) {
       double PJ[12];
       QuaternionPlusJacobian(&p.q[4 * i], PJ);
-      for (int row = 0; row < 2; ++row)
+      for (int row = 0; row < nr; ++row)
         for (int j = 0; j < 3; ++j) {
           double acc = 0.0;
           for (int a = 0; a < 4; ++a) acc += Jq[row * 4 + a] * PJ[a * 3 + j];
@@ -269,18 +322,18 @@ void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_
     if (p.t_off[i] >= 0) {
       for (int j = 0; j < p.t_dim[i]; ++j) {
         const int a = p.t_cols[3 * i + j];
-        F[0 * dc + n + j] = Jt[a]; F[1 * dc + n + j] = Jt[3 + a];
+        for (int row = 0; row < nr; ++row) F[row * dc + n + j] = Jt[row * 3 + a];
       }
       n += p.t_dim[i];
     }
     if (p.k_off[c] >= 0) {
       for (int j = 0; j < p.k_dim[c]; ++j) {
         const int a = p.k_cols[SBA_MAX_CAMERA_PARAMS * c + j];
-        F[0 * dc + n + j] = Jk[a]; F[1 * dc + n + j] = Jk[P + a];
+        for (int row = 0; row < nr; ++row) F[row * dc + n + j] = Jk[row * P + a];
       }
       n += p.k_dim[c];
     }
-    if (p.p_off[pt] >= 0) for (int j = 0; j < 6; ++j) E[j] = JX[j];
+    if (p.p_off[pt] >= 0) for (int j = 0; j < 3 * nr; ++j) E[j] = JX[j];
     // Corrector (ceres/internal/corrector.cc): Jacobian first, then residuals
     if (apply_loss) {
       const double sqrt_rho1 = std::sqrt(rho[1]);
@@ -292,17 +345,18 @@ void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_
         const double alpha = 1.0 - std::sqrt(D);
         residual_scaling = sqrt_rho1 / (1 - alpha); alpha_sq_norm = alpha / s;
       }
-      auto correct = [&](double* J0, double* J1) {
-        if (alpha_sq_norm == 0.0) { *J0 *= sqrt_rho1; *J1 *= sqrt_rho1; return; }
-        const double rtj = r[0] * *J0 + r[1] * *J1;
-        *J0 = sqrt_rho1 * (*J0 - alpha_sq_norm * r[0] * rtj);
-        *J1 = sqrt_rho1 * (*J1 - alpha_sq_norm * r[1] * rtj);
+      // one column: J[row * stride] for row < nr
+      auto correct = [&](double* J, int stride) {
+        if (alpha_sq_norm == 0.0) { for (int row = 0; row < nr; ++row) J[row * stride] *= sqrt_rho1; return; }
+        double rtj = 0.0;
+        for (int row = 0; row < nr; ++row) rtj += r[row] * J[row * stride];
+        for (int row = 0; row < nr; ++row) J[row * stride] = sqrt_rho1 * (J[row * stride] - alpha_sq_norm * r[row] * rtj);
       };
-      for (int j = 0; j < n; ++j) correct(&F[j], &F[dc + j]);
-      for (int j = 0; j < 3; ++j) correct(&E[j], &E[3 + j]);
-      r[0] *= residual_scaling; r[1] *= residual_scaling;
+      for (int j = 0; j < n; ++j) correct(&F[j], dc);
+      for (int j = 0; j < 3; ++j) correct(&E[j], 3);
+      for (int row = 0; row < nr; ++row) r[row] *= residual_scaling;
     }
-    lin->r[2 * k] = r[0]; lin->r[2 * k + 1] = r[1];
+    for (int row = 0; row < nr; ++row) lin->r[(size_t)nr * k + row] = r[row];
   }
   lin->cost = cost; lin->fixed_cost = fixed;
 }
@@ -313,11 +367,11 @@ double CostOnly(const BAProblem& p, int loss_type, double loss_scale, int num_th
   for (int64_t k = 0; k < p.n_obs; ++k) {
     if (!p.obs_active[k]) continue;
     const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
-    double r[2];
+    double r[3] = {0, 0, 0};
     EvalObsValue(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt],
-                 &p.cam[SBA_MAX_CAMERA_PARAMS * c], &p.obs_xy[2 * k], r);
+                 &p.cam[SBA_MAX_CAMERA_PARAMS * c], &p.obs_xy[2 * k], MapOf(p, i), p.sem_h, p.sem_w, p.sem_weight, r);
     double rho[3];
-    LossEval(loss_type, loss_scale, r[0] * r[0] + r[1] * r[1], rho);
+    LossEval(loss_type, loss_scale, r[0] * r[0] + r[1] * r[1] + r[2] * r[2], rho);
     cost += 0.5 * rho[0];
   }
   return cost;
@@ -386,8 +440,24 @@ struct StepContext {
   std::vector<double> g;     // [n_pvar*3]  E^T r
 };
 
+// Row accessors of one observation's blocks (nr rows): F row-major nr x dc, E row-major nr x 3, r[nr].
+#define OBS_F(lin, p, k) (&(lin).F[(size_t)(k) * (p).nr * (p).dc_max])
+#define OBS_E(lin, p, k) (&(lin).E[(size_t)(k) * (p).nr * 3])
+#define OBS_R(lin, p, k) (&(lin).r[(size_t)(k) * (p).nr])
+
+// f = F_k x  over the observation's camera columns
+static inline void RowsTimesX(const BAProblem& p, const double* F, const int* cols, int n, const double* x, double* f) {
+  const int dc = p.dc_max;
+  for (int row = 0; row < p.nr; ++row) {
+    double a = 0.0;
+    for (int j = 0; j < n; ++j) a += F[row * dc + j] * x[cols[j]];
+    f[row] = a;
+  }
+}
+
 static bool ComputePointBlocks(StepContext* c) {
   const BAProblem& p = *c->p;
+  const int nr = p.nr;
   c->Cinv.assign((size_t)p.n_pvar * 9, 0.0);
   c->g.assign((size_t)p.n_pvar * 3, 0.0);
   bool ok = true;
@@ -398,11 +468,12 @@ static bool ComputePointBlocks(StepContext* c) {
     double C[9] = {0}, g[3] = {0};
     for (int64_t idx = p.pt_ptr[pt]; idx < p.pt_ptr[pt + 1]; ++idx) {
       const int64_t k = p.pt_obs[idx];
-      const double* E = &c->lin->E[(size_t)k * 6];
-      const double* r = &c->lin->r[2 * k];
+      const double* E = OBS_E(*c->lin, p, k);
+      const double* r = OBS_R(*c->lin, p, k);
       for (int a = 0; a < 3; ++a) {
-        for (int b = 0; b < 3; ++b) C[a * 3 + b] += E[a] * E[b] + E[3 + a] * E[3 + b];
-        g[a] += E[a] * r[0] + E[3 + a] * r[1];
+        for (int b = 0; b < 3; ++b)
+          for (int row = 0; row < nr; ++row) C[a * 3 + b] += E[3 * row + a] * E[3 * row + b];
+        for (int row = 0; row < nr; ++row) g[a] += E[3 * row + a] * r[row];
       }
     }
     for (int a = 0; a < 3; ++a) C[a * 3 + a] += c->Dp[3 * po + a] * c->Dp[3 * po + a];
@@ -415,38 +486,59 @@ static bool ComputePointBlocks(StepContext* c) {
   return ok;
 }
 
+// per-thread accumulators over the camera columns, summed in thread order
+struct ThreadAcc {
+  std::vector<std::vector<double>> acc;
+  ThreadAcc(int nt, size_t n) : acc(std::max(1, nt), std::vector<double>(n, 0.0)) {}
+  void Sum(double* out, size_t n) const {
+    for (size_t j = 0; j < n; ++j) { double s = 0.0; for (const auto& a : acc) s += a[j]; out[j] += s; }
+  }
+};
+
 // rhs of the reduced system: F^T r - sum_p W_p Cinv_p g_p
 static void ReducedRhs(const StepContext& c, std::vector<double>* rhs) {
   const BAProblem& p = *c.p;
-  const int dc = p.dc_max;
+  const int dc = p.dc_max, nr = p.nr;
   rhs->assign(p.n_cdim, 0.0);
-  for (int64_t k = 0; k < p.n_obs; ++k) {
-    if (!p.obs_active[k]) continue;
-    int cols[24];
-    const int n = p.ObsCols(k, cols);
-    if (n == 0) continue;
-    const double* F = &c.lin->F[(size_t)k * 2 * dc];
-    const double* r = &c.lin->r[2 * k];
-    double e[2] = {r[0], r[1]};
-    const int po = p.p_off[p.obs_pt[k]];
-    if (po >= 0) {
-      const double* E = &c.lin->E[(size_t)k * 6];
-      const double* Ci = &c.Cinv[(size_t)po * 9];
-      const double* g = &c.g[(size_t)po * 3];
-      double w[3];
-      for (int a = 0; a < 3; ++a) w[a] = Ci[a * 3] * g[0] + Ci[a * 3 + 1] * g[1] + Ci[a * 3 + 2] * g[2];
-      e[0] -= E[0] * w[0] + E[1] * w[1] + E[2] * w[2];
-      e[1] -= E[3] * w[0] + E[4] * w[1] + E[5] * w[2];
+  const int nt = std::max(1, c.threads);
+  ThreadAcc ta(nt, p.n_cdim);
+#pragma omp parallel num_threads(nt)
+  {
+    std::vector<double>& acc = ta.acc[omp_get_thread_num()];
+#pragma omp for schedule(static)
+    for (int64_t k = 0; k < p.n_obs; ++k) {
+      if (!p.obs_active[k]) continue;
+      int cols[24];
+      const int n = p.ObsCols(k, cols);
+      if (n == 0) continue;
+      const double* F = OBS_F(*c.lin, p, k);
+      const double* r = OBS_R(*c.lin, p, k);
+      double e[3] = {0, 0, 0};
+      for (int row = 0; row < nr; ++row) e[row] = r[row];
+      const int po = p.p_off[p.obs_pt[k]];
+      if (po >= 0) {
+        const double* E = OBS_E(*c.lin, p, k);
+        const double* Ci = &c.Cinv[(size_t)po * 9];
+        const double* g = &c.g[(size_t)po * 3];
+        double w[3];
+        for (int a = 0; a < 3; ++a) w[a] = Ci[a * 3] * g[0] + Ci[a * 3 + 1] * g[1] + Ci[a * 3 + 2] * g[2];
+        for (int row = 0; row < nr; ++row) e[row] -= E[3 * row] * w[0] + E[3 * row + 1] * w[1] + E[3 * row + 2] * w[2];
+      }
+      for (int j = 0; j < n; ++j) {
+        double a = 0.0;
+        for (int row = 0; row < nr; ++row) a += F[row * dc + j] * e[row];
+        acc[cols[j]] += a;
+      }
     }
-    for (int j = 0; j < n; ++j) (*rhs)[cols[j]] += F[j] * e[0] + F[dc + j] * e[1];
   }
+  ta.Sum(rhs->data(), p.n_cdim);
 }
 
 // y = S x, S = F^T F + Dc^2 - sum_p W_p Cinv_p W_p^T, evaluated implicitly
 // (ImplicitSchurComplement::RightMultiply)
 static void SchurMatVec(const StepContext& c, const double* x, double* y) {
   const BAProblem& p = *c.p;
-  const int dc = p.dc_max;
+  const int dc = p.dc_max, nr = p.nr;
   std::vector<double> v((size_t)p.n_pvar * 3, 0.0);
 #pragma omp parallel for num_threads(c.threads) schedule(static)
   for (int pt = 0; pt < p.n_pt; ++pt) {
@@ -457,88 +549,94 @@ static void SchurMatVec(const StepContext& c, const double* x, double* y) {
       const int64_t k = p.pt_obs[idx];
       int cols[24];
       const int n = p.ObsCols(k, cols);
-      const double* F = &c.lin->F[(size_t)k * 2 * dc];
-      const double* E = &c.lin->E[(size_t)k * 6];
-      double f0 = 0, f1 = 0;
-      for (int j = 0; j < n; ++j) { f0 += F[j] * x[cols[j]]; f1 += F[dc + j] * x[cols[j]]; }
-      for (int a = 0; a < 3; ++a) u[a] += E[a] * f0 + E[3 + a] * f1;
+      const double* E = OBS_E(*c.lin, p, k);
+      double f[3];
+      RowsTimesX(p, OBS_F(*c.lin, p, k), cols, n, x, f);
+      for (int a = 0; a < 3; ++a)
+        for (int row = 0; row < nr; ++row) u[a] += E[3 * row + a] * f[row];
     }
     const double* Ci = &c.Cinv[(size_t)po * 9];
     for (int a = 0; a < 3; ++a) v[(size_t)po * 3 + a] = Ci[a * 3] * u[0] + Ci[a * 3 + 1] * u[1] + Ci[a * 3 + 2] * u[2];
   }
   const int nt = std::max(1, c.threads);
-  std::vector<std::vector<double>> acc(nt, std::vector<double>(p.n_cdim, 0.0));
+  ThreadAcc ta(nt, p.n_cdim);
 #pragma omp parallel num_threads(nt)
   {
-    std::vector<double>& a = acc[omp_get_thread_num()];
+    std::vector<double>& a = ta.acc[omp_get_thread_num()];
 #pragma omp for schedule(static)
     for (int64_t k = 0; k < p.n_obs; ++k) {
       if (!p.obs_active[k]) continue;
       int cols[24];
       const int n = p.ObsCols(k, cols);
       if (n == 0) continue;
-      const double* F = &c.lin->F[(size_t)k * 2 * dc];
-      double f0 = 0, f1 = 0;
-      for (int j = 0; j < n; ++j) { f0 += F[j] * x[cols[j]]; f1 += F[dc + j] * x[cols[j]]; }
+      const double* F = OBS_F(*c.lin, p, k);
+      double f[3];
+      RowsTimesX(p, F, cols, n, x, f);
       const int po = p.p_off[p.obs_pt[k]];
       if (po >= 0) {
-        const double* E = &c.lin->E[(size_t)k * 6];
+        const double* E = OBS_E(*c.lin, p, k);
         const double* w = &v[(size_t)po * 3];
-        f0 -= E[0] * w[0] + E[1] * w[1] + E[2] * w[2];
-        f1 -= E[3] * w[0] + E[4] * w[1] + E[5] * w[2];
+        for (int row = 0; row < nr; ++row) f[row] -= E[3 * row] * w[0] + E[3 * row + 1] * w[1] + E[3 * row + 2] * w[2];
       }
-      for (int j = 0; j < n; ++j) a[cols[j]] += F[j] * f0 + F[dc + j] * f1;
+      for (int j = 0; j < n; ++j) {
+        double s = 0.0;
+        for (int row = 0; row < nr; ++row) s += F[row * dc + j] * f[row];
+        a[cols[j]] += s;
+      }
     }
   }
-  for (int j = 0; j < p.n_cdim; ++j) {
-    double s = c.Dc[j] * c.Dc[j] * x[j];
-    for (int th = 0; th < nt; ++th) s += acc[th][j];
-    y[j] = s;
-  }
+  for (int j = 0; j < p.n_cdim; ++j) y[j] = c.Dc[j] * c.Dc[j] * x[j];
+  ta.Sum(y, p.n_cdim);
+}
+
+// W = F^T E (n x 3) of one observation
+static inline void ObsW(const BAProblem& p, const double* F, const double* E, int n, double* G /* [n*3] */) {
+  const int dc = p.dc_max;
+  for (int j = 0; j < n; ++j)
+    for (int m = 0; m < 3; ++m) {
+      double a = 0.0;
+      for (int row = 0; row < p.nr; ++row) a += F[row * dc + j] * E[3 * row + m];
+      G[j * 3 + m] = a;
+    }
 }
 
 // Explicit reduced camera matrix (SchurEliminator::Eliminate), dense row-major.
 static void BuildDenseSchur(const StepContext& c, std::vector<double>* Sout) {
   const BAProblem& p = *c.p;
-  const int dc = p.dc_max, n = p.n_cdim;
+  const int dc = p.dc_max, n = p.n_cdim, nr = p.nr;
   std::vector<double>& S = *Sout;
   S.assign((size_t)n * n, 0.0);
   for (int j = 0; j < n; ++j) S[(size_t)j * n + j] = c.Dc[j] * c.Dc[j];
-  // F^T F part (all active observations)
-  for (int64_t k = 0; k < p.n_obs; ++k) {
-    if (!p.obs_active[k]) continue;
-    int cols[24];
-    const int nc = p.ObsCols(k, cols);
-    const double* F = &c.lin->F[(size_t)k * 2 * dc];
-    for (int a = 0; a < nc; ++a)
-      for (int b = 0; b < nc; ++b)
-        S[(size_t)cols[a] * n + cols[b]] += F[a] * F[b] + F[dc + a] * F[dc + b];
-  }
-  // - W_p Cinv_p W_p^T
-  const bool priv = false;
-  (void)priv;
+  // per point: + F^T F of its observations, - W_p Cinv_p W_p^T  (constant points: only the first)
 #pragma omp parallel for num_threads(c.threads) schedule(dynamic, 64)
   for (int pt = 0; pt < p.n_pt; ++pt) {
     const int po = p.p_off[pt];
-    if (po < 0) continue;
-    const double* Ci = &c.Cinv[(size_t)po * 9];
     const int64_t b0 = p.pt_ptr[pt], b1 = p.pt_ptr[pt + 1];
     const int len = (int)(b1 - b0);
+    if (len == 0) continue;
     std::vector<double> G((size_t)len * 24 * 3), H((size_t)len * 24 * 3);
     std::vector<int> cols((size_t)len * 24), ncs(len);
     for (int a = 0; a < len; ++a) {
       const int64_t k = p.pt_obs[b0 + a];
-      ncs[a] = p.ObsCols(k, &cols[(size_t)a * 24]);
-      const double* F = &c.lin->F[(size_t)k * 2 * dc];
-      const double* E = &c.lin->E[(size_t)k * 6];
-      for (int j = 0; j < ncs[a]; ++j)
-        for (int m = 0; m < 3; ++m) G[((size_t)a * 24 + j) * 3 + m] = F[j] * E[m] + F[dc + j] * E[3 + m];
+      ncs[a] = p.obs_active[k] ? p.ObsCols(k, &cols[(size_t)a * 24]) : 0;
+      const double* F = OBS_F(*c.lin, p, k);
+      for (int ja = 0; ja < ncs[a]; ++ja)
+        for (int jb = 0; jb < ncs[a]; ++jb) {
+          double v = 0.0;
+          for (int row = 0; row < nr; ++row) v += F[row * dc + ja] * F[row * dc + jb];
+#pragma omp atomic
+          S[(size_t)cols[(size_t)a * 24 + ja] * n + cols[(size_t)a * 24 + jb]] += v;
+        }
+      if (po < 0) continue;
+      const double* Ci = &c.Cinv[(size_t)po * 9];
+      ObsW(p, F, OBS_E(*c.lin, p, k), ncs[a], &G[(size_t)a * 24 * 3]);
       for (int j = 0; j < ncs[a]; ++j)
         for (int m = 0; m < 3; ++m) {
           const double* g = &G[((size_t)a * 24 + j) * 3];
           H[((size_t)a * 24 + j) * 3 + m] = g[0] * Ci[m] + g[1] * Ci[3 + m] + g[2] * Ci[6 + m];
         }
     }
+    if (po < 0) continue;
     for (int a = 0; a < len; ++a)
       for (int b = 0; b < len; ++b)
         for (int ja = 0; ja < ncs[a]; ++ja) {
@@ -556,7 +654,7 @@ static void BuildDenseSchur(const StepContext& c, std::vector<double>* Sout) {
 // SCHUR_JACOBI: block diagonal of S at parameter-block granularity, inverted.
 static bool BuildSchurJacobi(const StepContext& c, std::vector<double>* Minv) {
   const BAProblem& p = *c.p;
-  const int dc = p.dc_max;
+  const int dc = p.dc_max, nr = p.nr;
   const int nb = (int)p.blk_off.size();
   std::vector<int> col2blk(p.n_cdim, -1);
   std::vector<size_t> boff(nb + 1, 0);
@@ -568,52 +666,58 @@ static bool BuildSchurJacobi(const StepContext& c, std::vector<double>* Minv) {
   for (int b = 0; b < nb; ++b)
     for (int j = 0; j < p.blk_dim[b]; ++j)
       M[boff[b] + (size_t)j * p.blk_dim[b] + j] = c.Dc[p.blk_off[b] + j] * c.Dc[p.blk_off[b] + j];
-  for (int64_t k = 0; k < p.n_obs; ++k) {
-    if (!p.obs_active[k]) continue;
-    int cols[24];
-    const int nc = p.ObsCols(k, cols);
-    const double* F = &c.lin->F[(size_t)k * 2 * dc];
-    for (int a = 0; a < nc; ++a)
-      for (int b = 0; b < nc; ++b) {
-        const int ba = col2blk[cols[a]];
-        if (ba != col2blk[cols[b]]) continue;
-        const int d = p.blk_dim[ba];
-        M[boff[ba] + (size_t)(cols[a] - p.blk_off[ba]) * d + (cols[b] - p.blk_off[ba])] +=
-            F[a] * F[b] + F[dc + a] * F[dc + b];
+  const int nt = std::max(1, c.threads);
+  ThreadAcc ta(nt, boff[nb]);
+#pragma omp parallel num_threads(nt)
+  {
+    std::vector<double>& Mt = ta.acc[omp_get_thread_num()];
+#pragma omp for schedule(static)
+    for (int pt = 0; pt < p.n_pt; ++pt) {
+      const int po = p.p_off[pt];
+      // T_{p,B} = sum over this point's observations touching block B of F_B^T E
+      std::vector<int> blks;
+      std::vector<std::vector<double>> Ts;
+      for (int64_t idx = p.pt_ptr[pt]; idx < p.pt_ptr[pt + 1]; ++idx) {
+        const int64_t k = p.pt_obs[idx];
+        if (!p.obs_active[k]) continue;
+        int cols[24];
+        const int nc = p.ObsCols(k, cols);
+        const double* F = OBS_F(*c.lin, p, k);
+        for (int a = 0; a < nc; ++a)
+          for (int b = 0; b < nc; ++b) {
+            const int ba = col2blk[cols[a]];
+            if (ba != col2blk[cols[b]]) continue;
+            const int d = p.blk_dim[ba];
+            double v = 0.0;
+            for (int row = 0; row < nr; ++row) v += F[row * dc + a] * F[row * dc + b];
+            Mt[boff[ba] + (size_t)(cols[a] - p.blk_off[ba]) * d + (cols[b] - p.blk_off[ba])] += v;
+          }
+        if (po < 0) continue;
+        double G[24 * 3];
+        ObsW(p, F, OBS_E(*c.lin, p, k), nc, G);
+        for (int j = 0; j < nc; ++j) {
+          const int b = col2blk[cols[j]];
+          size_t pos = std::find(blks.begin(), blks.end(), b) - blks.begin();
+          if (pos == blks.size()) { blks.push_back(b); Ts.emplace_back((size_t)p.blk_dim[b] * 3, 0.0); }
+          const int lj = cols[j] - p.blk_off[b];
+          for (int m = 0; m < 3; ++m) Ts[pos][(size_t)lj * 3 + m] += G[j * 3 + m];
+        }
       }
-  }
-  for (int pt = 0; pt < p.n_pt; ++pt) {
-    const int po = p.p_off[pt];
-    if (po < 0) continue;
-    const double* Ci = &c.Cinv[(size_t)po * 9];
-    // T_{p,B} = sum over this point's observations touching block B of F_B^T E
-    std::vector<int> blks;
-    std::vector<std::vector<double>> Ts;
-    for (int64_t idx = p.pt_ptr[pt]; idx < p.pt_ptr[pt + 1]; ++idx) {
-      const int64_t k = p.pt_obs[idx];
-      int cols[24];
-      const int nc = p.ObsCols(k, cols);
-      const double* F = &c.lin->F[(size_t)k * 2 * dc];
-      const double* E = &c.lin->E[(size_t)k * 6];
-      for (int j = 0; j < nc; ++j) {
-        const int b = col2blk[cols[j]];
-        size_t pos = std::find(blks.begin(), blks.end(), b) - blks.begin();
-        if (pos == blks.size()) { blks.push_back(b); Ts.emplace_back((size_t)p.blk_dim[b] * 3, 0.0); }
-        const int lj = cols[j] - p.blk_off[b];
-        for (int m = 0; m < 3; ++m) Ts[pos][(size_t)lj * 3 + m] += F[j] * E[m] + F[dc + j] * E[3 + m];
+      if (po < 0) continue;
+      const double* Ci = &c.Cinv[(size_t)po * 9];
+      for (size_t bi = 0; bi < blks.size(); ++bi) {
+        const int b = blks[bi], d = p.blk_dim[b];
+        const std::vector<double>& T = Ts[bi];
+        for (int a = 0; a < d; ++a) {
+          double h[3];
+          for (int m = 0; m < 3; ++m) h[m] = T[a * 3] * Ci[m] + T[a * 3 + 1] * Ci[3 + m] + T[a * 3 + 2] * Ci[6 + m];
+          for (int e = 0; e < d; ++e)
+            Mt[boff[b] + (size_t)a * d + e] -= h[0] * T[e * 3] + h[1] * T[e * 3 + 1] + h[2] * T[e * 3 + 2];
+        }
       }
     }
-    for (size_t bi = 0; bi < blks.size(); ++bi) {
-      const int b = blks[bi], d = p.blk_dim[b];
-      const std::vector<double>& T = Ts[bi];
-      for (int a = 0; a < d; ++a) {
-        double h[3];
-        for (int m = 0; m < 3; ++m) h[m] = T[a * 3] * Ci[m] + T[a * 3 + 1] * Ci[3 + m] + T[a * 3 + 2] * Ci[6 + m];
-        for (int e = 0; e < d; ++e)
-          M[boff[b] + (size_t)a * d + e] -= h[0] * T[e * 3] + h[1] * T[e * 3 + 1] + h[2] * T[e * 3 + 2];
-      }
-    }
   }
+  ta.Sum(M.data(), boff[nb]);
   Minv->assign(boff[nb], 0.0);
   for (int b = 0; b < nb; ++b)
     if (!InvertSPD(&M[boff[b]], p.blk_dim[b], &(*Minv)[boff[b]])) return false;
@@ -694,46 +798,78 @@ static int SolveCG(const StepContext& c, const std::vector<double>& Minv, const 
 // ---------------------------------------------------------------------------
 // TrustRegionMinimizer + LevenbergMarquardtStrategy (Ceres 2.1.0), App. B.3-B.4
 // ---------------------------------------------------------------------------
-static void ColumnSquaredNorms(const BAProblem& p, const Linearization& lin, std::vector<double>* nc,
-                               std::vector<double>* np) {
-  const int dc = p.dc_max;
+// mode 0: column square norms; mode 1: gradient J^T r.  Camera part through per-thread accumulators, point part
+// per point (CSR), so both are parallel and the result does not depend on the schedule.
+static void ColumnPass(const BAProblem& p, const Linearization& lin, int mode, std::vector<double>* nc,
+                       std::vector<double>* np, int threads) {
+  const int dc = p.dc_max, nr = p.nr;
   nc->assign(p.n_cdim, 0.0);
   np->assign((size_t)3 * p.n_pvar, 0.0);
-  for (int64_t k = 0; k < p.n_obs; ++k) {
-    if (!p.obs_active[k]) continue;
-    int cols[24];
-    const int n = p.ObsCols(k, cols);
-    const double* F = &lin.F[(size_t)k * 2 * dc];
-    for (int j = 0; j < n; ++j) (*nc)[cols[j]] += F[j] * F[j] + F[dc + j] * F[dc + j];
-    const int po = p.p_off[p.obs_pt[k]];
-    if (po >= 0) {
-      const double* E = &lin.E[(size_t)k * 6];
-      for (int a = 0; a < 3; ++a) (*np)[3 * (size_t)po + a] += E[a] * E[a] + E[3 + a] * E[3 + a];
+  const int nt = std::max(1, threads);
+  ThreadAcc ta(nt, p.n_cdim);
+#pragma omp parallel num_threads(nt)
+  {
+    std::vector<double>& acc = ta.acc[omp_get_thread_num()];
+#pragma omp for schedule(static)
+    for (int64_t k = 0; k < p.n_obs; ++k) {
+      if (!p.obs_active[k]) continue;
+      int cols[24];
+      const int n = p.ObsCols(k, cols);
+      const double* F = OBS_F(lin, p, k);
+      const double* r = OBS_R(lin, p, k);
+      for (int j = 0; j < n; ++j) {
+        double a = 0.0;
+        for (int row = 0; row < nr; ++row) a += F[row * dc + j] * (mode ? r[row] : F[row * dc + j]);
+        acc[cols[j]] += a;
+      }
+    }
+#pragma omp for schedule(static)
+    for (int pt = 0; pt < p.n_pt; ++pt) {
+      const int po = p.p_off[pt];
+      if (po < 0) continue;
+      double v[3] = {0, 0, 0};
+      for (int64_t idx = p.pt_ptr[pt]; idx < p.pt_ptr[pt + 1]; ++idx) {
+        const int64_t k = p.pt_obs[idx];
+        if (!p.obs_active[k]) continue;
+        const double* E = OBS_E(lin, p, k);
+        const double* r = OBS_R(lin, p, k);
+        for (int a = 0; a < 3; ++a)
+          for (int row = 0; row < nr; ++row) v[a] += E[3 * row + a] * (mode ? r[row] : E[3 * row + a]);
+      }
+      for (int a = 0; a < 3; ++a) (*np)[3 * (size_t)po + a] = v[a];
     }
   }
+  ta.Sum(nc->data(), p.n_cdim);
+}
+static void ColumnSquaredNorms(const BAProblem& p, const Linearization& lin, std::vector<double>* nc,
+                               std::vector<double>* np, int threads) {
+  ColumnPass(p, lin, 0, nc, np, threads);
 }
 
 static void ScaleColumns(const BAProblem& p, const std::vector<double>& sc, const std::vector<double>& sp,
                          Linearization* lin, int threads) {
-  const int dc = p.dc_max;
+  const int dc = p.dc_max, nr = p.nr;
 #pragma omp parallel for num_threads(threads) schedule(static)
   for (int64_t k = 0; k < p.n_obs; ++k) {
     if (!p.obs_active[k]) continue;
     int cols[24];
     const int n = p.ObsCols(k, cols);
-    double* F = &lin->F[(size_t)k * 2 * dc];
-    for (int j = 0; j < n; ++j) { F[j] *= sc[cols[j]]; F[dc + j] *= sc[cols[j]]; }
+    double* F = OBS_F(*lin, p, k);
+    for (int j = 0; j < n; ++j)
+      for (int row = 0; row < nr; ++row) F[row * dc + j] *= sc[cols[j]];
     const int po = p.p_off[p.obs_pt[k]];
     if (po >= 0) {
-      double* E = &lin->E[(size_t)k * 6];
-      for (int a = 0; a < 3; ++a) { E[a] *= sp[3 * (size_t)po + a]; E[3 + a] *= sp[3 * (size_t)po + a]; }
+      double* E = OBS_E(*lin, p, k);
+      for (int a = 0; a < 3; ++a)
+        for (int row = 0; row < nr; ++row) E[3 * row + a] *= sp[3 * (size_t)po + a];
     }
   }
 }
 
 // x_plus = Plus(x, delta) on every variable block (manifolds, App. A.1)
+struct State { std::vector<double> q, t, cam, X; };
 static void ApplyPlus(const BAProblem& src, const std::vector<double>& dc, const std::vector<double>& dp,
-                      BAProblem* dst) {
+                      State* dst) {
   dst->q = src.q; dst->t = src.t; dst->cam = src.cam; dst->X = src.X;
   for (int i = 0; i < src.n_img; ++i) {
     if (src.q_off[i] >= 0) QuaternionPlus(&src.q[4 * i], &dc[src.q_off[i]], &dst->q[4 * i]);
@@ -748,8 +884,10 @@ static void ApplyPlus(const BAProblem& src, const std::vector<double>& dc, const
     if (src.p_off[p] >= 0)
       for (int a = 0; a < 3; ++a) dst->X[3 * p + a] += dp[3 * (size_t)src.p_off[p] + a];
 }
+static void SwapState(BAProblem* p, State* s) { p->q.swap(s->q); p->t.swap(s->t); p->cam.swap(s->cam); p->X.swap(s->X); }
 
-static double AmbientNorm(const BAProblem& p, const BAProblem* other) {
+// norm over the variable blocks (ambient coordinates) of the state, or of its difference to `other`
+static double AmbientNorm(const BAProblem& p, const State* other) {
   double s = 0;
   auto acc = [&](const std::vector<double>& a, const std::vector<double>* b, size_t i) {
     const double d = b ? a[i] - (*b)[i] : a[i];
@@ -796,21 +934,8 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
 
   // gradient (unscaled J) for the max-norm column of the table
   auto gradient_max_norm = [&](const Linearization& l, const std::vector<double>* sc, const std::vector<double>* sp) {
-    std::vector<double> gc(p.n_cdim, 0.0), gp((size_t)3 * p.n_pvar, 0.0);
-    const int dc = p.dc_max;
-    for (int64_t k = 0; k < p.n_obs; ++k) {
-      if (!p.obs_active[k]) continue;
-      int cols[24];
-      const int n = p.ObsCols(k, cols);
-      const double* F = &l.F[(size_t)k * 2 * dc];
-      const double* r = &l.r[2 * k];
-      for (int j = 0; j < n; ++j) gc[cols[j]] += F[j] * r[0] + F[dc + j] * r[1];
-      const int po = p.p_off[p.obs_pt[k]];
-      if (po >= 0) {
-        const double* E = &l.E[(size_t)k * 6];
-        for (int a = 0; a < 3; ++a) gp[3 * (size_t)po + a] += E[a] * r[0] + E[3 + a] * r[1];
-      }
-    }
+    std::vector<double> gc, gp;
+    ColumnPass(p, l, 1, &gc, &gp, threads);
     double m = 0;
     for (int j = 0; j < p.n_cdim; ++j) m = std::max(m, std::fabs(sc ? gc[j] / (*sc)[j] : gc[j]));
     for (size_t j = 0; j < gp.size(); ++j) m = std::max(m, std::fabs(sp ? gp[j] / (*sp)[j] : gp[j]));
@@ -821,7 +946,7 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
   double gmax = gradient_max_norm(lin, nullptr, nullptr);
   if (o.jacobi_scaling) {
     std::vector<double> nc, np;
-    ColumnSquaredNorms(p, lin, &nc, &np);
+    ColumnSquaredNorms(p, lin, &nc, &np, threads);
     for (int j = 0; j < p.n_cdim; ++j) scale_c[j] = 1.0 / (1.0 + std::sqrt(nc[j]));
     for (size_t j = 0; j < np.size(); ++j) scale_p[j] = 1.0 / (1.0 + std::sqrt(np[j]));
     ScaleColumns(p, scale_c, scale_p, &lin, threads);
@@ -854,7 +979,7 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
 
     // ---- LevenbergMarquardtStrategy::ComputeStep
     if (!reuse_diagonal) {
-      ColumnSquaredNorms(p, lin, &diag_c, &diag_p);
+      ColumnSquaredNorms(p, lin, &diag_c, &diag_p, threads);
       for (auto& d : diag_c) d = std::min(std::max(d, o.min_lm_diagonal), o.max_lm_diagonal);
       for (auto& d : diag_p) d = std::min(std::max(d, o.min_lm_diagonal), o.max_lm_diagonal);
     }
@@ -888,7 +1013,6 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
     }
     if (solver_ok) {
       // back substitution: y_p = Cinv (g_p - sum_o E^T F y_c)
-      const int dc = p.dc_max;
 #pragma omp parallel for num_threads(threads) schedule(static)
       for (int pt = 0; pt < p.n_pt; ++pt) {
         const int po = p.p_off[pt];
@@ -898,11 +1022,11 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
           const int64_t k = p.pt_obs[idx];
           int cols[24];
           const int n = p.ObsCols(k, cols);
-          const double* F = &lin.F[(size_t)k * 2 * dc];
-          const double* E = &lin.E[(size_t)k * 6];
-          double f0 = 0, f1 = 0;
-          for (int j = 0; j < n; ++j) { f0 += F[j] * yc[cols[j]]; f1 += F[dc + j] * yc[cols[j]]; }
-          for (int a = 0; a < 3; ++a) u[a] -= E[a] * f0 + E[3 + a] * f1;
+          const double* E = OBS_E(lin, p, k);
+          double f[3];
+          RowsTimesX(p, OBS_F(lin, p, k), cols, n, yc.data(), f);
+          for (int a = 0; a < 3; ++a)
+            for (int row = 0; row < p.nr; ++row) u[a] -= E[3 * row + a] * f[row];
         }
         const double* Ci = &ctx.Cinv[(size_t)po * 9];
         for (int a = 0; a < 3; ++a) yp[3 * (size_t)po + a] = Ci[a * 3] * u[0] + Ci[a * 3 + 1] * u[1] + Ci[a * 3 + 2] * u[2];
@@ -921,22 +1045,22 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
       for (int j = 0; j < p.n_cdim; ++j) step_c[j] = -yc[j];
       for (size_t j = 0; j < yp.size(); ++j) step_p[j] = -yp[j];
       // model_cost_change = -(J step)'(r + J step / 2)
-      const int dc = p.dc_max;
       double acc = 0.0;
 #pragma omp parallel for num_threads(threads) reduction(+ : acc) schedule(static)
       for (int64_t k = 0; k < p.n_obs; ++k) {
         if (!p.obs_active[k]) continue;
         int cols[24];
         const int n = p.ObsCols(k, cols);
-        const double* F = &lin.F[(size_t)k * 2 * dc];
-        double m0 = 0, m1 = 0;
-        for (int j = 0; j < n; ++j) { m0 += F[j] * step_c[cols[j]]; m1 += F[dc + j] * step_c[cols[j]]; }
+        double m[3];
+        RowsTimesX(p, OBS_F(lin, p, k), cols, n, step_c.data(), m);
         const int po = p.p_off[p.obs_pt[k]];
         if (po >= 0) {
-          const double* E = &lin.E[(size_t)k * 6];
-          for (int a = 0; a < 3; ++a) { m0 += E[a] * step_p[3 * (size_t)po + a]; m1 += E[3 + a] * step_p[3 * (size_t)po + a]; }
+          const double* E = OBS_E(lin, p, k);
+          for (int row = 0; row < p.nr; ++row)
+            for (int a = 0; a < 3; ++a) m[row] += E[3 * row + a] * step_p[3 * (size_t)po + a];
         }
-        acc += m0 * (lin.r[2 * k] + m0 / 2.0) + m1 * (lin.r[2 * k + 1] + m1 / 2.0);
+        const double* r = OBS_R(lin, p, k);
+        for (int row = 0; row < p.nr; ++row) acc += m[row] * (r[row] + m[row] / 2.0);
       }
       model_cost_change = -acc;
       step_valid = model_cost_change > 0.0;
@@ -958,9 +1082,11 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
     for (int j = 0; j < p.n_cdim; ++j) delta_c[j] = step_c[j] * scale_c[j];
     for (size_t j = 0; j < step_p.size(); ++j) delta_p[j] = step_p[j] * scale_p[j];
 
-    BAProblem cand = p;  // structure + state copy (oracle: clarity over speed)
+    State cand;  // candidate state; the problem evaluates it in place (swapped in and out)
     ApplyPlus(p, delta_c, delta_p, &cand);
-    double cand_cost = CostOnly(cand, o.loss_function_type, o.loss_function_scale, threads);
+    SwapState(&p, &cand);
+    double cand_cost = CostOnly(p, o.loss_function_type, o.loss_function_scale, threads);
+    SwapState(&p, &cand);
     if (!std::isfinite(cand_cost)) cand_cost = std::numeric_limits<double>::max();
     const double step_norm = AmbientNorm(p, &cand);
     it.step_norm = step_norm;
@@ -981,7 +1107,7 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
     it.relative_decrease = relative_decrease;
     if (relative_decrease > o.min_relative_decrease) {
       // HandleSuccessfulStep
-      p.q = cand.q; p.t = cand.t; p.cam = cand.cam; p.X = cand.X;
+      SwapState(&p, &cand);
       x_norm = AmbientNorm(p, nullptr);
       Linearize(p, o.loss_function_type, o.loss_function_scale, true, &lin, threads);
       x_cost = lin.cost;

@@ -52,6 +52,14 @@ struct BAProblem {
   // CSR observation lists
   std::vector<int64_t> pt_ptr; std::vector<int64_t> pt_obs;
 
+  // extension X1 (no reference implementation): with per-image maps every residual
+  // block has a third row  r_s = sem_weight * bilinear(map_img, x, y)  at the projection (x, y), bilinear as
+  // Bitmap::InterpolateBilinear (src/util/bitmap.cc:238-269); the Jet of the interpolant is its Jacobian oracle.
+  int nr = 2;                       // residual rows per block
+  const float* sem_maps = nullptr;  // caller-owned, [n_img * sem_h * sem_w]
+  int sem_h = 0, sem_w = 0;
+  double sem_weight = 0.0;
+
   // counts (ceres::Solver::Summary)
   int num_residual_blocks = 0, num_residuals = 0, num_residuals_reduced = 0;
   int num_parameter_blocks_reduced = 0, num_parameters_reduced = 0, num_effective_parameters_reduced = 0;
@@ -60,10 +68,10 @@ struct BAProblem {
   int ObsCols(int64_t k, int* cols) const;  // camera-side global columns of obs k
 };
 
-struct Linearization {
-  std::vector<double> r;  // [2*n_obs]   (loss-corrected, NOT scaled)
-  std::vector<double> F;  // [n_obs*2*dc_max] camera-side local Jacobian, row-major 2 x dc_max
-  std::vector<double> E;  // [n_obs*6]
+struct Linearization {  // nr = BAProblem::nr rows per block
+  std::vector<double> r;  // [nr*n_obs]   (loss-corrected, NOT scaled)
+  std::vector<double> F;  // [n_obs*nr*dc_max] camera-side local Jacobian, row-major nr x dc_max
+  std::vector<double> E;  // [n_obs*nr*3]
   double cost = 0.0, fixed_cost = 0.0;
 };
 
@@ -74,6 +82,10 @@ void EvalRigObservation(int model, const double* rig_q, const double* rig_t, con
 void EvalObservation(int model, const double* q, const double* t, const double* X,
                      const double* params, const double* xy, double* r, double* Jq, double* Jt,
                      double* JX, double* Jk);
+// the same with the semantic row: r[3], every J block gets a third row (row-major 3 x cols); map == nullptr: 2 rows
+void EvalObservationSem(int model, const double* q, const double* t, const double* X, const double* params,
+                        const double* xy, const float* map, int H, int W, double weight, double* r, double* Jq,
+                        double* Jt, double* JX, double* Jk);
 
 void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_loss,
                Linearization* lin, int num_threads);

@@ -73,63 +73,78 @@ void oracle_eval_rig_observation_jac(int model, const double* rig_q, const doubl
   EvalRigObservation(model, rig_q, rig_t, rel_q, rel_t, X, params, xy, r, J);
 }
 
-// Problem::Evaluate equivalent in the sba_evaluate() output format (include/sba_b200.h).
-int oracle_ba_evaluate(const sba_problem_desc* d, int loss_type, double loss_scale, int apply_loss,
-                       int threads, double* cost, double* residuals, double* jac_pose,
-                       double* jac_intr, double* jac_point, double* jac_qvec_ambient) {
+// Problem::Evaluate equivalent in the sba_evaluate() / sba_get_semantic_jacobian() output format (include/sba_b200.h).
+// The first two rows of every block go to residuals / jac_*; the third (semantic, extension X1) row -- present when the
+// description carries maps -- to sem_residuals [n], sem_pose [n*6], sem_intr [n*12], sem_point [n*3].
+int oracle_ba_evaluate_rows(const sba_problem_desc* d, int loss_type, double loss_scale, int apply_loss,
+                            int threads, double* cost, double* residuals, double* jac_pose,
+                            double* jac_intr, double* jac_point, double* jac_qvec_ambient,
+                            double* sem_residuals, double* sem_pose, double* sem_intr, double* sem_point) {
   BAProblem p;
   p.Build(*d);
   if (threads <= 0) threads = omp_get_max_threads();
   Linearization lin;
   Linearize(p, loss_type, loss_scale, apply_loss != 0, &lin, threads);
   if (cost) *cost = lin.cost + lin.fixed_cost;
-  const int dc = p.dc_max;
+  const int dc = p.dc_max, nr = p.nr, KP = SBA_MAX_CAMERA_PARAMS;
+  if ((sem_residuals || sem_pose || sem_intr || sem_point) && nr != 3) return 1;
   for (int64_t k = 0; k < p.n_obs; ++k) {
     const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
-    const double* F = &lin.F[(size_t)k * 2 * dc];
-    if (residuals) {
-      if (p.obs_active[k]) { residuals[2 * k] = lin.r[2 * k]; residuals[2 * k + 1] = lin.r[2 * k + 1]; }
-      else {
-        double r[2];
-        EvalObservation(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
-                        &p.obs_xy[2 * k], r, nullptr, nullptr, nullptr, nullptr);
-        residuals[2 * k] = r[0]; residuals[2 * k + 1] = r[1];
-      }
-    }
+    const double* F = &lin.F[(size_t)k * nr * dc];
+    const double* E = &lin.E[(size_t)k * nr * 3];
+    const double* r = &lin.r[(size_t)k * nr];  // inactive blocks: the raw functor output
+    if (residuals) { residuals[2 * k] = r[0]; residuals[2 * k + 1] = r[1]; }
+    if (sem_residuals) sem_residuals[k] = r[2];
     int n = 0;
     if (jac_pose) std::memset(&jac_pose[k * 12], 0, 12 * sizeof(double));
-    if (jac_intr) std::memset(&jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS], 0, 2 * SBA_MAX_CAMERA_PARAMS * sizeof(double));
+    if (jac_intr) std::memset(&jac_intr[k * 2 * KP], 0, 2 * KP * sizeof(double));
     if (jac_point) std::memset(&jac_point[k * 6], 0, 6 * sizeof(double));
+    if (sem_pose) std::memset(&sem_pose[k * 6], 0, 6 * sizeof(double));
+    if (sem_intr) std::memset(&sem_intr[k * KP], 0, KP * sizeof(double));
+    if (sem_point) std::memset(&sem_point[k * 3], 0, 3 * sizeof(double));
     if (p.obs_active[k]) {
       if (p.q_off[i] >= 0) {
-        if (jac_pose) for (int j = 0; j < 3; ++j) { jac_pose[k * 12 + j] = F[n + j]; jac_pose[k * 12 + 6 + j] = F[dc + n + j]; }
+        for (int j = 0; j < 3; ++j) {
+          if (jac_pose) { jac_pose[k * 12 + j] = F[n + j]; jac_pose[k * 12 + 6 + j] = F[dc + n + j]; }
+          if (sem_pose) sem_pose[k * 6 + j] = F[2 * dc + n + j];
+        }
         n += 3;
       }
       if (p.t_off[i] >= 0) {
-        if (jac_pose) for (int j = 0; j < p.t_dim[i]; ++j) {
+        for (int j = 0; j < p.t_dim[i]; ++j) {
           const int a = p.t_cols[3 * i + j];
-          jac_pose[k * 12 + 3 + a] = F[n + j]; jac_pose[k * 12 + 9 + a] = F[dc + n + j];
+          if (jac_pose) { jac_pose[k * 12 + 3 + a] = F[n + j]; jac_pose[k * 12 + 9 + a] = F[dc + n + j]; }
+          if (sem_pose) sem_pose[k * 6 + 3 + a] = F[2 * dc + n + j];
         }
         n += p.t_dim[i];
       }
       if (p.k_off[c] >= 0) {
-        if (jac_intr) for (int j = 0; j < p.k_dim[c]; ++j) {
-          const int a = p.k_cols[SBA_MAX_CAMERA_PARAMS * c + j];
-          jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS + a] = F[n + j];
-          jac_intr[k * 2 * SBA_MAX_CAMERA_PARAMS + SBA_MAX_CAMERA_PARAMS + a] = F[dc + n + j];
+        for (int j = 0; j < p.k_dim[c]; ++j) {
+          const int a = p.k_cols[KP * c + j];
+          if (jac_intr) { jac_intr[k * 2 * KP + a] = F[n + j]; jac_intr[k * 2 * KP + KP + a] = F[dc + n + j]; }
+          if (sem_intr) sem_intr[k * KP + a] = F[2 * dc + n + j];
         }
         n += p.k_dim[c];
       }
-      if (jac_point && p.p_off[pt] >= 0) for (int j = 0; j < 6; ++j) jac_point[k * 6 + j] = lin.E[(size_t)k * 6 + j];
+      if (p.p_off[pt] >= 0) {
+        if (jac_point) for (int j = 0; j < 6; ++j) jac_point[k * 6 + j] = E[j];
+        if (sem_point) for (int j = 0; j < 3; ++j) sem_point[k * 3 + j] = E[6 + j];
+      }
     }
     if (jac_qvec_ambient) {
-      double r[2], Jq[8];
-      EvalObservation(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[SBA_MAX_CAMERA_PARAMS * c],
-                      &p.obs_xy[2 * k], r, Jq, nullptr, nullptr, nullptr);
+      double rr[3], Jq[12];
+      EvalObservation(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt], &p.cam[KP * c],
+                      &p.obs_xy[2 * k], rr, Jq, nullptr, nullptr, nullptr);
       for (int j = 0; j < 8; ++j) jac_qvec_ambient[k * 8 + j] = Jq[j];
     }
   }
   return 0;
+}
+int oracle_ba_evaluate(const sba_problem_desc* d, int loss_type, double loss_scale, int apply_loss,
+                       int threads, double* cost, double* residuals, double* jac_pose,
+                       double* jac_intr, double* jac_point, double* jac_qvec_ambient) {
+  return oracle_ba_evaluate_rows(d, loss_type, loss_scale, apply_loss, threads, cost, residuals, jac_pose, jac_intr,
+                                 jac_point, jac_qvec_ambient, nullptr, nullptr, nullptr, nullptr);
 }
 
 int oracle_ba_counts(const sba_problem_desc* d, sba_summary* s) {

@@ -112,9 +112,15 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
   rc = LaunchEvaluate(p, loss, false, false);
   p->jq_out = nullptr;
   if (rc) return rc;
+  if (sem_residuals && p->nr != 3) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sem_residuals requested but the problem has no semantic maps");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
   std::vector<D4> ER(TilePad(n) * 2), F(TilePad(n) * (dc / 2));  // tile-blocked, common.cuh
+  std::vector<D4> ES(sem_residuals ? (size_t)n : 0);
   std::vector<double> JQ;
   if (n > 0) {
+    if (sem_residuals) SBA_CUDA(cudaMemcpyAsync(ES.data(), p->d_ES.p, ES.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
     SBA_CUDA(cudaMemcpyAsync(ER.data(), p->d_ER.p, ER.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
     SBA_CUDA(cudaMemcpyAsync(F.data(), p->d_F.p, F.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
     if (jac_qvec_ambient) {
@@ -152,10 +158,39 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
       }
     }
     if (jac_qvec_ambient) for (int j = 0; j < 8; ++j) jac_qvec_ambient[8 * r + j] = JQ[(size_t)k * 8 + j];
+    if (sem_residuals) sem_residuals[r] = ES[k].w;
   }
-  if (sem_residuals) {
-    rc = EvaluateSemanticRows(p, sem_residuals);
-    if (rc) return rc;
+  return SBA_OK;
+}
+
+int sba_get_semantic_jacobian(sba_handle* h, double* jac_pose, double* jac_intr, double* jac_point) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  Problem* p = h->p;
+  if (p->nr != 3 || !p->linearized) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "no semantic row: the problem has no semantic maps, or sba_evaluate has not run");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  cudaStream_t st = p->stream;
+  const int n = p->n_obs, dc = p->dc, nq = FSUnits(dc);
+  std::vector<D4> ES((size_t)n), FS(TilePad(n) * nq);
+  if (n > 0) {
+    SBA_CUDA(cudaMemcpyAsync(ES.data(), p->d_ES.p, ES.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaMemcpyAsync(FS.data(), p->d_FS.p, FS.size() * sizeof(D4), cudaMemcpyDeviceToHost, st));
+  }
+  SBA_CUDA(cudaStreamSynchronize(st));
+  if ((rc = FetchHostOrder(p))) return rc;
+  auto slot = [&](int k, int j) { return reinterpret_cast<const double*>(&FS[FSUnit(k, j >> 2, nq)])[j & 3]; };
+  for (int k = 0; k < n; ++k) {
+    const int64_t r = p->h_local2ref[k];
+    const int c = p->h_img_cam[p->h_obs_img[k]];
+    if (jac_point) { jac_point[3 * r] = ES[k].x; jac_point[3 * r + 1] = ES[k].y; jac_point[3 * r + 2] = ES[k].z; }
+    if (jac_pose) for (int j = 0; j < 6; ++j) jac_pose[6 * r + j] = slot(k, j);
+    if (jac_intr) {
+      double* out = &jac_intr[(size_t)r * SBA_MAX_CAMERA_PARAMS];
+      for (int j = 0; j < SBA_MAX_CAMERA_PARAMS; ++j) out[j] = 0.0;
+      for (int s2 = 0; s2 < p->h_k_dim[c] && 6 + s2 < dc; ++s2) out[p->h_k_cols[12 * (size_t)c + s2]] = slot(k, 6 + s2);
+    }
   }
   return SBA_OK;
 }
@@ -267,6 +302,7 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
     run = [&]() { return LaunchEvaluate(p, loss, true, false); };
     // idx 8 + xy 16 in; r 16 + J 16*(dc+3) out; + parameter gathers once
     bytes = n_obs * (8 + 16 + 16 + 16 * (dc + 3)) + gathers;
+    if (p->nr == 3) bytes += n_obs * (32 + 32 * FSUnits((int)dc) + 4 * 4);  // third row out (ES + FS units) + four texels in
   } else if (s == "cost") {
     run = [&]() { return LaunchCostOnly(p, loss, false, &p->d_scalars.p->cand_cost); };
     bytes = n_obs * 24 + gathers;

@@ -53,10 +53,22 @@ __device__ __forceinline__ void St256(D4* p, const D4& v) {
 __host__ __device__ inline size_t FUnit(int k, int jj, int dch) { return ((size_t)(k >> 5) * dch + jj) * 32 + (k & 31); }
 __host__ __device__ inline size_t EUnit(int k, int u) { return ((size_t)(k >> 5) * 2 + u) * 32 + (k & 31); }
 inline size_t TilePad(size_t n_obs) { return (n_obs + 31) / 32 * 32; }
+// ---- third residual row (extension X1: the bilinear semantic row) ----
+// A problem created with semantic maps carries THREE residual rows per observation (nr = 3).  The two reprojection
+// rows keep the layout above; the third row lives in two streams of its own, so that a problem without maps
+// (nr = 2) moves not one byte more than before:
+//   ES[k]           = {d r_s/d X (3), r_s}                       one 32 B unit per observation, linear
+//   FS unit q of k  = d r_s / d s_j for slots j = 4q .. 4q+3     tile-blocked like F, FSUnits(DC) units per observation
+__host__ __device__ constexpr int FSUnits(int dc) { return (dc + 3) / 4; }
+__host__ __device__ inline size_t FSUnit(int k, int q, int nq) { return ((size_t)(k >> 5) * nq + q) * 32 + (k & 31); }
 #ifdef __CUDACC__
 // (d r0 / d s, d r1 / d s) of one slot of one observation: half a unit
 __device__ __forceinline__ double2 LoadSlot(const D4* __restrict__ F, int k, int slot, int dch) {
   return reinterpret_cast<const double2*>(F + FUnit(k, slot >> 1, dch))[slot & 1];
+}
+// d r_s / d s of one slot of one observation (third-row stream)
+__device__ __forceinline__ double LoadSlotS(const D4* __restrict__ FS, int k, int slot, int nq) {
+  return reinterpret_cast<const double*>(FS + FSUnit(k, slot >> 2, nq))[slot & 3];
 }
 #endif
 
@@ -87,6 +99,7 @@ struct StructView {
   int kmax;                   // max free intrinsics per camera
   int n_cdim;                 // compact camera-side dimension
   int n_pvar;                 // variable points
+  int nr;                     // residual rows per observation: 2, or 3 with the semantic row
   const int* img_cam;         // [n_img]
   const int* model;           // [n_cam]
   const int* col_img;         // [n_img*6]  compact column of pose slot or -1
@@ -100,6 +113,15 @@ struct StructView {
   const double* obs_xy;       // [n_obs*2]
   const uint8_t* obs_active;  // [n_obs] residual block kept in the reduced program
   const uint8_t* pose_const;  // [n_img]
+};
+
+// the third-row streams (null when the problem has two rows), the per-image maps they are sampled from
+struct Row3View {
+  D4* ES;             // [n_obs]
+  D4* FS;             // [TilePad(n_obs) * FSUnits(dc)]
+  const float* maps;  // [n_img * H * W] row-major, top-down
+  int H, W;
+  double weight;      // r_s = weight * bilinear(map_img, x, y)   (Bitmap::InterpolateBilinear convention, bitmap.cc:238-269)
 };
 
 struct LossView {

@@ -22,6 +22,32 @@ namespace sba {
 
 constexpr int kEvalThreads = 128;
 
+// Extension X1 (no reference implementation): the third residual row
+//   r_s = weight * bilinear(map_of_image, x, y)
+// sampled at the projection (x, y) with the convention of Bitmap::InterpolateBilinear
+// (/root/reference/src/util/bitmap.cc:238-269: FreeImage scanlines are bottom-up, x0 = floor(x), the sample is
+// rejected when a neighbour falls outside the image).  Its derivative w.r.t. (x, y) is that of the bilinear
+// interpolant inside the cell -- differences of the four texels -- and the row then shares the chain rule of the
+// reprojection rows: d r_s / d s = (g_x, g_y) . d (x, y) / d s.  A rejected sample contributes r_s = 0, J = 0.
+__device__ __forceinline__ bool BilinearWithGrad(const float* __restrict__ map, int H, int W, double x, double y,
+                                                 double* val, double* gx, double* gy) {
+  const double inv_y = H - 1 - y;
+  const double fx = floor(x), fy = floor(inv_y);
+  // (NaN fails every comparison: rejected)
+  if (!(fx >= 0.0 && fx + 1.0 < (double)W && fy >= 0.0 && fy + 1.0 < (double)H)) return false;
+  const int x0 = (int)fx, y0 = (int)fy;
+  const double dx = x - x0, dy = inv_y - y0, dx_1 = 1 - dx, dy_1 = 1 - dy;
+  const float* line0 = map + (size_t)(H - 1 - y0) * W + x0;
+  const float* line1 = line0 - W;  // scanline y0 + 1 is one row UP in the top-down map
+  const double a0 = __ldg(line0), a1 = __ldg(line0 + 1), b0 = __ldg(line1), b1 = __ldg(line1 + 1);
+  const double v0 = dx_1 * a0 + dx * a1;
+  const double v1 = dx_1 * b0 + dx * b1;
+  *val = dy_1 * v0 + dy * v1;
+  *gx = dy_1 * (a1 - a0) + dy * (b1 - b0);
+  *gy = -(v1 - v0);  // d / d y = - d / d inv_y
+  return true;
+}
+
 struct ObsGeom {
   double p[3];      // R(q) X + t
   double R[9];      // d p / d X  (the un-normalised rotation polynomial)
@@ -77,14 +103,15 @@ __device__ __forceinline__ void PickParam(const double (&Jk)[24], int amb, doubl
 #ifndef SBA_EVAL_MINB
 #define SBA_EVAL_MINB 4
 #endif
-template <int MODEL>
-__global__ void __launch_bounds__(kEvalThreads, SBA_EVAL_MINB)
+template <int MODEL, int NR>
+__global__ void __launch_bounds__(kEvalThreads, NR == 3 ? 3 : SBA_EVAL_MINB)
 eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_i,
             const double* __restrict__ scale_k, const unsigned long long* __restrict__ k_pack,
-            const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F,
+            const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F, Row3View R3,
             double* __restrict__ cost_partial, double* __restrict__ Jq_ambient, unsigned* ticket,
             DeviceScalars* sc) {
   constexpr int NP = MODEL >= 0 ? ModelNumParams(MODEL >= 0 ? MODEL : 0) : 12;
+  constexpr int NS = NR == 3 ? (6 + NP + 3) / 4 * 4 : 4;  // third-row slots held in registers, padded to whole units
   double cost = 0.0, fixed = 0.0;
   // grid-stride: the grid is sized to the machine (a few CTAs per SM), not to the problem, so the
   // per-block partial sums that the last block folds stay in the hundreds however large the scene is
@@ -143,12 +170,21 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
           Jq_ambient[(size_t)k * 8 + row * 4 + j] =
               AB[3 * row] * D[j] + AB[3 * row + 1] * D[4 + j] + AB[3 * row + 2] * D[8 + j];
     }
-    const double s = r0 * r0 + r1 * r1;
+    // third row: value and (g_x, g_y) = weight * d map / d (x, y)
+    double rs = 0.0, gx = 0.0, gy = 0.0;
+    if (NR == 3) {
+      double val;
+      if (BilinearWithGrad(R3.maps + (size_t)i * R3.H * R3.W, R3.H, R3.W, x, y, &val, &gx, &gy)) {
+        rs = R3.weight * val; gx *= R3.weight; gy *= R3.weight;
+      } else { gx = 0.0; gy = 0.0; }
+    }
+    const double s = r0 * r0 + r1 * r1 + (NR == 3 ? rs * rs : 0.0);
     double rho[3];
     LossEval(L.type, L.scale, s, rho);
     const int dch = S.dc >> 1;
     D4* Fk = F + FUnit(k, 0, dch);
     D4* Ek = ER + EUnit(k, 0);
+    const int nq = FSUnits(S.dc);
     const D4 zero = {0.0, 0.0, 0.0, 0.0};
     if (!active) {
       fixed += 0.5 * rho[0];
@@ -156,6 +192,10 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
       // the raw residual is still exported for the parity surface; E = 0 keeps it out of every product
       St256(Ek, zero);
       St256(Ek + 32, D4{0.0, 0.0, r0, r1});
+      if (NR == 3) {
+        for (int q = 0; q < nq; ++q) St256(R3.FS + FSUnit(k, q, nq), zero);
+        St256(R3.ES + k, D4{0.0, 0.0, 0.0, rs});
+      }
     } else {
       cost += 0.5 * rho[0];
       // corrector (ceres corrector.cc)
@@ -171,14 +211,22 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
           alpha_sq_norm = alpha / s;
         }
       }
-      auto correct = [&](double& j0, double& j1, double scale) {
+      // (j2: the third-row entry of the same column; untouched storage when NR == 2)
+      auto correct = [&](double& j0, double& j1, double& j2, double scale) {
         if (alpha_sq_norm != 0.0) {
-          const double rtj = r0 * j0 + r1 * j1;
+          const double rtj = r0 * j0 + r1 * j1 + (NR == 3 ? rs * j2 : 0.0);
           j0 -= alpha_sq_norm * r0 * rtj;
           j1 -= alpha_sq_norm * r1 * rtj;
+          if (NR == 3) j2 -= alpha_sq_norm * rs * rtj;
         }
         j0 = sqrt_rho1 * j0 * scale; j1 = sqrt_rho1 * j1 * scale;
+        if (NR == 3) j2 = sqrt_rho1 * j2 * scale;
       };
+      // third row of A * d(u,v)/dp:  (g_x, g_y) . AB
+      const double ABs[3] = {gx * AB[0] + gy * AB[3], gx * AB[1] + gy * AB[4], gx * AB[2] + gy * AB[5]};
+      double f2[NS];
+#pragma unroll
+      for (int j = 0; j < NS; ++j) f2[j] = 0.0;
       // pose slots: 0..2 quaternion tangent, 3..5 tvec
       {
         const double2* sp2 = reinterpret_cast<const double2*>(scale_i + 6 * (size_t)i);
@@ -190,11 +238,15 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
           f0[j] = AB[0] * g.G[j] + AB[1] * g.G[3 + j] + AB[2] * g.G[6 + j];
           f1[j] = AB[3] * g.G[j] + AB[4] * g.G[3 + j] + AB[5] * g.G[6 + j];
           f0[3 + j] = AB[j]; f1[3 + j] = AB[3 + j];
+          if (NR == 3) {
+            f2[j] = ABs[0] * g.G[j] + ABs[1] * g.G[3 + j] + ABs[2] * g.G[6 + j];
+            f2[3 + j] = ABs[j];
+          }
         }
 #pragma unroll
         for (int j = 0; j < 6; ++j) {
-          if (si[j] == 0.0) { f0[j] = 0.0; f1[j] = 0.0; }  // constant slot: exactly zero, whatever the value
-          else correct(f0[j], f1[j], si[j]);
+          if (si[j] == 0.0) { f0[j] = 0.0; f1[j] = 0.0; f2[NR == 3 ? j : 0] = 0.0; }  // constant slot: exactly zero, whatever the value
+          else correct(f0[j], f1[j], f2[NR == 3 ? j : 0], si[j]);
         }
 #pragma unroll
         for (int jj = 0; jj < 3; ++jj) St256(Fk + 32 * jj, D4{f0[2 * jj], f1[2 * jj], f0[2 * jj + 1], f1[2 * jj + 1]});
@@ -212,22 +264,28 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
               const int slot = 2 * jj - 6 + h;
               const double scl = sk[slot];
               PickParam<NP>(Jk, (int)((pack >> (4 * slot)) & 15ull), &f0[h], &f1[h]);
-              if (scl == 0.0) { f0[h] = 0.0; f1[h] = 0.0; }
-              else correct(f0[h], f1[h], scl);
+              double& fs = f2[NR == 3 ? 6 + slot : 0];
+              if (NR == 3) fs = gx * f0[h] + gy * f1[h];
+              if (scl == 0.0) { f0[h] = 0.0; f1[h] = 0.0; fs = 0.0; }
+              else correct(f0[h], f1[h], fs, scl);
             }
             St256(Fk + 32 * jj, D4{f0[0], f1[0], f0[1], f1[1]});
           }
         }
+        // units of the dc tier beyond this model's parameters (e.g. RADIAL, 5 free: dc = 14, slots 12-13) hold no
+        // column; they are multiplied by zeros downstream and must not be stale memory
+        for (int jj = 3 + (NP + 1) / 2; jj < dch; ++jj) St256(Fk + 32 * jj, zero);
       }
       // point block
-      double E[6];
+      double E[6], Es[3] = {0.0, 0.0, 0.0};
       const int po = S.p_off[pt];
       if (po >= 0) {
 #pragma unroll
         for (int j = 0; j < 3; ++j) {
           double j0 = AB[0] * g.R[j] + AB[1] * g.R[3 + j] + AB[2] * g.R[6 + j];
           double j1 = AB[3] * g.R[j] + AB[4] * g.R[3 + j] + AB[5] * g.R[6 + j];
-          correct(j0, j1, scale_p ? scale_p[3 * (size_t)po + j] : 1.0);
+          if (NR == 3) Es[j] = ABs[0] * g.R[j] + ABs[1] * g.R[3 + j] + ABs[2] * g.R[6 + j];
+          correct(j0, j1, Es[j], scale_p ? scale_p[3 * (size_t)po + j] : 1.0);
           E[j] = j0; E[3 + j] = j1;
         }
       } else {
@@ -237,6 +295,14 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
       r0 *= residual_scaling; r1 *= residual_scaling;
       St256(Ek, D4{E[0], E[1], E[2], E[3]});
       St256(Ek + 32, D4{E[4], E[5], r0, r1});
+      if (NR == 3) {
+        rs *= residual_scaling;
+#pragma unroll
+        for (int q = 0; q < NS / 4; ++q)
+          if (q < nq) St256(R3.FS + FSUnit(k, q, nq), D4{f2[4 * q], f2[4 * q + 1], f2[4 * q + 2], f2[4 * q + 3]});
+        for (int q = NS / 4; q < nq; ++q) St256(R3.FS + FSUnit(k, q, nq), zero);
+        St256(R3.ES + k, D4{Es[0], Es[1], Es[2], rs});
+      }
     }
   }
   double v[2] = {cost, fixed};
@@ -245,9 +311,9 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
 }
 
 // residual-only evaluation of the candidate point (Evaluator::Evaluate with no jacobian)
-template <int MODEL>
+template <int MODEL, int NR>
 __global__ void __launch_bounds__(kEvalThreads)
-cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_partial, unsigned* ticket,
+cost_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restrict__ cost_partial, unsigned* ticket,
             double* out_cost) {
   double cost = 0.0, fixed = 0.0;
   for (int k = blockIdx.x * kEvalThreads + threadIdx.x; k < S.n_obs; k += gridDim.x * kEvalThreads) {
@@ -277,8 +343,13 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
     if (MODEL >= 0) WorldToImageVal<(MODEL >= 0 ? MODEL : 0)>(prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
     else WorldToImageValDyn(model, prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
     const double r0 = x - xy.x, r1 = y - xy.y;
+    double rs = 0.0;
+    if (NR == 3) {
+      double val, gx, gy;
+      if (BilinearWithGrad(R3.maps + (size_t)i * R3.H * R3.W, R3.H, R3.W, x, y, &val, &gx, &gy)) rs = R3.weight * val;
+    }
     double rho[3];
-    LossEval(L.type, L.scale, r0 * r0 + r1 * r1, rho);
+    LossEval(L.type, L.scale, r0 * r0 + r1 * r1 + rs * rs, rho);
     if (S.obs_active[k]) cost += 0.5 * rho[0]; else fixed += 0.5 * rho[0];
   }
   double v[2] = {cost, fixed};
@@ -289,15 +360,22 @@ cost_kernel(ParamsView P, StructView S, LossView L, double* __restrict__ cost_pa
 
 template <int MODEL>
 static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool candidate, int blocks) {
-  eval_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(
-      p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_i.p : p->d_mask_i.p,
-      use_scale ? p->d_scale_k.p : p->d_mask_k.p, p->d_k_pack.p, use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p,
-      p->d_F.p, p->d_cost_partial.p, p->jq_out, p->d_tickets.p + 0, p->d_scalars.p);
+#define SBA_EVAL_ARGS                                                                                                  \
+  p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_i.p : p->d_mask_i.p,                                \
+      use_scale ? p->d_scale_k.p : p->d_mask_k.p, p->d_k_pack.p, use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p,      \
+      p->d_F.p, p->Row3(), p->d_cost_partial.p, p->jq_out, p->d_tickets.p + 0, p->d_scalars.p
+  if (p->nr == 3) eval_kernel<MODEL, 3><<<blocks, kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
+  else eval_kernel<MODEL, 2><<<blocks, kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
+#undef SBA_EVAL_ARGS
 }
 template <int MODEL>
 static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks, double* d_out_cost) {
-  cost_kernel<MODEL><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss,
-                                                             p->d_cost_partial.p, p->d_tickets.p + 1, d_out_cost);
+  if (p->nr == 3)
+    cost_kernel<MODEL, 3><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss, p->Row3(),
+                                                                  p->d_cost_partial.p, p->d_tickets.p + 1, d_out_cost);
+  else
+    cost_kernel<MODEL, 2><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss, p->Row3(),
+                                                                  p->d_cost_partial.p, p->d_tickets.p + 1, d_out_cost);
 }
 
 #define SBA_MODEL_SWITCH(m, CALL)                                            \

@@ -21,13 +21,13 @@ static int CamReduce(Problem* p, int mode, const double2* v, double* out, const 
                      const int* skip = nullptr, bool defer_allreduce = false) {
   if (p->n_cdim == 0) return SBA_OK;
   if (p->n_chunks > 0) {
-#define CALL(DC)                                                                                                        \
+#define CALL(DC, NR)                                                                                                    \
   do {                                                                                                                  \
-    if (mode == 0) cam_reduce_kernel<DC, 0><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
-    else if (mode == 1) cam_reduce_kernel<DC, 1><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
-    else cam_reduce_kernel<DC, 2><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, v, p->d_chunk_partial.p, skip); \
+    if (mode == 0) cam_reduce_kernel<DC, 0, NR><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, p->d_FS.p, p->d_ES.p, v, p->d_g1.p, p->d_chunk_partial.p, skip); \
+    else if (mode == 1) cam_reduce_kernel<DC, 1, NR><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, p->d_FS.p, p->d_ES.p, v, p->d_g1.p, p->d_chunk_partial.p, skip); \
+    else cam_reduce_kernel<DC, 2, NR><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, p->d_FS.p, p->d_ES.p, v, p->d_g1.p, p->d_chunk_partial.p, skip); \
   } while (0)
-    SBA_DC_SWITCH(p->dc, CALL)
+    SBA_DCNR_SWITCH(p->dc, p->nr, CALL)
 #undef CALL
     p->launches++;
   }
@@ -49,7 +49,8 @@ int ColumnNorms(Problem* p, double* d_nc, double* d_np, bool camera_part) {
   int rc = camera_part ? CamReduce(p, 2, nullptr, d_nc, nullptr, nullptr) : SBA_OK;
   if (rc) return rc;
   if (p->n_pvar > 0 && p->n_tiles > 0) {
-    point_sqnorm_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, d_np);
+    if (p->nr == 3) point_sqnorm_kernel<3><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p, d_np);
+    else point_sqnorm_kernel<2><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p, d_np);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
@@ -65,8 +66,8 @@ int InitJacobiScale(Problem* p) {
   if (p->n_pvar > 0) { jacobi_scale_kernel<<<DivUp(3 * p->n_pvar, 256), 256, 0, p->stream>>>(3 * p->n_pvar, p->d_sq_p.p, p->d_scale_p.p); p->launches++; }
   Expand(p, p->d_scale_c.p, p->d_scale_i.p, p->d_scale_k.p);
   if (p->n_obs > 0) {
-#define CALL(DC) scale_jacobian_kernel<DC><<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_scale_i.p, p->d_scale_k.p, p->d_scale_p.p, p->d_F.p, p->d_ER.p)
-    SBA_DC_SWITCH(p->dc, CALL)
+#define CALL(DC, NR) scale_jacobian_kernel<DC, NR><<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_scale_i.p, p->d_scale_k.p, p->d_scale_p.p, p->d_F.p, p->d_ER.p, p->d_FS.p, p->d_ES.p)
+    SBA_DCNR_SWITCH(p->dc, p->nr, CALL)
 #undef CALL
     p->launches++;
   }
@@ -83,8 +84,8 @@ int Gradient(Problem* p, bool with_norms) {
   int rc = SBA_OK;
   if (with_norms && p->n_cdim > 0) {  // (every rank takes the same branch: the collectives below must pair up)
     double* part2 = p->d_chunk_partial.p + (size_t)p->n_chunks * kMaxDC;
-#define CALL(DC) cam_reduce_kernel<DC, 3><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, nullptr, p->d_chunk_partial.p, nullptr, part2)
-    if (p->n_chunks > 0) { SBA_DC_SWITCH(p->dc, CALL) }
+#define CALL(DC, NR) cam_reduce_kernel<DC, 3, NR><<<p->n_chunks, 256, 0, p->stream>>>(p->Chunks(), p->d_F.p, p->d_ER.p, p->d_FS.p, p->d_ES.p, nullptr, nullptr, p->d_chunk_partial.p, nullptr, part2)
+    if (p->n_chunks > 0) { SBA_DCNR_SWITCH(p->dc, p->nr, CALL) }
 #undef CALL
     const int n = p->n_img * 6 + p->n_cam * 12;
     cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), p->d_chunk_partial.p, p->d_grad_c.p, nullptr, nullptr);
@@ -150,9 +151,14 @@ int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
 // grad_only: only g_p = E^T r (no LM diagonal needed yet)
 int PointBlocks(Problem* p, bool grad_only) {
   if (p->n_pvar > 0 && p->n_tiles > 0) {
-    point_blocks_kernel<<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p,
-                                                                   grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
-                                                                   p->d_gp.p, p->d_scalars.p);
+    if (p->nr == 3)
+      point_blocks_kernel<3><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
+                                                                        grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
+                                                                        p->d_gp.p, p->d_scalars.p);
+    else
+      point_blocks_kernel<2><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
+                                                                        grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
+                                                                        p->d_gp.p, p->d_scalars.p);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
@@ -162,8 +168,12 @@ int PointBlocks(Problem* p, bool grad_only) {
 // rhs = F^T (r - E C^{-1} g)   (reduced system right-hand side; Ceres solves S y = rhs, step = -y)
 int ReducedRhs(Problem* p, bool defer_allreduce) {
   if (p->n_obs > 0) {
-    rhs_e_kernel<<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_ER.p, p->d_Cinv.p, p->d_gp.p,
-                                                            reinterpret_cast<double2*>(p->d_g2.p));
+    if (p->nr == 3)
+      rhs_e_kernel<3><<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_ER.p, p->d_ES.p, p->d_Cinv.p, p->d_gp.p,
+                                                                 reinterpret_cast<double2*>(p->d_g2.p), p->d_g1.p);
+    else
+      rhs_e_kernel<2><<<DivUp(p->n_obs, 256), 256, 0, p->stream>>>(p->Struct(), p->d_ER.p, p->d_ES.p, p->d_Cinv.p, p->d_gp.p,
+                                                                 reinterpret_cast<double2*>(p->d_g2.p), p->d_g1.p);
     p->launches++;
   }
   defer_allreduce = defer_allreduce && p->comm != nullptr;
@@ -178,8 +188,8 @@ int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip) {
   if (p->bsr.enabled) return BlockSchurMatVec(p, d_x, d_y, skip);  // explicit block-sparse S (bsr.cu)
   Expand(p, d_x, p->d_xi.p, p->d_xc.p);
   if (p->n_tiles > 0) {
-#define CALL(DC) matvec_point_kernel<DC><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p), skip)
-    SBA_DC_SWITCH(p->dc, CALL)
+#define CALL(DC, NR) matvec_point_kernel<DC, NR><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p, p->d_Cinv.p, p->d_xi.p, p->d_xc.p, reinterpret_cast<double2*>(p->d_g2.p), p->d_g1.p, skip)
+    SBA_DCNR_SWITCH(p->dc, p->nr, CALL)
 #undef CALL
     p->launches++;
   }
@@ -191,8 +201,8 @@ int BackSubstitute(Problem* p, bool defer_allreduce) {
   Expand(p, p->d_yc.p, p->d_xi.p, p->d_xc.p);
   const int nb = std::min(DivUp(p->n_tiles, 4), p->n_sm * 16);  // grid-stride over warp tiles
   if (nb > 0) {
-#define CALL(DC) backsub_kernel<DC><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p, p->d_tickets.p + 2, &p->d_scalars.p->model_cost_change)
-    SBA_DC_SWITCH(p->dc, CALL)
+#define CALL(DC, NR) backsub_kernel<DC, NR><<<nb, 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p, p->d_Cinv.p, p->d_gp.p, p->d_xi.p, p->d_xc.p, p->d_yp.p, p->d_cost_partial.p, p->d_tickets.p + 2, &p->d_scalars.p->model_cost_change)
+    SBA_DCNR_SWITCH(p->dc, p->nr, CALL)
 #undef CALL
     p->launches++;
   } else {

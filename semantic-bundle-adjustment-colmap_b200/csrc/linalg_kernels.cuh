@@ -37,65 +37,129 @@ __global__ void expand_kernel(StructView S, const double* __restrict__ x, double
   }
 }
 
-template <int DC>
-__device__ inline void LoadRow(const D4* __restrict__ F, int k, double2 (&row)[DC]) {
+// DC x NR dispatch: CALL(DC, NR)
+#define SBA_DCNR_CASE(dcv, nr, CALL) case dcv: if ((nr) == 3) { CALL(dcv, 3); } else { CALL(dcv, 2); } break;
+#define SBA_DCNR_SWITCH(dc, nr, CALL)                                                              \
+  switch (dc) {                                                                                    \
+    SBA_DCNR_CASE(6, nr, CALL) SBA_DCNR_CASE(8, nr, CALL) SBA_DCNR_CASE(10, nr, CALL)              \
+    SBA_DCNR_CASE(14, nr, CALL)                                                                    \
+    default: if ((nr) == 3) { CALL(18, 3); } else { CALL(18, 2); } break;                          \
+  }
+
+// One observation's camera-side Jacobian block: a[j] = (d r0 / d s_j, d r1 / d s_j), s[j] = d r_s / d s_j (NR == 3)
+template <int DC, int NR> struct FRow { double2 a[DC]; double s[NR == 3 ? DC : 1]; };
+
+template <int DC, int NR>
+__device__ inline void LoadRow(const D4* __restrict__ F, const D4* __restrict__ FS, int k, FRow<DC, NR>& row) {
   const D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
   for (int jj = 0; jj < DC / 2; ++jj) {
     const D4 v = Ld256(f + 32 * jj);
-    row[2 * jj] = make_double2(v.x, v.y); row[2 * jj + 1] = make_double2(v.z, v.w);
+    row.a[2 * jj] = make_double2(v.x, v.y); row.a[2 * jj + 1] = make_double2(v.z, v.w);
+  }
+  if constexpr (NR == 3) {
+    constexpr int NQ = FSUnits(DC);
+    const D4* g = FS + FSUnit(k, 0, NQ);
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const D4 v = Ld256(g + 32 * q);
+      row.s[4 * q] = v.x;
+      if (4 * q + 1 < DC) row.s[4 * q + 1] = v.y;
+      if (4 * q + 2 < DC) row.s[4 * q + 2] = v.z;
+      if (4 * q + 3 < DC) row.s[4 * q + 3] = v.w;
+    }
   }
 }
 
-// f = F_k * x  (2-vector), x in padded form
-template <int DC>
-__device__ inline double2 RowTimesX(const double2 (&row)[DC], const double* __restrict__ xi,
-                                    const double* __restrict__ xc, int i, int c) {
+// f = F_k * x  (NR-vector), x in padded form
+template <int DC, int NR>
+__device__ inline void RowTimesX(const FRow<DC, NR>& row, const double* __restrict__ xi, const double* __restrict__ xc,
+                                 int i, int c, double (&f)[NR]) {
   const double2* pi = reinterpret_cast<const double2*>(xi + 6 * (size_t)i);
-  double f0 = 0.0, f1 = 0.0;
+#pragma unroll
+  for (int r = 0; r < NR; ++r) f[r] = 0.0;
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     const double2 v = __ldg(pi + j);
-    f0 += row[2 * j].x * v.x + row[2 * j + 1].x * v.y;
-    f1 += row[2 * j].y * v.x + row[2 * j + 1].y * v.y;
+    f[0] += row.a[2 * j].x * v.x + row.a[2 * j + 1].x * v.y;
+    f[1] += row.a[2 * j].y * v.x + row.a[2 * j + 1].y * v.y;
+    if constexpr (NR == 3) f[2] += row.s[2 * j] * v.x + row.s[2 * j + 1] * v.y;
   }
   if (DC > 6) {
     const double2* pc = reinterpret_cast<const double2*>(xc + 12 * (size_t)c);
 #pragma unroll
     for (int j = 0; j < (DC - 6) / 2; ++j) {
       const double2 v = __ldg(pc + j);
-      f0 += row[6 + 2 * j].x * v.x + row[7 + 2 * j].x * v.y;
-      f1 += row[6 + 2 * j].y * v.x + row[7 + 2 * j].y * v.y;
+      f[0] += row.a[6 + 2 * j].x * v.x + row.a[7 + 2 * j].x * v.y;
+      f[1] += row.a[6 + 2 * j].y * v.x + row.a[7 + 2 * j].y * v.y;
+      if constexpr (NR == 3) f[2] += row.s[6 + 2 * j] * v.x + row.s[7 + 2 * j] * v.y;
     }
   }
-  return make_double2(f0, f1);
 }
 
-struct ERec { double E[6]; double r0, r1; };
-__device__ inline ERec LoadER(const D4* __restrict__ ER, int k) {
+// E (NR x 3, row-major) and r (NR) of one observation
+template <int NR> struct ERec { double E[3 * NR]; double r[NR]; };
+template <int NR>
+__device__ inline ERec<NR> LoadER(const D4* __restrict__ ER, const D4* __restrict__ ES, int k) {
   const D4 a = Ld256(ER + EUnit(k, 0)), b = Ld256(ER + EUnit(k, 1));
-  ERec e;
+  ERec<NR> e;
   e.E[0] = a.x; e.E[1] = a.y; e.E[2] = a.z; e.E[3] = a.w; e.E[4] = b.x; e.E[5] = b.y;
-  e.r0 = b.z; e.r1 = b.w;
+  e.r[0] = b.z; e.r[1] = b.w;
+  if constexpr (NR == 3) {
+    const D4 c = Ld256(ES + k);
+    e.E[6] = c.x; e.E[7] = c.y; e.E[8] = c.z; e.r[2] = c.w;
+  }
   return e;
+}
+// u += E^T f,  f -= E w
+template <int NR>
+__device__ __forceinline__ void EtAdd(const ERec<NR>& e, const double (&f)[NR], double (&u)[3]) {
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r) u[a] += e.E[3 * r + a] * f[r];
+  }
+}
+template <int NR>
+__device__ __forceinline__ void ESub(const ERec<NR>& e, const double (&w)[3], double (&f)[NR]) {
+#pragma unroll
+  for (int r = 0; r < NR; ++r) f[r] -= e.E[3 * r] * w[0] + e.E[3 * r + 1] * w[1] + e.E[3 * r + 2] * w[2];
+}
+// the per-observation NR-vector scratch: (f0, f1) in v2[k], f2 in v1[k]
+template <int NR>
+__device__ __forceinline__ void StoreVec(double2* __restrict__ v2, double* __restrict__ v1, int k, const double (&f)[NR]) {
+  v2[k] = make_double2(f[0], f[1]);
+  if constexpr (NR == 3) v1[k] = f[2];
+}
+template <int NR>
+__device__ __forceinline__ void LoadVec(const double2* __restrict__ v2, const double* __restrict__ v1, int k, double (&f)[NR]) {
+  const double2 t = v2[k];
+  f[0] = t.x; f[1] = t.y;
+  if constexpr (NR == 3) f[2] = v1[k];
 }
 
 // ---- point-side squared column norms (Jacobi scaling / LM diagonal) -----------------
+template <int NR>
 __global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileView T, const D4* __restrict__ ER,
-                                                           double* __restrict__ np) {
+                                                           const D4* __restrict__ ES, double* __restrict__ np) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
   const int lane = threadIdx.x & 31;
   const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
+  auto sq = [](const ERec<NR>& e, int a) {
+    double v = e.E[a] * e.E[a] + e.E[3 + a] * e.E[3 + a];
+    if constexpr (NR == 3) v += e.E[6 + a] * e.E[6 + a];
+    return v;
+  };
   if (n <= 32) {
     const bool valid = lane < n;
     const int k = s0 + lane;
     const int pt = valid ? S.obs_pt[k] : -1 - lane;
     double v[3] = {0.0, 0.0, 0.0};
     if (valid) {
-      const ERec e = LoadER(ER, k);
+      const ERec<NR> e = LoadER<NR>(ER, ES, k);
 #pragma unroll
-      for (int a = 0; a < 3; ++a) v[a] = e.E[a] * e.E[a] + e.E[3 + a] * e.E[3 + a];
+      for (int a = 0; a < 3; ++a) v[a] = sq(e, a);
     }
     const Seg sg = MakeSeg(pt);
     SegSum<3>(sg, v);
@@ -107,9 +171,9 @@ __global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileVie
     const int pt = S.obs_pt[s0];
     double v[3] = {0.0, 0.0, 0.0};
     for (int k = s0 + lane; k < s0 + n; k += 32) {
-      const ERec e = LoadER(ER, k);
+      const ERec<NR> e = LoadER<NR>(ER, ES, k);
 #pragma unroll
-      for (int a = 0; a < 3; ++a) v[a] += e.E[a] * e.E[a] + e.E[3 + a] * e.E[3 + a];
+      for (int a = 0; a < 3; ++a) v[a] += sq(e, a);
     }
     WarpAllSum<3>(v);
     const int po = S.p_off[pt];
@@ -118,7 +182,9 @@ __global__ void __launch_bounds__(128) point_sqnorm_kernel(StructView S, TileVie
 }
 
 // ---- point blocks: C_p = E^T E + D_p^2, its inverse, and g_p = E^T r -----------------
+template <int NR>
 __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileView T, const D4* __restrict__ ER,
+                                                           const D4* __restrict__ ES,
                                                            const double* __restrict__ Dp, double* __restrict__ Cinv,
                                                            double* __restrict__ gp, DeviceScalars* sc) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -128,28 +194,33 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
   double v[9];
 #pragma unroll
   for (int a = 0; a < 9; ++a) v[a] = 0.0;
-  auto accum = [&](const ERec& e) {
+  auto accum = [&](const ERec<NR>& e) {
     v[0] += e.E[0] * e.E[0] + e.E[3] * e.E[3];
     v[1] += e.E[0] * e.E[1] + e.E[3] * e.E[4];
     v[2] += e.E[0] * e.E[2] + e.E[3] * e.E[5];
     v[3] += e.E[1] * e.E[1] + e.E[4] * e.E[4];
     v[4] += e.E[1] * e.E[2] + e.E[4] * e.E[5];
     v[5] += e.E[2] * e.E[2] + e.E[5] * e.E[5];
-    v[6] += e.E[0] * e.r0 + e.E[3] * e.r1;
-    v[7] += e.E[1] * e.r0 + e.E[4] * e.r1;
-    v[8] += e.E[2] * e.r0 + e.E[5] * e.r1;
+    v[6] += e.E[0] * e.r[0] + e.E[3] * e.r[1];
+    v[7] += e.E[1] * e.r[0] + e.E[4] * e.r[1];
+    v[8] += e.E[2] * e.r[0] + e.E[5] * e.r[1];
+    if constexpr (NR == 3) {
+      v[0] += e.E[6] * e.E[6]; v[1] += e.E[6] * e.E[7]; v[2] += e.E[6] * e.E[8];
+      v[3] += e.E[7] * e.E[7]; v[4] += e.E[7] * e.E[8]; v[5] += e.E[8] * e.E[8];
+      v[6] += e.E[6] * e.r[2]; v[7] += e.E[7] * e.r[2]; v[8] += e.E[8] * e.r[2];
+    }
   };
   int pt; bool writer;
   if (n <= 32) {
     const bool valid = lane < n;
     pt = valid ? S.obs_pt[s0 + lane] : -1 - lane;
-    if (valid) accum(LoadER(ER, s0 + lane));
+    if (valid) accum(LoadER<NR>(ER, ES, s0 + lane));
     const Seg sg = MakeSeg(pt);
     SegSum<9>(sg, v);
     writer = valid && sg.is_head;
   } else {
     pt = S.obs_pt[s0];
-    for (int k = s0 + lane; k < s0 + n; k += 32) accum(LoadER(ER, k));
+    for (int k = s0 + lane; k < s0 + n; k += 32) accum(LoadER<NR>(ER, ES, k));
     WarpAllSum<9>(v);
     writer = lane == 0;
   }
@@ -174,30 +245,34 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
 }
 
 // ---- e_k = r_k - E_k C_p^{-1} g_p  (right-hand side of the reduced system, before F^T) ----
-__global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const D4* __restrict__ ER,
+template <int NR>
+__global__ void __launch_bounds__(256) rhs_e_kernel(StructView S, const D4* __restrict__ ER, const D4* __restrict__ ES,
                                                     const double* __restrict__ Cinv, const double* __restrict__ gp,
-                                                    double2* __restrict__ out) {
+                                                    double2* __restrict__ out, double* __restrict__ out3) {
   const int k = blockIdx.x * 256 + threadIdx.x;
   if (k >= S.n_obs) return;
-  const ERec e = LoadER(ER, k);
-  double e0 = e.r0, e1 = e.r1;
+  const ERec<NR> e = LoadER<NR>(ER, ES, k);
+  double f[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) f[r] = e.r[r];
   const int po = S.p_off[S.obs_pt[k]];
   if (po >= 0) {
     const double g[3] = {gp[3 * (size_t)po], gp[3 * (size_t)po + 1], gp[3 * (size_t)po + 2]};
     double w[3];
     Sym3Mul(Cinv + 6 * (size_t)po, g, w);
-    e0 -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
-    e1 -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+    ESub<NR>(e, w, f);
   }
-  out[k] = make_double2(e0, e1);
+  StoreVec<NR>(out, out3, k, f);
 }
 
 // ---- implicit Schur product, point pass:  g_k = F_k x - E_k C_p^{-1} sum_{j in p} E_j^T F_j x ----
-template <int DC>
+template <int DC, int NR>
 __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileView T, const D4* __restrict__ ER,
-                                                           const D4* __restrict__ F, const double* __restrict__ Cinv,
+                                                           const D4* __restrict__ F, const D4* __restrict__ ES,
+                                                           const D4* __restrict__ FS, const double* __restrict__ Cinv,
                                                            const double* __restrict__ xi, const double* __restrict__ xc,
-                                                           double2* __restrict__ out, const int* __restrict__ skip) {
+                                                           double2* __restrict__ out, double* __restrict__ out3,
+                                                           const int* __restrict__ skip) {
   if (skip && *skip != 0) return;  // CG already stopped (the host polls its state only every few iterations)
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
@@ -207,18 +282,19 @@ __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileVie
     const bool valid = lane < n;
     const int k = s0 + lane;
     int pt = -1 - lane;
-    double2 f = make_double2(0.0, 0.0);
-    ERec e;
+    double f[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) f[r] = 0.0;
+    ERec<NR> e;
     double u[3] = {0.0, 0.0, 0.0};
     if (valid) {
       pt = S.obs_pt[k];
       const int i = S.obs_img[k];
-      double2 row[DC];
-      LoadRow<DC>(F, k, row);
-      f = RowTimesX<DC>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0);
-      e = LoadER(ER, k);
-#pragma unroll
-      for (int a = 0; a < 3; ++a) u[a] = e.E[a] * f.x + e.E[3 + a] * f.y;
+      FRow<DC, NR> row;
+      LoadRow<DC, NR>(F, FS, k, row);
+      RowTimesX<DC, NR>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0, f);
+      e = LoadER<NR>(ER, ES, k);
+      EtAdd<NR>(e, f, u);
     }
     const Seg sg = MakeSeg(pt);
     SegSum<3>(sg, u);
@@ -227,10 +303,9 @@ __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileVie
       if (po >= 0) {
         double w[3];
         Sym3Mul(Cinv + 6 * (size_t)po, u, w);
-        f.x -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
-        f.y -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
+        ESub<NR>(e, w, f);
       }
-      out[k] = f;
+      StoreVec<NR>(out, out3, k, f);
     }
   } else {  // one long point: two strided passes
     const int pt = S.obs_pt[s0];
@@ -238,24 +313,24 @@ __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileVie
     double u[3] = {0.0, 0.0, 0.0};
     for (int k = s0 + lane; k < s0 + n; k += 32) {
       const int i = S.obs_img[k];
-      double2 row[DC];
-      LoadRow<DC>(F, k, row);
-      const double2 f = RowTimesX<DC>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0);
-      const ERec e = LoadER(ER, k);
-#pragma unroll
-      for (int a = 0; a < 3; ++a) u[a] += e.E[a] * f.x + e.E[3 + a] * f.y;
-      out[k] = f;
+      FRow<DC, NR> row;
+      LoadRow<DC, NR>(F, FS, k, row);
+      double f[NR];
+      RowTimesX<DC, NR>(row, xi, xc, i, DC > 6 ? S.img_cam[i] : 0, f);
+      const ERec<NR> e = LoadER<NR>(ER, ES, k);
+      EtAdd<NR>(e, f, u);
+      StoreVec<NR>(out, out3, k, f);
     }
     WarpAllSum<3>(u);
     if (po >= 0) {
       double w[3];
       Sym3Mul(Cinv + 6 * (size_t)po, u, w);
       for (int k = s0 + lane; k < s0 + n; k += 32) {
-        const ERec e = LoadER(ER, k);
-        double2 f = out[k];
-        f.x -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
-        f.y -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
-        out[k] = f;
+        const ERec<NR> e = LoadER<NR>(ER, ES, k);
+        double f[NR];
+        LoadVec<NR>(out, out3, k, f);
+        ESub<NR>(e, w, f);
+        StoreVec<NR>(out, out3, k, f);
       }
     }
   }
@@ -263,48 +338,56 @@ __global__ void __launch_bounds__(128) matvec_point_kernel(StructView S, TileVie
 
 // ---- back-substitution y_p = C_p^{-1}(g_p - sum E^T F y_c), fused with the model cost change
 //      -(J step)^T (r + J step / 2), step = -y   ----
-template <int DC>
+template <int DC, int NR>
 __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, const D4* __restrict__ ER,
-                                                      const D4* __restrict__ F, const double* __restrict__ Cinv,
+                                                      const D4* __restrict__ F, const D4* __restrict__ ES,
+                                                      const D4* __restrict__ FS, const double* __restrict__ Cinv,
                                                       const double* __restrict__ gp, const double* __restrict__ yi,
                                                       const double* __restrict__ yc, double* __restrict__ yp,
                                                       double* __restrict__ partial, unsigned* ticket,
                                                       double* model_cost_change) {
   const int lane = threadIdx.x & 31;
   double acc = 0.0;
+  // m = -(F y_c) - E w;  acc += m . (r + m / 2)
+  auto model = [&](const ERec<NR>& e, const double (&f)[NR], const double (&w)[3], bool has_w) {
+    double m[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) m[r] = -f[r];
+    if (has_w) ESub<NR>(e, w, m);
+#pragma unroll
+    for (int r = 0; r < NR; ++r) acc += m[r] * (e.r[r] + 0.5 * m[r]);
+  };
   for (int tile = blockIdx.x * 4 + (threadIdx.x >> 5); tile < T.n_tiles; tile += gridDim.x * 4) {
     const int s0 = T.tile_start[tile], n = T.tile_start[tile + 1] - s0;
     if (n <= 32) {
       const bool valid = lane < n;
       const int k = s0 + lane;
       int pt = -1 - lane;
-      double2 f = make_double2(0.0, 0.0);
-      ERec e;
+      double f[NR];
+#pragma unroll
+      for (int r = 0; r < NR; ++r) f[r] = 0.0;
+      ERec<NR> e;
       double u[3] = {0.0, 0.0, 0.0};
       if (valid) {
         pt = S.obs_pt[k];
         const int i = S.obs_img[k];
-        double2 row[DC];
-        LoadRow<DC>(F, k, row);
-        f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
-        e = LoadER(ER, k);
-#pragma unroll
-        for (int a = 0; a < 3; ++a) u[a] = e.E[a] * f.x + e.E[3 + a] * f.y;
+        FRow<DC, NR> row;
+        LoadRow<DC, NR>(F, FS, k, row);
+        RowTimesX<DC, NR>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0, f);
+        e = LoadER<NR>(ER, ES, k);
+        EtAdd<NR>(e, f, u);
       }
       const Seg sg = MakeSeg(pt);
       SegSum<3>(sg, u);
       if (valid) {
         const int po = S.p_off[pt];
-        double m0 = -f.x, m1 = -f.y;
+        double w[3] = {0.0, 0.0, 0.0};
         if (po >= 0) {
           const double d[3] = {gp[3 * (size_t)po] - u[0], gp[3 * (size_t)po + 1] - u[1], gp[3 * (size_t)po + 2] - u[2]};
-          double w[3];
           Sym3Mul(Cinv + 6 * (size_t)po, d, w);
           if (sg.is_head) { yp[3 * (size_t)po] = w[0]; yp[3 * (size_t)po + 1] = w[1]; yp[3 * (size_t)po + 2] = w[2]; }
-          m0 -= e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2];
-          m1 -= e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2];
         }
-        acc += m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
+        model(e, f, w, po >= 0);
       }
     } else {
       const int pt = S.obs_pt[s0];
@@ -312,12 +395,12 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
       double u[3] = {0.0, 0.0, 0.0};
       for (int k = s0 + lane; k < s0 + n; k += 32) {
         const int i = S.obs_img[k];
-        double2 row[DC];
-        LoadRow<DC>(F, k, row);
-        const double2 f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
-        const ERec e = LoadER(ER, k);
-#pragma unroll
-        for (int a = 0; a < 3; ++a) u[a] += e.E[a] * f.x + e.E[3 + a] * f.y;
+        FRow<DC, NR> row;
+        LoadRow<DC, NR>(F, FS, k, row);
+        double f[NR];
+        RowTimesX<DC, NR>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0, f);
+        const ERec<NR> e = LoadER<NR>(ER, ES, k);
+        EtAdd<NR>(e, f, u);
       }
       WarpAllSum<3>(u);
       double w[3] = {0.0, 0.0, 0.0};
@@ -328,13 +411,12 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
       }
       for (int k = s0 + lane; k < s0 + n; k += 32) {
         const int i = S.obs_img[k];
-        double2 row[DC];
-        LoadRow<DC>(F, k, row);
-        const double2 f = RowTimesX<DC>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0);
-        const ERec e = LoadER(ER, k);
-        const double m0 = -f.x - (e.E[0] * w[0] + e.E[1] * w[1] + e.E[2] * w[2]);
-        const double m1 = -f.y - (e.E[3] * w[0] + e.E[4] * w[1] + e.E[5] * w[2]);
-        acc += m0 * (e.r0 + 0.5 * m0) + m1 * (e.r1 + 0.5 * m1);
+        FRow<DC, NR> row;
+        LoadRow<DC, NR>(F, FS, k, row);
+        double f[NR];
+        RowTimesX<DC, NR>(row, yi, yc, i, DC > 6 ? S.img_cam[i] : 0, f);
+        const ERec<NR> e = LoadER<NR>(ER, ES, k);
+        model(e, f, w, true);  // (w = 0 for a constant point: E is zero there anyway)
       }
     }
   }
@@ -348,9 +430,11 @@ __global__ void __launch_bounds__(128) backsub_kernel(StructView S, TileView T, 
 // MODE 0: F^T v (v per observation)   MODE 1: F^T r (r from ER)   MODE 2: column square norms
 // MODE 3: F^T r into partial AND the column square norms into partial2, one pass over F (after a new linearisation both
 //         are wanted: the gradient now, the norms by the next LM diagonal)
-template <int DC, int MODE>
+template <int DC, int MODE, int NR>
 __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* __restrict__ F,
-                                                         const D4* __restrict__ ER, const double2* __restrict__ v,
+                                                         const D4* __restrict__ ER, const D4* __restrict__ FS,
+                                                         const D4* __restrict__ ES, const double2* __restrict__ v,
+                                                         const double* __restrict__ v3,
                                                          double* __restrict__ partial, const int* __restrict__ skip,
                                                          double* __restrict__ partial2 = nullptr) {
   if (skip && *skip != 0) return;
@@ -363,22 +447,30 @@ __global__ void __launch_bounds__(256) cam_reduce_kernel(ChunkView C, const D4* 
   for (int j = 0; j < (MODE == 3 ? DC : 1); ++j) acc2[j] = 0.0;
   if (threadIdx.x < n) {
     const int k = C.cam_order[s0 + threadIdx.x];
-    double2 row[DC];
-    LoadRow<DC>(F, k, row);
-    if (MODE == 3) {
-      const double2 w = reinterpret_cast<const double2*>(ER + EUnit(k, 1))[1];
+    FRow<DC, NR> row;
+    LoadRow<DC, NR>(F, FS, k, row);
+    double w[NR];
+    if (MODE == 0) {
+      LoadVec<NR>(v, v3, k, w);
+    } else if (MODE == 1 || MODE == 3) {
+      const double2 t = reinterpret_cast<const double2*>(ER + EUnit(k, 1))[1];  // r = unit 1, z w
+      w[0] = t.x; w[1] = t.y;
+      if constexpr (NR == 3) w[2] = reinterpret_cast<const double*>(ES + k)[3];
+    }
+    if (MODE != 2) {
 #pragma unroll
       for (int j = 0; j < DC; ++j) {
-        acc[j] = row[j].x * w.x + row[j].y * w.y;
-        acc2[j] = row[j].x * row[j].x + row[j].y * row[j].y;
+        acc[j] = row.a[j].x * w[0] + row.a[j].y * w[1];
+        if constexpr (NR == 3) acc[j] += row.s[j] * w[2];
       }
-    } else if (MODE == 2) {
+    }
+    if (MODE == 2 || MODE == 3) {
 #pragma unroll
-      for (int j = 0; j < DC; ++j) acc[j] = row[j].x * row[j].x + row[j].y * row[j].y;
-    } else {
-      const double2 w = MODE == 0 ? v[k] : reinterpret_cast<const double2*>(ER + EUnit(k, 1))[1];  // r = unit 1, z w
-#pragma unroll
-      for (int j = 0; j < DC; ++j) acc[j] = row[j].x * w.x + row[j].y * w.y;
+      for (int j = 0; j < DC; ++j) {
+        double q = row.a[j].x * row.a[j].x + row.a[j].y * row.a[j].y;
+        if constexpr (NR == 3) q += row.s[j] * row.s[j];
+        if (MODE == 2) acc[j] = q; else acc2[MODE == 3 ? j : 0] = q;
+      }
     }
   }
   __shared__ double sm[8][DC];
@@ -455,29 +547,38 @@ __global__ void jacobi_scale_kernel(int n, const double* __restrict__ sqnorm, do
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j < n) scale[j] = 1.0 / (1.0 + sqrt(sqnorm[j]));
 }
-template <int DC>
+template <int DC, int NR>
 __global__ void __launch_bounds__(256) scale_jacobian_kernel(StructView S, const double* __restrict__ si,
                                                              const double* __restrict__ sc, const double* __restrict__ sp,
-                                                             D4* __restrict__ F, D4* __restrict__ ER) {
+                                                             D4* __restrict__ F, D4* __restrict__ ER,
+                                                             D4* __restrict__ FS, D4* __restrict__ ES) {
   const int k = blockIdx.x * 256 + threadIdx.x;
   if (k >= S.n_obs) return;
   const int i = S.obs_img[k];
+  const int c = DC > 6 ? S.img_cam[i] : 0;
+  double sl[DC];  // scale of every slot
+#pragma unroll
+  for (int j = 0; j < 6; ++j) sl[j] = si[6 * (size_t)i + j];
+#pragma unroll
+  for (int j = 6; j < DC; ++j) sl[j] = sc[12 * (size_t)c + j - 6];
   D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
-  for (int jj = 0; jj < 3; ++jj) {
-    const double s0 = si[6 * (size_t)i + 2 * jj], s1 = si[6 * (size_t)i + 2 * jj + 1];
+  for (int jj = 0; jj < DC / 2; ++jj) {
     D4 v = Ld256(f + 32 * jj);
-    v.x *= s0; v.y *= s0; v.z *= s1; v.w *= s1;
+    v.x *= sl[2 * jj]; v.y *= sl[2 * jj]; v.z *= sl[2 * jj + 1]; v.w *= sl[2 * jj + 1];
     St256(f + 32 * jj, v);
   }
-  if (DC > 6) {
-    const int c = S.img_cam[i];
+  if constexpr (NR == 3) {
+    constexpr int NQ = FSUnits(DC);
+    D4* g = FS + FSUnit(k, 0, NQ);
 #pragma unroll
-    for (int jj = 3; jj < DC / 2; ++jj) {
-      const double s0 = sc[12 * (size_t)c + 2 * jj - 6], s1 = sc[12 * (size_t)c + 2 * jj - 5];
-      D4 v = Ld256(f + 32 * jj);
-      v.x *= s0; v.y *= s0; v.z *= s1; v.w *= s1;
-      St256(f + 32 * jj, v);
+    for (int q = 0; q < NQ; ++q) {
+      D4 v = Ld256(g + 32 * q);
+      v.x *= sl[4 * q];
+      v.y *= 4 * q + 1 < DC ? sl[4 * q + 1 < DC ? 4 * q + 1 : 0] : 0.0;
+      v.z *= 4 * q + 2 < DC ? sl[4 * q + 2 < DC ? 4 * q + 2 : 0] : 0.0;
+      v.w *= 4 * q + 3 < DC ? sl[4 * q + 3 < DC ? 4 * q + 3 : 0] : 0.0;
+      St256(g + 32 * q, v);
     }
   }
   const int po = S.p_off[S.obs_pt[k]];
@@ -486,6 +587,11 @@ __global__ void __launch_bounds__(256) scale_jacobian_kernel(StructView S, const
     D4 a = Ld256(ER + EUnit(k, 0)), b = Ld256(ER + EUnit(k, 1));
     a.x *= s0; a.y *= s1; a.z *= s2; a.w *= s0; b.x *= s1; b.y *= s2;  // E row-major 2x3: (E0 E1 E2 | E3 E4 E5)
     St256(ER + EUnit(k, 0), a); St256(ER + EUnit(k, 1), b);
+    if constexpr (NR == 3) {
+      D4 e = Ld256(ES + k);
+      e.x *= s0; e.y *= s1; e.z *= s2;
+      St256(ES + k, e);
+    }
   }
 }
 

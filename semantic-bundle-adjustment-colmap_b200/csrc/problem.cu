@@ -295,7 +295,7 @@ ParamsView Problem::Params(bool candidate) const {
 StructView Problem::Struct() const {
   StructView s;
   s.n_img = n_img; s.n_cam = n_cam; s.n_pt = n_pt; s.n_obs = n_obs;
-  s.dc = dc; s.kmax = kmax; s.n_cdim = n_cdim; s.n_pvar = n_pvar;
+  s.dc = dc; s.kmax = kmax; s.n_cdim = n_cdim; s.n_pvar = n_pvar; s.nr = nr;
   s.img_cam = d_img_cam.p; s.model = d_model.p; s.col_img = d_col_img.p; s.col_cam = d_col_cam.p;
   s.k_cols = d_k_cols.p; s.k_slot = d_k_slot.p; s.k_dim = d_k_dim.p; s.p_off = d_p_off.p;
   s.obs_img = d_obs_img.p; s.obs_pt = d_obs_pt.p; s.obs_xy = d_obs_xy.p;
@@ -360,6 +360,11 @@ struct GlobalStructure {
   sba_summary counts;
 };
 
+// residual rows per block: the two reprojection rows, plus the semantic row when the problem carries maps (X1)
+static int RowsOf(const sba_problem_desc& d) {
+  return (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) ? 3 : 2;
+}
+
 static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
   const int n_img = d.num_images, n_cam = d.num_cameras, n_pt = d.num_points;
   const int64_t n_obs = d.num_observations;
@@ -421,7 +426,8 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
     s.num_parameter_blocks_reduced++; s.num_parameters_reduced += 3; s.num_effective_parameters_reduced += 3;
   }
   g->obs_active.assign(n_obs, 0);
-  s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(2 * n_obs);
+  const int nr = RowsOf(d);
+  s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(nr * n_obs);
   std::vector<int64_t> n_act(NT, 0);
   ParallelFor(NT, [&](int t) {
     int64_t kb, ke, na = 0; Slice(n_obs, NT, t, &kb, &ke);
@@ -433,7 +439,7 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
     }
     n_act[t] = na;
   });
-  for (int t = 0; t < NT; ++t) s.num_residuals_reduced += (int)(2 * n_act[t]);
+  for (int t = 0; t < NT; ++t) s.num_residuals_reduced += (int)(nr * n_act[t]);
 }
 
 int ProblemCounts(const sba_problem_desc* d, sba_summary* s) {
@@ -474,6 +480,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   tm.Lap("validate");
   const sba_problem_desc& d = *dp;
   Problem* p = new Problem();
+  p->nr = RowsOf(d);  // 3: the semantic row is part of every residual block (evaluation AND solve)
   // ---- device first: the label maps (61 MB at C2, 6 GB at C5) start moving on a side stream right away, so their
   //      DMA runs under the host set-up below instead of after it ----
   DevBuf<int> raw_img, raw_pt;   // the caller's observation arrays on the device (released after the final sync)
@@ -689,6 +696,10 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   tm.Lap("device order");
   const size_t nc = std::max(1, p->n_cdim), np3 = std::max(1, 3 * p->n_pvar);
   UP(p->d_ER.Alloc(TilePad(std::max(1, n_obs)) * 2)); UP(p->d_F.Alloc(TilePad(std::max(1, n_obs)) * (p->dc / 2)));
+  if (p->nr == 3) {
+    UP(p->d_ES.Alloc(TilePad(std::max(1, n_obs)))); UP(p->d_FS.Alloc(TilePad(std::max(1, n_obs)) * FSUnits(p->dc)));
+    UP(p->d_g1.Alloc((size_t)std::max(1, n_obs)));
+  }
   p->n_partial = std::max(std::max(DivUp(std::max(1, n_obs), 128), DivUp(std::max(1, p->n_tiles), 4)),
                           DivUp(p->n_img + p->n_cam + p->n_pt, 128)) + 8;
   UP(p->d_cost_partial.Alloc(4 * (size_t)p->n_partial));

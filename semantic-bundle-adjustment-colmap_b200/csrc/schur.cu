@@ -37,18 +37,25 @@ template <int DC> struct Elems { static constexpr int N = (DC * DC + 31) / 32; }
 
 // W_a = F_a^T E_a, H_a = W_a C^{-1}; one thread per (image-major position, slot) -- the rows of W / H are stored in
 // image-major order so that a chunk's rows are contiguous
-template <int DC>
+template <int DC, int NR>
 __global__ void __launch_bounds__(256) schur_wh_kernel(StructView S, const int* __restrict__ cam_order, const D4* __restrict__ ER,
-                                                       const D4* __restrict__ F, const double* __restrict__ Cinv,
+                                                       const D4* __restrict__ F, const D4* __restrict__ ES,
+                                                       const D4* __restrict__ FS, const double* __restrict__ Cinv,
                                                        double* __restrict__ W, double* __restrict__ H) {
   const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (t >= (int64_t)S.n_obs * DC) return;
   const int pos = (int)(t / DC);
   const int a = cam_order[pos];
-  const double2 f = LoadSlot(F, a, (int)(t - (int64_t)pos * DC), DC / 2);
+  const int slot = (int)(t - (int64_t)pos * DC);
+  const double2 f = LoadSlot(F, a, slot, DC / 2);
   const D4 ea = Ld256(ER + EUnit(a, 0));                                          // E0 E1 E2 E3
   const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];       // E4 E5
-  const double w[3] = {f.x * ea.x + f.y * ea.w, f.x * ea.y + f.y * eb.x, f.x * ea.z + f.y * eb.y};
+  double w[3] = {f.x * ea.x + f.y * ea.w, f.x * ea.y + f.y * eb.x, f.x * ea.z + f.y * eb.y};
+  if constexpr (NR == 3) {
+    const double fs = LoadSlotS(FS, a, slot, FSUnits(DC));
+    const D4 es = Ld256(ES + a);
+    w[0] += fs * es.x; w[1] += fs * es.y; w[2] += fs * es.z;
+  }
   double h[3] = {0.0, 0.0, 0.0};
   const int po = S.p_off[S.obs_pt[a]];
   if (po >= 0) Sym3Mul(Cinv + 6 * (size_t)po, w, h);
@@ -94,8 +101,8 @@ __device__ inline void Emit(const Sink& k, int row, int col, double v, bool same
 }
 
 // ---- diagonal contributions: chunk partial blocks -------------------------------------
-template <int DC>
-__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, const D4* __restrict__ F,
+template <int DC, int NR>
+__global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, const D4* __restrict__ F, const D4* __restrict__ FS,
                                                                const double* __restrict__ W, const double* __restrict__ H,
                                                                double* __restrict__ partial) {
   __shared__ double red[8][DC * DC];
@@ -119,6 +126,7 @@ __global__ void __launch_bounds__(256) schur_diag_chunk_kernel(ChunkView C, cons
       const double* h = H + 3 * (a + ja[q]);
       const double* wv = W + 3 * (a + jb[q]);
       acc[q] += (fa.x * fb.x + fa.y * fb.y) - (h[0] * wv[0] + h[1] * wv[1] + h[2] * wv[2]);
+      if constexpr (NR == 3) acc[q] += LoadSlotS(FS, obs, ja[q], FSUnits(DC)) * LoadSlotS(FS, obs, jb[q], FSUnits(DC));
     }
   }
 #pragma unroll
@@ -239,9 +247,10 @@ template <int DC> struct ObsLane {
 // partial[ch][e], e over the lower triangle (ja >= jb, e = ja (ja + 1) / 2 + jb).
 // A lane owns an observation and writes its own two rows (image-major, sector-aligned, 256-bit stores); only the current
 // H row is kept in registers, the diagonal entries of slot ja being formed as soon as H_ja exists.
-template <int DC>
+template <int DC, int NR>
 __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
-                                                             const D4* __restrict__ F, const double* __restrict__ Cinv,
+                                                             const D4* __restrict__ F, const D4* __restrict__ ES,
+                                                             const D4* __restrict__ FS, const double* __restrict__ Cinv,
                                                              double* __restrict__ W, double* __restrict__ H,
                                                              double* __restrict__ partial) {
   constexpr int NT = DC * (DC + 1) / 2, DH = DC / 2, RW = WRow(DC);
@@ -260,6 +269,20 @@ __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, Ch
     const D4 ea = Ld256(ER + EUnit(a, 0));
     const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];
     const double E[6] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y};
+    double fs[NR == 3 ? DC : 1], Es[3] = {0.0, 0.0, 0.0};  // third row (X1): F_s (DC), E_s (3)
+    if constexpr (NR == 3) {
+      constexpr int NQ = FSUnits(DC);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const D4 u = Ld256(FS + FSUnit(a, q, NQ));
+        fs[4 * q] = u.x;
+        if (4 * q + 1 < DC) fs[4 * q + 1 < DC ? 4 * q + 1 : 0] = u.y;
+        if (4 * q + 2 < DC) fs[4 * q + 2 < DC ? 4 * q + 2 : 0] = u.z;
+        if (4 * q + 3 < DC) fs[4 * q + 3 < DC ? 4 * q + 3 : 0] = u.w;
+      }
+      const D4 es = Ld256(ES + a);
+      Es[0] = es.x; Es[1] = es.y; Es[2] = es.z;
+    }
     const int po = S.p_off[S.obs_pt[a]];
     double ci[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     if (po >= 0) {
@@ -275,12 +298,15 @@ __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, Ch
 #pragma unroll
     for (int ja = 0; ja < DC; ++ja) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) w[3 * ja + c] = f[ja].x * E[c] + f[ja].y * E[3 + c];
+      for (int c = 0; c < 3; ++c) {
+        w[3 * ja + c] = f[ja].x * E[c] + f[ja].y * E[3 + c];
+        if constexpr (NR == 3) w[3 * ja + c] += fs[ja] * Es[c];
+      }
       Sym3Mul(ci, &w[3 * ja], &h[3 * ja]);
       // the entries of slot ja are final: they go straight to the reduction area, not through registers
 #pragma unroll
       for (int jb = 0; jb <= ja; ++jb)
-        sm[(ja * (ja + 1) / 2 + jb) * 256 + t] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y) -
+        sm[(ja * (ja + 1) / 2 + jb) * 256 + t] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y + (NR == 3 ? fs[NR == 3 ? ja : 0] * fs[NR == 3 ? jb : 0] : 0.0)) -
                                                  (h[3 * ja] * w[3 * jb] + h[3 * ja + 1] * w[3 * jb + 1] + h[3 * ja + 2] * w[3 * jb + 2]);
       // 32-byte units of the two rows leave as soon as they are complete (H is not needed again)
 #pragma unroll
@@ -487,18 +513,18 @@ static int EnsureBlockStorage(Problem* p) {
 }
 
 // W/H pass + diagonal chunks + pair segments into `sink`
-template <int DC>
+template <int DC, int NR>
 static cudaError_t AccumulateLane(Problem* p, const PairList& L, const Sink& sink) {
   constexpr size_t smem = ObsLane<DC>::kSmem;
   static bool attr_set[64] = {};
   if (!attr_set[p->device & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(schur_obs_lane_kernel<DC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(schur_obs_lane_kernel<DC, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set[p->device & 63] = true;
   }
   cudaStream_t st = p->stream;
-  schur_obs_lane_kernel<DC><<<p->n_chunks, 256, smem, st>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p, p->d_Cinv.p,
-                                                            p->d_W.p, p->d_H.p, p->d_chunk_block.p);
+  schur_obs_lane_kernel<DC, NR><<<p->n_chunks, 256, smem, st>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p,
+                                                                p->d_Cinv.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p);
   schur_diag_finalize_tri_kernel<DC><<<p->n_img, 64, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);
   p->launches += 2;
   if (L.n_seg > 0) {
@@ -516,13 +542,25 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
   if (p->n_obs == 0) return SBA_OK;
   SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * WRow(dc))); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * WRow(dc)));
   SBA_CUDA(p->d_chunk_block.Alloc((size_t)std::max(1, p->n_chunks) * dc * dc));
-  if (dc == 6) { SBA_CUDA(AccumulateLane<6>(p, L, sink)); return SBA_OK; }
-  if (dc == 8) { SBA_CUDA(AccumulateLane<8>(p, L, sink)); return SBA_OK; }
+  const bool r3 = p->nr == 3;
+  if (dc == 6 || dc == 8) {
+    cudaError_t e;
+    if (dc == 6) e = r3 ? AccumulateLane<6, 3>(p, L, sink) : AccumulateLane<6, 2>(p, L, sink);
+    else e = r3 ? AccumulateLane<8, 3>(p, L, sink) : AccumulateLane<8, 2>(p, L, sink);
+    SBA_CUDA(e);
+    return SBA_OK;
+  }
 #define CALL(DC)                                                                                                          \
   do {                                                                                                                    \
-    schur_wh_kernel<DC><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_cam_order.p, p->d_ER.p, p->d_F.p, p->d_Cinv.p, \
-                                                                          p->d_W.p, p->d_H.p);                            \
-    schur_diag_chunk_kernel<DC><<<p->n_chunks, 256, 0, st>>>(p->Chunks(), p->d_F.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p); \
+    if (r3) {                                                                                                             \
+      schur_wh_kernel<DC, 3><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_cam_order.p, p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p, \
+                                                                               p->d_Cinv.p, p->d_W.p, p->d_H.p);          \
+      schur_diag_chunk_kernel<DC, 3><<<p->n_chunks, 256, 0, st>>>(p->Chunks(), p->d_F.p, p->d_FS.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p); \
+    } else {                                                                                                              \
+      schur_wh_kernel<DC, 2><<<DivUp((int64_t)p->n_obs * DC, 256), 256, 0, st>>>(p->Struct(), p->d_cam_order.p, p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p, \
+                                                                               p->d_Cinv.p, p->d_W.p, p->d_H.p);          \
+      schur_diag_chunk_kernel<DC, 2><<<p->n_chunks, 256, 0, st>>>(p->Chunks(), p->d_F.p, p->d_FS.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p); \
+    }                                                                                                                     \
     schur_diag_finalize_kernel<DC><<<p->n_img, 128, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);          \
     p->launches += 3;                                                                                                     \
     if (L.n_seg > 0) {                                                                                                    \

@@ -501,66 +501,3 @@ extern "C" int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residua
   cudaStreamDestroy(st);
   return SBA_OK;
 }
-
-// =================================== K-SEM-BILIN (extension X1) ===============================
-namespace sba {
-
-__device__ inline double BilinearSample(const float* __restrict__ map, int H, int W, double x, double y, int* ok) {
-  const double inv_y = H - 1 - y;
-  const int x0 = CvtInt(floor(x)), x1 = x0 + 1;
-  const int y0 = CvtInt(floor(inv_y)), y1 = y0 + 1;
-  if (x0 < 0 || x1 >= W || y0 < 0 || y1 >= H || x1 < 0 || y1 < 0) { *ok = 0; return 0.0; }
-  const double dx = x - x0, dy = inv_y - y0, dx_1 = 1 - dx, dy_1 = 1 - dy;
-  const float* line0 = map + (size_t)(H - 1 - y0) * W;
-  const float* line1 = map + (size_t)(H - 1 - y1) * W;
-  const double v0 = dx_1 * __ldg(line0 + x0) + dx * __ldg(line0 + x1);
-  const double v1 = dx_1 * __ldg(line1 + x0) + dx * __ldg(line1 + x1);
-  *ok = 1;
-  return dy_1 * v0 + dy * v1;
-}
-
-__global__ void __launch_bounds__(128) sem_rows_kernel(ParamsView P, StructView S, const float* __restrict__ maps, int H, int W,
-                                                       double weight, double* __restrict__ out) {
-  const int k = blockIdx.x * 128 + threadIdx.x;
-  if (k >= S.n_obs) return;
-  const int i = S.obs_img[k], pt = S.obs_pt[k], c = S.img_cam[i];
-  const double* pose = P.pose + 8 * (size_t)i;
-  const double q[4] = {pose[0], pose[1], pose[2], pose[3]};
-  const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
-  double pr[3];
-  UnitQuatRotate(q, X, pr);
-  pr[0] += pose[4]; pr[1] += pose[5]; pr[2] += pose[6];
-  pr[0] /= pr[2]; pr[1] /= pr[2];
-  double prm[12];
-  for (int j = 0; j < 12; ++j) prm[j] = P.cam[12 * (size_t)c + j];
-  double x, y;
-  WorldToImageValDyn(S.model[c], prm, pr[0], pr[1], &x, &y);
-  int ok;
-  const double v = BilinearSample(maps + (size_t)i * H * W, H, W, x, y, &ok);
-  out[k] = ok ? weight * v : 0.0;
-}
-
-int EvaluateSemanticRows(Problem* p, double* sem_residuals_host) {
-  if (!p->d_sem_maps.p) {
-    SetError(SBA_ERR_INVALID_ARGUMENT, "sem_residuals requested but the problem has no semantic maps");
-    return SBA_ERR_INVALID_ARGUMENT;
-  }
-  const int n = p->n_obs;
-  if (n == 0) return SBA_OK;
-  DevBuf<double> d_out;
-  SBA_CUDA(d_out.Alloc(n));
-  sem_rows_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Params(false), p->Struct(), p->d_sem_maps.p, p->sem_h, p->sem_w,
-                                                        p->sem_weight, d_out.p);
-  p->launches++;
-  std::vector<double> h(n);
-  SBA_CUDA(cudaMemcpyAsync(h.data(), d_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
-  SBA_CUDA(cudaStreamSynchronize(p->stream));
-  {
-    const int frc = FetchHostOrder(p);
-    if (frc) return frc;
-  }
-  for (int k = 0; k < n; ++k) sem_residuals_host[p->h_local2ref[k]] = h[k];
-  return SBA_OK;
-}
-
-}  // namespace sba

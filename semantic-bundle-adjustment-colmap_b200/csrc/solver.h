@@ -192,6 +192,10 @@ struct Problem {
   // ---- device: linearisation ----
   DevBuf<D4> d_ER;       // [TilePad(n_obs)*2]       tile-blocked (common.cuh)
   DevBuf<D4> d_F;        // [TilePad(n_obs)*dc/2]    tile-blocked
+  int nr = 2;            // residual rows per observation: 3 when the problem carries the semantic row (extension X1)
+  DevBuf<D4> d_ES;       // [n_obs]                          third row: {E_s (3), r_s}
+  DevBuf<D4> d_FS;       // [TilePad(n_obs)*FSUnits(dc)]     third row of F, tile-blocked
+  DevBuf<double> d_g1;   // [n_obs] third component of the per-observation scratch vector (d_g2 holds the first two)
   DevBuf<double> d_cost_partial;  // [blocks*2]
   DevBuf<double> d_scale_c, d_scale_p;      // Jacobi scaling
   DevBuf<double> d_diag_c, d_diag_p;        // clamped column square norms
@@ -249,6 +253,7 @@ struct Problem {
 
   ~Problem();
   ParamsView Params(bool candidate = false) const;
+  Row3View Row3() const { return Row3View{d_ES.p, d_FS.p, d_sem_maps.p, sem_h, sem_w, sem_weight}; }
   StructView Struct() const;
   TileView Tiles() const;
   ChunkView Chunks() const;
@@ -304,8 +309,6 @@ int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
 int SolvePCGBlocks(Problem* p, const sba_solver_options& o);  // pcg_blocks.cu: one persistent kernel on the block-sparse S
 // lm.cu
 int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, void* user, sba_summary* s);
-// semantic.cu
-int EvaluateSemanticRows(Problem* p, double* sem_residuals_host);
 // comm.cu
 int CommGetUniqueId(void* id128);
 int CommInit(Problem* p, int nranks, int rank, const void* id128);

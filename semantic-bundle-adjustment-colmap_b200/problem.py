@@ -136,6 +136,11 @@ class Solver:
                                          *[capi.ptr(bufs[k], capi._dp) for k in ("r", "pose", "intr", "point", "qvec", "sem")]))
         out = {k: v for k, v in bufs.items() if v is not None}
         out["cost"] = cost.value
+        if "sem_jac" in want:  # Jacobian of the third (semantic) row of the evaluation just made
+            sp, si, sx = np.zeros((n, 6)), np.zeros((n, capi.MAX_CAMERA_PARAMS)), np.zeros((n, 3))
+            capi.check(self.lib.sba_get_semantic_jacobian(self._h, capi.ptr(sp, capi._dp), capi.ptr(si, capi._dp),
+                                                          capi.ptr(sx, capi._dp)))
+            out["sem_pose"], out["sem_intr"], out["sem_point"] = sp, si, sx
         return out
 
     def solve(self, options=None, callback=None):

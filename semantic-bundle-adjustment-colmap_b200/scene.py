@@ -15,10 +15,13 @@ from .problem import FlatProblem
 # BASELINE.json configs: (cameras, points, mean observations per point, model, free intrinsics)
 CONFIGS = {
     "C1": dict(n_cam=10, n_pt=2000, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, height=1000, refine_intr=True),
-    "C2": dict(n_cam=50, n_pt=20000, mean_track=7.5, model="SIMPLE_PINHOLE", width=640, height=480, refine_intr=False),
-    "C3": dict(n_cam=500, n_pt=200000, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, height=1000, refine_intr=True),
+    "C2": dict(n_cam=50, n_pt=20000, mean_track=7.5, model="SIMPLE_PINHOLE", width=640, height=480, refine_intr=False,
+               semantic="distance"),
+    "C3": dict(n_cam=500, n_pt=200000, mean_track=7.5, model="SIMPLE_RADIAL", width=640, height=480, refine_intr=True,
+               semantic="distance"),
     "C4": dict(n_cam=1778, n_pt=993000, mean_track=5.035, model="SIMPLE_RADIAL", width=1000, height=1000, refine_intr=True),
-    "C5": dict(n_cam=5000, n_pt=2000000, mean_track=7.5, model="SIMPLE_PINHOLE", width=640, height=480, refine_intr=False),
+    "C5": dict(n_cam=5000, n_pt=2000000, mean_track=7.5, model="SIMPLE_PINHOLE", width=640, height=480, refine_intr=False,
+               semantic="distance"),
 }
 
 
@@ -96,7 +99,8 @@ def _project(model, params, q, t, X, obs_img, obs_pt):
 
 
 def make_scene(n_cam, n_pt, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, height=1000, refine_intr=True,
-               seed=0, window=32, noise_px=2.0, perturb=True, label_maps=False, n_classes=8):
+               seed=0, window=32, noise_px=2.0, perturb=True, label_maps=False, n_classes=8, semantic=None,
+               sem_weight=0.1):
     """Returns (FlatProblem, ground_truth dict). Gauge as the reference controller fixes it
     (src/controllers/bundle_adjustment.cc:95-96): pose 0 constant, tvec[0] of pose 1 constant."""
     rng = np.random.default_rng(seed)
@@ -148,12 +152,21 @@ def make_scene(n_cam, n_pt, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, h
         cmask = sum(1 << j for j in capi.MODEL_PP_IDXS[mid])
     else:
         cmask = (1 << capi.MODEL_NUM_PARAMS[mid]) - 1
+    # semantic maps of extension X1: "labels" (piecewise constant class ids) or "distance" (truncated distance to the
+    # nearest label boundary, the smooth map a bilinear residual row has a gradient on); label_maps=True == "labels"
     sem = None
-    if label_maps:
+    if semantic is None and label_maps:
+        semantic = "labels"
+    if semantic == "labels":
         sem = make_label_maps(n_cam, height, width, n_classes, seed + 1)
+    elif semantic == "distance":
+        sem = make_distance_maps(n_cam, height, width, n_classes, seed + 1)
+    elif semantic is not None:
+        raise ValueError("semantic must be None, 'labels' or 'distance'")
     prob = FlatProblem(q0, t0, np.arange(n_cam), np.full(n_cam, mid), params, X0, obs_img, obs_pt, xy,
                        image_pose_constant=pose_const, image_tvec_constant_mask=tvec_mask,
-                       camera_param_constant_mask=np.full(n_cam, cmask, np.uint16), sem_maps=sem)
+                       camera_param_constant_mask=np.full(n_cam, cmask, np.uint16), sem_maps=sem,
+                       sem_weight=sem_weight)
     return prob, dict(q=q_gt, t=t_gt, X=X, params=params)
 
 
@@ -175,4 +188,24 @@ def make_label_maps(n_img, height, width, n_classes=8, seed=1, n_seeds=64):
         d = (xs[..., None] - sx) ** 2 + (ys[..., None] - sy) ** 2
         coarse = lab[np.argmin(d, axis=-1)].astype(np.float32)
         maps[i] = np.kron(coarse, np.ones((step, step), np.float32))[:height, :width]
+    return maps
+
+
+def make_distance_maps(n_img, height, width, n_classes=8, seed=1, n_unique=16, truncate=24.0):
+    """Distance maps (float32, pixels, truncated): Euclidean distance to the nearest boundary of a Voronoi label map.
+    `n_unique` distinct maps are generated and repeated over the images (the content does not matter to the solver,
+    every image still owns its own copy in memory)."""
+    from scipy import ndimage
+    nu = int(min(n_unique, n_img))
+    labels = make_label_maps(nu, height, width, n_classes, seed)
+    uniq = np.empty((nu, height, width), np.float32)
+    for i in range(nu):
+        lab = labels[i]
+        edge = np.zeros((height, width), bool)
+        edge[:, 1:] |= lab[:, 1:] != lab[:, :-1]
+        edge[1:, :] |= lab[1:, :] != lab[:-1, :]
+        uniq[i] = np.minimum(ndimage.distance_transform_edt(~edge), truncate).astype(np.float32)
+    maps = np.empty((n_img, height, width), np.float32)
+    for i in range(n_img):
+        maps[i] = uniq[i % nu]
     return maps

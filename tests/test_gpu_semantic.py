@@ -157,12 +157,13 @@ def test_cylinder_iou_parity(sba, oracle):
 
 
 def test_semantic_bilinear_rows(sba, oracle):
-    """Extension X1: weight * bilinear(label map, projection) per observation."""
+    """Extension X1, raw row: weight * bilinear(label map, projection) per observation (the row inside the residual
+    blocks, its Jacobian and the solve are covered by tests/test_semantic_row.py)."""
     prob, _ = sba.scene.make_scene(n_cam=5, n_pt=400, mean_track=4.0, model="SIMPLE_PINHOLE", width=160, height=120,
                                    refine_intr=False, seed=2, label_maps=True)
     prob.sem_weight = 0.5
     s = sba.Solver(prob)
-    ev = s.evaluate(want=("r", "sem"))
+    ev = s.evaluate(want=("r", "sem"), apply_loss=False)
     ref = np.zeros(prob.num_observations)
     d = prob.desc()
     assert oracle.oracle_ba_sem_rows(C.byref(d), sba.capi.ptr(ref, sba.capi._dp)) == 0
