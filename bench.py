@@ -100,8 +100,7 @@ def make_workload(m, name, n_gpus, strong=False):
     """Weak scaling (default): points (and with them observations) per GPU fixed, cameras fixed."""
     cfg = dict(m.scene.CONFIGS[name])
     cfg["n_pt"] = cfg["n_pt"] * (1 if strong else n_gpus)
-    label_maps = name in ("C2",)  # C5's 5k maps (6 GB) are generated only on request
-    prob, _ = m.scene.make_scene(seed=0, label_maps=label_maps, **cfg)
+    prob, _ = m.scene.make_scene(seed=0, **cfg)  # C2 / C3 / C5 carry their distance maps (scene.CONFIGS)
     return prob, cfg
 
 
