@@ -43,6 +43,8 @@ def load(capi):
     lib.oracle_ba_evaluate.restype = C.c_int
     lib.oracle_ba_evaluate_rows.argtypes = [PD, C.c_int, C.c_double, C.c_int, C.c_int] + [dp] * 10
     lib.oracle_ba_evaluate_rows.restype = C.c_int
+    lib.oracle_default_solver_options.argtypes = [C.POINTER(capi.SolverOptions)]
+    lib.oracle_default_solver_options.restype = None
     lib.oracle_ba_counts.argtypes = [PD, C.POINTER(capi.Summary)]
     lib.oracle_ba_solve.argtypes = [PD, C.POINTER(capi.SolverOptions), C.c_int, C.POINTER(capi.Summary),
                                     C.POINTER(capi.IterationSummary), C.c_int, ip, dp, dp, dp, dp]

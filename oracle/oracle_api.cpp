@@ -147,6 +147,22 @@ int oracle_ba_evaluate(const sba_problem_desc* d, int loss_type, double loss_sca
                                  jac_point, jac_qvec_ambient, nullptr, nullptr, nullptr, nullptr);
 }
 
+// BundleAdjustmentOptions' solver options (src/optim/bundle_adjustment.h:78-93) on top of the ceres::Solver::Options
+// 2.1.0 defaults, restated here so that the CPU arm of bench.py needs nothing from the product library.
+void oracle_default_solver_options(sba_solver_options* o) {
+  std::memset(o, 0, sizeof(*o));
+  o->linear_solver_type = SBA_SOLVER_AUTO;
+  o->max_num_iterations = 100;            // bundle_adjustment.h:85
+  o->max_linear_solver_iterations = 200;  // :86
+  o->min_linear_solver_iterations = 0;
+  o->max_num_consecutive_invalid_steps = 10;  // :87
+  o->function_tolerance = 0.0; o->gradient_tolerance = 0.0; o->parameter_tolerance = 0.0;  // :81-83
+  o->loss_function_type = SBA_LOSS_TRIVIAL; o->loss_function_scale = 1.0;
+  o->initial_trust_region_radius = 1e4; o->max_trust_region_radius = 1e16; o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3; o->min_lm_diagonal = 1e-6; o->max_lm_diagonal = 1e32;
+  o->eta = 1e-1; o->jacobi_scaling = 1; o->update_state_every_iteration = 0;
+}
+
 int oracle_ba_counts(const sba_problem_desc* d, sba_summary* s) {
   BAProblem p;
   p.Build(*d);

@@ -100,7 +100,7 @@ def _project(model, params, q, t, X, obs_img, obs_pt):
 
 def make_scene(n_cam, n_pt, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, height=1000, refine_intr=True,
                seed=0, window=32, noise_px=2.0, perturb=True, label_maps=False, n_classes=8, semantic=None,
-               sem_weight=0.1):
+               sem_weight=0.1, perturb_scale=1.0):
     """Returns (FlatProblem, ground_truth dict). Gauge as the reference controller fixes it
     (src/controllers/bundle_adjustment.cc:95-96): pose 0 constant, tvec[0] of pose 1 constant."""
     rng = np.random.default_rng(seed)
@@ -134,13 +134,13 @@ def make_scene(n_cam, n_pt, mean_track=7.5, model="SIMPLE_RADIAL", width=1000, h
 
     q0, t0, X0 = q_gt.copy(), t_gt.copy(), X.copy()
     if perturb:
-        t0 = t0 + rng.normal(0, 0.01, t0.shape)
-        w = rng.normal(0, 0.002, (n_cam, 3))
+        t0 = t0 + rng.normal(0, 0.01 * perturb_scale, t0.shape)
+        w = rng.normal(0, 0.002 * perturb_scale, (n_cam, 3))
         ang = np.linalg.norm(w, axis=1)
         dq = np.concatenate([np.cos(ang / 2)[:, None], (np.sin(ang / 2) / np.maximum(ang, 1e-300))[:, None] * w], axis=1)
         q0 = quat_mul(dq, q0)
         q0 /= np.linalg.norm(q0, axis=1, keepdims=True)
-        X0 = X0 + rng.normal(0, 0.01, X0.shape)
+        X0 = X0 + rng.normal(0, 0.01 * perturb_scale, X0.shape)
         q0[0], t0[0] = q_gt[0], t_gt[0]  # the gauge-fixing pose stays exact
 
     pose_const = np.zeros(n_cam, np.uint8); pose_const[0] = 1

@@ -213,6 +213,26 @@ def test_semantic_row_solve_parity_c2(sba, oracle):
 
 
 @pytest.mark.gpu
+def test_semantic_row_solve_parity_c2_bench_scene(sba, oracle):
+    """The scene bench.py solves (initial guess perturbed 30x harder): every one of the 10 iterations moves the cost and
+    the trust region rejects steps -- the device and the oracle must take the SAME accept / reject sequence."""
+    prob, _ = sba.scene.make_config("C2", perturb_scale=30.0)
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations = 10
+    rc, so, tro, _ = oracle_solve(oracle, sba.capi, prob, o)
+    s = sba.Solver(prob)
+    sg = s.solve(o)
+    trg = s.trace()
+    s.close()
+    assert len(trg) == len(tro) == 11
+    assert [t.step_is_successful for t in trg] == [t.step_is_successful for t in tro]
+    assert so.num_unsuccessful_steps >= 1 and all(abs(t.cost_change) > 1e-9 * t.cost for t in tro[1:])
+    for a, b in zip(trg, tro):
+        assert a.cost == pytest.approx(b.cost, rel=1e-8) and a.trust_region_radius == pytest.approx(b.trust_region_radius, rel=1e-6)
+    assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
+
+
+@pytest.mark.gpu
 def test_semantic_row_implicit_products_and_robust_solve(sba, oracle, monkeypatch):
     """Implicit Schur products (matvec_point / cam_reduce with three rows) and a Cauchy-loss solve."""
     prob = _scene(sba, model="SIMPLE_RADIAL", refine=True, n_cam=12, n_pt=1500, seed=10)
