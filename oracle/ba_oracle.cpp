@@ -1092,17 +1092,10 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
     it.step_norm = step_norm;
     it.cost_change = x_cost - cand_cost;
     // ParameterToleranceReached
-    if (step_norm <= o.parameter_tolerance * (x_norm + o.parameter_tolerance)) {
-      it.cost = x_cost + fixed_cost; it.trust_region_radius = radius; it.gradient_max_norm = trace->back().gradient_max_norm;
-      trace->push_back(it);
-      termination = SBA_CONVERGENCE; break;
-    }
+    // (Minimize() returns from both tests before the iteration's row is appended to Summary::iterations)
+    if (step_norm <= o.parameter_tolerance * (x_norm + o.parameter_tolerance)) { termination = SBA_CONVERGENCE; break; }
     // FunctionToleranceReached
-    if (std::fabs(it.cost_change) <= o.function_tolerance * x_cost) {
-      it.cost = x_cost + fixed_cost; it.trust_region_radius = radius; it.gradient_max_norm = trace->back().gradient_max_norm;
-      trace->push_back(it);
-      termination = SBA_CONVERGENCE; break;
-    }
+    if (std::fabs(it.cost_change) <= o.function_tolerance * x_cost) { termination = SBA_CONVERGENCE; break; }
     const double relative_decrease = (x_cost - cand_cost) / model_cost_change;
     it.relative_decrease = relative_decrease;
     if (relative_decrease > o.min_relative_decrease) {

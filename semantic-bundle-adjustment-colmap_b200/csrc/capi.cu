@@ -104,6 +104,8 @@ int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t ap
   int rc = CheckHandle(h);
   if (rc) return rc;
   Problem* p = h->p;
+  CommScope scope(p);
+  if (!scope.ok) return SBA_ERR_COMM;
   cudaStream_t st = p->stream;
   const int n = p->n_obs, dc = p->dc;
   DevBuf<double> d_jq;
@@ -203,12 +205,15 @@ int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callb
   sba_solver_options o;
   if (opts) o = *opts; else sba_default_solver_options(&o);
   if (o.max_num_iterations < 0 || o.max_linear_solver_iterations < 0 || !(o.initial_trust_region_radius > 0.0) ||
-      !(o.loss_function_scale > 0.0) || o.loss_function_type < 0 || o.loss_function_type > SBA_LOSS_CAUCHY ||
+      !(o.loss_function_scale >= 0.0) || (o.loss_function_scale == 0.0 && o.loss_function_type != SBA_LOSS_TRIVIAL) ||
+      o.loss_function_type < 0 || o.loss_function_type > SBA_LOSS_CAUCHY ||
       o.linear_solver_type < SBA_SOLVER_AUTO || o.linear_solver_type > SBA_ITERATIVE_SCHUR) {
     // Solver::Options::IsValid / BundleAdjustmentOptions::Check (bundle_adjustment.cc:70-73, 303-304)
     SetError(SBA_ERR_INVALID_ARGUMENT, "invalid solver options");
     return SBA_ERR_INVALID_ARGUMENT;
   }
+  CommScope scope(h->p);
+  if (!scope.ok) return SBA_ERR_COMM;
   return SolveLM(h->p, &o, cb, user, summary);
 }
 
@@ -289,6 +294,8 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
   if (rc) return rc;
   Problem* p = h->p;
   if (!stage || repeat <= 0) { SetError(SBA_ERR_INVALID_ARGUMENT, "bad stage / repeat"); return SBA_ERR_INVALID_ARGUMENT; }
+  CommScope scope(p);
+  if (!scope.ok) return SBA_ERR_COMM;
   sba_solver_options o;
   sba_default_solver_options(&o);
   const std::string s(stage);
@@ -385,6 +392,8 @@ int sba_schur_product(sba_handle* h, int32_t use_blocks, const double* x, double
   Problem* p = h->p;
   if (n) *n = p->n_cdim;
   if (!x || !y || p->n_cdim == 0) return SBA_OK;
+  CommScope scope(p);
+  if (!scope.ok) return SBA_ERR_COMM;
   sba_solver_options o;
   sba_default_solver_options(&o);
   if ((rc = PrepareLinearSystem(p, o))) return rc;

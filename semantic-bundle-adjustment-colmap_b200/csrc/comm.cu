@@ -14,6 +14,9 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "solver.h"
 
 namespace sba {
@@ -139,6 +142,8 @@ class Comm {
  public:
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  ncclUniqueId id{};               // the group this communicator was created for (cache key, with the shape)
+  std::atomic_flag in_use = ATOMIC_FLAG_INIT;  // held by the one API call that is issuing collectives (CommAcquire)
   bool p2p = false;  // the exchange areas are mapped on every rank
   P2PView view{};
 };
@@ -221,15 +226,21 @@ int CommInit(Problem* p, int nranks, int rank, const void* id128) {
     return SBA_ERR_INVALID_ARGUMENT;
   }
   if (!g_nccl.Load()) { SetError(SBA_ERR_COMM, "libnccl.so.2 could not be loaded"); return SBA_ERR_COMM; }
-  // One communicator per process and shape, shared by every handle (creating a communicator costs
-  // far more than a solve); it lives until the process exits.
+  // One communicator per process and GROUP (unique id + shape), shared by every handle that names that group (creating a
+  // communicator costs far more than a solve); it lives until the process exits.  A new id is a new group: it gets a
+  // communicator and exchange areas of its own, never the mappings of an older group.
+  // All handles of a group share one exchange area and one epoch sequence, so their collectives must not interleave:
+  // the API calls that issue collectives take the communicator for their duration (CommAcquire) and a second handle
+  // trying to solve at the same time is refused with SBA_ERR_COMM instead of corrupting the sums.
   static std::vector<Comm*> cache;
-  for (Comm* c : cache)
-    if (c->nranks == nranks && c->rank == rank) { p->comm = c; return SBA_OK; }
+  static std::mutex cache_mu;
+  std::lock_guard<std::mutex> lk(cache_mu);
   ncclUniqueId id;
   std::memcpy(&id, id128, sizeof(id));
+  for (Comm* c : cache)
+    if (c->nranks == nranks && c->rank == rank && std::memcmp(&c->id, &id, sizeof(id)) == 0) { p->comm = c; return SBA_OK; }
   Comm* c = new Comm();
-  c->nranks = nranks; c->rank = rank;
+  c->nranks = nranks; c->rank = rank; c->id = id;
   const ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
   if (r != ncclSuccess) { delete c; return NcclFail("ncclCommInitRank", r); }
   SetupP2P(c);
@@ -239,6 +250,11 @@ int CommInit(Problem* p, int nranks, int rank, const void* id128) {
 }
 
 void CommDestroy(Problem* p) { p->comm = nullptr; }  // communicators are process-wide (see CommInit)
+
+// Exclusive use of the handle's communicator for one API call (no-op on a single GPU).  false: another handle of the
+// same group is inside a call that issues collectives.
+bool CommAcquire(Problem* p) { return !p->comm || !p->comm->in_use.test_and_set(std::memory_order_acquire); }
+void CommRelease(Problem* p) { if (p->comm) p->comm->in_use.clear(std::memory_order_release); }
 
 static int AllReduce(Problem* p, double* d_buf, size_t n, ncclRedOp_t op) {
   if (!p->comm || n == 0) return SBA_OK;

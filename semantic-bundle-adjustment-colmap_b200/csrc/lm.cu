@@ -267,11 +267,10 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
     num_consecutive_invalid = 0;
     it.step_norm = hs->step_norm;
     it.cost_change = hs->cost_change;
-    if (hs->converged) {  // parameter / function tolerance
-      it.cost = x_cost + fixed_cost;
-      it.trust_region_radius = radius;
-      it.gradient_max_norm = p->trace.back().gradient_max_norm;
-      p->trace.push_back(it);
+    if (hs->converged) {
+      // parameter / function tolerance: TrustRegionMinimizer::Minimize returns right here, BEFORE the next
+      // FinalizeIterationAndCheckIfMinimizerCanContinue would append this iteration's row -- Summary::iterations (and
+      // num_iterations) do not contain it
       termination = SBA_CONVERGENCE;
       break;
     }

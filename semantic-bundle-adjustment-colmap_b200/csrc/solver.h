@@ -313,5 +313,16 @@ int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, 
 int CommGetUniqueId(void* id128);
 int CommInit(Problem* p, int nranks, int rank, const void* id128);
 void CommDestroy(Problem* p);
+bool CommAcquire(Problem* p);   // one collective-issuing API call at a time per communicator
+void CommRelease(Problem* p);
+struct CommScope {              // RAII: ok == false -> the caller returns SBA_ERR_COMM
+  Problem* p; bool ok;
+  explicit CommScope(Problem* q) : p(q), ok(CommAcquire(q)) {
+    if (!ok) SetError(SBA_ERR_COMM, "the communicator is in use by another handle of the same group (one solve at a time per group)");
+  }
+  ~CommScope() { if (ok) CommRelease(p); }
+  CommScope(const CommScope&) = delete;
+  CommScope& operator=(const CommScope&) = delete;
+};
 
 }  // namespace sba

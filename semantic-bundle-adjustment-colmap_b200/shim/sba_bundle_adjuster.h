@@ -258,6 +258,8 @@ class BundleAdjusterT {
     const sba_problem_desc d = flat_.Desc();
     sba_handle* h = nullptr;
     Check(sba_create(&d, &h));
+    // the handle is released on every way out, including an exception thrown by a user callback or by ScatterBack
+    struct HandleGuard { sba_handle* h; ~HandleGuard() { sba_destroy(h); } } guard{h};
     CallbackState st{this, reconstruction, h};
     const bool have_cb = !so.callbacks.empty();
     const int rc = sba_solve(h, &o, have_cb ? &BundleAdjusterT::Trampoline : nullptr, &st, &summary_);
@@ -268,7 +270,6 @@ class BundleAdjusterT {
       summary_.iterations.resize(static_cast<size_t>(n));
       ScatterBack(reconstruction, h);
     }
-    sba_destroy(h);
     Check(rc);
     if (options_.print_summary) PrintSolverSummary(summary_);
     return true;
