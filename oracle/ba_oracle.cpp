@@ -286,9 +286,15 @@ void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_
   lin->r.assign((size_t)nr * p.n_obs, 0.0);
   lin->F.assign((size_t)p.n_obs * nr * dc, 0.0);
   lin->E.assign((size_t)p.n_obs * nr * 3, 0.0);
-  double cost = 0.0, fixed = 0.0;
-#pragma omp parallel for num_threads(num_threads) reduction(+ : cost, fixed) schedule(static)
+  // (sums are kept per thread and combined in thread order: an OpenMP reduction clause combines in arrival order, which
+  //  makes the last bits of the cost -- and through the trust-region radius the whole inexact-Newton trajectory --
+  //  differ from run to run)
+  const int nt = std::max(1, num_threads);
+  std::vector<double> cost_t(nt * 8, 0.0), fixed_t(nt * 8, 0.0);
+#pragma omp parallel for num_threads(nt) schedule(static)
   for (int64_t k = 0; k < p.n_obs; ++k) {
+    double& cost = cost_t[8 * omp_get_thread_num()];
+    double& fixed = fixed_t[8 * omp_get_thread_num()];
     const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
     const int m = p.model[c], P = NumParams(m);
     double r[3] = {0, 0, 0}, Jq[12], Jt[9], JX[9], Jk[36];
@@ -358,14 +364,18 @@ void Linearize(const BAProblem& p, int loss_type, double loss_scale, bool apply_
     }
     for (int row = 0; row < nr; ++row) lin->r[(size_t)nr * k + row] = r[row];
   }
+  double cost = 0.0, fixed = 0.0;
+  for (int t = 0; t < nt; ++t) { cost += cost_t[8 * t]; fixed += fixed_t[8 * t]; }
   lin->cost = cost; lin->fixed_cost = fixed;
 }
 
 double CostOnly(const BAProblem& p, int loss_type, double loss_scale, int num_threads) {
-  double cost = 0.0;
-#pragma omp parallel for num_threads(num_threads) reduction(+ : cost) schedule(static)
+  const int nt = std::max(1, num_threads);
+  std::vector<double> cost_t(nt * 8, 0.0);  // per thread, combined in thread order (see Linearize)
+#pragma omp parallel for num_threads(nt) schedule(static)
   for (int64_t k = 0; k < p.n_obs; ++k) {
     if (!p.obs_active[k]) continue;
+    double& cost = cost_t[8 * omp_get_thread_num()];
     const int i = p.obs_img[k], c = p.img_cam[i], pt = p.obs_pt[k];
     double r[3] = {0, 0, 0};
     EvalObsValue(p.model[c], &p.q[4 * i], &p.t[3 * i], &p.X[3 * pt],
@@ -374,6 +384,8 @@ double CostOnly(const BAProblem& p, int loss_type, double loss_scale, int num_th
     LossEval(loss_type, loss_scale, r[0] * r[0] + r[1] * r[1] + r[2] * r[2], rho);
     cost += 0.5 * rho[0];
   }
+  double cost = 0.0;
+  for (int t = 0; t < nt; ++t) cost += cost_t[8 * t];
   return cost;
 }
 
@@ -1045,10 +1057,12 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
       for (int j = 0; j < p.n_cdim; ++j) step_c[j] = -yc[j];
       for (size_t j = 0; j < yp.size(); ++j) step_p[j] = -yp[j];
       // model_cost_change = -(J step)'(r + J step / 2)
-      double acc = 0.0;
-#pragma omp parallel for num_threads(threads) reduction(+ : acc) schedule(static)
+      const int nt = std::max(1, threads);
+      std::vector<double> acc_t(nt * 8, 0.0);  // per thread, combined in thread order (see Linearize)
+#pragma omp parallel for num_threads(nt) schedule(static)
       for (int64_t k = 0; k < p.n_obs; ++k) {
         if (!p.obs_active[k]) continue;
+        double& acc = acc_t[8 * omp_get_thread_num()];
         int cols[24];
         const int n = p.ObsCols(k, cols);
         double m[3];
@@ -1062,6 +1076,8 @@ int Solve(BAProblem* pp, const sba_solver_options& o, sba_summary* sum,
         const double* r = OBS_R(lin, p, k);
         for (int row = 0; row < p.nr; ++row) acc += m[row] * (r[row] + m[row] / 2.0);
       }
+      double acc = 0.0;
+      for (int t = 0; t < nt; ++t) acc += acc_t[8 * t];
       model_cost_change = -acc;
       step_valid = model_cost_change > 0.0;
     }

@@ -136,6 +136,25 @@ struct BlockCache {
 BlockCache g_blocks;
 }  // namespace
 
+// SBA_POISON=1 (diagnostics): every block handed out is filled with 0xFF bytes (a NaN in every double, -1 in every
+// int) first, so that a kernel reading memory nobody wrote fails the parity tests loudly instead of depending on
+// what the previous owner left there.
+// SBA_POISON_FROM / SBA_POISON_TO restrict it to the allocations with ordinal in [from, to) (bisecting for the buffer a
+// result depends on); SBA_POISON_LOG=1 prints ordinal and size of every allocation.
+static cudaError_t Poison(void* ptr, size_t bytes) {
+  static const bool on = getenv("SBA_POISON") != nullptr;
+  if (!on) return cudaSuccess;
+  static const long from = getenv("SBA_POISON_FROM") ? atol(getenv("SBA_POISON_FROM")) : 0;
+  static const long to = getenv("SBA_POISON_TO") ? atol(getenv("SBA_POISON_TO")) : (1l << 60);
+  static const bool log = getenv("SBA_POISON_LOG") != nullptr;
+  static std::atomic<long> ordinal{0};
+  const long k = ordinal.fetch_add(1);
+  if (log) fprintf(stderr, "[sba poison] alloc %ld: %zu bytes%s\n", k, bytes, (k >= from && k < to) ? " (poisoned)" : "");
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) e = cudaMemset(ptr, (k >= from && k < to) ? 0xFF : 0x00, bytes);
+  return e == cudaSuccess ? cudaDeviceSynchronize() : e;
+}
+
 cudaError_t CachedAlloc(void** ptr, size_t bytes, size_t* cap) {
   int dev = 0;
   cudaGetDevice(&dev);
@@ -149,7 +168,7 @@ cudaError_t CachedAlloc(void** ptr, size_t bytes, size_t* cap) {
       *ptr = it->second; *cap = it->first;
       g_blocks.cached_bytes[dev] -= it->first;
       fb.erase(it);
-      return cudaSuccess;
+      return Poison(*ptr, *cap);
     }
   }
   *cap = bytes;
@@ -160,7 +179,8 @@ cudaError_t CachedAlloc(void** ptr, size_t bytes, size_t* cap) {
     e = cudaMallocAsync(ptr, bytes, AllocStream());
   }
   // the allocation stream carries no kernels, so this returns at once; it makes the block usable from any stream
-  return e == cudaSuccess ? cudaStreamSynchronize(AllocStream()) : e;
+  if (e == cudaSuccess) e = cudaStreamSynchronize(AllocStream());
+  return e == cudaSuccess ? Poison(*ptr, bytes) : e;
 }
 
 // Contract (DevBuf): the stream that used the block has been synchronised, so any stream may reuse it at once.
