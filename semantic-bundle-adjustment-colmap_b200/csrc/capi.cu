@@ -334,7 +334,7 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
     run = [&]() { return BackSubstitute(p); };
     bytes = n_obs * (64 + 16 * dc + 8) + (int64_t)p->n_pvar * (48 + 24 + 24);
   } else if (s == "schur_dense") {
-    run = [&]() { return BuildDenseSchur(p); };
+    run = [&]() { return BuildDenseSchur(p, true); };  // as the LM step runs it: the reduced rhs rides on the same pass
     bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 96 + 8 * (int64_t)p->n_cdim * p->n_cdim;
   } else if (s == "schur_jacobi") {
     run = [&]() { return BuildSchurJacobi(p); };
@@ -346,7 +346,7 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
     if (!p->bsr.enabled) { SetError(SBA_ERR_INVALID_ARGUMENT, "the block-sparse Schur complement is not in use for this problem"); return SBA_ERR_INVALID_ARGUMENT; }
     const int64_t ne = dc * dc;
     if (s == "schur_blocks") {
-      run = [&]() { return BuildExplicitSchur(p); };
+      run = [&]() { return BuildExplicitSchur(p, true); };  // as the LM step runs it: the reduced rhs rides on the same pass
       bytes = n_obs * (16 * (dc + 3) + 16) + (int64_t)p->n_pvar * 48 + 8 * p->bsr.n_blocks * ne;
     } else {
       prep = [&]() { if (blocks_built) return (int)SBA_OK; blocks_built = true; return BuildExplicitSchur(p); };

@@ -45,6 +45,16 @@ static int CamReduce(Problem* p, int mode, const double2* v, double* out, const 
   return SBA_OK;
 }
 
+// chunk partials [n_chunks][dc] (written by a kernel of another file) -> compact camera-space vector `out`
+int FinalizeCameraVector(Problem* p, const double* d_partial, double* d_out) {
+  if (p->n_cdim == 0) return SBA_OK;
+  const int n = p->n_img * 6 + p->n_cam * 12;
+  cam_finalize_kernel<<<DivUp(n, 128), 128, 0, p->stream>>>(p->Struct(), p->Chunks(), d_partial, d_out, nullptr, nullptr);
+  p->launches++;
+  SBA_CUDA(cudaGetLastError());
+  return SBA_OK;
+}
+
 int ColumnNorms(Problem* p, double* d_nc, double* d_np, bool camera_part) {
   int rc = camera_part ? CamReduce(p, 2, nullptr, d_nc, nullptr, nullptr) : SBA_OK;
   if (rc) return rc;
@@ -154,11 +164,11 @@ int PointBlocks(Problem* p, bool grad_only) {
     if (p->nr == 3)
       point_blocks_kernel<3><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
                                                                         grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
-                                                                        p->d_gp.p, p->d_scalars.p);
+                                                                        p->d_Cfac.p, p->d_gp.p, p->d_scalars.p);
     else
       point_blocks_kernel<2><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
                                                                         grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
-                                                                        p->d_gp.p, p->d_scalars.p);
+                                                                        p->d_Cfac.p, p->d_gp.p, p->d_scalars.p);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());

@@ -186,6 +186,7 @@ template <int NR>
 __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileView T, const D4* __restrict__ ER,
                                                            const D4* __restrict__ ES,
                                                            const double* __restrict__ Dp, double* __restrict__ Cinv,
+                                                           double* __restrict__ Cfac,
                                                            double* __restrict__ gp, DeviceScalars* sc) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
@@ -230,14 +231,18 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
       if (Dp) {
         const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
         const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
-        double inv[6];
-        if (!InvertSym3(c, inv)) {
+        double inv[6], fac[6];
+        if (!InvertSym3(c, inv, fac)) {
           sc->solver_failed = 1;
 #pragma unroll
-          for (int a = 0; a < 6; ++a) inv[a] = 0.0;
+          for (int a = 0; a < 6; ++a) { inv[a] = 0.0; fac[a] = 0.0; }
         }
 #pragma unroll
         for (int a = 0; a < 6; ++a) Cinv[6 * (size_t)po + a] = inv[a];
+        if (Cfac) {
+#pragma unroll
+          for (int a = 0; a < 6; ++a) Cfac[6 * (size_t)po + a] = fac[a];
+        }
       }
       gp[3 * (size_t)po] = v[6]; gp[3 * (size_t)po + 1] = v[7]; gp[3 * (size_t)po + 2] = v[8];
     }

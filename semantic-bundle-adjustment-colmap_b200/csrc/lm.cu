@@ -206,14 +206,18 @@ int SolveLM(Problem* p, const sba_solver_options* op, sba_iteration_callback cb,
       if ((r = PrepareLMDiagonal(p, o))) return r;
       if ((r = PointBlocks(p, false))) return r;
       if (p->n_cdim > 0) {
-        if ((r = ReducedRhs(p, multi))) return r;  // multi-GPU: summed across ranks by the Schur build's all-reduce
+        if (iterative && (r = DecideBlockSchur(p))) return r;  // once per problem: explicit block-sparse S or implicit products
+        // the reduced right-hand side: formed by the explicit Schur build's own pass over the observations where that pass
+        // reads everything it needs (dc <= 8), else by a pass of its own.  Multi-GPU: summed across ranks by the Schur
+        // build's all-reduce either way.
+        const bool fused_rhs = SchurBuildsRhs(p) && (!iterative || p->bsr.enabled);
+        if (!fused_rhs && (r = ReducedRhs(p, multi))) return r;
         if (iterative) {
-          if ((r = DecideBlockSchur(p))) return r;  // once per problem: explicit block-sparse S or implicit products
-          if ((r = p->bsr.enabled ? BuildExplicitSchur(p) : BuildSchurJacobi(p))) return r;
+          if ((r = p->bsr.enabled ? BuildExplicitSchur(p, fused_rhs) : BuildSchurJacobi(p))) return r;
           if (marks) tm.Mark(1, st);
           if ((r = SolvePCG(p, o, &lin_iters))) return r;
         } else {
-          if ((r = BuildDenseSchur(p))) return r;
+          if ((r = BuildDenseSchur(p, fused_rhs))) return r;
           if (marks) tm.Mark(1, st);
           if ((r = CholeskySolve(p))) return r;
           lin_iters = 1;

@@ -243,21 +243,30 @@ template <int DC> struct ObsLane {
   static constexpr size_t kSmem = (size_t)(NT * 256 + NT * 8) * 8;
 };
 
-// W_a, H_a and the diagonal contribution F_a^T F_a - H_a W_a^T of every observation of one image chunk.
+// DC <= 8.  ONE row per observation instead of two: with C_p^{-1} = M^T M (M = L^{-1}, stored by point_blocks_kernel)
+//   U_a = (F_a^T E_a) M^T       (DC x 3)
+// gives H_a W_b^T = U_a U_b^T, so the pair pass gathers two rows of ONE array (half the bytes written here, half the
+// footprint the pair gathers have to find in L2) and the diagonal contribution is F_a^T F_a - U_a U_a^T.
 // partial[ch][e], e over the lower triangle (ja >= jb, e = ja (ja + 1) / 2 + jb).
-// A lane owns an observation and writes its own two rows (image-major, sector-aligned, 256-bit stores); only the current
-// H row is kept in registers, the diagonal entries of slot ja being formed as soon as H_ja exists.
+// A lane owns an observation and writes its own row (image-major, sector-aligned, 256-bit stores).
+// rhs_partial != null: the same pass also forms this chunk's part of the reduced right-hand side
+//   F_a^T (r_a - E_a C_p^{-1} g_p)
+// -- r rides in the ER record the lane loads anyway, g_p is one more 24 B gather -- which replaces rhs_e_kernel and a
+// cam_reduce pass over F (0.27 ms per LM iteration at C4).
 template <int DC, int NR>
-__global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
-                                                             const D4* __restrict__ F, const D4* __restrict__ ES,
-                                                             const D4* __restrict__ FS, const double* __restrict__ Cinv,
-                                                             double* __restrict__ W, double* __restrict__ H,
-                                                             double* __restrict__ partial) {
+__global__ void __launch_bounds__(256, 2) schur_obs_u_kernel(StructView S, ChunkView C, const D4* __restrict__ ER,
+                                                          const D4* __restrict__ F, const D4* __restrict__ ES,
+                                                          const D4* __restrict__ FS, const double* __restrict__ Cfac,
+                                                          const double* __restrict__ gp, double* __restrict__ U,
+                                                          double* __restrict__ partial, double* __restrict__ rhs_partial) {
   constexpr int NT = DC * (DC + 1) / 2, DH = DC / 2, RW = WRow(DC);
   extern __shared__ __align__(16) double sm[];  // [NT][256] blocks + [NT][8] partials
   double* part = sm + NT * 256;
   const int ch = blockIdx.x, t = threadIdx.x;
   const int s0 = C.chunk_start[ch], n = C.chunk_start[ch + 1] - s0;
+  double rhs[DC];
+#pragma unroll
+  for (int j = 0; j < DC; ++j) rhs[j] = 0.0;
   if (t < n) {
     const int a = C.cam_order[s0 + t];
     double2 f[DC];
@@ -266,10 +275,9 @@ __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, Ch
       const D4 u = Ld256(F + FUnit(a, jj, DH));
       f[2 * jj] = make_double2(u.x, u.y); f[2 * jj + 1] = make_double2(u.z, u.w);
     }
-    const D4 ea = Ld256(ER + EUnit(a, 0));
-    const double2 eb = reinterpret_cast<const double2*>(ER + EUnit(a, 1))[0];
+    const D4 ea = Ld256(ER + EUnit(a, 0)), eb = Ld256(ER + EUnit(a, 1));
     const double E[6] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y};
-    double fs[NR == 3 ? DC : 1], Es[3] = {0.0, 0.0, 0.0};  // third row (X1): F_s (DC), E_s (3)
+    double fs[NR == 3 ? DC : 1], Es[3] = {0.0, 0.0, 0.0}, rs = 0.0;  // third row (X1): F_s (DC), E_s (3), r_s
     if constexpr (NR == 3) {
       constexpr int NQ = FSUnits(DC);
 #pragma unroll
@@ -281,47 +289,59 @@ __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, Ch
         if (4 * q + 3 < DC) fs[4 * q + 3 < DC ? 4 * q + 3 : 0] = u.w;
       }
       const D4 es = Ld256(ES + a);
-      Es[0] = es.x; Es[1] = es.y; Es[2] = es.z;
+      Es[0] = es.x; Es[1] = es.y; Es[2] = es.z; rs = es.w;
     }
     const int po = S.p_off[S.obs_pt[a]];
-    double ci[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    double m[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // m00 m10 m11 m20 m21 m22
     if (po >= 0) {
-      const double2* cp = reinterpret_cast<const double2*>(Cinv + 6 * (size_t)po);
+      const double2* cp = reinterpret_cast<const double2*>(Cfac + 6 * (size_t)po);
       const double2 c0 = cp[0], c1 = cp[1], c2 = cp[2];
-      ci[0] = c0.x; ci[1] = c0.y; ci[2] = c1.x; ci[3] = c1.y; ci[4] = c2.x; ci[5] = c2.y;
+      m[0] = c0.x; m[1] = c0.y; m[2] = c1.x; m[3] = c1.y; m[4] = c2.x; m[5] = c2.y;
     }
-    D4* wrow = reinterpret_cast<D4*>(W + (size_t)(s0 + t) * RW);
-    D4* hrow = reinterpret_cast<D4*>(H + (size_t)(s0 + t) * RW);
-    double w[RW], h[RW];
+    if (rhs_partial) {
+      double e0 = eb.z, e1 = eb.w, e2 = rs;
+      if (po >= 0) {
+        const double g0 = gp[3 * (size_t)po], g1 = gp[3 * (size_t)po + 1], g2 = gp[3 * (size_t)po + 2];
+        const double v0 = m[0] * g0, v1 = m[1] * g0 + m[2] * g1, v2 = m[3] * g0 + m[4] * g1 + m[5] * g2;  // M g
+        const double w0 = m[0] * v0 + m[1] * v1 + m[3] * v2, w1 = m[2] * v1 + m[4] * v2, w2 = m[5] * v2;  // M^T M g
+        e0 -= E[0] * w0 + E[1] * w1 + E[2] * w2;
+        e1 -= E[3] * w0 + E[4] * w1 + E[5] * w2;
+        if constexpr (NR == 3) e2 -= Es[0] * w0 + Es[1] * w1 + Es[2] * w2;
+      }
 #pragma unroll
-    for (int q = DC * 3; q < RW; ++q) { w[q] = 0.0; h[q] = 0.0; }
+      for (int j = 0; j < DC; ++j) {
+        rhs[j] = f[j].x * e0 + f[j].y * e1;
+        if constexpr (NR == 3) rhs[j] += fs[j] * e2;
+      }
+    }
+    D4* urow = reinterpret_cast<D4*>(U + (size_t)(s0 + t) * RW);
+    double u[RW];
+#pragma unroll
+    for (int q = DC * 3; q < RW; ++q) u[q] = 0.0;
 #pragma unroll
     for (int ja = 0; ja < DC; ++ja) {
+      double w[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        w[3 * ja + c] = f[ja].x * E[c] + f[ja].y * E[3 + c];
-        if constexpr (NR == 3) w[3 * ja + c] += fs[ja] * Es[c];
+        w[c] = f[ja].x * E[c] + f[ja].y * E[3 + c];
+        if constexpr (NR == 3) w[c] += fs[ja] * Es[c];
       }
-      Sym3Mul(ci, &w[3 * ja], &h[3 * ja]);
+      u[3 * ja] = w[0] * m[0];
+      u[3 * ja + 1] = w[0] * m[1] + w[1] * m[2];
+      u[3 * ja + 2] = w[0] * m[3] + w[1] * m[4] + w[2] * m[5];
       // the entries of slot ja are final: they go straight to the reduction area, not through registers
 #pragma unroll
       for (int jb = 0; jb <= ja; ++jb)
         sm[(ja * (ja + 1) / 2 + jb) * 256 + t] = (f[ja].x * f[jb].x + f[ja].y * f[jb].y + (NR == 3 ? fs[NR == 3 ? ja : 0] * fs[NR == 3 ? jb : 0] : 0.0)) -
-                                                 (h[3 * ja] * w[3 * jb] + h[3 * ja + 1] * w[3 * jb + 1] + h[3 * ja + 2] * w[3 * jb + 2]);
-      // 32-byte units of the two rows leave as soon as they are complete (H is not needed again)
+                                                 (u[3 * ja] * u[3 * jb] + u[3 * ja + 1] * u[3 * jb + 1] + u[3 * ja + 2] * u[3 * jb + 2]);
+      // 32-byte units of the row leave as soon as they are complete
 #pragma unroll
       for (int q = 0; q < RW / 4; ++q)
-        if (4 * q + 3 < 3 * (ja + 1) && 4 * q + 3 >= 3 * ja) {
-          St256(wrow + q, D4{w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]});
-          St256(hrow + q, D4{h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]});
-        }
+        if (4 * q + 3 < 3 * (ja + 1) && 4 * q + 3 >= 3 * ja) St256(urow + q, D4{u[4 * q], u[4 * q + 1], u[4 * q + 2], u[4 * q + 3]});
     }
 #pragma unroll
     for (int q = 0; q < RW / 4; ++q)
-      if (4 * q + 3 >= 3 * DC) {  // the unit(s) that hold the padding
-        St256(wrow + q, D4{w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]});
-        St256(hrow + q, D4{h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]});
-      }
+      if (4 * q + 3 >= 3 * DC) St256(urow + q, D4{u[4 * q], u[4 * q + 1], u[4 * q + 2], u[4 * q + 3]});  // the unit(s) that hold the padding
   } else {
 #pragma unroll
     for (int e = 0; e < NT; ++e) sm[e * 256 + t] = 0.0;
@@ -342,6 +362,25 @@ __global__ void __launch_bounds__(256, 2) schur_obs_lane_kernel(StructView S, Ch
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc += part[t * 8 + i];
     partial[(size_t)ch * NT + t] = acc;
+  }
+  if (rhs_partial) {  // fixed tree: warp shuffles, then the eight warp sums in order (as cam_reduce_kernel)
+    __syncthreads();
+    double* rsm = sm;  // [8][DC]
+    const int lane = t & 31, w = t >> 5;
+#pragma unroll
+    for (int j = 0; j < DC; ++j) {
+      double a = rhs[j];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+      if (lane == 0) rsm[w * DC + j] = a;
+    }
+    __syncthreads();
+    if (t < DC) {
+      double a = 0.0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a += rsm[i * DC + t];
+      rhs_partial[(size_t)ch * DC + t] = a;
+    }
   }
 }
 
@@ -371,84 +410,50 @@ __global__ void __launch_bounds__(64) schur_diag_finalize_tri_kernel(StructView 
   }
 }
 
-// One warp per segment (<= 128 pairs of one key).  G lanes share a pair (G = 1: the lane holds the whole
-// DC x DC block; G = 2: half of its rows), so a lane carries RPL x DC accumulators over its <= 4 pairs.
-// The H_a / W_b rows of the 32 / G pairs of one trip are gathered by the whole warp with 16-byte cp.async
-// (consecutive lanes on consecutive chunks of a row: ~5 cache lines per instruction instead of 32), then every
-// lane reads its own two rows from shared memory with conflict-free 128-bit loads.
-template <int DC> struct PairLane {
-  static constexpr int G = DC > 6 ? 2 : 1, RPL = DC / G, PPI = 32 / G, NE = DC * DC, LD = PPI + 1;
-  static constexpr int CH = DC * 3 / 2, RU = (CH & 1) ? CH : CH + 1;
-  static constexpr int kStageD = 2 * PPI * RU * 2, kRedD = NE * LD;        // doubles
-  static constexpr int kWarpD = kStageD > kRedD ? kStageD : kRedD;
-};
-
-__device__ __forceinline__ void CpAsync16(void* smem_dst, const void* gsrc) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+// fp64 tensor-core MMA (DMMA): D(8x8) += A(8x4, row) * B(4x8, col)
+__device__ __forceinline__ void Dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
 }
 
+// One warp per segment (<= 128 pairs of one key): partial[seg] = - sum_pairs U_a U_b^T, one DMMA per pair.
+// U_a (DC x 3, DC <= 8) is the A operand of an m8n8k4 product as it lies in memory: lane l holds A[l / 4][l % 4] =
+// U_a[slot l / 4][coordinate l % 4] (the fourth coordinate and slots >= DC are zero), and the B operand B[k][n] =
+// U_b[slot n][coordinate k] sits at the SAME offset of row b -- so a pair is two 192-byte row reads (consecutive lanes
+// on consecutive doubles: whole sectors, no staging through shared memory) and one tensor-core instruction; the 8 x 8
+// accumulator stays in two registers per lane for the whole segment.  The pair ids are read ahead in blocks of 32
+// (one coalesced load, broadcast by shuffle), so the row loads of several pairs are in flight together.
 template <int DC>
-__global__ void __launch_bounds__(128, 4) schur_pair_lane_kernel(int n_seg, const int* __restrict__ seg_ptr,
-                                                              const unsigned long long* __restrict__ ab,
-                                                              const double* __restrict__ W, const double* __restrict__ H,
-                                                              double* __restrict__ partial) {
-  using P = PairLane<DC>;
-  constexpr int G = P::G, RPL = P::RPL, PPI = P::PPI, NE = P::NE, LD = P::LD, CH = P::CH, RU = P::RU;
-  __shared__ __align__(16) double smem[4][P::kWarpD];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int seg = blockIdx.x * 4 + warp;
-  if (seg >= n_seg) return;  // warps are independent (only __syncwarp below)
-  const int slot = lane / G, rg = lane % G;
+__global__ void __launch_bounds__(128) schur_pair_mma_kernel(int n_seg, const int* __restrict__ seg_ptr,
+                                                             const unsigned long long* __restrict__ ab,
+                                                             const double* __restrict__ U, double* __restrict__ partial) {
+  constexpr int RW = WRow(DC);
+  const int seg = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (seg >= n_seg) return;  // warps are independent
+  const int slot = lane >> 2, k = lane & 3;
+  const bool live = slot < DC && k < 3;
+  const int off = live ? slot * 3 + k : 0;
   const int t0 = seg_ptr[seg], np = seg_ptr[seg + 1] - t0;
-  double* my = smem[warp];
-  double2* st = reinterpret_cast<double2*>(my);  // [row 0: H_a | row 1: W_b][PPI][RU]
-  double acc[RPL][DC];
-#pragma unroll
-  for (int r = 0; r < RPL; ++r)
-#pragma unroll
-    for (int c = 0; c < DC; ++c) acc[r][c] = 0.0;
-  unsigned long long nxt = slot < np ? ab[t0 + slot] : ~0ull;
-  for (int base = 0; base < np; base += PPI) {
-    const unsigned long long cur = nxt;
-    nxt = (base + PPI + slot < np) ? ab[t0 + base + PPI + slot] : ~0ull;  // next trip's pair ids in flight
-    const int a = (int)(cur >> 32), b = (int)(cur & 0xffffffffull);      // -1 / -1 past the end of the segment
-#pragma unroll
-    for (int i = 0; i < 2 * PPI * CH / 32; ++i) {
-      const int k = lane + 32 * i;
-      const int row = k / (PPI * CH), rem = k - row * (PPI * CH), o = rem / CH, c = rem - o * CH;
-      const int src = __shfl_sync(0xffffffffu, row ? b : a, o * G);
-      if (src >= 0) CpAsync16(st + (size_t)(row * PPI + o) * RU + c, (row ? W : H) + (size_t)src * WRow(DC) + 2 * c);
+  double c0 = 0.0, c1 = 0.0;
+  for (int base = 0; base < np; base += 32) {
+    const int m = min(32, np - base);
+    const unsigned long long mine = lane < m ? ab[t0 + base + lane] : 0ull;
+    const int my_a = (int)(mine >> 32), my_b = (int)(mine & 0xffffffffull);
+#pragma unroll 8
+    for (int t = 0; t < m; ++t) {
+      const int a = __shfl_sync(0xffffffffu, my_a, t), b = __shfl_sync(0xffffffffu, my_b, t);
+      const double av = live ? __ldg(U + (size_t)a * RW + off) : 0.0;
+      const double bv = live ? __ldg(U + (size_t)b * RW + off) : 0.0;
+      Dmma884(c0, c1, av, bv);
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
-    if (a >= 0) {
-      const double2* hp = st + (size_t)slot * RU + rg * (RPL * 3 / 2);
-      const double2* wp = st + (size_t)(PPI + slot) * RU;
-      double h[RPL * 3], w[DC * 3];
-#pragma unroll
-      for (int q = 0; q < RPL * 3 / 2; ++q) { const double2 x = hp[q]; h[2 * q] = x.x; h[2 * q + 1] = x.y; }
-#pragma unroll
-      for (int q = 0; q < DC * 3 / 2; ++q) { const double2 x = wp[q]; w[2 * q] = x.x; w[2 * q + 1] = x.y; }
-#pragma unroll
-      for (int r = 0; r < RPL; ++r)
-#pragma unroll
-        for (int c = 0; c < DC; ++c)
-          acc[r][c] -= h[3 * r] * w[3 * c] + h[3 * r + 1] * w[3 * c + 1] + h[3 * r + 2] * w[3 * c + 2];
-    }
-    __syncwarp();  // the staging rows are overwritten by the next trip (and by the reduction)
   }
-#pragma unroll
-  for (int r = 0; r < RPL; ++r)
-#pragma unroll
-    for (int c = 0; c < DC; ++c) my[((rg * RPL + r) * DC + c) * LD + slot] = acc[r][c];
-  __syncwarp();
-  for (int e = lane; e < NE; e += 32) {
-    double s = 0.0;
-#pragma unroll
-    for (int j = 0; j < PPI; ++j) s += my[e * LD + j];
-    partial[(size_t)seg * NE + e] = s;
+  // accumulator layout: lane holds C[l / 4][2 (l % 4)], C[l / 4][2 (l % 4) + 1]
+  const int row = lane >> 2, col = 2 * (lane & 3);
+  if (row < DC) {
+    double* out = partial + (size_t)seg * DC * DC + row * DC;
+    if (col < DC) out[col] = -c0;
+    if (col + 1 < DC) out[col + 1] = -c1;
   }
 }
 
@@ -512,23 +517,24 @@ static int EnsureBlockStorage(Problem* p) {
   return SBA_OK;
 }
 
-// W/H pass + diagonal chunks + pair segments into `sink`
+// U pass (+ rhs) + diagonal chunks + pair segments into `sink`
 template <int DC, int NR>
-static cudaError_t AccumulateLane(Problem* p, const PairList& L, const Sink& sink) {
+static cudaError_t AccumulateLane(Problem* p, const PairList& L, const Sink& sink, bool with_rhs) {
   constexpr size_t smem = ObsLane<DC>::kSmem;
   static bool attr_set[64] = {};
   if (!attr_set[p->device & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(schur_obs_lane_kernel<DC, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(schur_obs_u_kernel<DC, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set[p->device & 63] = true;
   }
   cudaStream_t st = p->stream;
-  schur_obs_lane_kernel<DC, NR><<<p->n_chunks, 256, smem, st>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p,
-                                                                p->d_Cinv.p, p->d_W.p, p->d_H.p, p->d_chunk_block.p);
+  schur_obs_u_kernel<DC, NR><<<p->n_chunks, 256, smem, st>>>(p->Struct(), p->Chunks(), p->d_ER.p, p->d_F.p, p->d_ES.p, p->d_FS.p,
+                                                             p->d_Cfac.p, p->d_gp.p, p->d_W.p, p->d_chunk_block.p,
+                                                             with_rhs ? p->d_chunk_partial.p : nullptr);
   schur_diag_finalize_tri_kernel<DC><<<p->n_img, 64, 0, st>>>(p->Struct(), p->Chunks(), p->d_chunk_block.p, sink);
   p->launches += 2;
   if (L.n_seg > 0) {
-    schur_pair_lane_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.ab.p, p->d_W.p, p->d_H.p, L.partial.p);
+    schur_pair_mma_kernel<DC><<<DivUp(L.n_seg, 4), 128, 0, st>>>(L.n_seg, L.seg_ptr.p, L.ab.p, p->d_W.p, L.partial.p);
     schur_pair_emit_kernel<DC><<<DivUp(L.n_keys, 4), 128, 0, st>>>(p->Struct(), L.n_keys, L.key_seg_ptr.p, L.key_gi.p,
                                                                   L.key_gj.p, L.partial.p, sink);
     p->launches += 2;
@@ -536,18 +542,34 @@ static cudaError_t AccumulateLane(Problem* p, const PairList& L, const Sink& sin
   return cudaGetLastError();
 }
 
-static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
+bool SchurBuildsRhs(const Problem* p) { return p->dc <= 8 && p->n_obs_global > 0; }
+
+static int Accumulate(Problem* p, const PairList& L, const Sink& sink, bool with_rhs = false) {
   const int dc = p->dc;
   cudaStream_t st = p->stream;
-  if (p->n_obs == 0) return SBA_OK;
-  SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * WRow(dc))); SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * WRow(dc)));
+  with_rhs = with_rhs && SchurBuildsRhs(p);
+  p->rhs_from_schur = false;
+  if (p->n_obs == 0) {
+    if (with_rhs && p->n_cdim > 0) {  // an empty shard contributes a zero right-hand side
+      SBA_CUDA(cudaMemsetAsync(p->d_rhs.p, 0, (size_t)p->n_cdim * sizeof(double), st));
+      p->rhs_from_schur = true;
+    }
+    return SBA_OK;
+  }
+  SBA_CUDA(p->d_W.Alloc((size_t)p->n_obs * WRow(dc)));
+  if (dc > 8) SBA_CUDA(p->d_H.Alloc((size_t)p->n_obs * WRow(dc)));
   SBA_CUDA(p->d_chunk_block.Alloc((size_t)std::max(1, p->n_chunks) * dc * dc));
   const bool r3 = p->nr == 3;
   if (dc == 6 || dc == 8) {
     cudaError_t e;
-    if (dc == 6) e = r3 ? AccumulateLane<6, 3>(p, L, sink) : AccumulateLane<6, 2>(p, L, sink);
-    else e = r3 ? AccumulateLane<8, 3>(p, L, sink) : AccumulateLane<8, 2>(p, L, sink);
+    if (dc == 6) e = r3 ? AccumulateLane<6, 3>(p, L, sink, with_rhs) : AccumulateLane<6, 2>(p, L, sink, with_rhs);
+    else e = r3 ? AccumulateLane<8, 3>(p, L, sink, with_rhs) : AccumulateLane<8, 2>(p, L, sink, with_rhs);
     SBA_CUDA(e);
+    if (with_rhs) {
+      const int rc = FinalizeCameraVector(p, p->d_chunk_partial.p, p->d_rhs.p);
+      if (rc) return rc;
+      p->rhs_from_schur = true;
+    }
     return SBA_OK;
   }
 #define CALL(DC)                                                                                                          \
@@ -579,7 +601,7 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink) {
   return SBA_OK;
 }
 
-int BuildDenseSchur(Problem* p) {
+int BuildDenseSchur(Problem* p, bool with_rhs) {
   int rc = BuildPairLists(p, true);
   if (rc) return rc;
   const size_t n = p->n_cdim;
@@ -588,8 +610,9 @@ int BuildDenseSchur(Problem* p) {
   Sink sink;
   std::memset(&sink, 0, sizeof(sink));
   sink.kind = 0; sink.S = p->d_S.p; sink.n = (int)n; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
-  rc = Accumulate(p, p->pairs_dense, sink);
+  rc = Accumulate(p, p->pairs_dense, sink, with_rhs);
   if (rc) return rc;
+  if (p->rhs_from_schur) p->rhs_unreduced = p->comm != nullptr;
   rc = AllReduceSumWithRhs(p, p->d_S.p, n * n);  // the row behind S carries the reduced right-hand side along
   if (rc) return rc;
   p->chol_add_diag = (int)n <= kCholSmallMax;  // the small-system Cholesky adds D^2 while loading its diagonal tiles
@@ -650,7 +673,7 @@ __global__ void __launch_bounds__(128) bsr_precond_slots_kernel(StructView S, co
 }
 
 // Block-sparse S (bsr.cu) and the SCHUR_JACOBI preconditioner read off its diagonal blocks.
-int BuildExplicitSchur(Problem* p) {
+int BuildExplicitSchur(Problem* p, bool with_rhs) {
   BlockSchur& B = p->bsr;
   int rc = EnsureBlockStorage(p);
   if (rc) return rc;
@@ -659,8 +682,9 @@ int BuildExplicitSchur(Problem* p) {
   Sink sink;
   std::memset(&sink, 0, sizeof(sink));
   sink.kind = 2; sink.B = B.blocks.p; sink.n_img = p->n_img; sink.key_block = p->comm ? B.key_block.p : nullptr;
-  rc = Accumulate(p, p->pairs_dense, sink);
+  rc = Accumulate(p, p->pairs_dense, sink, with_rhs);
   if (rc) return rc;
+  if (p->rhs_from_schur) p->rhs_unreduced = p->comm != nullptr;
   rc = AllReduceSumWithRhs(p, B.blocks.p, (size_t)B.n_blocks * ne);
   if (rc) return rc;
   if (p->n_blk == 0) return SBA_OK;

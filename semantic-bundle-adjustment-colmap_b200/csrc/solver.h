@@ -201,6 +201,8 @@ struct Problem {
   DevBuf<double> d_diag_c, d_diag_p;        // clamped column square norms
   DevBuf<double> d_Dc, d_Dp;                // LM diagonal
   DevBuf<double> d_Cinv, d_gp;              // [n_pvar*6] sym inverse, [n_pvar*3]
+  DevBuf<double> d_Cfac;                    // [n_pvar*6] M = L^{-1} (lower) with C_p^{-1} = M^T M: U_a = (F_a^T E_a) M^T (schur.cu)
+  bool rhs_from_schur = false;              // the explicit Schur build of this iteration also leaves the reduced rhs in d_rhs
   DevBuf<double> d_chunk_partial;           // [n_chunks*dc] (or dc*dc for block sums)
   DevBuf<double> d_g2;                      // [n_obs*2] per-observation 2-vector scratch
   DevBuf<double> d_rhs, d_yc, d_yp, d_step_c, d_grad_c, d_grad_p, d_tmp_c;
@@ -278,6 +280,7 @@ int AllReduceMax(Problem* p, double* d_buf, size_t n);
 int InitJacobiScale(Problem* p);
 int PrepareLMDiagonal(Problem* p, const sba_solver_options& o);
 int PointBlocks(Problem* p, bool grad_only);
+int FinalizeCameraVector(Problem* p, const double* d_partial, double* d_out);
 int ReducedRhs(Problem* p, bool defer_allreduce = false);  // deferred: see Problem::rhs_unreduced, AllReduceSumWithRhs
 int SchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip = nullptr);  // *skip != 0: the big kernels return at once
 int BackSubstitute(Problem* p, bool defer_allreduce = false);
@@ -293,9 +296,13 @@ int BuildPairLists(Problem* p, bool dense);
 // pairs per segment: the lane-per-pair kernels (dc <= 8) amortise one reduction over 4 pairs per lane
 inline int PairSegmentSize(int dc) { return dc <= 8 ? 128 : 32; }
 // schur.cu
-int BuildDenseSchur(Problem* p);
+// with_rhs: the build's pass over the observations also forms the reduced right-hand side F^T (r - E C^{-1} g) into d_rhs
+// (dc <= 8: the lane kernels read everything it needs anyway); SchurBuildsRhs tells whether it will.  Otherwise the
+// caller runs ReducedRhs first.
+bool SchurBuildsRhs(const Problem* p);
+int BuildDenseSchur(Problem* p, bool with_rhs = false);
 int BuildSchurJacobi(Problem* p);
-int BuildExplicitSchur(Problem* p);   // iterative solver: block-sparse S + its SCHUR_JACOBI blocks (when bsr.enabled)
+int BuildExplicitSchur(Problem* p, bool with_rhs = false);   // iterative solver: block-sparse S + its SCHUR_JACOBI blocks (when bsr.enabled)
 // bsr.cu
 int DecideBlockSchur(Problem* p);     // builds the pair lists and the block structure; sets bsr.enabled
 int BlockSchurMatVec(Problem* p, const double* d_x, double* d_y, const int* skip);

@@ -61,7 +61,9 @@ __device__ inline void WarpAllSum(double (&v)[N]) {
 // inverse of a symmetric positive definite 3x3 given as (c00,c01,c02,c11,c12,c22)
 // through its Cholesky factor (what Eigen's LLT-based InvertPSDMatrix does on the
 // Ceres side); returns false when not positive definite.
-__device__ inline bool InvertSym3(const double c[6], double inv[6]) {
+// `fac` (optional) receives M = L^{-1} (lower: m00, m10, m11, m20, m21, m22) with inv = M^T M -- the explicit Schur
+// build multiplies by M^T once instead of by inv (schur.cu).
+__device__ inline bool InvertSym3(const double c[6], double inv[6], double* fac = nullptr) {
   const double l00s = c[0];
   if (!(l00s > 0.0)) return false;
   const double l00 = sqrt(l00s), i00 = 1.0 / l00;
@@ -84,6 +86,7 @@ __device__ inline bool InvertSym3(const double c[6], double inv[6]) {
   inv[3] = i11 * i11 + m21 * m21;
   inv[4] = m21 * i22;
   inv[5] = i22 * i22;
+  if (fac) { fac[0] = i00; fac[1] = m10; fac[2] = i11; fac[3] = m20; fac[4] = m21; fac[5] = i22; }
   return true;
 }
 
