@@ -248,21 +248,19 @@ int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec, do
   if (rc) return rc;
   Problem* p = h->p;
   cudaStream_t st = p->stream;
-  std::vector<double> pose((size_t)p->n_img * 8), X((size_t)p->n_pt * 3);
+  std::vector<double> pose((size_t)p->n_img * 8);
   if ((image_qvec || image_tvec) && p->n_img > 0)
     SBA_CUDA(cudaMemcpyAsync(pose.data(), p->d_pose.p, pose.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (camera_params && p->n_cam > 0)
     SBA_CUDA(cudaMemcpyAsync(camera_params, p->d_cam.p, (size_t)p->n_cam * 12 * sizeof(double), cudaMemcpyDeviceToHost, st));
-  if (points && p->n_pt > 0)
-    SBA_CUDA(cudaMemcpyAsync(X.data(), p->d_X.p, X.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   SBA_CUDA(cudaStreamSynchronize(st));
+  // the shard's points are one contiguous range of the caller's array (points [p0, p0 + n_pt)): they land in place
+  if (points && p->n_pt > 0)
+    SBA_CUDA(DownloadLarge(points + 3 * (size_t)p->h_pt_local2global[0], p->d_X.p, (size_t)p->n_pt * 3 * sizeof(double), st));
   for (int i = 0; i < p->n_img; ++i) {
     if (image_qvec) for (int j = 0; j < 4; ++j) image_qvec[4 * (size_t)i + j] = pose[8 * (size_t)i + j];
     if (image_tvec) for (int j = 0; j < 3; ++j) image_tvec[3 * (size_t)i + j] = pose[8 * (size_t)i + 4 + j];
   }
-  if (points)
-    for (int q = 0; q < p->n_pt; ++q)
-      for (int a = 0; a < 3; ++a) points[3 * (size_t)p->h_pt_local2global[q] + a] = X[3 * (size_t)q + a];
   return SBA_OK;
 }
 

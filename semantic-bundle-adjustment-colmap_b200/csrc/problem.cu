@@ -287,6 +287,68 @@ cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t s
   return (cudaError_t)err.load();
 }
 
+// The way back: device -> the caller's PAGEABLE array (sba_get_parameters: 24 MB of points at C4, 48 MB at C5).  The
+// DMA of each 2 MB chunk lands in a pinned buffer and a host thread copies it out while the next chunks are in flight;
+// a plain cudaMemcpy into pageable memory measured 14 ms for the 24 MB.  Synchronous: returns when dst is complete.
+cudaError_t DownloadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes == 0) return cudaSuccess;
+  {
+    cudaPointerAttributes at;
+    if (bytes < 4 * kStageChunk || (cudaPointerGetAttributes(&at, dst) == cudaSuccess && at.type == cudaMemoryTypeHost)) {
+      cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st);
+      return e == cudaSuccess ? cudaStreamSynchronize(st) : e;
+    }
+    cudaGetLastError();
+  }
+  std::lock_guard<std::mutex> lk(g_stage_mu);
+  if (!g_stage.ok) {
+    for (int t = 0; t < kStageThreads; ++t)
+      for (int d = 0; d < kStageDepth; ++d) {
+        cudaError_t e = cudaMallocHost((void**)&g_stage.buf[t][d], kStageChunk);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g_stage.ev[t][d], cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+      }
+    g_stage.ok = true;
+  }
+  cudaError_t e0 = cudaStreamSynchronize(st);  // src is complete; the chunk copies below use per-thread side streams
+  if (e0 != cudaSuccess) return e0;
+  const size_t n_chunks = (bytes + kStageChunk - 1) / kStageChunk;
+  std::atomic<size_t> next(0);
+  std::atomic<int> err((int)cudaSuccess);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto work = [&](int t) {
+    cudaSetDevice(dev);
+    cudaStream_t cs;
+    if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { err.store((int)cudaErrorUnknown); return; }
+    size_t pending[kStageDepth]; bool has[kStageDepth] = {};
+    auto drain = [&](int d) {
+      if (!has[d]) return;
+      cudaError_t e = cudaEventSynchronize(g_stage.ev[t][d]);
+      if (e != cudaSuccess) err.store((int)e);
+      const size_t off = pending[d] * kStageChunk, len = std::min(kStageChunk, bytes - off);
+      std::memcpy((char*)dst + off, g_stage.buf[t][d], len);
+      has[d] = false;
+    };
+    int d = 0;
+    for (size_t c; (c = next.fetch_add(1)) < n_chunks; d = (d + 1) % kStageDepth) {
+      drain(d);  // the buffer's previous chunk has been copied out
+      const size_t off = c * kStageChunk, len = std::min(kStageChunk, bytes - off);
+      cudaError_t e = cudaMemcpyAsync(g_stage.buf[t][d], (const char*)src + off, len, cudaMemcpyDeviceToHost, cs);
+      if (e == cudaSuccess) e = cudaEventRecord(g_stage.ev[t][d], cs);
+      if (e != cudaSuccess) err.store((int)e);
+      pending[d] = c; has[d] = true;
+    }
+    for (int k = 0; k < kStageDepth; ++k) drain((d + k) % kStageDepth);
+    cudaStreamDestroy(cs);
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < kStageThreads; ++t) th.emplace_back(work, t);
+  work(0);
+  for (auto& t : th) t.join();
+  return (cudaError_t)err.load();
+}
+
 void Problem::DropGraphs() {
   for (auto& g : graph_exec) { if (g) cudaGraphExecDestroy(g); g = nullptr; }
   graph_opts_valid = false;
@@ -374,31 +436,85 @@ static int Validate(const sba_problem_desc* d) {
 // (bundle_adjustment.cc:417-425, 480-530); counts follow Solver::Summary.
 struct GlobalStructure {
   std::vector<int> col_img, col_cam, k_cols, k_dim, t_dim, p_off_global, blk_off, blk_dim;
-  std::vector<uint8_t> obs_active;
   int n_cdim = 0, kmax = 0, n_pvar_global = 0, uniform_model = -1;
   bool shared_intrinsics = false;
   sba_summary counts;
 };
+
+// ---- set-up passes over the observation list, made on the device from the raw copy of the caller's arrays ----
+// (at C4 the three host passes they replace -- usage marks, counts per point, counts per image -- were 28 of the 38 ms
+//  of sba_create)
+__global__ void __launch_bounds__(256) hist_point_kernel(int64_t n, const int* __restrict__ pt, int* __restrict__ cnt) {
+  const int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (k < n) atomicAdd(cnt + pt[k], 1);
+}
+// per-image counts of the observations whose point lies in [p0, p1); a CTA counts into shared memory first when the
+// image table fits (n_img <= 8192), so the global atomics are one per image per CTA
+__global__ void __launch_bounds__(256) hist_image_kernel(int64_t n, const int* __restrict__ img, const int* __restrict__ pt,
+                                                         int p0, int p1, int n_img, int* __restrict__ cnt) {
+  extern __shared__ int sh[];
+  const bool use_sh = n_img <= 8192;
+  if (use_sh) { for (int i = threadIdx.x; i < n_img; i += 256) sh[i] = 0; __syncthreads(); }
+  for (int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x; k < n; k += (int64_t)gridDim.x * 256) {
+    const int q = pt[k];
+    if (q < p0 || q >= p1) continue;
+    if (use_sh) atomicAdd(sh + img[k], 1); else atomicAdd(cnt + img[k], 1);
+  }
+  if (use_sh) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_img; i += 256) if (sh[i]) atomicAdd(cnt + i, sh[i]);
+  }
+}
+// residual blocks kept in the reduced program: some parameter block of the observation is variable
+__global__ void __launch_bounds__(256) count_active_kernel(int64_t n, const int* __restrict__ img, const int* __restrict__ pt,
+                                                           const uint8_t* __restrict__ img_live, const uint8_t* __restrict__ pt_live,
+                                                           unsigned long long* __restrict__ out) {
+  unsigned c = 0;
+  for (int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x; k < n; k += (int64_t)gridDim.x * 256)
+    c += (img_live[img[k]] | pt_live[pt[k]]) ? 1u : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
+static cudaError_t DeviceHistogramImages(cudaStream_t st, int64_t n, const int* d_img, const int* d_pt, int p0, int p1,
+                                         int n_img, int* d_cnt, int n_sm) {
+  cudaError_t e = cudaMemsetAsync(d_cnt, 0, (size_t)std::max(1, n_img) * sizeof(int), st);
+  if (e != cudaSuccess || n == 0) return e;
+  const int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)n_sm * 8);
+  hist_image_kernel<<<blocks, 256, n_img <= 8192 ? (size_t)n_img * sizeof(int) : 0, st>>>(n, d_img, d_pt, p0, p1, n_img, d_cnt);
+  return cudaGetLastError();
+}
 
 // residual rows per block: the two reprojection rows, plus the semantic row when the problem carries maps (X1)
 static int RowsOf(const sba_problem_desc& d) {
   return (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) ? 3 : 2;
 }
 
-static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
+// pt_count / img_count: observations per point / per image of the WHOLE problem.  With a device they come from two
+// histogram kernels over the caller's arrays, which are on the device anyway (DeviceHistograms); the host-only entry
+// point (sba_problem_counts) counts here.  count_active: also count the residual blocks of the reduced program on the
+// host (a pass over the observation list); with a device that count is made there too (CountActiveOnDevice).
+static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt_count, const int* img_count,
+                    bool count_active) {
   const int n_img = d.num_images, n_cam = d.num_cameras, n_pt = d.num_points;
   const int64_t n_obs = d.num_observations;
   std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used(n_pt, 0);
   std::vector<int> cam_img_count(n_cam, 0);
   const int NT = std::max(1, std::min(HostThreads(), (int)(n_obs / 16384) + 1));
-  // every writer stores the same value 1 into a byte: the passes can share the mark arrays
-  ParallelFor(NT, [&](int t) {
-    int64_t kb, ke; Slice(n_obs, NT, t, &kb, &ke);
-    for (int64_t k = kb; k < ke; ++k) {
-      uint8_t& iu = img_used[d.obs_image[k]]; if (!iu) iu = 1;
-      uint8_t& pu = pt_used[d.obs_point[k]]; if (!pu) pu = 1;
-    }
-  });
+  if (pt_count && img_count) {
+    for (int i = 0; i < n_img; ++i) img_used[i] = img_count[i] > 0;
+    for (int q = 0; q < n_pt; ++q) pt_used[q] = pt_count[q] > 0;
+  } else {
+    // every writer stores the same value 1 into a byte: the passes can share the mark arrays
+    ParallelFor(NT, [&](int t) {
+      int64_t kb, ke; Slice(n_obs, NT, t, &kb, &ke);
+      for (int64_t k = kb; k < ke; ++k) {
+        uint8_t& iu = img_used[d.obs_image[k]]; if (!iu) iu = 1;
+        uint8_t& pu = pt_used[d.obs_point[k]]; if (!pu) pu = 1;
+      }
+    });
+  }
   for (int i = 0; i < n_img; ++i) if (img_used[i]) { cam_used[d.image_camera[i]] = 1; cam_img_count[d.image_camera[i]]++; }
   std::memset(&g->counts, 0, sizeof(g->counts));
   sba_summary& s = g->counts;
@@ -445,17 +561,15 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g) {
     g->p_off_global[p] = g->n_pvar_global++;
     s.num_parameter_blocks_reduced++; s.num_parameters_reduced += 3; s.num_effective_parameters_reduced += 3;
   }
-  g->obs_active.assign(n_obs, 0);
   const int nr = RowsOf(d);
   s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(nr * n_obs);
+  if (!count_active) return;
   std::vector<int64_t> n_act(NT, 0);
   ParallelFor(NT, [&](int t) {
     int64_t kb, ke, na = 0; Slice(n_obs, NT, t, &kb, &ke);
     for (int64_t k = kb; k < ke; ++k) {
       const int i = d.obs_image[k], c = d.image_camera[i], p = d.obs_point[k];
-      const bool act = g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off_global[p] >= 0;
-      g->obs_active[k] = act;
-      na += act;
+      na += g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off_global[p] >= 0;
     }
     n_act[t] = na;
   });
@@ -466,7 +580,7 @@ int ProblemCounts(const sba_problem_desc* d, sba_summary* s) {
   int rc = Validate(d);
   if (rc) return rc;
   GlobalStructure g;
-  Analyse(*d, &g);
+  Analyse(*d, &g, nullptr, nullptr, true);
   *s = g.counts;
   return SBA_OK;
 }
@@ -551,8 +665,27 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
     }
   }
   tm.Lap("start map upload");
+  // counts per point and per image of the whole problem: device histograms over the raw copy (host loops without a device)
+  const int n_pt_g = d.num_points;
+  const int64_t n_obs_g = d.num_observations;
+  std::vector<int> pt_count((size_t)std::max(1, n_pt_g), 0), img_count((size_t)std::max(1, d.num_images), 0);
+  DevBuf<int> d_pt_count, d_img_count;
+  if (!host_only) {
+    if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
+    UP(d_pt_count.Alloc(pt_count.size())); UP(d_img_count.Alloc(img_count.size()));
+    UP(d_pt_count.Zero(p->stream));
+    if (n_obs_g > 0) hist_point_kernel<<<DivUp(n_obs_g, 256), 256, 0, p->stream>>>(n_obs_g, raw_pt.p, d_pt_count.p);
+    UP(DeviceHistogramImages(p->stream, n_obs_g, raw_img.p, raw_pt.p, 0, n_pt_g, d.num_images, d_img_count.p, p->n_sm));
+    UP(cudaMemcpyAsync(pt_count.data(), d_pt_count.p, pt_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+    UP(cudaMemcpyAsync(img_count.data(), d_img_count.p, img_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+    UP(cudaStreamSynchronize(p->stream));
+    p->launches += 2;
+  } else {
+    for (int64_t k = 0; k < n_obs_g; ++k) { pt_count[d.obs_point[k]]++; img_count[d.obs_image[k]]++; }
+  }
+  tm.Lap("histograms");
   GlobalStructure g;
-  Analyse(d, &g);
+  Analyse(d, &g, pt_count.data(), img_count.data(), host_only);
   tm.Lap("analyse");
   p->counts = g.counts;
   p->n_img = d.num_images; p->n_cam = d.num_cameras;
@@ -575,16 +708,8 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   // Host: one counting pass by point (worker t owns a contiguous range of points and scans obs_point for them: no
   // atomics, no per-thread counters) gives the CSR over points, the shard's range and the warp tiles.  The sort itself
   // -- and every per-observation array -- is made on the DEVICE from the caller's arrays (cub stable radix sort).
-  const int n_pt_g = d.num_points;
-  const int64_t n_obs_g = d.num_observations;
-  const int NT = std::max(1, std::min(HostThreads(), (int)(n_obs_g / 16384) + 1));
   std::vector<int64_t> prefix(n_pt_g + 1, 0);
-  ParallelFor(NT, [&](int t) {
-    int64_t qb, qe; Slice(n_pt_g, NT, t, &qb, &qe);
-    int64_t* cnt = prefix.data() + 1;
-    for (int64_t k = 0; k < n_obs_g; ++k) { const int q = d.obs_point[k]; if (q >= qb && q < qe) cnt[q]++; }
-  });
-  for (int q = 0; q < n_pt_g; ++q) prefix[q + 1] += prefix[q];
+  for (int q = 0; q < n_pt_g; ++q) prefix[q + 1] = prefix[q] + pt_count[q];
   int p0 = 0, p1 = n_pt_g;
   ShardPointRange(prefix, p->shard_count, p->shard_rank, &p0, &p1);
   p->n_pt = p1 - p0;
@@ -620,17 +745,18 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   // ---- image-major chunks of <= 256: sizes from a counting pass by image over the shard's observations ----
   std::vector<int>& img_ptr = p->h_img_ptr;
   img_ptr.assign(p->n_img + 1, 0);
-  {
-    const int NI = std::max(1, std::min(NT, p->n_img));
-    ParallelFor(NI, [&](int t) {
-      int64_t ib, ie; Slice(p->n_img, NI, t, &ib, &ie);
-      for (int64_t k = 0; k < n_obs_g; ++k) {
-        const int i = d.obs_image[k], q = d.obs_point[k];
-        if (i >= ib && i < ie && q >= p0 && q < p1) img_ptr[i + 1]++;
-      }
-    });
+  if (p->shard_count > 1) {  // the shard's own per-image counts: observations whose point lies in [p0, p1)
+    if (!host_only) {
+      UP(DeviceHistogramImages(p->stream, n_obs_g, raw_img.p, raw_pt.p, p0, p1, p->n_img, d_img_count.p, p->n_sm));
+      UP(cudaMemcpyAsync(img_count.data(), d_img_count.p, img_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+      UP(cudaStreamSynchronize(p->stream));
+      p->launches++;
+    } else {
+      std::fill(img_count.begin(), img_count.end(), 0);
+      for (int64_t k = 0; k < n_obs_g; ++k) { const int q = d.obs_point[k]; if (q >= p0 && q < p1) img_count[d.obs_image[k]]++; }
+    }
   }
-  for (int i = 0; i < p->n_img; ++i) img_ptr[i + 1] += img_ptr[i];
+  for (int i = 0; i < p->n_img; ++i) img_ptr[i + 1] = img_ptr[i] + img_count[i];
   std::vector<int> chunk_start, chunk_img, img_chunk_ptr(p->n_img + 1, 0);
   for (int i = 0; i < p->n_img; ++i) {
     img_chunk_ptr[i] = (int)chunk_img.size();
@@ -655,8 +781,25 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   if (host_only) return SBA_OK;
 
   // ---- device ----
-  if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
   cudaStream_t st = p->stream;
+  {  // residual blocks of the reduced program (Summary::num_residuals_reduced): counted on the device
+    std::vector<uint8_t> img_live((size_t)std::max(1, p->n_img), 0), pt_live((size_t)std::max(1, n_pt_g), 0);
+    for (int i = 0; i < p->n_img; ++i) img_live[i] = (g.col_img[6 * (size_t)i] >= 0 || g.k_dim[d.image_camera[i]] > 0) ? 1 : 0;
+    for (int q = 0; q < n_pt_g; ++q) pt_live[q] = g.p_off_global[q] >= 0 ? 1 : 0;
+    DevBuf<uint8_t> d_il, d_pl;
+    DevBuf<unsigned long long> d_n;
+    UP(d_il.Upload(img_live, st)); UP(d_pl.Upload(pt_live, st)); UP(d_n.Alloc(1)); UP(d_n.Zero(st));
+    if (n_obs_g > 0) {
+      const int blocks = (int)std::min<int64_t>((n_obs_g + 255) / 256, (int64_t)p->n_sm * 8);
+      count_active_kernel<<<blocks, 256, 0, st>>>(n_obs_g, raw_img.p, raw_pt.p, d_il.p, d_pl.p, d_n.p);
+      p->launches++;
+    }
+    unsigned long long n_act = 0;
+    UP(cudaMemcpyAsync(&n_act, d_n.p, sizeof(n_act), cudaMemcpyDeviceToHost, st));
+    UP(cudaStreamSynchronize(st));  // (also: the temporaries above are released on scope exit)
+    p->counts.num_residuals_reduced = (int)(p->nr * (int64_t)n_act);
+  }
+  tm.Lap("active count");
   // parameters: one upload into the creation copies, device-to-device into the current / candidate buffers
   // (these three triples swap pointers during the solve, so they own their memory)
   std::vector<double> pose((size_t)p->n_img * 8, 0.0), cam((size_t)p->n_cam * 12, 0.0);

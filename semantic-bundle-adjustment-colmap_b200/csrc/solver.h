@@ -266,7 +266,8 @@ int BuildProblem(const sba_problem_desc* d, Problem** out, bool host_only);
 int FetchHostOrder(Problem* p);  // order.cu
 int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int n_pt_g, const int* d_raw_img,
                      const int* d_raw_pt, const double* d_raw_xy);
-cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st);  // fills h_local2ref / h_obs_img / h_obs_pt on first use (sba_evaluate)
+cudaError_t UploadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st);
+cudaError_t DownloadLarge(void* dst, const void* src, size_t bytes, cudaStream_t st);  // device -> (pageable) host, synchronous  // fills h_local2ref / h_obs_img / h_obs_pt on first use (sba_evaluate)
 int ProblemCounts(const sba_problem_desc* d, sba_summary* s);
 // eval.cu
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate, bool defer_allreduce = false);

@@ -166,8 +166,10 @@ class Solver:
 
     def parameters(self):
         p = self.problem
-        q = np.zeros_like(p.image_qvec); t = np.zeros_like(p.image_tvec)
-        cam = np.zeros_like(p.camera_params); X = p.points.copy()
+        q = np.empty_like(p.image_qvec); t = np.empty_like(p.image_tvec)
+        cam = np.empty_like(p.camera_params)
+        # a shard returns its own range of points; the rest keeps the caller's values
+        X = np.empty_like(p.points) if self._desc.shard_count <= 1 else p.points.copy()
         capi.check(self.lib.sba_get_parameters(self._h, capi.ptr(q, capi._dp), capi.ptr(t, capi._dp),
                                                capi.ptr(cam, capi._dp), capi.ptr(X, capi._dp)))
         return q, t, cam, X
