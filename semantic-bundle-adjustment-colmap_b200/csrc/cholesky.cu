@@ -19,34 +19,62 @@
 //   potrf_diag   1 CTA      : L_kk = chol(A_kk), Linv_kk = L_kk^{-1}
 //   trsm_panel   1 CTA/tile : L_ik = A_ik Linv_kk'                (i > k, incl. rhs row)
 //   syrk_update  1 CTA/tile : A_ij -= L_ik L_jk'                  (i >= j > k) -- fp64 DMMA
+#include <cstdio>
+#include <cstdlib>
+
 #include "reduce.cuh"
 #include "solver.h"
 
 namespace sba {
 
 constexpr int NB = 64;
-constexpr int LDS = NB + 1;
 
-__global__ void __launch_bounds__(256) chol_load_rhs_kernel(int n, const double* __restrict__ rhs, double* __restrict__ S) {
+__global__ void __launch_bounds__(256) chol_load_rhs_kernel(int n, int ld, const double* __restrict__ rhs, double* __restrict__ S) {
   const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j < n) S[(size_t)n * n + j] = rhs[j];
+  if (j < n) S[(size_t)n * ld + j] = rhs[j];
 }
 
-// ---- 64x64 diagonal block: warp-register Cholesky -----------------------------------------
-// The block is split 2x2 into 32x32 sub-blocks.  A 32x32 factorisation runs in ONE warp with
-// lane r holding row r in registers (fully unrolled, shuffles broadcast the pivot column), so
-// the 32-step dependency chain costs a shuffle + FMA per step instead of block-wide barriers.
-constexpr unsigned kFull = 0xffffffffu;
+__device__ __forceinline__ void CpAsync16(void* smem_dst, const void* gsrc, bool pred) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int bytes = pred ? 16 : 0;  // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(bytes) : "memory");
+}
 
-// in: a[c] = A[lane][c] (lower part valid).  out: a[c] = L[lane][c] (zero above the diagonal).
-__device__ inline bool Chol32(double (&a)[32], int lane) {
+__device__ __forceinline__ void CpAsync8(void* smem_dst, const void* gsrc, bool pred) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int bytes = pred ? 8 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(bytes) : "memory");
+}
+
+// ---- panel diagonal block (PB = 128): L_pp = chol(A_pp) and Linv_pp = L_pp^{-1}, one CTA ---------------------------
+// This kernel is the critical path of the factorisation (one launch per panel, nothing else can run until it ends), so
+// it is built for latency:
+//   * the block lives in ONE shared 128 x 129 array P: the factor L in the lower part (P[r][c], c <= r), the inverse
+//     X = L^{-1} transposed into the upper part (X[r][c] at P[c][r + 1], c <= r);
+//   * a 32 x 32 diagonal sub-block is factored by ONE warp in registers (lane r holds row r; the pivot column travels by
+//     shuffle; 1 / sqrt(d) is one rsqrt -- no fp64 division anywhere on the chain) and inverted by the same warp, a
+//     column per lane;
+//   * everything around it (rows below, trailing update, off-diagonal blocks of X) is 4 x 4 register-tiled GEMM work
+//     spread over all 256 threads.
+//   for each 32-column block kb:  warp 0: L_kk = chol(A_kk), X_kk = L_kk^{-1}
+//                                 all   : L_ik = A_ik X_kk^T (rows below), A_ij -= L_ik L_jk^T (rest of the block)
+//   then the off-diagonal blocks of X by block rows:  X_ij = -X_ii sum_{k=j..i-1} L_ik X_kj
+// A partial last panel (nb < 128) is padded with the identity, which keeps it well posed.
+constexpr int PB = 128, LDP = PB + 1, SB = 32;
+constexpr unsigned kFull = 0xffffffffu;
+struct DiagSmem { double P[PB][LDP]; double T[64 * 65]; };  // T: scratch, [96][33] or [64][65]
+
+// in: a[c] = A[lane][c] (lower part valid).  out: a[c] = L[lane][c] (zero above the diagonal); lane j returns 1 / L[j][j].
+__device__ inline bool Chol32(double (&a)[32], int lane, double* my_inv) {
   bool ok = true;
+  double mine = 1.0;
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
     double d = __shfl_sync(kFull, a[j], j);
     if (!(d > 0.0) || !isfinite(d)) { ok = false; d = 1.0; }
-    const double s = sqrt(d), inv = 1.0 / s;
-    const double l = (lane == j) ? s : (lane > j ? a[j] * inv : 0.0);
+    const double inv = rsqrt(d);
+    const double l = (lane == j) ? d * inv : (lane > j ? a[j] * inv : 0.0);
+    if (lane == j) mine = inv;
     a[j] = l;
 #pragma unroll
     for (int c = j + 1; c < 32; ++c) {
@@ -54,249 +82,343 @@ __device__ inline bool Chol32(double (&a)[32], int lane) {
       a[c] -= l * lc;
     }
   }
+  *my_inv = mine;
   return ok;
 }
 
-// lane c: column c of the inverse of the lower-triangular 32x32 L stored in shared memory
-// (row stride LDS, at L[0][0]); x[i] = Linv[i][c].
-__device__ inline void TriInv32(const double* __restrict__ L, int lane, double (&x)[32]) {
+// acc[i][j] += sum_{m in [m0, m1)} A(i, m) * B(j, m)
+template <class FA, class FB>
+__device__ __forceinline__ void Acc4x4(FA A, FB B, int m0, int m1, double (&acc)[4][4]) {
+#pragma unroll 4
+  for (int m = m0; m < m1; ++m) {
+    double a[4], b[4];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    double s = (i == lane) ? 1.0 : 0.0;
+    for (int i = 0; i < 4; ++i) { a[i] = A(i, m); b[i] = B(i, m); }
 #pragma unroll
-    for (int k = 0; k < i; ++k) s -= L[i * LDS + k] * x[k];   // x[k] == 0 for k < lane
-    x[i] = (i >= lane) ? s / L[i * LDS + i] : 0.0;
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
   }
 }
 
-__global__ void __launch_bounds__(128) potrf_diag_kernel(double* __restrict__ S, int n, int k0,
-                                                         double* __restrict__ Linv, DeviceScalars* sc) {
+__global__ void __launch_bounds__(256) chol_diag128_kernel(double* __restrict__ S, int n, int ld, int k0, double* __restrict__ Linv,
+                                                           DeviceScalars* sc, long long* __restrict__ trace) {
   extern __shared__ double smem[];
-  double(*A)[LDS] = reinterpret_cast<double(*)[LDS]>(smem);             // block, then its factor
-  double(*X)[LDS] = reinterpret_cast<double(*)[LDS]>(smem + NB * LDS);  // inverse of the factor
+  DiagSmem& M = *reinterpret_cast<DiagSmem*>(smem);
+  int n_stamp = 0;
+  auto stamp = [&]() {  // SBA_CHOL_TRACE=1: globaltimer at the phase boundaries of the first panel
+    if (trace && threadIdx.x == 0) { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); trace[n_stamp++] = t; }
+  };
+  stamp();
+  double(*P)[LDP] = M.P;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  const int nb = min(NB, n - k0);
-  for (int idx = tid; idx < NB * NB; idx += 128) {
-    const int r = idx / NB, c = idx - r * NB;
-    double v = (r == c) ? 1.0 : 0.0;   // identity padding keeps a partial block well posed
-    if (r < nb && c <= r) v = S[(size_t)(k0 + r) * n + k0 + c];
-    A[r][c] = v;
-    X[r][c] = 0.0;
+  const int nb = min(PB, n - k0);
+  auto X = [&](int r, int c) -> double& { return P[c][r + 1]; };  // entry (r, c), c <= r, of the inverse
+  // the lower part of the block: 8-byte cp.async, all of a thread's pieces in flight together (a plain load loop paid a
+  // global-memory round trip per element: 18 us); the upper part receives the inverse, every entry of which is written
+  // before it is read
+  for (int idx = tid; idx < PB * PB; idx += 256) {
+    const int r = idx / PB, c = idx - r * PB;
+    if (c > r) continue;
+    if (r < nb) CpAsync8(&P[r][c], S + (size_t)(k0 + r) * ld + k0 + c, true);
+    else P[r][c] = (r == c ? 1.0 : 0.0);
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
+  stamp();
   bool ok = true;
-  // (1) L11 = chol(A11)
-  if (w == 0) {
-    double a[32];
+  for (int kb = 0; kb < PB / SB; ++kb) {
+    const int o = kb * SB;
+    if (w == 0) {
+      double a[32], my_inv;
 #pragma unroll
-    for (int c = 0; c < 32; ++c) a[c] = A[lane][c];
-    ok = Chol32(a, lane);
+      for (int c = 0; c < 32; ++c) a[c] = P[o + lane][o + c];   // (entries above the diagonal: ignored by Chol32)
+      ok = Chol32(a, lane, &my_inv) && ok;
 #pragma unroll
-    for (int c = 0; c < 32; ++c) A[lane][c] = a[c];
-  }
-  __syncthreads();
-  // (2) warp 0: L21 = A21 L11^{-T} (one row per lane, forward substitution along the row);
-  //     warp 1: X11 = L11^{-1}
-  if (w == 0) {
-    double x[32];
+      for (int c = 0; c < 32; ++c) if (c <= lane) P[o + lane][o + c] = a[c];
+      __syncwarp();
+      // X_kk = L_kk^{-1}: lane c owns column c; x[i] = (delta_ic - sum_{k<i} L[i][k] x[k]) / L[i][i]
+      double x[32];
 #pragma unroll
-    for (int c = 0; c < 32; ++c) {
-      double s = A[32 + lane][c];
+      for (int i = 0; i < 32; ++i) {
+        double s0 = (i == lane) ? 1.0 : 0.0, s1 = 0.0;
 #pragma unroll
-      for (int m = 0; m < c; ++m) s -= x[m] * A[c][m];
-      x[c] = s / A[c][c];
-    }
+        for (int k = 0; k + 1 < i; k += 2) { s0 -= P[o + i][o + k] * x[k]; s1 -= P[o + i][o + k + 1] * x[k + 1]; }
+        if (i & 1) s0 -= P[o + i][o + i - 1] * x[i - 1];
+        const double di = __shfl_sync(kFull, my_inv, i);
+        x[i] = (i >= lane) ? (s0 + s1) * di : 0.0;   // x[k] == 0 for k < lane
+      }
 #pragma unroll
-    for (int c = 0; c < 32; ++c) A[32 + lane][c] = x[c];
-  } else if (w == 1) {
-    double x[32];
-    TriInv32(&A[0][0], lane, x);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) X[i][lane] = x[i];
-  }
-  __syncthreads();
-  // (3) A22 -= L21 L21^T   (4 warps: row = lane, 8 columns each)
-  {
-    double acc[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
-    for (int m = 0; m < 32; ++m) {
-      const double l = A[32 + lane][m];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += l * A[32 + w * 8 + e][m];
+      for (int i = 0; i < 32; ++i) if (i >= lane) X(o + i, o + lane) = x[i];
     }
     __syncthreads();
+    stamp();
+    const int R = PB - o - SB;  // rows below the diagonal block
+    if (R > 0) {
+      // L_ik = A_ik X_kk^T into T (the outputs of a row overwrite its inputs): 4 x 4 tiles, (R / 4) x 8 of them
+      for (int tile = tid; tile < (R / 4) * 8; tile += 256) {
+        const int ti = tile >> 3, tj = tile & 7;
+        double acc[4][4] = {};
+        auto A = [&](int i, int m) { return P[o + SB + 4 * ti + i][o + m]; };
+        Acc4x4(A, [&](int j, int m) { return X(o + 4 * tj + j, o + m); }, 0, 4 * tj, acc);
+        Acc4x4(A, [&](int j, int m) { return m <= 4 * tj + j ? X(o + (m <= 4 * tj + j ? 4 * tj + j : m), o + m) : 0.0; }, 4 * tj, 4 * tj + 4, acc);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) A[32 + lane][32 + w * 8 + e] -= acc[e];
-  }
-  __syncthreads();
-  // (4) L22 = chol(A22)
-  if (w == 0) {
-    double a[32];
+        for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int c = 0; c < 32; ++c) a[c] = A[32 + lane][32 + c];
-    ok = Chol32(a, lane) && ok;
+          for (int j = 0; j < 4; ++j) M.T[(4 * ti + i) * (SB + 1) + 4 * tj + j] = acc[i][j];
+      }
+      __syncthreads();
+      for (int idx = tid; idx < R * SB; idx += 256) { const int r = idx / SB, c = idx - r * SB; P[o + SB + r][o + c] = M.T[r * (SB + 1) + c]; }
+      __syncthreads();
+      stamp();
+      // A_ij -= L_ik L_jk^T on the lower part of the remaining R x R block: 4 x 4 tiles (ti >= tj)
+      const int TT = R / 4;
+      for (int tile = tid; tile < TT * (TT + 1) / 2; tile += 256) {
+        int ti = (int)((sqrtf(8.0f * (float)tile + 1.0f) - 1.0f) * 0.5f);
+        while ((ti + 1) * (ti + 2) / 2 <= tile) ++ti;
+        while (ti * (ti + 1) / 2 > tile) --ti;
+        const int tj = tile - ti * (ti + 1) / 2;
+        double acc[4][4] = {};
+        Acc4x4([&](int i, int m) { return P[o + SB + 4 * ti + i][o + m]; },
+               [&](int j, int m) { return P[o + SB + 4 * tj + j][o + m]; }, 0, SB, acc);
 #pragma unroll
-    for (int c = 0; c < 32; ++c) A[32 + lane][32 + c] = a[c];
-    if (!ok && lane == 0) { sc->chol_fail = 1; sc->solver_failed = 1; }
-  }
-  __syncthreads();
-  // (5) warp 0: X22 = L22^{-1};  warps 1..3 + 0 afterwards: T = L21 X11 (into the unused upper-right of A)
-  if (w == 0) {
-    double x[32];
-    TriInv32(&A[32][32], lane, x);
+        for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int i = 0; i < 32; ++i) X[32 + i][32 + lane] = x[i];
-  }
-  {
-    double acc[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
-    for (int m = 0; m < 32; ++m) {
-      const double l = A[32 + lane][m];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += l * X[m][w * 8 + e];
+          for (int j = 0; j < 4; ++j)
+            if (4 * tj + j <= 4 * ti + i) P[o + SB + 4 * ti + i][o + SB + 4 * tj + j] -= acc[i][j];
+      }
+      __syncthreads();
+      stamp();
     }
-#pragma unroll
-    for (int e = 0; e < 8; ++e) A[lane][32 + w * 8 + e] = acc[e];   // T[lane][.] parked above the diagonal
   }
-  __syncthreads();
-  // (6) X21 = -X22 T
-  {
-    double acc[8];
+  if (tid == 0 && !ok) { sc->chol_fail = 1; sc->solver_failed = 1; }
+  // the factor goes back while the inverse is completed
+  for (int idx = tid; idx < PB * PB; idx += 256) {
+    const int r = idx / PB, c = idx - r * PB;
+    if (r < nb && c <= r) S[(size_t)(k0 + r) * ld + k0 + c] = P[r][c];
+  }
+  // off-diagonal blocks of X in two levels of the 2 x 2 block inverse  X_lo,hi = -X_hi L_hi,lo X_lo  (4 x 4 tiles):
+  //   level 1: the 32-blocks (1,0) and (3,2), side by side;  level 2: the 64-block (rows 64.., columns ..63)
+  for (int level = 1; level <= 2; ++level) {
+    const int bs = level == 1 ? SB : 2 * SB, tpb = bs / 4;     // block size, tiles per block side
+    const int n_pairs = level == 1 ? 2 : 1, ldt = bs + 1;
+    for (int tile = tid; tile < n_pairs * tpb * tpb; tile += 256) {   // T = L_hi,lo X_lo
+      const int pr = tile / (tpb * tpb), rem = tile - pr * tpb * tpb, ti = rem / tpb, tj = rem - ti * tpb;
+      const int lo = pr * 2 * bs, hi = lo + bs;              // first row / column of the two diagonal blocks of the pair
+      const int col0 = lo + 4 * tj;                          // X[m][col] is zero for m < col
+      double acc[4][4] = {};
+      auto A = [&](int i, int m) { return P[hi + 4 * ti + i][m]; };
+      Acc4x4(A, [&](int j, int m) { return m >= col0 + j ? X(m >= col0 + j ? m : col0 + j, col0 + j) : 0.0; }, col0, col0 + 4, acc);
+      Acc4x4(A, [&](int j, int m) { return X(m, col0 + j); }, col0 + 4, hi, acc);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
-    for (int m = 0; m < 32; ++m) {
-      const double l = X[32 + lane][32 + m];
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += l * A[m][32 + w * 8 + e];
+        for (int j = 0; j < 4; ++j) M.T[(pr * bs + 4 * ti + i) * ldt + 4 * tj + j] = acc[i][j];
     }
+    __syncthreads();
+    for (int tile = tid; tile < n_pairs * tpb * tpb; tile += 256) {   // X_hi,lo = -X_hi T, X_hi lower triangular
+      const int pr = tile / (tpb * tpb), rem = tile - pr * tpb * tpb, ti = rem / tpb, tj = rem - ti * tpb;
+      const int lo = pr * 2 * bs, hi = lo + bs;
+      double acc[4][4] = {};
+      auto B = [&](int j, int m) { return M.T[(pr * bs + m) * ldt + 4 * tj + j]; };
+      Acc4x4([&](int i, int m) { return X(hi + 4 * ti + i, hi + m); }, B, 0, 4 * ti, acc);
+      Acc4x4([&](int i, int m) { return m <= 4 * ti + i ? X(hi + (m <= 4 * ti + i ? 4 * ti + i : m), hi + m) : 0.0; }, B,
+             4 * ti, 4 * ti + 4, acc);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) X[32 + lane][w * 8 + e] = -acc[e];
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) X(hi + 4 * ti + i, lo + 4 * tj + j) = -acc[i][j];
+    }
+    __syncthreads();
+    stamp();
   }
-  __syncthreads();
-  for (int idx = tid; idx < NB * NB; idx += 128) {
-    const int r = idx / NB, c = idx - r * NB;
-    if (r < nb && c <= r) S[(size_t)(k0 + r) * n + k0 + c] = A[r][c];
-    Linv[idx] = X[r][c];
+  for (int idx = tid; idx < PB * PB; idx += 256) {
+    const int r = idx / PB, c = idx - r * PB;
+    Linv[idx] = c <= r ? X(r, c) : 0.0;
   }
+  stamp();
 }
 
-// L_ik = A_ik * Linv_kk^T for the row tile starting at r0 = k0 + NB*(1 + blockIdx.x)
-__global__ void __launch_bounds__(256) trsm_panel_kernel(double* __restrict__ S, int n, int n_rows, int k0,
-                                                         const double* __restrict__ Linv) {
+// ---- panel rows below the diagonal block: L_ik = A_ik Linv_pp^T for a 64-row tile (incl. the rhs row) ----------------
+__global__ void __launch_bounds__(256) chol_trsm128_kernel(double* __restrict__ S, int n, int ld, int n_rows, int k0, int nb,
+                                                           const double* __restrict__ Linv) {
   extern __shared__ double smem[];
-  double(*A)[LDS] = reinterpret_cast<double(*)[LDS]>(smem);
-  double(*Li)[LDS] = reinterpret_cast<double(*)[LDS]>(smem + NB * LDS);
+  double(*A)[LDP] = reinterpret_cast<double(*)[LDP]>(smem);               // [64][129]
+  double(*Li)[LDP] = reinterpret_cast<double(*)[LDP]>(smem + NB * LDP);   // [128][129]
   const int tid = threadIdx.x;
-  const int nb = min(NB, n - k0);
   const int r0 = k0 + nb + NB * blockIdx.x;
   const int nr = min(NB, n_rows - r0);
-  for (int idx = tid; idx < NB * NB; idx += 256) {
-    const int r = idx / NB, c = idx - r * NB;
-    A[r][c] = (r < nr && c < nb) ? S[(size_t)(r0 + r) * n + k0 + c] : 0.0;
-    Li[r][c] = Linv[idx];
+  for (int idx = tid; idx < NB * PB; idx += 256) {
+    const int r = idx / PB, c = idx - r * PB;
+    A[r][c] = (r < nr && c < nb) ? S[(size_t)(r0 + r) * ld + k0 + c] : 0.0;
   }
+  for (int idx = tid; idx < PB * PB; idx += 256) Li[idx / PB][idx % PB] = Linv[idx];
   __syncthreads();
-  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
-  double acc[4][4];
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, 4 rows x 8 columns each (strided by 16)
+  double acc[4][8];
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-  for (int m = 0; m < nb; ++m) {
-    double av[4], bv[4];
+    for (int b = 0; b < 8; ++b) acc[a][b] = 0.0;
+  const int mend = min(nb, tx + 113);  // Linv[c][m] = 0 for m > c; the thread's largest column is tx + 112
+  for (int m = 0; m < mend; ++m) {
+    double av[4], bv[8];
 #pragma unroll
     for (int a = 0; a < 4; ++a) av[a] = A[ty + 16 * a][m];
 #pragma unroll
-    for (int b = 0; b < 4; ++b) bv[b] = Li[tx + 16 * b][m];  // Linv[c][m], zero for m > c
+    for (int b = 0; b < 8; ++b) bv[b] = Li[tx + 16 * b][m];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
-      for (int b = 0; b < 4; ++b) acc[a][b] += av[a] * bv[b];
+      for (int b = 0; b < 8; ++b) acc[a][b] += av[a] * bv[b];
   }
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
+    for (int b = 0; b < 8; ++b) {
       const int r = ty + 16 * a, c = tx + 16 * b;
-      if (r < nr && c < nb) S[(size_t)(r0 + r) * n + k0 + c] = acc[a][b];
+      if (r < nr && c < nb) S[(size_t)(r0 + r) * ld + k0 + c] = acc[a][b];
     }
 }
 
 // fp64 tensor-core MMA (DMMA): D(8x8) += A(8x4, row) * B(4x8, col)
-__device__ inline void Dmma884(double& d0, double& d1, double a, double b) {
+__device__ __forceinline__ void Dmma884(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                : "+d"(d0), "+d"(d1)
                : "d"(a), "d"(b));
 }
+// ---- trailing update: A_ij -= L_ik L_jk^T on 128 x 128 tiles of the lower triangle (rows up to n_rows) -------------
+// The one dense contraction of the path, on the fp64 tensor cores.  8 warps as 4 (rows) x 2 (columns): a warp owns a
+// 32 x 64 part of the tile = 4 x 8 DMMA accumulators (64 registers); per k-step of 4 it loads 4 A and 8 B fragments
+// from shared memory for 32 DMMAs.  The K = 128 panel is streamed in chunks of 32 columns through a double-buffered
+// cp.async pipeline (rows of S are contiguous in k: 256-byte runs).
+constexpr int TB = 128, KC = 32, LDK = KC + 4;
+struct SyrkSmem { double As[2][TB][LDK], Bs[2][TB][LDK]; };
 
-// A_ij -= L_ik L_jk^T on 64x64 tiles of the trailing lower triangle (rows up to n_rows).
-// 8 warps; warp w owns the 8-row strip w of the tile and sweeps the eight 8x8 column
-// blocks with DMMA: A fragment = L_ik[8 rows][4 k], B fragment = L_jk[8 cols][4 k].
-__global__ void __launch_bounds__(256) syrk_update_kernel(double* __restrict__ S, int n, int n_rows, int k0, int nb,
-                                                          int t0 /* first trailing row */, int m_tiles) {
-  constexpr int KC = 32, LDK = KC + 4;  // k-chunk staged in shared memory, padded to spread banks
-  __shared__ double As[NB][LDK];        // [row][k]
-  __shared__ double Bs[NB][LDK];
-  // linear tile id -> (bi >= bj) in the lower triangle of an m_tiles x m_tiles grid
-  const int t = blockIdx.x;
-  int bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-  while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
-  while (bi * (bi + 1) / 2 > t) --bi;
-  const int bj = t - bi * (bi + 1) / 2;
-  (void)m_tiles;
-  const int i0 = t0 + NB * bi, j0 = t0 + NB * bj;
-  const int tid = threadIdx.x;
-  const int w = tid >> 5, lane = tid & 31;
-  const int g = lane >> 2, q = lane & 3;  // fragment coordinates: row/col g, k index q
-  double acc[8][2];
+__global__ void __launch_bounds__(256) chol_syrk128_kernel(double* __restrict__ S, int n, int ld, int n_rows, int k0, int nb,
+                                                           int t0 /* first trailing row */, int first_column) {
+  extern __shared__ double smem[];
+  SyrkSmem& M = *reinterpret_cast<SyrkSmem*>(smem);
+  // first_column: the tiles of the first tile column (they hold the next panel: updated first, so that the next panel's
+  // factorisation can start while the rest of the update runs); else the rest of the lower triangle: linear tile id ->
+  // (bi >= bj >= 1)
+  int bi, bj;
+  if (first_column) { bi = blockIdx.x; bj = 0; }
+  else {
+    const int t = blockIdx.x;
+    bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
+    while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
+    while (bi * (bi + 1) / 2 > t) --bi;
+    bj = t - bi * (bi + 1) / 2 + 1;
+    bi += 1;
+  }
+  const int i0 = t0 + TB * bi, j0 = t0 + TB * bj;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  const int wr = w >> 1, wc = w & 1;        // warp's 32-row strip, 64-column half
+  const int g = lane >> 2, q = lane & 3;    // fragment coordinates: row/col g, k index q
+  // The accumulators start as -C: all of a thread's 32 loads of the tile are issued back to back here, in flight under
+  // the first operand chunk, and the result leaves as C_new = -(L L^T - C).  (A read-modify-write epilogue measured
+  // 64 % of the kernel's stall samples: 32 dependent load -> DADD -> store round trips per thread.)
+  double acc[4][8][2];
+  const bool pair_ok = (ld & 1) == 0;  // rows of S are 16-byte aligned: (c, c + 1) moves as one double2
 #pragma unroll
-  for (int cb = 0; cb < 8; ++cb) { acc[cb][0] = 0.0; acc[cb][1] = 0.0; }
-  for (int kc = 0; kc < nb; kc += KC) {
-    for (int idx = tid; idx < NB * KC; idx += 256) {
-      const int r = idx / KC, c = idx - r * KC;
-      As[r][c] = (i0 + r < n_rows && kc + c < nb) ? S[(size_t)(i0 + r) * n + k0 + kc + c] : 0.0;
-      Bs[r][c] = (j0 + r < n && kc + c < nb) ? S[(size_t)(j0 + r) * n + k0 + kc + c] : 0.0;
+  for (int a = 0; a < 4; ++a) {
+    const int r = i0 + 32 * wr + 8 * a + g;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int c = j0 + 64 * wc + 8 * b + 2 * q;
+      double v0 = 0.0, v1 = 0.0;
+      if (r < n_rows) {
+        const double* src = S + (size_t)r * ld + c;  // (dereferenced only where the guards below hold)
+        if (pair_ok && c + 1 < n && c + 1 <= r) { const double2 v = *reinterpret_cast<const double2*>(src); v0 = v.x; v1 = v.y; }
+        else {
+          if (c < n && c <= r) v0 = src[0];
+          if (c + 1 < n && c + 1 <= r) v1 = src[1];
+        }
+      }
+      acc[a][b][0] = -v0; acc[a][b][1] = -v1;
     }
+  }
+  const int n_chunks = (nb + KC - 1) / KC;
+  // 128 rows x 32 doubles of each operand per chunk.  Rows of S start 16-byte aligned only when n is even: then 16-byte
+  // pieces (8 per thread and operand), else 8-byte ones (16 per thread and operand); a piece outside the matrix or the
+  // panel is zero-filled (src-size 0).
+  const bool wide = (ld & 1) == 0;
+  auto stage = [&](int buf, int kc) {
+    if (wide) {
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int piece = tid + 256 * it;
+        const int r = piece >> 4, c2 = (piece & 15) * 2;
+        const bool kin = kc + c2 < nb;  // (nb is even whenever n is)
+        const int kk = k0 + (kin ? kc + c2 : 0);  // (an address inside the matrix also when nothing is read)
+        CpAsync16(&M.As[buf][r][c2], S + (size_t)min(i0 + r, n_rows - 1) * ld + kk, kin && (i0 + r < n_rows));
+        CpAsync16(&M.Bs[buf][r][c2], S + (size_t)min(j0 + r, n - 1) * ld + kk, kin && (j0 + r < n));
+      }
+    } else {
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int piece = tid + 256 * it;
+        const int r = piece >> 5, c = piece & 31;
+        const bool kin = kc + c < nb;
+        CpAsync8(&M.As[buf][r][c], S + (size_t)min(i0 + r, n_rows - 1) * ld + k0 + min(kc + c, nb - 1), kin && (i0 + r < n_rows));
+        CpAsync8(&M.Bs[buf][r][c], S + (size_t)min(j0 + r, n - 1) * ld + k0 + min(kc + c, nb - 1), kin && (j0 + r < n));
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  stage(0, 0);
+  for (int ch = 0; ch < n_chunks; ++ch) {
+    const int buf = ch & 1;
+    if (ch + 1 < n_chunks) { stage(buf ^ 1, (ch + 1) * KC); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 #pragma unroll
     for (int m = 0; m < KC; m += 4) {
-      const double a = As[8 * w + g][m + q];
+      double af[4], bf[8];
 #pragma unroll
-      for (int cb = 0; cb < 8; ++cb) {
-        const double b = Bs[8 * cb + g][m + q];
-        Dmma884(acc[cb][0], acc[cb][1], a, b);
-      }
+      for (int a = 0; a < 4; ++a) af[a] = M.As[buf][32 * wr + 8 * a + g][m + q];
+#pragma unroll
+      for (int b = 0; b < 8; ++b) bf[b] = M.Bs[buf][64 * wc + 8 * b + g][m + q];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) Dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
     }
-    __syncthreads();
+    __syncthreads();  // the buffer is refilled two chunks later
   }
   // D fragment: row g, cols 2q, 2q+1
-  const int r = i0 + 8 * w + g;
-  if (r < n_rows) {
 #pragma unroll
-    for (int cb = 0; cb < 8; ++cb) {
+  for (int a = 0; a < 4; ++a) {
+    const int r = i0 + 32 * wr + 8 * a + g;
+    if (r >= n_rows) continue;
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int c = j0 + 8 * cb + 2 * q + e;
-        if (c < n && c <= r) S[(size_t)r * n + c] -= acc[cb][e];
+    for (int b = 0; b < 8; ++b) {
+      const int c = j0 + 64 * wc + 8 * b + 2 * q;
+      double* dst = S + (size_t)r * ld + c;
+      if (pair_ok && c + 1 < n && c + 1 <= r) {
+        *reinterpret_cast<double2*>(dst) = make_double2(-acc[a][b][0], -acc[a][b][1]);
+      } else {
+        if (c < n && c <= r) dst[0] = -acc[a][b][0];
+        if (c + 1 < n && c + 1 <= r) dst[1] = -acc[a][b][1];
       }
     }
   }
 }
 
-// backward substitution sweep for block column k: every CTA recomputes
-// x_k = Linv_kk^T y_k (64x64, cheap) and then updates its slice of y_j -= L_kj^T x_k, j < k.
-__global__ void __launch_bounds__(256) back_sweep_kernel(const double* __restrict__ S, int n, int k0, int nb,
-                                                         const double* __restrict__ Linv, double* __restrict__ y,
-                                                         double* __restrict__ x) {
-  __shared__ double yk[NB], xk[NB];
+// backward substitution sweep for panel k: every CTA recomputes x_k = Linv_pp^T y_k (128 x 128, cheap) and then
+// updates its slice of y_j -= L_kj^T x_k, j < k.
+__global__ void __launch_bounds__(256) chol_back128_kernel(const double* __restrict__ S, int n, int ld, int k0, int nb,
+                                                           const double* __restrict__ Linv, double* __restrict__ y,
+                                                           double* __restrict__ x) {
+  __shared__ double yk[PB], xk[PB];
   const int tid = threadIdx.x;
-  if (tid < NB) yk[tid] = tid < nb ? y[k0 + tid] : 0.0;
+  if (tid < PB) yk[tid] = tid < nb ? y[k0 + tid] : 0.0;
   __syncthreads();
-  if (tid < NB) {
+  if (tid < PB) {
     double s = 0.0;
-    for (int m = tid; m < nb; ++m) s += Linv[m * NB + tid] * yk[m];  // (Linv^T)[tid][m]
+    for (int m = tid; m < nb; ++m) s += Linv[m * PB + tid] * yk[m];  // (Linv^T)[tid][m]
     xk[tid] = s;
     if (blockIdx.x == 0 && tid < nb) x[k0 + tid] = s;
   }
@@ -304,59 +426,90 @@ __global__ void __launch_bounds__(256) back_sweep_kernel(const double* __restric
   const int c = blockIdx.x * 256 + tid;
   if (c < k0) {
     double s = 0.0;
-    for (int r = 0; r < nb; ++r) s += S[(size_t)(k0 + r) * n + c] * xk[r];
+    for (int r = 0; r < nb; ++r) s += S[(size_t)(k0 + r) * ld + c] * xk[r];
     y[c] -= s;
   }
 }
 
-__global__ void __launch_bounds__(256) chol_fetch_y_kernel(int n, const double* __restrict__ S, double* __restrict__ y) {
+__global__ void __launch_bounds__(256) chol_fetch_y_kernel(int n, int ld, const double* __restrict__ S, double* __restrict__ y) {
   const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j < n) y[j] = S[(size_t)n * n + j];
+  if (j < n) y[j] = S[(size_t)n * ld + j];
 }
 
 int CholeskySolve(Problem* p) {
   const int n = p->n_cdim;
   if (n == 0) return SBA_OK;
   if (n <= kCholSmallMax) return CholeskySolveSmall(p);
-  static bool attr_set = false;
-  const int dyn = 2 * NB * LDS * (int)sizeof(double);
-  if (!attr_set) {
-    SBA_CUDA(cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-    SBA_CUDA(cudaFuncSetAttribute(trsm_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-    attr_set = true;
+  static bool attr_set[64] = {};
+  const int dyn_diag = (int)sizeof(DiagSmem), dyn_trsm = (NB + PB) * LDP * (int)sizeof(double), dyn_syrk = (int)sizeof(SyrkSmem);
+  if (!attr_set[p->device & 63]) {
+    SBA_CUDA(cudaFuncSetAttribute(chol_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_diag));
+    SBA_CUDA(cudaFuncSetAttribute(chol_trsm128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_trsm));
+    SBA_CUDA(cudaFuncSetAttribute(chol_syrk128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_syrk));
+    attr_set[p->device & 63] = true;
   }
   cudaStream_t st = p->stream;
+  if (!p->stream2) {  // (first factorisation of the handle: plain launches, never inside a capture)
+    SBA_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
+    for (auto& e : p->ev_chol) SBA_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
   double* S = p->d_S.p;
+  const int ld = DenseLd(n);  // even: every row of S starts 16-byte aligned
   const int n_rows = n + 1;
-  const int nblk = DivUp(n, NB);
-  SBA_CUDA(p->d_Linv.Alloc((size_t)nblk * NB * NB));
-  chol_load_rhs_kernel<<<DivUp(n, 256), 256, 0, st>>>(n, p->d_rhs.p, S);
+  const int nblk = DivUp(n, PB);
+  SBA_CUDA(p->d_Linv.Alloc((size_t)nblk * PB * PB));
+  chol_load_rhs_kernel<<<DivUp(n, 256), 256, 0, st>>>(n, ld, p->d_rhs.p, S);
   p->launches++;
+  static const bool want_trace = getenv("SBA_CHOL_TRACE") != nullptr;
+  DevBuf<long long> trace;
+  if (want_trace) { SBA_CUDA(trace.Alloc(32)); SBA_CUDA(trace.Zero(st)); }
+  // Two streams.  The panel chain (diagonal block, rows below) is latency-bound and serial; the trailing update is the
+  // bulk of the flops.  The update of panel k is split: the first tile column (= panel k + 1) goes first, then the
+  // side stream factors panel k + 1 while the main stream updates the rest.  The same dependencies are captured when
+  // the LM iteration is recorded as a CUDA graph.
+  cudaStream_t sb = p->stream2;
+  cudaEvent_t evA = p->ev_chol[0], evB = p->ev_chol[1];
+  SBA_CUDA(cudaEventRecord(evA, st));
+  SBA_CUDA(cudaStreamWaitEvent(sb, evA, 0));
   for (int kb = 0; kb < nblk; ++kb) {
-    const int k0 = kb * NB, nb = std::min(NB, n - k0);
-    double* Linv = p->d_Linv.p + (size_t)kb * NB * NB;
-    potrf_diag_kernel<<<1, 128, dyn, st>>>(S, n, k0, Linv, p->d_scalars.p);
-    const int rem_rows = n_rows - (k0 + nb);
-    const int row_tiles = DivUp(rem_rows, NB);
-    trsm_panel_kernel<<<row_tiles, 256, dyn, st>>>(S, n, n_rows, k0, Linv);
+    const int k0 = kb * PB, nb = std::min(PB, n - k0);
+    double* Linv = p->d_Linv.p + (size_t)kb * PB * PB;
+    chol_diag128_kernel<<<1, 256, dyn_diag, sb>>>(S, n, ld, k0, Linv, p->d_scalars.p, kb == 1 ? trace.p : nullptr);
+    const int rem_rows = n_rows - (k0 + nb);  // >= 1: the rhs row
+    chol_trsm128_kernel<<<DivUp(rem_rows, NB), 256, dyn_trsm, sb>>>(S, n, ld, n_rows, k0, nb, Linv);
     p->launches += 2;
+    SBA_CUDA(cudaEventRecord(evB, sb));
+    SBA_CUDA(cudaStreamWaitEvent(st, evB, 0));
     if (k0 + nb < n) {
-      const int m_tiles = row_tiles;  // tiles cover rows [k0+nb, n_rows); columns [k0+nb, n)
-      const int n_lower = m_tiles * (m_tiles + 1) / 2;
-      syrk_update_kernel<<<n_lower, 256, 0, st>>>(S, n, n_rows, k0, nb, k0 + nb, m_tiles);
+      const int m_tiles = DivUp(rem_rows, TB);  // tiles cover rows [k0+nb, n_rows); columns [k0+nb, n)
+      chol_syrk128_kernel<<<m_tiles, 256, dyn_syrk, st>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 1);
       p->launches++;
+      SBA_CUDA(cudaEventRecord(evA, st));
+      SBA_CUDA(cudaStreamWaitEvent(sb, evA, 0));
+      if (m_tiles > 1) {
+        chol_syrk128_kernel<<<m_tiles * (m_tiles - 1) / 2, 256, dyn_syrk, st>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 0);
+        p->launches++;
+      }
     }
   }
   // y = row n of the factor; back substitution into d_yc
-  chol_fetch_y_kernel<<<DivUp(n, 256), 256, 0, st>>>(n, S, p->d_tmp_c.p);
+  chol_fetch_y_kernel<<<DivUp(n, 256), 256, 0, st>>>(n, ld, S, p->d_tmp_c.p);
   p->launches++;
   for (int kb = nblk - 1; kb >= 0; --kb) {
-    const int k0 = kb * NB, nb = std::min(NB, n - k0);
-    back_sweep_kernel<<<std::max(1, DivUp(k0, 256)), 256, 0, st>>>(S, n, k0, nb, p->d_Linv.p + (size_t)kb * NB * NB,
-                                                                  p->d_tmp_c.p, p->d_yc.p);
+    const int k0 = kb * PB, nb = std::min(PB, n - k0);
+    chol_back128_kernel<<<std::max(1, DivUp(k0, 256)), 256, 0, st>>>(S, n, ld, k0, nb, p->d_Linv.p + (size_t)kb * PB * PB,
+                                                                   p->d_tmp_c.p, p->d_yc.p);
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());
+  if (want_trace) {
+    long long h[32];
+    SBA_CUDA(cudaMemcpyAsync(h, trace.p, sizeof(h), cudaMemcpyDeviceToHost, st));
+    SBA_CUDA(cudaStreamSynchronize(st));
+    std::fprintf(stderr, "[chol trace] diag128 panel 1, us between phase stamps (load | per 32-block: chol+inv, rows, update | X rows | store):");
+    for (int i = 1; i < 32 && h[i]; ++i) std::fprintf(stderr, " %.1f", (h[i] - h[i - 1]) * 1e-3);
+    std::fprintf(stderr, "\n");
+  }
   return SBA_OK;
 }
 

@@ -321,7 +321,7 @@ cudaError_t DownloadLarge(void* dst, const void* src, size_t bytes, cudaStream_t
     cudaSetDevice(dev);
     cudaStream_t cs;
     if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { err.store((int)cudaErrorUnknown); return; }
-    size_t pending[kStageDepth]; bool has[kStageDepth] = {};
+    size_t pending[kStageDepth] = {}; bool has[kStageDepth] = {};
     auto drain = [&](int d) {
       if (!has[d]) return;
       cudaError_t e = cudaEventSynchronize(g_stage.ev[t][d]);
@@ -358,6 +358,8 @@ Problem::~Problem() {
   if (stream) cudaStreamSynchronize(stream);  // buffers go back to the pool only once nothing uses them
   DropGraphs();
   CommDestroy(this);
+  if (stream2) { cudaStreamSynchronize(stream2); cudaStreamDestroy(stream2); }
+  for (auto& e : ev_chol) if (e) cudaEventDestroy(e);
   if (stream && h_scalars) {
     std::lock_guard<std::mutex> lk(g_ctx_mu);
     g_ctx_free.push_back(Ctx{device, stream, h_scalars});

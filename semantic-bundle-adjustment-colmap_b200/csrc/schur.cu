@@ -457,9 +457,9 @@ __global__ void __launch_bounds__(128) schur_pair_mma_kernel(int n_seg, const in
   }
 }
 
-__global__ void add_diag_dense_kernel(int n, double* __restrict__ S, const double* __restrict__ Dc) {
+__global__ void add_diag_dense_kernel(int n, int ld, double* __restrict__ S, const double* __restrict__ Dc) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j < n) S[(size_t)j * n + j] += Dc[j] * Dc[j];
+  if (j < n) S[(size_t)j * ld + j] += Dc[j] * Dc[j];
 }
 
 // block-Jacobi: add D^2, invert every block (dim <= 12) through its Cholesky factor
@@ -604,19 +604,19 @@ static int Accumulate(Problem* p, const PairList& L, const Sink& sink, bool with
 int BuildDenseSchur(Problem* p, bool with_rhs) {
   int rc = BuildPairLists(p, true);
   if (rc) return rc;
-  const size_t n = p->n_cdim;
-  SBA_CUDA(p->d_S.Alloc(std::max<size_t>(1, (n + 1) * n)));  // + one row: the right-hand side (cholesky.cu)
-  SBA_CUDA(cudaMemsetAsync(p->d_S.p, 0, n * n * sizeof(double), p->stream));
+  const size_t n = p->n_cdim, ld = DenseLd((int)n);
+  SBA_CUDA(p->d_S.Alloc(std::max<size_t>(1, (n + 1) * ld)));  // + one row: the right-hand side (cholesky.cu)
+  SBA_CUDA(cudaMemsetAsync(p->d_S.p, 0, n * ld * sizeof(double), p->stream));
   Sink sink;
   std::memset(&sink, 0, sizeof(sink));
-  sink.kind = 0; sink.S = p->d_S.p; sink.n = (int)n; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
+  sink.kind = 0; sink.S = p->d_S.p; sink.n = (int)ld; sink.shared_intr = p->shared_intrinsics ? 1 : 0;
   rc = Accumulate(p, p->pairs_dense, sink, with_rhs);
   if (rc) return rc;
   if (p->rhs_from_schur) p->rhs_unreduced = p->comm != nullptr;
-  rc = AllReduceSumWithRhs(p, p->d_S.p, n * n);  // the row behind S carries the reduced right-hand side along
+  rc = AllReduceSumWithRhs(p, p->d_S.p, n * ld);  // the row behind S carries the reduced right-hand side along
   if (rc) return rc;
   p->chol_add_diag = (int)n <= kCholSmallMax;  // the small-system Cholesky adds D^2 while loading its diagonal tiles
-  if (n > 0 && !p->chol_add_diag) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, p->d_S.p, p->d_Dc.p); p->launches++; }
+  if (n > 0 && !p->chol_add_diag) { add_diag_dense_kernel<<<DivUp(n, 256), 256, 0, p->stream>>>((int)n, (int)ld, p->d_S.p, p->d_Dc.p); p->launches++; }
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }

@@ -234,6 +234,8 @@ struct Problem {
   void DropGraphs();
 
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;           // side stream of the blocked Cholesky's panel chain (cholesky.cu), forked from `stream`
+  cudaEvent_t ev_chol[2] = {};
   int device = 0;
   int n_sm = 148;                           // multiprocessors of `device`
   int64_t launches = 0;
@@ -312,6 +314,9 @@ int CholeskySolve(Problem* p);  // d_S, d_rhs -> d_yc ; sets scalars.chol_fail
 // chol_small.cu
 constexpr int kCholSmallMax = 1024;
 int CholeskySolveSmall(Problem* p);  // n_cdim <= kCholSmallMax: one dataflow kernel
+// leading dimension of the dense reduced camera matrix d_S ((n + 1) rows: the last one is the right-hand side): n, rounded
+// up to even for the blocked factorisation so that every row starts on a 16-byte boundary (cp.async / double2 moves)
+inline int DenseLd(int n) { return n > kCholSmallMax ? (n + 1) / 2 * 2 : n; }
 // pcg.cu
 int SolvePCG(Problem* p, const sba_solver_options& o, int* iters);
 int SolvePCGBlocks(Problem* p, const sba_solver_options& o);  // pcg_blocks.cu: one persistent kernel on the block-sparse S
