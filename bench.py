@@ -441,6 +441,11 @@ def run_b200(args, m):
                          "ms_per_step": pg_s / e2e_steps * 1e3, "steps": e2e_steps,
                          "host_memory": "pageable numpy arrays (a COLMAP caller's std::vector)", "phases_ms": pg_phases},
         "roofline": roof, "stages": table, "final_cost": summ.final_cost,
+        # per-stage device time of the LAST timed solve (CUDA events between the stages; all zero when the iteration
+        # replays as a CUDA graph -- run with SBA_NO_GRAPHS=1 to fill them)
+        "solve_stage_ms": {"evaluate": summ.time_evaluate_s * 1e3, "eliminate": summ.time_eliminate_s * 1e3,
+                           "linear_solve": summ.time_linear_solve_s * 1e3, "update": summ.time_update_s * 1e3,
+                           "device_total": summ.device_time_s * 1e3},
     }
     if world > 1:
         # correctness gate of the sharded solve: rank 0 solves the SAME problem unsharded on its own GPU
