@@ -332,6 +332,62 @@ typedef struct sba_semantic_desc {
 int sba_semantic_evaluate(const sba_semantic_desc* d, double* residuals, int32_t* status,
                           double* jac, double* ms_device);
 
+/* --- SemanticBundleAdjuster as a solve (reference a11) -------------------
+ * src/optim/semantic_bundle_adjustment.cc:430-544 (Solve), :646-668 (SetUp: all ordered image pairs), :699-906
+ * (AddImagePairToProblem: grid of error_computation_pixel_step, zero-depth skip, constant-first / constant-second /
+ * both-variable functor), :670-693 (manifolds).  Pose-only problem: one residual block per (ordered pair, grid pixel with
+ * depth), central numeric differentiation, LM on the dense normal equations of the pose blocks (no point blocks to
+ * eliminate: SURVEY.md App. B.1).  Poses are updated IN PLACE, as the reference mutates the Reconstruction; the
+ * quaternions of all images are normalised first (:729-730).  Intrinsics are constant SIMPLE_PINHOLE (:604-644).
+ * Returns SBA_ERR_EMPTY_PROBLEM when no residual block remains (Solve returns false, :484-486). */
+typedef struct sba_semantic_problem {
+  int32_t num_images;            /* config_.Images() in iteration order */
+  int32_t height, width;
+  double* image_qvec;            /* [num_images*4] in / out */
+  double* image_tvec;            /* [num_images*3] in / out */
+  const double* camera_params;   /* [num_images*3] f, cx, cy of each image's camera */
+  const float* depth_maps;       /* [num_images*H*W] ROW-major (y*W+x) */
+  const float* semantic_maps;    /* [num_images*H*W] ROW-major */
+  const uint8_t* image_pose_constant;      /* [num_images] !refine_extrinsics || HasConstantPose; NULL = none */
+  const uint8_t* image_tvec_constant_mask; /* [num_images] bit k: tvec[k] constant (SetConstantTvec); NULL = none */
+  int32_t pixel_step;            /* error_computation_pixel_step, 10 (semantic_bundle_adjustment.h:83) */
+  double depth_error_threshold;  /* 2.0 (:78) */
+  double relative_step_size;     /* numeric_relative_step_size, 1e-3 (:89) */
+} sba_semantic_problem;
+
+/* opts: loss, iteration limits, tolerances as for sba_solve (linear_solver_type only names the policy: every choice is a
+ * dense Cholesky of the pose system here).  trace (nullable) receives up to trace_cap rows of the iteration table. */
+int sba_semantic_solve(const sba_semantic_problem* problem, const sba_solver_options* opts, sba_iteration_callback cb,
+                       void* user, sba_summary* summary, sba_iteration_summary* trace, int32_t trace_cap, int32_t* trace_n);
+
+/* --- GeometricSemanticBundleAdjuster as a solve (reference a12 + a13) ----
+ * src/optim/geometric_semantic_bundle_adjustment.cc:481-604 (Solve), :714-726 (ScaledLoss(nullptr, 1 / N_images) on every
+ * IoU block), :835-996 (per image x cylinder one of three functors: constant camera / both variable / constant
+ * geometry, for Cylinder and for CylinderBy2Points -- the five functors of geometric_semantic_cost_functions.h:33-348),
+ * :1126-1213 (QuaternionManifold on the cylinder quaternion, lower bound 0 on the radius), :670-693 pose manifolds.
+ * One residual 1 - IoU per (image, cylinder), central numeric differentiation, dense LM over poses and cylinders.
+ * The radius bound is enforced by clamping in Plus.  Only the TRIVIAL loss is legal (:699-706).
+ * The optional landmark blocks (include_landmark_error, default false, :729-794) are NOT part of this entry point.
+ * Poses and cylinders are updated in place. */
+typedef struct sba_cylinder_problem {
+  int32_t num_images;
+  int32_t height, width;
+  double* image_qvec;            /* [num_images*4] in / out (normalised first, :849) */
+  double* image_tvec;            /* [num_images*3] in / out */
+  const double* camera_params;   /* [num_images*3] */
+  const uint8_t* masks;          /* [num_images*H*W] ROW-major, non-zero = label == trunk_semantic_class (:1328-1333) */
+  const uint8_t* image_pose_constant;
+  const uint8_t* image_tvec_constant_mask;
+  int32_t num_cylinders;
+  int32_t cylinder_kind;         /* 0: Cylinder (qvec, tvec, radius, height); 1: CylinderBy2Points (tvec_1, tvec_2, radius) */
+  double* cylinder_params;       /* [num_cylinders*9] in / out; kind 0: q(4) t(3) r h; kind 1: t1(3) t2(3) r, two unused */
+  int32_t refine_geometry;       /* options_.refine_geometry (geometric_semantic_bundle_adjustment.h:78) */
+  double relative_step_size;     /* 1e-3 (:111) */
+} sba_cylinder_problem;
+
+int sba_cylinder_solve(const sba_cylinder_problem* problem, const sba_solver_options* opts, sba_iteration_callback cb,
+                       void* user, sba_summary* summary, sba_iteration_summary* trace, int32_t trace_cap, int32_t* trace_n);
+
 /* --- cylinder IoU residual (reference a12) ------------------------------
  * 1 - IoU of the projected cylinder quadrilateral against a boolean mask,
  * src/util/cylinder.h:27-121, 352-540. */

@@ -53,6 +53,12 @@ def load(capi):
     lib.oracle_ba_time_linearize.restype = C.c_double
     lib.oracle_semantic_evaluate.argtypes = [C.POINTER(capi.SemanticDesc), C.c_int, dp, ip, dp]
     lib.oracle_cylinder_evaluate.argtypes = [C.POINTER(capi.CylinderDesc), C.c_int, dp, dp]
+    lib.oracle_semantic_solve.argtypes = [C.POINTER(capi.SemanticProblem), C.POINTER(capi.SolverOptions), C.c_int,
+                                          C.POINTER(capi.Summary), C.POINTER(capi.IterationSummary), C.c_int, ip]
+    lib.oracle_semantic_solve.restype = C.c_int
+    lib.oracle_cylinder_solve.argtypes = [C.POINTER(capi.CylinderProblem), C.POINTER(capi.SolverOptions), C.c_int,
+                                          C.POINTER(capi.Summary), C.POINTER(capi.IterationSummary), C.c_int, ip]
+    lib.oracle_cylinder_solve.restype = C.c_int
     lib.oracle_draw_quadrilateral.argtypes = [dp, C.c_int, C.c_int, C.POINTER(C.c_uint8)]
     lib.oracle_cylinder_quadrilateral.argtypes = [dp, dp, dp, dp, dp, C.c_double, C.c_double, dp]
     lib.oracle_cylinder_quadrilateral.restype = C.c_int

@@ -110,6 +110,26 @@ class SemanticDesc(C.Structure):
     ]
 
 
+class SemanticProblem(C.Structure):
+    _fields_ = [
+        ("num_images", C.c_int32), ("height", C.c_int32), ("width", C.c_int32),
+        ("image_qvec", _dp), ("image_tvec", _dp), ("camera_params", _dp),
+        ("depth_maps", _fp), ("semantic_maps", _fp),
+        ("image_pose_constant", _u8p), ("image_tvec_constant_mask", _u8p),
+        ("pixel_step", C.c_int32), ("depth_error_threshold", C.c_double), ("relative_step_size", C.c_double),
+    ]
+
+
+class CylinderProblem(C.Structure):
+    _fields_ = [
+        ("num_images", C.c_int32), ("height", C.c_int32), ("width", C.c_int32),
+        ("image_qvec", _dp), ("image_tvec", _dp), ("camera_params", _dp), ("masks", _u8p),
+        ("image_pose_constant", _u8p), ("image_tvec_constant_mask", _u8p),
+        ("num_cylinders", C.c_int32), ("cylinder_kind", C.c_int32), ("cylinder_params", _dp),
+        ("refine_geometry", C.c_int32), ("relative_step_size", C.c_double),
+    ]
+
+
 class CylinderDesc(C.Structure):
     _fields_ = [
         ("num_images", C.c_int32), ("height", C.c_int32), ("width", C.c_int32),
@@ -164,6 +184,10 @@ SYMBOLS = {
     "sba_shard_points": (C.c_int, [C.POINTER(ProblemDesc), C.c_int32, C.c_int32, _u8p, _u8p]),
     "sba_semantic_evaluate": (C.c_int, [C.POINTER(SemanticDesc), _dp, _ip, _dp, _dp]),
     "sba_cylinder_evaluate": (C.c_int, [C.POINTER(CylinderDesc), _dp, _dp, _dp]),
+    "sba_semantic_solve": (C.c_int, [C.POINTER(SemanticProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,
+                                     C.POINTER(Summary), C.POINTER(IterationSummary), C.c_int32, _ip]),
+    "sba_cylinder_solve": (C.c_int, [C.POINTER(CylinderProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,
+                                     C.POINTER(Summary), C.POINTER(IterationSummary), C.c_int32, _ip]),
     "sba_rig_evaluate": (C.c_int, [C.POINTER(RigDesc), _dp, _dp, _dp]),
 }
 
