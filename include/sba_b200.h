@@ -414,6 +414,14 @@ typedef struct sba_cylinder_desc {
 int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residuals, double* jac,
                           double* ms_device);
 
+/* Parity surface of the two halves of the cylinder residual:
+ *   sba_cylinder_quadrilateral: Cylinder::ProjectToQuadrilateral (src/util/cylinder.h:352-474) per block -> pts8
+ *     [num_blocks*8] (x, y of the four vertices) and ok [num_blocks] (0 where the reference throws);
+ *   sba_draw_quadrilateral: drawQuadrilateral (src/util/cylinder.h:27-121) of four given vertices into a row-major
+ *     height x width mask (1 inside) -- identical vertices must give identical masks on both sides. */
+int sba_cylinder_quadrilateral(const sba_cylinder_desc* d, double* pts8, int32_t* ok);
+int sba_draw_quadrilateral(const double* pts8, int32_t height, int32_t width, uint8_t* mask);
+
 /* --- camera-rig reprojection functor (reference a3) ----------------------
  * RigBundleAdjustmentCostFunction, src/base/cost_functions.h:160-214: composed pose
  * q = rel_q (x) rig_q, t = R(rel_q) rig_t + rel_t, then the reprojection residual.  Evaluates a batch of

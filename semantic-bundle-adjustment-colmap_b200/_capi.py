@@ -184,6 +184,8 @@ SYMBOLS = {
     "sba_shard_points": (C.c_int, [C.POINTER(ProblemDesc), C.c_int32, C.c_int32, _u8p, _u8p]),
     "sba_semantic_evaluate": (C.c_int, [C.POINTER(SemanticDesc), _dp, _ip, _dp, _dp]),
     "sba_cylinder_evaluate": (C.c_int, [C.POINTER(CylinderDesc), _dp, _dp, _dp]),
+    "sba_cylinder_quadrilateral": (C.c_int, [C.POINTER(CylinderDesc), _dp, _ip]),
+    "sba_draw_quadrilateral": (C.c_int, [_dp, C.c_int32, C.c_int32, _u8p]),
     "sba_semantic_solve": (C.c_int, [C.POINTER(SemanticProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,
                                      C.POINTER(Summary), C.POINTER(IterationSummary), C.c_int32, _ip]),
     "sba_cylinder_solve": (C.c_int, [C.POINTER(CylinderProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,

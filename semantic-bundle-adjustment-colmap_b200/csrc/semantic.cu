@@ -295,3 +295,72 @@ extern "C" int sba_cylinder_evaluate(const sba_cylinder_desc* d, double* residua
   cudaStreamDestroy(st);
   return SBA_OK;
 }
+
+// ---- parity surface of the two halves of the cylinder residual ---------------------------------------------------
+namespace sba {
+__global__ void cyl_quad_kernel(int64_t n_blocks, CylView V, double* __restrict__ pts, int* __restrict__ ok) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_blocks) return;
+  const int im = V.b_img[k], cy = V.b_cyl[k];
+  double x[16];
+  for (int j = 0; j < 4; ++j) { x[j] = V.q[4 * im + j]; x[7 + j] = V.cq[4 * cy + j]; }
+  for (int j = 0; j < 3; ++j) { x[4 + j] = V.t[3 * im + j]; x[11 + j] = V.ct[3 * cy + j]; }
+  x[14] = V.cr[cy]; x[15] = V.ch[cy];
+  double p8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  ok[k] = CylinderQuad(x, V.cam + 3 * im, p8) ? 1 : 0;
+  for (int j = 0; j < 8; ++j) pts[k * 8 + j] = p8[j];
+}
+__global__ void __launch_bounds__(256) quad_draw_kernel(const double* __restrict__ pts8, int H, int W, uint8_t* __restrict__ mask) {
+  __shared__ QuadRaster R;
+  if (threadIdx.x == 0) BuildRaster(pts8, H, W, &R);
+  __syncthreads();
+  for (int idx = blockIdx.x * 256 + threadIdx.x; idx < H * W; idx += gridDim.x * 256) {
+    const int y = idx / W, x = idx - y * W;
+    mask[idx] = (InBox(R.bb, x, y) && RasterInside(R, x, y)) ? 1 : 0;
+  }
+}
+}  // namespace sba
+
+extern "C" int sba_cylinder_quadrilateral(const sba_cylinder_desc* d, double* pts8, int32_t* ok) {
+  if (!d || !pts8 || !ok || d->num_blocks < 0) { SetError(SBA_ERR_INVALID_ARGUMENT, "bad arguments"); return SBA_ERR_INVALID_ARGUMENT; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback"); return SBA_ERR_NO_DEVICE; }
+  const int64_t nb = d->num_blocks;
+  if (nb == 0) return SBA_OK;
+  cudaStream_t st = nullptr;
+  DevBuf<double> dq, dt, dc, dcq, dct, dcr, dch, dpts;
+  DevBuf<int> dbi, dbc, dok;
+  auto up = [&](auto& buf, const auto* src, size_t n) -> cudaError_t {
+    cudaError_t e = buf.Alloc(n);
+    if (e != cudaSuccess || !src || n == 0) return e;
+    return cudaMemcpy(buf.p, src, n * sizeof(*src), cudaMemcpyHostToDevice);
+  };
+  const size_t n_img = d->num_images, n_cyl = d->num_cylinders;
+  SBA_CUDA(up(dq, d->image_qvec, n_img * 4)); SBA_CUDA(up(dt, d->image_tvec, n_img * 3)); SBA_CUDA(up(dc, d->camera_params, n_img * 3));
+  SBA_CUDA(up(dcq, d->cyl_qvec, n_cyl * 4)); SBA_CUDA(up(dct, d->cyl_tvec, n_cyl * 3));
+  SBA_CUDA(up(dcr, d->cyl_radius, n_cyl)); SBA_CUDA(up(dch, d->cyl_height, n_cyl));
+  SBA_CUDA(up(dbi, d->block_image, nb)); SBA_CUDA(up(dbc, d->block_cylinder, nb));
+  SBA_CUDA(dpts.Alloc(nb * 8)); SBA_CUDA(dok.Alloc(nb));
+  CylView V;
+  V.H = d->height; V.W = d->width; V.q = dq.p; V.t = dt.p; V.cam = dc.p; V.masks = nullptr; V.pos_count = nullptr;
+  V.cq = dcq.p; V.ct = dct.p; V.cr = dcr.p; V.ch = dch.p; V.b_img = dbi.p; V.b_cyl = dbc.p; V.rel = d->relative_step_size;
+  cyl_quad_kernel<<<DivUp(nb, 128), 128, 0, st>>>(nb, V, dpts.p, dok.p);
+  SBA_CUDA(cudaGetLastError());
+  SBA_CUDA(cudaMemcpy(pts8, dpts.p, nb * 8 * sizeof(double), cudaMemcpyDeviceToHost));
+  SBA_CUDA(cudaMemcpy(ok, dok.p, nb * sizeof(int), cudaMemcpyDeviceToHost));
+  return SBA_OK;
+}
+
+extern "C" int sba_draw_quadrilateral(const double* pts8, int32_t height, int32_t width, uint8_t* mask) {
+  if (!pts8 || !mask || height <= 0 || width <= 0) { SetError(SBA_ERR_INVALID_ARGUMENT, "bad arguments"); return SBA_ERR_INVALID_ARGUMENT; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback"); return SBA_ERR_NO_DEVICE; }
+  DevBuf<double> dp;
+  DevBuf<uint8_t> dm;
+  SBA_CUDA(dp.Alloc(8)); SBA_CUDA(dm.Alloc((size_t)height * width));
+  SBA_CUDA(cudaMemcpy(dp.p, pts8, 8 * sizeof(double), cudaMemcpyHostToDevice));
+  quad_draw_kernel<<<64, 256>>>(dp.p, height, width, dm.p);
+  SBA_CUDA(cudaGetLastError());
+  SBA_CUDA(cudaMemcpy(mask, dm.p, (size_t)height * width, cudaMemcpyDeviceToHost));
+  return SBA_OK;
+}

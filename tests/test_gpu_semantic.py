@@ -145,15 +145,36 @@ def test_cylinder_iou_parity(sba, oracle):
     d.num_blocks = 9
     d.block_image, d.block_cylinder = capi.ptr(keep[8], capi._ip), capi.ptr(keep[9], capi._ip)
     d.relative_step_size = 1e-3
+    lib = capi.load()
+    # (1) the quadrilateral: device vertices against the oracle's, block by block
+    pg, okg = np.zeros((9, 8)), np.zeros(9, np.int32)
+    capi.check(lib.sba_cylinder_quadrilateral(C.byref(d), capi.ptr(pg, capi._dp), capi.ptr(okg, capi._ip)))
+    po = np.zeros((9, 8))
+    for k in range(9):
+        i, c = bi[k], bc[k]
+        ok = oracle.oracle_cylinder_quadrilateral(capi.ptr(q[i].copy(), capi._dp), capi.ptr(t[i].copy(), capi._dp),
+                                                  capi.ptr(cams[i].copy(), capi._dp), capi.ptr(cq[c].copy(), capi._dp),
+                                                  capi.ptr(ct[c].copy(), capi._dp), cr[c], ch[c], capi.ptr(pts, capi._dp))
+        assert ok == 1 and okg[k] == 1
+        po[k] = pts
+    assert np.abs(pg - po).max() <= 1e-11   # pixels; acos / sin / cos of the device and of libm differ by ulps
+    # (2) the rasteriser: IDENTICAL vertices in, identical masks out (drawQuadrilateral is integer work on given doubles)
+    for k in range(9):
+        mg, mo = np.zeros((H, W), np.uint8), np.zeros((H, W), np.uint8)
+        capi.check(lib.sba_draw_quadrilateral(capi.ptr(po[k].copy(), capi._dp), H, W, capi.ptr(mg, capi._u8p)))
+        oracle.oracle_draw_quadrilateral(capi.ptr(po[k].copy(), capi._dp), H, W, mo.ctypes.data_as(C.POINTER(C.c_uint8)))
+        assert mo.sum() > 50 and np.array_equal(mg, mo)
+    # (3) the residual 1 - IoU and its central differences: pixel counts are integers, so blocks whose vertices agree
+    # BITWISE must agree exactly; the others to the count one boundary pixel can move
     rg, jg, ro, jo = np.zeros(9), np.zeros((9, 16)), np.zeros(9), np.zeros((9, 16))
-    capi.check(capi.load().sba_cylinder_evaluate(C.byref(d), capi.ptr(rg, capi._dp), capi.ptr(jg, capi._dp), None))
+    capi.check(lib.sba_cylinder_evaluate(C.byref(d), capi.ptr(rg, capi._dp), capi.ptr(jg, capi._dp), None))
     oracle.oracle_cylinder_evaluate(C.byref(d), 0, capi.ptr(ro, capi._dp), capi.ptr(jo, capi._dp))
     assert ((ro > 0) & (ro < 1)).sum() >= 3 and np.count_nonzero(jo) > 0
-    # pixel counts are integers: equal unless a vertex sits within an ulp of a pixel boundary (acos/sin/cos differ by ulps)
-    assert np.allclose(rg, ro, rtol=0, atol=2e-3)
-    assert (rg == ro).sum() >= 7
-    close = np.isclose(jg, jo, rtol=1e-6, atol=1e-9)
-    assert close.mean() > 0.9
+    same = np.all(pg == po, axis=1)
+    assert np.array_equal(rg[same], ro[same])
+    assert np.array_equal(rg, ro), (rg - ro, np.abs(pg - po).max(axis=1))
+    # central differences over 32 perturbed evaluations per block: the same deltas, the same counts
+    assert np.array_equal(jg, jo), np.argwhere(jg != jo)
 
 
 def test_semantic_bilinear_rows(sba, oracle):

@@ -169,7 +169,7 @@ def test_semantic_solve_parity(sba, oracle, variant):
     assert rco == 0 and rcg == 0
     assert (sg.num_residual_blocks, sg.num_effective_parameters_reduced, sg.num_parameters_reduced) == \
            (so.num_residual_blocks, so.num_effective_parameters_reduced, so.num_parameters_reduced)
-    assert sg.initial_cost == so.initial_cost and so.num_successful_steps >= 1
+    assert sg.initial_cost == pytest.approx(so.initial_cost, rel=1e-12) and so.num_successful_steps >= 1
     _same_trace(trg, tro)
     assert np.allclose(kg[0], ko[0], atol=1e-9) and np.allclose(kg[1], ko[1], atol=1e-9)
 
