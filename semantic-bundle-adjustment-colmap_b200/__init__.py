@@ -15,3 +15,4 @@ from . import scene  # noqa: F401
 from . import model_io  # noqa: F401
 from . import filters  # noqa: F401
 from . import bundle_adjustment  # noqa: F401
+from . import semantic_adjusters  # noqa: F401  (SemanticBundleAdjuster / GeometricSemanticBundleAdjuster as solves)

@@ -13,6 +13,7 @@
 #include <limits>
 #include <stdexcept>
 #include <unordered_map>
+#include <string>
 #include <vector>
 
 #include "sba_b200.h"
@@ -128,6 +129,8 @@ class Image {
   void SetImageId(image_t id) { image_id_ = id; }
   camera_t CameraId() const { return camera_id_; }
   void SetCameraId(camera_t id) { camera_id_ = id; }
+  const std::string& Name() const { return name_; }   // src/base/image.h:150-152: keys the map tables of the semantic adjusters
+  void SetName(const std::string& name) { name_ = name; }
   Vector4d& Qvec() { return qvec_; }
   const Vector4d& Qvec() const { return qvec_; }
   Vector3d& Tvec() { return tvec_; }
@@ -152,6 +155,7 @@ class Image {
  private:
   image_t image_id_ = 0;
   camera_t camera_id_ = 0;
+  std::string name_;
   Vector4d qvec_{{1, 0, 0, 0}};
   Vector3d tvec_{{0, 0, 0}};
   std::vector<class Point2D> points2D_;

@@ -10,6 +10,7 @@
 
 #include "mock_reconstruction.h"
 #include "sba_bundle_adjuster.h"
+#include "sba_semantic_adjusters.h"
 
 using namespace sba_mock;
 using sba_shim::BundleAdjustmentConfig;
@@ -240,15 +241,148 @@ static void TestSolve() {
   }
 }
 
+// ---- the two semantic adjusters through their class shims (shim/sba_semantic_adjusters.h) ----------------------
+using SemanticBundleAdjuster = sba_shim::SemanticBundleAdjusterT<Reconstruction>;
+using GeometricSemanticBundleAdjuster = sba_shim::GeometricSemanticBundleAdjusterT<Reconstruction>;
+
+// n cameras with identity rotation at t = (tx, ty, 0.5 i) looking at the world plane Z = 5 carrying a checker of
+// labels; the depth of every pixel is then 5 + t_z, and the world point of pixel (x, y) is (u d - t_x, v d - t_y, 5).
+static void SemanticScene(int n, int H, int W, Reconstruction* rec, std::vector<sba_shim::FloatMap>* depth,
+                          std::vector<sba_shim::FloatMap>* label) {
+  const double f = 1.2 * W, cx = W / 2.0, cy = H / 2.0;
+  for (int i = 0; i < n; ++i) {
+    Camera cam;
+    cam.SetCameraId(static_cast<camera_t>(i)); cam.SetModelId(SBA_SIMPLE_PINHOLE); cam.Params() = {f, cx, cy};
+    rec->AddCamera(cam);
+    Image im;
+    im.SetImageId(static_cast<image_t>(i)); im.SetCameraId(static_cast<camera_t>(i)); im.SetName("img" + std::to_string(i) + ".png");
+    im.Tvec() = {{0.1 * i, -0.07 * i, 0.5 * i}};
+    rec->AddImage(im);
+    sba_shim::FloatMap d, l;
+    d.height = l.height = H; d.width = l.width = W;
+    d.data.assign(static_cast<size_t>(H) * W, static_cast<float>(5.0 + 0.5 * i)); l.data.resize(static_cast<size_t>(H) * W);
+    for (int y = 0; y < H; ++y)
+      for (int x = 0; x < W; ++x) {
+        const double dd = 5.0 + 0.5 * i, X = (x - cx) / f * dd - 0.1 * i, Y = (y - cy) / f * dd + 0.07 * i;
+        l.data[static_cast<size_t>(y) * W + x] = static_cast<float>((static_cast<long>(std::floor(X * 3.0)) + 3 * static_cast<long>(std::floor(Y * 3.0))) % 5 + 10);
+      }
+    depth->push_back(d); label->push_back(l);
+  }
+}
+
+static BundleAdjustmentConfig SemanticViews(int n) {
+  BundleAdjustmentConfig c;
+  for (int i = 0; i < n; ++i) { c.AddImage(static_cast<image_t>(i)); c.SetConstantCamera(static_cast<camera_t>(i)); }
+  c.SetConstantPose(0);
+  return c;
+}
+
+static void TestSemanticHost() {
+  Reconstruction rec;
+  std::vector<sba_shim::FloatMap> depth, label;
+  SemanticScene(3, 48, 64, &rec, &depth, &label);
+  auto throws = [&](const sba_shim::SemanticBundleAdjustmentOptions& o, const BundleAdjustmentConfig& c, Reconstruction* r) {
+    try { SemanticBundleAdjuster ba(o, c); for (int i = 0; i < 3; ++i) ba.SetMaps(r->Image(i).Name(), depth[i], label[i]); ba.Solve(r); }
+    catch (const std::runtime_error&) { return true; }
+    return false;
+  };
+  sba_shim::SemanticBundleAdjustmentOptions o;
+  CHECK_THAT(o.solver_options.function_tolerance == 1e-8 && o.solver_options.update_state_every_iteration);  // :116-127
+  CHECK_THAT(o.error_computation_pixel_step == 10 && o.depth_error_threshold == 2 && o.numeric_relative_step_size == 1e-3);
+  {  // Assert (semantic_bundle_adjustment.cc:604-644): intrinsics must be constant, SIMPLE_PINHOLE, refine_extrinsics
+    BundleAdjustmentConfig c = SemanticViews(3);
+    c.SetVariableCamera(1);
+    CHECK_THAT(throws(o, c, &rec));
+    Reconstruction other = rec;
+    other.Camera(2).SetModelId(SBA_SIMPLE_RADIAL);
+    CHECK_THAT(throws(o, SemanticViews(3), &other));
+    sba_shim::SemanticBundleAdjustmentOptions o2 = o;
+    o2.refine_extrinsics = false;
+    CHECK_THAT(throws(o2, SemanticViews(3), &rec));
+  }
+  sba_shim::GeometricSemanticBundleAdjustmentOptions g;
+  CHECK_THAT(g.trunk_semantic_class == 250. && g.refine_geometry && !g.include_landmark_error);
+}
+
+struct CountCalls : sba_shim::IterationCallback {
+  int calls = 0;
+  sba_shim::CallbackReturnType operator()(const sba_shim::IterationSummary&) override { ++calls; return sba_shim::SOLVER_CONTINUE; }
+};
+
+static void TestSemanticSolve() {
+  {  // SemanticBundleAdjuster::Solve on the device: poses move, the constant one does not, the cost does not go up
+    Reconstruction rec;
+    std::vector<sba_shim::FloatMap> depth, label;
+    SemanticScene(3, 96, 128, &rec, &depth, &label);
+    rec.Image(1).Tvec()[0] += 0.04; rec.Image(2).Tvec()[1] -= 0.05;  // the error to remove
+    const Reconstruction orig = rec;
+    sba_shim::SemanticBundleAdjustmentOptions o;
+    o.error_computation_pixel_step = 4;
+    o.solver_options.max_num_iterations = 15;
+    CountCalls cb;
+    o.solver_options.callbacks.push_back(&cb);
+    SemanticBundleAdjuster ba(o, SemanticViews(3));
+    for (int i = 0; i < 3; ++i) ba.SetMaps(rec.Image(i).Name(), depth[i], label[i]);
+    CHECK_THAT(ba.Solve(&rec));
+    const auto& s = ba.Summary();
+    CHECK_THAT(s.num_residual_blocks == 6 * 24 * 32 && s.num_effective_parameters_reduced == 12);
+    CHECK_THAT(s.final_cost < s.initial_cost && s.num_successful_steps >= 1);
+    CHECK_THAT(cb.calls == static_cast<int>(s.iterations.size()) && cb.calls >= 2);
+    CHECK_THAT(rec.Image(0).Tvec() == orig.Image(0).Tvec() && rec.Image(0).Qvec() == orig.Image(0).Qvec());
+    CHECK_THAT(rec.Image(1).Tvec() != orig.Image(1).Tvec());
+    std::printf("semantic: cost %.9g -> %.9g in %d iterations\n", s.initial_cost, s.final_cost, s.num_iterations);
+  }
+  {  // GeometricSemanticBundleAdjuster::Solve: masks = the library's own rasterisation of the true cylinder
+    Reconstruction rec;
+    std::vector<sba_shim::FloatMap> depth, label;
+    const int H = 96, W = 128;
+    SemanticScene(3, H, W, &rec, &depth, &label);
+    sba_shim::CylinderParams truth;
+    const double ang = 1.5707963267948966;
+    truth.v = {std::cos(ang / 2), std::sin(ang / 2), 0.0, 0.0, 0.1, 0.5, 5.0, 0.15, 1.2};  // axis towards -y, 5 m ahead
+    std::vector<sba_shim::FloatMap> sem(3);
+    for (int i = 0; i < 3; ++i) {
+      sba_cylinder_desc d{};
+      const double q[4] = {1, 0, 0, 0};
+      const double* t = rec.Image(i).Tvec().data();
+      const double cam[3] = {1.2 * W, W / 2.0, H / 2.0};
+      const int32_t bi = 0, bc = 0;
+      d.num_images = 1; d.height = H; d.width = W; d.image_qvec = q; d.image_tvec = t; d.camera_params = cam;
+      d.num_cylinders = 1; d.cyl_qvec = truth.v.data(); d.cyl_tvec = truth.v.data() + 4; d.cyl_radius = truth.v.data() + 7;
+      d.cyl_height = truth.v.data() + 8; d.num_blocks = 1; d.block_image = &bi; d.block_cylinder = &bc; d.relative_step_size = 1e-3;
+      double pts[8]; int32_t ok = 0;
+      CHECK_THAT(sba_cylinder_quadrilateral(&d, pts, &ok) == SBA_OK && ok == 1);
+      std::vector<uint8_t> m(static_cast<size_t>(H) * W);
+      CHECK_THAT(sba_draw_quadrilateral(pts, H, W, m.data()) == SBA_OK);
+      sem[i].height = H; sem[i].width = W; sem[i].data.resize(m.size());
+      for (size_t k = 0; k < m.size(); ++k) sem[i].data[k] = m[k] ? 250.f : 3.f;
+    }
+    sba_shim::GeometricSemanticBundleAdjustmentOptions o;
+    o.solver_options.max_num_iterations = 10;
+    GeometricSemanticBundleAdjuster ba(o, SemanticViews(3));
+    for (int i = 0; i < 3; ++i) ba.SetSemanticMap(rec.Image(i).Name(), sem[i]);
+    sba_shim::CylinderParams start = truth;
+    start.v[4] += 0.05; start.v[7] *= 1.3;  // shifted, too thick
+    ba.Cylinders().push_back(start);
+    CHECK_THAT(ba.Solve(&rec));
+    const auto& s = ba.Summary();
+    CHECK_THAT(s.num_residual_blocks == 3 && s.num_effective_parameters_reduced == 2 * 6 + 8);
+    CHECK_THAT(s.initial_cost > 0 && s.final_cost <= s.initial_cost && ba.Cylinders()[0].v[7] >= 0);
+    std::printf("cylinder: cost %.9g -> %.9g in %d iterations\n", s.initial_cost, s.final_cost, s.num_iterations);
+  }
+}
+
 int main(int argc, char** argv) {
   const bool solve = argc > 1 && std::strcmp(argv[1], "solve") == 0;
   TestCounts();
+  TestSemanticHost();
   if (solve) {
     if (sba_device_count() < 1) {
       std::printf("no CUDA device: the shim has no CPU solve\n");
       return 3;
     }
     TestSolve();
+    TestSemanticSolve();
   }
   std::printf("%s (%d failed)\n", g_failed ? "FAILED" : "OK", g_failed);
   return g_failed ? 1 : 0;

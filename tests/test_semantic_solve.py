@@ -209,3 +209,19 @@ def test_semantic_solve_callback_and_errors(sba, oracle):
     pg, kg = semantic_problem(sba, q, t, cams, depth, label, np.ones(3, np.uint8))
     rc, s, tr = _run(lib.sba_semantic_solve, pg, o, C.cast(None, capi.ITERATION_CALLBACK), None)
     assert rc == 5  # SBA_ERR_EMPTY_PROBLEM: Solve() returns false (semantic_bundle_adjustment.cc:484-486)
+
+
+@pytest.mark.gpu
+def test_python_wrappers(sba, oracle):
+    """semantic_adjusters.SemanticProblem / CylinderProblem: the Python mirror over the same two entry points."""
+    q, t, cams, depth, label = _perturbed_scene(sba, n_img=3, seed=1)
+    prob = sba.semantic_adjusters.SemanticProblem(q, t, cams, depth, label, image_pose_constant=[1, 0, 0], pixel_step=4)
+    s, rows = prob.solve(sba.semantic_adjusters.semantic_solver_options(10))
+    assert s is not None and s.final_cost <= s.initial_cost and len(rows) == s.num_iterations
+    assert np.array_equal(prob.image_tvec[0], t[0]) and not np.array_equal(prob.image_tvec, t) or s.num_successful_steps == 0
+    pc, keep = cylinder_problem(sba, oracle, kind=0)
+    cp = sba.semantic_adjusters.CylinderProblem(keep[0], keep[1], keep[2], keep[3], keep[6], image_pose_constant=[1, 0, 0])
+    s, rows = cp.solve(sba.semantic_adjusters.semantic_solver_options(6))
+    assert s is not None and s.num_residual_blocks == 9 and s.final_cost <= s.initial_cost
+    none, _ = sba.semantic_adjusters.SemanticProblem(q, t, cams, depth, label, image_pose_constant=[1, 1, 1]).solve()
+    assert none is None
