@@ -119,10 +119,21 @@ struct StructView {
 struct Row3View {
   D4* ES;             // [n_obs]
   D4* FS;             // [TilePad(n_obs) * FSUnits(dc)]
-  const float* maps;  // [n_img * H * W] row-major, top-down
+  const float* maps;  // [n_img * MapTiledSize(H, W)] top-down, in 8 x 4-texel tiles of 128 B (MapTexel below)
   int H, W;
   double weight;      // r_s = weight * bilinear(map_img, x, y)   (Bitmap::InterpolateBilinear convention, bitmap.cc:238-269)
 };
+
+// Label-map layout in HBM.  A bilinear sample reads a 2 x 2 texel footprint; in a row-major map its two rows are W * 4
+// bytes apart, i.e. two DRAM bursts per observation.  Tiles of 8 (x) by 4 (rows) texels = 128 B keep the footprint in
+// one burst for most samples (rows {0,1} and {2,3} of a tile share a 64 B half).
+constexpr int kMapTileW = 8, kMapTileH = 4;
+__host__ __device__ __forceinline__ size_t MapTiledSize(int H, int W) {
+  return (size_t)((H + kMapTileH - 1) / kMapTileH) * ((W + kMapTileW - 1) / kMapTileW) * (kMapTileW * kMapTileH);
+}
+__host__ __device__ __forceinline__ size_t MapTexel(int row, int x, int tiles_per_row) {
+  return ((size_t)(row >> 2) * tiles_per_row + (x >> 3)) * 32 + ((row & 3) << 3) + (x & 7);
+}
 
 struct LossView {
   int type;

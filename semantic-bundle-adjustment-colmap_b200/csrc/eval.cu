@@ -37,9 +37,10 @@ __device__ __forceinline__ bool BilinearWithGrad(const float* __restrict__ map, 
   if (!(fx >= 0.0 && fx + 1.0 < (double)W && fy >= 0.0 && fy + 1.0 < (double)H)) return false;
   const int x0 = (int)fx, y0 = (int)fy;
   const double dx = x - x0, dy = inv_y - y0, dx_1 = 1 - dx, dy_1 = 1 - dy;
-  const float* line0 = map + (size_t)(H - 1 - y0) * W + x0;
-  const float* line1 = line0 - W;  // scanline y0 + 1 is one row UP in the top-down map
-  const double a0 = __ldg(line0), a1 = __ldg(line0 + 1), b0 = __ldg(line1), b1 = __ldg(line1 + 1);
+  const int row0 = H - 1 - y0, row1 = row0 - 1;  // scanline y0 + 1 is one row UP in the top-down map
+  const int tpr = (W + kMapTileW - 1) / kMapTileW;
+  const double a0 = __ldg(map + MapTexel(row0, x0, tpr)), a1 = __ldg(map + MapTexel(row0, x0 + 1, tpr)),
+               b0 = __ldg(map + MapTexel(row1, x0, tpr)), b1 = __ldg(map + MapTexel(row1, x0 + 1, tpr));
   const double v0 = dx_1 * a0 + dx * a1;
   const double v1 = dx_1 * b0 + dx * b1;
   *val = dy_1 * v0 + dy * v1;
@@ -103,8 +104,9 @@ __device__ __forceinline__ void PickParam(const double (&Jk)[24], int amb, doubl
 #ifndef SBA_EVAL_MINB
 #define SBA_EVAL_MINB 4
 #endif
+// three-row instantiations: the three small models fit 128 registers without spills (4 CTAs / SM); the others keep 3
 template <int MODEL, int NR>
-__global__ void __launch_bounds__(kEvalThreads, NR == 3 ? 3 : SBA_EVAL_MINB)
+__global__ void __launch_bounds__(kEvalThreads, NR == 3 ? (MODEL <= 2 ? 4 : 3) : SBA_EVAL_MINB)
 eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_i,
             const double* __restrict__ scale_k, const unsigned long long* __restrict__ k_pack,
             const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F, Row3View R3,
@@ -174,7 +176,7 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
     double rs = 0.0, gx = 0.0, gy = 0.0;
     if (NR == 3) {
       double val;
-      if (BilinearWithGrad(R3.maps + (size_t)i * R3.H * R3.W, R3.H, R3.W, x, y, &val, &gx, &gy)) {
+      if (BilinearWithGrad(R3.maps + (size_t)i * MapTiledSize(R3.H, R3.W), R3.H, R3.W, x, y, &val, &gx, &gy)) {
         rs = R3.weight * val; gx *= R3.weight; gy *= R3.weight;
       } else { gx = 0.0; gy = 0.0; }
     }
@@ -346,7 +348,7 @@ cost_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restr
     double rs = 0.0;
     if (NR == 3) {
       double val, gx, gy;
-      if (BilinearWithGrad(R3.maps + (size_t)i * R3.H * R3.W, R3.H, R3.W, x, y, &val, &gx, &gy)) rs = R3.weight * val;
+      if (BilinearWithGrad(R3.maps + (size_t)i * MapTiledSize(R3.H, R3.W), R3.H, R3.W, x, y, &val, &gx, &gy)) rs = R3.weight * val;
     }
     double rho[3];
     LossEval(L.type, L.scale, r0 * r0 + r1 * r1 + rs * rs, rho);

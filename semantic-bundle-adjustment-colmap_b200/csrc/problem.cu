@@ -609,6 +609,19 @@ void ShardPointRange(const std::vector<int64_t>& pt_obs_prefix, int nranks, int 
   *p1 = std::min(std::max(cut(rank + 1), *p0), n_pt);
 }
 
+// row-major maps -> the tiled layout of common.cuh (MapTexel); padding texels are never sampled and stay 0
+__global__ void retile_maps_kernel(const float* __restrict__ src, float* __restrict__ dst, int n_img, int H, int W) {
+  const int tpr = (W + kMapTileW - 1) / kMapTileW;
+  const size_t per = MapTiledSize(H, W), total = per * n_img;
+  for (size_t o = blockIdx.x * (size_t)blockDim.x + threadIdx.x; o < total; o += (size_t)gridDim.x * blockDim.x) {
+    const size_t img = o / per, w = o - img * per;
+    const size_t tile = w >> 5;
+    const int in = (int)(w & 31);
+    const int row = (int)(tile / tpr) * kMapTileH + (in >> 3), x = (int)(tile % tpr) * kMapTileW + (in & 7);
+    dst[o] = (row < H && x < W) ? __ldg(src + (img * H + row) * (size_t)W + x) : 0.0f;
+  }
+}
+
 int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   HostTimer tm("create");
   int rc = Validate(dp);
@@ -621,6 +634,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   //      DMA runs under the host set-up below instead of after it ----
   DevBuf<int> raw_img, raw_pt;   // the caller's observation arrays on the device (released after the final sync)
   DevBuf<double> raw_xy;
+  DevBuf<float> map_stage;       // the caller's row-major label maps; re-tiled into d_sem_maps after the upload
 #define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); maps.Join(); cudaStreamSynchronize(CopyStream()); if (p->stream) cudaStreamSynchronize(p->stream); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
   struct MapUpload {
     std::thread th;
@@ -653,11 +667,12 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
     }
     if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) {
       const size_t n_map = (size_t)d.num_images * d.sem_height * d.sem_width;
-      cudaError_t e = p->d_sem_maps.Alloc(n_map);
+      cudaError_t e = map_stage.Alloc(n_map);
+      if (e == cudaSuccess) e = p->d_sem_maps.Alloc((size_t)d.num_images * MapTiledSize(d.sem_height, d.sem_width));
       if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("label maps: ") + cudaGetErrorString(e)); delete p; return SBA_ERR_CUDA; }
       p->sem_h = d.sem_height; p->sem_w = d.sem_width; p->sem_weight = d.sem_weight;
       const int dev = p->device;
-      float* dst = p->d_sem_maps.p;
+      float* dst = map_stage.p;
       const float* src = d.sem_maps;
       cudaStream_t cs = CopyStream();
       maps.th = std::thread([&maps, dev, dst, src, n_map, cs] {
@@ -887,6 +902,13 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   tm.Lap("allocs");
   maps.Join();  // every chunk of the map upload has been queued on the side stream
   UP(maps.err);
+  if (map_stage.p) {
+    const size_t n_out = (size_t)p->n_img * MapTiledSize(p->sem_h, p->sem_w);
+    retile_maps_kernel<<<(unsigned)std::min<size_t>(DivUp(n_out, 256), 148 * 64), 256, 0, CopyStream()>>>(
+        map_stage.p, p->d_sem_maps.p, p->n_img, p->sem_h, p->sem_w);
+    UP(cudaGetLastError());
+    p->launches += 1;
+  }
   UP(cudaStreamSynchronize(CopyStream()));
   UP(cudaStreamSynchronize(st));
   tm.Lap("maps + sync");
