@@ -16,13 +16,15 @@
 //     ER = double[8]  : E (2x3 d r/d X, row-major) + r(2)
 //     F  = double2[DC]: slot j -> (d r0/d s_j, d r1/d s_j); slots 0..2 quaternion tangent, 3..5 tvec,
 //                       6.. free intrinsics
-//   stored TILE-BLOCKED in 32-byte units (D4): observations are grouped in tiles of 32; inside a tile,
-//   unit u of all 32 observations is contiguous (1 KB):
-//     F  unit jj (slots 2jj, 2jj+1) of observation k : F [((k >> 5) * DC/2 + jj) * 32 + (k & 31)]
-//     ER unit u  (0: E0..E3, 1: E4 E5 r0 r1)         : ER[((k >> 5) * 2    + u ) * 32 + (k & 31)]
-//   A warp that walks consecutive observations (the point-sorted passes) moves whole 1 KB rows with one
-//   256-bit access per lane; a pass that gathers observations in image order touches DC/2 full 32 B sectors
-//   per observation -- no sector is ever fetched half used.
+//   stored TILE-BLOCKED in 32-byte units (D4), units PAIRED into 64-byte pieces: observations are grouped in tiles
+//   of 32; inside a tile, the pair (2m, 2m+1) of units of all 32 observations is contiguous (2 KB, lane-major), and an
+//   odd last unit is a 1 KB row of its own (PairedUnit below):
+//     F  unit jj (slots 2jj, 2jj+1) of observation k : F [PairedUnit(k, jj, DC/2)]
+//     ER unit u  (0: E0..E3, 1: E4 E5 r0 r1)         : ER[PairedUnit(k, u, 2)]
+//   A warp that walks consecutive observations (the point-sorted passes) moves the two halves of a 2 KB piece with two
+//   256-bit accesses per lane, every sector fully used.  A pass that gathers observations in image order (the Schur
+//   build, the F^T reductions) touches whole 64 B pieces: HBM delivers 64 B bursts, and with single 32 B units per
+//   row (round 1) such a gather fetched twice what it used (ncu: 1.99 GB of DRAM reads for 0.96 GB in the C4 build).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -50,8 +52,16 @@ __device__ __forceinline__ void St256(D4* p, const D4& v) {
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
 }
 #endif
-__host__ __device__ inline size_t FUnit(int k, int jj, int dch) { return ((size_t)(k >> 5) * dch + jj) * 32 + (k & 31); }
-__host__ __device__ inline size_t EUnit(int k, int u) { return ((size_t)(k >> 5) * 2 + u) * 32 + (k & 31); }
+__host__ __device__ inline size_t PairedUnit(int k, int u, int n) {
+  const size_t base = (size_t)(k >> 5) * n * 32;
+  const int lane = k & 31;
+#ifdef SBA_UNPAIRED
+  return base + (size_t)u * 32 + lane;
+#endif
+  return u < (n & ~1) ? base + (size_t)(u >> 1) * 64 + lane * 2 + (u & 1) : base + (size_t)(n - 1) * 32 + lane;
+}
+__host__ __device__ inline size_t FUnit(int k, int jj, int dch) { return PairedUnit(k, jj, dch); }
+__host__ __device__ inline size_t EUnit(int k, int u) { return PairedUnit(k, u, 2); }
 inline size_t TilePad(size_t n_obs) { return (n_obs + 31) / 32 * 32; }
 // ---- third residual row (extension X1: the bilinear semantic row) ----
 // A problem created with semantic maps carries THREE residual rows per observation (nr = 3).  The two reprojection
@@ -60,7 +70,7 @@ inline size_t TilePad(size_t n_obs) { return (n_obs + 31) / 32 * 32; }
 //   ES[k]           = {d r_s/d X (3), r_s}                       one 32 B unit per observation, linear
 //   FS unit q of k  = d r_s / d s_j for slots j = 4q .. 4q+3     tile-blocked like F, FSUnits(DC) units per observation
 __host__ __device__ constexpr int FSUnits(int dc) { return (dc + 3) / 4; }
-__host__ __device__ inline size_t FSUnit(int k, int q, int nq) { return ((size_t)(k >> 5) * nq + q) * 32 + (k & 31); }
+__host__ __device__ inline size_t FSUnit(int k, int q, int nq) { return PairedUnit(k, q, nq); }
 #ifdef __CUDACC__
 // (d r0 / d s, d r1 / d s) of one slot of one observation: half a unit
 __device__ __forceinline__ double2 LoadSlot(const D4* __restrict__ F, int k, int slot, int dch) {

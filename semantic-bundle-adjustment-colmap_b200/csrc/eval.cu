@@ -184,16 +184,14 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
     double rho[3];
     LossEval(L.type, L.scale, s, rho);
     const int dch = S.dc >> 1;
-    D4* Fk = F + FUnit(k, 0, dch);
-    D4* Ek = ER + EUnit(k, 0);
     const int nq = FSUnits(S.dc);
     const D4 zero = {0.0, 0.0, 0.0, 0.0};
     if (!active) {
       fixed += 0.5 * rho[0];
-      for (int jj = 0; jj < dch; ++jj) St256(Fk + 32 * jj, zero);
+      for (int jj = 0; jj < dch; ++jj) St256(F + FUnit(k, jj, dch), zero);
       // the raw residual is still exported for the parity surface; E = 0 keeps it out of every product
-      St256(Ek, zero);
-      St256(Ek + 32, D4{0.0, 0.0, r0, r1});
+      St256(ER + EUnit(k, 0), zero);
+      St256(ER + EUnit(k, 1), D4{0.0, 0.0, r0, r1});
       if (NR == 3) {
         for (int q = 0; q < nq; ++q) St256(R3.FS + FSUnit(k, q, nq), zero);
         St256(R3.ES + k, D4{0.0, 0.0, 0.0, rs});
@@ -251,7 +249,7 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
           else correct(f0[j], f1[j], f2[NR == 3 ? j : 0], si[j]);
         }
 #pragma unroll
-        for (int jj = 0; jj < 3; ++jj) St256(Fk + 32 * jj, D4{f0[2 * jj], f1[2 * jj], f0[2 * jj + 1], f1[2 * jj + 1]});
+        for (int jj = 0; jj < 3; ++jj) St256(F + FUnit(k, jj, dch), D4{f0[2 * jj], f1[2 * jj], f0[2 * jj + 1], f1[2 * jj + 1]});
       }
       // intrinsics slots
       if (dch > 3) {
@@ -271,12 +269,12 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
               if (scl == 0.0) { f0[h] = 0.0; f1[h] = 0.0; fs = 0.0; }
               else correct(f0[h], f1[h], fs, scl);
             }
-            St256(Fk + 32 * jj, D4{f0[0], f1[0], f0[1], f1[1]});
+            St256(F + FUnit(k, jj, dch), D4{f0[0], f1[0], f0[1], f1[1]});
           }
         }
         // units of the dc tier beyond this model's parameters (e.g. RADIAL, 5 free: dc = 14, slots 12-13) hold no
         // column; they are multiplied by zeros downstream and must not be stale memory
-        for (int jj = 3 + (NP + 1) / 2; jj < dch; ++jj) St256(Fk + 32 * jj, zero);
+        for (int jj = 3 + (NP + 1) / 2; jj < dch; ++jj) St256(F + FUnit(k, jj, dch), zero);
       }
       // point block
       double E[6], Es[3] = {0.0, 0.0, 0.0};
@@ -295,8 +293,8 @@ eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ s
         for (int j = 0; j < 6; ++j) E[j] = 0.0;
       }
       r0 *= residual_scaling; r1 *= residual_scaling;
-      St256(Ek, D4{E[0], E[1], E[2], E[3]});
-      St256(Ek + 32, D4{E[4], E[5], r0, r1});
+      St256(ER + EUnit(k, 0), D4{E[0], E[1], E[2], E[3]});
+      St256(ER + EUnit(k, 1), D4{E[4], E[5], r0, r1});
       if (NR == 3) {
         rs *= residual_scaling;
 #pragma unroll
@@ -318,8 +316,22 @@ __global__ void __launch_bounds__(kEvalThreads)
 cost_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restrict__ cost_partial, unsigned* ticket,
             double* out_cost) {
   double cost = 0.0, fixed = 0.0;
-  for (int k = blockIdx.x * kEvalThreads + threadIdx.x; k < S.n_obs; k += gridDim.x * kEvalThreads) {
-    const int i = S.obs_img[k], pt = S.obs_pt[k];
+  // the streamed inputs of the next trip are requested before this trip's gathers (as in eval_kernel)
+  const int stride = gridDim.x * kEvalThreads;
+  int k = blockIdx.x * kEvalThreads + threadIdx.x;
+  int i_n = 0, pt_n = 0; double2 xy_n = make_double2(0.0, 0.0); bool act_n = false;
+  if (k < S.n_obs) {
+    i_n = S.obs_img[k]; pt_n = S.obs_pt[k];
+    xy_n = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k); act_n = S.obs_active[k] != 0;
+  }
+  for (; k < S.n_obs; k += stride) {
+    const int i = i_n, pt = pt_n;
+    const double2 xy = xy_n;
+    const bool active = act_n;
+    if (k + stride < S.n_obs) {
+      i_n = S.obs_img[k + stride]; pt_n = S.obs_pt[k + stride];
+      xy_n = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k + stride); act_n = S.obs_active[k + stride] != 0;
+    }
     const int c = S.img_cam[i];
     const int model = MODEL >= 0 ? MODEL : S.model[c];
     const double2* pp = reinterpret_cast<const double2*>(P.pose + 8 * (size_t)i);
@@ -337,7 +349,6 @@ cost_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restr
         else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
       }
     }
-    const double2 xy = reinterpret_cast<const double2*>(S.obs_xy)[k];
     ObsGeom g;
     RotateWithJac(q, t, X, &g, false);
     const double iz = 1.0 / g.p[2];
@@ -352,7 +363,7 @@ cost_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restr
     }
     double rho[3];
     LossEval(L.type, L.scale, r0 * r0 + r1 * r1 + rs * rs, rho);
-    if (S.obs_active[k]) cost += 0.5 * rho[0]; else fixed += 0.5 * rho[0];
+    if (active) cost += 0.5 * rho[0]; else fixed += 0.5 * rho[0];
   }
   double v[2] = {cost, fixed};
   double* const out[2] = {out_cost, nullptr};

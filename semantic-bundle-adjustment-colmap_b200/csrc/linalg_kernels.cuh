@@ -51,18 +51,16 @@ template <int DC, int NR> struct FRow { double2 a[DC]; double s[NR == 3 ? DC : 1
 
 template <int DC, int NR>
 __device__ inline void LoadRow(const D4* __restrict__ F, const D4* __restrict__ FS, int k, FRow<DC, NR>& row) {
-  const D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
   for (int jj = 0; jj < DC / 2; ++jj) {
-    const D4 v = Ld256(f + 32 * jj);
+    const D4 v = Ld256(F + FUnit(k, jj, DC / 2));
     row.a[2 * jj] = make_double2(v.x, v.y); row.a[2 * jj + 1] = make_double2(v.z, v.w);
   }
   if constexpr (NR == 3) {
     constexpr int NQ = FSUnits(DC);
-    const D4* g = FS + FSUnit(k, 0, NQ);
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-      const D4 v = Ld256(g + 32 * q);
+      const D4 v = Ld256(FS + FSUnit(k, q, NQ));
       row.s[4 * q] = v.x;
       if (4 * q + 1 < DC) row.s[4 * q + 1] = v.y;
       if (4 * q + 2 < DC) row.s[4 * q + 2] = v.z;
@@ -566,24 +564,22 @@ __global__ void __launch_bounds__(256) scale_jacobian_kernel(StructView S, const
   for (int j = 0; j < 6; ++j) sl[j] = si[6 * (size_t)i + j];
 #pragma unroll
   for (int j = 6; j < DC; ++j) sl[j] = sc[12 * (size_t)c + j - 6];
-  D4* f = F + FUnit(k, 0, DC / 2);
 #pragma unroll
   for (int jj = 0; jj < DC / 2; ++jj) {
-    D4 v = Ld256(f + 32 * jj);
+    D4 v = Ld256(F + FUnit(k, jj, DC / 2));
     v.x *= sl[2 * jj]; v.y *= sl[2 * jj]; v.z *= sl[2 * jj + 1]; v.w *= sl[2 * jj + 1];
-    St256(f + 32 * jj, v);
+    St256(F + FUnit(k, jj, DC / 2), v);
   }
   if constexpr (NR == 3) {
     constexpr int NQ = FSUnits(DC);
-    D4* g = FS + FSUnit(k, 0, NQ);
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-      D4 v = Ld256(g + 32 * q);
+      D4 v = Ld256(FS + FSUnit(k, q, NQ));
       v.x *= sl[4 * q];
       v.y *= 4 * q + 1 < DC ? sl[4 * q + 1 < DC ? 4 * q + 1 : 0] : 0.0;
       v.z *= 4 * q + 2 < DC ? sl[4 * q + 2 < DC ? 4 * q + 2 : 0] : 0.0;
       v.w *= 4 * q + 3 < DC ? sl[4 * q + 3 < DC ? 4 * q + 3 : 0] : 0.0;
-      St256(g + 32 * q, v);
+      St256(FS + FSUnit(k, q, NQ), v);
     }
   }
   const int po = S.p_off[S.obs_pt[k]];
