@@ -165,6 +165,7 @@ struct ChunkView {
   const int* chunk_start;   // [n_chunks+1] into cam_order
   const int* chunk_img;     // [n_chunks]
   const int* cam_order;     // [n_obs] observation ids (point-sorted numbering), image-major
+  const int* cam_po;        // [n_obs] variable-point offset of the same observations (-1: constant point)
   const int* img_chunk_ptr; // [n_img+1] chunk range of each image
   const int* cam_img_ptr;   // [n_cam+1] CSR: images of each camera
   const int* cam_img_list;  // [n_img]

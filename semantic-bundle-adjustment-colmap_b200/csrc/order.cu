@@ -14,10 +14,13 @@
 
 namespace sba {
 
-// cam_pos[cam_order[k]] = k: image-major position of a point-sorted observation
-__global__ void invert_order_kernel(int n, const int* __restrict__ order, int* __restrict__ pos) {
+// cam_pos[cam_order[k]] = k: image-major position of a point-sorted observation;
+// cam_po[k] = p_off of the point of the k-th observation in image-major order (-1: constant point), so that an
+// image-major pass reaches its point's records with one dependent load instead of three
+__global__ void invert_order_kernel(int n, const int* __restrict__ order, int* __restrict__ pos,
+                                    const int* __restrict__ obs_pt, const int* __restrict__ p_off, int* __restrict__ cam_po) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n) pos[order[k]] = k;
+  if (k < n) { const int a = order[k]; pos[a] = k; cam_po[k] = p_off[obs_pt[a]]; }
 }
 
 __global__ void iota_kernel(unsigned* __restrict__ v, int64_t n) {
@@ -57,6 +60,7 @@ int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int 
   SBA_CUDA(p->d_obs_img.Alloc(std::max(1, n_obs))); SBA_CUDA(p->d_obs_pt.Alloc(std::max(1, n_obs)));
   SBA_CUDA(p->d_obs_xy.Alloc((size_t)std::max(1, n_obs) * 2)); SBA_CUDA(p->d_obs_active.Alloc(std::max(1, n_obs)));
   SBA_CUDA(p->d_cam_order.Alloc(std::max(1, n_obs))); SBA_CUDA(p->d_cam_pos.Alloc(std::max(1, n_obs)));
+  SBA_CUDA(p->d_cam_po.Alloc(std::max(1, n_obs)));
   if (n_obs == 0 || n_obs_g == 0) return SBA_OK;
   DevBuf<unsigned> idx, keys_out, vals_out, img_key;
   DevBuf<char> tmp;
@@ -78,7 +82,8 @@ int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int 
   // idx[0..n_obs) is still 0,1,2,...: the values of the image sort are the local point-sorted positions
   SBA_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, b2, img_key.p, keys_out.p, idx.p,
                                            reinterpret_cast<unsigned*>(p->d_cam_order.p), n_obs, 0, Bits(p->n_img), st));
-  invert_order_kernel<<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, p->d_cam_order.p, p->d_cam_pos.p);
+  invert_order_kernel<<<DivUp(n_obs, 256), 256, 0, st>>>(n_obs, p->d_cam_order.p, p->d_cam_pos.p, p->d_obs_pt.p, p->d_p_off.p,
+                                                             p->d_cam_po.p);
   p->launches += 3;
   SBA_CUDA(cudaGetLastError());
   SBA_CUDA(cudaStreamSynchronize(st));  // the temporaries above are released on return

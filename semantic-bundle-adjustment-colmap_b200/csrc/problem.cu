@@ -390,7 +390,7 @@ TileView Problem::Tiles() const { return TileView{n_tiles, d_tile_start.p}; }
 ChunkView Problem::Chunks() const {
   ChunkView c;
   c.n_chunks = n_chunks; c.chunk_start = d_chunk_start.p; c.chunk_img = d_chunk_img.p;
-  c.cam_order = d_cam_order.p; c.img_chunk_ptr = d_img_chunk_ptr.p;
+  c.cam_order = d_cam_order.p; c.cam_po = d_cam_po.p; c.img_chunk_ptr = d_img_chunk_ptr.p;
   c.cam_img_ptr = d_cam_img_ptr.p; c.cam_img_list = d_cam_img_list.p;
   return c;
 }

@@ -268,6 +268,7 @@ __global__ void __launch_bounds__(256, 2) schur_obs_u_kernel(StructView S, Chunk
 #pragma unroll
   for (int j = 0; j < DC; ++j) rhs[j] = 0.0;
   if (t < n) {
+    const int po = C.cam_po[s0 + t];
     const int a = C.cam_order[s0 + t];
     double2 f[DC];
 #pragma unroll
@@ -291,7 +292,6 @@ __global__ void __launch_bounds__(256, 2) schur_obs_u_kernel(StructView S, Chunk
       const D4 es = Ld256(ES + a);
       Es[0] = es.x; Es[1] = es.y; Es[2] = es.z; rs = es.w;
     }
-    const int po = S.p_off[S.obs_pt[a]];
     double m[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // m00 m10 m11 m20 m21 m22
     if (po >= 0) {
       const double2* cp = reinterpret_cast<const double2*>(Cfac + 6 * (size_t)po);
@@ -412,9 +412,10 @@ __global__ void __launch_bounds__(64) schur_diag_finalize_tri_kernel(StructView 
 
 // fp64 tensor-core MMA (DMMA): D(8x8) += A(8x4, row) * B(4x8, col)
 __device__ __forceinline__ void Dmma884(double& d0, double& d1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-               : "+d"(d0), "+d"(d1)
-               : "d"(a), "d"(b));
+  // (not volatile: a pure function of its operands, so that the loads of the following pairs can be scheduled above it)
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+      : "+d"(d0), "+d"(d1)
+      : "d"(a), "d"(b));
 }
 
 // One warp per segment (<= 128 pairs of one key): partial[seg] = - sum_pairs U_a U_b^T, one DMMA per pair.
@@ -440,12 +441,20 @@ __global__ void __launch_bounds__(128) schur_pair_mma_kernel(int n_seg, const in
     const int m = min(32, np - base);
     const unsigned long long mine = lane < m ? ab[t0 + base + lane] : 0ull;
     const int my_a = (int)(mine >> 32), my_b = (int)(mine & 0xffffffffull);
-#pragma unroll 8
-    for (int t = 0; t < m; ++t) {
-      const int a = __shfl_sync(0xffffffffu, my_a, t), b = __shfl_sync(0xffffffffu, my_b, t);
-      const double av = live ? __ldg(U + (size_t)a * RW + off) : 0.0;
-      const double bv = live ? __ldg(U + (size_t)b * RW + off) : 0.0;
-      Dmma884(c0, c1, av, bv);
+    // batches of 8 pairs: all 16 row loads are issued before the first product consumes one (a batch's tail repeats
+    // the last pair with zero operands)
+    for (int t = 0; t < m; t += 8) {
+      double av[8], bv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int src = min(t + u, m - 1);
+        const int a = __shfl_sync(0xffffffffu, my_a, src), b = __shfl_sync(0xffffffffu, my_b, src);
+        const bool on = live && t + u < m;
+        av[u] = on ? __ldg(U + (size_t)a * RW + off) : 0.0;
+        bv[u] = on ? __ldg(U + (size_t)b * RW + off) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) Dmma884(c0, c1, av[u], bv[u]);
     }
   }
   // accumulator layout: lane holds C[l / 4][2 (l % 4)], C[l / 4][2 (l % 4) + 1]

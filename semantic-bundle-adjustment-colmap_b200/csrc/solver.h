@@ -172,6 +172,7 @@ struct Problem {
   DevBuf<uint8_t> d_obs_active, d_pose_const;
   DevBuf<int> d_tile_start;  int n_tiles = 0;
   DevBuf<int> d_chunk_start, d_chunk_img, d_cam_order, d_img_chunk_ptr, d_cam_img_ptr, d_cam_img_list;
+  DevBuf<int> d_cam_po;      // [n_obs] p_off of the point of the k-th image-major observation
   DevBuf<int> d_cam_pos;     // [n_obs] inverse of d_cam_order: image-major position of an observation (rows of d_W / d_H)
   int n_chunks = 0;
   DevBuf<int> d_pt_ptr;      // [n_pt+1] CSR over point-sorted observations
