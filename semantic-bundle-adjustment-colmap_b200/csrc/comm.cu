@@ -146,22 +146,19 @@ class Comm {
   std::atomic_flag in_use = ATOMIC_FLAG_INIT;  // held by the one API call that is issuing collectives (CommAcquire)
   bool p2p = false;  // the exchange areas are mapped on every rank
   P2PView view{};
+  // second peer-mapped area, sized by the first problem that needs it: the vectors of the row-sharded PCG (pcg_blocks.cu)
+  void* pcg_area[kP2PMaxRanks] = {nullptr};
+  size_t pcg_bytes = 0;
 };
 
-static int NcclFail(const char* what, ncclResult_t r) {
-  SetError(SBA_ERR_COMM, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "nccl error"));
-  return SBA_ERR_COMM;
-}
-
-// Maps every rank's exchange area into this process.  Every step is followed by a consensus over NCCL, so either all
-// ranks switch to the peer-memory path or none does (SBA_NO_P2P_ALLREDUCE=1 keeps every collective on NCCL).
-static void SetupP2P(Comm* c) {
-  if (getenv("SBA_NO_P2P_ALLREDUCE") || c->nranks > kP2PMaxRanks) return;
+// cudaMalloc's `bytes` (zeroed) on this rank and maps every rank's block here through CUDA IPC.  Collective over the
+// communicator (NCCL on the default stream, with a consensus after each step): true on every rank or false on every rank.
+static bool MapPeerArea(Comm* c, size_t bytes, void** peer) {
   const int nr = c->nranks, hw = (int)(sizeof(cudaIpcMemHandle_t) / sizeof(int)), words = nr * (hw + 1);
   int ok = 1;
   void* area = nullptr;
-  if (cudaMalloc(&area, kP2PAreaBytes) != cudaSuccess) { ok = 0; area = nullptr; }
-  if (ok && cudaMemset(area, 0, kP2PAreaBytes) != cudaSuccess) ok = 0;
+  if (cudaMalloc(&area, bytes) != cudaSuccess) { ok = 0; area = nullptr; }
+  if (ok && cudaMemset(area, 0, bytes) != cudaSuccess) ok = 0;
   cudaIpcMemHandle_t mine;
   std::memset(&mine, 0, sizeof(mine));
   if (ok && cudaIpcGetMemHandle(&mine, area) != cudaSuccess) ok = 0;
@@ -177,9 +174,9 @@ static void SetupP2P(Comm* c) {
     return cudaMemcpy(h.data(), d, words * sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess;
   };
   auto all_ok = [&]() { for (int r = 0; r < nr; ++r) if (h[(size_t)nr * hw + r] != 1) return false; return true; };
-  if (cudaMalloc(&d, words * sizeof(int)) != cudaSuccess) { cudaGetLastError(); if (area) cudaFree(area); return; }  // (cannot even vote: NCCL only, and so will the peers' first gather fail loudly)
+  if (cudaMalloc(&d, words * sizeof(int)) != cudaSuccess) { cudaGetLastError(); if (area) cudaFree(area); return false; }  // (cannot even vote: the peers' gather fails loudly)
   bool good = gather() && all_ok();
-  void* peer[kP2PMaxRanks] = {nullptr};
+  for (int r = 0; r < nr; ++r) peer[r] = nullptr;
   if (good) {
     for (int r = 0; r < nr; ++r) {
       if (r == c->rank) { peer[r] = area; continue; }
@@ -196,9 +193,25 @@ static void SetupP2P(Comm* c) {
   if (!good) {
     for (int r = 0; r < nr; ++r) if (r != c->rank && peer[r]) cudaIpcCloseMemHandle(peer[r]);
     if (area) cudaFree(area);
+    for (int r = 0; r < nr; ++r) peer[r] = nullptr;
     cudaGetLastError();
-    return;
+    return false;
   }
+  return true;
+}
+
+static int NcclFail(const char* what, ncclResult_t r) {
+  SetError(SBA_ERR_COMM, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "nccl error"));
+  return SBA_ERR_COMM;
+}
+
+// Maps every rank's exchange area into this process.  Every step is followed by a consensus over NCCL, so either all
+// ranks switch to the peer-memory path or none does (SBA_NO_P2P_ALLREDUCE=1 keeps every collective on NCCL).
+static void SetupP2P(Comm* c) {
+  if (getenv("SBA_NO_P2P_ALLREDUCE") || c->nranks > kP2PMaxRanks) return;
+  void* peer[kP2PMaxRanks] = {nullptr};
+  if (!MapPeerArea(c, kP2PAreaBytes, peer)) return;
+  const int nr = c->nranks;
   P2PView& V = c->view;
   V.nranks = nr; V.rank = c->rank;
   for (int r = 0; r < nr; ++r) {
@@ -207,6 +220,31 @@ static void SetupP2P(Comm* c) {
   }
   V.epoch = V.flags[c->rank] + (size_t)kP2PMaxRanks * kP2PCtas;
   c->p2p = true;
+}
+
+// The peer-mapped area of the row-sharded PCG: every rank's block of >= `bytes`, as mapped here (area[rank] is the local
+// one).  Collective: every rank of the group calls it at the same point of its first solve.  SBA_ERR_COMM when the
+// group has no peer mapping (the caller then keeps the replicated solve).
+int CommPcgArea(Problem* p, size_t bytes, void** area, int* nranks, int* rank) {
+  Comm* c = p->comm;
+  if (!c || !c->p2p) return SBA_ERR_COMM;
+  if (c->pcg_bytes < bytes) {
+    SBA_CUDA(cudaDeviceSynchronize());
+    if (c->pcg_bytes) {
+      for (int r = 0; r < c->nranks; ++r) {
+        if (r != c->rank && c->pcg_area[r]) cudaIpcCloseMemHandle(c->pcg_area[r]);
+        else if (c->pcg_area[r]) cudaFree(c->pcg_area[r]);
+        c->pcg_area[r] = nullptr;
+      }
+      c->pcg_bytes = 0;
+    }
+    const size_t want = (bytes + (1u << 20) - 1) & ~((size_t)(1u << 20) - 1);
+    if (!MapPeerArea(c, want, c->pcg_area)) { SetError(SBA_ERR_COMM, "peer mapping of the PCG exchange area failed"); return SBA_ERR_COMM; }
+    c->pcg_bytes = want;
+  }
+  for (int r = 0; r < c->nranks; ++r) area[r] = c->pcg_area[r];
+  *nranks = c->nranks; *rank = c->rank;
+  return SBA_OK;
 }
 
 int CommGetUniqueId(void* id128) {
@@ -249,6 +287,7 @@ int CommInit(Problem* p, int nranks, int rank, const void* id128) {
   return SBA_OK;
 }
 
+bool CommHasPeerMemory(const Problem* p) { return p->comm && p->comm->p2p; }
 void CommDestroy(Problem* p) { p->comm = nullptr; }  // communicators are process-wide (see CommInit)
 
 // Exclusive use of the handle's communicator for one API call (no-op on a single GPU).  false: another handle of the

@@ -135,7 +135,8 @@ struct BlockSchur {
   int pcg_rows = 0;                  // block rows per CTA
   DevBuf<double> pcg_partials;       // [3 * pcg_grid]
   DevBuf<double> minv_s;             // [n_img * dc * dc] SCHUR_JACOBI inverse in slot space (zero outside a parameter block)
-  DevBuf<double> p_s, z_s, x_s;      // slot-space CG vectors other CTAs read (p_s: two buffers)
+  DevBuf<double> p_s;                // slot-space CG vectors other CTAs read: p [2][n_img*dc] | z | x (one GPU; N > 1: the peer-mapped area)
+  bool pcg_dist = false;             // N > 1: block rows split across the ranks (pcg_blocks.cu DIST)
 };
 
 struct Problem {
@@ -326,6 +327,8 @@ int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, 
 // comm.cu
 int CommGetUniqueId(void* id128);
 int CommInit(Problem* p, int nranks, int rank, const void* id128);
+int CommPcgArea(Problem* p, size_t bytes, void** area, int* nranks, int* rank);  // peer-mapped vectors of the row-sharded PCG (collective)
+bool CommHasPeerMemory(const Problem* p);
 void CommDestroy(Problem* p);
 bool CommAcquire(Problem* p);   // one collective-issuing API call at a time per communicator
 void CommRelease(Problem* p);

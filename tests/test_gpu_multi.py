@@ -1,6 +1,7 @@
 """Two ranks, one GPU each: the point-sharded solve -- with the small collectives on the
 peer-memory all-reduce kernel (csrc/comm.cu) and, separately, with every collective on NCCL -- must reach the cost of the
-unsharded solve on one GPU, and the two communication paths must agree with each other to the last bits.
+unsharded solve on one GPU, and the two communication paths must agree with each other to the last bits.  The opt-in
+row-sharded PCG (SBA_PCG_SHARDED=1, csrc/pcg_blocks.cu DIST) is checked against the replicated solve to rounding.
 
 Needs two GPUs: skipped on a one-GPU box (the bench lines under profiles/r01_bench_c2_*gpu_weak*.json carry the same
 comparison at 2 / 4 / 8 GPUs).  The reference has no distributed path; the oracle for the
@@ -71,12 +72,16 @@ def test_two_rank_solve_matches_single_gpu_on_both_collective_paths(tmp_path):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
-    peer = _run(tmp_path, {})
-    nccl = _run(tmp_path, {"SBA_NO_P2P_ALLREDUCE": "1"})
+    peer = _run(tmp_path, {})                                    # peer-memory all-reduce, replicated PCG (the default)
+    dist_pcg = _run(tmp_path, {"SBA_PCG_SHARDED": "1"})          # + the PCG's block rows split across the ranks
+    nccl = _run(tmp_path, {"SBA_NO_P2P_ALLREDUCE": "1"})         # everything on NCCL (replicated PCG)
     for key, res in peer.items():
         single = res["single"]
-        for c in res["sharded"]:
-            assert abs(c - single) <= 1e-7 * single, (key, c, single)   # north-star bar is 1e-6
-        assert max(res["sharded"]) - min(res["sharded"]) <= 1e-12 * single, (key, res)  # plain launches == graph replay
-        # two ranks: a sum of two terms is the same in either order, so the paths agree bit for bit
+        for run in (res, dist_pcg[key], nccl[key]):
+            for c in run["sharded"]:
+                assert abs(c - single) <= 1e-7 * single, (key, c, single)   # north-star bar is 1e-6
+            assert max(run["sharded"]) - min(run["sharded"]) <= 1e-12 * single, (key, run)  # plain launches == graph replay
+        # two ranks: a sum of two terms is the same in either order, so the two collective paths agree bit for bit
         assert res["sharded"][-1] == nccl[key]["sharded"][-1], (key, res, nccl[key])
+        # the row-sharded PCG adds its scalars rank by rank instead of CTA by CTA: same solve to rounding
+        assert abs(dist_pcg[key]["sharded"][-1] - res["sharded"][-1]) <= 1e-9 * single, (key, dist_pcg[key], res)
