@@ -256,7 +256,7 @@ int sba_get_parameters(sba_handle* h, double* image_qvec, double* image_tvec, do
   SBA_CUDA(cudaStreamSynchronize(st));
   // the shard's points are one contiguous range of the caller's array (points [p0, p0 + n_pt)): they land in place
   if (points && p->n_pt > 0)
-    SBA_CUDA(DownloadLarge(points + 3 * (size_t)p->h_pt_local2global[0], p->d_X.p, (size_t)p->n_pt * 3 * sizeof(double), st));
+    SBA_CUDA(DownloadLarge(points + 3 * (size_t)p->pt_base, p->d_X.p, (size_t)p->n_pt * 3 * sizeof(double), st));
   for (int i = 0; i < p->n_img; ++i) {
     if (image_qvec) for (int j = 0; j < 4; ++j) image_qvec[4 * (size_t)i + j] = pose[8 * (size_t)i + j];
     if (image_tvec) for (int j = 0; j < 3; ++j) image_tvec[3 * (size_t)i + j] = pose[8 * (size_t)i + 4 + j];

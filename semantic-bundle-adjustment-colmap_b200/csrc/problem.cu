@@ -725,22 +725,32 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   // Host: one counting pass by point (worker t owns a contiguous range of points and scans obs_point for them: no
   // atomics, no per-thread counters) gives the CSR over points, the shard's range and the warp tiles.  The sort itself
   // -- and every per-observation array -- is made on the DEVICE from the caller's arrays (cub stable radix sort).
-  std::vector<int64_t> prefix(n_pt_g + 1, 0);
-  for (int q = 0; q < n_pt_g; ++q) prefix[q + 1] = prefix[q] + pt_count[q];
   int p0 = 0, p1 = n_pt_g;
-  ShardPointRange(prefix, p->shard_count, p->shard_rank, &p0, &p1);
+  int64_t obs_base = 0;
+  if (p->shard_count > 1) {
+    std::vector<int64_t> prefix(n_pt_g + 1, 0);
+    for (int q = 0; q < n_pt_g; ++q) prefix[q + 1] = prefix[q] + pt_count[q];
+    ShardPointRange(prefix, p->shard_count, p->shard_rank, &p0, &p1);
+    obs_base = prefix[p0];
+  }
   p->n_pt = p1 - p0;
-  p->n_obs = (int)(prefix[p1] - prefix[p0]);
-  const int64_t obs_base = prefix[p0];
-  p->h_pt_local2global.resize(p->n_pt);
-  std::iota(p->h_pt_local2global.begin(), p->h_pt_local2global.end(), p0);
-  const int n_obs = p->n_obs;
-  p->h_p_off.assign(p->n_pt, -1);
-  p->n_pvar = 0;
-  for (int q = 0; q < p->n_pt; ++q) if (g.p_off_global[p0 + q] >= 0) p->h_p_off[q] = p->n_pvar++;
+  p->pt_base = p0;
+  // one pass over the shard's points: CSR over points and the offsets of the variable ones
   std::vector<int>& h_pt_ptr = p->h_pt_ptr;
   h_pt_ptr.resize(p->n_pt + 1);
-  for (int q = 0; q <= p->n_pt; ++q) h_pt_ptr[q] = (int)(prefix[p0 + q] - obs_base);
+  p->h_p_off.resize(p->n_pt);
+  p->n_pvar = 0;
+  {
+    int acc = 0;
+    h_pt_ptr[0] = 0;
+    for (int q = 0; q < p->n_pt; ++q) {
+      acc += pt_count[p0 + q];
+      h_pt_ptr[q + 1] = acc;
+      p->h_p_off[q] = g.p_off_global[p0 + q] >= 0 ? p->n_pvar++ : -1;
+    }
+    p->n_obs = acc;
+  }
+  const int n_obs = p->n_obs;
   tm.Lap("shard + point counts");
 
   // ---- warp tiles: whole points packed into <= kTile observations ----

@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -58,21 +59,48 @@ struct DevBuf {
 
 // The ~30 small structure arrays of a problem travel in ONE host -> device copy: they are packed (256 B aligned)
 // into a host block, copied once, and the DevBufs become views into the device block.
+// The ~22 small structure arrays of a problem travel as ONE block.  The host side of the block is a page-locked staging
+// buffer kept per process (grown on demand, guarded by a mutex for the duration of one create): arrays are copied into it
+// once and the upload is one DMA -- a growing std::vector re-allocated, zero-filled and page-faulted 12 MB per create at C4.
+struct PinnedStage {
+  char* p = nullptr; size_t cap = 0;
+  std::mutex mu;
+  static PinnedStage& Get() { static PinnedStage s; return s; }
+  bool Reserve(size_t bytes) {
+    if (bytes <= cap) return true;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    const size_t want = std::max<size_t>(bytes + bytes / 2, 1u << 20);
+    if (cudaMallocHost((void**)&p, want) != cudaSuccess) { cudaGetLastError(); p = nullptr; return false; }
+    cap = want;
+    return true;
+  }
+};
 struct DeviceArena {
-  std::vector<char> host;
   DevBuf<char> dev;
-  struct Slot { size_t off, bytes; };
+  struct Slot { size_t off, bytes; const void* src; };
+  std::vector<Slot> slots;
+  size_t size = 0;
   template <typename T>
-  Slot Push(const std::vector<T>& v) {
-    const size_t off = (host.size() + 255) / 256 * 256, bytes = v.size() * sizeof(T);
-    host.resize(off + std::max<size_t>(bytes, 1));
-    if (bytes) std::memcpy(host.data() + off, v.data(), bytes);
-    return Slot{off, bytes};
+  Slot Push(const std::vector<T>& v) {  // (v must stay alive until Upload)
+    const size_t off = (size + 255) / 256 * 256, bytes = v.size() * sizeof(T);
+    size = off + std::max<size_t>(bytes, 1);
+    slots.push_back(Slot{off, bytes, v.data()});
+    return slots.back();
   }
   cudaError_t Upload(cudaStream_t s) {
-    cudaError_t e = dev.Alloc(std::max<size_t>(host.size(), 1));
+    cudaError_t e = dev.Alloc(std::max<size_t>(size, 1));
     if (e != cudaSuccess) return e;
-    return cudaMemcpyAsync(dev.p, host.data(), host.size(), cudaMemcpyHostToDevice, s);
+    PinnedStage& st = PinnedStage::Get();
+    std::lock_guard<std::mutex> lk(st.mu);
+    if (!st.Reserve(size)) return cudaErrorMemoryAllocation;
+    for (const Slot& sl : slots)
+      if (sl.bytes) std::memcpy(st.p + sl.off, sl.src, sl.bytes);
+    e = cudaMemcpyAsync(dev.p, st.p, size, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(s);  // the staging buffer is shared: the copy has left it before the lock is released
+    slots.clear();
+    return e;
   }
   template <typename T>
   void Bind(DevBuf<T>* b, const Slot& s) { b->View(reinterpret_cast<T*>(dev.p + s.off), s.bytes / sizeof(T)); }
@@ -156,7 +184,7 @@ struct Problem {
   std::vector<int> h_obs_img, h_obs_pt;        // local, point-sorted
   std::vector<int> h_pt_ptr, h_img_ptr, h_cam_order;  // CSR over points; image-major list of local observation ids
   std::vector<int64_t> h_local2ref;            // local point-sorted position -> reference residual index
-  std::vector<int> h_pt_local2global;          // local point -> global point
+  int pt_base = 0;                             // local point q is global point pt_base + q (shards are contiguous ranges)
   std::vector<uint8_t> h_pose_const;
   std::vector<int> h_t_dim;
   sba_summary counts;                          // structural counts (global problem)
