@@ -260,6 +260,25 @@ int sba_evaluate(sba_handle* h, int32_t loss_function_type, double loss_function
  * jac_intr [n_obs*SBA_MAX_CAMERA_PARAMS] (ambient, constant params zero), jac_point [n_obs*3].  Any may be NULL. */
 int sba_get_semantic_jacobian(sba_handle* h, double* jac_pose, double* jac_intr, double* jac_point);
 
+/* --- cost evaluation that allocates nothing -----------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Returns 0.5 * sum rho(|r|^2) over all residual blocks at the handle's CURRENT parameters -- the value sba_evaluate
+ * returns in `cost` -- through a variant of the residual-only kernel whose scratch (per-CTA partial sums, arrival
+ * ticket, totals) is a file-scope `static __device__` array of SBA_NO_ALLOC_SCRATCH_BYTES instead of cudaMalloc'ed
+ * memory.  The call makes no cudaMalloc / cudaFree / allocating library call; inputs are the handle's device-resident
+ * problem, outputs are cost_host (host pointer) and / or cost_device (device pointer on the handle's GPU; the value is
+ * written by a kernel on the handle's stream); either may be NULL.  The call returns after a stream synchronisation.
+ * Limits: the launch grid min(ceil(n_obs / 128), 16 * SMs) must not exceed SBA_NO_ALLOC_MAX_CTAS
+ * (SBA_ERR_INVALID_ARGUMENT otherwise; 2368 CTAs on a 148-SM B200 for any n_obs); sharded handles are rejected.
+ * Every GPU that loads the library holds the array until the process exits.  ALL calls share it and it keeps the last
+ * call's contents (the entry point clears what must start at zero): calls are serialised inside the library, and a
+ * caller that bypasses that by overlapping two such launches on one GPU would race. */
+#define SBA_NO_ALLOC_MAX_CTAS 4096
+#define SBA_NO_ALLOC_SCRATCH_BYTES ((32 + 2 * SBA_NO_ALLOC_MAX_CTAS) * 8) /* 65 792 B */
+int sba_cost_no_alloc(sba_handle* h, int32_t loss_function_type, double loss_function_scale,
+                      double* cost_host, double* cost_device);
+
 /* --- solve -------------------------------------------------------------- */
 int sba_solve(sba_handle* h, const sba_solver_options* opts, sba_iteration_callback cb,
               void* user, sba_summary* summary);

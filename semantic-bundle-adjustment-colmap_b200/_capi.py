@@ -171,6 +171,7 @@ SYMBOLS = {
     "sba_device_count": (C.c_int, []),
     "sba_evaluate": (C.c_int, [C.c_void_p, C.c_int32, C.c_double, C.c_int32, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
     "sba_get_semantic_jacobian": (C.c_int, [C.c_void_p, _dp, _dp, _dp]),
+    "sba_cost_no_alloc": (C.c_int, [C.c_void_p, C.c_int32, C.c_double, _dp, C.c_void_p]),
     "sba_solve": (C.c_int, [C.c_void_p, C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p, C.POINTER(Summary)]),
     "sba_get_trace": (C.c_int, [C.c_void_p, C.POINTER(IterationSummary), C.c_int32, _ip]),
     "sba_get_parameters": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp]),

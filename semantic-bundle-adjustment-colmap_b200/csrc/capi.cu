@@ -98,6 +98,14 @@ static int CheckHandle(sba_handle* h) {
   return SBA_OK;
 }
 
+int sba_cost_no_alloc(sba_handle* h, int32_t loss_type, double loss_scale, double* cost_host, double* cost_device) {
+  int rc = CheckHandle(h);
+  if (rc) return rc;
+  if (!cost_host && !cost_device) { SetError(SBA_ERR_INVALID_ARGUMENT, "sba_cost_no_alloc: no output pointer"); return SBA_ERR_INVALID_ARGUMENT; }
+  const LossView loss = {loss_type, loss_scale, 1};
+  return CostNoAlloc(h->p, loss, cost_host, cost_device);
+}
+
 int sba_evaluate(sba_handle* h, int32_t loss_type, double loss_scale, int32_t apply_loss, double* cost,
                  double* residuals, double* jac_pose, double* jac_intr, double* jac_point,
                  double* jac_qvec_ambient, double* sem_residuals) {

@@ -13,6 +13,8 @@
 // 64 B ER record + 16*DC B F record out (tile-blocked 32 B units, common.cuh); poses / intrinsics /
 // points are gathered through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
 #include <algorithm>
+#include <mutex>
+#include <string>
 
 #include "device_math.cuh"
 #include "reduce.cuh"
@@ -434,6 +436,139 @@ int LaunchCostOnly(Problem* p, const LossView& loss, bool candidate, double* d_o
   // with_step_scalars: d_out_cost is &scalars->cand_cost and model_cost_change, step2_p, x2_p behind it still hold this
   // rank's partial sums (BackSubstitute / ApplyStep deferred theirs): one collective for the four
   return AllReduceSum(p, d_out_cost, with_step_scalars ? 4 : 1);
+}
+
+
+// ---- cost evaluation that allocates nothing (sba_cost_no_alloc, include/sba_b200.h) ----------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is cost_kernel with its scratch --
+// the per-CTA partial sums, the arrival ticket and the two totals of GridSum -- in a file-scope device array instead of
+// the handle's cudaMalloc'ed d_cost_partial / d_tickets / d_scalars.  Every GPU that loads the library holds the array
+// (kNoAllocScratchBytes = 65 792 B) until the process exits.  ALL calls on a device share it: two calls that overlap on
+// the GPU (different streams, different handles, different host threads) race on the partial sums and the ticket; calls
+// are serialised per process by a mutex and each call ends with a stream synchronisation, which is the supported use.
+constexpr int kNoAllocMaxCtas = SBA_NO_ALLOC_MAX_CTAS;       // launch grids beyond this are rejected
+constexpr int kNoAllocHead = 32;                             // doubles: [0] cost, [1] fixed cost, [2] ticket (as u32), pad to 256 B
+constexpr size_t kNoAllocScratchBytes = (size_t)(kNoAllocHead + 2 * kNoAllocMaxCtas) * sizeof(double);
+static_assert(kNoAllocScratchBytes == SBA_NO_ALLOC_SCRATCH_BYTES, "header constant");
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocHead + 2 * kNoAllocMaxCtas];
+
+template <int MODEL, int NR>
+__global__ void __launch_bounds__(kEvalThreads)
+cost_noalloc_kernel(ParamsView P, StructView S, LossView L, Row3View R3, double* __restrict__ scratch) {
+  double cost = 0.0, fixed = 0.0;
+  const int stride = gridDim.x * kEvalThreads;
+  for (int k = blockIdx.x * kEvalThreads + threadIdx.x; k < S.n_obs; k += stride) {
+    const int i = S.obs_img[k], pt = S.obs_pt[k];
+    const double2 xy = __ldcs(reinterpret_cast<const double2*>(S.obs_xy) + k);
+    const bool active = S.obs_active[k] != 0;
+    const int c = S.img_cam[i];
+    const int model = MODEL >= 0 ? MODEL : S.model[c];
+    const double2* pp = reinterpret_cast<const double2*>(P.pose + 8 * (size_t)i);
+    const double2 a0 = __ldg(pp), a1 = __ldg(pp + 1), a2 = __ldg(pp + 2), a3 = __ldg(pp + 3);
+    const double q[4] = {a0.x, a0.y, a1.x, a1.y};
+    const double t[3] = {a2.x, a2.y, a3.x};
+    const double X[3] = {P.X[3 * (size_t)pt], P.X[3 * (size_t)pt + 1], P.X[3 * (size_t)pt + 2]};
+    double prm[12];
+    {
+      const double2* cp = reinterpret_cast<const double2*>(P.cam + 12 * (size_t)c);
+      const int np = MODEL >= 0 ? ModelNumParams(MODEL) : 12;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        if (2 * j < np) { const double2 v = __ldg(cp + j); prm[2 * j] = v.x; prm[2 * j + 1] = v.y; }
+        else { prm[2 * j] = 0.0; prm[2 * j + 1] = 0.0; }
+      }
+    }
+    ObsGeom g;
+    RotateWithJac(q, t, X, &g, false);
+    const double iz = 1.0 / g.p[2];
+    double x, y;
+    if (MODEL >= 0) WorldToImageVal<(MODEL >= 0 ? MODEL : 0)>(prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
+    else WorldToImageValDyn(model, prm, g.p[0] * iz, g.p[1] * iz, &x, &y);
+    const double r0 = x - xy.x, r1 = y - xy.y;
+    double rs = 0.0;
+    if (NR == 3) {
+      double val, gx, gy;
+      if (BilinearWithGrad(R3.maps + (size_t)i * MapTiledSize(R3.H, R3.W), R3.H, R3.W, x, y, &val, &gx, &gy)) rs = R3.weight * val;
+    }
+    double rho[3];
+    LossEval(L.type, L.scale, r0 * r0 + r1 * r1 + rs * rs, rho);
+    if (active) cost += 0.5 * rho[0]; else fixed += 0.5 * rho[0];
+  }
+  double v[2] = {cost, fixed};
+  double* const out[2] = {scratch, scratch + 1};
+  GridSum<kEvalThreads, 2>(v, scratch + kNoAllocHead, reinterpret_cast<unsigned*>(scratch + 2), out);
+}
+
+__global__ void noalloc_total_kernel(const double* __restrict__ scratch, double* __restrict__ out) { *out = scratch[0] + scratch[1]; }
+
+// Device address of g_noalloc_scratch on the CURRENT device.  In host code the array's name is only a stand-in: the
+// address a kernel can use comes from cudaGetSymbolAddress, asked once per device.
+static int NoAllocScratchAddress(int device, double** out) {
+  constexpr int kMaxDevices = 64;
+  static double* addr[kMaxDevices] = {};
+  if (device < 0 || device >= kMaxDevices) { SetError(SBA_ERR_INVALID_ARGUMENT, "device ordinal out of range"); return SBA_ERR_INVALID_ARGUMENT; }
+  if (!addr[device]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      SetError(SBA_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+      return SBA_ERR_CUDA;
+    }
+    addr[device] = ptr;
+  }
+  *out = addr[device];
+  return SBA_OK;
+}
+
+// 0.5 sum rho over the residual blocks of the handle's CURRENT parameters (active + constant-only blocks, as the cost
+// sba_evaluate returns), with no cudaMalloc / cudaFree / allocating library call.  cost_host / cost_device: either may be
+// null.  Returns after the stream has been synchronised.
+int CostNoAlloc(Problem* p, const LossView& loss, double* cost_host, double* cost_device) {
+  static std::mutex mu;  // one call at a time per process: the scratch array is shared
+  std::lock_guard<std::mutex> lk(mu);
+  if (p->comm || p->shard_count > 1) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sba_cost_no_alloc: sharded handles are not supported (the sum would be this shard's part)");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  const int blocks = EvalGrid(p);
+  if (blocks > kNoAllocMaxCtas) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sba_cost_no_alloc: the launch needs " + std::to_string(blocks) + " CTAs, the static scratch holds " +
+                                           std::to_string(kNoAllocMaxCtas) + " (SBA_NO_ALLOC_MAX_CTAS)");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  int prev = -1;
+  SBA_CUDA(cudaGetDevice(&prev));
+  if (prev != p->device) SBA_CUDA(cudaSetDevice(p->device));
+  double* scratch = nullptr;
+  int rc = NoAllocScratchAddress(p->device, &scratch);
+  cudaStream_t st = p->stream;
+  cudaError_t e = cudaSuccess;
+  if (rc == SBA_OK) {
+    // the array keeps the last call's contents: totals and ticket start at zero (a call that died mid-way must not
+    // leave a ticket behind); the partial sums are written before they are read
+    e = cudaMemsetAsync(scratch, 0, kNoAllocHead * sizeof(double), st);
+    if (e == cudaSuccess && blocks > 0) {
+#define CALL(M)                                                                                                          \
+  do {                                                                                                                   \
+    if (p->nr == 3) cost_noalloc_kernel<M, 3><<<blocks, kEvalThreads, 0, st>>>(p->Params(false), p->Struct(), loss, p->Row3(), scratch); \
+    else cost_noalloc_kernel<M, 2><<<blocks, kEvalThreads, 0, st>>>(p->Params(false), p->Struct(), loss, p->Row3(), scratch);           \
+  } while (0)
+      SBA_MODEL_SWITCH(p->uniform_model, CALL)
+#undef CALL
+      p->launches++;
+      e = cudaGetLastError();
+    }
+    double h[2] = {0.0, 0.0};
+    if (e == cudaSuccess && cost_device) { noalloc_total_kernel<<<1, 1, 0, st>>>(scratch, cost_device); e = cudaGetLastError(); }
+    if (e == cudaSuccess && cost_host) e = cudaMemcpyAsync(h, scratch, sizeof(h), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess && cost_host) *cost_host = h[0] + h[1];
+  }
+  if (prev != p->device && prev >= 0) cudaSetDevice(prev);
+  if (rc) return rc;
+  if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("sba_cost_no_alloc: ") + cudaGetErrorString(e)); return SBA_ERR_CUDA; }
+  return SBA_OK;
 }
 
 }  // namespace sba

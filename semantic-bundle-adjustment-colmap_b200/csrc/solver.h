@@ -354,6 +354,7 @@ int SolvePCGBlocks(Problem* p, const sba_solver_options& o);  // pcg_blocks.cu: 
 int SolveLM(Problem* p, const sba_solver_options* o, sba_iteration_callback cb, void* user, sba_summary* s);
 // comm.cu
 int CommGetUniqueId(void* id128);
+int CostNoAlloc(Problem* p, const LossView& loss, double* cost_host, double* cost_device);  // eval.cu: static-scratch cost (sba_cost_no_alloc)
 int CommInit(Problem* p, int nranks, int rank, const void* id128);
 int CommPcgArea(Problem* p, size_t bytes, void** area, int* nranks, int* rank);  // peer-mapped vectors of the row-sharded PCG (collective)
 bool CommHasPeerMemory(const Problem* p);

@@ -143,6 +143,14 @@ class Solver:
             out["sem_pose"], out["sem_intr"], out["sem_point"] = sp, si, sx
         return out
 
+    def cost_no_alloc(self, loss_type=capi.LOSS_TRIVIAL, loss_scale=1.0, device_out=None):
+        """Cost at the current parameters through sba_cost_no_alloc (static device scratch, no allocation inside the
+        call).  device_out: optional device address (int) of one double on the handle's GPU that also receives it."""
+        cost = C.c_double()
+        capi.check(self.lib.sba_cost_no_alloc(self._h, loss_type, loss_scale, C.byref(cost),
+                                              C.c_void_p(device_out) if device_out else None))
+        return cost.value
+
     def solve(self, options=None, callback=None):
         o = options if options is not None else capi.default_solver_options()
         s = capi.Summary()
