@@ -302,6 +302,17 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
  * ::FilterObservationsWithNegativeDepth (src/base/reconstruction.cc:1472-1523, 647-665).  Either output may be NULL.
  * Only the geometry fields of `desc` are read (no constancy masks, no maps). */
 int sba_observation_errors(const sba_problem_desc* desc, double* sq_error, double* depth);
+/* Reconstruction::Normalize(extent, p0, p1, use_images) (src/base/reconstruction.cc:321-345; the mapper calls it after
+ * every global BA, src/sfm/incremental_mapper.cc:711).  In place on the caller's host arrays: all image poses
+ * (image_registered[i] != 0 marks reg_image_ids_; NULL = all registered) and all points.  Bounds and centroid come from
+ * the float-cast, per-axis sorted projection centres of the registered images (use_images) or points
+ * (ComputeBoundsAndCentroid, :358-422); the similarity (scale, identity rotation, -scale * centroid) is applied as
+ * Reconstruction::Transform does (:424-431; SimilarityTransform3::TransformPoint / ::TransformPose,
+ * src/base/similarity_transform.cc:211-240) -- quaternions come back normalised, through the rotation matrix.
+ * Fewer than two elements: nothing changes (:325-328).  scale_out / translation_out[3] (nullable): the transform applied. */
+int sba_normalize(int32_t num_images, double* image_qvec, double* image_tvec, const uint8_t* image_registered,
+                  int64_t num_points, double* points, double extent, double p0, double p1, int32_t use_images,
+                  double* scale_out, double* translation_out);
 /* Device blocks released by destroyed handles are kept (per device, up to a third of its memory) for the next handle
  * of the same shape; this hands them all back to the driver's pool.  Current device; no handle may be in a call. */
 void sba_release_cached_memory(void);

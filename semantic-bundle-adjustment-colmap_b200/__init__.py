@@ -16,3 +16,4 @@ from . import model_io  # noqa: F401
 from . import filters  # noqa: F401
 from . import bundle_adjustment  # noqa: F401
 from . import semantic_adjusters  # noqa: F401  (SemanticBundleAdjuster / GeometricSemanticBundleAdjuster as solves)
+from . import estimators  # noqa: F401  (RefineAbsolutePose through the device solve)

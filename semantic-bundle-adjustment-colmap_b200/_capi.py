@@ -178,6 +178,7 @@ SYMBOLS = {
     "sba_bench_stage": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int32, _dp, C.POINTER(C.c_int64)]),
     "sba_release_cached_memory": (None, []),
     "sba_observation_errors": (C.c_int, [C.POINTER(ProblemDesc), _dp, _dp]),
+    "sba_normalize": (C.c_int, [C.c_int32, _dp, _dp, _u8p, C.c_int64, _dp, C.c_double, C.c_double, C.c_double, C.c_int32, _dp, _dp]),
     "sba_schur_product": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _ip]),
     "sba_kernel_launch_count": (C.c_int64, [C.c_void_p]),
     "sba_comm_get_unique_id": (C.c_int, [C.c_void_p]),

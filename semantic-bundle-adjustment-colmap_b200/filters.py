@@ -113,3 +113,33 @@ def filter_points3D_with_large_reprojection_error(rec, max_reproj_error, point3D
                 delete_observation(rec, el.image_id, el.point2D_idx)
             p.error = total / p.track.Length()
     return num_filtered
+
+
+def device_normalize(qvec, tvec, registered, points, extent, p0, p1, use_images):
+    """sba_normalize on flat arrays (in place); returns (scale, translation)."""
+    scale, tr = C.c_double(), np.zeros(3)
+    capi.check(capi.load().sba_normalize(len(qvec), capi.ptr(qvec, capi._dp), capi.ptr(tvec, capi._dp), capi.ptr(registered, capi._u8p),
+                                         len(points), capi.ptr(points, capi._dp), extent, p0, p1, 1 if use_images else 0,
+                                         C.byref(scale), capi.ptr(tr, capi._dp)))
+    return scale.value, tr
+
+
+def normalize(rec, extent=10.0, p0=0.1, p1=0.9, use_images=True, registered_image_ids=None, normalize_fn=device_normalize):
+    """Reconstruction::Normalize (/root/reference/src/base/reconstruction.cc:321-345), the mapper's step after global BA
+    (/root/reference/src/sfm/incremental_mapper.cc:711).  The mirror Reconstruction has no registration flag: every image
+    counts as registered unless `registered_image_ids` is given.  Returns (scale, translation) of the similarity applied
+    ((1, 0) when fewer than two elements: nothing changes).  `normalize_fn` lets the tests substitute the oracle."""
+    if not extent > 0:
+        raise ValueError("extent must be positive")  # CHECK_GT, :323
+    ids = list(rec.images)
+    reg = np.ones(len(ids), np.uint8) if registered_image_ids is None else np.array([1 if i in set(registered_image_ids) else 0 for i in ids], np.uint8)
+    q = np.array([rec.images[i].qvec for i in ids], dtype=np.float64).reshape(-1, 4)
+    t = np.array([rec.images[i].tvec for i in ids], dtype=np.float64).reshape(-1, 3)
+    pids = list(rec.points3D)
+    X = np.array([rec.points3D[p].xyz for p in pids], dtype=np.float64).reshape(-1, 3)
+    scale, tr = normalize_fn(q, t, reg, X, extent, p0, p1, use_images)
+    for k, i in enumerate(ids):
+        rec.images[i].qvec[:] = q[k]; rec.images[i].tvec[:] = t[k]
+    for k, p in enumerate(pids):
+        rec.points3D[p].xyz[:] = X[k]
+    return scale, tr

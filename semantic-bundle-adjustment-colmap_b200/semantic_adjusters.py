@@ -4,10 +4,12 @@
 714-996).  Images are given in the iteration order of config.Images() (= residual order); poses (and cylinders) are
 updated in place, as the reference mutates the Reconstruction.  Nothing here computes residuals on the CPU."""
 import ctypes as C
+import os
 
 import numpy as np
 
 from . import _capi as capi
+from . import model_io
 
 
 def semantic_solver_options(max_num_iterations=100):
@@ -17,6 +19,35 @@ def semantic_solver_options(max_num_iterations=100):
     o.max_num_iterations = max_num_iterations
     o.update_state_every_iteration = 1
     return o
+
+
+class StepDumper:
+    """Per-iteration dump of the two semantic adjusters: SBACallbackFunctor (semantic_bundle_adjustment.cc:1090-1123) and the
+    GSBA callback (geometric_semantic_bundle_adjustment.cc:1482-1558) write, after EVERY iteration (0 = the starting point),
+        <optim_steps_folder>/step_<iteration>/{cameras,images,points3D}.bin      Reconstruction::Write
+        <optim_steps_folder>/step_<iteration>/text/{cameras,images,points3D}.txt Reconstruction::WriteText
+        <optim_steps_folder>/step_<iteration>/cylinders.txt                      exportCylindersToText (GSBA only)
+    which needs solver_options.update_state_every_iteration (semantic_bundle_adjustment.h:129): the device solve then
+    copies the current poses (and cylinders) into the problem's arrays before each callback.  Use as the `callback` of
+    SemanticProblem.solve / CylinderProblem.solve; `image_ids[k]` is the Reconstruction image behind the problem's k-th pose.
+    The reference's JPG mask renderings and CSV error export are not written (no image codec in this package)."""
+
+    def __init__(self, problem, reconstruction, image_ids, optim_steps_folder, inner=None):
+        self.problem, self.rec, self.image_ids, self.folder, self.inner = problem, reconstruction, list(image_ids), optim_steps_folder, inner
+        self.steps = []
+
+    def __call__(self, it):
+        for k, image_id in enumerate(self.image_ids):
+            im = self.rec.Image(image_id)
+            im.Qvec()[:] = self.problem.image_qvec[k]
+            im.Tvec()[:] = self.problem.image_tvec[k]
+        step = os.path.join(self.folder, "step_%d" % it.iteration)
+        model_io.write_model(self.rec, step, ".bin")
+        model_io.write_model(self.rec, os.path.join(step, "text"), ".txt")
+        if hasattr(self.problem, "cylinder_params") and getattr(self.problem, "cylinder_kind", 0) == 0:
+            model_io.write_cylinders(os.path.join(step, "cylinders.txt"), self.problem.cylinder_params)
+        self.steps.append(it.iteration)
+        return int(self.inner(it) or 0) if self.inner is not None else 0
 
 
 class _PoseProblem:

@@ -167,3 +167,63 @@ def test_filters_on_the_device_equal_the_oracle_run(sba, oracle):
     sa, sb = snapshot(a), snapshot(b)
     assert sa[0] == sb[0] and sa[1] == sb[1]
     assert all(abs(sa[2][k] - sb[2][k]) <= 1e-10 * max(1.0, abs(sb[2][k])) for k in sb[2])
+
+
+# ------------------------------------------------------------------ Reconstruction::Normalize
+def _normalize_inputs(sba, seed=0, n_img=40, n_pt=3000):
+    rng = np.random.default_rng(seed)
+    q = rng.normal(size=(n_img, 4)); q[::7] *= 3.0          # not normalised on purpose; some w < 0
+    t = rng.normal(scale=4.0, size=(n_img, 3)) + np.array([30.0, -12.0, 5.0])
+    X = rng.normal(scale=6.0, size=(n_pt, 3)) + np.array([-20.0, 8.0, 40.0])
+    reg = np.ones(n_img, np.uint8); reg[3] = 0; reg[min(11, n_img - 1)] = 0
+    return q, t, reg, X
+
+
+def test_normalize_oracle_properties(sba):
+    """The restatement itself: extent of the robust box of the transformed centres = `extent`, centroid at the origin,
+    projections unchanged (a similarity of the world does not move image points)."""
+    from oracle import normalize_oracle as no
+    q, t, reg, X = _normalize_inputs(sba)
+    q0, t0, X0 = q.copy(), t.copy(), X.copy()
+    s, tr = no.normalize(q, t, reg, X, 10.0, 0.1, 0.9, True)
+    centres = np.array([-(no.quat_to_rot(q[i]).T @ t[i]) for i in np.nonzero(reg)[0]])
+    lo, hi, mean = no.bounds_and_centroid(centres, 0.1, 0.9)
+    assert abs(np.linalg.norm(hi - lo) - 10.0) < 1e-5 and np.linalg.norm(mean) < 1e-5   # float-cast coordinates
+    for i in (0, 3, 17):
+        a = no.quat_to_rot(q0[i]) @ X0[5] + t0[i]
+        b = no.quat_to_rot(q[i]) @ X[5] + t[i]
+        assert np.allclose(a[:2] / a[2], b[:2] / b[2], rtol=1e-12) and np.isclose(b[2], s * a[2], rtol=1e-12)
+        assert np.isclose(np.linalg.norm(q[i]), 1.0, rtol=1e-14)
+    # fewer than two elements: untouched
+    q1, t1, X1 = q0[:1].copy(), t0[:1].copy(), X0.copy()
+    assert no.normalize(q1, t1, np.ones(1, np.uint8), X1, 10.0, 0.1, 0.9, True)[0] == 1.0 and np.array_equal(X1, X0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("use_images", [True, False])
+def test_normalize_device_matches_oracle(sba, use_images):
+    from oracle import normalize_oracle as no
+    q, t, reg, X = _normalize_inputs(sba, seed=4)
+    qo, to, Xo = q.copy(), t.copy(), X.copy()
+    s_ref, tr_ref = no.normalize(qo, to, reg, Xo, 10.0, 0.1, 0.9, use_images)
+    s, tr = sba.filters.device_normalize(q, t, reg, X, 10.0, 0.1, 0.9, use_images)
+    assert abs(s - s_ref) <= 1e-13 * s_ref and np.allclose(tr, tr_ref, rtol=1e-12, atol=1e-12)
+    assert np.allclose(X, Xo, rtol=1e-12, atol=1e-12) and np.allclose(t, to, rtol=1e-12, atol=1e-12)
+    assert np.allclose(q, qo, rtol=0, atol=1e-14)
+    # through the Reconstruction mirror, and the degenerate cases
+    rec = sba.Reconstruction()
+    rec.AddCamera(sba.Camera(1, "SIMPLE_PINHOLE", [500.0, 320.0, 240.0], 640, 480))
+    q2, t2, _, X2 = _normalize_inputs(sba, seed=9, n_img=5, n_pt=50)
+    for i in range(5):
+        rec.AddImage(sba.Image(i + 1, 1, q2[i], t2[i], name="i%d.png" % i))
+    for k in range(50):
+        rec.AddPoint3D(X2[k], [])
+    s2, _ = sba.filters.normalize(rec)
+    qo2, to2, Xo2 = q2.copy(), t2.copy(), X2.copy()
+    s2_ref, _ = no.normalize(qo2, to2, np.ones(5, np.uint8), Xo2, 10.0, 0.1, 0.9, True)
+    assert abs(s2 - s2_ref) <= 1e-13 * s2_ref and np.allclose(rec.Image(3).Tvec(), to2[2], rtol=1e-12, atol=1e-12)
+    lib = sba.capi.load()
+    assert lib.sba_normalize(0, None, None, None, 0, None, 0.0, 0.1, 0.9, 1, None, None) == sba.capi.ERR_INVALID_ARGUMENT
+    one_q, one_t = q[:1].copy(), t[:1].copy()
+    assert sba.filters.device_normalize(one_q, one_t, np.ones(1, np.uint8), X.copy(), 10.0, 0.1, 0.9, True)[0] == 1.0
+    assert np.array_equal(one_q, q[:1])

@@ -225,3 +225,43 @@ def test_python_wrappers(sba, oracle):
     assert s is not None and s.num_residual_blocks == 9 and s.final_cost <= s.initial_cost
     none, _ = sba.semantic_adjusters.SemanticProblem(q, t, cams, depth, label, image_pose_constant=[1, 1, 1]).solve()
     assert none is None
+
+
+@pytest.mark.gpu
+def test_per_iteration_dump_directories(sba, oracle, tmp_path):
+    """SBACallbackFunctor / the GSBA callback (semantic_bundle_adjustment.cc:1104-1119,
+    geometric_semantic_bundle_adjustment.cc:1546-1556): step_k/ holds the binary model, step_k/text the text model (and
+    cylinders.txt), with the poses of iteration k -- the last one equals the solve's result."""
+    ba, io, sa = sba.bundle_adjustment, sba.model_io, sba.semantic_adjusters
+    q, t, cams, depth, label = _perturbed_scene(sba, n_img=3, seed=1)
+    rec = ba.Reconstruction()
+    H, W = depth.shape[1:]
+    for k in range(3):
+        rec.AddCamera(ba.Camera(k + 1, "SIMPLE_PINHOLE", list(cams[k]), W, H))
+        rec.AddImage(ba.Image(10 + k, k + 1, q[k], t[k], name="frame_%d.png" % k))
+    prob = sa.SemanticProblem(q, t, cams, depth, label, image_pose_constant=[1, 0, 0], pixel_step=4)
+    dump = sa.StepDumper(prob, rec, [10, 11, 12], str(tmp_path / "optim_steps"))
+    s, rows = prob.solve(sa.semantic_solver_options(5), callback=dump)
+    assert s is not None and dump.steps == [r.iteration for r in rows] and dump.steps[0] == 0
+    first = io.read_model(str(tmp_path / "optim_steps" / "step_0"))
+    assert np.allclose(first.Image(11).Tvec(), t[1], rtol=0, atol=0)          # iteration 0 = the starting point
+    last = io.read_model(str(tmp_path / "optim_steps" / ("step_%d" % dump.steps[-1])))
+    txt = io.read_model(str(tmp_path / "optim_steps" / ("step_%d" % dump.steps[-1]) / "text"))
+    for k in range(3):
+        assert np.array_equal(last.Image(10 + k).Tvec(), prob.image_tvec[k])   # binary: exact
+        assert np.array_equal(last.Image(10 + k).Qvec(), prob.image_qvec[k])
+        assert np.allclose(txt.Image(10 + k).Tvec(), prob.image_tvec[k], rtol=1e-15, atol=0)
+    if s.num_successful_steps > 0:
+        assert not np.array_equal(last.Image(11).Tvec(), first.Image(11).Tvec())
+    # cylinders
+    pc, keep = cylinder_problem(sba, oracle, kind=0)
+    cp = sa.CylinderProblem(keep[0], keep[1], keep[2], keep[3], keep[6], image_pose_constant=[1, 0, 0])
+    rec2 = ba.Reconstruction()
+    for k in range(len(keep[0])):
+        rec2.AddCamera(ba.Camera(k + 1, "SIMPLE_PINHOLE", list(np.asarray(keep[2]).reshape(-1, 3)[k]), keep[3].shape[2], keep[3].shape[1]))
+        rec2.AddImage(ba.Image(k + 1, k + 1, np.asarray(keep[0]).reshape(-1, 4)[k], np.asarray(keep[1]).reshape(-1, 3)[k], name="c%d.png" % k))
+    dump2 = sa.StepDumper(cp, rec2, [k + 1 for k in range(len(keep[0]))], str(tmp_path / "gsba_steps"))
+    s2, rows2 = cp.solve(sa.semantic_solver_options(4), callback=dump2)
+    assert s2 is not None and len(dump2.steps) == len(rows2)
+    cyl = io.read_cylinders(str(tmp_path / "gsba_steps" / ("step_%d" % dump2.steps[-1]) / "cylinders.txt"))
+    assert np.allclose(np.asarray(cyl).reshape(-1, 9), cp.cylinder_params, rtol=1e-5, atol=1e-6)  # "%g": 6 digits
