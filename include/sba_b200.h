@@ -481,6 +481,49 @@ typedef struct sba_rig_desc {
  * d r / d (rig_q(4), rig_t(3), rel_q(4), rel_t(3), point(3), camera params(12)), as CostFunction::Evaluate returns. */
 int sba_rig_evaluate(const sba_rig_desc* d, double* residuals, double* jac, double* ms_device);
 
+/* --- RigBundleAdjuster as a solve ------------
+ * RigBundleAdjuster::Solve, src/optim/bundle_adjustment.cc:789-1140.  The flat problem holds what SetUp adds to Ceres:
+ * one residual block per kept observation with the parameter blocks (rig pose of the snapshot, relative pose of the
+ * camera in the rig, point, intrinsics) (:1017-1031).  An image OUTSIDE every rig (:981-1014) is a block whose
+ * "relative pose" is the image's own pose and whose rig pose is a constant identity (1,0,0,0 | 0,0,0): the composed
+ * pose and its Jacobian are then exactly those of the ordinary functor.  Constancy:
+ *   rig_pose_constant[i]       1: q and t constant (the identity above)
+ *   rel_pose_constant[i]       1: q and t constant (reference camera of a rig, :1040-1046; refine_relative_poses = false;
+ *                              images with constant pose)
+ *   rel_tvec_constant_mask[i]  bit j: tvec[j] constant (SubsetManifold, :1049-1053)
+ *   camera_param_constant_mask, point_constant: as in sba_problem_desc
+ * Blocks that no residual block names are left untouched.  All parameter arrays are IN/OUT.
+ * SMALL-PROBLEM PATH: the LM step solves the dense normal equations over ALL blocks, points included (what the Schur
+ * solvers compute after eliminating the points, to rounding); J is held dense and problems with
+ * 2 * num_blocks * tangent_dimension > 2^28 are refused with SBA_ERR_INVALID_ARGUMENT.
+ * Returns SBA_ERR_EMPTY_PROBLEM when there is no residual block (Solve returns false, :824-826). */
+typedef struct sba_rig_problem {
+  int32_t num_rig_poses;
+  double* rig_qvec;                   /* [num_rig_poses*4] */
+  double* rig_tvec;                   /* [num_rig_poses*3] */
+  const uint8_t* rig_pose_constant;   /* [num_rig_poses] nullable */
+  int32_t num_rel_poses;
+  double* rel_qvec;                   /* [num_rel_poses*4] */
+  double* rel_tvec;                   /* [num_rel_poses*3] */
+  const uint8_t* rel_pose_constant;       /* [num_rel_poses] nullable */
+  const uint8_t* rel_tvec_constant_mask;  /* [num_rel_poses] nullable */
+  int32_t num_cameras;
+  const int32_t* camera_model;        /* [num_cameras] */
+  double* camera_params;              /* [num_cameras*SBA_MAX_CAMERA_PARAMS] */
+  const uint16_t* camera_param_constant_mask; /* [num_cameras] nullable */
+  int32_t num_points;
+  double* points;                     /* [num_points*3] */
+  const uint8_t* point_constant;      /* [num_points] nullable */
+  int64_t num_blocks;
+  const int32_t* block_rig;           /* [num_blocks] */
+  const int32_t* block_rel;           /* [num_blocks] */
+  const int32_t* block_camera;        /* [num_blocks] */
+  const int32_t* block_point;         /* [num_blocks] */
+  const double* block_xy;             /* [num_blocks*2] */
+} sba_rig_problem;
+int sba_rig_solve(sba_rig_problem* problem, const sba_solver_options* opts, sba_iteration_callback cb, void* user,
+                  sba_summary* summary, sba_iteration_summary* trace, int32_t trace_cap, int32_t* trace_n);
+
 #ifdef __cplusplus
 }
 #endif

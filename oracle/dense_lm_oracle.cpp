@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "ba_oracle.h"
+#include "projection.h"
 #include "rotation.h"
 #include "semantic_oracle.h"
 
@@ -71,9 +72,12 @@ struct DenseProblem {
   std::function<double(const std::vector<double>& delta, double* step2, double* x2)> candidate;  // also stores the candidate
   std::function<void()> accept;
   int loss_type = SBA_LOSS_TRIVIAL; double loss_scale = 1.0; double loss_weight = 1.0;  // rho(s) = weight * loss(s)
+  // optional: H, g, cost of the current point for problems whose blocks are not single rows (the rig solve)
+  std::function<void(std::vector<double>*, std::vector<double>*, double*)> linearize;
 };
 
 void Linearize(const DenseProblem& P, std::vector<double>* H, std::vector<double>* g, double* cost) {
+  if (P.linearize) { P.linearize(H, g, cost); return; }
   std::vector<Row> rows;
   P.rows(&rows);
   const int n = P.n;
@@ -501,6 +505,167 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
   std::memcpy(d->image_qvec, q.data(), q.size() * sizeof(double));
   std::memcpy(d->image_tvec, t.data(), t.size() * sizeof(double));
   if (n_cyl > 0) std::memcpy(d->cylinder_params, cyl.data(), cyl.size() * sizeof(double));
+  return rc;
+}
+
+// ---- RigBundleAdjuster as a solve (/root/reference/src/optim/bundle_adjustment.cc:789-1140) ---------------------------
+// The flat problem of sba_rig_solve (include/sba_b200.h): two-row blocks over (rig pose, relative pose, point,
+// intrinsics) with the Jet Jacobian of the rig functor (EvalRigObservation, ba_oracle.cpp), QuaternionManifold /
+// SubsetManifold columns, the loss corrector on the 2-vector, dense normal equations over all blocks.
+int oracle_rig_solve(sba_rig_problem* d, const sba_solver_options* o, int threads, sba_summary* summary,
+                     sba_iteration_summary* trace, int32_t trace_cap, int32_t* trace_n) {
+  (void)threads;
+  std::memset(summary, 0, sizeof(*summary));
+  if (trace_n) *trace_n = 0;
+  const int n_rig = d->num_rig_poses, n_rel = d->num_rel_poses, n_pose = n_rig + n_rel, n_cam = d->num_cameras, n_pt = d->num_points;
+  const int64_t n_obs = d->num_blocks;
+  if (n_obs == 0) return SBA_ERR_EMPTY_PROBLEM;
+  std::vector<uint8_t> use_pose(n_pose, 0), use_cam(n_cam, 0), use_pt(n_pt, 0);
+  for (int64_t k = 0; k < n_obs; ++k) {
+    use_pose[d->block_rig[k]] = use_pose[n_rig + d->block_rel[k]] = 1;
+    use_cam[d->block_camera[k]] = 1; use_pt[d->block_point[k]] = 1;
+  }
+  std::vector<int> qcol(n_pose, -1), tcol(3 * (size_t)n_pose, -1), pcol(12 * (size_t)std::max(1, n_cam), -1), xcol(std::max(1, n_pt), -1);
+  int n = 0;
+  for (int i = 0; i < n_pose; ++i) {
+    const bool rig = i < n_rig;
+    const int j = rig ? i : i - n_rig;
+    const bool konst = rig ? (d->rig_pose_constant && d->rig_pose_constant[j]) : (d->rel_pose_constant && d->rel_pose_constant[j]);
+    if (!use_pose[i] || konst) continue;
+    qcol[i] = n; n += 3;
+    summary->num_parameter_blocks_reduced++; summary->num_parameters_reduced += 4;
+    const unsigned mask = (!rig && d->rel_tvec_constant_mask) ? d->rel_tvec_constant_mask[j] & 7u : 0u;
+    if (mask != 7u) {
+      for (int c = 0; c < 3; ++c) if (!(mask >> c & 1u)) tcol[3 * (size_t)i + c] = n++;
+      summary->num_parameter_blocks_reduced++; summary->num_parameters_reduced += 3;
+    }
+  }
+  for (int c = 0; c < n_cam; ++c) {
+    if (!use_cam[c]) continue;
+    const int np = NumParams(d->camera_model[c]);
+    const unsigned mask = d->camera_param_constant_mask ? d->camera_param_constant_mask[c] : 0u;
+    bool any = false;
+    for (int j = 0; j < np; ++j) if (!(mask >> j & 1u)) { pcol[12 * (size_t)c + j] = n++; any = true; }
+    if (any) { summary->num_parameter_blocks_reduced++; summary->num_parameters_reduced += np; }
+  }
+  for (int p = 0; p < n_pt; ++p) {
+    if (!use_pt[p] || (d->point_constant && d->point_constant[p])) continue;
+    xcol[p] = n; n += 3;
+    summary->num_parameter_blocks_reduced++; summary->num_parameters_reduced += 3;
+  }
+  summary->num_residual_blocks = (int)n_obs; summary->num_residuals = summary->num_residuals_reduced = 2 * (int)n_obs;
+  summary->num_effective_parameters_reduced = n;
+  summary->linear_solver_type_used = SBA_DENSE_SCHUR;
+  // current and candidate state
+  struct State { std::vector<double> q, t, cam, X; };
+  State cur, cand;
+  cur.q.resize(4 * (size_t)n_pose); cur.t.resize(3 * (size_t)n_pose);
+  for (int i = 0; i < n_rig; ++i) { std::memcpy(&cur.q[4 * (size_t)i], d->rig_qvec + 4 * (size_t)i, 32); std::memcpy(&cur.t[3 * (size_t)i], d->rig_tvec + 3 * (size_t)i, 24); }
+  for (int i = 0; i < n_rel; ++i) { std::memcpy(&cur.q[4 * (size_t)(n_rig + i)], d->rel_qvec + 4 * (size_t)i, 32); std::memcpy(&cur.t[3 * (size_t)(n_rig + i)], d->rel_tvec + 3 * (size_t)i, 24); }
+  cur.cam.assign(d->camera_params, d->camera_params + 12 * (size_t)n_cam);
+  cur.X.assign(d->points, d->points + 3 * (size_t)n_pt);
+  cand = cur;
+  auto block = [&](const State& S, int64_t k, double* r, double* J) {
+    const int a = d->block_rig[k], b = n_rig + d->block_rel[k], c = d->block_camera[k], p = d->block_point[k];
+    EvalRigObservation(d->camera_model[c], &S.q[4 * (size_t)a], &S.t[3 * (size_t)a], &S.q[4 * (size_t)b], &S.t[3 * (size_t)b],
+                       &S.X[3 * (size_t)p], &S.cam[12 * (size_t)c], d->block_xy + 2 * k, r, J);
+  };
+  auto cost_of = [&](const State& S) {
+    double c = 0.0;
+    for (int64_t k = 0; k < n_obs; ++k) {
+      double r[2], rho[3];
+      block(S, k, r, nullptr);
+      LossEvalD(o->loss_function_type, o->loss_function_scale, r[0] * r[0] + r[1] * r[1], rho);
+      c += 0.5 * rho[0];
+    }
+    return c;
+  };
+  DenseProblem P;
+  P.n = n;
+  P.linearize = [&](std::vector<double>* H, std::vector<double>* g, double* cost) {
+    H->assign((size_t)n * n, 0.0); g->assign(n, 0.0);
+    double c = 0.0;
+    constexpr int W = 4 + 3 + 4 + 3 + 3 + SBA_MAX_CAMERA_PARAMS;
+    for (int64_t k = 0; k < n_obs; ++k) {
+      const int a = d->block_rig[k], b = n_rig + d->block_rel[k], cm = d->block_camera[k], p = d->block_point[k];
+      double r[2], J[2 * W], rho[3];
+      block(cur, k, r, J);
+      const double s = r[0] * r[0] + r[1] * r[1];
+      LossEvalD(o->loss_function_type, o->loss_function_scale, s, rho);
+      c += 0.5 * rho[0];
+      const double sq = std::sqrt(rho[1]);
+      double rscale = sq, asn = 0.0;
+      if (!(s == 0.0 || rho[2] <= 0.0)) {
+        const double alpha = 1.0 - std::sqrt(1.0 + 2.0 * s * rho[2] / rho[1]);
+        rscale = sq / (1.0 - alpha); asn = alpha / s;
+      }
+      int col[27]; double j0[27], j1[27]; int m = 0;
+      auto put = [&](int cidx, double x0, double x1) {
+        if (cidx < 0) return;
+        if (asn != 0.0) { const double rtj = r[0] * x0 + r[1] * x1; x0 -= asn * r[0] * rtj; x1 -= asn * r[1] * rtj; }
+        col[m] = cidx; j0[m] = sq * x0; j1[m] = sq * x1; ++m;
+      };
+      const double* A = J; const double* B = J + W;
+      double l0[3], l1[3];
+      if (qcol[a] >= 0) { QuatTangentRow(&cur.q[4 * (size_t)a], A, l0); QuatTangentRow(&cur.q[4 * (size_t)a], B, l1); for (int j = 0; j < 3; ++j) put(qcol[a] + j, l0[j], l1[j]); }
+      for (int j = 0; j < 3; ++j) put(tcol[3 * (size_t)a + j], A[4 + j], B[4 + j]);
+      if (qcol[b] >= 0) { QuatTangentRow(&cur.q[4 * (size_t)b], A + 7, l0); QuatTangentRow(&cur.q[4 * (size_t)b], B + 7, l1); for (int j = 0; j < 3; ++j) put(qcol[b] + j, l0[j], l1[j]); }
+      for (int j = 0; j < 3; ++j) put(tcol[3 * (size_t)b + j], A[11 + j], B[11 + j]);
+      if (xcol[p] >= 0) for (int j = 0; j < 3; ++j) put(xcol[p] + j, A[14 + j], B[14 + j]);
+      for (int j = 0; j < 12; ++j) put(pcol[12 * (size_t)cm + j], A[17 + j], B[17 + j]);
+      const double r0 = r[0] * rscale, r1 = r[1] * rscale;
+      for (int x = 0; x < m; ++x) {
+        (*g)[col[x]] += j0[x] * r0 + j1[x] * r1;
+        for (int y = 0; y < m; ++y) (*H)[(size_t)col[x] * n + col[y]] += j0[x] * j0[y] + j1[x] * j1[y];
+      }
+    }
+    *cost = c;
+  };
+  P.candidate = [&](const std::vector<double>& delta, double* step2, double* x2) {
+    *step2 = 0.0; *x2 = 0.0;
+    cand = cur;
+    for (int i = 0; i < n_pose; ++i) {
+      if (qcol[i] >= 0) {
+        const double* q = &cur.q[4 * (size_t)i];
+        QuaternionPlus(q, &delta[qcol[i]], &cand.q[4 * (size_t)i]);
+        for (int a = 0; a < 4; ++a) { const double e = cand.q[4 * (size_t)i + a] - q[a]; *step2 += e * e; *x2 += q[a] * q[a]; }
+      }
+      bool var = false;
+      for (int a = 0; a < 3; ++a) var = var || tcol[3 * (size_t)i + a] >= 0;
+      if (var) for (int a = 0; a < 3; ++a) {
+        const int c = tcol[3 * (size_t)i + a];
+        const double t = cur.t[3 * (size_t)i + a];
+        if (c >= 0) cand.t[3 * (size_t)i + a] = t + delta[c];
+        const double e = cand.t[3 * (size_t)i + a] - t; *step2 += e * e; *x2 += t * t;
+      }
+    }
+    for (int c = 0; c < n_cam; ++c) {
+      bool var = false;
+      for (int j = 0; j < 12; ++j) var = var || pcol[12 * (size_t)c + j] >= 0;
+      if (!var) continue;
+      const int np = NumParams(d->camera_model[c]);
+      for (int j = 0; j < np; ++j) {
+        const int cc = pcol[12 * (size_t)c + j];
+        const double v = cur.cam[12 * (size_t)c + j];
+        if (cc >= 0) cand.cam[12 * (size_t)c + j] = v + delta[cc];
+        const double e = cand.cam[12 * (size_t)c + j] - v; *step2 += e * e; *x2 += v * v;
+      }
+    }
+    for (int p = 0; p < n_pt; ++p) if (xcol[p] >= 0) for (int a = 0; a < 3; ++a) {
+      const double v = cur.X[3 * (size_t)p + a];
+      cand.X[3 * (size_t)p + a] = v + delta[xcol[p] + a];
+      const double e = cand.X[3 * (size_t)p + a] - v; *step2 += e * e; *x2 += v * v;
+    }
+    return cost_of(cand);
+  };
+  P.accept = [&]() { cur = cand; };
+  std::vector<sba_iteration_summary> rows;
+  const int rc = SolveDense(P, *o, summary, &rows);
+  if (trace && trace_n) { const int k = std::min<int>((int)rows.size(), trace_cap); for (int i = 0; i < k; ++i) trace[i] = rows[i]; *trace_n = k; }
+  for (int i = 0; i < n_rig; ++i) { std::memcpy(d->rig_qvec + 4 * (size_t)i, &cur.q[4 * (size_t)i], 32); std::memcpy(d->rig_tvec + 3 * (size_t)i, &cur.t[3 * (size_t)i], 24); }
+  for (int i = 0; i < n_rel; ++i) { std::memcpy(d->rel_qvec + 4 * (size_t)i, &cur.q[4 * (size_t)(n_rig + i)], 32); std::memcpy(d->rel_tvec + 3 * (size_t)i, &cur.t[3 * (size_t)(n_rig + i)], 24); }
+  if (n_cam) std::memcpy(d->camera_params, cur.cam.data(), cur.cam.size() * sizeof(double));
+  if (n_pt) std::memcpy(d->points, cur.X.data(), cur.X.size() * sizeof(double));
   return rc;
 }
 

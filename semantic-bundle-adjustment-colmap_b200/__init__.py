@@ -17,3 +17,4 @@ from . import filters  # noqa: F401
 from . import bundle_adjustment  # noqa: F401
 from . import semantic_adjusters  # noqa: F401  (SemanticBundleAdjuster / GeometricSemanticBundleAdjuster as solves)
 from . import estimators  # noqa: F401  (RefineAbsolutePose through the device solve)
+from . import rig_adjuster  # noqa: F401  (RigBundleAdjuster over sba_rig_solve)

@@ -154,6 +154,18 @@ class RigDesc(C.Structure):
 
 RIG_JAC_COLS = 4 + 3 + 4 + 3 + 3 + 12
 
+
+class RigProblem(C.Structure):
+    _fields_ = [
+        ("num_rig_poses", C.c_int32), ("rig_qvec", _dp), ("rig_tvec", _dp), ("rig_pose_constant", _u8p),
+        ("num_rel_poses", C.c_int32), ("rel_qvec", _dp), ("rel_tvec", _dp), ("rel_pose_constant", _u8p),
+        ("rel_tvec_constant_mask", _u8p),
+        ("num_cameras", C.c_int32), ("camera_model", _ip), ("camera_params", _dp), ("camera_param_constant_mask", _u16p),
+        ("num_points", C.c_int32), ("points", _dp), ("point_constant", _u8p),
+        ("num_blocks", C.c_int64), ("block_rig", _ip), ("block_rel", _ip), ("block_camera", _ip), ("block_point", _ip),
+        ("block_xy", _dp),
+    ]
+
 ITERATION_CALLBACK = C.CFUNCTYPE(C.c_int, C.POINTER(IterationSummary), C.c_void_p)
 
 # every entry point include/sba_b200.h declares: name -> (restype, argtypes)
@@ -193,6 +205,8 @@ SYMBOLS = {
     "sba_cylinder_solve": (C.c_int, [C.POINTER(CylinderProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,
                                      C.POINTER(Summary), C.POINTER(IterationSummary), C.c_int32, _ip]),
     "sba_rig_evaluate": (C.c_int, [C.POINTER(RigDesc), _dp, _dp, _dp]),
+    "sba_rig_solve": (C.c_int, [C.POINTER(RigProblem), C.POINTER(SolverOptions), ITERATION_CALLBACK, C.c_void_p,
+                                C.POINTER(Summary), C.POINTER(IterationSummary), C.c_int32, _ip]),
 }
 
 _lib = None

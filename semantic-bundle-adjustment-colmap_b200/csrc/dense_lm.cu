@@ -172,7 +172,8 @@ int DenseLMSolve(DenseGroups& G, const sba_solver_options& o, const DenseLMCallb
   auto linearize = [&](double* cost, double* gmax) -> int {
     int r = F.linearize();
     if (r) return r;
-    if ((r = AssembleDense(G, H.p, g.p, scal.p + 2, st, &launches))) return r;
+    if (F.assemble) { if ((r = F.assemble(H.p, g.p, scal.p + 2))) return r; }
+    else if ((r = AssembleDense(G, H.p, g.p, scal.p + 2, st, &launches))) return r;
     double h[1];
     SBA_CUDA(cudaMemcpyAsync(h, scal.p + 2, sizeof(double), cudaMemcpyDeviceToHost, st));
     SBA_CUDA(cudaStreamSynchronize(st));

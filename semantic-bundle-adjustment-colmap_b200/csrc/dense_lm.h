@@ -48,6 +48,9 @@ struct DenseLMCallbacks {
   sba_iteration_callback cb = nullptr;        // solver_options.callbacks
   void* user = nullptr;
   std::function<void()> before_callback;      // update_state_every_iteration: make the current point visible to cb
+  // optional: H (n x n row-major, both triangles), g (n), cost of the current point, in place of the group records
+  // (problems whose residual blocks span more than two entities: the rig solve); G then only carries n
+  std::function<int(double* d_H, double* d_g, double* d_cost)> assemble;
 };
 
 // Runs the LM loop; summary counts (num_residuals ...) are the caller's.  trace receives the iteration table.
