@@ -448,6 +448,10 @@ def run_b200(args, m):
                            "device_total": summ.device_time_s * 1e3},
     }
     if world > 1:
+        # per-rank timeline of the last timed solve (filled when SBA_NO_GRAPHS=1 keeps plain launches with stage events)
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, dict(line["solve_stage_ms"], rank=rank))
+        line["solve_stage_ms_per_rank"] = per_rank
         # correctness gate of the sharded solve: rank 0 solves the SAME problem unsharded on its own GPU
         s.close()
         rel = None
