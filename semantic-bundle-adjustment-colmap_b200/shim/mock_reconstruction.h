@@ -164,7 +164,7 @@ class Image {
 class Reconstruction {
  public:
   void AddCamera(const class Camera& c) { cameras_[c.CameraId()] = c; }
-  void AddImage(const class Image& im) { images_[im.ImageId()] = im; }
+  void AddImage(const class Image& im) { images_[im.ImageId()] = im; reg_image_ids_.push_back(im.ImageId()); }  // (every mock image is registered)
   point3D_t AddPoint3D(const Vector3d& xyz, const Track& track) {  // reconstruction.cc:299-324
     const point3D_t id = ++num_added_points3D_;
     class Point3D& p = points3D_[id];
@@ -187,11 +187,14 @@ class Reconstruction {
   size_t NumImages() const { return images_.size(); }
   size_t NumPoints3D() const { return points3D_.size(); }
   const std::unordered_map<point3D_t, class Point3D>& Points3D() const { return points3D_; }
+  const std::unordered_map<image_t, class Image>& Images() const { return images_; }   // reconstruction.h:96
+  const std::vector<image_t>& RegImageIds() const { return reg_image_ids_; }           // reconstruction.h:99
 
  private:
   std::unordered_map<camera_t, class Camera> cameras_;
   std::unordered_map<image_t, class Image> images_;
   std::unordered_map<point3D_t, class Point3D> points3D_;
+  std::vector<image_t> reg_image_ids_;
   point3D_t num_added_points3D_ = 0;
 };
 

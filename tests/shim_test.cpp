@@ -10,6 +10,7 @@
 
 #include "mock_reconstruction.h"
 #include "sba_bundle_adjuster.h"
+#include "sba_mapper_passes.h"
 #include "sba_semantic_adjusters.h"
 
 using namespace sba_mock;
@@ -372,6 +373,53 @@ static void TestSemanticSolve() {
   }
 }
 
+// ---- mapper-side passes (shim/sba_mapper_passes.h) ------------------------------------------------------------------
+static void TestMapperPasses() {
+  {  // Normalize: the robust box of the projection centres gets extent 10 and its centroid the origin; projections stay
+    Reconstruction rec; Generate(6, 50, &rec);
+    const Reconstruction orig = rec;
+    const double scale = sba_shim::Normalize(&rec);
+    CHECK_THAT(scale > 0.0 && scale != 1.0);
+    const auto& p0 = *orig.Points3D().begin();
+    const Vector3d a = orig.Image(2).Tvec(), b = rec.Image(2).Tvec();
+    const Vector3d X0 = p0.second.XYZ(), X1 = rec.Point3D(p0.first).XYZ();
+    // identity rotations (Generate): camera frame = X + t; a similarity of the world scales it
+    for (int j = 0; j < 3; ++j) CHECK_THAT(std::fabs((X1[j] + b[j]) - scale * (X0[j] + a[j])) < 1e-9 * (1.0 + std::fabs(scale * (X0[j] + a[j]))));
+    Reconstruction one; Generate(1, 10, &one);
+    const Reconstruction one_orig = one;
+    CHECK_THAT(sba_shim::Normalize(&one) == 1.0 && one.Image(0).Tvec() == one_orig.Image(0).Tvec());
+    bool threw = false;
+    try { sba_shim::Normalize(&rec, 0.0); } catch (const std::invalid_argument&) { threw = true; }
+    CHECK_THAT(threw);
+  }
+  {  // RefineAbsolutePose: image 1 of a generated scene, pose perturbed, points constant
+    Reconstruction rec; Generate(2, 100, &rec);
+    const Image& im = rec.Image(1);
+    std::vector<Vector2d> xy; std::vector<Vector3d> X; std::vector<char> mask;
+    for (const auto& p2 : im.Points2D()) { xy.push_back(p2.XY()); X.push_back(rec.Point3D(p2.Point3DId()).XYZ()); mask.push_back(1); }
+    mask[3] = 0; xy[3][0] += 300.0;
+    Vector4d q = im.Qvec(); Vector3d t = im.Tvec();
+    const Vector3d t_true = t;
+    t[0] += 0.05; t[1] -= 0.04; q[1] += 0.01;
+    const Vector3d t_start = t;
+    Camera cam = rec.Camera(im.CameraId());
+    const std::vector<double> params0 = cam.Params();
+    sba_shim::AbsolutePoseRefinementOptions o;
+    o.print_summary = false;
+    sba_summary s{};
+    CHECK_THAT(sba_shim::RefineAbsolutePose(o, mask, xy, X, &q, &t, &cam, &s));
+    CHECK_THAT(s.num_residuals_reduced == 198 && s.num_effective_parameters_reduced == 6 + 2);
+    CHECK_THAT(s.final_cost < 0.5 * s.initial_cost);  // (the observations carry U[-2, 2] px of noise: the floor is ~56)
+    double d0 = 0.0, d1 = 0.0;
+    for (int j = 0; j < 2; ++j) { d0 += (t_start[j] - t_true[j]) * (t_start[j] - t_true[j]); d1 += (t[j] - t_true[j]) * (t[j] - t_true[j]); }
+    CHECK_THAT(d1 < d0);
+    CHECK_THAT(cam.Params()[1] == params0[1] && cam.Params()[2] == params0[2]);  // principal point never refined
+    std::printf("refine_absolute_pose: cost %.6g -> %.6g in %d iterations\n", s.initial_cost, s.final_cost, s.num_iterations);
+    std::vector<char> none(mask.size(), 0);
+    CHECK_THAT(sba_shim::RefineAbsolutePose(o, none, xy, X, &q, &t, &cam));
+  }
+}
+
 int main(int argc, char** argv) {
   const bool solve = argc > 1 && std::strcmp(argv[1], "solve") == 0;
   TestCounts();
@@ -383,6 +431,7 @@ int main(int argc, char** argv) {
     }
     TestSolve();
     TestSemanticSolve();
+    TestMapperPasses();
   }
   std::printf("%s (%d failed)\n", g_failed ? "FAILED" : "OK", g_failed);
   return g_failed ? 1 : 0;
