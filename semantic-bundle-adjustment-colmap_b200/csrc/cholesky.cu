@@ -240,45 +240,81 @@ __global__ void __launch_bounds__(256) chol_diag128_kernel(double* __restrict__ 
   stamp();
 }
 
-// ---- panel rows below the diagonal block: L_ik = A_ik Linv_pp^T for a 64-row tile (incl. the rhs row) ----------------
+// ---- panel rows below the diagonal block: L_ik = A_ik Linv_pp^T for a tile of 16 * RPT rows (incl. the rhs row) ------
+// RPT = 4 (64-row tiles) for the bulk of a panel; RPT = 1 (16-row tiles, eight CTAs for 128 rows) for the rows of the
+// NEXT diagonal tile, which sit on the factorisation's critical chain: there the latency of one CTA is what counts.
+template <int RPT>
 __global__ void __launch_bounds__(256) chol_trsm128_kernel(double* __restrict__ S, int n, int ld, int n_rows, int k0, int nb,
-                                                           const double* __restrict__ Linv) {
+                                                           const double* __restrict__ Linv, int row_off) {
+  constexpr int NBT = 16 * RPT;
   extern __shared__ double smem[];
-  double(*A)[LDP] = reinterpret_cast<double(*)[LDP]>(smem);               // [64][129]
-  double(*Li)[LDP] = reinterpret_cast<double(*)[LDP]>(smem + NB * LDP);   // [128][129]
+  double(*A)[LDP] = reinterpret_cast<double(*)[LDP]>(smem);                // [NBT][129]
+  double(*Li)[LDP] = reinterpret_cast<double(*)[LDP]>(smem + NBT * LDP);   // [128][129]
   const int tid = threadIdx.x;
-  const int r0 = k0 + nb + NB * blockIdx.x;
-  const int nr = min(NB, n_rows - r0);
-  for (int idx = tid; idx < NB * PB; idx += 256) {
+  const int r0 = k0 + nb + row_off + NBT * blockIdx.x;
+  const int nr = min(NBT, n_rows - r0);
+  for (int idx = tid; idx < NBT * PB; idx += 256) {
     const int r = idx / PB, c = idx - r * PB;
     A[r][c] = (r < nr && c < nb) ? S[(size_t)(r0 + r) * ld + k0 + c] : 0.0;
   }
   for (int idx = tid; idx < PB * PB; idx += 256) Li[idx / PB][idx % PB] = Linv[idx];
   __syncthreads();
-  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, 4 rows x 8 columns each (strided by 16)
-  double acc[4][8];
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, RPT rows x 8 columns each (strided by 16)
+  double acc[RPT][8];
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < RPT; ++a)
 #pragma unroll
     for (int b = 0; b < 8; ++b) acc[a][b] = 0.0;
   const int mend = min(nb, tx + 113);  // Linv[c][m] = 0 for m > c; the thread's largest column is tx + 112
   for (int m = 0; m < mend; ++m) {
-    double av[4], bv[8];
+    double av[RPT], bv[8];
 #pragma unroll
-    for (int a = 0; a < 4; ++a) av[a] = A[ty + 16 * a][m];
+    for (int a = 0; a < RPT; ++a) av[a] = A[ty + 16 * a][m];
 #pragma unroll
     for (int b = 0; b < 8; ++b) bv[b] = Li[tx + 16 * b][m];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < RPT; ++a)
 #pragma unroll
       for (int b = 0; b < 8; ++b) acc[a][b] += av[a] * bv[b];
   }
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < RPT; ++a)
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
       const int r = ty + 16 * a, c = tx + 16 * b;
       if (r < nr && c < nb) S[(size_t)(r0 + r) * ld + k0 + c] = acc[a][b];
+    }
+}
+
+// ---- update of the NEXT diagonal tile alone: A_tt -= L_tk L_tk^T (rows / columns [t0, t0 + 128)) in 32 x 32 pieces,
+// one CTA per piece of the lower triangle (grid 4 x 4, ten CTAs work).  On the critical chain: ten small CTAs finish in
+// a few microseconds where the 128 x 128 DMMA tile of chol_syrk128_kernel takes ~40 in one.
+__global__ void __launch_bounds__(256) chol_syrk_next_diag_kernel(double* __restrict__ S, int n, int ld, int n_rows, int k0, int nb,
+                                                                  int t0) {
+  if (blockIdx.x > blockIdx.y) return;
+  extern __shared__ double smem[];
+  double(*As)[LDP] = reinterpret_cast<double(*)[LDP]>(smem);             // [32][129]
+  double(*Bs)[LDP] = reinterpret_cast<double(*)[LDP]>(smem + 32 * LDP);  // [32][129]
+  const int tid = threadIdx.x;
+  const int i0 = t0 + 32 * blockIdx.y, j0 = t0 + 32 * blockIdx.x;
+  for (int idx = tid; idx < 32 * PB; idx += 256) {
+    const int r = idx / PB, c = idx - r * PB;
+    As[r][c] = (i0 + r < n_rows && c < nb) ? S[(size_t)(i0 + r) * ld + k0 + c] : 0.0;
+    Bs[r][c] = (j0 + r < n_rows && c < nb) ? S[(size_t)(j0 + r) * ld + k0 + c] : 0.0;
+  }
+  __syncthreads();
+  const int tx = tid & 15, ty = tid >> 4;
+  double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+  for (int m = 0; m < nb; ++m) {
+    const double a0 = As[ty][m], a1 = As[ty + 16][m], b0 = Bs[tx][m], b1 = Bs[tx + 16][m];
+    acc[0][0] += a0 * b0; acc[0][1] += a0 * b1; acc[1][0] += a1 * b0; acc[1][1] += a1 * b1;
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int r = i0 + ty + 16 * a, c = j0 + tx + 16 * b;
+      if (r < n_rows && c < n && c <= r && r < t0 + PB && c < t0 + PB) S[(size_t)r * ld + c] -= acc[a][b];
     }
 }
 
@@ -297,14 +333,14 @@ constexpr int TB = 128, KC = 32, LDK = KC + 4;
 struct SyrkSmem { double As[2][TB][LDK], Bs[2][TB][LDK]; };
 
 __global__ void __launch_bounds__(256) chol_syrk128_kernel(double* __restrict__ S, int n, int ld, int n_rows, int k0, int nb,
-                                                           int t0 /* first trailing row */, int first_column) {
+                                                           int t0 /* first trailing row */, int first_column, int bi0) {
   extern __shared__ double smem[];
   SyrkSmem& M = *reinterpret_cast<SyrkSmem*>(smem);
   // first_column: the tiles of the first tile column (they hold the next panel: updated first, so that the next panel's
   // factorisation can start while the rest of the update runs); else the rest of the lower triangle: linear tile id ->
   // (bi >= bj >= 1)
   int bi, bj;
-  if (first_column) { bi = blockIdx.x; bj = 0; }
+  if (first_column) { bi = blockIdx.x + bi0; bj = 0; }
   else {
     const int t = blockIdx.x;
     bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
@@ -441,16 +477,24 @@ int CholeskySolve(Problem* p) {
   if (n == 0) return SBA_OK;
   if (n <= kCholSmallMax) return CholeskySolveSmall(p);
   static bool attr_set[64] = {};
-  const int dyn_diag = (int)sizeof(DiagSmem), dyn_trsm = (NB + PB) * LDP * (int)sizeof(double), dyn_syrk = (int)sizeof(SyrkSmem);
+  const int dyn_diag = (int)sizeof(DiagSmem), dyn_trsm = (NB + PB) * LDP * (int)sizeof(double), dyn_trsm1 = (16 + PB) * LDP * (int)sizeof(double), dyn_syrk = (int)sizeof(SyrkSmem), dyn_next = 64 * LDP * (int)sizeof(double);
   if (!attr_set[p->device & 63]) {
     SBA_CUDA(cudaFuncSetAttribute(chol_diag128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_diag));
-    SBA_CUDA(cudaFuncSetAttribute(chol_trsm128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_trsm));
+    SBA_CUDA(cudaFuncSetAttribute(chol_trsm128_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_trsm));
+    SBA_CUDA(cudaFuncSetAttribute(chol_trsm128_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_trsm1));
+    SBA_CUDA(cudaFuncSetAttribute(chol_syrk_next_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_next));
     SBA_CUDA(cudaFuncSetAttribute(chol_syrk128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_syrk));
     attr_set[p->device & 63] = true;
   }
   cudaStream_t st = p->stream;
   if (!p->stream2) {  // (first factorisation of the handle: plain launches, never inside a capture)
-    SBA_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
+    // The chain kernels are a handful of CTAs that must not queue behind the hundreds of pending CTAs of a trailing
+    // update (a syrk CTA owns a whole SM: 254 registers x 256 threads): the chain stream gets the highest priority, the
+    // panel stream the next, the main stream keeps the default (lowest).
+    int prio_lo = 0, prio_hi = 0;
+    SBA_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    SBA_CUDA(cudaStreamCreateWithPriority(&p->stream2, cudaStreamNonBlocking, prio_hi));
+    SBA_CUDA(cudaStreamCreateWithPriority(&p->stream3, cudaStreamNonBlocking, std::min(prio_lo, prio_hi + 1)));
     for (auto& e : p->ev_chol) SBA_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   double* S = p->d_S.p;
@@ -463,35 +507,70 @@ int CholeskySolve(Problem* p) {
   static const bool want_trace = getenv("SBA_CHOL_TRACE") != nullptr;
   DevBuf<long long> trace;
   if (want_trace) { SBA_CUDA(trace.Alloc(32)); SBA_CUDA(trace.Zero(st)); }
-  // Two streams.  The panel chain (diagonal block, rows below) is latency-bound and serial; the trailing update is the
-  // bulk of the flops.  The update of panel k is split: the first tile column (= panel k + 1) goes first, then the
-  // side stream factors panel k + 1 while the main stream updates the rest.  The same dependencies are captured when
-  // the LM iteration is recorded as a CUDA graph.
-  cudaStream_t sb = p->stream2;
-  cudaEvent_t evA = p->ev_chol[0], evB = p->ev_chol[1];
-  SBA_CUDA(cudaEventRecord(evA, st));
-  SBA_CUDA(cudaStreamWaitEvent(sb, evA, 0));
+  // Three streams.  What is serial in a right-looking factorisation is the chain
+  //   diag(k) -> L of the NEXT diagonal tile's rows -> update of the next diagonal tile -> diag(k + 1),
+  // so only those small pieces (one CTA, two CTAs, one CTA) ride on the chain stream sD; the rest of panel k's rows and
+  // the first tile column of its update go to sT, the bulk of the update (tiles bi >= bj >= 1) to the main stream.  Per
+  // panel the chain is diag + two small kernels instead of diag + whole panel solve + first tile column (round 2's first
+  // version: 199 us per panel on average at n = 4000, profiles/r02_launches_c3_chol.csv; this schedule: 154 us, of which
+  // the chain alone -- measured with the other kernels left out -- is ~140: the diagonal factor 82-95 us, the two chain
+  // kernels and three dependent-launch gaps the rest).
+  // Who writes what, per panel k with t0 = k0 + nb (tile coordinates relative to t0, 128 rows each):
+  //   D2   [sD] rows [t0, t0 + 128) of column k            needs diag(k), first(k-1)
+  //   D3   [sD] tile (0, 0)                                needs D2, rest(k-1)            -> diag(k + 1)
+  //   trsm [sT] rows >= t0 + 128 of column k               needs diag(k), first(k-1)
+  //   first[sT] tiles (bi >= 1, 0)                         needs trsm, D2, rest(k-1)
+  //   rest [st] tiles (bi >= bj >= 1)                      needs trsm, rest(k-1)
+  // The same dependencies are captured when the LM iteration is recorded as a CUDA graph.
+  cudaStream_t sD = p->stream2, sT = p->stream3;
+  cudaEvent_t eFork = p->ev_chol[0], eDiag = p->ev_chol[1], eD2 = p->ev_chol[2], eTrsm = p->ev_chol[3], eFirst = p->ev_chol[4],
+              eRest = p->ev_chol[5], eJoinD = p->ev_chol[6], eJoinT = p->ev_chol[7];
+  SBA_CUDA(cudaEventRecord(eFork, st));
+  SBA_CUDA(cudaStreamWaitEvent(sD, eFork, 0));
+  SBA_CUDA(cudaStreamWaitEvent(sT, eFork, 0));
+  bool have_first = false, have_rest = false;
   for (int kb = 0; kb < nblk; ++kb) {
     const int k0 = kb * PB, nb = std::min(PB, n - k0);
     double* Linv = p->d_Linv.p + (size_t)kb * PB * PB;
-    chol_diag128_kernel<<<1, 256, dyn_diag, sb>>>(S, n, ld, k0, Linv, p->d_scalars.p, kb == 1 ? trace.p : nullptr);
-    const int rem_rows = n_rows - (k0 + nb);  // >= 1: the rhs row
-    chol_trsm128_kernel<<<DivUp(rem_rows, NB), 256, dyn_trsm, sb>>>(S, n, ld, n_rows, k0, nb, Linv);
+    const int rem_rows = n_rows - (k0 + nb);      // >= 1: the rhs row
+    const int d2_rows = std::min(rem_rows, TB);   // rows of the next diagonal tile: on the chain, in 16-row tiles
+    const int row_tiles = DivUp(rem_rows - d2_rows, NB);  // 64-row tiles of the rest of the panel
+    const bool trailing = k0 + nb < n;
+    const int m_tiles = DivUp(rem_rows, TB);      // tiles cover rows [k0+nb, n_rows); columns [k0+nb, n)
+    chol_diag128_kernel<<<1, 256, dyn_diag, sD>>>(S, n, ld, k0, Linv, p->d_scalars.p, kb == 1 ? trace.p : nullptr);
+    SBA_CUDA(cudaEventRecord(eDiag, sD));
+    if (have_first) SBA_CUDA(cudaStreamWaitEvent(sD, eFirst, 0));
+    chol_trsm128_kernel<1><<<DivUp(d2_rows, 16), 256, dyn_trsm1, sD>>>(S, n, ld, n_rows, k0, nb, Linv, 0);
+    SBA_CUDA(cudaEventRecord(eD2, sD));
     p->launches += 2;
-    SBA_CUDA(cudaEventRecord(evB, sb));
-    SBA_CUDA(cudaStreamWaitEvent(st, evB, 0));
-    if (k0 + nb < n) {
-      const int m_tiles = DivUp(rem_rows, TB);  // tiles cover rows [k0+nb, n_rows); columns [k0+nb, n)
-      chol_syrk128_kernel<<<m_tiles, 256, dyn_syrk, st>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 1);
+    SBA_CUDA(cudaStreamWaitEvent(sT, eDiag, 0));
+    if (row_tiles > 0) {
+      chol_trsm128_kernel<4><<<row_tiles, 256, dyn_trsm, sT>>>(S, n, ld, n_rows, k0, nb, Linv, d2_rows);
       p->launches++;
-      SBA_CUDA(cudaEventRecord(evA, st));
-      SBA_CUDA(cudaStreamWaitEvent(sb, evA, 0));
+    }
+    SBA_CUDA(cudaEventRecord(eTrsm, sT));
+    if (trailing) {
+      if (have_rest) SBA_CUDA(cudaStreamWaitEvent(sD, eRest, 0));
+      chol_syrk_next_diag_kernel<<<dim3(4, 4), 256, dyn_next, sD>>>(S, n, ld, n_rows, k0, nb, k0 + nb);
+      p->launches++;
       if (m_tiles > 1) {
-        chol_syrk128_kernel<<<m_tiles * (m_tiles - 1) / 2, 256, dyn_syrk, st>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 0);
-        p->launches++;
+        SBA_CUDA(cudaStreamWaitEvent(sT, eD2, 0));
+        if (have_rest) SBA_CUDA(cudaStreamWaitEvent(sT, eRest, 0));
+        chol_syrk128_kernel<<<m_tiles - 1, 256, dyn_syrk, sT>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 1, 1);
+        SBA_CUDA(cudaEventRecord(eFirst, sT));
+        have_first = true;
+        SBA_CUDA(cudaStreamWaitEvent(st, eTrsm, 0));
+        chol_syrk128_kernel<<<m_tiles * (m_tiles - 1) / 2, 256, dyn_syrk, st>>>(S, n, ld, n_rows, k0, nb, k0 + nb, 0, 0);
+        SBA_CUDA(cudaEventRecord(eRest, st));
+        have_rest = true;
+        p->launches += 2;
       }
     }
   }
+  SBA_CUDA(cudaEventRecord(eJoinD, sD));
+  SBA_CUDA(cudaEventRecord(eJoinT, sT));
+  SBA_CUDA(cudaStreamWaitEvent(st, eJoinD, 0));
+  SBA_CUDA(cudaStreamWaitEvent(st, eJoinT, 0));
   // y = row n of the factor; back substitution into d_yc
   chol_fetch_y_kernel<<<DivUp(n, 256), 256, 0, st>>>(n, ld, S, p->d_tmp_c.p);
   p->launches++;

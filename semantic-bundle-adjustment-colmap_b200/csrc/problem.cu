@@ -359,6 +359,7 @@ Problem::~Problem() {
   DropGraphs();
   CommDestroy(this);
   if (stream2) { cudaStreamSynchronize(stream2); cudaStreamDestroy(stream2); }
+  if (stream3) { cudaStreamSynchronize(stream3); cudaStreamDestroy(stream3); }
   for (auto& e : ev_chol) if (e) cudaEventDestroy(e);
   if (stream && h_scalars) {
     std::lock_guard<std::mutex> lk(g_ctx_mu);

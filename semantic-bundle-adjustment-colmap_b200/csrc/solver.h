@@ -264,8 +264,8 @@ struct Problem {
   void DropGraphs();
 
   cudaStream_t stream = nullptr;
-  cudaStream_t stream2 = nullptr;           // side stream of the blocked Cholesky's panel chain (cholesky.cu), forked from `stream`
-  cudaEvent_t ev_chol[2] = {};
+  cudaStream_t stream2 = nullptr, stream3 = nullptr;  // side streams of the blocked Cholesky (cholesky.cu), forked from `stream`
+  cudaEvent_t ev_chol[8] = {};
   int device = 0;
   int n_sm = 148;                           // multiprocessors of `device`
   int64_t launches = 0;
