@@ -13,6 +13,7 @@
 // 64 B ER record + 16*DC B F record out (tile-blocked 32 B units, common.cuh); poses / intrinsics /
 // points are gathered through L2 (n_img*64 B + n_cam*96 B + n_pt*24 B per evaluation).
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 
@@ -107,8 +108,9 @@ __device__ __forceinline__ void PickParam(const double (&Jk)[24], int amb, doubl
 #define SBA_EVAL_MINB 4
 #endif
 // three-row instantiations: the three small models fit 128 registers without spills (4 CTAs / SM); the others keep 3
+constexpr int EvalResident(int model, int nr) { return nr == 3 ? (model <= 2 ? 4 : 3) : SBA_EVAL_MINB; }  // CTAs per SM (launch bounds)
 template <int MODEL, int NR>
-__global__ void __launch_bounds__(kEvalThreads, NR == 3 ? (MODEL <= 2 ? 4 : 3) : SBA_EVAL_MINB)
+__global__ void __launch_bounds__(kEvalThreads, EvalResident(MODEL, NR))
 eval_kernel(ParamsView P, StructView S, LossView L, const double* __restrict__ scale_i,
             const double* __restrict__ scale_k, const unsigned long long* __restrict__ k_pack,
             const double* __restrict__ scale_p, D4* __restrict__ ER, D4* __restrict__ F, Row3View R3,
@@ -379,12 +381,17 @@ static void LaunchEvalT(Problem* p, const LossView& loss, bool use_scale, bool c
   p->Params(candidate), p->Struct(), loss, use_scale ? p->d_scale_i.p : p->d_mask_i.p,                                \
       use_scale ? p->d_scale_k.p : p->d_mask_k.p, p->d_k_pack.p, use_scale ? p->d_scale_p.p : nullptr, p->d_ER.p,      \
       p->d_F.p, p->Row3(), p->d_cost_partial.p, p->jq_out, p->d_tickets.p + 0, p->d_scalars.p
-  if (p->nr == 3) eval_kernel<MODEL, 3><<<blocks, kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
-  else eval_kernel<MODEL, 2><<<blocks, kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
+  // one resident wave: the kernel is grid-stride with uniform work per observation, and more CTAs than fit at once only
+  // add a tail (C4: 0.298 ms at 16 CTAs per SM, 0.288 ms at the 4 that are resident)
+  if (p->nr == 3) eval_kernel<MODEL, 3><<<std::min(blocks, p->n_sm * EvalResident(MODEL, 3)), kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
+  else eval_kernel<MODEL, 2><<<std::min(blocks, p->n_sm * EvalResident(MODEL, 2)), kEvalThreads, 0, p->stream>>>(SBA_EVAL_ARGS);
 #undef SBA_EVAL_ARGS
 }
 template <int MODEL>
 static void LaunchCostT(Problem* p, const LossView& loss, bool candidate, int blocks, double* d_out_cost) {
+  // (two rows, measured at C4: 0.095 ms at 8 CTAs per SM against 0.117 ms at 16; three rows want the parallelism for
+  // their texel loads: C5 0.735 ms at 16 against 0.797 ms at 8)
+  if (p->nr != 3) blocks = std::min(blocks, p->n_sm * 8);
   if (p->nr == 3)
     cost_kernel<MODEL, 3><<<blocks, kEvalThreads, 0, p->stream>>>(p->Params(candidate), p->Struct(), loss, p->Row3(),
                                                                   p->d_cost_partial.p, p->d_tickets.p + 1, d_out_cost);
