@@ -397,8 +397,12 @@ int sba_semantic_solve(const sba_semantic_problem* problem, const sba_solver_opt
  * :1126-1213 (QuaternionManifold on the cylinder quaternion, lower bound 0 on the radius), :670-693 pose manifolds.
  * One residual 1 - IoU per (image, cylinder), central numeric differentiation, dense LM over poses and cylinders.
  * The radius bound is enforced by clamping in Plus.  Only the TRIVIAL loss is legal (:699-706).
- * The optional landmark blocks (include_landmark_error, default false, :729-794) are NOT part of this entry point.
- * Poses and cylinders are updated in place. */
+ * Optional landmark blocks (include_landmark_error, :729-794, 1361-1469): num_landmarks > 0 adds one ordinary
+ * reprojection block per listed observation (BundleAdjustment[ConstantPose]CostFunction<SimplePinholeCameraModel>,
+ * intrinsics constant) under ScaledLoss(nullptr, landmark_error_weight / total number of 2-D features) (:758-765), and
+ * the 3-D points become parameter blocks (constant where point_constant says so, :1448-1469).  The step is then the
+ * dense normal-equations solve over poses, cylinders AND points (small problems: 2 * num_landmarks * tangent
+ * dimension <= 2^28).  Poses, cylinders and points are updated in place. */
 typedef struct sba_cylinder_problem {
   int32_t num_images;
   int32_t height, width;
@@ -413,6 +417,15 @@ typedef struct sba_cylinder_problem {
   double* cylinder_params;       /* [num_cylinders*9] in / out; kind 0: q(4) t(3) r h; kind 1: t1(3) t2(3) r, two unused */
   int32_t refine_geometry;       /* options_.refine_geometry (geometric_semantic_bundle_adjustment.h:78) */
   double relative_step_size;     /* 1e-3 (:111) */
+  /* landmark blocks (all zero / NULL: none) */
+  int32_t num_points;
+  double* points;                /* [num_points*3] in / out */
+  const uint8_t* point_constant; /* [num_points] nullable */
+  int64_t num_landmarks;
+  const int32_t* landmark_image; /* [num_landmarks] */
+  const int32_t* landmark_point; /* [num_landmarks] */
+  const double* landmark_xy;     /* [num_landmarks*2] */
+  double landmark_weight;        /* options_.landmark_error_weight / total_num_2d_features (:758) */
 } sba_cylinder_problem;
 
 int sba_cylinder_solve(const sba_cylinder_problem* problem, const sba_solver_options* opts, sba_iteration_callback cb,

@@ -63,7 +63,7 @@ void CholSolve(const std::vector<double>& L, int n, std::vector<double>& b) {
 }
 
 // One residual block after manifold projection: r, columns and their Jacobian entries (before the loss corrector)
-struct Row { double r; int n; int col[16]; double j[16]; };
+struct Row { double r; int n; int col[16]; double j[16]; double w = 0.0; };  // w > 0: this row's own ScaledLoss weight
 
 struct DenseProblem {
   int n = 0;  // tangent dimension
@@ -87,7 +87,7 @@ void Linearize(const DenseProblem& P, std::vector<double>* H, std::vector<double
     const double s = b.r * b.r;
     double rho[3];
     LossEvalD(P.loss_type, P.loss_scale, s, rho);
-    for (double& v : rho) v *= P.loss_weight;  // ScaledLoss
+    for (double& v : rho) v *= (b.w > 0.0 ? b.w : P.loss_weight);  // ScaledLoss
     c += 0.5 * rho[0];
     const double sq = std::sqrt(rho[1]);
     double jscale = sq, rscale = sq;
@@ -395,7 +395,17 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
   std::vector<double> cyl(d->cylinder_params, d->cylinder_params + 9 * (size_t)n_cyl), cylc;
   PoseVars V;
   DenseProblem P;
-  int off = V.Build(n_img, d->image_pose_constant, d->image_tvec_constant_mask, 0, summary, n_cyl > 0);
+  // optional landmark blocks (:729-794, 1361-1469): ordinary SIMPLE_PINHOLE reprojection blocks, constant intrinsics,
+  // ScaledLoss(nullptr, landmark_weight); the points join the parameter blocks
+  const int64_t n_lm = d->num_landmarks;
+  const int n_pts = n_lm > 0 ? d->num_points : 0;
+  std::vector<uint8_t> has_lm(n_img, 0), pc2(n_img, 0);
+  for (int64_t k = 0; k < n_lm; ++k) has_lm[d->landmark_image[k]] = 1;
+  for (int i = 0; i < n_img; ++i) pc2[i] = (d->image_pose_constant && d->image_pose_constant[i]) || !(n_cyl > 0 || has_lm[i]);
+  int off = V.Build(n_img, pc2.data(), d->image_tvec_constant_mask, 0, summary, true);
+  for (int i = 0; i < n_img; ++i) if (has_lm[i]) NormalizeQ(&q[4 * i]);  // image.NormalizeQvec(), :1371
+  std::vector<double> X, Xc;
+  if (n_lm > 0) X.assign(d->points, d->points + 3 * (size_t)n_pts);
   struct Blk { int im, cy; };
   std::vector<Blk> blocks;
   for (int i = 0; i < n_img; ++i) {
@@ -413,11 +423,22 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
       summary->num_effective_parameters_reduced += cdim;
     }
   }
+  std::vector<int> xcol(std::max(1, n_pts), -1);
+  {
+    std::vector<uint8_t> used(std::max(1, n_pts), 0);
+    for (int64_t k = 0; k < n_lm; ++k) used[d->landmark_point[k]] = 1;
+    for (int p = 0; p < n_pts; ++p) {
+      if (!used[p] || (d->point_constant && d->point_constant[p])) continue;
+      xcol[p] = off; off += 3;
+      summary->num_parameter_blocks_reduced += 1; summary->num_parameters_reduced += 3; summary->num_effective_parameters_reduced += 3;
+    }
+  }
   P.n = off;
   P.loss_weight = 1.0 / n_img;  // ScaledLoss(nullptr, 1 / N_images)
-  summary->num_residual_blocks = summary->num_residuals = summary->num_residuals_reduced = (int)blocks.size();
+  summary->num_residual_blocks = (int)blocks.size() + (int)n_lm;
+  summary->num_residuals = summary->num_residuals_reduced = (int)blocks.size() + 2 * (int)n_lm;
   summary->linear_solver_type_used = n_img <= 50 ? SBA_DENSE_SCHUR : (n_img <= 1000 ? SBA_SPARSE_SCHUR : SBA_ITERATIVE_SCHUR);
-  if (blocks.empty()) return SBA_ERR_EMPTY_PROBLEM;
+  if (blocks.empty() && n_lm == 0) return SBA_ERR_EMPTY_PROBLEM;
   std::vector<int> pos(n_img, 0);
   for (int i = 0; i < n_img; ++i) for (size_t j = 0; j < HW; ++j) pos[i] += d->masks[i * HW + j] != 0;
   const int nc = kind == 0 ? 16 : 14;
@@ -432,8 +453,29 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
     for (int j = 0; j < 3; ++j) x[4 + j] = T[3 * b.im + j];
     for (int j = 0; j < 9; ++j) x[7 + j] = C[9 * b.cy + j];
   };
+  const double ident_q[4] = {1.0, 0.0, 0.0, 0.0}, ident_t[3] = {0.0, 0.0, 0.0};
+  auto landmark = [&](const std::vector<double>& Q, const std::vector<double>& T, const std::vector<double>& PX, int64_t k, double* r, double* J) {
+    const int i = d->landmark_image[k], p = d->landmark_point[k];
+    double prm[SBA_MAX_CAMERA_PARAMS] = {0};
+    for (int a = 0; a < 3; ++a) prm[a] = d->camera_params[3 * (size_t)i + a];
+    // the ordinary functor = the rig functor on a constant identity rig pose (exactly: q (x) 1 = q, R(q) 0 + t = t)
+    EvalRigObservation(SBA_SIMPLE_PINHOLE, ident_q, ident_t, &Q[4 * (size_t)i], &T[3 * (size_t)i], &PX[3 * (size_t)p], prm,
+                       d->landmark_xy + 2 * k, r, J);
+  };
   P.rows = [&](std::vector<Row>* rows) {
-    rows->assign(blocks.size(), Row());
+    rows->assign(blocks.size() + 2 * (size_t)n_lm, Row());
+    for (int64_t k = 0; k < n_lm; ++k) {
+      double r[2], J[2 * 29];
+      landmark(q, t, X, k, r, J);
+      const int i = d->landmark_image[k], p = d->landmark_point[k];
+      for (int rr = 0; rr < 2; ++rr) {
+        Row& row = (*rows)[blocks.size() + 2 * (size_t)k + rr];
+        row.n = 0; row.r = r[rr]; row.w = d->landmark_weight;
+        const double* A = J + 29 * rr;
+        V.Append(i, &q[4 * (size_t)i], A + 7, A + 11, &row);
+        if (xcol[p] >= 0) for (int a = 0; a < 3; ++a) { row.col[row.n] = xcol[p] + a; row.j[row.n++] = A[14 + a]; }
+      }
+    }
 #pragma omp parallel for num_threads(threads) schedule(dynamic, 1)
     for (int64_t k = 0; k < (int64_t)blocks.size(); ++k) {
       std::vector<uint8_t> scratch;
@@ -466,7 +508,12 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
     }
   };
   P.candidate = [&](const std::vector<double>& delta, double* step2, double* x2) {
-    qc = q; tc = t; cylc = cyl;
+    qc = q; tc = t; cylc = cyl; Xc = X;
+    for (int p = 0; p < n_pts; ++p) if (xcol[p] >= 0) for (int a = 0; a < 3; ++a) {
+      const double v = X[3 * (size_t)p + a];
+      Xc[3 * (size_t)p + a] = v + delta[xcol[p] + a];
+      const double e = Xc[3 * (size_t)p + a] - v; *step2 += e * e; *x2 += v * v;
+    }
     for (int i = 0; i < n_img; ++i) V.Plus(i, &q[4 * i], &t[3 * i], delta, &qc[4 * i], &tc[3 * i], step2, x2);
     if (cdim)
       for (int c = 0; c < n_cyl; ++c) {
@@ -492,9 +539,14 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
       const double r = residual(b, x, &scratch);
       c += 0.5 * P.loss_weight * r * r;
     }
+    for (int64_t k = 0; k < n_lm; ++k) {
+      double r[2];
+      landmark(qc, tc, Xc, k, r, nullptr);
+      c += 0.5 * d->landmark_weight * (r[0] * r[0] + r[1] * r[1]);
+    }
     return c;
   };
-  P.accept = [&]() { q.swap(qc); t.swap(tc); cyl.swap(cylc); };
+  P.accept = [&]() { q.swap(qc); t.swap(tc); cyl.swap(cylc); X.swap(Xc); };
   std::vector<sba_iteration_summary> trace;
   const int rc = SolveDense(P, *o, summary, &trace);
   if (trace_out && n_trace) {
@@ -505,6 +557,7 @@ int oracle_cylinder_solve(const sba_cylinder_problem* d, const sba_solver_option
   std::memcpy(d->image_qvec, q.data(), q.size() * sizeof(double));
   std::memcpy(d->image_tvec, t.data(), t.size() * sizeof(double));
   if (n_cyl > 0) std::memcpy(d->cylinder_params, cyl.data(), cyl.size() * sizeof(double));
+  if (n_lm > 0) std::memcpy(d->points, X.data(), X.size() * sizeof(double));
   return rc;
 }
 

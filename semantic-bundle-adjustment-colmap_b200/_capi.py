@@ -127,6 +127,9 @@ class CylinderProblem(C.Structure):
         ("image_pose_constant", _u8p), ("image_tvec_constant_mask", _u8p),
         ("num_cylinders", C.c_int32), ("cylinder_kind", C.c_int32), ("cylinder_params", _dp),
         ("refine_geometry", C.c_int32), ("relative_step_size", C.c_double),
+        ("num_points", C.c_int32), ("points", _dp), ("point_constant", _u8p),
+        ("num_landmarks", C.c_int64), ("landmark_image", _ip), ("landmark_point", _ip), ("landmark_xy", _dp),
+        ("landmark_weight", C.c_double),
     ]
 
 

@@ -19,6 +19,7 @@
 #include <climits>
 
 #include "dense_lm.h"
+#include "rig_lin.cuh"
 #include "semantic_device.cuh"
 
 namespace sba {
@@ -229,6 +230,29 @@ __global__ void cyl_plus_kernel(CylSolveView V, const int* __restrict__ ent_off,
   out[0] = step2; out[1] = x2;
 }
 
+// landmark blocks: X+ = X + delta on the variable points (constant ones copied); adds their part of |x+ - x|^2, |x|^2 to out[0..1]
+__global__ void __launch_bounds__(256) lm_points_plus_kernel(int n_pt, const double* __restrict__ X, const int* __restrict__ xcol,
+                                                             const double* __restrict__ delta, double* __restrict__ X2,
+                                                             double* __restrict__ out) {
+  __shared__ double sa[256], sb[256];
+  double s2 = 0.0, x2 = 0.0;
+  for (int p = threadIdx.x; p < n_pt; p += 256)
+    for (int j = 0; j < 3; ++j) {
+      const double x = X[3 * (size_t)p + j];
+      const double v = xcol[p] >= 0 ? x + delta[xcol[p] + j] : x;
+      X2[3 * (size_t)p + j] = v;
+      if (xcol[p] >= 0) { s2 += (v - x) * (v - x); x2 += x * x; }
+    }
+  sa[threadIdx.x] = s2; sb[threadIdx.x] = x2;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) { sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out[0] += sa[0]; out[1] += sb[0]; }
+}
+__global__ void add_scalar_kernel(double* __restrict__ dst, const double* __restrict__ src) { *dst += *src; }
+
 __global__ void cyl_sum_kernel(int n, const double* __restrict__ v, double* __restrict__ out) {
   if (threadIdx.x == 0 && blockIdx.x == 0) { double s = 0.0; for (int i = 0; i < n; ++i) s += v[i]; *out = s; }
 }
@@ -247,6 +271,16 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
     SetError(SBA_ERR_INVALID_ARGUMENT, "bad cylinder problem");
     return SBA_ERR_INVALID_ARGUMENT;
   }
+  const int64_t n_lm = d->num_landmarks;
+  const int n_pts = d->num_points;
+  if (n_lm < 0 || n_pts < 0 || (n_lm > 0 && (!d->points || !d->landmark_image || !d->landmark_point || !d->landmark_xy || n_pts == 0 ||
+                                              !(d->landmark_weight > 0.0)))) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "bad landmark blocks"); return SBA_ERR_INVALID_ARGUMENT;
+  }
+  for (int64_t k = 0; k < n_lm; ++k)
+    if (d->landmark_image[k] < 0 || d->landmark_image[k] >= d->num_images || d->landmark_point[k] < 0 || d->landmark_point[k] >= n_pts) {
+      SetError(SBA_ERR_INVALID_ARGUMENT, "landmark index out of range"); return SBA_ERR_INVALID_ARGUMENT;
+    }
   sba_solver_options o;
   if (opts) o = *opts; else sba_default_solver_options(&o);
   if (o.loss_function_type != SBA_LOSS_TRIVIAL) {  // geometric_semantic_bundle_adjustment.cc:699-706
@@ -273,10 +307,11 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
   }
   DenseGroups G;
   int off = 0;
-  std::vector<uint8_t> img_in_problem(n_img, 0);
+  std::vector<uint8_t> img_in_problem(n_img, 0), img_has_lm(n_img, 0);
+  for (int64_t k = 0; k < n_lm; ++k) img_has_lm[d->landmark_image[k]] = 1;
   for (int i = 0; i < n_img; ++i) {
     int dim = 0;
-    if (!pc[i] && n_cyl > 0) { dim = 3; for (int a = 0; a < 3; ++a) dim += !((tm[i] >> a) & 1); }
+    if (!pc[i] && (n_cyl > 0 || img_has_lm[i])) { dim = 3; for (int a = 0; a < 3; ++a) dim += !((tm[i] >> a) & 1); }
     G.ent_off.push_back(off); G.ent_dim.push_back(dim);
     off += dim;
     if (dim) {
@@ -301,7 +336,21 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
       summary->num_effective_parameters_reduced += dim;
     }
   }
+  // (tangent columns of poses and cylinders end here; the variable points of the landmark blocks follow)
+  std::vector<uint8_t> pt_used(std::max(1, n_pts), 0);
+  for (int64_t k = 0; k < n_lm; ++k) pt_used[d->landmark_point[k]] = 1;
+  std::vector<int> xcol(std::max(1, n_pts), -1);
+  for (int p = 0; p < n_pts && n_lm > 0; ++p) {
+    if (!pt_used[p] || (d->point_constant && d->point_constant[p])) continue;
+    xcol[p] = off; off += 3;
+    summary->num_parameter_blocks_reduced += 1; summary->num_parameters_reduced += 3; summary->num_effective_parameters_reduced += 3;
+  }
   G.n = off;
+  if (n_lm > 0 && 2 * n_lm * (int64_t)std::max(1, off) > kRigMaxJacDoubles) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sba_cylinder_solve: the landmark blocks hold their Jacobian dense; 2 * landmarks * tangent dimension exceeds 2^28");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  for (int i = 0; i < n_img; ++i) if (img_has_lm[i]) img_in_problem[i] = 1;  // image.NormalizeQvec(), :1371
   // a pose only owns columns when one of its blocks is in the problem (always, when there are cylinders)
   std::vector<double> q(d->image_qvec, d->image_qvec + 4 * (size_t)n_img), t(d->image_tvec, d->image_tvec + 3 * (size_t)n_img);
   for (int i = 0; i < n_img; ++i) {
@@ -310,13 +359,16 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
     if (nrm == 0.0) { q[4 * i] = 1.0; q[4 * i + 1] = q[4 * i + 2] = q[4 * i + 3] = 0.0; }
     else for (int a = 0; a < 4; ++a) q[4 * i + a] /= nrm;
   }
+  // one more pose slot behind the images: the constant identity the landmark blocks use as their "rig pose" (rig_lin.cuh)
+  q.insert(q.end(), {1.0, 0.0, 0.0, 0.0}); t.insert(t.end(), {0.0, 0.0, 0.0});
   std::vector<double> cyl((size_t)std::max(1, n_cyl) * 9, 0.0);
   for (int c = 0; c < n_cyl; ++c) for (int a = 0; a < 9; ++a) cyl[9 * (size_t)c + a] = d->cylinder_params[9 * (size_t)c + a];
   int rc = G.Upload(st);
   if (rc) return rc;
-  summary->num_residual_blocks = summary->num_residuals = summary->num_residuals_reduced = G.n_groups;
+  summary->num_residual_blocks = G.n_groups + (int)n_lm;
+  summary->num_residuals = summary->num_residuals_reduced = G.n_groups + 2 * (int)n_lm;
   summary->linear_solver_type_used = n_img <= 50 ? SBA_DENSE_SCHUR : (n_img <= 1000 ? SBA_SPARSE_SCHUR : SBA_ITERATIVE_SCHUR);
-  if (G.n_groups == 0) {
+  if (G.n_groups == 0 && n_lm == 0) {
     SetError(SBA_ERR_EMPTY_PROBLEM, "no residual blocks");
     return SBA_ERR_EMPTY_PROBLEM;
   }
@@ -327,7 +379,7 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
   DevBuf<uint8_t> dmask, dpc, dtm;
   DevBuf<int> dpos, dgi, dgc;
   SBA_CUDA(dq.Upload(q, st)); SBA_CUDA(dt.Upload(t, st)); SBA_CUDA(dcyl.Upload(cyl, st));
-  SBA_CUDA(dq2.Alloc(q.size())); SBA_CUDA(dt2.Alloc(t.size())); SBA_CUDA(dcyl2.Alloc(cyl.size()));
+  SBA_CUDA(dq2.Upload(q, st)); SBA_CUDA(dt2.Upload(t, st)); SBA_CUDA(dcyl2.Alloc(cyl.size()));  // (both pose buffers hold the identity slot)
   SBA_CUDA(dcam.Alloc((size_t)n_img * 3));
   SBA_CUDA(cudaMemcpyAsync(dcam.p, d->camera_params, (size_t)n_img * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
   SBA_CUDA(dmask.Alloc(n_img * HW));
@@ -339,6 +391,31 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
   SBA_CUDA(gcost.Alloc(G.n_groups)); SBA_CUDA(scal.Alloc(4));
   cyl_mask_count_kernel<<<n_img, 256, 0, st>>>(dmask.p, HW, dpos.p);
   SBA_CUDA(cudaStreamSynchronize(st));  // the host vectors above are read by the asynchronous copies
+  // ---- landmark blocks: reprojection blocks (identity "rig" pose, image pose, point, constant SIMPLE_PINHOLE camera) ----
+  DevBuf<double> dX, dX2, dcam12, dlxy, dJ, drf, dlpart;
+  DevBuf<int> dmodel, dqcol, dtcol, dpcol, dxcol, dla, dlb, dlp;
+  const int64_t lm_rows = 2 * n_lm;
+  const int lm_blocks = (int)DivUp(std::max<int64_t>(1, n_lm), 128);
+  if (n_lm > 0) {
+    std::vector<double> hX(d->points, d->points + 3 * (size_t)n_pts), cam12(12 * (size_t)n_img, 0.0);
+    for (int i = 0; i < n_img; ++i) for (int a = 0; a < 3; ++a) cam12[12 * (size_t)i + a] = d->camera_params[3 * (size_t)i + a];
+    std::vector<int> model(n_img, SBA_SIMPLE_PINHOLE), qcol(n_img + 1, -1), tcol(3 * (size_t)(n_img + 1), -1), pcol(12 * (size_t)n_img, -1);
+    for (int i = 0; i < n_img; ++i) {
+      if (!G.ent_dim[i]) continue;
+      qcol[i] = G.ent_off[i];
+      int c = 3;
+      for (int a = 0; a < 3; ++a) if (!((tm[i] >> a) & 1)) tcol[3 * (size_t)i + a] = G.ent_off[i] + c++;
+    }
+    std::vector<int> la(n_lm, n_img), lb(d->landmark_image, d->landmark_image + n_lm), lp(d->landmark_point, d->landmark_point + n_lm);
+    std::vector<double> lxy(d->landmark_xy, d->landmark_xy + 2 * n_lm);
+    SBA_CUDA(dX.Upload(hX, st)); SBA_CUDA(dX2.Upload(hX, st)); SBA_CUDA(dcam12.Upload(cam12, st)); SBA_CUDA(dmodel.Upload(model, st));
+    SBA_CUDA(dqcol.Upload(qcol, st)); SBA_CUDA(dtcol.Upload(tcol, st)); SBA_CUDA(dpcol.Upload(pcol, st)); SBA_CUDA(dxcol.Upload(xcol, st));
+    SBA_CUDA(dla.Upload(la, st)); SBA_CUDA(dlb.Upload(lb, st)); SBA_CUDA(dlp.Upload(lp, st)); SBA_CUDA(dlxy.Upload(lxy, st));
+    SBA_CUDA(dJ.Alloc((size_t)lm_rows * std::max(1, G.n))); SBA_CUDA(dJ.Zero(st));
+    SBA_CUDA(drf.Alloc(lm_rows)); SBA_CUDA(dlpart.Alloc(lm_blocks));
+    SBA_CUDA(cudaStreamSynchronize(st));
+  }
+  const LossView lm_loss = {SBA_LOSS_TRIVIAL, 1.0, 1};  // ScaledLoss(nullptr, weight): the weight rides in the view
   CylSolveView V;
   V.n_img = n_img; V.n_cyl = n_cyl; V.H = H; V.W = W; V.kind = kind; V.refine_geometry = refine_geometry ? 1 : 0;
   V.q = dq.p; V.t = dt.p; V.cyl = dcyl.p; V.cam = dcam.p; V.masks = dmask.p; V.pos_count = dpos.p;
@@ -351,7 +428,18 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
     v.q = second ? dq2.p : dq.p; v.t = second ? dt2.p : dt.p; v.cyl = second ? dcyl2.p : dcyl.p;
     return v;
   };
+  auto lm_view = [&](bool candidate) {
+    const CylSolveView v = view(candidate);
+    const bool second = candidate == cand_is_2;
+    RigView R;
+    R.n_pose = n_img + 1; R.n_cam = n_img; R.n_pt = n_pts; R.n = G.n; R.n_obs = n_lm;
+    R.pq = v.q; R.pt = v.t; R.cam = dcam12.p; R.X = second ? dX2.p : dX.p; R.model = dmodel.p;
+    R.qcol = dqcol.p; R.tcol = dtcol.p; R.pcol = dpcol.p; R.xcol = dxcol.p;
+    R.b_a = dla.p; R.b_b = dlb.p; R.b_c = dlb.p; R.b_p = dlp.p; R.b_xy = dlxy.p; R.weight = d->landmark_weight;
+    return R;
+  };
   auto read_back = [&]() -> int {
+    if (n_lm > 0) SBA_CUDA(cudaMemcpyAsync(d->points, lm_view(false).X, 3 * (size_t)n_pts * sizeof(double), cudaMemcpyDeviceToHost, st));
     const CylSolveView v = view(false);
     SBA_CUDA(cudaMemcpyAsync(d->image_qvec, v.q, 4 * (size_t)n_img * sizeof(double), cudaMemcpyDeviceToHost, st));
     SBA_CUDA(cudaMemcpyAsync(d->image_tvec, v.t, 3 * (size_t)n_img * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -364,23 +452,47 @@ extern "C" int sba_cylinder_solve(const sba_cylinder_problem* d, const sba_solve
   if (o.update_state_every_iteration) F.before_callback = [&]() { read_back(); };
   F.linearize = [&]() -> int {
     const CylSolveView v = view(false);
-    cyl_eval_kernel<<<G.n_groups * n_eval, 256, 0, st>>>(v, n_eval, vals.p, deltas.p);
-    cyl_record_kernel<<<DivUp(G.n_groups, 128), 128, 0, st>>>(v, G.n_groups, n_eval, vals.p, deltas.p, G.d_rec.p, nullptr);
+    if (G.n_groups > 0) {
+      cyl_eval_kernel<<<G.n_groups * n_eval, 256, 0, st>>>(v, n_eval, vals.p, deltas.p);
+      cyl_record_kernel<<<DivUp(G.n_groups, 128), 128, 0, st>>>(v, G.n_groups, n_eval, vals.p, deltas.p, G.d_rec.p, nullptr);
+    }
     SBA_CUDA(cudaGetLastError());
     return SBA_OK;
   };
+  if (n_lm > 0)  // H, g, cost = the group records of the IoU blocks + J^T J, J^T r, cost of the landmark blocks
+    F.assemble = [&](double* d_H, double* d_g, double* d_cost) -> int {
+      SBA_CUDA(cudaMemsetAsync(d_H, 0, (size_t)G.n * G.n * sizeof(double), st));
+      const int rc2 = AssembleDense(G, d_H, d_g, d_cost, st, nullptr);
+      if (rc2) return rc2;
+      rig_lin_kernel<true><<<lm_blocks, 128, 0, st>>>(lm_view(false), lm_loss, dJ.p, drf.p, dlpart.p);
+      rig_sum_kernel<<<1, 256, 0, st>>>(dlpart.p, lm_blocks, 1, 1, scal.p + 3);
+      const int tiles = DivUp(G.n, 32);
+      rig_jtj_kernel<<<dim3(tiles, tiles), dim3(32, 32), 0, st>>>(G.n, lm_rows, dJ.p, d_H, 1);
+      rig_jtr_kernel<<<DivUp(G.n, 128), 128, 0, st>>>(G.n, lm_rows, dJ.p, drf.p, d_g, 1);
+      add_scalar_kernel<<<1, 1, 0, st>>>(d_cost, scal.p + 3);
+      SBA_CUDA(cudaGetLastError());
+      return SBA_OK;
+    };
   F.candidate = [&](const double* d_delta, double* cost, double* step2, double* x2) -> int {
     const CylSolveView cur = view(false), cand = view(true);
     cyl_plus_kernel<<<1, 32, 0, st>>>(cur, G.d_ent_off.p, d_delta, const_cast<double*>(cand.q), const_cast<double*>(cand.t),
                                       const_cast<double*>(cand.cyl), scal.p);
-    cyl_eval_kernel<<<G.n_groups, 256, 0, st>>>(cand, 1, vals.p, deltas.p);
-    cyl_record_kernel<<<DivUp(G.n_groups, 128), 128, 0, st>>>(cand, G.n_groups, 1, vals.p, deltas.p, nullptr, gcost.p);
+    if (G.n_groups > 0) {
+      cyl_eval_kernel<<<G.n_groups, 256, 0, st>>>(cand, 1, vals.p, deltas.p);
+      cyl_record_kernel<<<DivUp(G.n_groups, 128), 128, 0, st>>>(cand, G.n_groups, 1, vals.p, deltas.p, nullptr, gcost.p);
+    }
     cyl_sum_kernel<<<1, 32, 0, st>>>(G.n_groups, gcost.p, scal.p + 2);
+    if (n_lm > 0) {
+      const RigView rc_cur = lm_view(false), rc_cand = lm_view(true);
+      lm_points_plus_kernel<<<1, 256, 0, st>>>(n_pts, rc_cur.X, dxcol.p, d_delta, const_cast<double*>(rc_cand.X), scal.p);
+      rig_lin_kernel<false><<<lm_blocks, 128, 0, st>>>(rc_cand, lm_loss, nullptr, nullptr, dlpart.p);
+      rig_sum_kernel<<<1, 256, 0, st>>>(dlpart.p, lm_blocks, 1, 1, scal.p + 3);
+    }
     SBA_CUDA(cudaGetLastError());
-    double h[3];
-    SBA_CUDA(cudaMemcpyAsync(h, scal.p, 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    double h[4] = {0.0, 0.0, 0.0, 0.0};
+    SBA_CUDA(cudaMemcpyAsync(h, scal.p, (n_lm > 0 ? 4 : 3) * sizeof(double), cudaMemcpyDeviceToHost, st));
     SBA_CUDA(cudaStreamSynchronize(st));
-    *step2 = h[0]; *x2 = h[1]; *cost = h[2];
+    *step2 = h[0]; *x2 = h[1]; *cost = h[2] + h[3];
     return SBA_OK;
   };
   F.accept = [&]() { cand_is_2 = !cand_is_2; };

@@ -109,7 +109,8 @@ class CylinderProblem(_PoseProblem):
     """Geometric-semantic BA: one residual 1 - IoU per (image, cylinder); cylinder_kind 0 = (q, t, r, h), 1 = (t1, t2, r)."""
 
     def __init__(self, image_qvec, image_tvec, camera_params, masks, cylinder_params, cylinder_kind=0, refine_geometry=True,
-                 image_pose_constant=None, image_tvec_constant_mask=None, relative_step_size=1e-3):
+                 image_pose_constant=None, image_tvec_constant_mask=None, relative_step_size=1e-3, points=None,
+                 point_constant=None, landmark_image=None, landmark_point=None, landmark_xy=None, landmark_error_weight=1.0):
         n = self._poses(image_qvec, image_tvec, camera_params, image_pose_constant, image_tvec_constant_mask)
         self.masks = np.ascontiguousarray(masks, dtype=np.uint8)
         assert self.masks.shape[0] == n
@@ -117,6 +118,14 @@ class CylinderProblem(_PoseProblem):
         cp = capi.as_f64(cylinder_params).reshape(len(cylinder_params), -1)
         self.cylinder_params[:, :cp.shape[1]] = cp
         self.cylinder_kind, self.refine_geometry, self.relative_step_size = cylinder_kind, refine_geometry, relative_step_size
+        # optional landmark blocks (include_landmark_error): every listed 2-D feature of the config images
+        self.points = None if points is None else capi.as_f64(points).reshape(-1, 3).copy()
+        if self.points is not None:
+            self.point_constant = (np.zeros(len(self.points), np.uint8) if point_constant is None
+                                   else np.ascontiguousarray(point_constant, dtype=np.uint8))
+            self.landmark_image, self.landmark_point = capi.as_i32(landmark_image), capi.as_i32(landmark_point)
+            self.landmark_xy = capi.as_f64(landmark_xy).reshape(-1, 2)
+            self.landmark_weight = landmark_error_weight / max(1, len(self.landmark_image))  # (:758: weight / total_num_2d_features)
 
     def desc(self):
         p = capi.CylinderProblem()
@@ -128,6 +137,11 @@ class CylinderProblem(_PoseProblem):
         p.num_cylinders, p.cylinder_kind = len(self.cylinder_params), self.cylinder_kind
         p.cylinder_params = capi.ptr(self.cylinder_params, capi._dp)
         p.refine_geometry, p.relative_step_size = 1 if self.refine_geometry else 0, self.relative_step_size
+        if self.points is not None:
+            p.num_points, p.points, p.point_constant = len(self.points), capi.ptr(self.points, capi._dp), capi.ptr(self.point_constant, capi._u8p)
+            p.num_landmarks = len(self.landmark_image)
+            p.landmark_image, p.landmark_point = capi.ptr(self.landmark_image, capi._ip), capi.ptr(self.landmark_point, capi._ip)
+            p.landmark_xy, p.landmark_weight = capi.ptr(self.landmark_xy, capi._dp), self.landmark_weight
         return p
 
     def solve(self, options=None, callback=None):

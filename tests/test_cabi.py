@@ -33,8 +33,9 @@ def test_header_symbols_are_exported_and_typed(sba):
 
 def test_struct_sizes_match_header(sba):
     # sizeof computed by the C compiler for the header's structs == ctypes mirror
-    src = '#include "sba_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu",sizeof(sba_problem_desc),' \
-          'sizeof(sba_solver_options),sizeof(sba_iteration_summary),sizeof(sba_summary),sizeof(sba_semantic_desc),sizeof(sba_cylinder_desc));}'
+    src = '#include "sba_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu",sizeof(sba_problem_desc),' \
+          'sizeof(sba_solver_options),sizeof(sba_iteration_summary),sizeof(sba_summary),sizeof(sba_semantic_desc),sizeof(sba_cylinder_desc),' \
+          'sizeof(sba_semantic_problem),sizeof(sba_cylinder_problem),sizeof(sba_rig_desc),sizeof(sba_rig_problem));}'
     import tempfile
     with tempfile.TemporaryDirectory() as d:
         open(os.path.join(d, "s.c"), "w").write(src)
@@ -42,7 +43,8 @@ def test_struct_sizes_match_header(sba):
         sizes = [int(x) for x in subprocess.check_output([os.path.join(d, "s")]).split()]
     c = sba.capi
     assert sizes == [C.sizeof(c.ProblemDesc), C.sizeof(c.SolverOptions), C.sizeof(c.IterationSummary),
-                     C.sizeof(c.Summary), C.sizeof(c.SemanticDesc), C.sizeof(c.CylinderDesc)]
+                     C.sizeof(c.Summary), C.sizeof(c.SemanticDesc), C.sizeof(c.CylinderDesc), C.sizeof(c.SemanticProblem),
+                     C.sizeof(c.CylinderProblem), C.sizeof(c.RigDesc), C.sizeof(c.RigProblem)]
 
 
 def test_default_options_are_the_reference_defaults(sba):

@@ -265,3 +265,68 @@ def test_per_iteration_dump_directories(sba, oracle, tmp_path):
     assert s2 is not None and len(dump2.steps) == len(rows2)
     cyl = io.read_cylinders(str(tmp_path / "gsba_steps" / ("step_%d" % dump2.steps[-1]) / "cylinders.txt"))
     assert np.allclose(np.asarray(cyl).reshape(-1, 9), cp.cylinder_params, rtol=1e-5, atol=1e-6)  # "%g": 6 digits
+
+
+# ------------------------------------------------------------------ a13: optional landmark blocks (include_landmark_error)
+def add_landmarks(sba, p, keep, n_pts=40, seed=0, weight=1.0, const_points=()):
+    """Reprojection blocks of every point in every image (SIMPLE_PINHOLE, the cylinder scene's cameras) with 1 px noise,
+    ScaledLoss weight = landmark_error_weight / number of 2-D features (geometric_semantic_bundle_adjustment.cc:758)."""
+    capi = sba.capi
+    rng = np.random.default_rng(seed + 50)
+    q, t, cams = keep[0].reshape(-1, 4), keep[1].reshape(-1, 3), np.asarray(keep[2]).reshape(-1, 3)
+    n_img = len(q)
+    X = np.column_stack([rng.uniform(-1.5, 1.5, n_pts), rng.uniform(-1.0, 1.0, n_pts), rng.uniform(4, 7, n_pts)])
+    li, lp, lxy = [], [], []
+    for i in range(n_img):
+        R = sba.scene.rotmat_from_quat((q[i] / np.linalg.norm(q[i]))[None])[0]
+        Pc = X @ R.T + t[i]
+        xy = cams[i, 0] * Pc[:, :2] / Pc[:, 2:3] + cams[i, 1:3] + rng.normal(0, 1.0, (n_pts, 2))
+        li += [i] * n_pts; lp += list(range(n_pts)); lxy.append(xy)
+    X += rng.normal(0, 0.05, X.shape)   # the points start off their true positions
+    pc = np.zeros(n_pts, np.uint8); pc[list(const_points)] = 1
+    extra = [np.ascontiguousarray(X), pc, np.asarray(li, np.int32), np.asarray(lp, np.int32), np.ascontiguousarray(np.vstack(lxy))]
+    p.num_points, p.points, p.point_constant = n_pts, capi.ptr(extra[0], capi._dp), capi.ptr(extra[1], capi._u8p)
+    p.num_landmarks, p.landmark_image, p.landmark_point = len(li), capi.ptr(extra[2], capi._ip), capi.ptr(extra[3], capi._ip)
+    p.landmark_xy, p.landmark_weight = capi.ptr(extra[4], capi._dp), weight / len(li)
+    keep.append(extra)
+    return p, keep
+
+
+def test_oracle_cylinder_solve_with_landmarks(sba, oracle):
+    p, keep = cylinder_problem(sba, oracle, kind=0, pose_const=[1, 0, 0])
+    p, keep = add_landmarks(sba, p, keep, const_points=(0, 1))
+    X0 = keep[-1][0].copy()
+    rc, s, tr = _run(oracle.oracle_cylinder_solve, p, _opts(sba.capi, oracle, 8), 0)
+    assert rc == 0
+    # 9 IoU blocks + 3 x 40 landmark blocks of two rows; 2 poses x 6 + 3 cylinders x 8 + 38 variable points x 3
+    assert (s.num_residual_blocks, s.num_residuals_reduced) == (9 + 120, 9 + 240)
+    assert s.num_effective_parameters_reduced == 12 + 24 + 38 * 3
+    assert s.final_cost < s.initial_cost
+    X1 = keep[-1][0]
+    assert np.array_equal(X1[:2], X0[:2]) and not np.array_equal(X1[2:], X0[2:])   # constant points stay, the others move
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,pc,weight", [(0, [1, 0, 0], 1.0), (1, [0, 0, 0], 50.0)])
+def test_cylinder_solve_with_landmarks_parity(sba, oracle, kind, pc, weight):
+    o = _opts(sba.capi, oracle, 6)
+    po, ko = add_landmarks(sba, *cylinder_problem(sba, oracle, kind=kind, pose_const=pc), weight=weight, const_points=(3,))
+    pg, kg = add_landmarks(sba, *cylinder_problem(sba, oracle, kind=kind, pose_const=pc), weight=weight, const_points=(3,))
+    rco, so, tro = _run(oracle.oracle_cylinder_solve, po, o, 0)
+    rcg, sg, trg = _run(sba.capi.load().sba_cylinder_solve, pg, o, C.cast(None, sba.capi.ITERATION_CALLBACK), None)
+    assert rco == 0 and rcg == 0
+    assert (sg.num_residual_blocks, sg.num_residuals_reduced, sg.num_effective_parameters_reduced) == \
+           (so.num_residual_blocks, so.num_residuals_reduced, so.num_effective_parameters_reduced)
+    assert sg.initial_cost == pytest.approx(so.initial_cost, rel=1e-12)
+    _same_trace(trg, tro, rel=1e-7)
+    assert np.allclose(kg[-1][0], ko[-1][0], atol=1e-6) and np.allclose(kg[1], ko[1], atol=1e-6) and np.allclose(kg[6], ko[6], atol=1e-6)
+    assert np.array_equal(kg[-1][0][3], ko[-1][0][3])
+    # the Python wrapper carries the same blocks
+    e = kg[-1]
+    cp = sba.semantic_adjusters.CylinderProblem(*cylinder_problem(sba, oracle, kind=kind, pose_const=pc)[1][:4],
+                                                cylinder_problem(sba, oracle, kind=kind)[1][6], cylinder_kind=kind, image_pose_constant=pc,
+                                                points=add_landmarks(sba, *cylinder_problem(sba, oracle, kind=kind))[1][-1][0],
+                                                point_constant=e[1], landmark_image=e[2], landmark_point=e[3], landmark_xy=e[4],
+                                                landmark_error_weight=weight)
+    s2, rows2 = cp.solve(sba.semantic_adjusters.semantic_solver_options(6))
+    assert s2 is not None and s2.num_residual_blocks == sg.num_residual_blocks and s2.final_cost == pytest.approx(sg.final_cost, rel=1e-9)
