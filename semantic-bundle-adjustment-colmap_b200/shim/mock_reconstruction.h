@@ -198,5 +198,98 @@ class Reconstruction {
   point3D_t num_added_points3D_ = 0;
 };
 
+// ---- CameraRig: the part the rig bundle adjuster uses (/root/reference/src/base/camera_rig.h:27-107, camera_rig.cc:86-110,
+// 230-258; pose helpers /root/reference/src/base/pose.cc:82-143, 192-196) ----------------------------------------------
+class CameraRig {
+ public:
+  void AddCamera(camera_t camera_id, const Vector4d& rel_qvec, const Vector3d& rel_tvec) { rig_cameras_[camera_id] = {rel_qvec, rel_tvec}; order_.push_back(camera_id); }
+  void AddSnapshot(const std::vector<image_t>& image_ids) { snapshots_.push_back(image_ids); }
+  void SetRefCameraId(camera_t id) { ref_camera_id_ = id; }
+  camera_t RefCameraId() const { return ref_camera_id_; }
+  bool HasCamera(camera_t id) const { return rig_cameras_.count(id) > 0; }
+  size_t NumCameras() const { return rig_cameras_.size(); }
+  size_t NumSnapshots() const { return snapshots_.size(); }
+  const std::vector<camera_t>& GetCameraIds() const { return order_; }
+  const std::vector<std::vector<image_t>>& Snapshots() const { return snapshots_; }
+  Vector4d& RelativeQvec(camera_t id) { return rig_cameras_.at(id).first; }
+  const Vector4d& RelativeQvec(camera_t id) const { return rig_cameras_.at(id).first; }
+  Vector3d& RelativeTvec(camera_t id) { return rig_cameras_.at(id).second; }
+  const Vector3d& RelativeTvec(camera_t id) const { return rig_cameras_.at(id).second; }
+  void Check(const Reconstruction& rec) const {  // camera_rig.cc:86-110
+    if (!HasCamera(ref_camera_id_)) throw std::invalid_argument("reference camera is not part of the rig");
+    for (const auto& kv : rig_cameras_) rec.Camera(kv.first);
+    for (const auto& snap : snapshots_) {
+      if (snap.empty() || snap.size() > NumCameras()) throw std::invalid_argument("invalid snapshot");
+      bool has_ref = false;
+      for (image_t id : snap) {
+        if (!HasCamera(rec.Image(id).CameraId())) throw std::invalid_argument("snapshot image's camera is not part of the rig");
+        has_ref = has_ref || rec.Image(id).CameraId() == ref_camera_id_;
+      }
+      if (!has_ref) throw std::invalid_argument("snapshot without the reference camera");
+    }
+  }
+  // average of the rig poses the snapshot's images imply (camera_rig.cc:230-258)
+  void ComputeAbsolutePose(size_t snapshot_idx, const Reconstruction& rec, Vector4d* abs_qvec, Vector3d* abs_tvec) const {
+    const auto& snap = snapshots_.at(snapshot_idx);
+    double A[4][4] = {};
+    *abs_tvec = {0.0, 0.0, 0.0};
+    Vector4d last{};
+    for (image_t id : snap) {
+      const Image& im = rec.Image(id);
+      const Vector4d rq = Normalized(RelativeQvec(im.CameraId()));
+      const Vector4d inv{rq[0], -rq[1], -rq[2], -rq[3]};                      // InvertQuaternion
+      const Vector4d q = Normalized(Mul(inv, Normalized(im.Qvec())));         // ConcatenateQuaternions(image, inv_rel) = inv_rel * image
+      const Vector3d d{im.Tvec()[0] - RelativeTvec(im.CameraId())[0], im.Tvec()[1] - RelativeTvec(im.CameraId())[1], im.Tvec()[2] - RelativeTvec(im.CameraId())[2]};
+      const Vector3d t = Rot(inv, d);
+      for (int a = 0; a < 4; ++a) for (int b = 0; b < 4; ++b) A[a][b] += q[a] * q[b];
+      for (int a = 0; a < 3; ++a) (*abs_tvec)[a] += t[a];
+      last = q;
+    }
+    for (int a = 0; a < 3; ++a) (*abs_tvec)[a] /= (double)snap.size();
+    if (snap.size() == 1) { *abs_qvec = last; return; }
+    // AverageQuaternions (pose.cc:118-143): eigenvector of the largest eigenvalue of sum q q^T -- cyclic Jacobi on the 4 x 4
+    double V[4][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}};
+    for (int sweep = 0; sweep < 50; ++sweep) {
+      double off = 0.0;
+      for (int p = 0; p < 4; ++p) for (int q = p + 1; q < 4; ++q) off += A[p][q] * A[p][q];
+      if (off < 1e-30) break;
+      for (int p = 0; p < 4; ++p)
+        for (int q = p + 1; q < 4; ++q) {
+          if (std::fabs(A[p][q]) < 1e-300) continue;
+          const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+          const double tt = (theta >= 0 ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+          const double c = 1.0 / std::sqrt(tt * tt + 1.0), s = tt * c;
+          for (int k = 0; k < 4; ++k) { const double akp = A[k][p], akq = A[k][q]; A[k][p] = c * akp - s * akq; A[k][q] = s * akp + c * akq; }
+          for (int k = 0; k < 4; ++k) { const double apk = A[p][k], aqk = A[q][k]; A[p][k] = c * apk - s * aqk; A[q][k] = s * apk + c * aqk; }
+          for (int k = 0; k < 4; ++k) { const double vkp = V[k][p], vkq = V[k][q]; V[k][p] = c * vkp - s * vkq; V[k][q] = s * vkp + c * vkq; }
+        }
+    }
+    int best = 0;
+    for (int k = 1; k < 4; ++k) if (A[k][k] > A[best][best]) best = k;
+    *abs_qvec = {V[0][best], V[1][best], V[2][best], V[3][best]};
+  }
+
+ private:
+  static Vector4d Normalized(const Vector4d& q) {
+    const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    return n == 0.0 ? Vector4d{1.0, 0.0, 0.0, 0.0} : Vector4d{q[0] / n, q[1] / n, q[2] / n, q[3] / n};
+  }
+  static Vector4d Mul(const Vector4d& a, const Vector4d& b) {
+    return {a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3], a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+            a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1], a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]};
+  }
+  static Vector3d Rot(const Vector4d& qv, const Vector3d& p) {
+    const Vector4d q = Normalized(qv);
+    const double w = q[0], x = q[1], y = q[2], z = q[3];
+    return {(1 - 2 * (y * y + z * z)) * p[0] + 2 * (x * y - w * z) * p[1] + 2 * (x * z + w * y) * p[2],
+            2 * (x * y + w * z) * p[0] + (1 - 2 * (x * x + z * z)) * p[1] + 2 * (y * z - w * x) * p[2],
+            2 * (x * z - w * y) * p[0] + 2 * (y * z + w * x) * p[1] + (1 - 2 * (x * x + y * y)) * p[2]};
+  }
+  camera_t ref_camera_id_ = std::numeric_limits<camera_t>::max();
+  std::unordered_map<camera_t, std::pair<Vector4d, Vector3d>> rig_cameras_;
+  std::vector<camera_t> order_;
+  std::vector<std::vector<image_t>> snapshots_;
+};
+
 }  // namespace sba_mock
 #endif  // SBA_SHIM_MOCK_RECONSTRUCTION_H_

@@ -11,6 +11,7 @@
 #include "mock_reconstruction.h"
 #include "sba_bundle_adjuster.h"
 #include "sba_mapper_passes.h"
+#include "sba_rig_bundle_adjuster.h"
 #include "sba_semantic_adjusters.h"
 
 using namespace sba_mock;
@@ -420,6 +421,48 @@ static void TestMapperPasses() {
   }
 }
 
+// ---- RigBundleAdjuster (shim/sba_rig_bundle_adjuster.h): the reference's own rig tests, bundle_adjustment_test.cc:755-969 ----
+using RigBundleAdjuster = sba_shim::RigBundleAdjusterT<Reconstruction, sba_mock::CameraRig>;
+static void RigScene(size_t n_img, const std::vector<std::vector<image_t>>& snaps, Reconstruction* rec, std::vector<sba_mock::CameraRig>* rigs,
+                     BundleAdjustmentConfig* config) {
+  Generate(n_img, 100, rec);
+  if (n_img > 2) { rec->Image(2).SetCameraId(0); rec->Image(3).SetCameraId(1); }
+  rigs->emplace_back();
+  (*rigs)[0].AddCamera(0, Vector4d{1, 0, 0, 0}, Vector3d{0, 0, 0});
+  (*rigs)[0].AddCamera(1, Vector4d{1, 0, 0, 0}, Vector3d{0, 0, 0});
+  for (const auto& s : snaps) (*rigs)[0].AddSnapshot(s);
+  (*rigs)[0].SetRefCameraId(0);
+  for (image_t i = 0; i < n_img; ++i) config->AddImage(i);
+}
+static void TestRigSolve() {
+  BundleAdjustmentOptions opt;
+  opt.print_summary = false;
+  struct Case { size_t n; std::vector<std::vector<image_t>> snaps; bool refine; int res, eff; };
+  const std::vector<Case> cases = {{2, {{0, 1}}, true, 400, 316}, {4, {{0, 1}, {2, 3}}, true, 800, 322},
+                                   {4, {{0, 1}, {2, 3}}, false, 800, 316}, {4, {{0, 1}, {2}}, true, 800, 328}};
+  for (const Case& c : cases) {
+    Reconstruction rec; std::vector<sba_mock::CameraRig> rigs; BundleAdjustmentConfig config;
+    RigScene(c.n, c.snaps, &rec, &rigs, &config);
+    const Reconstruction orig = rec;
+    const auto orig_rigs = rigs;
+    sba_shim::RigBundleAdjusterOptions ro;
+    ro.refine_relative_poses = c.refine;
+    RigBundleAdjuster ba(opt, ro, config);
+    CHECK_THAT(ba.Solve(&rec, &rigs));
+    const auto& s = ba.Summary();
+    CHECK_THAT(s.num_residuals_reduced == c.res && s.num_effective_parameters_reduced == c.eff);
+    CHECK_THAT(s.final_cost < s.initial_cost);
+    // CheckVariableCameraRig / CheckConstantCameraRig: the reference camera's relative pose never moves, the other
+    // one only with refine_relative_poses
+    CHECK_THAT(rigs[0].RelativeTvec(0) == orig_rigs[0].RelativeTvec(0) && rigs[0].RelativeQvec(0) == orig_rigs[0].RelativeQvec(0));
+    CHECK_THAT((rigs[0].RelativeTvec(1) != orig_rigs[0].RelativeTvec(1)) == c.refine);
+    CHECK_THAT(rec.Image(0).Tvec() != orig.Image(0).Tvec());
+    for (const auto& kv : rec.Points3D()) CHECK_THAT(kv.second.XYZ() != orig.Point3D(kv.first).XYZ());
+    std::printf("rig %zu views%s: cost %.6g -> %.6g, %d / %d\n", c.n, c.refine ? "" : " (constant relative poses)", s.initial_cost,
+                s.final_cost, s.num_residuals_reduced, s.num_effective_parameters_reduced);
+  }
+}
+
 int main(int argc, char** argv) {
   const bool solve = argc > 1 && std::strcmp(argv[1], "solve") == 0;
   TestCounts();
@@ -432,6 +475,7 @@ int main(int argc, char** argv) {
     TestSolve();
     TestSemanticSolve();
     TestMapperPasses();
+    TestRigSolve();
   }
   std::printf("%s (%d failed)\n", g_failed ? "FAILED" : "OK", g_failed);
   return g_failed ? 1 : 0;

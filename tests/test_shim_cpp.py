@@ -14,7 +14,7 @@ EXE = os.path.join(ROOT, "tests", "shim_test.bin")
 def shim_exe(sba):
     sba.capi.load()  # the C-ABI library must exist (build() made it); never built lazily here
     src = os.path.join(ROOT, "tests", "shim_test.cpp")
-    hdrs = [os.path.join(PKG, "shim", h) for h in ("sba_bundle_adjuster.h", "sba_semantic_adjusters.h", "sba_mapper_passes.h", "mock_reconstruction.h")]
+    hdrs = [os.path.join(PKG, "shim", h) for h in ("sba_bundle_adjuster.h", "sba_semantic_adjusters.h", "sba_mapper_passes.h", "sba_rig_bundle_adjuster.h", "mock_reconstruction.h")]
     lib = os.path.join(PKG, "libsba_b200.so")
     newest = max(os.path.getmtime(p) for p in [src, lib] + hdrs)
     if not os.path.exists(EXE) or os.path.getmtime(EXE) < newest:
@@ -34,4 +34,4 @@ def test_shim_solve_on_device(shim_exe):
     out = subprocess.run([shim_exe, "solve"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "two_view: cost" in out.stdout and "semantic: cost" in out.stdout and "cylinder: cost" in out.stdout
-    assert "refine_absolute_pose: cost" in out.stdout
+    assert "refine_absolute_pose: cost" in out.stdout and out.stdout.count("rig ") == 4
