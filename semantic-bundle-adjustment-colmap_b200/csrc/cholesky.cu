@@ -253,11 +253,26 @@ __global__ void __launch_bounds__(256) chol_trsm128_kernel(double* __restrict__ 
   const int tid = threadIdx.x;
   const int r0 = k0 + nb + row_off + NBT * blockIdx.x;
   const int nr = min(NBT, n_rows - r0);
-  for (int idx = tid; idx < NBT * PB; idx += 256) {
-    const int r = idx / PB, c = idx - r * PB;
-    A[r][c] = (r < nr && c < nb) ? S[(size_t)(r0 + r) * ld + k0 + c] : 0.0;
+  // all loads of a batch are issued before the first shared-memory store (these kernels sit on the factorisation's
+  // critical chain: with the loads trickling out four at a time the 16-row variant took 24 us, most of it waiting)
+  {
+    double va[(NBT * PB) / 256];
+#pragma unroll
+    for (int it = 0; it < (NBT * PB) / 256; ++it) {
+      const int idx = tid + 256 * it, r = idx / PB, c = idx - r * PB;
+      va[it] = (r < nr && c < nb) ? S[(size_t)(r0 + r) * ld + k0 + c] : 0.0;
+    }
+#pragma unroll
+    for (int it = 0; it < (NBT * PB) / 256; ++it) { const int idx = tid + 256 * it; A[idx / PB][idx % PB] = va[it]; }
   }
-  for (int idx = tid; idx < PB * PB; idx += 256) Li[idx / PB][idx % PB] = Linv[idx];
+#pragma unroll 1
+  for (int b0 = 0; b0 < PB * PB; b0 += 256 * 16) {
+    double vl[16];
+#pragma unroll
+    for (int it = 0; it < 16; ++it) vl[it] = Linv[b0 + tid + 256 * it];
+#pragma unroll
+    for (int it = 0; it < 16; ++it) { const int idx = b0 + tid + 256 * it; Li[idx / PB][idx % PB] = vl[it]; }
+  }
   __syncthreads();
   const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, RPT rows x 8 columns each (strided by 16)
   double acc[RPT][8];
@@ -297,10 +312,16 @@ __global__ void __launch_bounds__(256) chol_syrk_next_diag_kernel(double* __rest
   double(*Bs)[LDP] = reinterpret_cast<double(*)[LDP]>(smem + 32 * LDP);  // [32][129]
   const int tid = threadIdx.x;
   const int i0 = t0 + 32 * blockIdx.y, j0 = t0 + 32 * blockIdx.x;
-  for (int idx = tid; idx < 32 * PB; idx += 256) {
-    const int r = idx / PB, c = idx - r * PB;
-    As[r][c] = (i0 + r < n_rows && c < nb) ? S[(size_t)(i0 + r) * ld + k0 + c] : 0.0;
-    Bs[r][c] = (j0 + r < n_rows && c < nb) ? S[(size_t)(j0 + r) * ld + k0 + c] : 0.0;
+  {
+    double va[16], vb[16];  // 32 x 128 of each operand: 16 loads per thread and operand, all in flight together
+#pragma unroll
+    for (int it = 0; it < 16; ++it) {
+      const int idx = tid + 256 * it, r = idx / PB, c = idx - r * PB;
+      va[it] = (i0 + r < n_rows && c < nb) ? S[(size_t)(i0 + r) * ld + k0 + c] : 0.0;
+      vb[it] = (j0 + r < n_rows && c < nb) ? S[(size_t)(j0 + r) * ld + k0 + c] : 0.0;
+    }
+#pragma unroll
+    for (int it = 0; it < 16; ++it) { const int idx = tid + 256 * it; As[idx / PB][idx % PB] = va[it]; Bs[idx / PB][idx % PB] = vb[it]; }
   }
   __syncthreads();
   const int tx = tid & 15, ty = tid >> 4;
