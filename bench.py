@@ -331,7 +331,7 @@ def io_bytes(prob, out):
 
 def stages_for(m, summ):
     dense = summ.linear_solver_type_used != m.capi.ITERATIVE_SCHUR
-    return ["eval", "cost", "point_blocks", "rhs", "backsub"] + (
+    return ["eval", "cost", "point_blocks", "point_refresh", "rhs", "backsub"] + (
         ["schur_dense", "cholesky"] if dense else ["schur_jacobi", "matvec", "schur_blocks", "matvec_blocks"])
 
 

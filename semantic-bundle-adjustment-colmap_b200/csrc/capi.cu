@@ -320,8 +320,11 @@ int sba_bench_stage(sba_handle* h, const char* stage, int32_t repeat, double* ms
     run = [&]() { return LaunchCostOnly(p, loss, false, &p->d_scalars.p->cand_cost); };
     bytes = n_obs * 24 + gathers;
   } else if (s == "point_blocks") {
-    run = [&]() { return PointBlocks(p, false); };
-    bytes = n_obs * (64 + 4) + (int64_t)p->n_pvar * (24 + 48 + 24);
+    run = [&]() { p->ete_valid = false; return PointBlocks(p, false); };  // the pass over ER (after an accepted step)
+    bytes = n_obs * (64 + 4) + (int64_t)p->n_pvar * (24 + 48 + 24 + 48);
+  } else if (s == "point_refresh") {
+    run = [&]() { return PointBlocks(p, false); };  // the per-iteration form: cached E^T E + the new LM diagonal
+    bytes = (int64_t)p->n_pvar * (48 + 24 + 48 + 48);
   } else if (s == "rhs") {
     run = [&]() { return ReducedRhs(p); };
     bytes = n_obs * (64 + 16 * dc + 16 + 16 + 8);

@@ -413,6 +413,7 @@ static int EvalGrid(const Problem* p) { return std::min(DivUp(p->n_obs, kEvalThr
 
 int LaunchEvaluate(Problem* p, const LossView& loss, bool use_scale, bool candidate, bool defer_allreduce) {
   p->colnorm_current = false;  // a new Jacobian: d_sq_c is stale until ColumnNorms / Gradient(with_norms)
+  p->ete_valid = false;        // ... and the cached E_p^T E_p until the next pass over ER (PointBlocks)
   const int blocks = EvalGrid(p);
   if (blocks > 0) {
 #define CALL(M) LaunchEvalT<M>(p, loss, use_scale, candidate, blocks)

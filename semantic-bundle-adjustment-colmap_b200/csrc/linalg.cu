@@ -82,6 +82,7 @@ int InitJacobiScale(Problem* p) {
     p->launches++;
   }
   p->colnorm_current = false;  // the stored Jacobian was rescaled
+  p->ete_valid = false;
   SBA_CUDA(cudaGetLastError());
   return SBA_OK;
 }
@@ -161,14 +162,19 @@ int PrepareLMDiagonal(Problem* p, const sba_solver_options& o) {
 // grad_only: only g_p = E^T r (no LM diagonal needed yet)
 int PointBlocks(Problem* p, bool grad_only) {
   if (p->n_pvar > 0 && p->n_tiles > 0) {
-    if (p->nr == 3)
+    if (!grad_only && p->ete_valid) {  // E unchanged since the last pass over ER: only D_p^2 is new
+      point_blocks_refresh_kernel<<<DivUp(p->n_pvar, 256), 256, 0, p->stream>>>(p->n_pvar, p->d_EtE.p, p->d_Dp.p, p->d_Cinv.p,
+                                                                                 p->d_Cfac.p, p->d_scalars.p);
+    } else if (p->nr == 3) {
       point_blocks_kernel<3><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
                                                                         grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
-                                                                        p->d_Cfac.p, p->d_gp.p, p->d_scalars.p);
-    else
+                                                                        p->d_Cfac.p, p->d_gp.p, p->d_EtE.p, p->d_scalars.p);
+    } else {
       point_blocks_kernel<2><<<DivUp(p->n_tiles, 4), 128, 0, p->stream>>>(p->Struct(), p->Tiles(), p->d_ER.p, p->d_ES.p,
                                                                         grad_only ? nullptr : p->d_Dp.p, p->d_Cinv.p,
-                                                                        p->d_Cfac.p, p->d_gp.p, p->d_scalars.p);
+                                                                        p->d_Cfac.p, p->d_gp.p, p->d_EtE.p, p->d_scalars.p);
+    }
+    p->ete_valid = true;
     p->launches++;
   }
   SBA_CUDA(cudaGetLastError());

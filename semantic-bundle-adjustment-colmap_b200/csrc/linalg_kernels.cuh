@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
                                                            const D4* __restrict__ ES,
                                                            const double* __restrict__ Dp, double* __restrict__ Cinv,
                                                            double* __restrict__ Cfac,
-                                                           double* __restrict__ gp, DeviceScalars* sc) {
+                                                           double* __restrict__ gp, double* __restrict__ EtE, DeviceScalars* sc) {
   const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (tile >= T.n_tiles) return;
   const int lane = threadIdx.x & 31;
@@ -226,6 +226,10 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
   if (writer) {
     const int po = S.p_off[pt];
     if (po >= 0) {
+      if (EtE) {
+#pragma unroll
+        for (int a = 0; a < 6; ++a) EtE[6 * (size_t)po + a] = v[a];
+      }
       if (Dp) {
         const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
         const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
@@ -245,6 +249,27 @@ __global__ void __launch_bounds__(128) point_blocks_kernel(StructView S, TileVie
       gp[3 * (size_t)po] = v[6]; gp[3 * (size_t)po + 1] = v[7]; gp[3 * (size_t)po + 2] = v[8];
     }
   }
+}
+
+// The same blocks from the cached E_p^T E_p when only the LM diagonal changed (every iteration changes D_p; E changes
+// with an accepted step only, and the pass that follows it -- the gradient's -- leaves E^T E behind): one thread per
+// variable point, 72 B in and 96 B out instead of a pass over all ER records (C4: 0.144 -> ~0.04 ms).
+__global__ void __launch_bounds__(256) point_blocks_refresh_kernel(int n_pvar, const double* __restrict__ EtE,
+                                                                   const double* __restrict__ Dp, double* __restrict__ Cinv,
+                                                                   double* __restrict__ Cfac, DeviceScalars* sc) {
+  const int po = blockIdx.x * 256 + threadIdx.x;
+  if (po >= n_pvar) return;
+  const double* v = EtE + 6 * (size_t)po;
+  const double d0 = Dp[3 * (size_t)po], d1 = Dp[3 * (size_t)po + 1], d2 = Dp[3 * (size_t)po + 2];
+  const double c[6] = {v[0] + d0 * d0, v[1], v[2], v[3] + d1 * d1, v[4], v[5] + d2 * d2};
+  double inv[6], fac[6];
+  if (!InvertSym3(c, inv, fac)) {
+    sc->solver_failed = 1;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { inv[a] = 0.0; fac[a] = 0.0; }
+  }
+#pragma unroll
+  for (int a = 0; a < 6; ++a) { Cinv[6 * (size_t)po + a] = inv[a]; Cfac[6 * (size_t)po + a] = fac[a]; }
 }
 
 // ---- e_k = r_k - E_k C_p^{-1} g_p  (right-hand side of the reduced system, before F^T) ----

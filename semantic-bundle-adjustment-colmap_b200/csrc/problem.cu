@@ -901,7 +901,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   UP(p->d_sq_p.Alloc(np3));
   UP(p->d_diag_c.Alloc(nc)); UP(p->d_diag_p.Alloc(np3)); UP(p->d_Dc.Alloc(nc)); UP(p->d_Dp.Alloc(np3));
   UP(p->d_Cinv.Alloc((size_t)std::max(1, p->n_pvar) * 6)); UP(p->d_gp.Alloc(np3));
-  UP(p->d_Cfac.Alloc((size_t)std::max(1, p->n_pvar) * 6));
+  UP(p->d_Cfac.Alloc((size_t)std::max(1, p->n_pvar) * 6)); UP(p->d_EtE.Alloc((size_t)std::max(1, p->n_pvar) * 6));
   UP(p->d_chunk_partial.Alloc((size_t)std::max(1, p->n_chunks) * kMaxDC * 2));
   UP(p->d_g2.Alloc((size_t)std::max(1, n_obs) * 2));
   UP(p->d_rhs.Alloc(nc)); UP(p->d_yc.Alloc(nc)); UP(p->d_yp.Alloc(np3)); UP(p->d_step_c.Alloc(nc));

@@ -231,6 +231,9 @@ struct Problem {
   DevBuf<double> d_diag_c, d_diag_p;        // clamped column square norms
   DevBuf<double> d_Dc, d_Dp;                // LM diagonal
   DevBuf<double> d_Cinv, d_gp;              // [n_pvar*6] sym inverse, [n_pvar*3]
+  DevBuf<double> d_EtE;                     // [n_pvar*6] E_p^T E_p of the current linearisation (without D_p^2): the LM diagonal
+                                            // changes every iteration, E only with an accepted step (PointBlocks, linalg.cu)
+  bool ete_valid = false;                   // d_EtE and d_gp belong to the current d_ER
   DevBuf<double> d_Cfac;                    // [n_pvar*6] M = L^{-1} (lower) with C_p^{-1} = M^T M: U_a = (F_a^T E_a) M^T (schur.cu)
   bool rhs_from_schur = false;              // the explicit Schur build of this iteration also leaves the reduced rhs in d_rhs
   DevBuf<double> d_chunk_partial;           // [n_chunks*dc] (or dc*dc for block sums)
