@@ -221,6 +221,19 @@ typedef int (*sba_iteration_callback)(const sba_iteration_summary* it, void* use
 /* --- lifecycle ---------------------------------------------------------- */
 void sba_default_solver_options(sba_solver_options* o);
 int sba_create(const sba_problem_desc* desc, sba_handle** out);
+/* Label maps that stay on the device across problems.  The reference loads an image's label map once and every
+ * BundleAdjuster::Solve of the mapper reads the same maps (src/optim/bundle_adjustment.cc:361-372 hands the image's
+ * map to each cost functor; the mapper calls Solve after every batch of registrations, src/sfm/incremental_mapper.cc:
+ * 640-711): sba_maps_create copies `maps` ([num_images*height*width] row-major, top-down, as sba_problem_desc::
+ * sem_maps) to the current device once, sba_create_with_maps builds a problem over them without moving them again
+ * (desc->sem_maps must be NULL, desc->num_images must equal the set's; desc->sem_weight applies; sem_height / sem_width
+ * of the descriptor are ignored).  The set is reference-counted: sba_maps_destroy may be called while handles created
+ * over it are alive, the device memory goes with the last of them.  Results are bit-identical to sba_create with the
+ * same maps in the descriptor. */
+typedef struct sba_maps sba_maps;
+int sba_maps_create(int32_t num_images, int32_t height, int32_t width, const float* maps, sba_maps** out);
+void sba_maps_destroy(sba_maps* maps);
+int sba_create_with_maps(const sba_problem_desc* desc, const sba_maps* maps, sba_handle** out);
 /* Host-only: the structural counts Ceres reports for this problem (Solver::Summary
  * num_residuals_reduced, num_effective_parameters_reduced, ... as pinned by
  * src/optim/bundle_adjustment_test.cc:186-645).  Needs no device. */

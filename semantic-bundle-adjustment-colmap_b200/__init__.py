@@ -7,7 +7,7 @@ BundleAdjustmentOptions mirror (`bundle_adjustment`), the synthetic scene genera
 either side of the path (`model_io`: sparse model binary / text, float32 TIFF maps, cylinders.txt).
 """
 from . import _capi as capi  # noqa: F401
-from .problem import FlatProblem, Solver, comm_unique_id  # noqa: F401
+from .problem import FlatProblem, ResidentMaps, Solver, comm_unique_id  # noqa: F401
 from .bundle_adjustment import (  # noqa: F401
     BundleAdjuster, BundleAdjustmentConfig, BundleAdjustmentOptions, Camera, Image, Point2D, Point3D,
     Reconstruction, Track, TrackElement)

@@ -175,6 +175,9 @@ ITERATION_CALLBACK = C.CFUNCTYPE(C.c_int, C.POINTER(IterationSummary), C.c_void_
 SYMBOLS = {
     "sba_default_solver_options": (None, [C.POINTER(SolverOptions)]),
     "sba_create": (C.c_int, [C.POINTER(ProblemDesc), C.POINTER(C.c_void_p)]),
+    "sba_maps_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, _fp, C.POINTER(C.c_void_p)]),
+    "sba_maps_destroy": (None, [C.c_void_p]),
+    "sba_create_with_maps": (C.c_int, [C.POINTER(ProblemDesc), C.c_void_p, C.POINTER(C.c_void_p)]),
     "sba_problem_counts": (C.c_int, [C.POINTER(ProblemDesc), C.POINTER(Summary)]),
     "sba_destroy": (None, [C.c_void_p]),
     "sba_set_device": (C.c_int, [C.c_int32]),

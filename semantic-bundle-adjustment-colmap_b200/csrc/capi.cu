@@ -71,6 +71,35 @@ int sba_create(const sba_problem_desc* desc, sba_handle** out) {
   return SBA_OK;
 }
 
+struct sba_maps { MapSet* m; };
+
+int sba_maps_create(int32_t num_images, int32_t height, int32_t width, const float* maps, sba_maps** out) {
+  if (!out) { SetError(SBA_ERR_INVALID_ARGUMENT, "null output map set"); return SBA_ERR_INVALID_ARGUMENT; }
+  *out = nullptr;
+  MapSet* m = nullptr;
+  const int rc = BuildMapSet(num_images, height, width, maps, &m);
+  if (rc) return rc;
+  *out = new sba_maps{m};
+  return SBA_OK;
+}
+
+void sba_maps_destroy(sba_maps* maps) {
+  if (!maps) return;
+  MapSetRelease(maps->m);  // the device block goes once the last handle created over it is destroyed
+  delete maps;
+}
+
+int sba_create_with_maps(const sba_problem_desc* desc, const sba_maps* maps, sba_handle** out) {
+  if (!out) { SetError(SBA_ERR_INVALID_ARGUMENT, "null output handle"); return SBA_ERR_INVALID_ARGUMENT; }
+  *out = nullptr;
+  if (!maps || !maps->m) { SetError(SBA_ERR_INVALID_ARGUMENT, "null map set"); return SBA_ERR_INVALID_ARGUMENT; }
+  Problem* p = nullptr;
+  const int rc = BuildProblem(desc, &p, false, maps->m);
+  if (rc) return rc;
+  *out = new sba_handle{p};
+  return SBA_OK;
+}
+
 void* sba_host_alloc(uint64_t bytes) {
   void* p = nullptr;
   if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {

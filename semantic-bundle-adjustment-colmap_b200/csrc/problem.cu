@@ -358,6 +358,7 @@ Problem::~Problem() {
   if (stream) cudaStreamSynchronize(stream);  // buffers go back to the pool only once nothing uses them
   DropGraphs();
   CommDestroy(this);
+  if (shared_maps) { MapSetRelease(shared_maps); shared_maps = nullptr; }
   if (stream2) { cudaStreamSynchronize(stream2); cudaStreamDestroy(stream2); }
   if (stream3) { cudaStreamSynchronize(stream3); cudaStreamDestroy(stream3); }
   for (auto& e : ev_chol) if (e) cudaEventDestroy(e);
@@ -490,7 +491,8 @@ static cudaError_t DeviceHistogramImages(cudaStream_t st, int64_t n, const int* 
 }
 
 // residual rows per block: the two reprojection rows, plus the semantic row when the problem carries maps (X1)
-static int RowsOf(const sba_problem_desc& d) {
+static int RowsOf(const sba_problem_desc& d, const MapSet* shared = nullptr) {
+  if (shared) return 3;
   return (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) ? 3 : 2;
 }
 
@@ -499,7 +501,7 @@ static int RowsOf(const sba_problem_desc& d) {
 // point (sba_problem_counts) counts here.  count_active: also count the residual blocks of the reduced program on the
 // host (a pass over the observation list); with a device that count is made there too (CountActiveOnDevice).
 static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt_count, const int* img_count,
-                    bool count_active) {
+                    bool count_active, const MapSet* shared = nullptr) {
   const int n_img = d.num_images, n_cam = d.num_cameras, n_pt = d.num_points;
   const int64_t n_obs = d.num_observations;
   std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used(n_pt, 0);
@@ -564,7 +566,7 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt
     g->p_off_global[p] = g->n_pvar_global++;
     s.num_parameter_blocks_reduced++; s.num_parameters_reduced += 3; s.num_effective_parameters_reduced += 3;
   }
-  const int nr = RowsOf(d);
+  const int nr = RowsOf(d, shared);
   s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(nr * n_obs);
   if (!count_active) return;
   std::vector<int64_t> n_act(NT, 0);
@@ -623,14 +625,76 @@ __global__ void retile_maps_kernel(const float* __restrict__ src, float* __restr
   }
 }
 
-int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
+// ---- label maps kept on the device across problems (sba_maps_create) ----
+// The reference loads an image's label map once and every BundleAdjuster::Solve of the mapper reads the same maps
+// (/root/reference/src/optim/bundle_adjustment.cc:361-372 hands the map of the image to each cost functor); at C5 they
+// are 6.5 GB, and moving them host -> device is 134 of the 231 ms of a create + solve + read-back.
+void MapSetRelease(MapSet* m) {
+  if (m && m->refs.fetch_sub(1) == 1) {
+    int prev = -1;
+    const int dev = m->device;
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    cudaDeviceSynchronize();  // no kernel of a destroyed handle may still read the block when it returns to the pool
+    delete m;
+    if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+  }
+}
+
+int BuildMapSet(int n_img, int h, int w, const float* maps, MapSet** out) {
+  *out = nullptr;
+  if (n_img <= 0 || h <= 0 || w <= 0 || !maps) {
+    SetError(SBA_ERR_INVALID_ARGUMENT, "sba_maps_create: num_images, height, width must be positive and maps non-null");
+    return SBA_ERR_INVALID_ARGUMENT;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    SetError(SBA_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+    return SBA_ERR_NO_DEVICE;
+  }
+  MapSet* m = new MapSet();
+  m->n_img = n_img; m->h = h; m->w = w;
+  cudaGetDevice(&m->device);
+  const size_t n_map = (size_t)n_img * h * w, n_out = (size_t)n_img * MapTiledSize(h, w);
+  DevBuf<float> stage;
+  cudaStream_t cs = CopyStream();
+  cudaError_t e = stage.Alloc(n_map);
+  if (e == cudaSuccess) e = m->tiled.Alloc(n_out);
+  if (e == cudaSuccess) e = UploadLarge(stage.p, maps, n_map * sizeof(float), cs);
+  if (e == cudaSuccess) {
+    retile_maps_kernel<<<(unsigned)std::min<size_t>(DivUp(n_out, 256), 148 * 64), 256, 0, cs>>>(stage.p, m->tiled.p, n_img, h, w);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(cs);
+  else cudaStreamSynchronize(cs);
+  if (e != cudaSuccess) {
+    SetError(SBA_ERR_CUDA, std::string("sba_maps_create: ") + cudaGetErrorString(e));
+    delete m;
+    return SBA_ERR_CUDA;
+  }
+  *out = m;
+  return SBA_OK;
+}
+
+int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapSet* shared) {
   HostTimer tm("create");
   int rc = Validate(dp);
   if (rc) return rc;
+  if (shared) {  // label maps already on the device (sba_maps_create): the descriptor must not carry a second set
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (host_only || dp->sem_maps || shared->n_img != dp->num_images || shared->device != dev) {
+      SetError(SBA_ERR_INVALID_ARGUMENT, dp->sem_maps ? "sba_create_with_maps: desc->sem_maps must be null when a resident map set is given"
+               : shared->n_img != dp->num_images ? "sba_create_with_maps: the map set holds a different number of images than the problem"
+                                                 : "sba_create_with_maps: the map set lives on another device than the current one");
+      return SBA_ERR_INVALID_ARGUMENT;
+    }
+  }
   tm.Lap("validate");
   const sba_problem_desc& d = *dp;
   Problem* p = new Problem();
-  p->nr = RowsOf(d);  // 3: the semantic row is part of every residual block (evaluation AND solve)
+  p->nr = RowsOf(d, shared);  // 3: the semantic row is part of every residual block (evaluation AND solve)
   // ---- device first: the label maps (61 MB at C2, 6 GB at C5) start moving on a side stream right away, so their
   //      DMA runs under the host set-up below instead of after it ----
   DevBuf<int> raw_img, raw_pt;   // the caller's observation arrays on the device (released after the final sync)
@@ -666,7 +730,12 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
       if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("observation upload: ") + cudaGetErrorString(e)); delete p; return SBA_ERR_CUDA; }
       std::memset(p->h_scalars, 0, sizeof(DeviceScalars));
     }
-    if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) {
+    if (shared) {  // a view: the set is reference-counted and outlives the handle
+      shared->refs.fetch_add(1);
+      p->shared_maps = shared;
+      p->d_sem_maps.View(shared->tiled.p, shared->tiled.n);
+      p->sem_h = shared->h; p->sem_w = shared->w; p->sem_weight = d.sem_weight;
+    } else if (d.sem_maps && d.sem_height > 0 && d.sem_width > 0 && d.num_images > 0) {
       const size_t n_map = (size_t)d.num_images * d.sem_height * d.sem_width;
       cudaError_t e = map_stage.Alloc(n_map);
       if (e == cudaSuccess) e = p->d_sem_maps.Alloc((size_t)d.num_images * MapTiledSize(d.sem_height, d.sem_width));
@@ -703,7 +772,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only) {
   }
   tm.Lap("histograms");
   GlobalStructure g;
-  Analyse(d, &g, pt_count.data(), img_count.data(), host_only);
+  Analyse(d, &g, pt_count.data(), img_count.data(), host_only, shared);
   tm.Lap("analyse");
   p->counts = g.counts;
   p->n_img = d.num_images; p->n_cam = d.num_cameras;

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstring>
 #include <mutex>
+#include <atomic>
 #include <vector>
 
 #include "common.cuh"
@@ -275,6 +276,7 @@ struct Problem {
   int64_t collectives = 0;
   // extension X1: per-image semantic maps (row-major float), sampled bilinearly at the projection
   DevBuf<float> d_sem_maps;  int sem_h = 0, sem_w = 0;  double sem_weight = 0.0;
+  struct MapSet* shared_maps = nullptr;     // d_sem_maps is a view into this reference-counted set (sba_create_with_maps)
   bool solved = false;
   bool linearized = false;
   bool cost_unreduced = false;              // multi-GPU: scalars->cost / fixed_cost are partial sums; Gradient(with_norms) carries them
@@ -297,7 +299,15 @@ struct Problem {
 };
 
 // problem.cu
-int BuildProblem(const sba_problem_desc* d, Problem** out, bool host_only);
+// label maps resident on one device across problems (sba_maps_create): tiled like Problem::d_sem_maps
+struct MapSet {
+  DevBuf<float> tiled;
+  int device = 0, n_img = 0, h = 0, w = 0;
+  std::atomic<int> refs{1};  // the caller's reference + one per live handle created over it
+};
+int BuildMapSet(int n_img, int h, int w, const float* maps, MapSet** out);
+void MapSetRelease(MapSet* m);
+int BuildProblem(const sba_problem_desc* d, Problem** out, bool host_only, MapSet* shared = nullptr);
 int FetchHostOrder(Problem* p);  // order.cu
 int BuildDeviceOrder(Problem* p, int p0, int64_t obs_base, int64_t n_obs_g, int n_pt_g, const int* d_raw_img,
                      const int* d_raw_pt, const double* d_raw_xy);

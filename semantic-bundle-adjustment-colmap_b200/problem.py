@@ -56,7 +56,7 @@ class FlatProblem:
         self._arena = arena
         return self
 
-    def desc(self, shard_rank=0, shard_count=1):
+    def desc(self, shard_rank=0, shard_count=1, with_maps=True):
         d = capi.ProblemDesc()
         d.num_images, d.num_cameras, d.num_points = len(self.image_camera), len(self.camera_model), len(self.points)
         d.num_observations = len(self.obs_image)
@@ -73,7 +73,9 @@ class FlatProblem:
         d.obs_image = capi.ptr(self.obs_image, capi._ip)
         d.obs_point = capi.ptr(self.obs_point, capi._ip)
         d.obs_xy = capi.ptr(self.obs_xy, capi._dp)
-        if self.sem_maps is not None:
+        if self.sem_maps is not None and not with_maps:
+            d.sem_weight = self.sem_weight  # the maps themselves are already on the device (ResidentMaps)
+        elif self.sem_maps is not None:
             d.sem_maps = capi.ptr(self.sem_maps, capi._fp)
             d.sem_height, d.sem_width = self.sem_maps.shape[1], self.sem_maps.shape[2]
             d.sem_weight = self.sem_weight
@@ -95,15 +97,46 @@ class FlatProblem:
         return pk, ok
 
 
-class Solver:
-    """One `sba_handle`: device-resident problem + LM solver."""
+class ResidentMaps:
+    """Label maps kept on the device across problems (`sba_maps_create`): the reference loads an image's map once and
+    every global bundle adjustment of the mapper reads the same maps (/root/reference/src/optim/bundle_adjustment.cc:361-372)."""
 
-    def __init__(self, problem, shard_rank=0, shard_count=1):
+    def __init__(self, sem_maps):
+        maps = np.ascontiguousarray(sem_maps, dtype=np.float32)
+        if maps.ndim != 3:
+            raise ValueError("sem_maps must be [num_images, height, width]")
+        self.lib = capi.load()
+        self._m = C.c_void_p()
+        self.shape = maps.shape
+        capi.check(self.lib.sba_maps_create(maps.shape[0], maps.shape[1], maps.shape[2], capi.ptr(maps, capi._fp), C.byref(self._m)))
+
+    def close(self):
+        if self._m:
+            self.lib.sba_maps_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Solver:
+    """One `sba_handle`: device-resident problem + LM solver.  `maps`: a ResidentMaps set to build the problem over
+    (the problem's own `sem_maps`, if any, are then not uploaded again; its `sem_weight` applies)."""
+
+    def __init__(self, problem, shard_rank=0, shard_count=1, maps=None):
         self.problem = problem
         self.lib = capi.load()
         self._h = C.c_void_p()
-        self._desc = problem.desc(shard_rank, shard_count)
-        capi.check(self.lib.sba_create(C.byref(self._desc), C.byref(self._h)))
+        self._desc = problem.desc(shard_rank, shard_count, with_maps=maps is None)
+        if maps is None:
+            capi.check(self.lib.sba_create(C.byref(self._desc), C.byref(self._h)))
+        else:
+            if not maps._m:
+                raise ValueError("the ResidentMaps set has been closed")
+            capi.check(self.lib.sba_create_with_maps(C.byref(self._desc), maps._m, C.byref(self._h)))
 
     def close(self):
         if self._h:

@@ -248,3 +248,43 @@ def test_semantic_row_implicit_products_and_robust_solve(sba, oracle, monkeypatc
     y_imp, y_blk = s.schur_product(x, use_blocks=False), s.schur_product(x, use_blocks=True)
     s.close()
     assert np.linalg.norm(y_imp - y_blk) <= 1e-11 * np.linalg.norm(y_blk)
+
+
+@pytest.mark.gpu
+def test_resident_maps_solve_is_bit_identical(sba):
+    """sba_maps_create + sba_create_with_maps (maps uploaded once, problems built over them) against sba_create with the
+    maps in the descriptor: the same bits, for two problems over one set, also after the caller's reference is gone."""
+    capi = sba.capi
+    prob = _scene(sba, model="SIMPLE_RADIAL", refine=True, n_cam=12, n_pt=1500, seed=8)
+    o = capi.default_solver_options()
+    o.max_num_iterations = 6
+    s = sba.Solver(prob)
+    ref = s.solve(o)
+    ref_params = s.parameters()
+    ref_eval = s.evaluate(want=("r", "sem"))
+    s.close()
+    maps = sba.ResidentMaps(prob.sem_maps)
+    a, b = sba.Solver(prob, maps=maps), sba.Solver(prob, maps=maps)
+    maps.close()  # the set lives on until the last handle over it is destroyed
+    for t in (a, b):
+        got = t.solve(o)
+        assert (got.final_cost, got.num_residuals, got.num_successful_steps) == (ref.final_cost, ref.num_residuals, ref.num_successful_steps)
+        assert all(np.array_equal(x, y) for x, y in zip(t.parameters(), ref_params))
+        ev = t.evaluate(want=("r", "sem"))
+        assert np.array_equal(ev["sem"], ref_eval["sem"]) and np.array_equal(ev["r"], ref_eval["r"])
+        t.close()
+    with pytest.raises(ValueError):
+        sba.Solver(prob, maps=maps)  # closed
+    # error behaviour of the entry point: a second set in the descriptor, a set of another size, a null set
+    maps = sba.ResidentMaps(prob.sem_maps)
+    h = C.c_void_p()
+    d = prob.desc()  # carries sem_maps
+    assert capi.load().sba_create_with_maps(C.byref(d), maps._m, C.byref(h)) == capi.ERR_INVALID_ARGUMENT and not h
+    assert b"sem_maps must be null" in capi.load().sba_last_error()
+    small = sba.ResidentMaps(prob.sem_maps[:5])
+    d = prob.desc(with_maps=False)
+    assert capi.load().sba_create_with_maps(C.byref(d), small._m, C.byref(h)) == capi.ERR_INVALID_ARGUMENT and not h
+    assert capi.load().sba_create_with_maps(C.byref(d), None, C.byref(h)) == capi.ERR_INVALID_ARGUMENT and not h
+    m0 = C.c_void_p()
+    assert capi.load().sba_maps_create(0, 4, 4, None, C.byref(m0)) == capi.ERR_INVALID_ARGUMENT and not m0
+    small.close(); maps.close()
