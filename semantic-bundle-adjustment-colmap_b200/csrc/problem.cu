@@ -440,6 +440,7 @@ static int Validate(const sba_problem_desc* d) {
 // (bundle_adjustment.cc:417-425, 480-530); counts follow Solver::Summary.
 struct GlobalStructure {
   std::vector<int> col_img, col_cam, k_cols, k_dim, t_dim, p_off_global, blk_off, blk_dim;
+  std::vector<uint8_t> pt_live;  // p_off_global >= 0, as bytes
   int n_cdim = 0, kmax = 0, n_pvar_global = 0, uniform_model = -1;
   bool shared_intrinsics = false;
   sba_summary counts;
@@ -504,13 +505,13 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt
                     bool count_active, const MapSet* shared = nullptr) {
   const int n_img = d.num_images, n_cam = d.num_cameras, n_pt = d.num_points;
   const int64_t n_obs = d.num_observations;
-  std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used(n_pt, 0);
+  std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used;
   std::vector<int> cam_img_count(n_cam, 0);
   const int NT = std::max(1, std::min(HostThreads(), (int)(n_obs / 16384) + 1));
   if (pt_count && img_count) {
-    for (int i = 0; i < n_img; ++i) img_used[i] = img_count[i] > 0;
-    for (int q = 0; q < n_pt; ++q) pt_used[q] = pt_count[q] > 0;
+    for (int i = 0; i < n_img; ++i) img_used[i] = img_count[i] > 0;  // (the points: one pass below, straight from pt_count)
   } else {
+    pt_used.assign(n_pt, 0);
     // every writer stores the same value 1 into a byte: the passes can share the mark arrays
     ParallelFor(NT, [&](int t) {
       int64_t kb, ke; Slice(n_obs, NT, t, &kb, &ke);
@@ -560,11 +561,21 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt
   }
   g->uniform_model = first_model < 0 ? -1 : first_model;
   g->n_cdim = off;
-  g->p_off_global.assign(n_pt, -1);
-  for (int p = 0; p < n_pt; ++p) {
-    if (!pt_used[p] || (d.point_constant && d.point_constant[p])) continue;
-    g->p_off_global[p] = g->n_pvar_global++;
-    s.num_parameter_blocks_reduced++; s.num_parameters_reduced += 3; s.num_effective_parameters_reduced += 3;
+  // one pass over the points (2 M at C5: every extra host pass is ~2 ms of sba_create): offsets of the variable ones and the
+  // byte mask the device's residual count reads
+  g->p_off_global.resize(n_pt);
+  g->pt_live.resize(std::max(1, n_pt));
+  {
+    const uint8_t* pc = d.point_constant;
+    const uint8_t* used = pt_used.empty() ? nullptr : pt_used.data();
+    int nv = 0;
+    for (int p = 0; p < n_pt; ++p) {
+      const bool var = (used ? used[p] != 0 : pt_count[p] > 0) && !(pc && pc[p]);
+      g->p_off_global[p] = var ? nv++ : -1;
+      g->pt_live[p] = var ? 1 : 0;
+    }
+    g->n_pvar_global = nv;
+    s.num_parameter_blocks_reduced += nv; s.num_parameters_reduced += 3 * nv; s.num_effective_parameters_reduced += 3 * nv;
   }
   const int nr = RowsOf(d, shared);
   s.num_residual_blocks = (int)n_obs; s.num_residuals = (int)(nr * n_obs);
@@ -805,38 +816,36 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   }
   p->n_pt = p1 - p0;
   p->pt_base = p0;
-  // one pass over the shard's points: CSR over points and the offsets of the variable ones
+  // one pass over the shard's points: CSR over points, the offsets of the variable ones, and the warp tiles (whole
+  // points packed into <= kTile observations)
   std::vector<int>& h_pt_ptr = p->h_pt_ptr;
   h_pt_ptr.resize(p->n_pt + 1);
   p->h_p_off.resize(p->n_pt);
   p->n_pvar = 0;
-  {
-    int acc = 0;
-    h_pt_ptr[0] = 0;
-    for (int q = 0; q < p->n_pt; ++q) {
-      acc += pt_count[p0 + q];
-      h_pt_ptr[q + 1] = acc;
-      p->h_p_off[q] = g.p_off_global[p0 + q] >= 0 ? p->n_pvar++ : -1;
-    }
-    p->n_obs = acc;
-  }
-  const int n_obs = p->n_obs;
-  tm.Lap("shard + point counts");
-
-  // ---- warp tiles: whole points packed into <= kTile observations ----
   std::vector<int> tile_start;
+  tile_start.reserve((size_t)(n_obs_g / kTile) * 2 + 16);
   {
-    int cur = 0, fill = 0;
+    int acc = 0, fill = 0, nv = 0;
+    const int* cnt = pt_count.data() + p0;
+    const int* go = g.p_off_global.data() + p0;
+    h_pt_ptr[0] = 0;
     tile_start.push_back(0);
     for (int q = 0; q < p->n_pt; ++q) {
-      const int len = h_pt_ptr[q + 1] - h_pt_ptr[q];
-      if (len == 0) continue;
-      if (fill > 0 && fill + len > kTile) { tile_start.push_back(cur); fill = 0; }
-      cur += len; fill += len;
-      if (fill >= kTile) { tile_start.push_back(cur); fill = 0; }
+      const int len = cnt[q];
+      p->h_p_off[q] = go[q] >= 0 ? nv++ : -1;
+      if (len) {
+        if (fill > 0 && fill + len > kTile) { tile_start.push_back(acc); fill = 0; }
+        acc += len; fill += len;
+        if (fill >= kTile) { tile_start.push_back(acc); fill = 0; }
+      }
+      h_pt_ptr[q + 1] = acc;
     }
-    if (tile_start.back() != cur) tile_start.push_back(cur);
+    if (tile_start.back() != acc) tile_start.push_back(acc);
+    p->n_obs = acc;
+    p->n_pvar = nv;
   }
+  const int n_obs = p->n_obs;
+  tm.Lap("shard + point counts + tiles");
   p->n_tiles = (int)tile_start.size() - 1;
 
   // ---- image-major chunks of <= 256: sizes from a counting pass by image over the shard's observations ----
@@ -873,16 +882,16 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   std::vector<int> col_blk(std::max(1, p->n_cdim), 0);
   for (int b = 0; b < p->n_blk; ++b)
     for (int j = 0; j < p->h_blk_dim[b]; ++j) col_blk[p->h_blk_off[b] + j] = b;
-  tm.Lap("tiles + chunks");
+  tm.Lap("chunks");
   *out = p;
   if (host_only) return SBA_OK;
 
   // ---- device ----
   cudaStream_t st = p->stream;
   {  // residual blocks of the reduced program (Summary::num_residuals_reduced): counted on the device
-    std::vector<uint8_t> img_live((size_t)std::max(1, p->n_img), 0), pt_live((size_t)std::max(1, n_pt_g), 0);
+    std::vector<uint8_t> img_live((size_t)std::max(1, p->n_img), 0);
+    const std::vector<uint8_t>& pt_live = g.pt_live;
     for (int i = 0; i < p->n_img; ++i) img_live[i] = (g.col_img[6 * (size_t)i] >= 0 || g.k_dim[d.image_camera[i]] > 0) ? 1 : 0;
-    for (int q = 0; q < n_pt_g; ++q) pt_live[q] = g.p_off_global[q] >= 0 ? 1 : 0;
     DevBuf<uint8_t> d_il, d_pl;
     DevBuf<unsigned long long> d_n;
     UP(d_il.Upload(img_live, st)); UP(d_pl.Upload(pt_live, st)); UP(d_n.Alloc(1)); UP(d_n.Zero(st));
