@@ -127,8 +127,7 @@ int DecideBlockSchur(Problem* p) {
   const int64_t cells = (int64_t)n_img * n_img;
   if (cells > 0x7fffffffLL || (p->comm && cells > (1ll << 27))) return SBA_OK;
   {  // the pair list grows with the square of the track length: bound it before building it
-    double pairs = 0.0;
-    for (int q = 0; q < p->n_pt; ++q) { const double k = p->h_pt_ptr[q + 1] - p->h_pt_ptr[q]; pairs += 0.5 * k * (k - 1.0); }
+    const double pairs = p->pair_estimate;  // (from the point pass of sba_create)
     size_t free_b = 0, total_b = 0;
     SBA_CUDA(cudaMemGetInfo(&free_b, &total_b));
     double too_many = (pairs > 1.5e9 || pairs * 40.0 > 0.25 * (double)free_b) ? 1.0 : 0.0;  // 32-bit pair offsets; 40 B per pair while sorting

@@ -439,8 +439,13 @@ static int Validate(const sba_problem_desc* d) {
 // from the parameter blocks / manifolds the reference sets up
 // (bundle_adjustment.cc:417-425, 480-530); counts follow Solver::Summary.
 struct GlobalStructure {
-  std::vector<int> col_img, col_cam, k_cols, k_dim, t_dim, p_off_global, blk_off, blk_dim;
-  std::vector<uint8_t> pt_live;  // p_off_global >= 0, as bytes
+  std::vector<int> col_img, col_cam, k_cols, k_dim, t_dim, blk_off, blk_dim;
+  // per point of the whole problem: offset among the variable points (or -1) and the same as a byte mask; in the
+  // caller's buffers (the page-locked scratch of sba_create) or in the two vectors
+  int* p_off = nullptr;
+  uint8_t* pt_live = nullptr;
+  std::vector<int> p_off_store;
+  std::vector<uint8_t> pt_live_store;
   int n_cdim = 0, kmax = 0, n_pvar_global = 0, uniform_model = -1;
   bool shared_intrinsics = false;
   sba_summary counts;
@@ -502,7 +507,7 @@ static int RowsOf(const sba_problem_desc& d, const MapSet* shared = nullptr) {
 // point (sba_problem_counts) counts here.  count_active: also count the residual blocks of the reduced program on the
 // host (a pass over the observation list); with a device that count is made there too (CountActiveOnDevice).
 static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt_count, const int* img_count,
-                    bool count_active, const MapSet* shared = nullptr) {
+                    bool count_active, const MapSet* shared = nullptr, int* p_off_out = nullptr, uint8_t* pt_live_out = nullptr) {
   const int n_img = d.num_images, n_cam = d.num_cameras, n_pt = d.num_points;
   const int64_t n_obs = d.num_observations;
   std::vector<uint8_t> img_used(n_img, 0), cam_used(n_cam, 0), pt_used;
@@ -563,15 +568,18 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt
   g->n_cdim = off;
   // one pass over the points (2 M at C5: every extra host pass is ~2 ms of sba_create): offsets of the variable ones and the
   // byte mask the device's residual count reads
-  g->p_off_global.resize(n_pt);
-  g->pt_live.resize(std::max(1, n_pt));
+  if (p_off_out && pt_live_out) { g->p_off = p_off_out; g->pt_live = pt_live_out; }
+  else {
+    g->p_off_store.resize(std::max(1, n_pt)); g->pt_live_store.resize(std::max(1, n_pt));
+    g->p_off = g->p_off_store.data(); g->pt_live = g->pt_live_store.data();
+  }
   {
     const uint8_t* pc = d.point_constant;
     const uint8_t* used = pt_used.empty() ? nullptr : pt_used.data();
     int nv = 0;
     for (int p = 0; p < n_pt; ++p) {
       const bool var = (used ? used[p] != 0 : pt_count[p] > 0) && !(pc && pc[p]);
-      g->p_off_global[p] = var ? nv++ : -1;
+      g->p_off[p] = var ? nv++ : -1;
       g->pt_live[p] = var ? 1 : 0;
     }
     g->n_pvar_global = nv;
@@ -585,7 +593,7 @@ static void Analyse(const sba_problem_desc& d, GlobalStructure* g, const int* pt
     int64_t kb, ke, na = 0; Slice(n_obs, NT, t, &kb, &ke);
     for (int64_t k = kb; k < ke; ++k) {
       const int i = d.obs_image[k], c = d.image_camera[i], p = d.obs_point[k];
-      na += g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off_global[p] >= 0;
+      na += g->col_img[6 * (size_t)i] >= 0 || g->k_dim[c] > 0 || g->p_off[p] >= 0;
     }
     n_act[t] = na;
   });
@@ -766,24 +774,41 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   // counts per point and per image of the whole problem: device histograms over the raw copy (host loops without a device)
   const int n_pt_g = d.num_points;
   const int64_t n_obs_g = d.num_observations;
-  std::vector<int> pt_count((size_t)std::max(1, n_pt_g), 0), img_count((size_t)std::max(1, d.num_images), 0);
+  // Per-point host arrays of the whole problem (counts, offsets, live mask) live in a page-locked scratch block kept per
+  // process; the CSR over points, the offsets and the tiles are written straight into the arena's staging block.  The
+  // stage mutex is held from here until the arena upload has left the block (one create at a time per process through
+  // this stretch).
+  PinnedStage& stg = PinnedStage::Get();
+  std::unique_lock<std::mutex> stage_lock(stg.mu, std::defer_lock);
+  const size_t npg = (size_t)std::max(1, n_pt_g), npg4 = (npg * sizeof(int) + 255) / 256 * 256;
+  std::vector<int> v_cnt, img_count((size_t)std::max(1, d.num_images), 0);
+  int* pt_count = nullptr;
+  int* p_off_scratch = nullptr;
+  uint8_t* live_scratch = nullptr;
   DevBuf<int> d_pt_count, d_img_count;
   if (!host_only) {
+    stage_lock.lock();
+    if (!stg.ReserveScratch(2 * npg4 + npg + 256)) { SetError(SBA_ERR_CUDA, "page-locked scratch for sba_create: out of memory"); maps.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA; }
+    pt_count = reinterpret_cast<int*>(stg.q);
+    p_off_scratch = reinterpret_cast<int*>(stg.q + npg4);
+    live_scratch = reinterpret_cast<uint8_t*>(stg.q + 2 * npg4);
     if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
-    UP(d_pt_count.Alloc(pt_count.size())); UP(d_img_count.Alloc(img_count.size()));
+    UP(d_pt_count.Alloc(npg)); UP(d_img_count.Alloc(img_count.size()));
     UP(d_pt_count.Zero(p->stream));
     if (n_obs_g > 0) hist_point_kernel<<<DivUp(n_obs_g, 256), 256, 0, p->stream>>>(n_obs_g, raw_pt.p, d_pt_count.p);
     UP(DeviceHistogramImages(p->stream, n_obs_g, raw_img.p, raw_pt.p, 0, n_pt_g, d.num_images, d_img_count.p, p->n_sm));
-    UP(cudaMemcpyAsync(pt_count.data(), d_pt_count.p, pt_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+    UP(cudaMemcpyAsync(pt_count, d_pt_count.p, npg * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
     UP(cudaMemcpyAsync(img_count.data(), d_img_count.p, img_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
     UP(cudaStreamSynchronize(p->stream));
     p->launches += 2;
   } else {
+    v_cnt.assign(npg, 0);
+    pt_count = v_cnt.data();
     for (int64_t k = 0; k < n_obs_g; ++k) { pt_count[d.obs_point[k]]++; img_count[d.obs_image[k]]++; }
   }
   tm.Lap("histograms");
   GlobalStructure g;
-  Analyse(d, &g, pt_count.data(), img_count.data(), host_only, shared);
+  Analyse(d, &g, pt_count, img_count.data(), host_only, shared, p_off_scratch, live_scratch);
   tm.Lap("analyse");
   p->counts = g.counts;
   p->n_img = d.num_images; p->n_cam = d.num_cameras;
@@ -818,35 +843,51 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   p->pt_base = p0;
   // one pass over the shard's points: CSR over points, the offsets of the variable ones, and the warp tiles (whole
   // points packed into <= kTile observations)
-  std::vector<int>& h_pt_ptr = p->h_pt_ptr;
-  h_pt_ptr.resize(p->n_pt + 1);
-  p->h_p_off.resize(p->n_pt);
+  DeviceArena& A = p->arena;
+  DeviceArena::Slot s_pt_ptr{}, s_p_off{}, s_tile{};
+  std::vector<int> v_pt_ptr, v_p_off, v_tile;  // host-only: no staging block
+  const size_t tile_bound = (size_t)(n_obs_g / kTile) * 2 + 16;  // two consecutive tiles hold >= kTile observations
+  int *h_pt_ptr, *h_p_off, *tile_start;
+  if (!host_only) {
+    if (!stg.Reserve(((size_t)p->n_pt * 2 + 1 + tile_bound) * sizeof(int) + 4 * 256 + (1u << 20))) {
+      SetError(SBA_ERR_CUDA, "page-locked staging block for sba_create: out of memory");
+      maps.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA;
+    }
+    h_pt_ptr = A.Claim<int>((size_t)p->n_pt + 1, &s_pt_ptr);
+    h_p_off = A.Claim<int>((size_t)p->n_pt, &s_p_off);
+    tile_start = A.Claim<int>(tile_bound, &s_tile);
+  } else {
+    v_pt_ptr.resize((size_t)p->n_pt + 1); v_p_off.resize(std::max(1, p->n_pt)); v_tile.resize(tile_bound);
+    h_pt_ptr = v_pt_ptr.data(); h_p_off = v_p_off.data(); tile_start = v_tile.data();
+  }
   p->n_pvar = 0;
-  std::vector<int> tile_start;
-  tile_start.reserve((size_t)(n_obs_g / kTile) * 2 + 16);
   {
-    int acc = 0, fill = 0, nv = 0;
-    const int* cnt = pt_count.data() + p0;
-    const int* go = g.p_off_global.data() + p0;
+    int acc = 0, fill = 0, nv = 0, nt = 0;
+    double pairs = 0.0;
+    const int* cnt = pt_count + p0;
+    const int* go = g.p_off + p0;
     h_pt_ptr[0] = 0;
-    tile_start.push_back(0);
+    tile_start[nt++] = 0;
     for (int q = 0; q < p->n_pt; ++q) {
       const int len = cnt[q];
-      p->h_p_off[q] = go[q] >= 0 ? nv++ : -1;
+      h_p_off[q] = go[q] >= 0 ? nv++ : -1;
       if (len) {
-        if (fill > 0 && fill + len > kTile) { tile_start.push_back(acc); fill = 0; }
+        if (fill > 0 && fill + len > kTile) { tile_start[nt++] = acc; fill = 0; }
         acc += len; fill += len;
-        if (fill >= kTile) { tile_start.push_back(acc); fill = 0; }
+        if (fill >= kTile) { tile_start[nt++] = acc; fill = 0; }
+        pairs += 0.5 * (double)len * (double)(len - 1);
       }
       h_pt_ptr[q + 1] = acc;
     }
-    if (tile_start.back() != acc) tile_start.push_back(acc);
+    if (tile_start[nt - 1] != acc) tile_start[nt++] = acc;
     p->n_obs = acc;
     p->n_pvar = nv;
+    p->n_tiles = nt - 1;
+    p->pair_estimate = pairs;
+    if (!host_only) A.ShrinkLast<int>(&s_tile, (size_t)nt);
   }
   const int n_obs = p->n_obs;
   tm.Lap("shard + point counts + tiles");
-  p->n_tiles = (int)tile_start.size() - 1;
 
   // ---- image-major chunks of <= 256: sizes from a counting pass by image over the shard's observations ----
   std::vector<int>& img_ptr = p->h_img_ptr;
@@ -890,11 +931,11 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   cudaStream_t st = p->stream;
   {  // residual blocks of the reduced program (Summary::num_residuals_reduced): counted on the device
     std::vector<uint8_t> img_live((size_t)std::max(1, p->n_img), 0);
-    const std::vector<uint8_t>& pt_live = g.pt_live;
     for (int i = 0; i < p->n_img; ++i) img_live[i] = (g.col_img[6 * (size_t)i] >= 0 || g.k_dim[d.image_camera[i]] > 0) ? 1 : 0;
     DevBuf<uint8_t> d_il, d_pl;
     DevBuf<unsigned long long> d_n;
-    UP(d_il.Upload(img_live, st)); UP(d_pl.Upload(pt_live, st)); UP(d_n.Alloc(1)); UP(d_n.Zero(st));
+    UP(d_il.Upload(img_live, st)); UP(d_pl.Alloc(npg)); UP(d_n.Alloc(1)); UP(d_n.Zero(st));
+    UP(cudaMemcpyAsync(d_pl.p, g.pt_live, npg, cudaMemcpyHostToDevice, st));  // (from the page-locked scratch)
     if (n_obs_g > 0) {
       const int blocks = (int)std::min<int64_t>((n_obs_g + 255) / 256, (int64_t)p->n_sm * 8);
       count_active_kernel<<<blocks, 256, 0, st>>>(n_obs_g, raw_img.p, raw_pt.p, d_il.p, d_pl.p, d_n.p);
@@ -938,15 +979,15 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
       mk[12 * (size_t)c + j] = p->h_col_cam[12 * (size_t)c + j] >= 0 ? 1.0 : 0.0;
       pack[c] |= (unsigned long long)(p->h_k_cols[12 * (size_t)c + j] & 15) << (4 * j);
     }
-  DeviceArena& A = p->arena;
   const auto s_img_cam = A.Push(p->h_img_cam), s_model = A.Push(p->h_model), s_col_img = A.Push(p->h_col_img),
              s_col_cam = A.Push(p->h_col_cam), s_k_cols = A.Push(p->h_k_cols), s_k_slot = A.Push(p->h_k_slot),
-             s_k_dim = A.Push(p->h_k_dim), s_p_off = A.Push(p->h_p_off), s_pose_const = A.Push(p->h_pose_const),
-             s_tile = A.Push(tile_start), s_chunk_start = A.Push(chunk_start), s_chunk_img = A.Push(chunk_img),
+             s_k_dim = A.Push(p->h_k_dim), s_pose_const = A.Push(p->h_pose_const),
+             s_chunk_start = A.Push(chunk_start), s_chunk_img = A.Push(chunk_img),
              s_img_chunk = A.Push(img_chunk_ptr), s_cam_img_ptr = A.Push(cam_img_ptr), s_cam_img_list = A.Push(cam_img_list),
-             s_pt_ptr = A.Push(h_pt_ptr), s_blk_off = A.Push(p->h_blk_off), s_blk_dim = A.Push(p->h_blk_dim),
+             s_blk_off = A.Push(p->h_blk_off), s_blk_dim = A.Push(p->h_blk_dim),
              s_col_blk = A.Push(col_blk), s_mi = A.Push(mi), s_mk = A.Push(mk), s_pack = A.Push(pack);
-  UP(A.Upload(st));
+  UP(A.Upload(st, true));  // (the per-point arrays were written in place; the stage mutex is ours since the histograms)
+  stage_lock.unlock();
   A.Bind(&p->d_img_cam, s_img_cam); A.Bind(&p->d_model, s_model); A.Bind(&p->d_col_img, s_col_img);
   A.Bind(&p->d_col_cam, s_col_cam); A.Bind(&p->d_k_cols, s_k_cols); A.Bind(&p->d_k_slot, s_k_slot);
   A.Bind(&p->d_k_dim, s_k_dim); A.Bind(&p->d_p_off, s_p_off); A.Bind(&p->d_pose_const, s_pose_const);

@@ -64,22 +64,26 @@ struct DevBuf {
 // buffer kept per process (grown on demand, guarded by a mutex for the duration of one create): arrays are copied into it
 // once and the upload is one DMA -- a growing std::vector re-allocated, zero-filled and page-faulted 12 MB per create at C4.
 struct PinnedStage {
-  char* p = nullptr; size_t cap = 0;
+  char* p = nullptr; size_t cap = 0;   // staging block of the arena upload
+  char* q = nullptr; size_t qcap = 0;  // scratch of one create: per-point counts, offsets and live mask of the whole problem
   std::mutex mu;
   static PinnedStage& Get() { static PinnedStage s; return s; }
-  bool Reserve(size_t bytes) {
-    if (bytes <= cap) return true;
-    if (p) cudaFreeHost(p);
-    p = nullptr; cap = 0;
+  static bool Grow(char** blk, size_t* have, size_t bytes, size_t keep) {
+    if (bytes <= *have) return true;
     const size_t want = std::max<size_t>(bytes + bytes / 2, 1u << 20);
-    if (cudaMallocHost((void**)&p, want) != cudaSuccess) { cudaGetLastError(); p = nullptr; return false; }
-    cap = want;
+    char* nb = nullptr;
+    if (cudaMallocHost((void**)&nb, want) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (*blk && keep) std::memcpy(nb, *blk, std::min(keep, *have));
+    if (*blk) cudaFreeHost(*blk);
+    *blk = nb; *have = want;
     return true;
   }
+  bool Reserve(size_t bytes, size_t keep = 0) { return Grow(&p, &cap, bytes, keep); }
+  bool ReserveScratch(size_t bytes) { return Grow(&q, &qcap, bytes, 0); }
 };
 struct DeviceArena {
   DevBuf<char> dev;
-  struct Slot { size_t off, bytes; const void* src; };
+  struct Slot { size_t off, bytes; const void* src; };  // src == nullptr: written in place (Claim)
   std::vector<Slot> slots;
   size_t size = 0;
   template <typename T>
@@ -89,14 +93,33 @@ struct DeviceArena {
     slots.push_back(Slot{off, bytes, v.data()});
     return slots.back();
   }
-  cudaError_t Upload(cudaStream_t s) {
+  // An array written straight into the staging block: no host vector (12 MB of them were allocated, zero-filled and
+  // page-faulted per create at C4) and no copy at Upload.  The caller holds PinnedStage::mu from the first Claim until
+  // Upload(s, true) returns and has Reserved the staging block for every Claim it makes.
+  template <typename T>
+  T* Claim(size_t count, Slot* sl) {
+    const size_t off = (size + 255) / 256 * 256, bytes = count * sizeof(T);
+    size = off + std::max<size_t>(bytes, 1);
+    slots.push_back(Slot{off, bytes, nullptr});
+    *sl = slots.back();
+    return reinterpret_cast<T*>(PinnedStage::Get().p + off);
+  }
+  template <typename T>
+  void ShrinkLast(Slot* sl, size_t count) {  // the most recent Claim turned out smaller than its bound
+    Slot& b = slots.back();
+    b.bytes = count * sizeof(T);
+    size = b.off + std::max<size_t>(b.bytes, 1);
+    *sl = b;
+  }
+  cudaError_t Upload(cudaStream_t s, bool locked = false) {
     cudaError_t e = dev.Alloc(std::max<size_t>(size, 1));
     if (e != cudaSuccess) return e;
     PinnedStage& st = PinnedStage::Get();
-    std::lock_guard<std::mutex> lk(st.mu);
-    if (!st.Reserve(size)) return cudaErrorMemoryAllocation;
+    std::unique_lock<std::mutex> lk(st.mu, std::defer_lock);
+    if (!locked) lk.lock();
+    if (!st.Reserve(size, locked ? size : 0)) return cudaErrorMemoryAllocation;  // (growing keeps what was written in place)
     for (const Slot& sl : slots)
-      if (sl.bytes) std::memcpy(st.p + sl.off, sl.src, sl.bytes);
+      if (sl.bytes && sl.src) std::memcpy(st.p + sl.off, sl.src, sl.bytes);
     e = cudaMemcpyAsync(dev.p, st.p, size, cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return e;
     e = cudaStreamSynchronize(s);  // the staging buffer is shared: the copy has left it before the lock is released
@@ -180,10 +203,11 @@ struct Problem {
   bool shared_intrinsics = false;  // some camera with free intrinsics is used by >1 image
 
   // ---- host copies of structure (small) ----
-  std::vector<int> h_img_cam, h_model, h_col_img, h_col_cam, h_k_cols, h_k_slot, h_k_dim, h_p_off;
+  std::vector<int> h_img_cam, h_model, h_col_img, h_col_cam, h_k_cols, h_k_slot, h_k_dim;
   std::vector<int> h_blk_off, h_blk_dim;       // SCHUR_JACOBI parameter blocks (compact cols)
   std::vector<int> h_obs_img, h_obs_pt;        // local, point-sorted
-  std::vector<int> h_pt_ptr, h_img_ptr, h_cam_order;  // CSR over points; image-major list of local observation ids
+  std::vector<int> h_img_ptr, h_cam_order;  // image-major list of local observation ids
+  double pair_estimate = 0.0;               // sum over points of k (k - 1) / 2: the size of the pair list (bsr.cu)
   std::vector<int64_t> h_local2ref;            // local point-sorted position -> reference residual index
   int pt_base = 0;                             // local point q is global point pt_base + q (shards are contiguous ranges)
   std::vector<uint8_t> h_pose_const;
