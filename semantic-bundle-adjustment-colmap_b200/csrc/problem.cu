@@ -397,7 +397,10 @@ ChunkView Problem::Chunks() const {
   return c;
 }
 
-static int Validate(const sba_problem_desc* d) {
+// check_observations = false: the caller checks the index ranges of the observation list on the device (sba_create: a
+// multi-threaded host pass over obs_image / obs_point leaves their cache lines spread over the cores' private caches,
+// and the DMA that follows then reads them at 10-15 GB/s instead of 55 -- 3.4 ms of a 12.9 ms create at C4)
+static int Validate(const sba_problem_desc* d, bool check_observations = true) {
   if (!d) { SetError(SBA_ERR_INVALID_ARGUMENT, "null problem description"); return SBA_ERR_INVALID_ARGUMENT; }
   if (d->num_images < 0 || d->num_cameras < 0 || d->num_points < 0 || d->num_observations < 0 ||
       d->num_observations > 2000000000LL) {
@@ -416,7 +419,7 @@ static int Validate(const sba_problem_desc* d) {
     if (d->image_camera[i] < 0 || d->image_camera[i] >= d->num_cameras) {
       SetError(SBA_ERR_INVALID_ARGUMENT, "image_camera out of range"); return SBA_ERR_INVALID_ARGUMENT;
     }
-  {
+  if (check_observations) {
     const int64_t n = d->num_observations;
     const int NT = std::max(1, std::min(HostThreads(), (int)(n / 16384) + 1));
     std::atomic<int> bad(0);
@@ -454,21 +457,28 @@ struct GlobalStructure {
 // ---- set-up passes over the observation list, made on the device from the raw copy of the caller's arrays ----
 // (at C4 the three host passes they replace -- usage marks, counts per point, counts per image -- were 28 of the 38 ms
 //  of sba_create)
-__global__ void __launch_bounds__(256) hist_point_kernel(int64_t n, const int* __restrict__ pt, int* __restrict__ cnt) {
+// (both histogram kernels also validate the index ranges: *bad becomes 1, nothing is counted out of bounds)
+__global__ void __launch_bounds__(256) hist_point_kernel(int64_t n, const int* __restrict__ pt, int n_pt, int* __restrict__ cnt,
+                                                         int* __restrict__ bad) {
   const int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (k < n) atomicAdd(cnt + pt[k], 1);
+  if (k >= n) return;
+  const int q = pt[k];
+  if ((unsigned)q < (unsigned)n_pt) atomicAdd(cnt + q, 1);
+  else *bad = 1;
 }
 // per-image counts of the observations whose point lies in [p0, p1); a CTA counts into shared memory first when the
 // image table fits (n_img <= 8192), so the global atomics are one per image per CTA
 __global__ void __launch_bounds__(256) hist_image_kernel(int64_t n, const int* __restrict__ img, const int* __restrict__ pt,
-                                                         int p0, int p1, int n_img, int* __restrict__ cnt) {
+                                                         int p0, int p1, int n_img, int* __restrict__ cnt, int* __restrict__ bad) {
   extern __shared__ int sh[];
   const bool use_sh = n_img <= 8192;
   if (use_sh) { for (int i = threadIdx.x; i < n_img; i += 256) sh[i] = 0; __syncthreads(); }
   for (int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x; k < n; k += (int64_t)gridDim.x * 256) {
     const int q = pt[k];
+    const int i = img[k];
+    if ((unsigned)i >= (unsigned)n_img) { if (bad) *bad = 1; continue; }
     if (q < p0 || q >= p1) continue;
-    if (use_sh) atomicAdd(sh + img[k], 1); else atomicAdd(cnt + img[k], 1);
+    if (use_sh) atomicAdd(sh + i, 1); else atomicAdd(cnt + i, 1);
   }
   if (use_sh) {
     __syncthreads();
@@ -488,11 +498,11 @@ __global__ void __launch_bounds__(256) count_active_kernel(int64_t n, const int*
 }
 
 static cudaError_t DeviceHistogramImages(cudaStream_t st, int64_t n, const int* d_img, const int* d_pt, int p0, int p1,
-                                         int n_img, int* d_cnt, int n_sm) {
+                                         int n_img, int* d_cnt, int n_sm, int* d_bad = nullptr) {
   cudaError_t e = cudaMemsetAsync(d_cnt, 0, (size_t)std::max(1, n_img) * sizeof(int), st);
   if (e != cudaSuccess || n == 0) return e;
   const int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)n_sm * 8);
-  hist_image_kernel<<<blocks, 256, n_img <= 8192 ? (size_t)n_img * sizeof(int) : 0, st>>>(n, d_img, d_pt, p0, p1, n_img, d_cnt);
+  hist_image_kernel<<<blocks, 256, n_img <= 8192 ? (size_t)n_img * sizeof(int) : 0, st>>>(n, d_img, d_pt, p0, p1, n_img, d_cnt, d_bad);
   return cudaGetLastError();
 }
 
@@ -698,7 +708,7 @@ int BuildMapSet(int n_img, int h, int w, const float* maps, MapSet** out) {
 
 int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapSet* shared) {
   HostTimer tm("create");
-  int rc = Validate(dp);
+  int rc = Validate(dp, host_only);  // with a device the observation indices are checked there (histogram kernels)
   if (rc) return rc;
   if (shared) {  // label maps already on the device (sba_maps_create): the descriptor must not carry a second set
     int dev = -1;
@@ -744,7 +754,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
         // the caller's observation arrays go up as they are; the device sorts them (order.cu)
         e = UploadLarge(raw_pt.p, d.obs_point, no * sizeof(int), p->stream);
         if (e == cudaSuccess) e = UploadLarge(raw_img.p, d.obs_image, no * sizeof(int), p->stream);
-        if (e == cudaSuccess) e = UploadLarge(raw_xy.p, d.obs_xy, 2 * no * sizeof(double), p->stream);
+        // (obs_xy -- two thirds of the bytes -- follows the histogram kernels below: its DMA runs under the host's point passes)
       }
       if (e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string("observation upload: ") + cudaGetErrorString(e)); delete p; return SBA_ERR_CUDA; }
       std::memset(p->h_scalars, 0, sizeof(DeviceScalars));
@@ -788,19 +798,41 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   DevBuf<int> d_pt_count, d_img_count;
   if (!host_only) {
     stage_lock.lock();
-    if (!stg.ReserveScratch(2 * npg4 + npg + 256)) { SetError(SBA_ERR_CUDA, "page-locked scratch for sba_create: out of memory"); maps.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA; }
+    if (!stg.ReserveScratch(2 * npg4 + npg + 1024)) { SetError(SBA_ERR_CUDA, "page-locked scratch for sba_create: out of memory"); maps.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA; }
     pt_count = reinterpret_cast<int*>(stg.q);
     p_off_scratch = reinterpret_cast<int*>(stg.q + npg4);
     live_scratch = reinterpret_cast<uint8_t*>(stg.q + 2 * npg4);
     if (cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device) != cudaSuccess || p->n_sm <= 0) p->n_sm = 148;
-    UP(d_pt_count.Alloc(npg)); UP(d_img_count.Alloc(img_count.size()));
-    UP(d_pt_count.Zero(p->stream));
-    if (n_obs_g > 0) hist_point_kernel<<<DivUp(n_obs_g, 256), 256, 0, p->stream>>>(n_obs_g, raw_pt.p, d_pt_count.p);
-    UP(DeviceHistogramImages(p->stream, n_obs_g, raw_img.p, raw_pt.p, 0, n_pt_g, d.num_images, d_img_count.p, p->n_sm));
+    if (tm.on) { UP(cudaStreamSynchronize(p->stream)); tm.Lap("(timing only) observation upload done"); }
+    DevBuf<int> d_bad;
+    UP(d_pt_count.Alloc(npg)); UP(d_img_count.Alloc(img_count.size())); UP(d_bad.Alloc(1));
+    UP(d_pt_count.Zero(p->stream)); UP(d_bad.Zero(p->stream));
+    if (n_obs_g > 0) hist_point_kernel<<<DivUp(n_obs_g, 256), 256, 0, p->stream>>>(n_obs_g, raw_pt.p, n_pt_g, d_pt_count.p, d_bad.p);
+    UP(DeviceHistogramImages(p->stream, n_obs_g, raw_img.p, raw_pt.p, 0, n_pt_g, d.num_images, d_img_count.p, p->n_sm, d_bad.p));
+    int* h_bad = reinterpret_cast<int*>(stg.q + 2 * npg4 + (npg + 255) / 256 * 256);
+    *h_bad = 0;
+    UP(cudaMemcpyAsync(h_bad, d_bad.p, sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+    if (tm.on) { UP(cudaStreamSynchronize(p->stream)); tm.Lap("(timing only) histogram kernels done"); }
     UP(cudaMemcpyAsync(pt_count, d_pt_count.p, npg * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
     UP(cudaMemcpyAsync(img_count.data(), d_img_count.p, img_count.size() * sizeof(int), cudaMemcpyDeviceToHost, p->stream));
-    UP(cudaStreamSynchronize(p->stream));
+    {
+      cudaEvent_t counted = nullptr;
+      UP(cudaEventCreateWithFlags(&counted, cudaEventDisableTiming));
+      cudaError_t e = cudaEventRecord(counted, p->stream);
+      if (e == cudaSuccess && n_obs_g > 0)
+        e = UploadLarge(raw_xy.p, d.obs_xy, 2 * (size_t)n_obs_g * sizeof(double), p->stream);
+      if (e == cudaSuccess) e = cudaEventSynchronize(counted);  // the counts are on the host; obs_xy is still on its way
+      cudaEventDestroy(counted);
+      UP(e);
+    }
     p->launches += 2;
+    if (*h_bad) {
+      cudaStreamSynchronize(p->stream);
+      SetError(SBA_ERR_INVALID_ARGUMENT, "observation index out of range");
+      maps.Join(); cudaStreamSynchronize(CopyStream());
+      delete p;
+      return SBA_ERR_INVALID_ARGUMENT;
+    }
   } else {
     v_cnt.assign(npg, 0);
     pt_count = v_cnt.data();
@@ -868,15 +900,23 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
     const int* go = g.p_off + p0;
     h_pt_ptr[0] = 0;
     tile_start[nt++] = 0;
+    // (branch-free: the boundary is stored every time and kept only when a tile closes -- the three data-dependent
+    //  branches of the plain form mispredict on every other point, 2.9 ms for 1 M points)
     for (int q = 0; q < p->n_pt; ++q) {
       const int len = cnt[q];
-      h_p_off[q] = go[q] >= 0 ? nv++ : -1;
-      if (len) {
-        if (fill > 0 && fill + len > kTile) { tile_start[nt++] = acc; fill = 0; }
-        acc += len; fill += len;
-        if (fill >= kTile) { tile_start[nt++] = acc; fill = 0; }
-        pairs += 0.5 * (double)len * (double)(len - 1);
-      }
+      const int var = go[q] >= 0;
+      h_p_off[q] = var ? nv : -1;
+      nv += var;
+      const int close_before = (fill > 0) & (fill + len > kTile);  // (len == 0 never closes: fill < kTile here)
+      tile_start[nt] = acc;
+      nt += close_before;
+      fill = close_before ? 0 : fill;
+      acc += len; fill += len;
+      const int close_after = fill >= kTile;
+      tile_start[nt] = acc;
+      nt += close_after;
+      fill = close_after ? 0 : fill;
+      pairs += 0.5 * (double)len * (double)(len - 1);
       h_pt_ptr[q + 1] = acc;
     }
     if (tile_start[nt - 1] != acc) tile_start[nt++] = acc;

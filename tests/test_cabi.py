@@ -156,3 +156,21 @@ def test_world_size_2_gloo_sharded_reduction(sba, oracle, tmp_path):
     outs = [p.communicate(timeout=300)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+@pytest.mark.gpu
+def test_observation_indices_are_checked_on_the_device(sba):
+    """sba_create leaves the range check of obs_image / obs_point to its histogram kernels (no host pass over the
+    observation list): out-of-range and negative indices are refused with the same error, nothing is built."""
+    prob, _ = sba.scene.make_scene(n_cam=6, n_pt=400, mean_track=4.0)
+    for field, value in (("obs_point", len(prob.points)), ("obs_point", -1), ("obs_image", len(prob.image_camera)), ("obs_image", -7)):
+        arrays = {k: getattr(prob, k).copy() for k in ("obs_image", "obs_point")}
+        arrays[field][len(arrays[field]) // 2] = value
+        bad = sba.FlatProblem(prob.image_qvec, prob.image_tvec, prob.image_camera, prob.camera_model, prob.camera_params,
+                              prob.points, arrays["obs_image"], arrays["obs_point"], prob.obs_xy)
+        with pytest.raises(sba.capi.SbaError) as e:
+            sba.Solver(bad)
+        assert e.value.code == sba.capi.ERR_INVALID_ARGUMENT and "out of range" in str(e.value)
+    s = sba.Solver(prob)  # and the library is still usable afterwards
+    assert s.solve().final_cost > 0
+    s.close()
