@@ -479,7 +479,7 @@ def run_b200(args, m):
                                       "ok": bool(rel <= 1e-6)}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # bounded sample: the same scene, the first CPU_ITERS LM iterations (the metric is per observation x iteration)
-        cpu_iters = LM_ITERS if n_obs < 1000000 else 2
+        cpu_iters = LM_ITERS if n_obs < 6000000 else 2  # C4: the whole solve, ~10 s on 16 threads; C5: 2 iterations, ~9 s
         threads = host_cores(args)
         dt, so, tro = cpu_solve(m, prob, oracle_options(m, len(prob.image_camera), cpu_iters), threads)
         it_o = so.num_successful_steps + so.num_unsuccessful_steps
