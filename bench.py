@@ -305,7 +305,7 @@ def resident_rate(s, o, n_obs, steps, warmup, barrier=lambda: None):
 
 def e2e_rate(new_solver, o, steps, warmup, barrier=lambda: None):
     """create (H2D) -> solve -> read back (D2H) -> destroy, a fresh handle every step, wall clock."""
-    total, phases, out = 0.0, np.zeros(3), None
+    total, phases, out, each = 0.0, np.zeros(3), None, []
     for i in range(warmup + steps):
         barrier()
         t = time.perf_counter()
@@ -319,7 +319,10 @@ def e2e_rate(new_solver, o, steps, warmup, barrier=lambda: None):
         if i >= warmup:
             total += dt
             phases += np.array([t1 - t, t2 - t1, t + dt - t2])
-    return total, dict(zip(("create_h2d", "solve", "read_back_destroy"), (phases / steps * 1e3).round(3).tolist())), out
+            each.append(round(dt * 1e3, 2))
+    ph = dict(zip(("create_h2d", "solve", "read_back_destroy"), (phases / steps * 1e3).round(3).tolist()))
+    ph["each_step_total"] = each  # (a single slow step -- a host hiccup -- shows here instead of hiding in the mean)
+    return total, ph, out
 
 
 def io_bytes(prob, out):

@@ -839,30 +839,11 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
     for (int64_t k = 0; k < n_obs_g; ++k) { pt_count[d.obs_point[k]]++; img_count[d.obs_image[k]]++; }
   }
   tm.Lap("histograms");
-  GlobalStructure g;
-  Analyse(d, &g, pt_count, img_count.data(), host_only, shared, p_off_scratch, live_scratch);
-  tm.Lap("analyse");
-  p->counts = g.counts;
-  p->n_img = d.num_images; p->n_cam = d.num_cameras;
-  p->n_pt_global = d.num_points; p->n_obs_global = d.num_observations;
-  p->kmax = g.kmax; p->dc = DcTier(g.kmax); p->n_cdim = g.n_cdim;
-  p->uniform_model = g.uniform_model; p->shared_intrinsics = g.shared_intrinsics;
   p->shard_count = d.shard_count > 0 ? d.shard_count : 1;
   p->shard_rank = d.shard_count > 0 ? d.shard_rank : 0;
-  p->h_img_cam.assign(d.image_camera, d.image_camera + p->n_img);
-  p->h_model.assign(d.camera_model, d.camera_model + p->n_cam);
-  p->h_col_img = g.col_img; p->h_col_cam = g.col_cam; p->h_k_cols = g.k_cols; p->h_k_dim = g.k_dim;
-  p->h_k_slot.assign((size_t)p->n_cam * 12, -1);
-  for (int c = 0; c < p->n_cam; ++c)
-    for (int j = 0; j < g.k_dim[c]; ++j) p->h_k_slot[12 * (size_t)c + g.k_cols[12 * (size_t)c + j]] = j;
-  p->h_blk_off = g.blk_off; p->h_blk_dim = g.blk_dim; p->h_t_dim = g.t_dim;
-  p->h_pose_const.assign(p->n_img, 0);
-  for (int i = 0; i < p->n_img; ++i) p->h_pose_const[i] = g.col_img[6 * (size_t)i] < 0 ? 1 : 0;
-
-  // ---- shard: contiguous global point range balanced by observation count ----
-  // Host: one counting pass by point (worker t owns a contiguous range of points and scans obs_point for them: no
-  // atomics, no per-thread counters) gives the CSR over points, the shard's range and the warp tiles.  The sort itself
-  // -- and every per-observation array -- is made on the DEVICE from the caller's arrays (cub stable radix sort).
+  // ---- shard: contiguous global point range balanced by observation count (from the counts alone) ----
+  // The sort of the observations -- and every per-observation array -- is made on the DEVICE from the caller's arrays
+  // (cub stable radix sort, order.cu); the host only walks the points.
   int p0 = 0, p1 = n_pt_g;
   int64_t obs_base = 0;
   if (p->shard_count > 1) {
@@ -873,8 +854,6 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   }
   p->n_pt = p1 - p0;
   p->pt_base = p0;
-  // one pass over the shard's points: CSR over points, the offsets of the variable ones, and the warp tiles (whole
-  // points packed into <= kTile observations)
   DeviceArena& A = p->arena;
   DeviceArena::Slot s_pt_ptr{}, s_p_off{}, s_tile{};
   std::vector<int> v_pt_ptr, v_p_off, v_tile;  // host-only: no staging block
@@ -892,21 +871,20 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
     v_pt_ptr.resize((size_t)p->n_pt + 1); v_p_off.resize(std::max(1, p->n_pt)); v_tile.resize(tile_bound);
     h_pt_ptr = v_pt_ptr.data(); h_p_off = v_p_off.data(); tile_start = v_tile.data();
   }
-  p->n_pvar = 0;
-  {
-    int acc = 0, fill = 0, nv = 0, nt = 0;
+  // CSR over the shard's points and the warp tiles (whole points packed into <= kTile observations): a sequential scan
+  // that needs the counts only -- on a thread of its own, under the analysis of the parameter blocks below
+  int n_tile_starts = 0;
+  std::thread tiler([&, p0]() {
+    int acc = 0, fill = 0, nt = 0;
     double pairs = 0.0;
     const int* cnt = pt_count + p0;
-    const int* go = g.p_off + p0;
+    const int n_pt = p->n_pt;
     h_pt_ptr[0] = 0;
     tile_start[nt++] = 0;
-    // (branch-free: the boundary is stored every time and kept only when a tile closes -- the three data-dependent
-    //  branches of the plain form mispredict on every other point, 2.9 ms for 1 M points)
-    for (int q = 0; q < p->n_pt; ++q) {
+    // (branch-free: the boundary is stored every time and kept only when a tile closes -- the data-dependent branches
+    //  of the plain form mispredict on every other point)
+    for (int q = 0; q < n_pt; ++q) {
       const int len = cnt[q];
-      const int var = go[q] >= 0;
-      h_p_off[q] = var ? nv : -1;
-      nv += var;
       const int close_before = (fill > 0) & (fill + len > kTile);  // (len == 0 never closes: fill < kTile here)
       tile_start[nt] = acc;
       nt += close_before;
@@ -921,13 +899,37 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
     }
     if (tile_start[nt - 1] != acc) tile_start[nt++] = acc;
     p->n_obs = acc;
-    p->n_pvar = nv;
     p->n_tiles = nt - 1;
     p->pair_estimate = pairs;
-    if (!host_only) A.ShrinkLast<int>(&s_tile, (size_t)nt);
+    n_tile_starts = nt;
+  });
+  GlobalStructure g;
+  Analyse(d, &g, pt_count, img_count.data(), host_only, shared, p_off_scratch, live_scratch);
+  {  // the shard's offsets among its own variable points
+    int nv = 0;
+    const int* go = g.p_off + p0;
+    for (int q = 0; q < p->n_pt; ++q) { const int var = go[q] >= 0; h_p_off[q] = var ? nv : -1; nv += var; }
+    p->n_pvar = nv;
   }
+  tm.Lap("analyse + offsets");
+  p->counts = g.counts;
+  p->n_img = d.num_images; p->n_cam = d.num_cameras;
+  p->n_pt_global = d.num_points; p->n_obs_global = d.num_observations;
+  p->kmax = g.kmax; p->dc = DcTier(g.kmax); p->n_cdim = g.n_cdim;
+  p->uniform_model = g.uniform_model; p->shared_intrinsics = g.shared_intrinsics;
+  p->h_img_cam.assign(d.image_camera, d.image_camera + p->n_img);
+  p->h_model.assign(d.camera_model, d.camera_model + p->n_cam);
+  p->h_col_img = g.col_img; p->h_col_cam = g.col_cam; p->h_k_cols = g.k_cols; p->h_k_dim = g.k_dim;
+  p->h_k_slot.assign((size_t)p->n_cam * 12, -1);
+  for (int c = 0; c < p->n_cam; ++c)
+    for (int j = 0; j < g.k_dim[c]; ++j) p->h_k_slot[12 * (size_t)c + g.k_cols[12 * (size_t)c + j]] = j;
+  p->h_blk_off = g.blk_off; p->h_blk_dim = g.blk_dim; p->h_t_dim = g.t_dim;
+  p->h_pose_const.assign(p->n_img, 0);
+  for (int i = 0; i < p->n_img; ++i) p->h_pose_const[i] = g.col_img[6 * (size_t)i] < 0 ? 1 : 0;
+  tiler.join();
+  if (!host_only) A.ShrinkLast<int>(&s_tile, (size_t)n_tile_starts);
   const int n_obs = p->n_obs;
-  tm.Lap("shard + point counts + tiles");
+  tm.Lap("blocks + tile scan joined");
 
   // ---- image-major chunks of <= 256: sizes from a counting pass by image over the shard's observations ----
   std::vector<int>& img_ptr = p->h_img_ptr;
