@@ -174,3 +174,16 @@ def test_observation_indices_are_checked_on_the_device(sba):
     s = sba.Solver(prob)  # and the library is still usable afterwards
     assert s.solve().final_cost > 0
     s.close()
+
+
+def test_resident_maps_need_a_device(sba):
+    """sba_maps_create has no host form: without a device it fails loudly, like sba_create."""
+    lib = sba.capi.load()
+    if lib.sba_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    import numpy as np
+    with pytest.raises(sba.capi.SbaError) as e:
+        sba.ResidentMaps(np.zeros((2, 4, 4), np.float32))
+    assert e.value.code == sba.capi.ERR_NO_DEVICE
+    with pytest.raises(ValueError):
+        sba.ResidentMaps(np.zeros((4, 4), np.float32))
