@@ -221,15 +221,16 @@ typedef int (*sba_iteration_callback)(const sba_iteration_summary* it, void* use
 /* --- lifecycle ---------------------------------------------------------- */
 void sba_default_solver_options(sba_solver_options* o);
 int sba_create(const sba_problem_desc* desc, sba_handle** out);
-/* Label maps that stay on the device across problems.  The reference loads an image's label map once and every
- * BundleAdjuster::Solve of the mapper reads the same maps (src/optim/bundle_adjustment.cc:361-372 hands the image's
- * map to each cost functor; the mapper calls Solve after every batch of registrations, src/sfm/incremental_mapper.cc:
- * 640-711): sba_maps_create copies `maps` ([num_images*height*width] row-major, top-down, as sba_problem_desc::
- * sem_maps) to the current device once, sba_create_with_maps builds a problem over them without moving them again
- * (desc->sem_maps must be NULL, desc->num_images must equal the set's; desc->sem_weight applies; sem_height / sem_width
- * of the descriptor are ignored).  The set is reference-counted: sba_maps_destroy may be called while handles created
- * over it are alive, the device memory goes with the last of them.  Results are bit-identical to sba_create with the
- * same maps in the descriptor. */
+/* Label maps that stay on the device across problems.  The reference's semantic adjusters read every image's label
+ * map once (SemanticBundleAdjuster::ReadDepthAndSemanticMaps, src/optim/semantic_bundle_adjustment.cc:1020-1066), keep
+ * them in a member (semantic_maps_, semantic_bundle_adjustment.h:260) and hand pointers to every cost functor
+ * (:728-729, :823); the maps of an image do not change between the mapper's adjustments (AdjustGlobalBundle,
+ * src/sfm/incremental_mapper.cc:668-711).  sba_maps_create copies `maps` ([num_images*height*width] row-major,
+ * top-down, as sba_problem_desc::sem_maps) to the current device once; sba_create_with_maps builds a problem over
+ * them without moving them again (desc->sem_maps must be NULL, desc->num_images must equal the set's;
+ * desc->sem_weight applies; sem_height / sem_width of the descriptor are ignored).  The set is reference-counted:
+ * sba_maps_destroy may be called while handles created over it are alive, the device memory goes with the last of
+ * them.  Results are bit-identical to sba_create with the same maps in the descriptor. */
 typedef struct sba_maps sba_maps;
 int sba_maps_create(int32_t num_images, int32_t height, int32_t width, const float* maps, sba_maps** out);
 void sba_maps_destroy(sba_maps* maps);

@@ -655,9 +655,10 @@ __global__ void retile_maps_kernel(const float* __restrict__ src, float* __restr
 }
 
 // ---- label maps kept on the device across problems (sba_maps_create) ----
-// The reference loads an image's label map once and every BundleAdjuster::Solve of the mapper reads the same maps
-// (/root/reference/src/optim/bundle_adjustment.cc:361-372 hands the map of the image to each cost functor); at C5 they
-// are 6.5 GB, and moving them host -> device is 134 of the 231 ms of a create + solve + read-back.
+// The reference's semantic adjusters read every image's map once and keep it for all their cost functors
+// (SemanticBundleAdjuster::ReadDepthAndSemanticMaps, /root/reference/src/optim/semantic_bundle_adjustment.cc:1020-1066;
+// semantic_maps_, semantic_bundle_adjustment.h:260); the maps do not change between the mapper's adjustments.  At C5
+// they are 6.5 GB, and moving them host -> device is ~110 of the 220 ms of a create + solve + read-back.
 void MapSetRelease(MapSet* m) {
   if (m && m->refs.fetch_sub(1) == 1) {
     int prev = -1;

@@ -98,8 +98,9 @@ class FlatProblem:
 
 
 class ResidentMaps:
-    """Label maps kept on the device across problems (`sba_maps_create`): the reference loads an image's map once and
-    every global bundle adjustment of the mapper reads the same maps (/root/reference/src/optim/bundle_adjustment.cc:361-372)."""
+    """Label maps kept on the device across problems (`sba_maps_create`): the reference's semantic adjusters read every
+    image's map once and keep it for all their cost functors (ReadDepthAndSemanticMaps,
+    /root/reference/src/optim/semantic_bundle_adjustment.cc:1020-1066; `semantic_maps_`, semantic_bundle_adjustment.h:260)."""
 
     def __init__(self, sem_maps):
         maps = np.ascontiguousarray(sem_maps, dtype=np.float32)
