@@ -730,13 +730,13 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   DevBuf<int> raw_img, raw_pt;   // the caller's observation arrays on the device (released after the final sync)
   DevBuf<double> raw_xy;
   DevBuf<float> map_stage;       // the caller's row-major label maps; re-tiled into d_sem_maps after the upload
-#define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); maps.Join(); cudaStreamSynchronize(CopyStream()); if (p->stream) cudaStreamSynchronize(p->stream); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
+#define UP(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { SetError(SBA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); maps.Join(); xy_up.Join(); cudaStreamSynchronize(CopyStream()); if (p->stream) cudaStreamSynchronize(p->stream); delete p; *out = nullptr; return SBA_ERR_CUDA; } } while (0)
   struct MapUpload {
     std::thread th;
     cudaError_t err = cudaSuccess;
     void Join() { if (th.joinable()) th.join(); }
     ~MapUpload() { Join(); }
-  } maps;
+  } maps, xy_up;  // xy_up: obs_xy out of PAGEABLE memory (staged by host threads) runs under the host's point passes
   if (!host_only) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -820,14 +820,33 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
       cudaEvent_t counted = nullptr;
       UP(cudaEventCreateWithFlags(&counted, cudaEventDisableTiming));
       cudaError_t e = cudaEventRecord(counted, p->stream);
-      if (e == cudaSuccess && n_obs_g > 0)
-        e = UploadLarge(raw_xy.p, d.obs_xy, 2 * (size_t)n_obs_g * sizeof(double), p->stream);
+      if (e == cudaSuccess && n_obs_g > 0) {
+        const size_t xy_bytes = 2 * (size_t)n_obs_g * sizeof(double);
+        cudaPointerAttributes at;
+        const bool dma = xy_bytes < 4 * kStageChunk ||
+                         (cudaPointerGetAttributes(&at, d.obs_xy) == cudaSuccess && at.type == cudaMemoryTypeHost);
+        cudaGetLastError();
+        if (dma) {  // page-locked source (or small): one asynchronous copy
+          e = UploadLarge(raw_xy.p, d.obs_xy, xy_bytes, p->stream);
+        } else {    // pageable: the staging copies keep host threads busy for ~2.5 ms at C4 -- not this one
+          const int dev = p->device;
+          double* dst = raw_xy.p;
+          const double* src = d.obs_xy;
+          cudaStream_t s = p->stream;
+          MapUpload* up = &xy_up;
+          xy_up.th = std::thread([up, dev, dst, src, xy_bytes, s] {
+            cudaSetDevice(dev);
+            up->err = UploadLarge(dst, src, xy_bytes, s);
+          });
+        }
+      }
       if (e == cudaSuccess) e = cudaEventSynchronize(counted);  // the counts are on the host; obs_xy is still on its way
       cudaEventDestroy(counted);
       UP(e);
     }
     p->launches += 2;
     if (*h_bad) {
+      xy_up.Join();
       cudaStreamSynchronize(p->stream);
       SetError(SBA_ERR_INVALID_ARGUMENT, "observation index out of range");
       maps.Join(); cudaStreamSynchronize(CopyStream());
@@ -863,7 +882,7 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
   if (!host_only) {
     if (!stg.Reserve(((size_t)p->n_pt * 2 + 1 + tile_bound) * sizeof(int) + 4 * 256 + (1u << 20))) {
       SetError(SBA_ERR_CUDA, "page-locked staging block for sba_create: out of memory");
-      maps.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA;
+      maps.Join(); xy_up.Join(); cudaStreamSynchronize(CopyStream()); cudaStreamSynchronize(p->stream); delete p; return SBA_ERR_CUDA;
     }
     h_pt_ptr = A.Claim<int>((size_t)p->n_pt + 1, &s_pt_ptr);
     h_p_off = A.Claim<int>((size_t)p->n_pt, &s_p_off);
@@ -1043,6 +1062,8 @@ int BuildProblem(const sba_problem_desc* dp, Problem** out, bool host_only, MapS
 
   // point-sorted observations and the image-major list, sorted on the device from the raw copies
   {
+    xy_up.Join();  // (pageable obs_xy: every chunk has been queued on the stream)
+    UP(xy_up.err);
     const int orc = BuildDeviceOrder(p, p0, obs_base, n_obs_g, n_pt_g, raw_img.p, raw_pt.p, raw_xy.p);
     if (orc) { maps.Join(); cudaStreamSynchronize(CopyStream()); delete p; *out = nullptr; return orc; }
   }
