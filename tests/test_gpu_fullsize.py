@@ -1,5 +1,5 @@
 """Size-independent properties at BASELINE.json's full sizes (C4: 1778 cameras / 993 k points / 5 M observations, the
-headline workload; C3 with the three-row residual).  The oracle needs ~10 s per LM iteration at this size, so parity
+headline workload; C3 and C5 -- the north-star configuration -- with the three-row residual).  The oracle needs ~10 s per LM iteration at this size, so parity
 here is through properties the domain offers: the cost is a checksum of the residuals, two evaluation kernels and the
 allocation-free one must agree on it, the reduced camera matrix is linear and symmetric and its two representations
 (implicit products over J, explicit block-sparse S) are the same operator, the order of the caller's observation list
@@ -105,5 +105,40 @@ def test_c3_three_row_cost_is_the_checksum_of_all_rows(sba):
         assert np.count_nonzero(ev["sem"]) > 0.5 * len(ev["sem"])
         assert abs(ev["cost"] - checksum) <= 1e-12 * checksum
         assert abs(s.cost_no_alloc() - checksum) <= 1e-12 * checksum
+    finally:
+        s.close()
+
+
+@pytest.mark.gpu
+def test_c5_three_rows_and_resident_maps_at_full_size(sba):
+    """The north-star configuration (5000 cameras / 2 M points / 15 M observations, 6.1 GB of label maps): the cost is the
+    checksum of all three residual rows, two LM iterations never raise it, and a problem built over resident maps
+    (sba_maps_create) ends on the same bits as one that carries the maps in its descriptor."""
+    prob, _ = sba.scene.make_config("C5")
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations = 2
+    o.function_tolerance = o.gradient_tolerance = o.parameter_tolerance = 0.0
+    maps = sba.ResidentMaps(prob.sem_maps)
+    s = sba.Solver(prob, maps=maps)
+    try:
+        ev = s.evaluate(want=("r", "sem"))
+        assert ev["r"].shape == (prob.num_observations, 2) and np.isfinite(ev["r"]).all() and np.isfinite(ev["sem"]).all()
+        checksum = 0.5 * (float(np.sum(ev["r"].astype(np.longdouble) ** 2)) + float(np.sum(ev["sem"].astype(np.longdouble) ** 2)))
+        assert np.count_nonzero(ev["sem"]) > 0.5 * len(ev["sem"])
+        assert abs(ev["cost"] - checksum) <= 1e-12 * checksum
+        del ev
+        a = s.solve(o)
+        costs = [r.cost for r in s.trace()]
+        assert abs(costs[0] - checksum) <= 1e-12 * checksum
+        assert all(y <= x for x, y in zip(costs, costs[1:])) and a.final_cost < a.initial_cost
+        assert a.num_residuals == 3 * prob.num_observations
+        Xa = s.parameters()[3]
+    finally:
+        s.close()
+        maps.close()
+    s = sba.Solver(prob)
+    try:
+        b = s.solve(o)
+        assert b.final_cost == a.final_cost and np.array_equal(s.parameters()[3], Xa)
     finally:
         s.close()
