@@ -288,3 +288,26 @@ def test_resident_maps_solve_is_bit_identical(sba):
     m0 = C.c_void_p()
     assert capi.load().sba_maps_create(0, 4, 4, None, C.byref(m0)) == capi.ERR_INVALID_ARGUMENT and not m0
     small.close(); maps.close()
+
+
+@pytest.mark.gpu
+def test_resident_maps_under_point_shards(sba):
+    """The multi-GPU layout over a resident map set (every rank keeps the maps of all images):
+    each shard's three rows are the unsharded handle's, bit for bit, and the shards partition the observations."""
+    prob = _scene(sba, model="SIMPLE_RADIAL", refine=True, n_cam=9, n_pt=900, seed=12)
+    s = sba.Solver(prob)
+    full = s.evaluate(want=("r", "sem"))
+    s.close()
+    maps = sba.ResidentMaps(prob.sem_maps)
+    covered = np.zeros(prob.num_observations, bool)
+    for rank in range(3):
+        _, obs_keep = prob.shard_masks(3, rank)
+        own = obs_keep.astype(bool)
+        sh = sba.Solver(prob, shard_rank=rank, shard_count=3, maps=maps)
+        ev = sh.evaluate(want=("r", "sem"))
+        sh.close()
+        assert np.array_equal(ev["r"][own], full["r"][own]) and np.array_equal(ev["sem"][own], full["sem"][own])
+        assert not ev["r"][~own].any() and not ev["sem"][~own].any()
+        covered |= own
+    maps.close()
+    assert covered.all() and np.count_nonzero(full["sem"]) > 0
