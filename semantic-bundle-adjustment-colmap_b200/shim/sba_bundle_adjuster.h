@@ -7,13 +7,17 @@
 //   BundleAdjuster            /root/reference/src/optim/bundle_adjustment.h:171-203
 // but hands the arithmetic to libsba_b200.so through the C ABI of include/sba_b200.h instead of
 // building a ceres::Problem.  Everything below is host integer work: walking the containers in the
-// reference's residual order (SetUp, bundle_adjustment.cc:326-342) and packing plain arrays.
+// reference's residual order (SetUp, bundle_adjustment.cc:326-342) and packing plain arrays.  At the headline size
+// (1778 images / 1 M points / 5 M observations) Flatten takes ~0.2 s on one host core (tools/shim_flatten_bench.cpp;
+// 1.1 s with two hash lookups per observation), against 33 ms for everything from sba_create to the read-back.
 //
 // The adjuster is a template over the Reconstruction type.  It only uses the accessor contract
 //   rec->Image(id)  : CameraId(), NormalizeQvec(), Qvec().data(), Tvec().data(), Points2D(), Point2D(i)
 //   Point2D         : HasPoint3D(), Point3DId(), XY().data()
 //   rec->Camera(id) : ModelId(), NumParams(), ParamsData(), FocalLengthIdxs(), PrincipalPointIdxs(), ExtraParamsIdxs()
 //   rec->Point3D(id): XYZ().data(), Track().Length(), Track().Elements() -> {image_id, point2D_idx}
+//   rec->Points3D() : iterable of (point3D_t, Point3D) with size()   (reconstruction.h:97; walked instead of one hash
+//                     lookup per point when most of the reconstruction's points take part)
 // (src/base/{reconstruction,image,camera,point2d,point3d,track}.h), so the same header compiles against
 // COLMAP's own classes and against shim/mock_reconstruction.h (tests/shim_test.cpp).
 //
@@ -22,7 +26,10 @@
 #define SBA_SHIM_BUNDLE_ADJUSTER_H_
 
 #include <cmath>
+#include <chrono>
 #include <cstdint>
+#include <mutex>
+#include <type_traits>
 #include <cstdio>
 #include <stdexcept>
 #include <string>
@@ -187,6 +194,48 @@ class BundleAdjustmentConfig {
 };
 
 // ---- flattened problem: the arrays behind one sba_problem_desc ---------------------------------------
+// point3D id -> dense slot.  COLMAP hands point ids out from a counter (Reconstruction::AddPoint3D,
+// src/base/reconstruction.cc:299-304), so the ids a problem meets are dense up to the gaps deleted points leave: a direct
+// table when the largest id is within a small factor of the number of observations, a hash map otherwise.  (Two hash
+// lookups per observation were 0.8 of the 1.1 s Flatten took at C4's size.)
+class PointSlots {
+ public:
+  struct Entry { int32_t slot; uint32_t seen; };  // seen: point3D_num_observations_ of the reference (bundle_adjustment.h:202)
+  static bool& ForceHash() { static bool f = false; return f; }  // tests: take the fallback for sparse ids
+  void Reset(point3D_t max_id, size_t expected) {
+    dense_ = max_id < 16 * static_cast<point3D_t>(expected) + (1u << 20);
+    if (ForceHash()) dense_ = false;
+    table_.clear(); map_.clear();
+    if (dense_) table_.assign(static_cast<size_t>(max_id) + 1, Entry{-1, 0});
+    else map_.reserve(expected);
+  }
+  Entry* Find(point3D_t id) {
+    if (dense_) return (id < table_.size() && table_[static_cast<size_t>(id)].slot >= 0) ? &table_[static_cast<size_t>(id)] : nullptr;
+    auto it = map_.find(id);
+    return it == map_.end() ? nullptr : &it->second;
+  }
+  Entry* Insert(point3D_t id, int32_t slot) {
+    if (dense_) {
+      if (id >= table_.size()) table_.resize(static_cast<size_t>(id) + 1, Entry{-1, 0});  // (an id the size pass did not see)
+      table_[static_cast<size_t>(id)] = Entry{slot, 0};
+      return &table_[static_cast<size_t>(id)];
+    }
+    return &map_.emplace(id, Entry{slot, 0}).first->second;
+  }
+  void Prefetch(point3D_t id) const {
+#if defined(__GNUC__) || defined(__clang__)
+    if (dense_ && id < table_.size()) __builtin_prefetch(&table_[static_cast<size_t>(id)]);
+#else
+    (void)id;
+#endif
+  }
+
+ private:
+  bool dense_ = false;
+  std::vector<Entry> table_;
+  std::unordered_map<point3D_t, Entry> map_;
+};
+
 struct FlatProblem {
   std::vector<double> qvec, tvec, cam_params, points, obs_xy;
   std::vector<int32_t> image_camera, camera_model, obs_image, obs_point;
@@ -196,6 +245,13 @@ struct FlatProblem {
   std::vector<image_t> image_ids;
   std::vector<camera_t> camera_ids;
   std::vector<point3D_t> point_ids;
+
+  void Clear() {  // keeps the capacity (and with it the mapped pages) of every array
+    qvec.clear(); tvec.clear(); cam_params.clear(); points.clear(); obs_xy.clear();
+    image_camera.clear(); camera_model.clear(); obs_image.clear(); obs_point.clear();
+    pose_constant.clear(); tvec_mask.clear(); point_constant.clear(); cam_mask.clear();
+    image_ids.clear(); camera_ids.clear(); point_ids.clear();
+  }
 
   sba_problem_desc Desc() const {
     sba_problem_desc d{};
@@ -222,6 +278,29 @@ struct FlatProblem {
   }
 };
 
+// The arrays of the last adjusters of this process, kept for the next ones: a mapper adjusts again and again with problems
+// of growing size, and 150 MB of freshly mapped vectors cost ~45 ms of page faults per Flatten at C4's size.
+class FlatPool {
+ public:
+  static FlatProblem Take() {
+    std::lock_guard<std::mutex> lk(Mu());
+    auto& f = Free();
+    if (f.empty()) return FlatProblem();
+    FlatProblem p = std::move(f.back());
+    f.pop_back();
+    p.Clear();
+    return p;
+  }
+  static void Give(FlatProblem&& p) {
+    std::lock_guard<std::mutex> lk(Mu());
+    if (Free().size() < 2) Free().push_back(std::move(p));
+  }
+
+ private:
+  static std::mutex& Mu() { static std::mutex m; return m; }
+  static std::vector<FlatProblem>& Free() { static std::vector<FlatProblem> f; return f; }
+};
+
 // ---- BundleAdjuster --------------------------------------------------------------------------------
 template <class Reconstruction>
 class BundleAdjusterT {
@@ -230,6 +309,9 @@ class BundleAdjusterT {
       : options_(options), config_(config) {  // both copied by value, bundle_adjustment.cc:252-256
     if (!options_.Check()) throw std::invalid_argument("BundleAdjustmentOptions::Check failed");
   }
+  ~BundleAdjusterT() { FlatPool::Give(std::move(flat_)); }
+  BundleAdjusterT(const BundleAdjusterT&) = delete;
+  BundleAdjusterT& operator=(const BundleAdjusterT&) = delete;
 
   // bundle_adjustment.cc:258-320.  true unless the problem is empty; convergence does not matter (:319).
   bool Solve(Reconstruction* reconstruction) {
@@ -279,19 +361,40 @@ class BundleAdjusterT {
 
   // Residual blocks in the reference order -> plain arrays (a7).  Public for the parity tests.
   const FlatProblem& Flatten(Reconstruction* rec) {
-    flat_ = FlatProblem();
-    image_slot_.clear(); camera_slot_.clear(); point_slot_.clear();
-    seen_per_point_.clear(); problem_cameras_.clear();
+    FlatPool::Give(std::move(flat_));
+    flat_ = FlatPool::Take();
+    image_slot_.clear(); camera_slot_.clear();
+    problem_cameras_.clear();
+    {  // size pass: observation count and the largest point id (sequential reads of the images' Points2D)
+      size_t n_obs = 0;
+      point3D_t max_id = 0;
+      for (image_t id : config_.Images())
+        for (const auto& p2 : rec->Image(id).Points2D())
+          if (p2.HasPoint3D()) { ++n_obs; if (p2.Point3DId() > max_id) max_id = p2.Point3DId(); }
+      for (point3D_t id : config_.VariablePoints()) if (id > max_id) max_id = id;
+      for (point3D_t id : config_.ConstantPoints()) if (id > max_id) max_id = id;
+      point_slot_.Reset(max_id, n_obs + config_.NumPoints());
+      flat_.obs_image.reserve(n_obs); flat_.obs_point.reserve(n_obs); flat_.obs_xy.reserve(2 * n_obs);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
     for (image_t id : config_.Images()) AddImage(id, rec);                 // :330-332
+    const auto t1 = std::chrono::steady_clock::now();
     for (point3D_t id : config_.VariablePoints()) AddPoint(id, rec);       // :333-335
     for (point3D_t id : config_.ConstantPoints()) AddPoint(id, rec);       // :336-338
+    const auto t2 = std::chrono::steady_clock::now();
     PackCameras(rec);                                                      // ParameterizeCameras :480-516
     PackPoints(rec);                                                       // ParameterizePoints  :518-530
     PackPoses(rec);
+    const auto t3 = std::chrono::steady_clock::now();
+    flatten_ms_[0] = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    flatten_ms_[1] = std::chrono::duration<double, std::milli>(t2 - t1).count();
+    flatten_ms_[2] = std::chrono::duration<double, std::milli>(t3 - t2).count();
     return flat_;
   }
 
   const BundleAdjustmentConfig& Config() const { return config_; }
+  // host time of the last Flatten: images' observations, extra track elements of the config's points, parameter packing (ms)
+  const double* FlattenPhaseMs() const { return flatten_ms_; }
 
   static void PrintSolverSummary(const SolverSummary& s) {  // bundle_adjustment.cc:1142-1196
     static const char* kTerm[] = {"Convergence", "No convergence", "Failure", "User success", "User failure"};
@@ -343,13 +446,11 @@ class BundleAdjusterT {
     flat_.camera_ids.push_back(id);
     return s;
   }
-  int32_t PointSlot(point3D_t id) {
-    auto it = point_slot_.find(id);
-    if (it != point_slot_.end()) return it->second;
+  PointSlots::Entry* PointSlot(point3D_t id) {
+    if (PointSlots::Entry* e = point_slot_.Find(id)) return e;
     const int32_t s = static_cast<int32_t>(flat_.point_ids.size());
-    point_slot_.emplace(id, s);
     flat_.point_ids.push_back(id);
-    return s;
+    return point_slot_.Insert(id, s);
   }
   void PushObservation(int32_t img, int32_t pt, const double* xy) {
     flat_.obs_image.push_back(img);
@@ -364,12 +465,18 @@ class BundleAdjusterT {
     const bool constant_pose = !options_.refine_extrinsics || config_.HasConstantPose(image_id);
     size_t n = 0;
     int32_t slot = -1;
-    for (const auto& p2 : image.Points2D()) {
+    const auto& points2D = image.Points2D();
+    const size_t n2 = points2D.size();
+    constexpr size_t kAhead = 12;  // the id -> slot table is read at random: ask for the entries a few features ahead
+    for (size_t i = 0; i < n2; ++i) {
+      if (i + kAhead < n2 && points2D[i + kAhead].HasPoint3D()) point_slot_.Prefetch(points2D[i + kAhead].Point3DId());
+      const auto& p2 = points2D[i];
       if (!p2.HasPoint3D()) continue;
       if (slot < 0) slot = ImageSlot(image_id, constant_pose);
       ++n;
-      seen_per_point_[p2.Point3DId()] += 1;
-      PushObservation(slot, PointSlot(p2.Point3DId()), p2.XY().data());
+      PointSlots::Entry* e = PointSlot(p2.Point3DId());
+      e->seen += 1;  // point3D_num_observations_ (:371)
+      PushObservation(slot, e->slot, p2.XY().data());
     }
     if (n == 0) return;
     problem_cameras_.insert(image.CameraId());
@@ -383,18 +490,18 @@ class BundleAdjusterT {
 
   void AddPoint(point3D_t pid, Reconstruction* rec) {  // AddPointToProblem :429-478
     auto& p3 = rec->Point3D(pid);
-    size_t& seen = seen_per_point_[pid];
-    if (seen == p3.Track().Length()) return;
+    const PointSlots::Entry* known = point_slot_.Find(pid);
+    if ((known ? known->seen : 0u) == p3.Track().Length()) return;
     for (const auto& el : p3.Track().Elements()) {
       if (config_.HasImage(el.image_id)) continue;
-      ++seen;
+      PointSlot(pid)->seen += 1;
       auto& image = rec->Image(el.image_id);
       if (problem_cameras_.count(image.CameraId()) == 0) {  // :456-459
         problem_cameras_.insert(image.CameraId());
         config_.SetConstantCamera(image.CameraId());
       }
       CameraSlot(image.CameraId());
-      PushObservation(ImageSlot(el.image_id, true), PointSlot(pid), image.Point2D(el.point2D_idx).XY().data());
+      PushObservation(ImageSlot(el.image_id, true), PointSlot(pid)->slot, image.Point2D(el.point2D_idx).XY().data());
     }
   }
 
@@ -423,14 +530,24 @@ class BundleAdjusterT {
   }
 
   void PackPoints(Reconstruction* rec) {
-    flat_.point_constant.assign(flat_.point_ids.size(), 0);
-    flat_.points.resize(3 * flat_.point_ids.size());
-    for (size_t s = 0; s < flat_.point_ids.size(); ++s) {
-      const point3D_t pid = flat_.point_ids[s];
-      auto& p3 = rec->Point3D(pid);
+    const size_t n = flat_.point_ids.size();
+    flat_.point_constant.assign(n, 0);
+    flat_.points.resize(3 * n);
+    auto pack = [this](size_t s, point3D_t pid, const auto& p3, uint32_t seen) {
       const double* X = p3.XYZ().data();
       for (int k = 0; k < 3; ++k) flat_.points[3 * s + k] = X[k];
-      if (p3.Track().Length() > seen_per_point_[pid] || config_.HasConstantPoint(pid)) flat_.point_constant[s] = 1;
+      if (p3.Track().Length() > seen || config_.HasConstantPoint(pid)) flat_.point_constant[s] = 1;
+    };
+    if (2 * n >= rec->Points3D().size()) {
+      // most of the reconstruction's points take part (global bundle adjustment): one walk over the container instead of
+      // a hash lookup per point (reconstruction.h:97)
+      for (const auto& el : rec->Points3D())
+        if (const PointSlots::Entry* e = point_slot_.Find(el.first)) pack(static_cast<size_t>(e->slot), el.first, el.second, e->seen);
+    } else {
+      for (size_t s = 0; s < n; ++s) {
+        const point3D_t pid = flat_.point_ids[s];
+        pack(s, pid, rec->Point3D(pid), point_slot_.Find(pid)->seen);
+      }
     }
   }
 
@@ -464,9 +581,19 @@ class BundleAdjusterT {
       double* prm = cam.ParamsData();
       for (size_t j = 0; j < cam.NumParams(); ++j) prm[j] = c[SBA_MAX_CAMERA_PARAMS * s + j];
     }
-    for (size_t s = 0; s < flat_.point_ids.size(); ++s) {
-      double* Xd = rec->Point3D(flat_.point_ids[s]).XYZ().data();
-      for (int k = 0; k < 3; ++k) Xd[k] = X[3 * s + k];
+    if (2 * flat_.point_ids.size() >= rec->Points3D().size()) {
+      // (the container is walked through its const accessor, reconstruction.h:97; the Reconstruction itself is ours to write)
+      for (const auto& el : rec->Points3D())
+        if (const PointSlots::Entry* e = point_slot_.Find(el.first)) {
+          using P3 = std::remove_const_t<std::remove_reference_t<decltype(el.second)>>;
+          double* Xd = const_cast<P3&>(el.second).XYZ().data();
+          for (int k = 0; k < 3; ++k) Xd[k] = X[3 * static_cast<size_t>(e->slot) + k];
+        }
+    } else {
+      for (size_t s = 0; s < flat_.point_ids.size(); ++s) {
+        double* Xd = rec->Point3D(flat_.point_ids[s]).XYZ().data();
+        for (int k = 0; k < 3; ++k) Xd[k] = X[3 * s + k];
+      }
     }
   }
 
@@ -477,8 +604,8 @@ class BundleAdjusterT {
   FlatProblem flat_;
   std::unordered_map<image_t, int32_t> image_slot_;
   std::unordered_map<camera_t, int32_t> camera_slot_;
-  std::unordered_map<point3D_t, int32_t> point_slot_;
-  std::unordered_map<point3D_t, size_t> seen_per_point_;   // point3D_num_observations_, bundle_adjustment.h:202
+  double flatten_ms_[3] = {0, 0, 0};
+  PointSlots point_slot_;
   std::unordered_set<camera_t> problem_cameras_;           // camera_ids_, bundle_adjustment.h:201
 };
 

@@ -6,6 +6,7 @@
 // Built and run by tests/test_shim_cpp.py.  Exit code 0 == every check passed.
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <random>
 
 #include "mock_reconstruction.h"
@@ -58,6 +59,101 @@ static void Generate(size_t num_images, size_t num_points, Reconstruction* rec, 
     Track tr;
     for (size_t i = 0; i < num_images; ++i) tr.AddElement(static_cast<image_t>(i), static_cast<uint32_t>(j));
     rec->AddPoint3D(xyz[j], tr);
+  }
+}
+
+// The residual order of the reference (SetUp, bundle_adjustment.cc:326-478), restated with ordered maps and no shortcuts:
+// images of the config in set order, their features with a 3-D point in feature order; then the config's variable and
+// constant points, each adding its track elements from images outside the config.  Slots are handed out in first-seen
+// order.  Flatten -- which maps point ids through a direct table or a hash map and walks the point container for the
+// packing -- must produce the same arrays on random scenes: partial configs, features without points, deleted
+// observations, points of the config, both id maps.
+static void TestFlattenOrder() {
+  for (int seed = 0; seed < 60; ++seed) {
+    std::mt19937_64 rng(static_cast<unsigned>(seed));
+    const int n_img = 3 + seed % 7, n_pt = 20 + (seed * 13) % 150;
+    Reconstruction rec;
+    for (camera_t c = 1; c <= 2; ++c) {
+      Camera cam; cam.SetCameraId(c); cam.SetModelId(c == 1 ? SBA_SIMPLE_RADIAL : SBA_SIMPLE_PINHOLE);
+      for (auto& v : cam.Params()) v = 100.0 + static_cast<double>(rng() % 100);
+      rec.AddCamera(cam);
+    }
+    std::vector<std::vector<Vector2d>> xy(static_cast<size_t>(n_img));
+    std::vector<Track> tracks(static_cast<size_t>(n_pt));
+    for (auto& tr : tracks) {
+      const int len = 2 + static_cast<int>(rng() % 3), first = static_cast<int>(rng() % static_cast<unsigned>(n_img));
+      for (int k = 0; k < len && k < n_img; ++k) {
+        const size_t i = static_cast<size_t>((first + k) % n_img);
+        tr.AddElement(static_cast<image_t>(i + 1), static_cast<uint32_t>(xy[i].size()));
+        xy[i].push_back({{static_cast<double>(rng() % 640), static_cast<double>(rng() % 480)}});
+      }
+    }
+    for (int i = 0; i < n_img; ++i) {
+      for (int e = 0; e < 3; ++e) xy[static_cast<size_t>(i)].push_back({{1.0, 2.0}});  // features without a 3-D point
+      Image im; im.SetImageId(static_cast<image_t>(i + 1)); im.SetCameraId(static_cast<camera_t>(1 + i % 2)); im.SetPoints2D(xy[static_cast<size_t>(i)]);
+      im.Qvec() = {{1.0, 0.0, 0.0, 0.0}}; im.Tvec() = {{0.1 * i, 0.2, 0.3}};
+      rec.AddImage(im);
+    }
+    std::vector<point3D_t> ids;
+    for (int p = 0; p < n_pt; ++p) ids.push_back(rec.AddPoint3D({{static_cast<double>(p), 1.0 + seed, 2.0}}, tracks[static_cast<size_t>(p)]));
+    for (int k = 0; k < 3; ++k) {  // some features lose their point
+      const image_t i = static_cast<image_t>(1 + rng() % static_cast<unsigned>(n_img));
+      for (uint32_t j = 0; j < rec.Image(i).Points2D().size(); ++j)
+        if (rec.Image(i).Point2D(j).HasPoint3D() && rec.Point3D(rec.Image(i).Point2D(j).Point3DId()).Track().Length() > 2) { rec.DeleteObservation(i, j); break; }
+    }
+    BundleAdjustmentConfig config;
+    const int n_cfg = seed % 3 == 0 ? n_img : 1 + static_cast<int>(rng() % static_cast<unsigned>(n_img));  // global or local
+    for (int i = 0; i < n_cfg; ++i) config.AddImage(static_cast<image_t>(1 + (i * 2) % n_img));
+    for (int k = 0; k < 5; ++k) {
+      const point3D_t id = ids[rng() % ids.size()];
+      if (!config.HasPoint(id)) { if (k % 2) config.AddVariablePoint(id); else config.AddConstantPoint(id); }
+    }
+    // ---- the plain restatement ----
+    std::vector<int32_t> want_img, want_pt;
+    std::vector<double> want_xy;
+    std::vector<image_t> img_ids;
+    std::vector<point3D_t> pt_ids;
+    std::map<image_t, int32_t> img_slot;
+    std::map<point3D_t, int32_t> pt_slot;
+    std::map<point3D_t, size_t> seen;
+    auto slot_of = [](auto& m, auto& order, auto id) { auto it = m.find(id); if (it != m.end()) return it->second; const int32_t s = static_cast<int32_t>(order.size()); m[id] = s; order.push_back(id); return s; };
+    for (image_t id : config.Images())
+      for (const auto& p2 : rec.Image(id).Points2D()) {
+        if (!p2.HasPoint3D()) continue;
+        want_img.push_back(slot_of(img_slot, img_ids, id));
+        want_pt.push_back(slot_of(pt_slot, pt_ids, p2.Point3DId()));
+        want_xy.push_back(p2.XY()[0]); want_xy.push_back(p2.XY()[1]);
+        seen[p2.Point3DId()] += 1;
+      }
+    auto add_point = [&](point3D_t pid) {
+      const auto& p3 = rec.Point3D(pid);
+      if (seen[pid] == p3.Track().Length()) return;
+      for (const auto& el : p3.Track().Elements()) {
+        if (config.HasImage(el.image_id)) continue;
+        seen[pid] += 1;
+        want_img.push_back(slot_of(img_slot, img_ids, el.image_id));
+        want_pt.push_back(slot_of(pt_slot, pt_ids, pid));
+        const auto& x = rec.Image(el.image_id).Point2D(el.point2D_idx).XY();
+        want_xy.push_back(x[0]); want_xy.push_back(x[1]);
+      }
+    };
+    for (point3D_t id : config.VariablePoints()) add_point(id);
+    for (point3D_t id : config.ConstantPoints()) add_point(id);
+    for (int use_hash = 0; use_hash < 2; ++use_hash) {
+      sba_shim::PointSlots::ForceHash() = use_hash != 0;
+      BundleAdjuster ba(BundleAdjustmentOptions(), config);
+      const sba_shim::FlatProblem& f = ba.Flatten(&rec);
+      CHECK_THAT(f.obs_image == want_img && f.obs_point == want_pt && f.obs_xy == want_xy);
+      CHECK_THAT(f.image_ids == img_ids && f.point_ids == pt_ids);
+      bool packed = f.points.size() == 3 * pt_ids.size() && f.point_constant.size() == pt_ids.size();
+      for (size_t s = 0; packed && s < pt_ids.size(); ++s) {
+        const auto& p3 = rec.Point3D(pt_ids[s]);
+        packed = f.points[3 * s] == p3.XYZ()[0] && f.points[3 * s + 1] == p3.XYZ()[1] && f.points[3 * s + 2] == p3.XYZ()[2] &&
+                 f.point_constant[s] == ((p3.Track().Length() > seen[pt_ids[s]] || config.HasConstantPoint(pt_ids[s])) ? 1 : 0);
+      }
+      CHECK_THAT(packed);
+    }
+    sba_shim::PointSlots::ForceHash() = false;
   }
 }
 
@@ -466,6 +562,7 @@ static void TestRigSolve() {
 int main(int argc, char** argv) {
   const bool solve = argc > 1 && std::strcmp(argv[1], "solve") == 0;
   TestCounts();
+  TestFlattenOrder();
   TestSemanticHost();
   if (solve) {
     if (sba_device_count() < 1) {
