@@ -1,7 +1,7 @@
 // Host side of the drop-in at the headline size: how long the shim takes to walk a Reconstruction of C4's shape
 // (1778 images / ~1 M points / ~5 M observations, every image in the config) into the arrays of sba_problem_desc, and to
 // store the result back.  No device needed: only Flatten and the scatter loops run.
-//   g++ -O2 -std=c++17 -Iinclude -Isemantic-bundle-adjustment-colmap_b200/shim tools/shim_flatten_bench.cpp \
+//   g++ -O2 -std=c++17 -Iinclude -Isemantic-bundle-adjustment-colmap_b200/shim tools/shim_flatten_bench.cpp
 //       -Lsemantic-bundle-adjustment-colmap_b200 -lsba_b200 -Wl,-rpath,$PWD/semantic-bundle-adjustment-colmap_b200 -o /tmp/flatten_bench
 #include <chrono>
 #include <cstdio>
