@@ -8,7 +8,9 @@
 // differentiation, the loss corrector and the trust-region loop follow Ceres 2.1.0 (un-vendored) --
 // the same restatement as ba_oracle.cpp, on dense normal equations because these problems have no point blocks
 // (App. B.1).  Written residual block by residual block (Jacobian rows in compact tangent columns), not pair by pair
-// as the device does.  PARITY UNPINNED: the reference has no test for any of this.
+// as the device does.  PARITY: the residual blocks are UNPINNED (the reference has no test for any of this); the
+// trust-region loop (SolveDense) is pinned by the iteration table Ceres' documentation publishes for Powell's function
+// (oracle_powell_solve below, tests/test_oracle_golden.py).
 #include <omp.h>
 
 #include <algorithm>
@@ -719,6 +721,57 @@ int oracle_rig_solve(sba_rig_problem* d, const sba_solver_options* o, int thread
   for (int i = 0; i < n_rel; ++i) { std::memcpy(d->rel_qvec + 4 * (size_t)i, &cur.q[4 * (size_t)(n_rig + i)], 32); std::memcpy(d->rel_tvec + 3 * (size_t)i, &cur.t[3 * (size_t)(n_rig + i)], 24); }
   if (n_cam) std::memcpy(d->camera_params, cur.cam.data(), cur.cam.size() * sizeof(double));
   if (n_pt) std::memcpy(d->points, cur.X.data(), cur.X.size() * sizeof(double));
+  return rc;
+}
+
+// Powell's singular function through the same LM loop -- the one solve in Ceres' own documentation whose iteration
+// table is published (docs/source/nnls_tutorial.rst, "Powell's Function": f1 = x1 + 10 x2, f2 = sqrt(5) (x3 - x4),
+// f3 = (x2 - 2 x3)^2, f4 = sqrt(10) (x1 - x4)^2 from x = (3, -1, 0, 1), Solver::Options defaults, DENSE_QR).  A dense QR
+// of the augmented Jacobian and the Cholesky of the normal equations solve the same regularised system, so the table
+// pins the trust-region loop restated here (and, through the shared SolveDense, the loops of the semantic, cylinder
+// and rig solves): radius update, step acceptance, LM diagonal with its clamp, Jacobi scaling, the termination tests.
+int oracle_powell_solve(const sba_solver_options* o, double* x, sba_summary* summary, sba_iteration_summary* trace, int32_t trace_cap,
+                        int32_t* trace_n) {
+  if (!o || !x || !summary) return SBA_ERR_INVALID_ARGUMENT;
+  std::memset(summary, 0, sizeof(*summary));
+  std::vector<double> cur(x, x + 4), cand(4);
+  auto residuals = [](const std::vector<double>& v, double f[4]) {
+    f[0] = v[0] + 10.0 * v[1];
+    f[1] = std::sqrt(5.0) * (v[2] - v[3]);
+    f[2] = (v[1] - 2.0 * v[2]) * (v[1] - 2.0 * v[2]);
+    f[3] = std::sqrt(10.0) * (v[0] - v[3]) * (v[0] - v[3]);
+  };
+  DenseProblem P;
+  P.n = 4;
+  P.rows = [&](std::vector<Row>* rows) {
+    double f[4];
+    residuals(cur, f);
+    rows->clear();
+    Row r;
+    r.n = 4;
+    for (int a = 0; a < 4; ++a) r.col[a] = a;
+    auto push = [&](double res, double j0, double j1, double j2, double j3) { r.r = res; r.j[0] = j0; r.j[1] = j1; r.j[2] = j2; r.j[3] = j3; rows->push_back(r); };
+    push(f[0], 1.0, 10.0, 0.0, 0.0);
+    push(f[1], 0.0, 0.0, std::sqrt(5.0), -std::sqrt(5.0));
+    const double a = 2.0 * (cur[1] - 2.0 * cur[2]);
+    push(f[2], 0.0, a, -2.0 * a, 0.0);
+    const double b = 2.0 * std::sqrt(10.0) * (cur[0] - cur[3]);
+    push(f[3], b, 0.0, 0.0, -b);
+  };
+  P.candidate = [&](const std::vector<double>& delta, double* step2, double* x2) {
+    *step2 = 0.0; *x2 = 0.0;
+    for (int a = 0; a < 4; ++a) { cand[a] = cur[a] + delta[a]; *step2 += delta[a] * delta[a]; *x2 += cur[a] * cur[a]; }
+    double f[4];
+    residuals(cand, f);
+    return 0.5 * (f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3]);
+  };
+  P.accept = [&]() { cur = cand; };
+  summary->num_residual_blocks = 4; summary->num_residuals = 4; summary->num_residuals_reduced = 4;
+  summary->num_parameter_blocks_reduced = 4; summary->num_parameters_reduced = 4; summary->num_effective_parameters_reduced = 4;
+  std::vector<sba_iteration_summary> rows;
+  const int rc = SolveDense(P, *o, summary, &rows);
+  if (trace && trace_n) { const int k = std::min<int>((int)rows.size(), trace_cap); for (int i = 0; i < k; ++i) trace[i] = rows[i]; *trace_n = k; }
+  for (int a = 0; a < 4; ++a) x[a] = cur[a];
   return rc;
 }
 

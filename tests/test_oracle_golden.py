@@ -138,3 +138,62 @@ def test_bilinear_known_answers(oracle):
     assert oracle.oracle_bilinear(fp, 11, 11, 5.5, 5.5, C.byref(ok)) == 0.25
     oracle.oracle_bilinear(fp, 11, 11, 10.5, 5.0, C.byref(ok))
     assert ok.value == 0  # x1 >= width is rejected, bitmap.cc:249-251
+
+
+# Ceres Solver's own documentation prints the iteration table of one solve: Powell's singular function
+# (docs/source/nnls_tutorial.rst, section "Powell's Function": f1 = x1 + 10 x2, f2 = sqrt(5) (x3 - x4), f3 = (x2 - 2 x3)^2,
+# f4 = sqrt(10) (x1 - x4)^2 from x = (3, -1, 0, 1); Solver::Options defaults, DENSE_QR, minimizer_progress_to_stdout).
+# Columns transcribed from that page: iter, cost, cost_change, |gradient| (max norm), |step|, tr_ratio, tr_radius.
+# No Ceres ran here -- the numbers are the published ones -- but 15 rows of 6 printed quantities leave no room for a
+# different trust-region loop: radius update, acceptance test, LM diagonal and its clamp, Jacobi scaling, termination.
+POWELL_TABLE = """
+   0  1.075000e+02    0.00e+00    1.55e+02   0.00e+00   0.00e+00  1.00e+04
+   1  5.036190e+00    1.02e+02    2.00e+01   2.16e+00   9.53e-01  3.00e+04
+   2  3.148168e-01    4.72e+00    2.50e+00   6.23e-01   9.37e-01  9.00e+04
+   3  1.967760e-02    2.95e-01    3.13e-01   3.08e-01   9.37e-01  2.70e+05
+   4  1.229900e-03    1.84e-02    3.91e-02   1.54e-01   9.37e-01  8.10e+05
+   5  7.687123e-05    1.15e-03    4.89e-03   7.69e-02   9.37e-01  2.43e+06
+   6  4.804625e-06    7.21e-05    6.11e-04   3.85e-02   9.37e-01  7.29e+06
+   7  3.003028e-07    4.50e-06    7.64e-05   1.92e-02   9.37e-01  2.19e+07
+   8  1.877006e-08    2.82e-07    9.54e-06   9.62e-03   9.37e-01  6.56e+07
+   9  1.173223e-09    1.76e-08    1.19e-06   4.81e-03   9.37e-01  1.97e+08
+  10  7.333425e-11    1.10e-09    1.49e-07   2.40e-03   9.37e-01  5.90e+08
+  11  4.584044e-12    6.88e-11    1.86e-08   1.20e-03   9.37e-01  1.77e+09
+  12  2.865573e-13    4.30e-12    2.33e-09   6.02e-04   9.37e-01  5.31e+09
+  13  1.791438e-14    2.69e-13    2.91e-10   3.01e-04   9.37e-01  1.59e+10
+  14  1.120029e-15    1.68e-14    3.64e-11   1.51e-04   9.37e-01  4.78e+10
+"""
+
+
+def _powell(sba, oracle, max_iterations):
+    o = sba.capi.default_solver_options()  # Solver::Options defaults of Ceres 2.1
+    o.max_num_iterations = max_iterations
+    o.function_tolerance, o.gradient_tolerance, o.parameter_tolerance = 1e-6, 1e-10, 1e-8
+    x = (C.c_double * 4)(3.0, -1.0, 0.0, 1.0)
+    s = sba.capi.Summary()
+    tr = (sba.capi.IterationSummary * 64)()
+    n = C.c_int32()
+    assert oracle.oracle_powell_solve(C.byref(o), x, C.byref(s), tr, 64, C.byref(n)) == 0
+    return s, [tr[i] for i in range(n.value)], list(x)
+
+
+def test_lm_loop_reproduces_the_iteration_table_ceres_publishes(sba, oracle):
+    """The trust-region loop of the oracle (oracle/dense_lm_oracle.cpp SolveDense -- the loop behind the semantic,
+    cylinder and rig solves, and equal to the Schur-eliminated loop of ba_oracle.cpp on bundle-adjustment problems,
+    tests/test_rig_solve.py) against the one LM trajectory Ceres documents, digit for digit as printed."""
+    s, trace, x = _powell(sba, oracle, 100)
+    want = [line.split() for line in POWELL_TABLE.strip().splitlines()]
+    assert len(trace) == len(want) == 15
+    for row, w in zip(trace, want):
+        got = ["%d" % row.iteration, "%.6e" % row.cost, "%.2e" % row.cost_change, "%.2e" % row.gradient_max_norm,
+               "%.2e" % row.step_norm, "%.2e" % row.relative_decrease, "%.2e" % row.trust_region_radius]
+        assert got == w, (got, w)
+    # "Gradient tolerance reached. Gradient max norm: 3.642190e-11 <= 1.000000e-10" and the final point of the report
+    assert s.termination_type == sba.capi.CONVERGENCE and "%.6e" % trace[-1].gradient_max_norm == "3.642190e-11"
+    assert ["%g" % v for v in x] == ["0.000146222", "-1.46222e-05", "2.40957e-05", "2.40957e-05"]
+    assert "%.6e" % s.initial_cost == "1.075000e+02" and "%.6e" % s.final_cost == "1.120029e-15"
+    assert (s.num_successful_steps, s.num_unsuccessful_steps) == (14, 0)
+    # the same page in the documentation of older releases stops one iteration earlier and prints that point
+    s13, trace13, x13 = _powell(sba, oracle, 13)
+    assert s13.termination_type == sba.capi.NO_CONVERGENCE and len(trace13) == 14
+    assert ["%g" % v for v in x13] == ["0.000292189", "-2.92189e-05", "4.79511e-05", "4.79511e-05"]
