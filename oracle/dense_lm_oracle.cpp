@@ -775,4 +775,30 @@ int oracle_powell_solve(const sba_solver_options* o, double* x, sba_summary* sum
   return rc;
 }
 
+// The other table of the same tutorial page ("Hello World!"): r = 10 - x from x = 0.5, one parameter.
+int oracle_helloworld_solve(const sba_solver_options* o, double* x, sba_summary* summary, sba_iteration_summary* trace,
+                            int32_t trace_cap, int32_t* trace_n) {
+  if (!o || !x || !summary) return SBA_ERR_INVALID_ARGUMENT;
+  std::memset(summary, 0, sizeof(*summary));
+  double cur = *x, cand = 0.0;
+  DenseProblem P;
+  P.n = 1;
+  P.rows = [&](std::vector<Row>* rows) {
+    rows->clear();
+    Row r;
+    r.n = 1; r.col[0] = 0; r.r = 10.0 - cur; r.j[0] = -1.0;
+    rows->push_back(r);
+  };
+  P.candidate = [&](const std::vector<double>& delta, double* step2, double* x2) {
+    cand = cur + delta[0]; *step2 = delta[0] * delta[0]; *x2 = cur * cur;
+    return 0.5 * (10.0 - cand) * (10.0 - cand);
+  };
+  P.accept = [&]() { cur = cand; };
+  std::vector<sba_iteration_summary> rows;
+  const int rc = SolveDense(P, *o, summary, &rows);
+  if (trace && trace_n) { const int k = std::min<int>((int)rows.size(), trace_cap); for (int i = 0; i < k; ++i) trace[i] = rows[i]; *trace_n = k; }
+  *x = cur;
+  return rc;
+}
+
 }  // extern "C"

@@ -65,6 +65,8 @@ def load(capi):
     lib.oracle_powell_solve.argtypes = [C.POINTER(capi.SolverOptions), C.POINTER(C.c_double), C.POINTER(capi.Summary),
                                         C.POINTER(capi.IterationSummary), C.c_int32, C.POINTER(C.c_int32)]
     lib.oracle_powell_solve.restype = C.c_int
+    lib.oracle_helloworld_solve.argtypes = lib.oracle_powell_solve.argtypes
+    lib.oracle_helloworld_solve.restype = C.c_int
     lib.oracle_draw_quadrilateral.argtypes = [dp, C.c_int, C.c_int, C.POINTER(C.c_uint8)]
     lib.oracle_cylinder_quadrilateral.argtypes = [dp, dp, dp, dp, dp, C.c_double, C.c_double, dp]
     lib.oracle_cylinder_quadrilateral.restype = C.c_int

@@ -197,3 +197,30 @@ def test_lm_loop_reproduces_the_iteration_table_ceres_publishes(sba, oracle):
     s13, trace13, x13 = _powell(sba, oracle, 13)
     assert s13.termination_type == sba.capi.NO_CONVERGENCE and len(trace13) == 14
     assert ["%g" % v for v in x13] == ["0.000292189", "-2.92189e-05", "4.79511e-05", "4.79511e-05"]
+
+
+HELLO_TABLE = """
+   0  4.512500e+01    0.00e+00    9.50e+00   0.00e+00   0.00e+00  1.00e+04
+   1  4.511598e-07    4.51e+01    9.50e-04   9.50e+00   1.00e+00  3.00e+04
+   2  5.012552e-16    4.51e-07    3.17e-08   9.50e-04   1.00e+00  9.00e+04
+"""
+
+
+def test_lm_loop_reproduces_the_hello_world_table(sba, oracle):
+    """The other iteration table of the same page (section "Hello World!": r = 10 - x from x = 0.5; the report prints
+    "x : 0.5 -> 10", final cost 5.012552e-16, CONVERGENCE): a full step with ratio 1 and the function-tolerance exit."""
+    o = sba.capi.default_solver_options()
+    o.max_num_iterations = 100
+    o.function_tolerance, o.gradient_tolerance, o.parameter_tolerance = 1e-6, 1e-10, 1e-8
+    x = (C.c_double * 1)(0.5)
+    s = sba.capi.Summary()
+    tr = (sba.capi.IterationSummary * 16)()
+    n = C.c_int32()
+    assert oracle.oracle_helloworld_solve(C.byref(o), x, C.byref(s), tr, 16, C.byref(n)) == 0
+    want = [line.split() for line in HELLO_TABLE.strip().splitlines()]
+    assert n.value == len(want)
+    for row, w in zip([tr[i] for i in range(n.value)], want):
+        got = ["%d" % row.iteration, "%.6e" % row.cost, "%.2e" % row.cost_change, "%.2e" % row.gradient_max_norm,
+               "%.2e" % row.step_norm, "%.2e" % row.relative_decrease, "%.2e" % row.trust_region_radius]
+        assert got == w, (got, w)
+    assert s.termination_type == sba.capi.CONVERGENCE and "%g" % x[0] == "10" and "%.6e" % s.final_cost == "5.012552e-16"
