@@ -227,3 +227,41 @@ def test_normalize_device_matches_oracle(sba, use_images):
     one_q, one_t = q[:1].copy(), t[:1].copy()
     assert sba.filters.device_normalize(one_q, one_t, np.ones(1, np.uint8), X.copy(), 10.0, 0.1, 0.9, True)[0] == 1.0
     assert np.array_equal(one_q, q[:1])
+
+
+def _replay_reference_normalize_test(normalize):
+    """TestNormalize of the reference, /root/reference/src/base/reconstruction_test.cc:230-286, statement by statement:
+    three images with identity rotation at tvec z = -10, 0, 10 (no 3-D points), normalised while unregistered, registered,
+    with another extent, with the full percentile range, and after four more images joined."""
+    q = np.tile([1.0, 0.0, 0.0, 0.0], (3, 1))
+    t = np.zeros((3, 3))
+    t[:, 2] = [-10.0, 0.0, 10.0]
+    pts = np.zeros((0, 3))
+    reg = np.zeros(3, np.uint8)
+    normalize(q, t, reg, pts, 10.0, 0.1, 0.9, True)                      # :237-243 nothing registered: untouched
+    assert np.allclose(t[:, 2], [-10, 0, 10], atol=1e-6)
+    reg[:] = 1
+    normalize(q, t, reg, pts, 10.0, 0.1, 0.9, True)                      # :244-250
+    assert np.allclose(t[:, 2], [-5, 0, 5], atol=1e-6)
+    normalize(q, t, reg, pts, 5.0, 0.1, 0.9, True)                       # :251-254
+    assert np.allclose(t[:, 2], [-2.5, 0, 2.5], atol=1e-6)
+    normalize(q, t, reg, pts, 10.0, 0.0, 1.0, True)                      # :255-258
+    assert np.allclose(t[:, 2], [-5, 0, 5], atol=1e-6)
+    normalize(q, t, reg, pts, 20.0, 0.1, 0.9, True)                      # :259
+    q = np.vstack([q, np.tile([1.0, 0.0, 0.0, 0.0], (4, 1))])           # :260-277 images 4..7
+    t = np.vstack([t, np.zeros((4, 3))])
+    t[3:, 2] = [-7.5, -5.0, 5.0, 7.5]
+    reg = np.ones(7, np.uint8)
+    normalize(q, t, reg, pts, 10.0, 0.0, 1.0, True)                      # :278-285
+    assert np.allclose(t[:, 2], [-5, 0, 5, -3.75, -2.5, 2.5, 3.75], atol=1e-6)
+    assert np.allclose(t[:, :2], 0.0, atol=1e-12) and np.allclose(q, [1, 0, 0, 0], atol=1e-12)
+
+
+def test_normalize_oracle_passes_the_reference_test():
+    from oracle import normalize_oracle as no
+    _replay_reference_normalize_test(no.normalize)
+
+
+@pytest.mark.gpu
+def test_normalize_device_passes_the_reference_test(sba):
+    _replay_reference_normalize_test(sba.filters.device_normalize)
