@@ -68,7 +68,11 @@ def AverageQuaternions(qvecs, weights):  # pose.cc:118-143: eigenvector of the l
         A += w * np.outer(q, q)
     A /= float(sum(weights))
     _, vec = np.linalg.eigh(A)  # ascending eigenvalues, as Eigen::SelfAdjointEigenSolver
-    return vec[:, 3].copy()
+    q = vec[:, 3].copy()
+    # an eigenvector's sign is the solver's choice: Eigen's returns the representative the reference's own test expects
+    # (pose_test.cc:188-226: w > 0 in every case); LAPACK's may return the other one -- the same rotation
+    k = int(np.flatnonzero(np.abs(q) > 0)[0])
+    return -q if q[k] < 0 else q
 
 
 class CameraRig:
