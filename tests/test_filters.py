@@ -265,3 +265,29 @@ def test_normalize_oracle_passes_the_reference_test():
 @pytest.mark.gpu
 def test_normalize_device_passes_the_reference_test(sba):
     _replay_reference_normalize_test(sba.filters.device_normalize)
+
+
+def test_error_and_depth_pass_the_reference_projection_tests(oracle):
+    """/root/reference/src/base/projection_test.cc:95-124 (TestCalculateSquaredReprojectionError, the (qvec, tvec) overloads),
+    :180-198 (TestCalculateDepth) and :200-222 (TestHasPointPositiveDepth) on the oracle's per-observation pass: identity
+    pose, SIMPLE_PINHOLE f = 1, c = (0, 0); a point's own projection has error exactly 0, the projection shifted by (1, 1)
+    has squared error 2 (1e-6 %), depths 0 / 0 / 1 / -1 and the positive-depth predicate !, !, ok, !."""
+    e, z = C.c_double(), C.c_double()
+    q, t = np.array([1.0, 0, 0, 0]), np.array([0.0, 0, 0])
+    cam = np.array([1.0, 0.0, 0.0] + [0.0] * 9)
+
+    def run(X, xy):
+        X, xy = np.ascontiguousarray(X, dtype=np.float64), np.ascontiguousarray(xy, dtype=np.float64)
+        oracle.oracle_observation_error(0, *[v.ctypes.data_as(dp) for v in (q, t, X, cam, xy)], C.byref(e), C.byref(z))
+        return e.value, z.value
+    rng = np.random.default_rng(3)
+    for _ in range(20):                                  # Eigen::Vector3d::Random().cwiseAbs()
+        X = np.abs(rng.uniform(-1, 1, 3)) + 1e-3
+        xy = X[:2] / X[2]
+        assert run(X, xy)[0] == 0.0                      # BOOST_CHECK_EQUAL(error1, 0)
+        assert abs(run(X, xy + 1)[0] - 2.0) <= 2.0 * 1e-8  # BOOST_CHECK_CLOSE(error3, 2, 1e-6): tolerance in percent
+    depths = [run(X, [0.0, 0.0])[1] for X in ([0.0, 0, 0], [0.0, 2, 0], [0.0, 0, 1], [0.0, 0, -1])]
+    assert depths == [0.0, 0.0, 1.0, -1.0]
+    assert [d >= np.finfo(np.float64).eps for d in depths] == [False, False, True, False]  # projection.cc:191-195
+    # a point that is not in front of the camera has the largest error (projection.cc:117-119)
+    assert run([0.0, 0, -1], [0.0, 0.0])[0] == np.finfo(np.float64).max and run([0.0, 2, 0], [0.0, 0.0])[0] == np.finfo(np.float64).max
