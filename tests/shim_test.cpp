@@ -375,6 +375,25 @@ static BundleAdjustmentConfig SemanticViews(int n) {
   return c;
 }
 
+// camera_rig_test.cc:288-330 (TestComputeAbsolutePose) on the mock's CameraRig -- the class the rig shim is tested with:
+// two rig cameras at relative translations (0,1,2) and (3,4,5), images at (0,0,0) and (3,3,3) -> rig pose (1,0,0,0), (0,-1,-2).
+static void TestMockCameraRig() {
+  sba_mock::CameraRig rig;
+  rig.AddCamera(0, {{1, 0, 0, 0}}, {{0, 1, 2}});
+  rig.AddCamera(1, {{1, 0, 0, 0}}, {{3, 4, 5}});
+  rig.AddSnapshot({0, 1});
+  Reconstruction rec;
+  for (camera_t c = 0; c < 2; ++c) { Camera cam; cam.SetCameraId(c); cam.SetModelId(SBA_PINHOLE); cam.Params() = {1, 1, 0.5, 0.5}; rec.AddCamera(cam); }
+  Image a; a.SetImageId(0); a.SetCameraId(0); a.Tvec() = {{0, 0, 0}}; rec.AddImage(a);
+  Image b; b.SetImageId(1); b.SetCameraId(1); b.Tvec() = {{3, 3, 3}}; rec.AddImage(b);
+  rig.SetRefCameraId(0);
+  rig.Check(rec);
+  Vector4d q; Vector3d t;
+  rig.ComputeAbsolutePose(0, rec, &q, &t);
+  CHECK_THAT(std::fabs(std::fabs(q[0]) - 1.0) < 1e-12 && std::fabs(q[1]) < 1e-12 && std::fabs(q[2]) < 1e-12 && std::fabs(q[3]) < 1e-12);
+  CHECK_THAT(t[0] == 0.0 && t[1] == -1.0 && t[2] == -2.0);
+}
+
 static void TestSemanticHost() {
   Reconstruction rec;
   std::vector<sba_shim::FloatMap> depth, label;
@@ -563,6 +582,7 @@ int main(int argc, char** argv) {
   const bool solve = argc > 1 && std::strcmp(argv[1], "solve") == 0;
   TestCounts();
   TestFlattenOrder();
+  TestMockCameraRig();
   TestSemanticHost();
   if (solve) {
     if (sba_device_count() < 1) {
