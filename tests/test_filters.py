@@ -291,3 +291,72 @@ def test_error_and_depth_pass_the_reference_projection_tests(oracle):
     assert [d >= np.finfo(np.float64).eps for d in depths] == [False, False, True, False]  # projection.cc:191-195
     # a point that is not in front of the camera has the largest error (projection.cc:117-119)
     assert run([0.0, 0, -1], [0.0, 0.0])[0] == np.finfo(np.float64).max and run([0.0, 2, 0], [0.0, 0.0])[0] == np.finfo(np.float64).max
+
+
+def _reference_test_reconstruction(sba, num_images):
+    """GenerateReconstruction of reconstruction_test.cc:42-66: one PINHOLE camera (f = 1 on a 1 x 1 image: params
+    1, 1, 0.5, 0.5), identity poses, ten features at (0, 0) per image."""
+    rec = sba.Reconstruction()
+    rec.AddCamera(sba.Camera(1, "PINHOLE", [1.0, 1.0, 0.5, 0.5], 1, 1))
+    for i in range(1, num_images + 1):
+        im = sba.Image(i, 1, [1.0, 0, 0, 0], [0.0, 0, 0], name="image%d" % i)
+        im.points2D = [sba.Point2D(np.zeros(2)) for _ in range(10)]
+        rec.AddImage(im)
+    return rec
+
+
+def _add_observation(rec, pid, image_id, idx):  # Reconstruction::AddObservation, reconstruction.cc:326-339
+    rec.Point3D(pid).track.AddElement(image_id, idx)
+    rec.Image(image_id).points2D[idx].point3D_id = pid
+
+
+def test_negative_depth_filter_passes_the_reference_test(sba, oracle):
+    """TestFilterObservationsWithNegativeDepth, reconstruction_test.cc:510-532, statement by statement."""
+    fl = sba.filters
+    fn = oracle_errors(oracle)
+    rec = _reference_test_reconstruction(sba, 2)
+    pid = rec.AddPoint3D([0.0, 0.0, 1.0], [])
+    for z in (1.0, 0.001, 0.0):                      # no observation yet: nothing can be filtered
+        rec.Point3D(pid).xyz[2] = z
+        fl.filter_observations_with_negative_depth(rec, errors_fn=fn)
+        assert len(rec.points3D) == 1
+    _add_observation(rec, pid, 1, 0)
+    rec.Point3D(pid).xyz[2] = 0.001
+    fl.filter_observations_with_negative_depth(rec, errors_fn=fn)
+    assert len(rec.points3D) == 1
+    rec.Point3D(pid).xyz[2] = 0.0                    # in the image plane: not in front of the camera
+    fl.filter_observations_with_negative_depth(rec, errors_fn=fn)
+    assert len(rec.points3D) == 0 and not rec.Image(1).points2D[0].HasPoint3D()
+
+
+@pytest.mark.parametrize("all_points", [False, True])
+def test_reprojection_filter_passes_the_reference_tests(sba, oracle, all_points):
+    """The reprojection-error half of TestFilterPoints3D / TestFilterAllPoints (reconstruction_test.cc:394-435, 479-508;
+    the statements with min_tri_angle = 0, where FilterPoints3D is FilterPoints3DWithLargeReprojectionError followed by
+    an angle filter that deletes nothing a two-view point has): points without a pair of observations go, a point whose
+    projection error is 0.1 px stays at max_reproj_error 0.1 and goes at 0.09."""
+    fl = sba.filters
+    fn = oracle_errors(oracle)
+    rng = np.random.default_rng(1)
+
+    def run(max_err, ids):
+        fl.filter_points3D_with_large_reprojection_error(rec, max_err, point3D_ids=None if all_points else ids, errors_fn=fn)
+        return len(rec.points3D)
+    rec = _reference_test_reconstruction(sba, 2)
+    p1 = rec.AddPoint3D(rng.uniform(-1, 1, 3), [])
+    if not all_points:
+        assert run(0.0, []) == 1 and run(0.0, [p1 + 1]) == 1   # no id / an id that does not exist
+    assert run(0.0, [p1]) == 0                                 # no observation
+    p2 = rec.AddPoint3D(rng.uniform(-1, 1, 3), [])
+    _add_observation(rec, p2, 1, 0)
+    assert run(0.0, [p2]) == 0                                 # one observation
+    p3 = rec.AddPoint3D([-0.5, -0.5, 1.0], [])
+    _add_observation(rec, p3, 1, 0)
+    _add_observation(rec, p3, 2, 0)
+    assert run(0.0, [p3]) == 1                                 # projects onto its features: error 0 is not > 0
+    fl.delete_point3D(rec, p3)                                 # (the reference's next statement removes it by triangulation angle)
+    p4 = rec.AddPoint3D([-0.6, -0.5, 1.0], [])
+    _add_observation(rec, p4, 1, 0)
+    _add_observation(rec, p4, 2, 0)
+    assert run(0.1, [p4]) == 1
+    assert run(0.09, [p4]) == 0
