@@ -96,3 +96,15 @@ def test_camera_rig_compute_absolute_pose(sba):  # camera_rig_test.cc:288-330
     twice.SetRefCameraId(0)
     with pytest.raises(ValueError):
         twice.Check(rec)
+
+
+def test_camera_param_idxs(sba):  # camera_test.cc:130-138, 254-256: group sizes of FULL_OPENCV and SIMPLE_PINHOLE
+    cam = sba.Camera(1, "FULL_OPENCV", [1.0] * 12, 1, 1)
+    assert (len(cam.FocalLengthIdxs()), len(cam.PrincipalPointIdxs()), len(cam.ExtraParamsIdxs())) == (2, 2, 8)
+    cam = sba.Camera(1, "SIMPLE_PINHOLE", [1.0, 0.5, 0.5], 1, 1)
+    assert (len(cam.FocalLengthIdxs()), len(cam.PrincipalPointIdxs()), len(cam.ExtraParamsIdxs())) == (1, 2, 0)
+    # every parameter of every model belongs to exactly one group (camera_models.h:189-349)
+    for mid, n in sba.capi.MODEL_NUM_PARAMS.items() if isinstance(sba.capi.MODEL_NUM_PARAMS, dict) else enumerate(sba.capi.MODEL_NUM_PARAMS):
+        cam = sba.Camera(1, int(mid), [1.0] * int(n), 1, 1)
+        groups = list(cam.FocalLengthIdxs()) + list(cam.PrincipalPointIdxs()) + list(cam.ExtraParamsIdxs())
+        assert sorted(groups) == list(range(int(n)))
