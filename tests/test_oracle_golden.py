@@ -224,3 +224,34 @@ def test_lm_loop_reproduces_the_hello_world_table(sba, oracle):
                "%.2e" % row.step_norm, "%.2e" % row.relative_decrease, "%.2e" % row.trust_region_radius]
         assert got == w, (got, w)
     assert s.termination_type == sba.capi.CONVERGENCE and "%g" % x[0] == "10" and "%.6e" % s.final_cost == "5.012552e-16"
+
+
+@pytest.mark.parametrize("loss,scale", [(1, 1.0), (1, 0.7), (2, 1.0), (2, 2.5)])
+def test_loss_and_corrector_against_the_published_definitions(sba, oracle, loss, scale):
+    """Ceres' documentation defines the losses this path uses (nnls_modeling, "Instances": SoftLOneLoss rho(s) = 2 (sqrt(1 + s) - 1),
+    CauchyLoss rho(s) = log(1 + s), each scaled as a^2 rho(s / a^2)) and the corrector (corrector.h: residual and Jacobian
+    are scaled so that the Gauss-Newton model of 1/2 rho(|r|^2) has gradient rho' J^T r; with rho'' <= 0 -- both losses
+    are concave -- the correction is the plain sqrt(rho') scaling).  In 50-digit arithmetic from the raw residuals:
+    cost = 1/2 sum rho(s), corrected rows = sqrt(rho'(s)) x raw rows, and J_c^T r_c = rho' J^T r per block."""
+    from mpmath import mp, mpf, sqrt as msqrt, log as mlog
+    from util import oracle_evaluate
+    mp.dps = 50
+    prob, _ = sba.scene.make_scene(n_cam=4, n_pt=60, mean_track=3.0, model="SIMPLE_RADIAL", refine_intr=True, seed=6)
+    raw = oracle_evaluate(oracle, sba.capi, prob, loss, scale, apply_loss=False)
+    cor = oracle_evaluate(oracle, sba.capi, prob, loss, scale, apply_loss=True)
+    a2 = mpf(scale) ** 2
+    total = mpf(0)
+    for k in range(prob.num_observations):
+        s = mpf(float(raw["r"][k, 0])) ** 2 + mpf(float(raw["r"][k, 1])) ** 2
+        if loss == 1:
+            rho, d1 = 2 * a2 * (msqrt(1 + s / a2) - 1), 1 / msqrt(1 + s / a2)
+        else:
+            rho, d1 = a2 * mlog(1 + s / a2), 1 / (1 + s / a2)
+        total += rho / 2
+        w = float(msqrt(d1))
+        assert np.allclose(cor["r"][k], w * raw["r"][k], rtol=1e-13, atol=0)
+        for blk in ("pose", "intr", "point"):
+            assert np.allclose(cor[blk][k], w * raw[blk][k], rtol=1e-13, atol=1e-300)
+            assert np.allclose(cor[blk][k].T @ cor["r"][k], float(d1) * (raw[blk][k].T @ raw["r"][k]), rtol=1e-12, atol=1e-12)
+    assert abs(cor["cost"] - float(total)) <= 1e-13 * float(total) and abs(raw["cost"] - float(total)) <= 1e-13 * float(total)
+    assert float(total) < 0.5 * float(np.sum(raw["r"] ** 2)) or scale > 2  # the loss does damp these residuals
