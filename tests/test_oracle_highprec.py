@@ -207,3 +207,42 @@ def test_rig_jets_against_fifty_digit_arithmetic(oracle, model, params):
         assert abs(r[0] - float(r_hp[0])) <= 2e-13 * max(1.0, abs(float(r_hp[0])))
         assert np.allclose(J[:, :17 + P], J_hp, rtol=2e-13, atol=2e-13 * scale), (model, np.abs(J[:, :17 + P] - J_hp).max())
         assert not J[:, 17 + P:].any()
+
+
+def test_pose_tangent_jacobian_is_the_derivative_along_the_quaternion_manifold(sba, oracle):
+    """ceres::QuaternionManifold (manifold.h; SURVEY.md App. A.1): Plus(x, d) = [cos|d|, sin|d| / |d| d] (x) x.  The pose
+    block the oracle hands to the solver is 2 x 6 in the tangent layout (rotation increment, translation): its first three
+    columns must be d r(Plus(q, d)) / d d at d = 0, taken here at 50 digits through the third writing of the functor."""
+    from mpmath import cos as mcos, sin as msin
+    from util import oracle_evaluate
+    prob, _ = sba.scene.make_scene(n_cam=3, n_pt=12, mean_track=3.0, model="SIMPLE_RADIAL", refine_intr=True, seed=11)
+    ev = oracle_evaluate(oracle, sba.capi, prob, 0, 1.0, apply_loss=False, qvec=True)
+    P = 4
+
+    def plus(q, d):
+        n = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2])
+        if n == 0:
+            return q
+        s = msin(n) / n
+        return quat_product((mcos(n), s * d[0], s * d[1], s * d[2]), q)
+    h = mpf("1e-25")
+    checked = 0
+    for k in range(0, prob.num_observations, 5):
+        i, pt = int(prob.obs_image[k]), int(prob.obs_point[k])
+        c = int(prob.image_camera[i])
+        if prob.image_pose_constant[i]:
+            continue
+        checked += 1
+        q = [mpf(float(v)) for v in prob.image_qvec[i]]
+        rest = [mpf(float(v)) for v in list(prob.image_tvec[i]) + list(prob.points[pt]) + list(prob.camera_params[c][:P])]
+        xy = (mpf(float(prob.obs_xy[k, 0])), mpf(float(prob.obs_xy[k, 1])))
+        J_hp = np.zeros((2, 3))
+        for j in range(3):
+            dplus, dminus = [mpf(0)] * 3, [mpf(0)] * 3
+            dplus[j], dminus[j] = h, -h
+            a = residual(2, list(plus(q, dplus)) + rest, P, xy)
+            b = residual(2, list(plus(q, dminus)) + rest, P, xy)
+            J_hp[0, j], J_hp[1, j] = float((a[0] - b[0]) / (2 * h)), float((a[1] - b[1]) / (2 * h))
+        scale = max(1.0, float(np.abs(J_hp).max()))
+        assert np.allclose(ev["pose"][k][:, :3], J_hp, rtol=1e-12, atol=1e-12 * scale), (k, ev["pose"][k][:, :3], J_hp)
+    assert checked >= 3
