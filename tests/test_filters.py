@@ -360,3 +360,11 @@ def test_reprojection_filter_passes_the_reference_tests(sba, oracle, all_points)
     _add_observation(rec, p4, 2, 0)
     assert run(0.1, [p4]) == 1
     assert run(0.09, [p4]) == 0
+
+
+def test_bounds_and_centroid_pass_the_reference_test():
+    """TestComputeBoundsAndCentroid, reconstruction_test.cc:288-319: points (3,0,0), (0,3,0), (0,0,3) over the full
+    percentile range have centroid (1,1,1) and bounding box (0,0,0) - (3,3,3)."""
+    from oracle import normalize_oracle as no
+    lo, hi, mean = no.bounds_and_centroid(np.array([[3.0, 0, 0], [0, 3.0, 0], [0, 0, 3.0]]), 0.0, 1.0)
+    assert np.allclose(mean, 1.0, atol=1e-6) and np.allclose(lo, 0.0, atol=1e-6) and np.allclose(hi, 3.0, atol=1e-6)
