@@ -8,7 +8,7 @@
 // but hands the arithmetic to libsba_b200.so through the C ABI of include/sba_b200.h instead of
 // building a ceres::Problem.  Everything below is host integer work: walking the containers in the
 // reference's residual order (SetUp, bundle_adjustment.cc:326-342) and packing plain arrays.  At the headline size
-// (1778 images / 1 M points / 5 M observations) Flatten takes 0.2-0.35 s on one host core (tools/shim_flatten_bench.cpp;
+// (1778 images / 1 M points / 5 M observations) Flatten takes 0.17-0.35 s on one host core (tools/shim_flatten_bench.cpp;
 // 1.1 s with two hash lookups per observation), against 33 ms for everything from sba_create to the read-back.
 //
 // The adjuster is a template over the Reconstruction type.  It only uses the accessor contract
