@@ -73,7 +73,7 @@ class FlatProblem:
         d.obs_image = capi.ptr(self.obs_image, capi._ip)
         d.obs_point = capi.ptr(self.obs_point, capi._ip)
         d.obs_xy = capi.ptr(self.obs_xy, capi._dp)
-        if self.sem_maps is not None and not with_maps:
+        if not with_maps:
             d.sem_weight = self.sem_weight  # the maps themselves are already on the device (ResidentMaps)
         elif self.sem_maps is not None:
             d.sem_maps = capi.ptr(self.sem_maps, capi._fp)
