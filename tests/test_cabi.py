@@ -187,3 +187,24 @@ def test_resident_maps_need_a_device(sba):
     assert e.value.code == sba.capi.ERR_NO_DEVICE
     with pytest.raises(ValueError):
         sba.ResidentMaps(np.zeros((4, 4), np.float32))
+
+
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: include/sba_b200.h must compile as C99 (what cgo / JNI / a C caller sees), warnings as errors,
+    and a C translation unit must link against the library."""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no C compiler")
+    src = tmp_path / "abi.c"
+    src.write_text('#include <stdio.h>\n#include "sba_b200.h"\n'
+                   'int main(void) { sba_solver_options o; sba_default_solver_options(&o);\n'
+                   '  printf("%s %d %d\\n", sba_version(), (int)sizeof(sba_problem_desc), o.max_num_iterations); return 0; }\n')
+    pkg = os.path.join(root, "semantic-bundle-adjustment-colmap_b200")
+    exe = tmp_path / "abi"
+    subprocess.check_call([gcc, "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I" + os.path.join(root, "include"), str(src),
+                           "-o", str(exe), "-L" + pkg, "-lsba_b200", "-Wl,-rpath," + pkg])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.startswith("sba_b200"), out.stdout + out.stderr
