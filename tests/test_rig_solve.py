@@ -179,3 +179,44 @@ def test_rig_bundle_adjuster_mirror(sba, oracle):
     s0 = sba.capi.Summary(); n0 = C.c_int32()
     o = ba.SolverOptions()
     assert sba.capi.load().sba_rig_solve(C.byref(d), C.byref(o), C.cast(None, sba.capi.ITERATION_CALLBACK), None, C.byref(s0), None, 0, C.byref(n0)) == sba.capi.ERR_EMPTY_PROBLEM
+
+
+@pytest.mark.parametrize("loss,perturb,refine_focal", [(0, 0.15, True), (2, 0.15, True), (1, 0.3, False), (0, 0.5, True)])
+def test_dense_and_schur_loops_of_the_oracle_agree_row_for_row(sba, oracle, loss, perturb, refine_focal):
+    """The link of the pinning chain between the LM loop held to Ceres' published table (SolveDense, reached here through
+    oracle_rig_solve with no rigs: dense normal equations over ALL blocks) and the Schur-eliminated loop of ba_oracle.cpp
+    that the device's bundle-adjustment solves follow: on perturbed scenes -- far enough that steps are REJECTED and the
+    radius shrinks -- with the trivial and both robust losses, every row of the two iteration tables agrees: accepted /
+    rejected, cost to 1e-8, trust-region radius to 1e-8."""
+    ra = sba.rig_adjuster
+    rec = generate_reconstruction(sba, 4, 50, seed=5)
+    rng = np.random.default_rng(8)
+    for im in rec.images.values():
+        im.tvec = np.asarray(im.tvec) + rng.normal(0, perturb, 3)
+        im.qvec = ra.NormalizeQuaternion(np.asarray(im.qvec) + rng.normal(0, 0.05 * perturb, 4))
+    for p in rec.points3D.values():
+        p.xyz = np.asarray(p.xyz) + rng.normal(0, perturb, 3)
+    config = sba.BundleAdjustmentConfig()
+    for i in range(4):
+        config.AddImage(i)
+    config.SetConstantPose(0)
+    config.SetConstantTvec(1, [0])
+    opts = sba.BundleAdjustmentOptions()
+    opts.loss_function_type = loss
+    opts.refine_focal_length = refine_focal
+    ba_ref = sba.BundleAdjuster(opts, config)
+    flat = ba_ref.Flatten(copy.deepcopy(rec))
+    o = ba_ref.SolverOptions()
+    o.max_num_iterations = 12
+    o.linear_solver_type = sba.capi.DENSE_SCHUR
+    rc, s_ref, tr_ref, _ = oracle_solve(oracle, sba.capi, flat, o)
+    assert rc == 0
+    f = ra.RigBundleAdjuster(opts, ra.RigBundleAdjusterOptions(), config).Flatten(copy.deepcopy(rec), [], errors_fn=oracle_errors(oracle))
+    rc, s, tr, g = run_oracle(sba, oracle, f, o)
+    assert rc == 0 and len(tr) == len(tr_ref) and s.termination_type == s_ref.termination_type
+    for a, b in zip(tr, tr_ref):
+        assert a.step_is_successful == b.step_is_successful and a.step_is_valid == b.step_is_valid
+        assert abs(a.cost - b.cost) <= 1e-8 * b.cost, (a.iteration, a.cost, b.cost)
+        assert abs(a.trust_region_radius - b.trust_region_radius) <= 1e-8 * b.trust_region_radius
+    if perturb >= 0.3:
+        assert any(not r.step_is_successful for r in tr_ref[1:]), "the scene was meant to produce rejected steps"
