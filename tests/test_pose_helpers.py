@@ -108,3 +108,18 @@ def test_camera_param_idxs(sba):  # camera_test.cc:130-138, 254-256: group sizes
         cam = sba.Camera(1, int(mid), [1.0] * int(n), 1, 1)
         groups = list(cam.FocalLengthIdxs()) + list(cam.PrincipalPointIdxs()) + list(cam.ExtraParamsIdxs())
         assert sorted(groups) == list(range(int(n)))
+
+
+def test_normalize_quaternion(sba):  # pose_test.cc:121-136, on the helper and on Image::NormalizeQvec of the mirror
+    ra = sba.rig_adjuster
+    half = np.sqrt(2) / 2
+
+    def through_image(q):
+        im = sba.Image(1, 1, q, [0.0, 0, 0])
+        im.NormalizeQvec()
+        return np.asarray(im.Qvec())
+    for fn in (ra.NormalizeQuaternion, through_image):
+        for q in (I, [2.0, 0, 0, 0], [0.5, 0, 0, 0], [0.0, 0, 0, 0]):
+            assert np.array_equal(fn(np.array(q)), I)
+        assert np.allclose(fn(np.array([1.0, 1, 0, 0])), [half, half, 0, 0], rtol=0, atol=1e-15)
+        assert np.allclose(fn(np.array([0.5, 0.5, 0, 0])), [half, half, 0, 0], rtol=0, atol=1e-15)
