@@ -325,6 +325,21 @@ def e2e_rate(new_solver, o, steps, warmup, barrier=lambda: None):
     return total, ph, out
 
 
+def host_flatten(prob):
+    """Host side of the drop-in, measured beside the device path: the C++ shim's Flatten (shim/sba_bundle_adjuster.h) over a mock
+    Reconstruction of the workload's size -- what a COLMAP caller pays before sba_create sees an array.  Built by build();
+    None when the helper is missing or fails (it is a report, not part of any timed region)."""
+    exe = os.path.join(ROOT, "tools", "shim_flatten_bench.bin")
+    try:
+        out = subprocess.run([exe, str(len(prob.image_camera)), str(len(prob.points)), "--json"], capture_output=True, text=True, timeout=180)
+        d = json.loads(out.stdout.strip().splitlines()[-1])
+        d["what"] = ("BundleAdjusterT::Flatten over a mock Reconstruction of this many images / points (mean track 5.03), one host "
+                     "thread, median / min / max of 3; not included in e2e")
+        return d
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": str(e)[:200]}
+
+
 def io_bytes(prob, out):
     h2d = int(prob.image_qvec.nbytes + prob.image_tvec.nbytes + prob.camera_params.nbytes + prob.points.nbytes +
               prob.obs_xy.nbytes + prob.obs_image.nbytes + prob.obs_point.nbytes +
@@ -457,6 +472,7 @@ def run_b200(args, m):
                          "ms_per_step": pg_s / e2e_steps * 1e3, "steps": e2e_steps,
                          "host_memory": "pageable numpy arrays (a COLMAP caller's std::vector)", "phases_ms": pg_phases},
         "e2e_maps_resident": e2e_resident_maps,
+        "host_flatten": host_flatten(prob) if (rank == 0 and world == 1) else None,
         "roofline": roof, "stages": table, "final_cost": summ.final_cost,
         # per-stage device time of the LAST timed solve (CUDA events between the stages; all zero when the iteration
         # replays as a CUDA graph -- run with SBA_NO_GRAPHS=1 to fill them)

@@ -5,7 +5,10 @@
 //       -Lsemantic-bundle-adjustment-colmap_b200 -lsba_b200 -Wl,-rpath,$PWD/semantic-bundle-adjustment-colmap_b200 -o /tmp/flatten_bench
 #include <chrono>
 #include <cstdio>
+#include <algorithm>
 #include <random>
+#include <string>
+#include <vector>
 
 #include "mock_reconstruction.h"
 #include "sba_bundle_adjuster.h"
@@ -47,11 +50,22 @@ int main(int argc, char** argv) {
   config.SetConstantPose(1);
   config.SetConstantTvec(2, {0});
   sba_shim::BundleAdjustmentOptions options;
+  const bool json = argc > 3 && std::string(argv[3]) == "--json";
+  std::vector<double> ms;
   for (int rep = 0; rep < 3; ++rep) {
     sba_shim::BundleAdjusterT<Reconstruction> ba(options, config);
     const double t0 = Now();
     const auto& flat = ba.Flatten(&rec);
     const double t1 = Now();
+    ms.push_back((t1 - t0) * 1e3);
+    if (json) {
+      if (rep == 2) {
+        std::sort(ms.begin(), ms.end());
+        std::printf("{\"flatten_ms\": %.2f, \"flatten_ms_min\": %.2f, \"flatten_ms_max\": %.2f, \"observations\": %zu, \"points\": %zu, \"images\": %zu}\n",
+                    ms[1], ms[0], ms[2], flat.obs_image.size(), flat.point_ids.size(), flat.image_ids.size());
+      }
+      continue;
+    }
     std::printf("Flatten: %zu observations, %zu points, %zu images in %.1f ms\n", flat.obs_image.size(), flat.point_ids.size(),
                 flat.image_ids.size(), (t1 - t0) * 1e3);
     std::printf("         observations %.1f ms, extra track elements %.1f ms, parameter packing %.1f ms\n", ba.FlattenPhaseMs()[0],
