@@ -35,3 +35,15 @@ def test_shim_solve_on_device(shim_exe):
     assert out.returncode == 0, out.stdout + out.stderr
     assert "two_view: cost" in out.stdout and "semantic: cost" in out.stdout and "cylinder: cost" in out.stdout
     assert "refine_absolute_pose: cost" in out.stdout and out.stdout.count("rig ") == 4
+
+
+def test_flatten_bench_helper_reports_json(sba):
+    """tools/shim_flatten_bench.bin (built by __graft_entry__.build()) -- the helper behind bench.py's `host_flatten` key."""
+    import json
+    exe = os.path.join(ROOT, "tools", "shim_flatten_bench.bin")
+    if not os.path.exists(exe):
+        pytest.skip("helper not built (run __graft_entry__.build())")
+    out = subprocess.run([exe, "20", "3000", "--json"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    d = json.loads(out.stdout.strip().splitlines()[-1])
+    assert d["images"] == 20 and d["points"] == 3000 and d["observations"] > 2 * 3000 and d["flatten_ms"] > 0
